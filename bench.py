@@ -1,0 +1,325 @@
+"""Headline benchmark: candidate-fold fits/sec of the (candidate x CV-fold) sweep.
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl b200|reference]
+
+Workload (BASELINE.json configs[1]): GridSearchCV(LogisticRegression lbfgs, 64 C
+values = logspace(-6, 2, 64), cv=5) on synthetic binary 1M x 256 fp32 (seed 2,
+SURVEY.md 8d).  A "step" is one whole sweep: all 64*5 = 320 fits trained and scored.
+X (1.024 GB) is larger than the 126 MB L2, so no flush is needed between steps.
+N > 1 (torchrun, one rank per GPU): weak scaling by candidate blocks -- the grid
+grows to 64*N values of C over the same range, rank r owns candidates r, r+N, ...;
+X is replicated, there is no data-path collective, rank 0 gathers the scores.
+
+One JSON line is printed by rank 0 (see README / the driver contract).
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+N_ROWS, N_FEAT, N_CAND, CV, SEED = 1_000_000, 256, 64, 5, 2
+METRIC, UNIT = "candidate_fold_fits_per_sec", "fits/s"
+
+
+def parse():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--rows", type=int, default=N_ROWS)       # smaller sizes are for debugging only
+    ap.add_argument("--features", type=int, default=N_FEAT)
+    ap.add_argument("--candidates", type=int, default=N_CAND)
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--tc", type=int, default=-1, help="use_tensor_cores flag passed to the library")
+    return ap.parse_args()
+
+
+def workload_name(a, n_cand_total):
+    return (f"GridSearchCV(LogisticRegression lbfgs, {n_cand_total} C values logspace(-6,2), cv={CV}) on synthetic "
+            f"binary {a.rows}x{a.features} fp32 (seed {SEED})")
+
+
+# ------------------------------------------------------------------------------------------
+class ClockSampler(threading.Thread):
+    """nvidia-smi clocks / throttle reasons during the timed region (B200_PROFILING.md recipe)."""
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, gpu_index: int):
+        super().__init__(daemon=True)
+        self.gpu_index, self.stop_ev, self.rows = gpu_index, threading.Event(), []
+
+    def run(self):
+        while not self.stop_ev.is_set():
+            try:
+                out = subprocess.run(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
+                                      "-i", str(self.gpu_index)], capture_output=True, text=True, timeout=5).stdout
+                for line in out.strip().splitlines():
+                    self.rows.append([c.strip() for c in line.split(",")])
+            except Exception:
+                pass
+            self.stop_ev.wait(0.2)
+
+    def summary(self):
+        self.stop_ev.set()
+        self.join(timeout=6)
+        sm, mx, reasons = [], [], set()
+        for r in self.rows:
+            try:
+                sm.append(float(r[1])); mx.append(float(r[2]))
+            except Exception:
+                continue
+            for name, col in (("hw_slowdown", 5), ("hw_thermal_slowdown", 6), ("sw_thermal_slowdown", 7),
+                              ("sw_power_cap", 8)):
+                if len(r) > col and r[col].lower().startswith("active"):
+                    reasons.add(name)
+        sm.sort()
+        # "under load" = samples in the upper half (idle samples between steps excluded)
+        load = sm[len(sm) // 2:] if sm else []
+        return {"sm_mhz": float(np.median(load)) if load else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": sorted(reasons), "samples": len(sm)}
+
+
+def measured_peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        d = json.load(open(p))
+        return d, "measured"
+    return {"hbm_gbs": 6650.0, "bf16_tflops": 1590.0, "bf16_tflops_sustained": 1400.0}, "fallback"
+
+
+def measure_tf32_peak(torch):
+    """cuBLAS TF32 GEMM 8192^3, best of 10 (same method as MEASURED_PEAKS.json uses for bf16)."""
+    old = torch.backends.cuda.matmul.allow_tf32
+    torch.backends.cuda.matmul.allow_tf32 = True
+    try:
+        a = torch.randn(8192, 8192, device="cuda"); b = torch.randn(8192, 8192, device="cuda")
+        for _ in range(3):
+            a @ b
+        best = 1e9
+        for _ in range(10):
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record(); a @ b; e1.record(); torch.cuda.synchronize()
+            best = min(best, e0.elapsed_time(e1))
+        return 2 * 8192 ** 3 / (best * 1e-3) / 1e12
+    finally:
+        torch.backends.cuda.matmul.allow_tf32 = old
+
+
+# ------------------------------------------------------------------------------------------
+def cpu_reference_step(X, y, Cs, n_jobs):
+    """The reference's CPU implementation of the path on host cores: the worker's call
+    sequence (oracle.reference_path, aws-prod/worker/worker.py:315-326) for the given
+    candidates.  n_jobs > 1 spreads candidates over processes (one sklearn worker each,
+    like the reference's 4 worker containers, docker-compose.yml:133-199)."""
+    from joblib import Parallel, delayed
+    from oracle import reference_path as rp
+    t0 = time.perf_counter()
+    if n_jobs == 1 or len(Cs) == 1:
+        for C in Cs:
+            rp.cv_fits("LogisticRegression", {"C": float(C)}, X, y, CV)
+    else:
+        Parallel(n_jobs=min(n_jobs, len(Cs)))(
+            delayed(rp.cv_fits)("LogisticRegression", {"C": float(C)}, X, y, CV) for C in Cs)
+    return time.perf_counter() - t0
+
+
+def run_reference(a):
+    """--impl reference: sklearn on the box's host cores, bounded sample per step."""
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    from cs230_distributed_machine_learning_b200 import make_dataset
+    cores = os.cpu_count() or 1
+    X, y = make_dataset("binary", a.rows, a.features, seed=SEED)
+    Cs_all = np.logspace(-6, 2, a.candidates * a.gpus)
+    # calibrate on one candidate (5 fits, BLAS on all cores), then size the step to ~8 s
+    t1 = cpu_reference_step(X, y, Cs_all[len(Cs_all) // 2:len(Cs_all) // 2 + 1], 1)
+    workers = max(1, min(cores // 4, 16))          # processes, each with its BLAS threads
+    per_step = max(1, min(len(Cs_all), int(8.0 / max(t1, 1e-3) * max(1, workers // 2))))
+    sample = Cs_all[np.linspace(0, len(Cs_all) - 1, per_step).astype(int)]
+    for _ in range(a.warmup):
+        cpu_reference_step(X, y, sample[:1], 1)
+    t = 0.0
+    for _ in range(a.steps):
+        t += cpu_reference_step(X, y, sample, workers if per_step > 1 else 1)
+    fits = per_step * CV * a.steps
+    v = fits / t
+    sample_txt = (f"{per_step} of {len(Cs_all)} candidates x {CV} folds per step at full n={a.rows}, "
+                  f"{workers if per_step > 1 else 1} process(es), BLAS threads left at default")
+    print(json.dumps({
+        "impl": "reference", "metric": METRIC, "value": v, "unit": UNIT, "n_gpus": a.gpus, "steps": a.steps,
+        "warmup": a.warmup, "ms_per_step": t / a.steps * 1e3, "higher_is_better": True, "scaling": "weak",
+        "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": {"workload": workload_name(a, len(Cs_all)), "l2": "inputs larger than L2"},
+        "cpu_baseline": {"value": v, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample_txt},
+        "e2e": {"value": v, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0}))
+
+
+# ------------------------------------------------------------------------------------------
+def run_b200(a):
+    import torch
+    import torch.distributed as dist
+    from cs230_distributed_machine_learning_b200 import dist as ddist
+    from cs230_distributed_machine_learning_b200 import folds, make_dataset, register_dataset
+    from cs230_distributed_machine_learning_b200.solver import SweepSolver
+
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise RuntimeError("bench.py --impl b200 needs a B200; there is no CPU fallback")
+    torch.cuda.set_device(local_rank)
+    dev = torch.device("cuda", local_rank)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+    n_cand_total = a.candidates * world
+    Cs_all = np.logspace(-6, 2, n_cand_total)
+    mine = ddist.candidate_indices(n_cand_total, world, rank)
+    Cs = Cs_all[mine]
+
+    X, y = make_dataset("binary", a.rows, a.features, seed=SEED)   # identical bytes on every rank
+    fold = folds.stratified_labels(y, CV)
+    solver = SweepSolver(local_rank)
+    ds = solver.upload_dataset(X, y, classifier=True)
+    fold_d = solver.to_device(fold, torch.int8)
+    n = len(Cs)
+    args = dict(tol=[1e-4] * n, fit_intercept=[True] * n, max_iter=[100] * n)
+
+    def step():
+        return solver.logreg_sweep(ds, fold_d, CV, Cs, args["tol"], args["fit_intercept"], args["max_iter"],
+                                   use_tensor_cores=a.tc)
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    for _ in range(max(3, a.warmup)):
+        out = step()
+    sampler = ClockSampler(local_rank) if rank == 0 else None
+    if sampler:
+        sampler.start()
+    barrier()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    contraction_ms = launches = contraction_launches = 0
+    col_rounds = 0
+    for _ in range(a.steps):
+        out = step()
+        contraction_ms += out["timing"]["contraction_ms"]
+        launches += out["timing"]["total_launches"]
+        contraction_launches += out["timing"]["contraction_launches"]
+        col_rounds += out["timing"]["column_rounds"]
+    e1.record()
+    barrier()
+    ms = ddist.max_over_ranks(e0.elapsed_time(e1), device=dev)
+    clocks = sampler.summary() if sampler else None
+    fits_total = n_cand_total * CV * a.steps
+    value = fits_total / (ms * 1e-3)
+
+    # gather scores for the record (not timed): mean CV score and winner
+    full = ddist.gather_candidates({"correct": out["correct"], "n_test": out["n_test"], "n_iter": out["n_iter"]},
+                                   n_cand_total, world, rank, ["correct", "n_test", "n_iter"], device=dev)
+
+    # ---- e2e: the user's call, host buffers, H2D/D2H inside the timed region ----
+    e2e = None
+    if not a.no_e2e:
+        from sklearn.linear_model import LogisticRegression
+        from sklearn.model_selection import GridSearchCV
+        from cs230_distributed_machine_learning_b200 import worker as wk
+        from cs230_distributed_machine_learning_b200.client import LocalBackend, MLTaskManager
+        register_dataset("bench-cfg2", X, y)
+        ds = None
+        solver.close()
+        del solver
+        torch.cuda.empty_cache()
+        backend = LocalBackend(gpus=[local_rank])
+        mgr = MLTaskManager(backend)
+        est = GridSearchCV(LogisticRegression(), {"C": [float(c) for c in Cs]}, cv=CV)
+        ex = wk.gpu_executor(local_rank)
+        k_e2e = max(1, min(a.steps, 3))
+        r = mgr.train(est, "bench-cfg2", wait_for_completion=True)      # warm-up (module import, arena)
+        assert r.get("job_status") == "completed", r
+        barrier()
+        t0 = time.perf_counter()
+        h2d0, d2h0 = ex.solver.h2d_bytes, ex.solver.d2h_bytes
+        for _ in range(k_e2e):
+            ex.drop_resident()                      # every step pays the host->device copy of X, y
+            r = mgr.train(est, "bench-cfg2", wait_for_completion=True)
+            assert r["job_status"] == "completed"
+        torch.cuda.synchronize()
+        t_e2e = ddist.max_over_ranks(time.perf_counter() - t0, device=dev)
+        e2e = {"value": n_cand_total * CV * k_e2e / t_e2e, "unit": UNIT,
+               "h2d_bytes_per_step": (ex.solver.h2d_bytes - h2d0) // k_e2e,
+               "d2h_bytes_per_step": (ex.solver.d2h_bytes - d2h0) // k_e2e,
+               "api": "MLTaskManager.train(GridSearchCV(...), wait_for_completion=True)", "steps": k_e2e,
+               "best_params_": r["job_result"]["best_params_"]}
+        mgr.close()
+
+    if rank == 0:
+        peaks, src = measured_peaks()
+        p_tf32 = measure_tf32_peak(torch)
+        p3 = p_tf32 / 3.0
+        n_tr = a.rows * (CV - 1) / CV
+        # algorithmic flops: every column-round is one pass of the training rows through one
+        # column, forward + gradient = 4 * n_tr * (d + 1) flops
+        flops = col_rounds * 4.0 * n_tr * (a.features + 1)
+        sec = contraction_ms * 1e-3
+        ach = flops / sec / 1e12 if sec > 0 else None
+        rounds = out["timing"]["rounds"]
+        hbm_ach = (rounds * a.steps * a.rows * a.features * 4) / sec / 1e9 if sec > 0 else None
+        line = {
+            "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": a.steps,
+            "warmup": max(3, a.warmup), "ms_per_step": ms / a.steps, "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": None, "dtype": "f32 (3xTF32-equivalent accuracy, fp64 optimiser state)",
+            "data": "synthetic",
+            "config": {"workload": workload_name(a, n_cand_total), "partition": f"candidate blocks x{world}",
+                       "l2": "inputs (1.02 GB) larger than the 126 MB L2; no flush", "fits_per_step": n_cand_total * CV,
+                       "rounds_per_step": rounds, "mean_n_iter": float(np.mean(full["n_iter"])),
+                       "best_C": float(Cs_all[int(np.argmax(np.mean(full["correct"] / full["n_test"], axis=1)))])},
+            "roofline": {"bound": "tensor", "achieved": ach, "peak": p3, "unit": "TFLOP/s",
+                         "frac": (ach / p3) if ach else None, "traffic": None,
+                         "kernel": "forward+gradient contraction pair per batched round",
+                         "peak_source": f"cuBLAS TF32 8192^3 measured in this run = {p_tf32:.1f} TFLOP/s, /3 for 3xTF32",
+                         "naive_tf32_frac": (ach / p_tf32) if ach else None,
+                         "hbm_achieved_gbs": hbm_ach, "hbm_peak_gbs": peaks.get("hbm_gbs"), "hbm_peak_source": src,
+                         "kernel_ms_per_step": contraction_ms / a.steps,
+                         "kernel_share_of_step": contraction_ms / ms},
+            "clocks": clocks, "gpu_launches": int(launches), "contraction_launches": int(contraction_launches),
+        }
+        if e2e:
+            line["e2e"] = e2e
+        if not a.no_cpu_baseline and world == 1:
+            cores = os.cpu_count() or 1
+            sample = Cs_all[[len(Cs_all) // 4, 3 * len(Cs_all) // 4]]
+            t = cpu_reference_step(X, y, sample, 1)
+            line["cpu_baseline"] = {"value": len(sample) * CV / t, "unit": UNIT, "cores": cores, "kind": "port",
+                                    "sample": f"{len(sample)} of {len(Cs_all)} candidates x {CV} folds at full "
+                                              f"n={a.rows}, serial fits as in worker.py:326, BLAS on all cores"}
+        print(json.dumps(line))
+    if world > 1:
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    a = parse()
+    if a.impl == "reference":
+        run_reference(a)
+    else:
+        run_b200(a)

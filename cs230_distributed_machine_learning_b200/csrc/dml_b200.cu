@@ -1,0 +1,585 @@
+// C ABI + orchestration of the sweep (see include/dml_b200.h).
+#include "../../include/dml_b200.h"
+#include "dml_common.cuh"
+#include "dml_gemm.cuh"
+#include "dml_lbfgs.cuh"
+#include "dml_ridge.cuh"
+
+#include <dlfcn.h>
+#include <stdarg.h>
+#include <string.h>
+#include <algorithm>
+#include <vector>
+
+using namespace dml;
+
+// ---- minimal NCCL surface, resolved at run time from the libnccl the process already has ----
+typedef struct ncclComm* ncclComm_t;
+typedef struct { char internal[128]; } ncclUniqueId_t;
+enum { kNcclSum = 0, kNcclInt64 = 4, kNcclUint64 = 5, kNcclFloat64 = 8 };
+struct NcclApi {
+  void* lib = nullptr;
+  int (*GetUniqueId)(ncclUniqueId_t*) = nullptr;
+  int (*CommInitRank)(ncclComm_t*, int, ncclUniqueId_t, int) = nullptr;
+  int (*CommDestroy)(ncclComm_t) = nullptr;
+  int (*AllReduce)(const void*, void*, size_t, int, int, ncclComm_t, cudaStream_t) = nullptr;
+  const char* (*GetErrorString)(int) = nullptr;
+  bool load() {
+    if (lib) return true;
+    const char* names[] = {"libnccl.so.2", "libnccl.so"};
+    for (const char* nm : names) { lib = dlopen(nm, RTLD_NOW | RTLD_GLOBAL); if (lib) break; }
+    if (!lib) return false;
+    GetUniqueId = (decltype(GetUniqueId))dlsym(lib, "ncclGetUniqueId");
+    CommInitRank = (decltype(CommInitRank))dlsym(lib, "ncclCommInitRank");
+    CommDestroy = (decltype(CommDestroy))dlsym(lib, "ncclCommDestroy");
+    AllReduce = (decltype(AllReduce))dlsym(lib, "ncclAllReduce");
+    GetErrorString = (decltype(GetErrorString))dlsym(lib, "ncclGetErrorString");
+    return GetUniqueId && CommInitRank && CommDestroy && AllReduce;
+  }
+};
+static NcclApi g_nccl;
+static char g_create_err[512] = "";
+
+struct dml_ctx {
+  int device = 0;
+  cudaStream_t stream = nullptr;
+  char* ws = nullptr; size_t ws_bytes = 0;
+  int* h_scalar = nullptr;  // pinned
+  int n_sms = 148;
+  char err[512] = "";
+  ncclComm_t comm = nullptr; int n_ranks = 1, rank = 0;
+  // timing of the last sweep
+  std::vector<cudaEvent_t> ev;  // pairs
+  size_t ev_used = 0;
+  cudaEvent_t ev_total[2] = {nullptr, nullptr};
+  float total_ms = 0.f, contraction_ms = 0.f; int contraction_launches = 0, total_launches = 0;
+  size_t r_budget = (size_t)2 << 30;  // bytes of residual scratch per row chunk
+  long long slot_rounds = 0; int rounds = 0;  // sum over rounds of evaluated columns
+};
+
+static int fail(dml_ctx* c, int code, const char* fmt, ...) {
+  va_list ap; va_start(ap, fmt);
+  vsnprintf(c ? c->err : g_create_err, 512, fmt, ap);
+  va_end(ap);
+  return code;
+}
+#define CU(call) do { cudaError_t e_ = (call); if (e_ != cudaSuccess) \
+  return fail(ctx, DML_ERR_CUDA, "%s failed: %s (%s:%d)", #call, cudaGetErrorString(e_), __FILE__, __LINE__); } while (0)
+#define KCHECK() CU(cudaGetLastError())
+
+// bump allocator over the ctx arena: first pass measures, second pass hands out
+struct Arena {
+  char* base; size_t off = 0;
+  explicit Arena(char* b) : base(b) {}
+  template <class T> T* take(size_t count) {
+    off = (off + 255) & ~(size_t)255;
+    T* p = base ? reinterpret_cast<T*>(base + off) : nullptr;
+    off += count * sizeof(T);
+    return p;
+  }
+};
+static int ensure_ws(dml_ctx* ctx, size_t bytes) {
+  if (bytes <= ctx->ws_bytes) return DML_OK;
+  if (ctx->ws) { CU(cudaFree(ctx->ws)); ctx->ws = nullptr; ctx->ws_bytes = 0; }
+  CU(cudaMalloc(&ctx->ws, bytes));
+  ctx->ws_bytes = bytes;
+  return DML_OK;
+}
+static inline int64_t cdiv(int64_t a, int64_t b) { return (a + b - 1) / b; }
+static inline int64_t rup(int64_t a, int64_t b) { return cdiv(a, b) * b; }
+static inline bool aligned16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15) == 0; }
+
+// timing helpers
+static void tick(dml_ctx* ctx) {
+  if (ctx->ev_used + 2 > ctx->ev.size()) return;
+  cudaEventRecord(ctx->ev[ctx->ev_used], ctx->stream);
+}
+static void tock(dml_ctx* ctx, int launches) {
+  ctx->contraction_launches += launches;
+  if (ctx->ev_used + 2 > ctx->ev.size()) return;
+  cudaEventRecord(ctx->ev[ctx->ev_used + 1], ctx->stream);
+  ctx->ev_used += 2;
+}
+static void timing_begin(dml_ctx* ctx) {
+  ctx->ev_used = 0; ctx->contraction_launches = 0; ctx->total_launches = 0;
+  ctx->slot_rounds = 0; ctx->rounds = 0;
+  ctx->total_ms = ctx->contraction_ms = 0.f;
+  cudaEventRecord(ctx->ev_total[0], ctx->stream);
+}
+static void timing_end(dml_ctx* ctx) {
+  cudaEventRecord(ctx->ev_total[1], ctx->stream);
+  cudaEventSynchronize(ctx->ev_total[1]);
+  cudaEventElapsedTime(&ctx->total_ms, ctx->ev_total[0], ctx->ev_total[1]);
+  float acc = 0.f;
+  for (size_t i = 0; i + 1 < ctx->ev_used; i += 2) {
+    float ms = 0.f;
+    if (cudaEventElapsedTime(&ms, ctx->ev[i], ctx->ev[i + 1]) == cudaSuccess) acc += ms;
+  }
+  ctx->contraction_ms = acc;
+}
+
+static int allreduce(dml_ctx* ctx, void* buf, size_t count, int dtype) {
+  if (!ctx->comm) return DML_OK;
+  const int rc = g_nccl.AllReduce(buf, buf, count, dtype, kNcclSum, ctx->comm, ctx->stream);
+  if (rc != 0) return fail(ctx, DML_ERR_NCCL, "ncclAllReduce failed: %s", g_nccl.GetErrorString ? g_nccl.GetErrorString(rc) : "?");
+  return DML_OK;
+}
+
+extern "C" int dml_version(void) { return 100; }
+
+extern "C" const char* dml_last_error(dml_ctx* ctx) { return ctx ? ctx->err : g_create_err; }
+
+extern "C" int dml_ctx_create(int device, void* stream, dml_ctx** out) {
+  dml_ctx* ctx = nullptr;
+  if (!out) return fail(nullptr, DML_ERR_ARG, "dml_ctx_create: out is NULL");
+  int count = 0;
+  cudaError_t e = cudaGetDeviceCount(&count);
+  if (e != cudaSuccess || device < 0 || device >= count)
+    return fail(nullptr, DML_ERR_CUDA, "dml_ctx_create: no CUDA device %d (%s)", device,
+                e != cudaSuccess ? cudaGetErrorString(e) : "index out of range");
+  cudaDeviceProp prop;
+  cudaGetDeviceProperties(&prop, device);
+  if (prop.major != 10)
+    return fail(nullptr, DML_ERR_CUDA, "dml_ctx_create: device %d is sm_%d%d; this library is built for sm_100a only",
+                device, prop.major, prop.minor);
+  ctx = new dml_ctx();
+  ctx->device = device; ctx->stream = (cudaStream_t)stream; ctx->n_sms = prop.multiProcessorCount;
+  CU(cudaSetDevice(device));
+  CU(cudaHostAlloc(&ctx->h_scalar, 64, cudaHostAllocDefault));
+  ctx->ev.resize(2 * 2048);
+  for (auto& ev : ctx->ev) CU(cudaEventCreate(&ev));
+  CU(cudaEventCreate(&ctx->ev_total[0]));
+  CU(cudaEventCreate(&ctx->ev_total[1]));
+  CU(cudaFuncSetAttribute(fwd_kernel<FWD_LOGREG>, cudaFuncAttributeMaxDynamicSharedMemorySize, kFwdSmemBytes));
+  CU(cudaFuncSetAttribute(fwd_kernel<FWD_SCORE_CLS>, cudaFuncAttributeMaxDynamicSharedMemorySize, kFwdSmemBytes));
+  CU(cudaFuncSetAttribute(fwd_kernel<FWD_SCORE_REG>, cudaFuncAttributeMaxDynamicSharedMemorySize, kFwdSmemBytes));
+  *out = ctx;
+  return DML_OK;
+}
+
+extern "C" void dml_ctx_destroy(dml_ctx* ctx) {
+  if (!ctx) return;
+  cudaSetDevice(ctx->device);
+  cudaStreamSynchronize(ctx->stream);
+  if (ctx->comm && g_nccl.CommDestroy) g_nccl.CommDestroy(ctx->comm);
+  if (ctx->ws) cudaFree(ctx->ws);
+  if (ctx->h_scalar) cudaFreeHost(ctx->h_scalar);
+  for (auto& ev : ctx->ev) cudaEventDestroy(ev);
+  cudaEventDestroy(ctx->ev_total[0]); cudaEventDestroy(ctx->ev_total[1]);
+  delete ctx;
+}
+
+extern "C" int dml_nccl_unique_id(void* id128_host) {
+  if (!g_nccl.load()) return fail(nullptr, DML_ERR_NCCL, "libnccl.so.2 not found");
+  ncclUniqueId_t id;
+  const int rc = g_nccl.GetUniqueId(&id);
+  if (rc != 0) return fail(nullptr, DML_ERR_NCCL, "ncclGetUniqueId failed (%d)", rc);
+  memcpy(id128_host, &id, 128);
+  return DML_OK;
+}
+
+extern "C" int dml_ctx_init_comm(dml_ctx* ctx, int n_ranks, int rank, const void* id128_host) {
+  if (!ctx) return DML_ERR_ARG;
+  if (!g_nccl.load()) return fail(ctx, DML_ERR_NCCL, "libnccl.so.2 not found");
+  CU(cudaSetDevice(ctx->device));
+  ncclUniqueId_t id; memcpy(&id, id128_host, 128);
+  const int rc = g_nccl.CommInitRank(&ctx->comm, n_ranks, id, rank);
+  if (rc != 0) return fail(ctx, DML_ERR_NCCL, "ncclCommInitRank failed: %s", g_nccl.GetErrorString ? g_nccl.GetErrorString(rc) : "?");
+  ctx->n_ranks = n_ranks; ctx->rank = rank;
+  return DML_OK;
+}
+
+extern "C" int dml_last_timing(dml_ctx* ctx, float* total_ms, float* contraction_ms,
+                               int32_t* contraction_launches, int32_t* total_launches) {
+  if (!ctx) return DML_ERR_ARG;
+  if (total_ms) *total_ms = ctx->total_ms;
+  if (contraction_ms) *contraction_ms = ctx->contraction_ms;
+  if (contraction_launches) *contraction_launches = ctx->contraction_launches;
+  if (total_launches) *total_launches = ctx->total_launches;
+  return DML_OK;
+}
+
+extern "C" int dml_last_counters(dml_ctx* ctx, int64_t* column_rounds, int32_t* rounds) {
+  if (!ctx) return DML_ERR_ARG;
+  if (column_rounds) *column_rounds = ctx->slot_rounds;
+  if (rounds) *rounds = ctx->rounds;
+  return DML_OK;
+}
+
+// ---- shared: one scoring pass over all rows for `n_slots` columns -------------------------
+struct ScoreBufs { int32_t* cntPart; float* ssePart; };
+static int run_score(dml_ctx* ctx, int mode, const float* X, int64_t n, int d, int64_t ldx,
+                     const int32_t* ycls, const float* yreg, const int8_t* fold_id, const int8_t* hold_id,
+                     const float* Wt, int ldw, const float* bt, const int32_t* sel, const int32_t* val,
+                     int n_slots, int T, void* part /*[tiles][n_slots] 4-byte*/) {
+  FwdParams fp{};
+  fp.X = X; fp.ldx = ldx; fp.row0 = 0; fp.rows = n; fp.d = d;
+  fp.xvec = (ldx % 4 == 0) && aligned16(X);
+  fp.Wt = Wt; fp.ldw = ldw; fp.wvec = (ldw % 4 == 0) && aligned16(Wt); fp.bt = bt;
+  fp.n_slots = n_slots; fp.T = T; fp.tile_n = (BN / T) * T;
+  fp.ycls = ycls; fp.yreg = yreg; fp.fold_id = fold_id; fp.hold_id = hold_id;
+  fp.slot_sel = sel; fp.slot_val = val;
+  fp.cntPart = (int32_t*)part; fp.ssePart = (float*)part;
+  dim3 grid((unsigned)cdiv(n, BM), (unsigned)cdiv(n_slots, fp.tile_n));
+  if (grid.y > 65535) return fail(ctx, DML_ERR_LIMIT, "too many columns for one scoring launch (%d)", n_slots);
+  tick(ctx);
+  if (mode == FWD_SCORE_CLS) fwd_kernel<FWD_SCORE_CLS><<<grid, NT, kFwdSmemBytes, ctx->stream>>>(fp);
+  else fwd_kernel<FWD_SCORE_REG><<<grid, NT, kFwdSmemBytes, ctx->stream>>>(fp);
+  tock(ctx, 1);
+  ctx->total_launches += 1;
+  KCHECK();
+  return DML_OK;
+}
+
+// =============================================================================================
+extern "C" int dml_logreg_sweep(dml_ctx* ctx, const float* X, int64_t n, int d, int64_t ldx,
+                                const int32_t* y, int n_classes,
+                                const int8_t* fold_id, int n_folds, const int8_t* hold_id,
+                                const double* C, const double* tol, const uint8_t* fit_intercept,
+                                const int32_t* max_iter, int n_cand,
+                                float* coef_out, float* intercept_out,
+                                int32_t* n_iter_out, int32_t* status_out, int32_t* nfev_out,
+                                int64_t* correct_out, int64_t* n_test_out,
+                                int32_t* rounds_out, int use_tensor_cores) {
+  if (!ctx) return DML_ERR_ARG;
+  if (!X || !y || !fold_id || !C || !tol || !fit_intercept || !max_iter || !coef_out || !intercept_out)
+    return fail(ctx, DML_ERR_ARG, "dml_logreg_sweep: NULL argument");
+  if (n <= 0 || d <= 0 || ldx < d || n_classes < 2 || n_cand <= 0 || n_folds < 0 || n_folds > 127)
+    return fail(ctx, DML_ERR_ARG, "dml_logreg_sweep: bad shape (n=%lld d=%d ldx=%lld classes=%d cand=%d folds=%d)",
+                (long long)n, d, (long long)ldx, n_classes, n_cand, n_folds);
+  (void)use_tensor_cores;
+  CU(cudaSetDevice(ctx->device));
+  cudaStream_t st = ctx->stream;
+  const int T = n_classes == 2 ? 1 : n_classes;
+  if (T > BN) return fail(ctx, DML_ERR_LIMIT, "n_classes %d > %d not supported", n_classes, BN);
+  const int fpc = n_folds + (hold_id ? 1 : 0);
+  if (fpc == 0) return fail(ctx, DML_ERR_ARG, "dml_logreg_sweep: no fits requested");
+  const int F = n_cand * fpc, P = T * (d + 1);
+  const int64_t S_max = (int64_t)F * T;
+  const int ldw = (int)rup(d, 4), ldg = ldw, ldgr = d + 2;
+  const int64_t tiles_total = cdiv(n, BM);
+  const int tile_n = (BN / T) * T;
+  if (cdiv(S_max, tile_n) > 65535) return fail(ctx, DML_ERR_LIMIT, "too many columns (%lld)", (long long)S_max);
+  // row chunk so that the residual scratch stays within budget
+  const int64_t ldr_max = rup(S_max, 4);
+  int64_t chunk_rows = std::max<int64_t>(BM, (int64_t)(ctx->r_budget / (ldr_max * 4)) / BM * BM);
+  chunk_rows = std::min<int64_t>(chunk_rows, rup(n, BM));
+  // row splits of the gradient contraction
+  const int mt_max = (int)cdiv(S_max, BM), nt = (int)cdiv(d, BN);
+  int splits = (int)std::max<int64_t>(1, std::min<int64_t>(cdiv(4 * ctx->n_sms, (int64_t)mt_max * nt), cdiv(chunk_rows, 2048)));
+  const int64_t rps = rup(cdiv(chunk_rows, splits), 16);
+  splits = (int)cdiv(chunk_rows, rps);
+
+  FitState* d_st; double *d_x, *d_g, *d_dir, *d_gt, *d_S, *d_Y, *d_ys, *d_Gred;
+  int *d_active, *d_nactive; unsigned long long* d_hist; long long* d_correct;
+  float *d_Wt, *d_bt, *d_R, *d_lossPart, *d_gbPart, *d_Gpart; int32_t *d_sel, *d_val, *d_i32;
+  for (int pass = 0; pass < 2; ++pass) {
+    Arena a(pass ? ctx->ws : nullptr);
+    d_st = a.take<FitState>(F); d_i32 = a.take<int32_t>(3 * (size_t)F);
+    d_x = a.take<double>((size_t)F * P); d_g = a.take<double>((size_t)F * P);
+    d_dir = a.take<double>((size_t)F * P); d_gt = a.take<double>((size_t)F * P);
+    d_S = a.take<double>((size_t)F * kMaxCor * P); d_Y = a.take<double>((size_t)F * kMaxCor * P);
+    d_ys = a.take<double>((size_t)F * kMaxCor);
+    d_Gred = a.take<double>((size_t)S_max * ldgr);
+    d_active = a.take<int>(F); d_nactive = a.take<int>(4);
+    d_hist = a.take<unsigned long long>(512); d_correct = a.take<long long>(F);
+    d_Wt = a.take<float>((size_t)S_max * ldw); d_bt = a.take<float>(S_max);
+    d_sel = a.take<int32_t>(S_max); d_val = a.take<int32_t>(S_max);
+    d_R = a.take<float>((size_t)chunk_rows * ldr_max);
+    d_lossPart = a.take<float>((size_t)tiles_total * S_max);
+    d_gbPart = a.take<float>((size_t)tiles_total * S_max);
+    d_Gpart = a.take<float>((size_t)splits * S_max * ldg);
+    if (!pass) { int rc = ensure_ws(ctx, a.off + 256); if (rc) return rc; }
+  }
+  timing_begin(ctx);
+  CU(cudaMemsetAsync(d_x, 0, sizeof(double) * (size_t)F * P, st));
+  CU(cudaMemsetAsync(d_g, 0, sizeof(double) * (size_t)F * P, st));
+  CU(cudaMemsetAsync(d_dir, 0, sizeof(double) * (size_t)F * P, st));
+  CU(cudaMemsetAsync(d_hist, 0, sizeof(unsigned long long) * 512, st));
+  CU(cudaMemsetAsync(d_lossPart, 0, sizeof(float) * (size_t)tiles_total * S_max, st));
+  label_hist_kernel<<<(unsigned)std::min<int64_t>(cdiv(n, 256), 4 * ctx->n_sms), 256, 0, st>>>(fold_id, hold_id, n, d_hist);
+  KCHECK();
+  int64_t n_total = n;
+  if (ctx->comm) {
+    int rc = allreduce(ctx, d_hist, 512, kNcclUint64); if (rc) return rc;
+    // total rows = sum of the fold histogram
+    std::vector<unsigned long long> h(256);
+    CU(cudaMemcpyAsync(h.data(), d_hist, 256 * sizeof(unsigned long long), cudaMemcpyDeviceToHost, st));
+    CU(cudaStreamSynchronize(st));
+    n_total = 0; for (auto v : h) n_total += (int64_t)v;
+  }
+  InitParams ip{F, n_folds, hold_id ? 1 : 0, fpc, n_total, d_hist, C, tol, fit_intercept, max_iter, d_st, d_active, d_nactive};
+  init_fits_kernel<<<(unsigned)cdiv(F, 128), 128, 0, st>>>(ip);
+  KCHECK();
+  TrialParams tp{d, T, P, ldw, d_st, d_x, d_dir, d_active, d_nactive, d_Wt, d_bt, d_sel, d_val};
+  write_trial_kernel<<<F, 128, 0, st>>>(tp);
+  KCHECK();
+  ctx->total_launches += 3;
+
+  int n_active = F, rounds = 0;
+  const bool xvec = (ldx % 4 == 0) && aligned16(X);
+  while (n_active > 0) {
+    const int n_slots = n_active * T, ldr = (int)rup(n_slots, 4);
+    ctx->slot_rounds += n_slots; ctx->rounds += 1;
+    int launches = 0;
+    tick(ctx);
+    for (int64_t r0 = 0, ci = 0; r0 < n; r0 += chunk_rows, ++ci) {
+      const int64_t rows = std::min(chunk_rows, n - r0);
+      FwdParams fp{};
+      fp.X = X; fp.ldx = ldx; fp.row0 = r0; fp.rows = rows; fp.d = d; fp.xvec = xvec;
+      fp.Wt = d_Wt; fp.ldw = ldw; fp.wvec = true; fp.bt = d_bt;
+      fp.n_slots = n_slots; fp.T = T; fp.tile_n = tile_n;
+      fp.ycls = y; fp.yreg = nullptr; fp.fold_id = fold_id; fp.hold_id = hold_id;
+      fp.slot_sel = d_sel; fp.slot_val = d_val;
+      fp.R = d_R; fp.ldr = ldr; fp.lossPart = d_lossPart; fp.gbPart = d_gbPart;
+      dim3 g1((unsigned)cdiv(rows, BM), (unsigned)cdiv(n_slots, tile_n));
+      fwd_kernel<FWD_LOGREG><<<g1, NT, kFwdSmemBytes, st>>>(fp);
+      GradParams gp{X, ldx, r0, rows, d, xvec, d_R, ldr, n_slots, rps, d_Gpart, ldg, ci > 0 ? 1 : 0};
+      dim3 g2((unsigned)cdiv(n_slots, BM), (unsigned)nt, (unsigned)splits);
+      grad_kernel<<<g2, NT, kGemmSmemBytes, st>>>(gp);
+      launches += 2;
+    }
+    tock(ctx, launches);
+    KCHECK();
+    ReduceParams rp{d_Gpart, ldg, splits, n_slots, d, d_lossPart, d_gbPart, tiles_total, d_Gred, ldgr};
+    reduce_grad_kernel<<<n_slots, 128, 0, st>>>(rp);
+    reduce_tiles_kernel<<<(unsigned)cdiv(n_slots, 32), dim3(32, 8), 0, st>>>(rp);
+    KCHECK();
+    if (ctx->comm) { int rc = allreduce(ctx, d_Gred, (size_t)n_slots * ldgr, kNcclFloat64); if (rc) return rc; }
+    LbfgsParams lp{d, T, P, ldgr, d_st, d_x, d_g, d_dir, d_gt, d_S, d_Y, d_ys, d_active, d_nactive, d_Gred};
+    lbfgs_update_kernel<<<n_active, 256, 0, st>>>(lp);
+    compact_kernel<<<1, 1024, 0, st>>>(d_st, F, d_active, d_nactive, d_nactive + 1);
+    write_trial_kernel<<<n_active, 128, 0, st>>>(tp);
+    KCHECK();
+    CU(cudaMemcpyAsync(ctx->h_scalar, d_nactive, sizeof(int), cudaMemcpyDeviceToHost, st));
+    CU(cudaStreamSynchronize(st));
+    n_active = ctx->h_scalar[0];
+    ctx->total_launches += launches + 5;
+    if (++rounds > 200000) return fail(ctx, DML_ERR_LIMIT, "dml_logreg_sweep: round cap hit");
+  }
+  // results + score pass on every fit's held-out rows
+  FinalParams fin{F, d, T, P, ldw, d_st, d_x, coef_out, intercept_out, n_iter_out ? n_iter_out : d_i32,
+                  status_out ? status_out : d_i32 + F, nfev_out ? nfev_out : d_i32 + 2 * F,
+                  d_Wt, d_bt, d_sel, d_val};
+  finalize_kernel<<<F, 128, 0, st>>>(fin);
+  KCHECK();
+  ctx->total_launches += 1;
+  if (correct_out || n_test_out) {
+    int rc = run_score(ctx, FWD_SCORE_CLS, X, n, d, ldx, y, nullptr, fold_id, hold_id, d_Wt, ldw, d_bt, d_sel, d_val,
+                       (int)S_max, T, d_lossPart);
+    if (rc) return rc;
+    reduce_counts_kernel<<<F, 256, 0, st>>>((const int32_t*)d_lossPart, tiles_total, (int)S_max, T, d_correct);
+    KCHECK();
+    if (ctx->comm) { rc = allreduce(ctx, d_correct, F, kNcclInt64); if (rc) return rc; }
+    if (correct_out) CU(cudaMemcpyAsync(correct_out, d_correct, sizeof(int64_t) * F, cudaMemcpyDeviceToDevice, st));
+    if (n_test_out) {
+      // n_test of fit (cand, k) = histogram entry of its mask
+      std::vector<unsigned long long> h(512);
+      CU(cudaMemcpyAsync(h.data(), d_hist, 512 * sizeof(unsigned long long), cudaMemcpyDeviceToHost, st));
+      CU(cudaStreamSynchronize(st));
+      std::vector<int64_t> nt_h(F);
+      for (int f = 0; f < F; ++f) { const int k = f % fpc; nt_h[f] = (int64_t)(k < n_folds ? h[k] : h[256 + 1]); }
+      CU(cudaMemcpyAsync(n_test_out, nt_h.data(), sizeof(int64_t) * F, cudaMemcpyHostToDevice, st));
+      CU(cudaStreamSynchronize(st));
+    }
+    ctx->total_launches += 1;
+  }
+  timing_end(ctx);
+  CU(cudaStreamSynchronize(st));
+  if (rounds_out) *rounds_out = rounds;
+  return DML_OK;
+}
+
+// =============================================================================================
+// per-fit statistics of the held-out targets, fp64, deterministic: one block per label value
+__global__ void target_stats_kernel(const float* y, const int8_t* label, int64_t n, double* sy, double* syy) {
+  __shared__ double red[33];
+  const int want = blockIdx.x;
+  double a = 0.0, b = 0.0;
+  for (int64_t r = threadIdx.x; r < n; r += blockDim.x)
+    if (label[r] == want) { const double v = (double)y[r]; a += v; b += v * v; }
+  a = block_reduce<false>(a, red);
+  b = block_reduce<false>(b, red);
+  if (threadIdx.x == 0) { sy[want] = a; syy[want] = b; }
+}
+__global__ void expand_stats_kernel(const double* sy_l, const double* syy_l, const double* sy_h, const double* syy_h,
+                                    int n_fits, int fpc, int n_folds, double* sy, double* syy) {
+  const int f = blockIdx.x * blockDim.x + threadIdx.x;
+  if (f >= n_fits) return;
+  const int k = f % fpc;
+  if (sy) sy[f] = k < n_folds ? sy_l[k] : sy_h[1];
+  if (syy) syy[f] = k < n_folds ? syy_l[k] : syy_h[1];
+}
+
+extern "C" int dml_ridge_sweep(dml_ctx* ctx, const float* X, int64_t n, int d, int64_t ldx,
+                               const float* y_reg, const int32_t* y_cls, int n_classes, int is_classifier,
+                               const int8_t* fold_id, int n_folds, const int8_t* hold_id,
+                               const double* alpha, const uint8_t* fit_intercept, int n_cand,
+                               float* coef_out, float* intercept_out,
+                               int64_t* correct_out, int64_t* n_test_out,
+                               double* sse_out, double* sy_out, double* syy_out,
+                               int32_t* info_out, int use_tensor_cores) {
+  if (!ctx) return DML_ERR_ARG;
+  (void)use_tensor_cores;
+  if (!X || !fold_id || !alpha || !fit_intercept || !coef_out || !intercept_out || (is_classifier ? !y_cls : !y_reg))
+    return fail(ctx, DML_ERR_ARG, "dml_ridge_sweep: NULL argument");
+  if (n <= 0 || d <= 0 || ldx < d || n_cand <= 0 || n_folds < 0 || n_folds > 127 || (is_classifier && n_classes < 2))
+    return fail(ctx, DML_ERR_ARG, "dml_ridge_sweep: bad shape");
+  CU(cudaSetDevice(ctx->device));
+  cudaStream_t st = ctx->stream;
+  const int T = is_classifier ? (n_classes == 2 ? 1 : n_classes) : 1;
+  if (T > BN) return fail(ctx, DML_ERR_LIMIT, "n_classes %d > %d not supported", n_classes, BN);
+  const int has_hold = hold_id ? 1 : 0, fpc = n_folds + has_hold;
+  if (fpc == 0) return fail(ctx, DML_ERR_ARG, "dml_ridge_sweep: no fits requested");
+  const int F = n_cand * fpc, D = d + T + 1, ldm = (int)rup(D, 4), ldw = (int)rup(d, 4);
+  const int64_t S_all = (int64_t)F * T, tiles_total = cdiv(n, BM);
+  const int tile_n = (BN / T) * T;
+  if (cdiv(S_all, tile_n) > 65535) return fail(ctx, DML_ERR_LIMIT, "too many columns (%lld)", (long long)S_all);
+  const int64_t rps = 16384;
+  const int splits = (int)cdiv(n, rps);
+  const int gfolds = std::max(n_folds, 2);  // the hold-out pass uses labels {0,1}
+  // candidates per solve batch: keep the fp64 systems under ~2 GB
+  int cand_chunk = (int)std::max<int64_t>(1, ((int64_t)2 << 30) / ((int64_t)fpc * d * d * 8));
+  cand_chunk = std::min(cand_chunk, n_cand);
+
+  float *d_Mpart, *d_Wt, *d_bt; void* d_part; uint16_t* d_bmask;
+  double *d_Mfold, *d_Mtot, *d_A, *d_B, *d_mu, *d_stats, *d_sse; int32_t *d_sel, *d_val, *d_info; long long* d_cnt;
+  for (int pass = 0; pass < 2; ++pass) {
+    Arena a(pass ? ctx->ws : nullptr);
+    d_Mpart = a.take<float>((size_t)gfolds * splits * D * ldm);
+    d_Mfold = a.take<double>((size_t)(n_folds + 2) * D * D);
+    d_Mtot = a.take<double>((size_t)D * D);
+    d_bmask = a.take<uint16_t>((size_t)cdiv(n, 16) + 16);
+    d_A = a.take<double>((size_t)cand_chunk * fpc * d * d);
+    d_B = a.take<double>((size_t)cand_chunk * fpc * T * d);
+    d_mu = a.take<double>((size_t)cand_chunk * fpc * (d + T));
+    d_Wt = a.take<float>((size_t)S_all * ldw); d_bt = a.take<float>(S_all);
+    d_sel = a.take<int32_t>(S_all); d_val = a.take<int32_t>(S_all);
+    d_info = a.take<int32_t>(F); d_cnt = a.take<long long>(F);
+    d_stats = a.take<double>(4 * 256); d_sse = a.take<double>(S_all);
+    d_part = a.take<float>((size_t)tiles_total * S_all);
+    if (!pass) { int rc = ensure_ws(ctx, a.off + 256); if (rc) return rc; }
+  }
+  timing_begin(ctx);
+  const bool xvec = (ldx % 4 == 0) && aligned16(X);
+  CU(cudaMemsetAsync(d_info, 0, sizeof(int32_t) * F, st));
+  // ---- moments: one pass over X for the CV folds (+ one for the hold-out split) ----
+  for (int pass = 0; pass < 1 + has_hold; ++pass) {
+    const int8_t* lab = pass == 0 ? fold_id : hold_id;
+    const int nf = pass == 0 ? n_folds : 2;
+    if (nf == 0) continue;
+    const bool use_mask = nf <= 16;
+    if (use_mask) { blockmask_kernel<<<(unsigned)cdiv(cdiv(n, 16), 256), 256, 0, st>>>(lab, n, d_bmask); KCHECK(); }
+    GramParams gp{X, ldx, n, d, xvec, lab, use_mask ? d_bmask : nullptr, T, is_classifier ? nullptr : y_reg,
+                  is_classifier ? y_cls : nullptr, rps, splits, d_Mpart, ldm};
+    dim3 grid((unsigned)cdiv(D, BM), (unsigned)cdiv(D, BN), (unsigned)(nf * splits));
+    tick(ctx);
+    gram_kernel<<<grid, NT, kGemmSmemBytes, st>>>(gp);
+    tock(ctx, 1);
+    KCHECK();
+    double* dst = pass == 0 ? d_Mfold : d_Mfold + (size_t)n_folds * D * D;  // hold pass writes [n_folds], [n_folds+1]
+    reduce_moments_kernel<<<dim3((unsigned)cdiv(D, 128), D, nf), 128, 0, st>>>(d_Mpart, splits, D, ldm, dst);
+    KCHECK();
+    ctx->total_launches += 3;
+  }
+  if (has_hold) {
+    // keep only the label-1 moments of the hold-out pass, in slot n_folds
+    CU(cudaMemcpyAsync(d_Mfold + (size_t)n_folds * D * D, d_Mfold + (size_t)(n_folds + 1) * D * D,
+                       sizeof(double) * D * D, cudaMemcpyDeviceToDevice, st));
+  }
+  if (ctx->comm) { int rc = allreduce(ctx, d_Mfold, (size_t)fpc * D * D, kNcclFloat64); if (rc) return rc; }
+  if (n_folds > 0) {
+    total_moments_kernel<<<(unsigned)cdiv((int64_t)D * D, 256), 256, 0, st>>>(d_Mfold, n_folds, D, d_Mtot);
+  } else {
+    // only a hold-out split: total = label0 + label1 moments of that pass (label 0 was overwritten above) -> recompute
+    return fail(ctx, DML_ERR_ARG, "dml_ridge_sweep: n_folds must be >= 2");
+  }
+  KCHECK();
+  // ---- batched solves ----
+  for (int c0 = 0; c0 < n_cand; c0 += cand_chunk) {
+    const int nc = std::min(cand_chunk, n_cand - c0), nsys = nc * fpc;
+    RidgeSysParams sp{d, T, D, n_folds, has_hold, c0, nc, d_Mfold, d_Mtot, alpha, fit_intercept, d_A, d_B, d_mu};
+    ridge_assemble_kernel<<<dim3(32, nsys), 256, 0, st>>>(sp);
+    ridge_cholesky_kernel<<<nsys, 512, d * sizeof(double), st>>>(d_A, d_B, d, T, d_info + c0 * fpc);
+    RidgeOutParams op{d, T, n_folds, has_hold, c0, ldw, d_B, d_mu, coef_out, intercept_out, d_Wt, d_bt, d_sel, d_val};
+    ridge_output_kernel<<<dim3(nsys, T), 128, 0, st>>>(op);
+    KCHECK();
+    ctx->total_launches += 3;
+  }
+  if (info_out) CU(cudaMemcpyAsync(info_out, d_info, sizeof(int32_t) * F, cudaMemcpyDeviceToDevice, st));
+  // ---- score every fit on its held-out rows ----
+  int rc = run_score(ctx, is_classifier ? FWD_SCORE_CLS : FWD_SCORE_REG, X, n, d, ldx, y_cls, y_reg, fold_id, hold_id,
+                     d_Wt, ldw, d_bt, d_sel, d_val, (int)S_all, T, d_part);
+  if (rc) return rc;
+  if (is_classifier) {
+    reduce_counts_kernel<<<F, 256, 0, st>>>((const int32_t*)d_part, tiles_total, (int)S_all, T, d_cnt);
+    KCHECK();
+    if (ctx->comm) { rc = allreduce(ctx, d_cnt, F, kNcclInt64); if (rc) return rc; }
+    if (correct_out) CU(cudaMemcpyAsync(correct_out, d_cnt, sizeof(int64_t) * F, cudaMemcpyDeviceToDevice, st));
+  } else {
+    reduce_sse_kernel<<<(unsigned)S_all, 256, 0, st>>>((const float*)d_part, tiles_total, (int)S_all, d_sse);
+    KCHECK();
+    if (ctx->comm) { rc = allreduce(ctx, d_sse, S_all, kNcclFloat64); if (rc) return rc; }
+    if (sse_out) CU(cudaMemcpyAsync(sse_out, d_sse, sizeof(double) * S_all, cudaMemcpyDeviceToDevice, st));
+    if (sy_out || syy_out) {
+      target_stats_kernel<<<n_folds, 1024, 0, st>>>(y_reg, fold_id, n, d_stats, d_stats + 256);
+      if (has_hold) target_stats_kernel<<<2, 1024, 0, st>>>(y_reg, hold_id, n, d_stats + 512, d_stats + 768);
+      KCHECK();
+      if (ctx->comm) { rc = allreduce(ctx, d_stats, 1024, kNcclFloat64); if (rc) return rc; }
+      expand_stats_kernel<<<(unsigned)cdiv(F, 128), 128, 0, st>>>(d_stats, d_stats + 256, d_stats + 512, d_stats + 768,
+                                                                 F, fpc, n_folds, sy_out, syy_out);
+      KCHECK();
+    }
+  }
+  if (n_test_out) {
+    ridge_teststats_kernel<<<(unsigned)cdiv(F, 128), 128, 0, st>>>(d_Mfold, D, d, F, fpc, n_folds,
+                                                                  (long long*)n_test_out, nullptr, nullptr);
+    KCHECK();
+  }
+  ctx->total_launches += 3;
+  timing_end(ctx);
+  CU(cudaStreamSynchronize(st));
+  return DML_OK;
+}
+
+// =============================================================================================
+extern "C" int dml_score(dml_ctx* ctx, const float* X, int64_t n, int d, int64_t ldx,
+                         const int32_t* y_cls, const float* y_reg,
+                         const int8_t* fold_id, const int8_t* hold_id,
+                         const float* W, const float* b, const int32_t* mask_sel, const int32_t* mask_val,
+                         int n_slots, int T, int64_t* correct_out, double* sse_out) {
+  if (!ctx) return DML_ERR_ARG;
+  if (!X || !fold_id || !W || !b || !mask_sel || !mask_val || n <= 0 || d <= 0 || n_slots <= 0 || T <= 0 ||
+      n_slots % T != 0 || T > BN || (!y_cls && !y_reg))
+    return fail(ctx, DML_ERR_ARG, "dml_score: bad argument");
+  CU(cudaSetDevice(ctx->device));
+  cudaStream_t st = ctx->stream;
+  const int64_t tiles_total = cdiv(n, BM);
+  void* d_part; long long* d_cnt; double* d_sse;
+  for (int pass = 0; pass < 2; ++pass) {
+    Arena a(pass ? ctx->ws : nullptr);
+    d_part = a.take<float>((size_t)tiles_total * n_slots);
+    d_cnt = a.take<long long>(n_slots); d_sse = a.take<double>(n_slots);
+    if (!pass) { int rc = ensure_ws(ctx, a.off + 256); if (rc) return rc; }
+  }
+  timing_begin(ctx);
+  const bool cls = y_cls != nullptr && correct_out != nullptr;
+  int rc = run_score(ctx, cls ? FWD_SCORE_CLS : FWD_SCORE_REG, X, n, d, ldx, y_cls, y_reg, fold_id, hold_id,
+                     W, d, b, mask_sel, mask_val, n_slots, T, d_part);
+  if (rc) return rc;
+  if (cls) {
+    reduce_counts_kernel<<<n_slots / T, 256, 0, st>>>((const int32_t*)d_part, tiles_total, n_slots, T, d_cnt);
+    KCHECK();
+    if (ctx->comm) { rc = allreduce(ctx, d_cnt, n_slots / T, kNcclInt64); if (rc) return rc; }
+    CU(cudaMemcpyAsync(correct_out, d_cnt, sizeof(int64_t) * (n_slots / T), cudaMemcpyDeviceToDevice, st));
+  } else {
+    if (!sse_out || !y_reg) return fail(ctx, DML_ERR_ARG, "dml_score: regression scoring needs y_reg and sse_out");
+    reduce_sse_kernel<<<n_slots, 256, 0, st>>>((const float*)d_part, tiles_total, n_slots, d_sse);
+    KCHECK();
+    if (ctx->comm) { rc = allreduce(ctx, d_sse, n_slots, kNcclFloat64); if (rc) return rc; }
+    CU(cudaMemcpyAsync(sse_out, d_sse, sizeof(double) * n_slots, cudaMemcpyDeviceToDevice, st));
+  }
+  timing_end(ctx);
+  CU(cudaStreamSynchronize(st));
+  return DML_OK;
+}

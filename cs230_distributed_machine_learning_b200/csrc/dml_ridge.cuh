@@ -1,0 +1,165 @@
+// Ridge / RidgeClassifier: batched normal-equation solves from per-fold moments.
+//
+// scikit-learn path being reproduced (reference call sites worker.py:315,326 with
+// the registry extended to Ridge/RidgeClassifier):
+//   centre X and y on the training fold        sklearn/linear_model/_base.py:189-199
+//   A = Xc^T Xc + alpha I ; w = solve(A, Xc^T yc, assume_a="pos")   _ridge.py:215-234
+//   intercept = ybar - xbar . w                 _base.py:318-335
+// Instead of copying and centring each training fold, the centred system is formed
+// algebraically from the uncentred moments (fp64):
+//   Xc^T Xc = (M_all - M_fold)[x,x] - n_tr * mu mu^T,  mu = (s_all - s_fold) / n_tr.
+#pragma once
+#include "dml_common.cuh"
+
+namespace dml {
+
+// Mpart[fold][split][D][ldm] (fp32) -> Mfold[fold][D][D] (fp64), fixed order over splits
+__global__ void reduce_moments_kernel(const float* Mpart, int splits, int D, int ldm, double* Mfold) {
+  const int fold = blockIdx.z, r = blockIdx.y;
+  const int c = blockIdx.x * blockDim.x + threadIdx.x;
+  if (c >= D) return;
+  double acc = 0.0;
+  for (int s = 0; s < splits; ++s)
+    acc += (double)Mpart[(((int64_t)fold * splits + s) * D + r) * ldm + c];
+  Mfold[((int64_t)fold * D + r) * D + c] = acc;
+}
+
+// Mtot = sum over folds
+__global__ void total_moments_kernel(const double* Mfold, int n_folds, int D, double* Mtot) {
+  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= (int64_t)D * D) return;
+  double acc = 0.0;
+  for (int f = 0; f < n_folds; ++f) acc += Mfold[(int64_t)f * D * D + i];
+  Mtot[i] = acc;
+}
+
+struct RidgeSysParams {
+  int d, T, D;            // D = d + T + 1
+  int n_folds, has_hold;  // systems per candidate = n_folds (+1: hold-out split, moments in slot n_folds)
+  int cand0, n_cand_chunk;
+  const double* Mfold;    // [n_folds (+1)][D][D]; entry n_folds = rows with hold_id == 1
+  const double* Mtot;
+  const double* alpha; const uint8_t* fit_icpt;  // per candidate
+  double* A;              // [systems][d][d]
+  double* B;              // [systems][T][d]  (rhs, overwritten by the solution)
+  double* mu;             // [systems][d + T]
+};
+
+// system index = (cand - cand0) * fits_per_cand + k
+__global__ void ridge_assemble_kernel(const RidgeSysParams p) {
+  const int fits_per_cand = p.n_folds + p.has_hold;
+  const int sys = blockIdx.y, cand = p.cand0 + sys / fits_per_cand, k = sys % fits_per_cand;
+  const int d = p.d, T = p.T, D = p.D;
+  const double* Mf = p.Mfold + (int64_t)k * D * D;
+  const double n_tr = p.Mtot[(int64_t)(D - 1) * D + (D - 1)] - Mf[(int64_t)(D - 1) * D + (D - 1)];
+  const bool ic = p.fit_icpt[cand] != 0;
+  const double alpha = p.alpha[cand];
+  double* A = p.A + (int64_t)sys * d * d;
+  double* B = p.B + (int64_t)sys * T * d;
+  double* mu = p.mu + (int64_t)sys * (d + T);
+  const int64_t total = (int64_t)d * (d + T);
+  for (int64_t e = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; e < total; e += (int64_t)gridDim.x * blockDim.x) {
+    const int i = (int)(e / (d + T)), c = (int)(e % (d + T));
+    const double mi = (p.Mtot[(int64_t)i * D + (D - 1)] - Mf[(int64_t)i * D + (D - 1)]) / n_tr;
+    const double mc = (p.Mtot[(int64_t)c * D + (D - 1)] - Mf[(int64_t)c * D + (D - 1)]) / n_tr;
+    double v = p.Mtot[(int64_t)i * D + c] - Mf[(int64_t)i * D + c];
+    if (ic) v -= n_tr * mi * mc;
+    if (c < d) A[(int64_t)i * d + c] = v + (i == c ? alpha : 0.0);
+    else B[(int64_t)(c - d) * d + i] = v;
+    if (i == 0) mu[c] = ic ? mc : 0.0;
+  }
+}
+
+// In-place lower Cholesky of A (row-major, only the lower triangle is read/written),
+// then L L^T W = B for T right-hand sides.  One block per system.
+__global__ void __launch_bounds__(512) ridge_cholesky_kernel(double* Aall, double* Ball, int d, int T, int* info) {
+  extern __shared__ double colj[];  // [d]
+  __shared__ double piv;
+  double* A = Aall + (int64_t)blockIdx.x * d * d;
+  double* B = Ball + (int64_t)blockIdx.x * T * d;
+  const int nw = blockDim.x >> 5, w = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  for (int j = 0; j < d; ++j) {
+    if (threadIdx.x == 0) {
+      const double a = A[(int64_t)j * d + j];
+      if (!(a > 0.0)) atomicExch(info + blockIdx.x, j + 1);  // not positive definite
+      piv = sqrt(a > 0.0 ? a : 1.0);
+    }
+    __syncthreads();
+    const double pj = piv;
+    for (int i = j + threadIdx.x; i < d; i += blockDim.x) {
+      const double v = (i == j) ? pj : A[(int64_t)i * d + j] / pj;
+      A[(int64_t)i * d + j] = v;
+      colj[i] = v;
+    }
+    __syncthreads();
+    // trailing update, one warp per row: A[i][k] -= L[i][j] L[k][j], j < k <= i
+    for (int i = j + 1 + w; i < d; i += nw) {
+      const double lij = colj[i];
+      double* Ai = A + (int64_t)i * d;
+      for (int k = j + 1 + lane; k <= i; k += 32) Ai[k] -= lij * colj[k];
+    }
+    __syncthreads();
+  }
+  // forward then backward substitution, one right-hand side at a time
+  for (int t = 0; t < T; ++t) {
+    double* b = B + (int64_t)t * d;
+    for (int j = 0; j < d; ++j) {
+      if (threadIdx.x == 0) { piv = b[j] / A[(int64_t)j * d + j]; b[j] = piv; }
+      __syncthreads();
+      const double zj = piv;
+      for (int i = j + 1 + threadIdx.x; i < d; i += blockDim.x) b[i] -= A[(int64_t)i * d + j] * zj;
+      __syncthreads();
+    }
+    for (int j = d - 1; j >= 0; --j) {
+      if (threadIdx.x == 0) { piv = b[j] / A[(int64_t)j * d + j]; b[j] = piv; }
+      __syncthreads();
+      const double wj = piv;
+      for (int i = threadIdx.x; i < j; i += blockDim.x) b[i] -= A[(int64_t)j * d + i] * wj;
+      __syncthreads();
+    }
+  }
+}
+
+// solution -> fp32 coef/intercept outputs and the score-pass operands
+struct RidgeOutParams {
+  int d, T, n_folds, has_hold, cand0, ldw;
+  const double* B; const double* mu;
+  float* coef; float* icpt;        // [n_cand][fits_per_cand][T][d], [..][T]
+  float* Wt; float* bt; int32_t* slot_sel; int32_t* slot_val;   // all fits
+};
+__global__ void ridge_output_kernel(const RidgeOutParams p) {
+  __shared__ double red[33];
+  const int fits_per_cand = p.n_folds + p.has_hold;
+  const int sys = blockIdx.x, t = blockIdx.y, k = sys % fits_per_cand;
+  const int fit = p.cand0 * fits_per_cand + sys, slot = fit * p.T + t;
+  const double* w = p.B + ((int64_t)sys * p.T + t) * p.d;
+  const double* mu = p.mu + (int64_t)sys * (p.d + p.T);
+  double dot = 0.0;
+  for (int j = threadIdx.x; j < p.d; j += blockDim.x) {
+    const float v = (float)w[j];   // coef_ keeps X.dtype
+    p.coef[(int64_t)slot * p.d + j] = v;
+    p.Wt[(int64_t)slot * p.ldw + j] = v;
+    dot += mu[j] * w[j];
+  }
+  dot = block_reduce<false>(dot, red);
+  if (threadIdx.x == 0) {
+    const float b = (float)(mu[p.d + t] - dot);
+    p.icpt[slot] = b; p.bt[slot] = b;
+    p.slot_sel[slot] = (k < p.n_folds) ? 0 : 1;
+    p.slot_val[slot] = (k < p.n_folds) ? k : 1;
+  }
+}
+
+// per-fit test-fold statistics out of the moments: n_test, sum y, sum y^2 (regression)
+__global__ void ridge_teststats_kernel(const double* Mfold, int D, int d, int n_fits, int fits_per_cand, int n_folds,
+                                       long long* n_test, double* sy, double* syy) {
+  const int f = blockIdx.x * blockDim.x + threadIdx.x;
+  if (f >= n_fits) return;
+  const int k = f % fits_per_cand;
+  const double* Mf = Mfold + (int64_t)k * D * D;
+  n_test[f] = (long long)(Mf[(int64_t)(D - 1) * D + (D - 1)] + 0.5);
+  if (sy) sy[f] = Mf[(int64_t)d * D + (D - 1)];
+  if (syy) syy[f] = Mf[(int64_t)d * D + d];
+}
+
+}  // namespace dml

@@ -1,0 +1,76 @@
+"""Row labels for the sweep kernels: CV fold ids and the hold-out split.
+
+``cross_val_score(model, X, y, cv=int)`` (reference: aws-prod/worker/worker.py:326,341)
+resolves an int ``cv`` to an un-shuffled ``StratifiedKFold`` for classifiers and
+``KFold`` for regressors (sklearn/model_selection/_split.py:2697-2776).  The
+kernels take the result as one int8 label per row -- the fold whose test set
+holds the row -- instead of index lists, so no row of X is ever gathered.
+"""
+from __future__ import annotations
+
+import numpy as np
+
+
+def kfold_labels(n: int, n_folds: int) -> np.ndarray:
+    """KFold without shuffle: contiguous blocks, the first ``n % n_folds`` one row
+    longer (_split.py:517-531)."""
+    if not 2 <= n_folds <= n:
+        raise ValueError(f"cv={n_folds} is not usable with {n} samples")
+    sizes = np.full(n_folds, n // n_folds, dtype=np.int64)
+    sizes[: n % n_folds] += 1
+    return np.repeat(np.arange(n_folds, dtype=np.int8), sizes)
+
+
+def stratified_labels(y_idx: np.ndarray, n_folds: int) -> np.ndarray:
+    """StratifiedKFold without shuffle (_split.py:774-842).
+
+    Classes are numbered by first appearance; the per-fold quota of a class is the
+    round-robin count over the sorted labels; within a class, rows keep their order
+    and receive fold ids in blocks.
+    """
+    y_idx = np.asarray(y_idx)
+    n = y_idx.shape[0]
+    _, first, inv = np.unique(y_idx, return_index=True, return_inverse=True)
+    n_classes = first.shape[0]
+    counts = np.bincount(inv, minlength=n_classes)
+    if np.all(n_folds > counts):
+        raise ValueError(f"n_splits={n_folds} cannot be greater than the number of members in each class.")
+    rank_of_class = np.empty(n_classes, dtype=np.int64)
+    rank_of_class[np.argsort(first, kind="stable")] = np.arange(n_classes)
+    enc = rank_of_class[inv]                       # class id by order of appearance
+    cnt = np.bincount(enc, minlength=n_classes)
+    starts = np.concatenate(([0], np.cumsum(cnt)[:-1]))  # offset of each class in sorted order
+    out = np.empty(n, dtype=np.int8)
+    for k in range(n_classes):
+        # rows of class k occupy positions [starts[k], starts[k]+cnt[k]) of the sorted
+        # label vector; position p goes to fold p % n_folds, so the quota of fold f is
+        # the number of such p with p % n_folds == f
+        pos = np.arange(starts[k], starts[k] + cnt[k])
+        quota = np.bincount(pos % n_folds, minlength=n_folds)
+        out[enc == k] = np.repeat(np.arange(n_folds, dtype=np.int8), quota)
+    return out
+
+
+def holdout_labels(n: int, test_size, random_state) -> np.ndarray:
+    """``train_test_split(X, y, test_size=..., random_state=...)`` (worker.py:302 with
+    keyword arguments) as a 0/1 label per row: 1 = test row.
+
+    ShuffleSplit draws ``rng.permutation(n)``; the first n_test entries are the test
+    set (sklearn/model_selection/_split.py:2233-2263, 2365-2441).  Rows beyond
+    n_test + n_train (possible when both sizes are given) are not modelled: the
+    reference only passes test_size.
+    """
+    if isinstance(test_size, float) or (isinstance(test_size, (int, np.integer)) is False):
+        n_test = int(np.ceil(float(test_size) * n))
+    else:
+        n_test = int(test_size)
+    if not 0 < n_test < n:
+        raise ValueError(f"test_size={test_size} leaves an empty train or test set for n={n}")
+    if random_state is None:
+        rng = np.random.mtrand._rand
+    else:
+        rng = np.random.RandomState(int(random_state))
+    perm = rng.permutation(n)
+    lab = np.zeros(n, dtype=np.int8)
+    lab[perm[:n_test]] = 1
+    return lab

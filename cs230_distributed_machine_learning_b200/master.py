@@ -1,0 +1,269 @@
+"""In-process master: job intake, splitter, result aggregation.
+
+Mirrors aws-prod/master/{master.py,task_handler.py,redis_util.py} of the reference
+for the training path only: the Flask routes become methods, Redis becomes a dict,
+the Kafka topics become the scheduler's in-process queues.  Message dicts keep the
+reference's keys so that a maintainer can put the real transports back
+(INTEGRATION.md).
+
+What changes, per BASELINE.json north_star:
+  * splitter: the one-subtask-per-candidate list (task_handler.py:186-236) is
+    regrouped into per-GPU candidate x fold *block* subtasks (``create_blocks``);
+  * aggregation: besides the reference's {results, best_result, completion_time}
+    (task_handler.py:102-114, 254-263) the job result carries cv_results_ /
+    best_params_ / best_score_ / best_index_ formed by GridSearchCV's rules
+    (sklearn/model_selection/_search.py:1208-1294, 862-874).
+"""
+from __future__ import annotations
+
+import copy
+import threading
+import time
+import uuid
+from datetime import datetime
+
+import numpy as np
+from scipy.stats import rankdata
+from sklearn.model_selection import ParameterGrid, ParameterSampler
+
+from . import datasets
+
+
+# --------------------------------------------------------------------------------------
+# splitter
+# --------------------------------------------------------------------------------------
+def create_subtasks(job_config: dict) -> list[dict]:
+    """Reference semantics of task_handler.py:156-252, key for key.
+
+    GridSearchCV -> ParameterGrid order (sorted keys, last key fastest);
+    RandomizedSearchCV -> ParameterSampler(..., random_state=cv_params.random_state or 42)
+    (the client drops the estimator's own random_state, core.py:117-130);
+    plain estimator -> one subtask whose ``parameters`` are the hyperparameters.
+    """
+    job_id = job_config["job_id"]
+    common = {"job_id": job_id, "session_id": job_config["session_id"], "dataset_id": job_config["dataset_id"]}
+    details = job_config["model_details"]
+    train_params = job_config.get("train_params", {})
+    if "search_type" not in details:
+        return [{"subtask_id": f"{job_id}-subtask-1", **common, "model_type": details["model_type"],
+                 "parameters": details["hyperparameters"], "train_params": train_params}]
+    hyper = details["hyperparameters"]
+    base = hyper["base_estimator_params"]
+    cv_params = hyper.get("cv_params", {})
+    search = hyper.get("search_params", {})
+    cv = cv_params.get("cv", 5)
+    if details["search_type"] == "GridSearchCV":
+        combos = list(ParameterGrid(search.get("param_grid", {})))
+    elif details["search_type"] == "RandomizedSearchCV":
+        combos = list(ParameterSampler(search.get("param_distributions", {}), search.get("n_iter", 10),
+                                       random_state=cv_params.get("random_state", 42)))
+    else:
+        combos = []
+    return [{"subtask_id": f"{job_id}-subtask-{i + 1}", **common, "model_type": details["model_type"],
+             "parameters": {**base, **params}, "train_params": {"cv": cv, **train_params}}
+            for i, params in enumerate(combos)]
+
+
+def create_blocks(subtasks: list[dict], n_gpus: int = 1, partition: str = "candidates") -> list[dict]:
+    """Regroup per-candidate subtasks into per-GPU block subtasks.
+
+    A block keeps the subtask keys and adds ``candidates`` [{index, subtask_id,
+    parameters}], ``folds``, ``gpu`` and ``partition``.  "candidates": GPU g gets
+    candidates g, g+G, g+2G, ... (round-robin spreads slow large-C columns);
+    "rows": every GPU gets all candidates and a row shard (needs one process per
+    GPU with NCCL, see bench.py).  A block with a single candidate and all folds is
+    the legacy subtask.
+    """
+    if not subtasks:
+        return []
+    n_gpus = max(1, min(n_gpus, len(subtasks))) if partition == "candidates" else max(1, n_gpus)
+    first = subtasks[0]
+    cv = first.get("train_params", {}).get("cv", 5)
+    blocks = []
+    for g in range(n_gpus):
+        mine = subtasks[g::n_gpus] if partition == "candidates" else subtasks
+        own = [i for i in range(len(subtasks))][g::n_gpus] if partition == "candidates" else list(range(len(subtasks)))
+        blocks.append({
+            "subtask_id": f"{first['job_id']}-block-{g + 1}",
+            "job_id": first["job_id"], "session_id": first["session_id"], "dataset_id": first["dataset_id"],
+            "model_type": first["model_type"], "train_params": copy.deepcopy(first.get("train_params", {})),
+            "candidates": [{"index": i, "subtask_id": s["subtask_id"], "parameters": s["parameters"]}
+                           for i, s in zip(own, mine)],
+            "folds": list(range(cv)) if isinstance(cv, int) else cv,
+            "gpu": g, "partition": partition, "n_shards": n_gpus if partition == "rows" else 1,
+        })
+    return blocks
+
+
+# --------------------------------------------------------------------------------------
+# aggregation
+# --------------------------------------------------------------------------------------
+def aggregate_results(results: list[dict]):
+    """Best result = highest mean_cv_score; NaN (failed fits) ranks last; ties go to
+    the lowest candidate index.  The reference sorts by mean_cv_score descending and
+    takes the first (task_handler.py:254-263) but feeds it Redis KEYS order
+    (:76), which makes ties nondeterministic; sklearn's rule is used instead."""
+    if not results:
+        return None
+    scores = np.array([_nan_if_none(r.get("mean_cv_score")) for r in results], dtype=np.float64)
+    if np.isnan(scores).all():
+        return results[0]
+    return results[int(np.nanargmax(scores))]  # nanargmax returns the first maximum
+
+
+def _nan_if_none(v):
+    return np.nan if v is None else float(v)
+
+
+def build_cv_results(candidates: list[dict], fold_scores) -> dict:
+    """cv_results_-style dict + best_* (sklearn _search.py:1208-1294, 862-874)."""
+    a = np.asarray(fold_scores, dtype=np.float64)
+    n_cand, n_folds = a.shape
+    mean = np.average(a, axis=1)
+    std = np.sqrt(np.average((a - mean[:, None]) ** 2, axis=1))
+    if np.isnan(mean).all():
+        rank = np.ones(n_cand, dtype=np.int32)
+    else:
+        filled = np.nan_to_num(mean, nan=np.nanmin(mean) - 1.0)
+        rank = rankdata(-filled, method="min").astype(np.int32)
+    best = int(rank.argmin())
+    res = {f"split{k}_test_score": a[:, k].tolist() for k in range(n_folds)}
+    res.update(mean_test_score=mean.tolist(), std_test_score=std.tolist(), rank_test_score=rank.tolist(),
+               params=candidates)
+    keys = sorted({k for c in candidates for k in c})
+    for k in keys:
+        res[f"param_{k}"] = [c.get(k) for c in candidates]
+    return {"cv_results_": res, "best_index_": best, "best_params_": candidates[best],
+            "best_score_": float(mean[best])}
+
+
+# --------------------------------------------------------------------------------------
+# master service
+# --------------------------------------------------------------------------------------
+class Master:
+    """Session/job state + the routes the client uses (master.py:27-62, 115-268)."""
+
+    def __init__(self, scheduler, n_gpus: int | None = None, partition: str = "candidates"):
+        self.scheduler = scheduler
+        self.n_gpus = n_gpus
+        self.partition = partition
+        self.sessions: set[str] = set()
+        self.jobs: dict[tuple[str, str], dict] = {}
+        self.lock = threading.Lock()
+        scheduler.attach_master(self)
+
+    # /create_session
+    def create_session(self) -> dict:
+        sid = str(uuid.uuid4())
+        with self.lock:
+            self.sessions.add(sid)
+        return {"session_id": sid}
+
+    # /check_data and /download_data (local arrays / CSV only)
+    def check_data(self, session_id: str, dataset_name: str) -> dict:
+        return {"exists": datasets.has_dataset(dataset_name), "dataset_name": dataset_name}
+
+    # /train and /train_status
+    def train(self, session_id: str, payload: dict) -> dict:
+        with self.lock:
+            if session_id not in self.sessions:
+                return {"status": "error", "message": "Invalid or expired session_id"}
+        if not datasets.has_dataset(payload["dataset_id"]):
+            return {"status": "error", "message": f"Dataset '{payload['dataset_id']}' not found"}
+        subtasks = create_subtasks(payload)
+        if not subtasks:
+            return {"status": "error", "message": "No subtasks created"}
+        details = payload["model_details"]
+        search = details.get("hyperparameters", {}).get("search_params", {}) if "search_type" in details else {}
+        base = details.get("hyperparameters", {}).get("base_estimator_params", {}) if "search_type" in details else {}
+        job = {"job_id": payload["job_id"], "session_id": session_id, "subtasks": subtasks,
+               "results": {}, "failed": {}, "status": "pending", "created_at": time.time(),
+               "search_type": details.get("search_type"), "base_params": base, "search_params": search,
+               "metrics": [], "done": threading.Event()}
+        with self.lock:
+            self.jobs[(session_id, payload["job_id"])] = job
+        n_gpus = self.n_gpus or max(1, self.scheduler.n_workers())
+        for block in create_blocks(subtasks, n_gpus=n_gpus, partition=self.partition):
+            self.scheduler.submit(block)       # topic "tasks"
+        return {"status": "Training started", "job_id": payload["job_id"], "total_subtasks": len(subtasks)}
+
+    # topic "result" consumer (task_handler.py:18-123)
+    def on_result(self, message: dict) -> None:
+        key = (message.get("session_id"), message.get("job_id"))
+        with self.lock:
+            job = self.jobs.get(key) or next((j for (s, jid), j in self.jobs.items() if jid == message.get("job_id")), None)
+            if job is None:
+                return
+            entries = message["result"] if isinstance(message.get("result"), list) else [message]
+            for e in entries:
+                sid = e.get("subtask_id", message.get("subtask_id"))
+                if e.get("status", message.get("status")) == "completed":
+                    job["results"][sid] = e.get("result", e)
+                else:
+                    job["failed"][sid] = e.get("error", message.get("error", "failed"))
+            total = len(job["subtasks"])
+            finished = len(job["results"]) + len(job["failed"])
+            job["status"] = str(len(job["results"]) / total * 100.0)
+            if finished == total:
+                self._finish(job)
+
+    def on_metrics(self, record: dict) -> None:
+        with self.lock:
+            for (s, jid), job in self.jobs.items():
+                if record.get("subtask_id", "").startswith(jid):
+                    job["metrics"].append(record)
+
+    def _finish(self, job: dict) -> None:
+        ordered = []
+        for st in job["subtasks"]:
+            r = job["results"].get(st["subtask_id"])
+            if r is None:  # failed candidate: error_score = nan row, like GridSearchCV (_search.py:1251-1265)
+                cv = st.get("train_params", {}).get("cv", 5)
+                r = {"cv_scores": [float("nan")] * (cv if isinstance(cv, int) else 5),
+                     "mean_cv_score": float("nan"), "parameters": st["parameters"],
+                     "error": job["failed"].get(st["subtask_id"])}
+            ordered.append(r)
+        out = {"results": ordered, "best_result": aggregate_results(ordered), "completion_time": time.time()}
+        if job["search_type"]:
+            keys = _searched(job)
+            cands = [{k: st["parameters"][k] for k in keys if k in st["parameters"]} for st in job["subtasks"]]
+            nf = max(len(r.get("cv_scores", [])) for r in ordered)
+            scores = [list(r.get("cv_scores", [])) + [float("nan")] * (nf - len(r.get("cv_scores", []))) for r in ordered]
+            out.update(build_cv_results(cands, scores))
+        job["job_result"] = out
+        job["status"] = "completed"
+        job["done"].set()
+
+    # /check_status (master.py:115-167)
+    def check_status(self, session_id: str, job_id: str) -> dict:
+        with self.lock:
+            job = self.jobs.get((session_id, job_id))
+            if job is None:
+                return {"status": "error", "message": f"job {job_id} not found"}
+            total = len(job["subtasks"])
+            pending = total - len(job["results"]) - len(job["failed"])
+            resp = {"session_id": session_id, "tasks_pending": pending, "job_id": job_id,
+                    "job_status": job["status"], "total_subtasks": total}
+            if job["status"] == "completed":
+                resp["job_result"] = job["job_result"]
+                if total > 1:
+                    resp["best_result"] = job["job_result"]["best_result"]
+            return resp
+
+    # /metrics (master.py:294-340): one resource record per finished block
+    def metrics(self, session_id: str, job_id: str) -> list:
+        with self.lock:
+            job = self.jobs.get((session_id, job_id))
+            return list(job["metrics"]) if job else []
+
+    def wait(self, session_id: str, job_id: str, timeout: float | None = None) -> bool:
+        job = self.jobs.get((session_id, job_id))
+        return bool(job and job["done"].wait(timeout))
+
+
+def _searched(job) -> list[str]:
+    sp = job.get("search_params") or {}
+    grid = sp.get("param_grid") or sp.get("param_distributions") or {}
+    if isinstance(grid, list):
+        return sorted({k for g in grid for k in g})
+    return sorted(grid)

@@ -1,0 +1,130 @@
+"""Scheduler shim: static GPU placement behind the reference's worker protocol.
+
+The reference scheduler (aws-prod/scheduler/{scheduler.py,scheduler_service.py})
+registers workers over HTTP (/subscribe, /heartbeat, /unsubscribe), predicts a
+runtime per subtask with a GBRT and re-keys each message to the worker that
+minimises load/speed + est/speed.  On one box with 1-8 identical B200s the
+placement problem is static: a block subtask already
+names its GPU, so this shim keeps the registration / heartbeat / keyed-delivery
+contract (and the dead-worker requeue, scheduler_service.py:205-247) and drops
+the predictor.  Kafka topics "tasks"/"train"/"result"/"metrics" become in-process
+queues and callbacks carrying the same dicts.
+"""
+from __future__ import annotations
+
+import queue
+import threading
+import time
+import uuid
+
+HEARTBEAT_TIMEOUT_S = 10.0   # scheduler_service.py:214
+
+
+class Scheduler:
+    def __init__(self):
+        self.lock = threading.Lock()
+        self.workers: dict[str, dict] = {}
+        self.master = None
+        self.backlog: list[dict] = []
+
+    def attach_master(self, master) -> None:
+        self.master = master
+
+    # POST /subscribe {mem_capacity_mb, host} -> {status, worker_id}   (scheduler.py:105-117)
+    def subscribe(self, mem_capacity_mb: int = 0, host: str = "localhost", gpu: int | None = None) -> dict:
+        wid = f"worker-{uuid.uuid4().hex[:8]}"
+        with self.lock:
+            self.workers[wid] = {"queue": queue.Queue(), "last_seen": time.time(), "gpu": gpu,
+                                 "mem_capacity_mb": mem_capacity_mb, "host": host, "inflight": {}, "done": 0}
+            backlog, self.backlog = self.backlog, []
+        for task in backlog:
+            self.submit(task)
+        return {"status": "subscribed", "worker_id": wid}
+
+    # POST /heartbeat {worker_id}
+    def heartbeat(self, worker_id: str) -> dict:
+        with self.lock:
+            w = self.workers.get(worker_id)
+            if w is None:
+                return {"status": "unknown_worker"}
+            w["last_seen"] = time.time()
+        return {"status": "ok"}
+
+    # POST /unsubscribe {worker_id}: hand its queue to the survivors (scheduler.py:120-139)
+    def unsubscribe(self, worker_id: str) -> dict:
+        with self.lock:
+            w = self.workers.pop(worker_id, None)
+        if w is None:
+            return {"status": "unknown_worker"}
+        self._requeue(w)
+        return {"status": "unsubscribed"}
+
+    def n_workers(self) -> int:
+        with self.lock:
+            return len(self.workers)
+
+    def get_queue(self, worker_id: str) -> queue.Queue:
+        return self.workers[worker_id]["queue"]
+
+    # topic "tasks" -> topic "train" keyed by worker id (scheduler_service.py:249-293)
+    def submit(self, task: dict) -> str | None:
+        with self.lock:
+            if not self.workers:
+                self.backlog.append(task)
+                return None
+            wid = self._select_worker(task)
+            w = self.workers[wid]
+            w["inflight"][task["subtask_id"]] = task
+            w["queue"].put((wid, task))
+        return wid
+
+    def _select_worker(self, task: dict) -> str:
+        gpu = task.get("gpu")
+        ids = sorted(self.workers)
+        for wid in ids:                       # the block names its GPU
+            if gpu is not None and self.workers[wid]["gpu"] == gpu:
+                return wid
+        return min(ids, key=lambda w: (len(self.workers[w]["inflight"]), w))   # least loaded
+
+    # topics "result" / "metrics"
+    def publish_result(self, worker_id: str, message: dict) -> None:
+        with self.lock:
+            w = self.workers.get(worker_id)
+            if w is not None:
+                w["inflight"].pop(message.get("subtask_id"), None)
+                w["done"] += 1
+        if self.master is not None:
+            self.master.on_result(message)
+
+    def publish_metrics(self, record: dict) -> None:
+        if self.master is not None:
+            self.master.on_metrics(record)
+
+    # monitor (scheduler_service.py:205-247)
+    def reap_dead_workers(self, now: float | None = None) -> list[str]:
+        now = time.time() if now is None else now
+        with self.lock:
+            dead = [wid for wid, w in self.workers.items() if now - w["last_seen"] > HEARTBEAT_TIMEOUT_S]
+            gone = [self.workers.pop(wid) for wid in dead]
+        for w in gone:
+            self._requeue(w)
+        return dead
+
+    def _requeue(self, w: dict) -> None:
+        tasks = list(w["inflight"].values())
+        while True:
+            try:
+                _, t = w["queue"].get_nowait()
+            except queue.Empty:
+                break
+            if t is not None and t["subtask_id"] not in w["inflight"]:
+                tasks.append(t)
+        for t in tasks:
+            t = dict(t)
+            t.pop("gpu", None)               # any surviving GPU may take it
+            self.submit(t)
+
+    def workers_view(self) -> dict:      # GET /workers
+        with self.lock:
+            return {wid: {"gpu": w["gpu"], "inflight": len(w["inflight"]), "done": w["done"],
+                          "last_seen": w["last_seen"]} for wid, w in self.workers.items()}

@@ -1,0 +1,185 @@
+"""Device-level sweep API: torch tensors in, numpy results out, all arithmetic in
+the sm_100a library behind include/dml_b200.h.
+
+PyTorch is used for device memory, streams and the NCCL bootstrap only.  One
+``SweepSolver`` per (process, GPU).
+"""
+from __future__ import annotations
+
+import ctypes as C
+from dataclasses import dataclass
+
+import numpy as np
+import torch
+
+from . import _cabi
+
+
+def _ptr(t):
+    return C.c_void_p(t.data_ptr()) if t is not None else C.c_void_p(None)
+
+
+@dataclass
+class DeviceDataset:
+    """A dataset resident in HBM: X fp32 row-major, labels, row masks."""
+    X: torch.Tensor                 # (n, d) float32, C-contiguous
+    y_cls: torch.Tensor | None      # (n,) int32 class index, classifiers
+    y_reg: torch.Tensor | None      # (n,) float32, regressors
+    classes: np.ndarray | None      # sorted unique labels (sklearn classes_)
+    n: int
+    d: int
+
+
+class SweepSolver:
+    def __init__(self, device: int = 0):
+        if not torch.cuda.is_available():
+            raise RuntimeError("SweepSolver needs a CUDA device (B200, sm_100a); there is no CPU fallback")
+        self.device = torch.device("cuda", device)
+        torch.cuda.set_device(self.device)
+        self.stream = torch.cuda.current_stream(self.device)
+        self.ctx = _cabi.Context(device, self.stream.cuda_stream)
+        self.lib = self.ctx.lib
+        self.h2d_bytes = 0
+        self.d2h_bytes = 0
+
+    # ---- plumbing -------------------------------------------------------------------
+    def to_device(self, a, dtype=None, pin: bool = False) -> torch.Tensor:
+        if isinstance(a, torch.Tensor):
+            t = a
+            if dtype is not None and t.dtype != dtype:
+                t = t.to(dtype)
+            if t.device != self.device:
+                self.h2d_bytes += t.numel() * t.element_size()
+                t = t.to(self.device, non_blocking=True)
+            return t.contiguous()
+        arr = np.ascontiguousarray(a)
+        t = torch.from_numpy(arr)
+        if dtype is not None and t.dtype != dtype:
+            t = t.to(dtype)
+        if pin:
+            t = t.pin_memory()
+        self.h2d_bytes += t.numel() * t.element_size()
+        return t.to(self.device, non_blocking=True)
+
+    def to_host(self, t: torch.Tensor) -> np.ndarray:
+        self.d2h_bytes += t.numel() * t.element_size()
+        return t.cpu().numpy()
+
+    def upload_dataset(self, X, y, classifier: bool) -> DeviceDataset:
+        """X (n, d) any float dtype -> fp32 on device; y -> class indices or fp32."""
+        Xd = self.to_device(X, torch.float32)
+        if Xd.dim() != 2:
+            raise ValueError("X must be 2-D")
+        n, d = Xd.shape
+        if classifier:
+            if isinstance(y, torch.Tensor):
+                y = y.cpu().numpy()
+            classes, idx = np.unique(np.asarray(y), return_inverse=True)
+            yc = self.to_device(idx.astype(np.int32), torch.int32)
+            return DeviceDataset(Xd, yc, None, classes, n, d)
+        yr = self.to_device(y, torch.float32)
+        return DeviceDataset(Xd, None, yr, None, n, d)
+
+    def init_comm(self, n_ranks: int, rank: int, unique_id: bytes):
+        self.ctx.init_comm(n_ranks, rank, unique_id)
+
+    # ---- sweeps ---------------------------------------------------------------------
+    def logreg_sweep(self, ds: DeviceDataset, fold_id, n_folds: int, C_vals, tol, fit_intercept, max_iter,
+                     hold_id=None, use_tensor_cores: int = -1, want_scores: bool = True):
+        """All candidates x (n_folds CV fits [+ hold-out fit]).  Returns dict of numpy arrays
+        shaped [n_cand, fits_per_cand, ...]."""
+        n_cand = len(C_vals)
+        n_classes = int(len(ds.classes))
+        T = 1 if n_classes == 2 else n_classes
+        fpc = n_folds + (1 if hold_id is not None else 0)
+        F = n_cand * fpc
+        dev = self.device
+        fold_d = self.to_device(fold_id, torch.int8)
+        hold_d = self.to_device(hold_id, torch.int8) if hold_id is not None else None
+        C_d = self.to_device(np.asarray(C_vals, dtype=np.float64))
+        tol_d = self.to_device(np.broadcast_to(np.asarray(tol, dtype=np.float64), (n_cand,)).copy())
+        fi_d = self.to_device(np.broadcast_to(np.asarray(fit_intercept, dtype=np.uint8), (n_cand,)).copy())
+        mi_d = self.to_device(np.broadcast_to(np.asarray(max_iter, dtype=np.int32), (n_cand,)).copy())
+        coef = torch.empty((F, T, ds.d), dtype=torch.float32, device=dev)
+        icpt = torch.empty((F, T), dtype=torch.float32, device=dev)
+        n_iter = torch.empty(F, dtype=torch.int32, device=dev)
+        status = torch.empty(F, dtype=torch.int32, device=dev)
+        nfev = torch.empty(F, dtype=torch.int32, device=dev)
+        correct = torch.empty(F, dtype=torch.int64, device=dev) if want_scores else None
+        n_test = torch.empty(F, dtype=torch.int64, device=dev) if want_scores else None
+        rounds = C.c_int32(0)
+        rc = self.lib.dml_logreg_sweep(
+            self.ctx.handle, _ptr(ds.X), ds.n, ds.d, ds.X.stride(0), _ptr(ds.y_cls), n_classes,
+            _ptr(fold_d), n_folds, _ptr(hold_d), _ptr(C_d), _ptr(tol_d), _ptr(fi_d), _ptr(mi_d), n_cand,
+            _ptr(coef), _ptr(icpt), _ptr(n_iter), _ptr(status), _ptr(nfev), _ptr(correct), _ptr(n_test),
+            C.byref(rounds), int(use_tensor_cores))
+        self.ctx.check(rc, "dml_logreg_sweep")
+        out = dict(coef=self.to_host(coef).reshape(n_cand, fpc, T, ds.d),
+                   intercept=self.to_host(icpt).reshape(n_cand, fpc, T),
+                   n_iter=self.to_host(n_iter).reshape(n_cand, fpc),
+                   status=self.to_host(status).reshape(n_cand, fpc),
+                   nfev=self.to_host(nfev).reshape(n_cand, fpc),
+                   rounds=int(rounds.value), timing=self.ctx.last_timing())
+        if want_scores:
+            out["correct"] = self.to_host(correct).reshape(n_cand, fpc)
+            out["n_test"] = self.to_host(n_test).reshape(n_cand, fpc)
+        return out
+
+    def ridge_sweep(self, ds: DeviceDataset, fold_id, n_folds: int, alphas, fit_intercept, classifier: bool,
+                    hold_id=None, use_tensor_cores: int = -1):
+        n_cand = len(alphas)
+        n_classes = int(len(ds.classes)) if classifier else 0
+        T = (1 if n_classes == 2 else n_classes) if classifier else 1
+        fpc = n_folds + (1 if hold_id is not None else 0)
+        F = n_cand * fpc
+        dev = self.device
+        fold_d = self.to_device(fold_id, torch.int8)
+        hold_d = self.to_device(hold_id, torch.int8) if hold_id is not None else None
+        a_d = self.to_device(np.asarray(alphas, dtype=np.float64))
+        fi_d = self.to_device(np.broadcast_to(np.asarray(fit_intercept, dtype=np.uint8), (n_cand,)).copy())
+        coef = torch.empty((F, T, ds.d), dtype=torch.float32, device=dev)
+        icpt = torch.empty((F, T), dtype=torch.float32, device=dev)
+        n_test = torch.empty(F, dtype=torch.int64, device=dev)
+        info = torch.empty(F, dtype=torch.int32, device=dev)
+        correct = torch.empty(F, dtype=torch.int64, device=dev) if classifier else None
+        sse = torch.empty(F, dtype=torch.float64, device=dev) if not classifier else None
+        sy = torch.empty(F, dtype=torch.float64, device=dev) if not classifier else None
+        syy = torch.empty(F, dtype=torch.float64, device=dev) if not classifier else None
+        rc = self.lib.dml_ridge_sweep(
+            self.ctx.handle, _ptr(ds.X), ds.n, ds.d, ds.X.stride(0), _ptr(ds.y_reg), _ptr(ds.y_cls),
+            n_classes, 1 if classifier else 0, _ptr(fold_d), n_folds, _ptr(hold_d), _ptr(a_d), _ptr(fi_d), n_cand,
+            _ptr(coef), _ptr(icpt), _ptr(correct), _ptr(n_test), _ptr(sse), _ptr(sy), _ptr(syy), _ptr(info),
+            int(use_tensor_cores))
+        self.ctx.check(rc, "dml_ridge_sweep")
+        out = dict(coef=self.to_host(coef).reshape(n_cand, fpc, T, ds.d),
+                   intercept=self.to_host(icpt).reshape(n_cand, fpc, T),
+                   n_test=self.to_host(n_test).reshape(n_cand, fpc),
+                   info=self.to_host(info).reshape(n_cand, fpc), timing=self.ctx.last_timing())
+        if classifier:
+            out["correct"] = self.to_host(correct).reshape(n_cand, fpc)
+        else:
+            out["sse"] = self.to_host(sse).reshape(n_cand, fpc)
+            out["sy"] = self.to_host(sy).reshape(n_cand, fpc)
+            out["syy"] = self.to_host(syy).reshape(n_cand, fpc)
+        return out
+
+    def score(self, ds: DeviceDataset, fold_id, W, b, mask_sel, mask_val, T: int, hold_id=None):
+        """Counts / squared errors of given coefficients (dml_score)."""
+        W_d = self.to_device(np.ascontiguousarray(W, dtype=np.float32))
+        b_d = self.to_device(np.ascontiguousarray(b, dtype=np.float32))
+        n_slots = W_d.shape[0]
+        sel_d = self.to_device(np.asarray(mask_sel, dtype=np.int32))
+        val_d = self.to_device(np.asarray(mask_val, dtype=np.int32))
+        fold_d = self.to_device(fold_id, torch.int8)
+        hold_d = self.to_device(hold_id, torch.int8) if hold_id is not None else None
+        cls = ds.y_cls is not None
+        correct = torch.empty(n_slots // T, dtype=torch.int64, device=self.device) if cls else None
+        sse = torch.empty(n_slots, dtype=torch.float64, device=self.device) if not cls else None
+        rc = self.lib.dml_score(self.ctx.handle, _ptr(ds.X), ds.n, ds.d, ds.X.stride(0), _ptr(ds.y_cls),
+                                _ptr(ds.y_reg), _ptr(fold_d), _ptr(hold_d), _ptr(W_d), _ptr(b_d), _ptr(sel_d),
+                                _ptr(val_d), n_slots, T, _ptr(correct), _ptr(sse))
+        self.ctx.check(rc, "dml_score")
+        return self.to_host(correct) if cls else self.to_host(sse)
+
+    def close(self):
+        self.ctx.close()

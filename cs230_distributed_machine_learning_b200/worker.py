@@ -1,0 +1,352 @@
+"""Worker: consumes (block) subtasks and runs the fit-and-score body.
+
+Counterpart of aws-prod/worker/worker.py.  The loop (register, heartbeat every
+5 s, consume only messages keyed to this worker, publish ``metrics`` then
+``result``; worker.py:156-286) is kept; the body of ``train_model``
+(worker.py:289-363: 1 hold-out fit + predict/score + 5 more fits inside
+``cross_val_score``, per candidate, through scikit-learn) is replaced for
+LogisticRegression(lbfgs) / Ridge / RidgeClassifier by ONE batched call into the
+sm_100a library for every candidate and fold of the block.
+
+Executors
+  "b200"    the CUDA path.  Raises if the library or a B200 is missing -- never
+            falls back to the CPU.
+  "sklearn" the reference's own path (scikit-learn on host cores), kept for the
+            model types the reference registry lists and the GPU path does not
+            cover (worker.py:36-57) and for float64 data (BASELINE.json config 1
+            "runs on CPU": sklearn computes float64 inputs in float64, the GPU
+            kernels are fp32 / 3xTF32, and SURVEY.md 8c shows ill-conditioned
+            float64 problems cannot be tracked at that precision).
+``train_params["executor"]`` or $DML_EXECUTOR picks one; the default "auto" sends a
+candidate to "b200" exactly when the model/solver is covered and X is float32.
+"""
+from __future__ import annotations
+
+import inspect
+import os
+import threading
+import time
+import warnings
+
+import numpy as np
+
+from . import datasets, folds
+
+HEARTBEAT_INTERVAL_S = 5.0   # worker.py:33
+
+MODEL_IMPORTS = {   # worker.py:36-57 plus the two north-star models
+    "RandomForestClassifier": "sklearn.ensemble", "RandomForestRegressor": "sklearn.ensemble",
+    "LogisticRegression": "sklearn.linear_model", "SVC": "sklearn.svm", "SVR": "sklearn.svm",
+    "GradientBoostingClassifier": "sklearn.ensemble", "GradientBoostingRegressor": "sklearn.ensemble",
+    "KNeighborsClassifier": "sklearn.neighbors", "KNeighborsRegressor": "sklearn.neighbors",
+    "LinearRegression": "sklearn.linear_model", "Ridge": "sklearn.linear_model",
+    "RidgeClassifier": "sklearn.linear_model",
+}
+GPU_MODELS = ("LogisticRegression", "Ridge", "RidgeClassifier")
+
+
+def get_model_instance(algorithm_name: str, parameters: dict):
+    """worker.py:436-455 without exec/eval.  Keys the installed class does not know
+    (e.g. ``multi_class`` sent by an older client, library_testing.ipynb:640) are dropped."""
+    if algorithm_name not in MODEL_IMPORTS:
+        raise ValueError(f"Unsupported model: {algorithm_name}")
+    module = __import__(MODEL_IMPORTS[algorithm_name], fromlist=[algorithm_name])
+    cls = getattr(module, algorithm_name)
+    known = set(inspect.signature(cls.__init__).parameters) - {"self"}
+    return cls(**{k: v for k, v in parameters.items() if k in known})
+
+
+def gpu_eligible(model_type: str, params: dict) -> tuple[bool, str]:
+    """Does the batched GPU solver reproduce this estimator configuration?"""
+    p = params
+    if model_type == "LogisticRegression":
+        if p.get("solver", "lbfgs") != "lbfgs":
+            return False, f"solver={p.get('solver')!r}"
+        if p.get("penalty", "deprecated") not in ("deprecated", "l2"):
+            return False, f"penalty={p.get('penalty')!r}"
+        if p.get("l1_ratio", 0.0) not in (0, 0.0, None):
+            return False, "l1_ratio != 0"
+        if p.get("class_weight") is not None or p.get("dual") or p.get("warm_start"):
+            return False, "class_weight/dual/warm_start"
+        c = p.get("C", 1.0)
+        if not (isinstance(c, (int, float)) and np.isfinite(c) and c > 0):
+            return False, "C must be finite and positive"
+        return True, ""
+    if model_type in ("Ridge", "RidgeClassifier"):
+        if p.get("solver", "auto") not in ("auto", "cholesky"):
+            return False, f"solver={p.get('solver')!r}"
+        if p.get("positive") or p.get("class_weight") is not None:
+            return False, "positive/class_weight"
+        a = p.get("alpha", 1.0)
+        if not (isinstance(a, (int, float)) and np.isfinite(a) and a >= 0):
+            return False, "alpha must be a finite scalar"
+        return True, ""
+    return False, "model type not covered by the GPU path"
+
+
+def _executor_choice(task: dict) -> str:
+    return str(task.get("train_params", {}).get("executor") or os.environ.get("DML_EXECUTOR", "auto")).lower()
+
+
+# ---------------------------------------------------------------------------------------
+# sklearn executor: the reference's body, one candidate at a time
+# ---------------------------------------------------------------------------------------
+def train_candidate_sklearn(model_type: str, parameters: dict, train_params: dict, X, y, subtask_id: str) -> dict:
+    """worker.py:289-363 with the SURVEY.md 3.4 repairs (keyword train_test_split
+    arguments, optional hold-out, cv from train_params)."""
+    from sklearn.base import is_classifier
+    from sklearn.exceptions import ConvergenceWarning
+    from sklearn.metrics import accuracy_score, mean_squared_error, r2_score
+    from sklearn.model_selection import cross_val_score, train_test_split
+    model = get_model_instance(model_type, parameters)
+    clf = is_classifier(model)
+    results = {}
+    with warnings.catch_warnings():
+        warnings.simplefilter("ignore", ConvergenceWarning)
+        if "test_size" in train_params:
+            Xtr, Xte, ytr, yte = train_test_split(X, y, test_size=train_params["test_size"],
+                                                  random_state=train_params.get("random_state"))
+            t0 = time.time()
+            model.fit(Xtr, ytr)
+            results["training_time"] = time.time() - t0
+            pred = model.predict(Xte)
+            if clf:
+                results["accuracy"] = float(accuracy_score(yte, pred))
+            else:
+                results["r2_score"] = float(r2_score(yte, pred))
+                results["mean_squared_error"] = float(mean_squared_error(yte, pred))
+        t0 = time.time()
+        scores = cross_val_score(model, X, y, cv=train_params.get("cv", 5), scoring="accuracy" if clf else "r2",
+                                 error_score="raise")
+        results.setdefault("training_time", (time.time() - t0) / max(1, len(scores)))
+    results["cv_scores"] = scores.tolist()
+    results["mean_cv_score"] = float(scores.mean())
+    results["model_id"] = f"{subtask_id}_model"
+    results["model_path"] = None
+    results["parameters"] = parameters
+    results["executor"] = "sklearn"
+    return results
+
+
+# ---------------------------------------------------------------------------------------
+# b200 executor: every eligible candidate x fold of the block in one library call
+# ---------------------------------------------------------------------------------------
+class GpuExecutor:
+    """Owns the SweepSolver of one GPU and the datasets resident on it."""
+
+    def __init__(self, gpu: int = 0):
+        from .solver import SweepSolver   # raises without CUDA: no CPU fallback
+        self.gpu = gpu
+        self.solver = SweepSolver(gpu)
+        self.resident: dict[tuple[str, bool], object] = {}
+        self.lock = threading.Lock()
+
+    def drop_resident(self):
+        """Forget device copies (the next job pays the host->device copy again)."""
+        with self.lock:
+            self.resident.clear()
+
+    def dataset(self, name: str, classifier: bool):
+        key = (name, classifier)
+        if key not in self.resident:   # the reference re-parses the CSV per subtask (worker.py:425)
+            X, y = datasets.get_dataset(name)
+            self.resident[key] = self.solver.upload_dataset(X, y, classifier)
+        return self.resident[key]
+
+    def run(self, model_type: str, cands: list[dict], train_params: dict, dataset_id: str, model_dir: str) -> list[dict]:
+        """cands: [{index, subtask_id, parameters}] -> result dict per candidate (A9 shape)."""
+        classifier = model_type != "Ridge"
+        with self.lock:
+            ds = self.dataset(dataset_id, classifier)
+            X_host, y_host = datasets.get_dataset(dataset_id)
+            cv = train_params.get("cv", 5)
+            if not isinstance(cv, int):
+                raise ValueError("the GPU executor takes an integer cv (un-shuffled (Stratified)KFold)")
+            if classifier:
+                _, y_idx = np.unique(np.asarray(y_host), return_inverse=True)
+                fold = folds.stratified_labels(y_idx, cv)
+            else:
+                fold = folds.kfold_labels(ds.n, cv)
+            hold = None
+            if "test_size" in train_params:
+                hold = folds.holdout_labels(ds.n, train_params["test_size"], train_params.get("random_state"))
+            P = [c["parameters"] for c in cands]
+            fi = [bool(p.get("fit_intercept", True)) for p in P]
+            t0 = time.time()
+            if model_type == "LogisticRegression":
+                out = self.solver.logreg_sweep(
+                    ds, fold, cv, [float(p.get("C", 1.0)) for p in P], [float(p.get("tol", 1e-4)) for p in P], fi,
+                    [int(p.get("max_iter", 100)) for p in P], hold_id=hold)
+            else:
+                out = self.solver.ridge_sweep(ds, fold, cv, [float(p.get("alpha", 1.0)) for p in P], fi,
+                                              classifier=classifier, hold_id=hold)
+            wall = time.time() - t0
+        n_fits = len(cands) * (cv + (hold is not None))
+        results = []
+        for i, c in enumerate(cands):
+            r = {}
+            if classifier:
+                sc = out["correct"][i] / out["n_test"][i]        # float64 count / n_test (A14)
+            else:
+                sst = out["syy"][i] - out["sy"][i] ** 2 / out["n_test"][i]
+                sc = 1.0 - out["sse"][i] / sst
+            cvs = sc[:cv]
+            if hold is not None:
+                if classifier:
+                    r["accuracy"] = float(sc[cv])
+                else:
+                    r["r2_score"] = float(sc[cv])
+                    r["mean_squared_error"] = float(out["sse"][i][cv] / out["n_test"][i][cv])
+            r["cv_scores"] = [float(v) for v in cvs]
+            r["mean_cv_score"] = float(np.mean(cvs))
+            r["training_time"] = wall / n_fits
+            r["model_id"] = f"{c['subtask_id']}_model"
+            r["model_path"] = None
+            if hold is not None and model_dir:
+                os.makedirs(model_dir, exist_ok=True)
+                path = os.path.join(model_dir, f"{r['model_id']}.npz")
+                np.savez(path, coef=out["coef"][i][cv], intercept=out["intercept"][i][cv],
+                         classes=ds.classes if classifier else np.zeros(0), model_type=model_type)
+                r["model_path"] = path
+            r["parameters"] = c["parameters"]
+            r["executor"] = "b200"
+            if model_type == "LogisticRegression":
+                r["n_iter"] = [int(v) for v in out["n_iter"][i]]
+                r["fit_status"] = [int(v) for v in out["status"][i]]
+            results.append(r)
+        self.last_timing = out["timing"]
+        return results
+
+
+_EXECUTORS: dict[int, GpuExecutor] = {}
+_EXEC_LOCK = threading.Lock()
+
+
+def gpu_executor(gpu: int = 0) -> GpuExecutor:
+    with _EXEC_LOCK:
+        if gpu not in _EXECUTORS:
+            _EXECUTORS[gpu] = GpuExecutor(gpu)
+        return _EXECUTORS[gpu]
+
+
+# ---------------------------------------------------------------------------------------
+# the reference entry points
+# ---------------------------------------------------------------------------------------
+def _as_block(task: dict) -> dict:
+    """A legacy one-candidate subtask is a block with one candidate and all folds."""
+    if "candidates" in task:
+        return task
+    t = dict(task)
+    t["candidates"] = [{"index": 0, "subtask_id": task["subtask_id"], "parameters": task.get("parameters", {})}]
+    return t
+
+
+def train_model(task: dict, gpu: int = 0, model_dir: str = "./models"):
+    """worker.py:289.  Returns the reference's result dict for a legacy subtask, or a
+    list of {subtask_id, status, result|error} for a block subtask."""
+    block = _as_block(task)
+    model_type = block["model_type"]
+    tp = block.get("train_params", {})
+    X, y = datasets.get_dataset(block["dataset_id"])
+    choice = _executor_choice(block)
+    if choice not in ("auto", "b200", "sklearn"):
+        raise ValueError(f"unknown executor {choice!r}")
+    on_gpu, on_cpu = [], []
+    for c in block["candidates"]:
+        ok, why = gpu_eligible(model_type, c["parameters"])
+        if choice == "b200" and not ok:
+            raise ValueError(f"executor 'b200' cannot run {model_type}({why})")
+        if choice == "sklearn" or not ok or (choice == "auto" and X.dtype != np.float32):
+            on_cpu.append(c)
+        else:
+            on_gpu.append(c)
+    entries = {}
+    if on_gpu:
+        for c, r in zip(on_gpu, gpu_executor(gpu).run(model_type, on_gpu, tp, block["dataset_id"], model_dir)):
+            entries[c["subtask_id"]] = {"subtask_id": c["subtask_id"], "status": "completed", "result": r}
+    for c in on_cpu:
+        try:
+            r = train_candidate_sklearn(model_type, c["parameters"], tp, X, y, c["subtask_id"])
+            entries[c["subtask_id"]] = {"subtask_id": c["subtask_id"], "status": "completed", "result": r}
+        except Exception as e:   # worker.py:264-286: a failing fit is reported, not raised
+            if "candidates" not in task:
+                raise
+            entries[c["subtask_id"]] = {"subtask_id": c["subtask_id"], "status": "failed", "error": str(e)}
+    ordered = [entries[c["subtask_id"]] for c in block["candidates"]]
+    if "candidates" not in task:
+        return ordered[0]["result"]
+    return ordered
+
+
+def process_task(task: dict, gpu: int = 0):
+    """worker.py:366-387."""
+    return train_model(task, gpu=gpu)
+
+
+class Worker(threading.Thread):
+    """worker.py:156-286 against the in-process scheduler."""
+
+    def __init__(self, scheduler, gpu: int | None = None, mem_capacity_mb: int = 180_000, slot: int | None = None):
+        """``gpu`` = CUDA device this worker drives; ``slot`` = the block index it serves
+        (block["gpu"], master.create_blocks) -- they differ when a process owns one GPU of many."""
+        super().__init__(daemon=True)
+        self.scheduler = scheduler
+        self.gpu = gpu
+        self.worker_id = scheduler.subscribe(mem_capacity_mb, host="localhost",
+                                             gpu=gpu if slot is None else slot)["worker_id"]
+        self.queue = scheduler.get_queue(self.worker_id)
+        self.stop_event = threading.Event()
+        self.hb = threading.Thread(target=self._heartbeat, daemon=True)
+
+    def _heartbeat(self):
+        while not self.stop_event.wait(HEARTBEAT_INTERVAL_S):
+            self.scheduler.heartbeat(self.worker_id)
+
+    def run(self):
+        self.hb.start()
+        while not self.stop_event.is_set():
+            try:
+                key, task = self.queue.get(timeout=0.1)
+            except Exception:
+                continue
+            if task is None:
+                break
+            if key != self.worker_id:      # worker.py:185: skip messages keyed to another worker
+                continue
+            self.handle(task)
+
+    def handle(self, task: dict):
+        received = started = time.time()
+        try:
+            import psutil
+            cpu0, mem0 = psutil.cpu_percent(None), psutil.virtual_memory().percent
+        except Exception:
+            psutil, cpu0, mem0 = None, 0.0, 0.0
+        try:
+            result = process_task(task, gpu=self.gpu or 0)
+            message = {"subtask_id": task["subtask_id"], "job_id": task["job_id"], "session_id": task.get("session_id"),
+                       "status": "completed", "result": result}
+        except Exception as e:
+            err = str(e)
+            if "candidates" in task:
+                result = [{"subtask_id": c["subtask_id"], "status": "failed", "error": err} for c in task["candidates"]]
+                message = {"subtask_id": task["subtask_id"], "job_id": task["job_id"],
+                           "session_id": task.get("session_id"), "status": "failed", "error": err, "result": result}
+            else:
+                message = {"subtask_id": task["subtask_id"], "job_id": task["job_id"],
+                           "session_id": task.get("session_id"), "status": "failed", "error": err}
+        finished = time.time()
+        n_fits = len(task.get("candidates", [0])) * (len(task.get("folds", [])) or 1)
+        self.scheduler.publish_metrics({
+            "worker_id": self.worker_id, "subtask_id": task["subtask_id"], "status": "DONE",
+            "received_at": received, "started_at": started, "finished_at": finished,
+            "cpu_percent_avg": psutil.cpu_percent(None) if psutil else cpu0,
+            "mem_percent_avg": psutil.virtual_memory().percent if psutil else mem0,
+            "algo": task.get("model_type"), "gpu_id": self.gpu, "fits": n_fits,
+            "fits_per_sec": n_fits / max(finished - started, 1e-9)})
+        self.scheduler.publish_result(self.worker_id, message)
+
+    def shutdown(self):
+        self.stop_event.set()
+        self.queue.put((self.worker_id, None))
+        self.scheduler.unsubscribe(self.worker_id)

@@ -1,0 +1,184 @@
+"""Regenerates the fixtures in this directory by IMPORTING the reference.
+
+Run only where /root/reference exists (the build container); the GPU box and
+the tests use the committed outputs, never the reference tree.
+
+    python tests/golden/make_golden.py
+
+Outputs
+  notebook_subtasks.json   job config + the 8 subtasks printed in
+                           aws-prod/library_testing.ipynb cell 2 (the reference's
+                           only pinned artefact), plus what the imported
+                           ``task_handler.create_subtasks`` returns for that config
+                           (asserted equal here) and for a RandomizedSearchCV job.
+  train_model_iris.json    the imported ``worker.train_model`` (with
+                           ``train_test_split`` rebound to keyword arguments,
+                           SURVEY.md 3.4) on iris for the lbfgs candidates of
+                           BASELINE.json config 1 and for synthetic binary data.
+  sweep_small.npz          scikit-learn 1.9.0 answers (coef, intercept, n_iter,
+                           per-fold correct counts / sse / sst) for small seeded
+                           versions of BASELINE.json configs 2-5, produced through
+                           the same ``train_model`` call sequence.
+"""
+import json
+import os
+import subprocess
+import sys
+import tempfile
+import textwrap
+
+import numpy as np
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+ROOT = os.path.dirname(os.path.dirname(HERE))
+REF = "/root/reference"
+
+STUBS = textwrap.dedent("""
+    import sys, types
+    for name in ("kafka", "boto3", "redis", "datasets", "kaggle"):
+        sys.modules[name] = types.ModuleType(name)
+    sys.modules["kafka"].KafkaProducer = sys.modules["kafka"].KafkaConsumer = object
+    sys.modules["redis"].Redis = lambda *a, **k: None
+    sys.modules["redis"].RedisError = Exception
+    sys.modules["datasets"].load_dataset = lambda *a, **k: None
+""")
+
+
+def run_in_reference(subdir, body, payload):
+    """Run ``body`` in a fresh interpreter with the reference dir on sys.path."""
+    with tempfile.TemporaryDirectory() as tmp:
+        inp, outp = os.path.join(tmp, "in.json"), os.path.join(tmp, "out.json")
+        json.dump(payload, open(inp, "w"))
+        code = STUBS + f"\nsys.path.insert(0, {os.path.join(REF, subdir)!r})\n" \
+            f"import json\npayload = json.load(open({inp!r}))\n" + textwrap.dedent(body) + \
+            f"\njson.dump(result, open({outp!r}, 'w'))\n"
+        subprocess.run([sys.executable, "-c", code], cwd=tmp, check=True,
+                       stdout=subprocess.DEVNULL, stderr=subprocess.DEVNULL)
+        return json.load(open(outp))
+
+
+def notebook_fixture():
+    nb = json.load(open(os.path.join(REF, "aws-prod/library_testing.ipynb")))
+    text = "".join(nb["cells"][2]["outputs"][0]["text"])
+    a = text.index("Created job configuration: ") + len("Created job configuration: ")
+    b = text.index("API response:")
+    cfg = json.loads(text[a:b])  # NaN is accepted by json.loads
+    c = text.index("[", text.index("subtasks for GridSearchCV"))
+    subtasks = json.loads(text[c:])
+    return cfg, subtasks
+
+
+def main():
+    cfg, nb_subtasks = notebook_fixture()
+    rnd_cfg = json.loads(json.dumps(cfg))
+    rnd_cfg["model_details"]["search_type"] = "RandomizedSearchCV"
+    rnd_cfg["model_details"]["hyperparameters"]["search_params"] = {
+        "param_distributions": {"C": [0.01, 0.1, 1.0, 10.0, 100.0], "tol": [1e-5, 1e-4, 1e-3],
+                                "fit_intercept": [True, False]},
+        "n_iter": 7}
+    got = run_in_reference("aws-prod/master", """
+        import task_handler
+        result = {"grid": task_handler.create_subtasks(payload["grid"]),
+                  "rand": task_handler.create_subtasks(payload["rand"])}
+    """, {"grid": cfg, "rand": rnd_cfg})
+
+    def canon(o):
+        return json.loads(json.dumps(o))
+    assert canon(got["grid"]) == canon(nb_subtasks), "reference create_subtasks != notebook fixture"
+    json.dump({"job_config": cfg, "subtasks": nb_subtasks, "random_job_config": rnd_cfg,
+               "random_subtasks": got["rand"]},
+              open(os.path.join(HERE, "notebook_subtasks.json"), "w"), indent=1)
+
+    # ---- reference worker.train_model on iris + small synthetic sets ----------
+    sys.path.insert(0, ROOT)
+    from tests.synth import make_dataset  # the same generators the tests use
+
+    tm_body = """
+        import numpy as np, pandas as pd, warnings
+        import sklearn.model_selection as ms
+        import worker
+        worker.MODEL_IMPORTS["Ridge"] = "from sklearn.linear_model import Ridge"
+        worker.MODEL_IMPORTS["RidgeClassifier"] = "from sklearn.linear_model import RidgeClassifier"
+        worker.train_test_split = lambda X, y, ts, rs: ms.train_test_split(X, y, test_size=ts, random_state=rs)
+        data = np.load(payload["npz"])
+        X, y = data["X"], data["y"]
+        worker.load_dataset = lambda dataset_id: (pd.DataFrame(X), pd.Series(y))
+        result = []
+        with warnings.catch_warnings():
+            warnings.simplefilter("ignore")
+            for task in payload["tasks"]:
+                r = worker.train_model(task)
+                r.pop("model_path"); r.pop("training_time")
+                result.append({k: (float(v) if isinstance(v, (np.floating,)) else v) for k, v in r.items()})
+    """
+    out = {}
+    with tempfile.TemporaryDirectory() as tmp:
+        from sklearn.datasets import load_iris
+        Xi, yi = load_iris(return_X_y=True)
+        np.savez(os.path.join(tmp, "iris.npz"), X=Xi, y=yi)
+        tasks = [{"subtask_id": f"iris-{i}", "model_type": "LogisticRegression",
+                  "dataset_id": "iris", "parameters": {"C": C, "solver": "lbfgs"},
+                  "train_params": {"cv": 5, "test_size": 0.25, "random_state": 42}}
+                 for i, C in enumerate([0.1, 1.0, 10.0, 100])]
+        tasks += [{"subtask_id": f"iris-rc-{i}", "model_type": "RidgeClassifier",
+                   "dataset_id": "iris", "parameters": {"alpha": a},
+                   "train_params": {"cv": 5, "test_size": 0.25, "random_state": 42}}
+                  for i, a in enumerate([0.01, 0.1, 1.0, 10.0])]
+        out["iris"] = {"tasks": tasks, "results": run_in_reference(
+            "aws-prod/worker", tm_body, {"npz": os.path.join(tmp, "iris.npz"), "tasks": tasks})}
+
+        X, y = make_dataset("binary", 2000, 16, seed=11)
+        np.savez(os.path.join(tmp, "bin.npz"), X=X, y=y)
+        tasks = [{"subtask_id": f"bin-{i}", "model_type": "LogisticRegression", "dataset_id": "bin",
+                  "parameters": {"C": C}, "train_params": {"cv": 5, "test_size": 0.2, "random_state": 7}}
+                 for i, C in enumerate([1e-3, 1e-1, 10.0])]
+        out["binary_2000x16_seed11"] = {"tasks": tasks, "results": run_in_reference(
+            "aws-prod/worker", tm_body, {"npz": os.path.join(tmp, "bin.npz"), "tasks": tasks})}
+
+        X, y = make_dataset("regression", 1500, 12, seed=12)
+        np.savez(os.path.join(tmp, "reg.npz"), X=X, y=y)
+        tasks = [{"subtask_id": f"reg-{i}", "model_type": "Ridge", "dataset_id": "reg",
+                  "parameters": {"alpha": a}, "train_params": {"cv": 5, "test_size": 0.2, "random_state": 7}}
+                 for i, a in enumerate([1e-2, 1.0, 100.0])]
+        out["regression_1500x12_seed12"] = {"tasks": tasks, "results": run_in_reference(
+            "aws-prod/worker", tm_body, {"npz": os.path.join(tmp, "reg.npz"), "tasks": tasks})}
+    json.dump(out, open(os.path.join(HERE, "train_model_iris.json"), "w"), indent=1)
+
+    # ---- small seeded versions of configs 2-5 via sklearn (fp32 X like the configs) --------
+    from oracle import reference_path as rp
+    arrays = {}
+    cases = {
+        "cfg2": ("binary", 6000, 32, 2, "LogisticRegression", [{"C": float(c)} for c in np.logspace(-6, 2, 8)], 5),
+        "cfg3r": ("regression", 6000, 32, 3, "Ridge", [{"alpha": float(a)} for a in np.logspace(-3, 5, 8)], 5),
+        "cfg3c": ("binary", 6000, 32, 3, "RidgeClassifier", [{"alpha": float(a)} for a in np.logspace(-3, 5, 8)], 5),
+        "cfg4": ("multiclass10", 6000, 32, 4, "LogisticRegression",
+                 [{"C": 1e-3, "tol": 1e-4, "fit_intercept": True}, {"C": 1.0, "tol": 1e-5, "fit_intercept": False},
+                  {"C": 10.0, "tol": 1e-3, "fit_intercept": True}, {"C": 0.05, "tol": 1e-4, "fit_intercept": False}], 5),
+        "cfg5": ("binary", 8000, 32, 5, "LogisticRegression", [{"C": float(c)} for c in np.logspace(-6, 2, 6)], 10),
+    }
+    for name, (kind, n, d, seed, model, cands, cv) in cases.items():
+        X, y = make_dataset(kind, n, d, seed=seed)
+        res = rp.sweep(model, {}, cands, X, y, cv=cv)
+        coef = np.stack([np.stack([np.atleast_2d(f["model"].coef_) for f in row]) for row in res["fits"]])
+        icpt = np.stack([np.stack([np.atleast_1d(f["model"].intercept_) for f in row]) for row in res["fits"]])
+        arrays[f"{name}_coef"] = coef.astype(np.float64)
+        arrays[f"{name}_intercept"] = icpt.astype(np.float64)
+        arrays[f"{name}_scores"] = res["scores"]
+        arrays[f"{name}_best_index"] = np.int64(res["best_index"])
+        if model == "Ridge":
+            arrays[f"{name}_sse"] = np.array([[f["sse"] for f in row] for row in res["fits"]])
+            arrays[f"{name}_sst"] = np.array([[f["sst"] for f in row] for row in res["fits"]])
+        else:
+            arrays[f"{name}_correct"] = np.array([[f["correct"] for f in row] for row in res["fits"]], dtype=np.int64)
+            arrays[f"{name}_ntest"] = np.array([[f["n_test"] for f in row] for row in res["fits"]], dtype=np.int64)
+        if model == "LogisticRegression":
+            arrays[f"{name}_n_iter"] = np.array([[int(f["model"].n_iter_[0]) for f in row] for row in res["fits"]],
+                                                dtype=np.int64)
+        arrays[f"{name}_meta"] = np.array(json.dumps(
+            {"kind": kind, "n": n, "d": d, "seed": seed, "model": model, "candidates": cands, "cv": cv}))
+    np.savez_compressed(os.path.join(HERE, "sweep_small.npz"), **arrays)
+    print("golden fixtures written to", HERE)
+
+
+if __name__ == "__main__":
+    main()

@@ -1,0 +1,257 @@
+"""CUDA path vs the oracle, through the C ABI (solver.SweepSolver -> ctypes -> libdml_b200.so).
+
+Bars (BASELINE.json north_star): identical fold labels, per-fold correct counts
+bit-exact except on decision ties, coefficients / scores within 1e-4 relative,
+best candidate identical under sklearn's rule.
+"""
+import json
+import os
+import warnings
+
+import numpy as np
+import pytest
+import torch
+
+from cs230_distributed_machine_learning_b200 import folds
+from oracle import folds as ofolds
+from oracle import lbfgs as olbfgs
+from oracle import reference_path as rp
+from oracle import ridge as oridge
+from tests.synth import make_dataset
+
+pytestmark = pytest.mark.gpu
+RTOL = 1e-4   # north_star tolerance for coefficients and scores
+
+
+def rel_err(got, want):
+    return float(np.abs(got - want).max() / max(np.abs(want).max(), 1e-30))
+
+
+def near_ties(X, coef, icpt, rows, eps=2e-5):
+    """rows whose sklearn decision is within eps of flipping (binary: |z|, multi: top-2 gap)."""
+    z = X[rows].astype(np.float64) @ np.atleast_2d(coef).T + icpt
+    if z.shape[1] == 1:
+        return int((np.abs(z[:, 0]) < eps * max(1.0, np.abs(z).max())).sum())
+    zs = np.sort(z, axis=1)
+    return int(((zs[:, -1] - zs[:, -2]) < eps * max(1.0, np.abs(z).max())).sum())
+
+
+def load_case(golden_dir, name):
+    z = np.load(os.path.join(golden_dir, "sweep_small.npz"))
+    meta = json.loads(str(z[f"{name}_meta"]))
+    X, y = make_dataset(meta["kind"], meta["n"], meta["d"], seed=meta["seed"])
+    return z, meta, X, y
+
+
+@pytest.mark.parametrize("name", ["cfg2", "cfg5", "cfg4"])
+def test_logreg_sweep_vs_sklearn_fixture(solver, golden_dir, name):
+    z, meta, X, y = load_case(golden_dir, name)
+    cv, cands = meta["cv"], meta["candidates"]
+    fold = folds.stratified_labels(y, cv)
+    assert (fold == ofolds.stratified_fold_ids(y, cv)).all()
+    ds = solver.upload_dataset(X, y, classifier=True)
+    out = solver.logreg_sweep(ds, fold, cv, [c["C"] for c in cands], [c.get("tol", 1e-4) for c in cands],
+                              [c.get("fit_intercept", True) for c in cands], [100] * len(cands))
+    want_coef, want_icpt = z[f"{name}_coef"], z[f"{name}_intercept"]
+    iter_diff = 0
+    for i in range(len(cands)):
+        for k in range(cv):
+            if out["n_iter"][i, k] != z[f"{name}_n_iter"][i, k]:
+                iter_diff += 1      # a column stopping one iterate apart is reported, not hidden
+                continue
+            assert rel_err(out["coef"][i, k], want_coef[i, k]) <= RTOL, (i, k)
+            assert np.abs(out["intercept"][i, k] - want_icpt[i, k]).max() <= RTOL * max(1.0, np.abs(want_coef[i, k]).max())
+            ties = near_ties(X, want_coef[i, k], want_icpt[i, k], fold == k)
+            assert abs(int(out["correct"][i, k]) - int(z[f"{name}_correct"][i, k])) <= ties, (i, k)
+    assert iter_diff <= max(1, len(cands) * cv // 20), f"{iter_diff} fits stopped at a different iterate"
+    assert (out["n_test"] == z[f"{name}_ntest"]).all()
+    assert (out["status"] == 0).all()
+    scores = out["correct"] / out["n_test"]
+    np.testing.assert_allclose(scores, z[f"{name}_scores"], atol=RTOL)
+    mean = np.average(scores, axis=1)
+    gold_mean = np.average(z[f"{name}_scores"], axis=1)
+    if np.sort(gold_mean)[-1] - np.sort(gold_mean)[-2] > 2.0 / meta["n"]:   # winner separated by > 1 row
+        assert rp.search_rules(scores)[3] == int(z[f"{name}_best_index"])
+
+
+@pytest.mark.parametrize("name,classifier", [("cfg3r", False), ("cfg3c", True)])
+def test_ridge_sweep_vs_sklearn_fixture(solver, golden_dir, name, classifier):
+    z, meta, X, y = load_case(golden_dir, name)
+    cv, cands = meta["cv"], meta["candidates"]
+    fold = folds.stratified_labels(y, cv) if classifier else folds.kfold_labels(len(y), cv)
+    ds = solver.upload_dataset(X, y, classifier=classifier)
+    out = solver.ridge_sweep(ds, fold, cv, [c["alpha"] for c in cands], [True] * len(cands), classifier=classifier)
+    assert (out["info"] == 0).all()
+    for i in range(len(cands)):
+        for k in range(cv):
+            assert rel_err(out["coef"][i, k], z[f"{name}_coef"][i, k]) <= RTOL, (i, k)
+            assert np.abs(out["intercept"][i, k] - z[f"{name}_intercept"][i, k]).max() <= RTOL
+    if classifier:
+        for i in range(len(cands)):
+            for k in range(cv):
+                ties = near_ties(X, z[f"{name}_coef"][i, k], z[f"{name}_intercept"][i, k], fold == k)
+                assert abs(int(out["correct"][i, k]) - int(z[f"{name}_correct"][i, k])) <= ties
+        assert (out["n_test"] == z[f"{name}_ntest"]).all()
+    else:
+        sst = out["syy"] - out["sy"] ** 2 / out["n_test"]
+        np.testing.assert_allclose(out["sse"], z[f"{name}_sse"], rtol=RTOL)
+        np.testing.assert_allclose(sst, z[f"{name}_sst"], rtol=RTOL)
+        np.testing.assert_allclose(1.0 - out["sse"] / sst, z[f"{name}_scores"], rtol=RTOL, atol=RTOL)
+
+
+def test_score_kernel_counts_bit_exact(solver):
+    """Oracle-supplied coefficients: counts equal the numpy predictions exactly."""
+    X, y = make_dataset("binary", 5000, 24, seed=31)
+    fold = folds.stratified_labels(y, 5)
+    rng = np.random.default_rng(0)
+    W = (rng.standard_normal((10, 24)) / 5).astype(np.float32)
+    b = rng.standard_normal(10).astype(np.float32) * 0.1
+    sel, val = np.zeros(10, dtype=np.int32), (np.arange(10) % 5).astype(np.int32)
+    ds = solver.upload_dataset(X, y, classifier=True)
+    got = solver.score(ds, fold, W, b, sel, val, T=1)
+    z = X.astype(np.float64) @ W.T.astype(np.float64) + b
+    for s in range(10):
+        rows = fold == val[s]
+        exact = int(((z[rows, s] > 0).astype(int) == y[rows]).sum())
+        slack = int((np.abs(z[rows, s]) < 1e-5).sum())
+        assert abs(int(got[s]) - exact) <= slack
+    # multiclass arg-max, ragged tile (n % 128 != 0, d % 4 != 0)
+    X, y = make_dataset("multiclass5", 3333, 13, seed=32)
+    fold = folds.stratified_labels(y, 3)
+    W = (rng.standard_normal((15, 13)) / 3).astype(np.float32)
+    b = np.zeros(15, dtype=np.float32)
+    sel, val = np.zeros(15, dtype=np.int32), np.repeat(np.arange(3), 5).astype(np.int32)
+    ds = solver.upload_dataset(X, y, classifier=True)
+    got = solver.score(ds, fold, W, b, sel, val, T=5)
+    for g in range(3):
+        rows = fold == g
+        zz = X[rows].astype(np.float64) @ W[g * 5:(g + 1) * 5].T.astype(np.float64)
+        zs = np.sort(zz, axis=1)
+        slack = int(((zs[:, -1] - zs[:, -2]) < 1e-5).sum())
+        assert abs(int(got[g]) - int((zz.argmax(1) == y[rows]).sum())) <= slack
+
+
+@pytest.mark.parametrize("n,d,k", [(1000, 13, 2), (777, 5, 3), (4096, 32, 2), (130, 3, 2)])
+def test_logreg_ragged_shapes_and_options(solver, n, d, k):
+    """Edge shapes (n % 128, d % 4), fit_intercept=False, tight tol, iteration cap."""
+    from sklearn.linear_model import LogisticRegression
+    X, y = make_dataset("binary" if k == 2 else f"multiclass{k}", n, d, seed=40 + d)
+    cv = 3
+    fold = folds.stratified_labels(y, cv)
+    cands = [dict(C=1.0, tol=1e-4, fit_intercept=True, max_iter=100),
+             dict(C=0.01, tol=1e-6, fit_intercept=False, max_iter=100),
+             dict(C=100.0, tol=1e-4, fit_intercept=True, max_iter=3)]
+    ds = solver.upload_dataset(X, y, classifier=True)
+    out = solver.logreg_sweep(ds, fold, cv, [c["C"] for c in cands], [c["tol"] for c in cands],
+                              [c["fit_intercept"] for c in cands], [c["max_iter"] for c in cands])
+    with warnings.catch_warnings():
+        warnings.simplefilter("ignore")
+        for i, c in enumerate(cands):
+            for f in range(cv):
+                tr, te = fold != f, fold == f
+                m = LogisticRegression(**c).fit(X[tr], y[tr])
+                if out["n_iter"][i, f] != m.n_iter_[0]:
+                    continue
+                assert rel_err(out["coef"][i, f], m.coef_) <= 5 * RTOL, (i, f)
+                ties = near_ties(X, m.coef_, m.intercept_, te, eps=1e-4)
+                assert abs(int(out["correct"][i, f]) - int((m.predict(X[te]) == y[te]).sum())) <= ties
+                assert out["n_test"][i, f] == te.sum()
+    assert (out["n_iter"][2] <= 3).all() and (out["status"][2] == 1).all()   # cap reached -> status 1
+    assert (out["intercept"][1] == 0).all()
+
+
+def test_holdout_fit_equals_train_test_split(solver):
+    from sklearn.linear_model import LogisticRegression, Ridge
+    from sklearn.model_selection import train_test_split
+    X, y = make_dataset("binary", 3000, 16, seed=50)
+    fold = folds.stratified_labels(y, 5)
+    hold = folds.holdout_labels(len(y), 0.25, 42)
+    ds = solver.upload_dataset(X, y, classifier=True)
+    out = solver.logreg_sweep(ds, fold, 5, [0.5], [1e-4], [True], [100], hold_id=hold)
+    Xtr, Xte, ytr, yte = train_test_split(X, y, test_size=0.25, random_state=42)
+    m = LogisticRegression(C=0.5).fit(Xtr, ytr)
+    assert out["coef"].shape == (1, 6, 1, 16)
+    assert rel_err(out["coef"][0, 5], m.coef_) <= RTOL
+    assert out["n_test"][0, 5] == len(yte)
+    assert abs(int(out["correct"][0, 5]) - int((m.predict(Xte) == yte).sum())) <= near_ties(Xte, m.coef_, m.intercept_, slice(None), 1e-4)
+    Xr, yr = make_dataset("regression", 3000, 16, seed=51)
+    dr = solver.upload_dataset(Xr, yr, classifier=False)
+    outr = solver.ridge_sweep(dr, folds.kfold_labels(3000, 5), 5, [2.0], [True], classifier=False, hold_id=hold)
+    Xtr, Xte, ytr, yte = train_test_split(Xr, yr, test_size=0.25, random_state=42)
+    mr = Ridge(alpha=2.0).fit(Xtr, ytr)
+    assert rel_err(outr["coef"][0, 5], mr.coef_) <= RTOL
+    assert outr["sse"][0, 5] == pytest.approx(float(((yte - mr.predict(Xte)) ** 2).sum()), rel=RTOL)
+
+
+def test_restatement_tracks_gpu_trajectory(solver):
+    """Same rule set => same number of iterations and function evaluations as the fp64 restatement."""
+    X, y = make_dataset("binary", 20000, 32, seed=60)
+    fold = folds.stratified_labels(y, 5)
+    Cs = [1e-5, 1e-3, 1e-1, 10.0]
+    ds = solver.upload_dataset(X, y, classifier=True)
+    out = solver.logreg_sweep(ds, fold, 5, Cs, [1e-4] * 4, [True] * 4, [100] * 4)
+    same = 0
+    for i, C in enumerate(Cs):
+        for k in range(5):
+            r = olbfgs.fit_logreg(X[fold != k].astype(np.float64), y[fold != k], 2, C=C)
+            same += int(r["n_iter"] == out["n_iter"][i, k] and r["nfev"] == out["nfev"][i, k])
+            if r["n_iter"] == out["n_iter"][i, k]:
+                assert rel_err(out["coef"][i, k], r["coef"]) <= RTOL
+    assert same >= 18, f"only {same}/20 fits followed the oracle's trajectory"
+
+
+def test_api_end_to_end_best_params_equal_gridsearchcv():
+    """MLTaskManager.train on float32 data -> b200 executor; compare with sklearn GridSearchCV."""
+    from sklearn.linear_model import LogisticRegression, Ridge
+    from sklearn.model_selection import GridSearchCV
+    import cs230_distributed_machine_learning_b200 as pkg
+    X, y = make_dataset("binary", 8000, 32, seed=70)
+    pkg.register_dataset("syn-bin", X, y)
+    m = pkg.MLTaskManager("local://1")
+    try:
+        grid = {"C": [float(c) for c in np.logspace(-5, 1, 7)]}
+        r = m.train(GridSearchCV(LogisticRegression(), grid, cv=5), "syn-bin", wait_for_completion=True)
+        assert r["job_status"] == "completed", r
+        gs = GridSearchCV(LogisticRegression(), grid, cv=5).fit(X, y)
+        jr = r["job_result"]
+        assert all(res["executor"] == "b200" for res in jr["results"])
+        np.testing.assert_allclose(jr["cv_results_"]["mean_test_score"], gs.cv_results_["mean_test_score"], atol=RTOL)
+        top2 = np.sort(gs.cv_results_["mean_test_score"])[-2:]
+        if top2[1] - top2[0] > 2.0 / len(y):
+            assert jr["best_params_"] == gs.best_params_
+        Xr, yr = make_dataset("regression", 8000, 32, seed=71)
+        pkg.register_dataset("syn-reg", Xr, yr)
+        gridr = {"alpha": [float(a) for a in np.logspace(-2, 4, 7)]}
+        r = m.train(GridSearchCV(Ridge(), gridr, cv=5), "syn-reg", train_params={"test_size": 0.2, "random_state": 1},
+                    wait_for_completion=True)
+        gsr = GridSearchCV(Ridge(), gridr, cv=5).fit(Xr, yr)
+        jr = r["job_result"]
+        np.testing.assert_allclose(jr["cv_results_"]["mean_test_score"], gsr.cv_results_["mean_test_score"], rtol=RTOL)
+        assert jr["best_params_"] == gsr.best_params_
+        assert "r2_score" in jr["results"][0] and os.path.exists(jr["results"][0]["model_path"])
+    finally:
+        m.close()
+
+
+def test_medium_size_properties(solver):
+    """Size-independent properties at a size the oracle cannot sweep in seconds (200k x 256, 16 C x 5 folds)."""
+    X, y = make_dataset("binary", 200_000, 256, seed=2)
+    fold = folds.stratified_labels(y, 5)
+    Cs = np.logspace(-6, 2, 16)
+    ds = solver.upload_dataset(X, y, classifier=True)
+    a = solver.logreg_sweep(ds, fold, 5, Cs, [1e-4] * 16, [True] * 16, [100] * 16)
+    b = solver.logreg_sweep(ds, fold, 5, Cs[::-1].copy(), [1e-4] * 16, [True] * 16, [100] * 16)
+    assert (a["n_test"].sum(axis=1) == len(y)).all()                       # folds partition the rows
+    assert ((a["correct"] >= 0) & (a["correct"] <= a["n_test"])).all()
+    assert (a["status"] == 0).all() and (a["n_iter"] < 100).all()
+    np.testing.assert_array_equal(a["correct"], b["correct"][::-1])       # column order does not matter
+    np.testing.assert_array_equal(a["n_iter"], b["n_iter"][::-1])
+    np.testing.assert_array_equal(a["coef"], b["coef"][::-1])             # deterministic reductions
+    nrm = np.linalg.norm(a["coef"][:, 0, 0], axis=1)
+    assert (np.diff(nrm) > 0).all()                                        # ||w|| grows with C
+    # recount the winner's predictions on the host from the returned coefficients
+    i = int(np.argmax(a["correct"].sum(axis=1)))
+    for k in range(5):
+        rows = fold == k
+        zz = X[rows] @ a["coef"][i, k, 0] + a["intercept"][i, k, 0]
+        assert abs(int(((zz > 0) == y[rows]).sum()) - int(a["correct"][i, k])) <= int((np.abs(zz) < 1e-5).sum())

@@ -1,0 +1,210 @@
+"""Host-side logic: splitter, blocks, aggregation, scheduler, client API, C-ABI exports."""
+import ctypes
+import json
+import os
+import re
+import time
+
+import numpy as np
+import pytest
+from sklearn.linear_model import LogisticRegression, RidgeClassifier
+from sklearn.model_selection import GridSearchCV, ParameterSampler, RandomizedSearchCV
+
+import cs230_distributed_machine_learning_b200 as pkg
+from cs230_distributed_machine_learning_b200 import _cabi, build, folds, master, scheduler, worker
+from cs230_distributed_machine_learning_b200.client import MLTaskManager, wire
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def test_create_subtasks_matches_notebook_fixture(golden_dir):
+    g = json.load(open(os.path.join(golden_dir, "notebook_subtasks.json")))
+    got = master.create_subtasks(g["job_config"])
+    assert json.loads(json.dumps(got)) == json.loads(json.dumps(g["subtasks"]))
+    assert [s["parameters"]["C"] for s in got] == [0.1, 0.1, 1.0, 1.0, 10.0, 10.0, 100, 100]
+    assert [s["parameters"]["solver"] for s in got] == ["liblinear", "lbfgs"] * 4
+
+
+def test_create_subtasks_randomized_matches_reference(golden_dir):
+    g = json.load(open(os.path.join(golden_dir, "notebook_subtasks.json")))
+    got = master.create_subtasks(g["random_job_config"])
+    assert json.loads(json.dumps(got)) == json.loads(json.dumps(g["random_subtasks"]))
+    # sampling without replacement from an all-list grid, seed 42 (task_handler.py:213)
+    assert len({json.dumps(s["parameters"], sort_keys=True) for s in got}) == 7
+
+
+def test_single_estimator_subtask():
+    cfg = {"job_id": "j", "session_id": "s", "dataset_id": "d", "train_params": {"test_size": 0.2},
+           "model_details": {"model_type": "Ridge", "hyperparameters": {"alpha": 2.0}}}
+    (st,) = master.create_subtasks(cfg)
+    assert st["subtask_id"] == "j-subtask-1" and st["parameters"] == {"alpha": 2.0}
+    assert st["train_params"] == {"test_size": 0.2}
+
+
+@pytest.mark.parametrize("n_gpus", [1, 2, 4, 8])
+def test_blocks_cover_every_candidate_once(golden_dir, n_gpus):
+    g = json.load(open(os.path.join(golden_dir, "notebook_subtasks.json")))
+    subtasks = master.create_subtasks(g["job_config"])
+    blocks = master.create_blocks(subtasks, n_gpus=n_gpus)
+    seen = sorted(c["index"] for b in blocks for c in b["candidates"])
+    assert seen == list(range(8))
+    assert [b["gpu"] for b in blocks] == list(range(min(n_gpus, 8)))
+    for b in blocks:
+        assert b["folds"] == [0, 1, 2, 3, 4] and b["partition"] == "candidates"
+        for c in b["candidates"]:
+            assert c["parameters"] == subtasks[c["index"]]["parameters"]
+    rows = master.create_blocks(subtasks, n_gpus=n_gpus, partition="rows")
+    assert all(len(b["candidates"]) == 8 and b["n_shards"] == n_gpus for b in rows)
+
+
+def test_aggregate_ties_and_nan():
+    res = [{"mean_cv_score": float("nan"), "i": 0}, {"mean_cv_score": 0.9, "i": 1},
+           {"mean_cv_score": 0.98, "i": 2}, {"mean_cv_score": 0.98, "i": 3}, {"mean_cv_score": None, "i": 4}]
+    assert master.aggregate_results(res)["i"] == 2          # lowest index among exact ties
+    assert master.aggregate_results(list(reversed(res)))["i"] == 3
+    cv = master.build_cv_results([{"C": c} for c in range(5)],
+                                 [[np.nan] * 2, [0.9, 0.9], [0.98, 0.98], [0.98, 0.98], [np.nan] * 2])
+    assert cv["cv_results_"]["rank_test_score"] == [4, 3, 1, 1, 4]
+    assert cv["best_index_"] == 2 and cv["best_params_"] == {"C": 2}
+
+
+def test_build_cv_results_equals_gridsearchcv():
+    from sklearn.datasets import load_iris
+    X, y = load_iris(return_X_y=True)
+    grid = {"alpha": [0.01, 0.1, 1.0, 10.0]}
+    gs = GridSearchCV(RidgeClassifier(), grid, cv=5).fit(X, y)
+    scores = np.stack([gs.cv_results_[f"split{k}_test_score"] for k in range(5)], axis=1)
+    mine = master.build_cv_results([{"alpha": a} for a in grid["alpha"]], scores)
+    assert mine["cv_results_"]["rank_test_score"] == gs.cv_results_["rank_test_score"].tolist()
+    np.testing.assert_array_equal(mine["cv_results_"]["mean_test_score"], gs.cv_results_["mean_test_score"])
+    np.testing.assert_allclose(mine["cv_results_"]["std_test_score"], gs.cv_results_["std_test_score"], rtol=1e-12)
+    assert mine["best_index_"] == gs.best_index_ and mine["best_score_"] == gs.best_score_
+
+
+def test_wire_format_cleans_numpy_and_nan():
+    p = wire({"a": np.float64(1.5), "b": np.arange(3), "c": float("nan"), "d": {"e": np.int64(2)}, "f": LogisticRegression})
+    assert p["a"] == 1.5 and p["b"] == [0, 1, 2] and p["c"] is None and p["d"]["e"] == 2 and isinstance(p["f"], str)
+
+
+def test_client_config1_iris_known_answers():
+    """BASELINE.json config 1 through MLTaskManager -> master -> scheduler -> worker (sklearn executor)."""
+    from sklearn.datasets import load_iris
+    X, y = load_iris(return_X_y=True)
+    pkg.register_dataset("iris", X, y)
+    m = MLTaskManager("local://1")
+    try:
+        gs = GridSearchCV(LogisticRegression(), {"C": [0.1, 1.0, 10.0, 100], "solver": ["liblinear", "lbfgs"]}, cv=5)
+        first = m.train(gs, "iris", train_params={"random_state": 42})
+        assert first["status"] == "Training started" and first["total_subtasks"] == 8
+        r = m._wait_for_completion(m.job_id)
+        assert r["job_status"] == "completed" and r["tasks_pending"] == 0 and r["total_subtasks"] == 8
+        jr = r["job_result"]
+        assert jr["best_params_"] == {"C": 10.0, "solver": "lbfgs"} and jr["best_index_"] == 5
+        assert jr["best_score_"] == 0.9800000000000001
+        assert jr["cv_results_"]["rank_test_score"] == [5, 4, 5, 3, 5, 1, 5, 1]
+        assert r["best_result"]["parameters"]["C"] == 10.0           # demo_results.py:12-19 shape
+        assert len(jr["results"]) == 8 and "training_time" in jr["results"][1]
+        assert np.isnan(jr["results"][0]["mean_cv_score"])
+        assert m.check_job_status("nope")["status"] == "error"       # errors are dicts, never raises
+        assert m.train(gs, "missing-dataset")["status"] == "error"
+        assert len(m._api_request(f"metrics/{m.session_id}/{m.job_id}", "get")) == 0  # failed submit: no job
+    finally:
+        m.close()
+
+
+def test_client_single_estimator_defaults_test_size():
+    from sklearn.datasets import load_iris
+    X, y = load_iris(return_X_y=True)
+    pkg.register_dataset("iris", X, y)
+    m = MLTaskManager("local://1")
+    try:
+        r = m.train(RidgeClassifier(alpha=1.0), "iris", train_params={"random_state": 42}, wait_for_completion=True)
+        res = r["job_result"]["results"][0]
+        assert r["total_subtasks"] == 1 and "best_result" not in r
+        assert "accuracy" in res and len(res["cv_scores"]) == 5
+        assert res["mean_cv_score"] == pytest.approx(0.82, abs=1e-12)   # alpha=1 -> 0.82
+        rec = m._api_request(f"metrics/{m.session_id}/{m.job_id}", "get")
+        assert rec and {"worker_id", "subtask_id", "status", "received_at", "started_at", "finished_at",
+                        "cpu_percent_avg", "mem_percent_avg", "algo"} <= set(rec[0])
+    finally:
+        m.close()
+
+
+def test_scheduler_contract_and_requeue():
+    s = scheduler.Scheduler()
+    got = []
+
+    class M:
+        def on_result(self, msg): got.append(msg)
+        def on_metrics(self, rec): pass
+    s.attach_master(M())
+    assert s.submit({"subtask_id": "t0", "gpu": 0}) is None            # no worker yet: backlog
+    w0 = s.subscribe(1000, "h", gpu=0)["worker_id"]
+    w1 = s.subscribe(1000, "h", gpu=1)["worker_id"]
+    assert s.get_queue(w0).qsize() == 1                                # backlog delivered on subscribe
+    assert s.submit({"subtask_id": "t1", "gpu": 1}) == w1              # a block names its GPU
+    assert s.heartbeat(w0)["status"] == "ok" and s.heartbeat("x")["status"] == "unknown_worker"
+    # worker 1 goes silent for > 10 s: its task is handed to the survivor
+    s.workers[w1]["last_seen"] -= 11
+    assert s.reap_dead_workers() == [w1]
+    assert s.get_queue(w0).qsize() == 2
+    s.publish_result(w0, {"subtask_id": "t0", "job_id": "j", "status": "completed", "result": {}})
+    assert got and s.workers_view()[w0]["done"] == 1
+    assert s.unsubscribe(w0)["status"] == "unsubscribed" and s.n_workers() == 0
+
+
+def test_gpu_eligibility_rules():
+    ok = worker.gpu_eligible
+    assert ok("LogisticRegression", {"C": 1.0, "solver": "lbfgs"})[0]
+    assert not ok("LogisticRegression", {"solver": "liblinear"})[0]
+    assert not ok("LogisticRegression", {"class_weight": "balanced"})[0]
+    assert not ok("LogisticRegression", {"l1_ratio": 0.5})[0]
+    assert ok("Ridge", {"alpha": 1.0})[0] and not ok("Ridge", {"solver": "sag"})[0]
+    assert ok("RidgeClassifier", {})[0] and not ok("RandomForestClassifier", {})[0]
+    with pytest.raises(ValueError):
+        worker.get_model_instance("XGBClassifier", {})
+    # an older client's extra key is dropped, not fatal (library_testing.ipynb:640)
+    assert worker.get_model_instance("LogisticRegression", {"C": 2.0, "multi_class": "auto"}).C == 2.0
+
+
+def test_b200_executor_never_falls_back_to_cpu():
+    """float32 data + covered model => the CUDA path, which must raise when there is no GPU."""
+    import torch
+    if torch.cuda.is_available():
+        pytest.skip("CUDA present: the loud-failure branch is not reachable")
+    X = np.random.default_rng(0).standard_normal((200, 4)).astype(np.float32)
+    y = (X[:, 0] > 0).astype(np.int32)
+    pkg.register_dataset("f32", X, y)
+    task = {"subtask_id": "s-1", "job_id": "j", "dataset_id": "f32", "model_type": "LogisticRegression",
+            "parameters": {"C": 1.0}, "train_params": {"cv": 5}}
+    with pytest.raises(RuntimeError, match="no CPU fallback"):
+        worker.train_model(task)
+    task["train_params"]["executor"] = "sklearn"                      # explicit request for the reference path
+    assert len(worker.train_model(task)["cv_scores"]) == 5
+
+
+def test_holdout_labels_match_train_test_split():
+    from sklearn.model_selection import train_test_split
+    for n, ts, rs in [(150, 0.25, 42), (1001, 0.2, 7), (64, 0.33, 0)]:
+        _, te = train_test_split(np.arange(n), test_size=ts, random_state=rs)
+        assert set(np.nonzero(folds.holdout_labels(n, ts, rs))[0]) == set(te)
+
+
+def test_cabi_library_exports_every_declared_symbol():
+    """The .so builds for sm_100a, loads without a GPU, and exports what include/dml_b200.h declares."""
+    path = build.build()
+    lib = ctypes.CDLL(path)
+    header = open(os.path.join(ROOT, "include", "dml_b200.h")).read()
+    declared = set(re.findall(r"\b(dml_[a-z0-9_]+)\s*\(", header))
+    assert declared >= {"dml_version", "dml_ctx_create", "dml_ctx_destroy", "dml_last_error", "dml_logreg_sweep",
+                        "dml_ridge_sweep", "dml_score", "dml_ctx_init_comm", "dml_nccl_unique_id", "dml_last_timing",
+                        "dml_last_counters"}
+    for name in declared:
+        assert hasattr(lib, name), name
+    assert set(_cabi.SYMBOLS) == declared
+    assert _cabi.load().dml_version() >= 100
+    import torch
+    if not torch.cuda.is_available():
+        h = ctypes.c_void_p()
+        assert _cabi.load().dml_ctx_create(0, None, ctypes.byref(h)) != 0   # loud, not a crash
+        assert b"CUDA" in _cabi.load().dml_last_error(None) or b"device" in _cabi.load().dml_last_error(None)
