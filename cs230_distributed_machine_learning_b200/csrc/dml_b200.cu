@@ -256,7 +256,7 @@ extern "C" int dml_logreg_sweep(dml_ctx* ctx, const float* X, int64_t n, int d, 
   if (fpc == 0) return fail(ctx, DML_ERR_ARG, "dml_logreg_sweep: no fits requested");
   const int F = n_cand * fpc, P = T * (d + 1);
   const int64_t S_max = (int64_t)F * T;
-  const int ldw = (int)rup(d, 4), ldg = ldw, ldgr = d + 2;
+  const int ldw = (int)rup(d, 4), ldg = (int)rup(d + 1, 4), ldgr = d + 2;
   const int64_t tiles_total = cdiv(n, BM);
   const int tile_n = (BN / T) * T;
   if (cdiv(S_max, tile_n) > 65535) return fail(ctx, DML_ERR_LIMIT, "too many columns (%lld)", (long long)S_max);
@@ -265,14 +265,17 @@ extern "C" int dml_logreg_sweep(dml_ctx* ctx, const float* X, int64_t n, int d, 
   int64_t chunk_rows = std::max<int64_t>(BM, (int64_t)(ctx->r_budget / (ldr_max * 4)) / BM * BM);
   chunk_rows = std::min<int64_t>(chunk_rows, rup(n, BM));
   // row splits of the gradient contraction
-  const int mt_max = (int)cdiv(S_max, BM), nt = (int)cdiv(d, BN);
-  int splits = (int)std::max<int64_t>(1, std::min<int64_t>(cdiv(4 * ctx->n_sms, (int64_t)mt_max * nt), cdiv(chunk_rows, 2048)));
+  const int mt_max = (int)cdiv(S_max, BM), nt = (int)cdiv(d + 1, BN);
+  // short fp32 accumulation chains (<= 2048 rows), fp64 across splits: keeps the gradient noise
+  // near 1e-7 relative (DESIGN.md "precision"); at least enough splits to fill the machine
+  int splits = (int)std::max<int64_t>(cdiv(chunk_rows, 2048), std::min<int64_t>(cdiv(2 * ctx->n_sms, (int64_t)mt_max * nt), cdiv(chunk_rows, 256)));
   const int64_t rps = rup(cdiv(chunk_rows, splits), 16);
   splits = (int)cdiv(chunk_rows, rps);
+  (void)mt_max;
 
   FitState* d_st; double *d_x, *d_g, *d_dir, *d_gt, *d_S, *d_Y, *d_ys, *d_Gred;
   int *d_active, *d_nactive; unsigned long long* d_hist; long long* d_correct;
-  float *d_Wt, *d_bt, *d_R, *d_lossPart, *d_gbPart, *d_Gpart; int32_t *d_sel, *d_val, *d_i32;
+  float *d_Wt, *d_bt, *d_R, *d_Gpart; double* d_lossPart; int32_t *d_sel, *d_val, *d_i32, *d_cntPart;
   for (int pass = 0; pass < 2; ++pass) {
     Arena a(pass ? ctx->ws : nullptr);
     d_st = a.take<FitState>(F); d_i32 = a.take<int32_t>(3 * (size_t)F);
@@ -286,8 +289,8 @@ extern "C" int dml_logreg_sweep(dml_ctx* ctx, const float* X, int64_t n, int d, 
     d_Wt = a.take<float>((size_t)S_max * ldw); d_bt = a.take<float>(S_max);
     d_sel = a.take<int32_t>(S_max); d_val = a.take<int32_t>(S_max);
     d_R = a.take<float>((size_t)chunk_rows * ldr_max);
-    d_lossPart = a.take<float>((size_t)tiles_total * S_max);
-    d_gbPart = a.take<float>((size_t)tiles_total * S_max);
+    d_lossPart = a.take<double>((size_t)tiles_total * F);
+    d_cntPart = a.take<int32_t>((size_t)tiles_total * S_max);
     d_Gpart = a.take<float>((size_t)splits * S_max * ldg);
     if (!pass) { int rc = ensure_ws(ctx, a.off + 256); if (rc) return rc; }
   }
@@ -296,7 +299,6 @@ extern "C" int dml_logreg_sweep(dml_ctx* ctx, const float* X, int64_t n, int d, 
   CU(cudaMemsetAsync(d_g, 0, sizeof(double) * (size_t)F * P, st));
   CU(cudaMemsetAsync(d_dir, 0, sizeof(double) * (size_t)F * P, st));
   CU(cudaMemsetAsync(d_hist, 0, sizeof(unsigned long long) * 512, st));
-  CU(cudaMemsetAsync(d_lossPart, 0, sizeof(float) * (size_t)tiles_total * S_max, st));
   label_hist_kernel<<<(unsigned)std::min<int64_t>(cdiv(n, 256), 4 * ctx->n_sms), 256, 0, st>>>(fold_id, hold_id, n, d_hist);
   KCHECK();
   int64_t n_total = n;
@@ -331,19 +333,20 @@ extern "C" int dml_logreg_sweep(dml_ctx* ctx, const float* X, int64_t n, int d, 
       fp.n_slots = n_slots; fp.T = T; fp.tile_n = tile_n;
       fp.ycls = y; fp.yreg = nullptr; fp.fold_id = fold_id; fp.hold_id = hold_id;
       fp.slot_sel = d_sel; fp.slot_val = d_val;
-      fp.R = d_R; fp.ldr = ldr; fp.lossPart = d_lossPart; fp.gbPart = d_gbPart;
+      fp.R = d_R; fp.ldr = ldr; fp.lossPart = d_lossPart;
       dim3 g1((unsigned)cdiv(rows, BM), (unsigned)cdiv(n_slots, tile_n));
       fwd_kernel<FWD_LOGREG><<<g1, NT, kFwdSmemBytes, st>>>(fp);
-      GradParams gp{X, ldx, r0, rows, d, xvec, d_R, ldr, n_slots, rps, d_Gpart, ldg, ci > 0 ? 1 : 0};
-      dim3 g2((unsigned)cdiv(n_slots, BM), (unsigned)nt, (unsigned)splits);
+      GradParams gp{X, ldx, r0, rows, d, xvec, d_R, ldr, n_slots, rps, d_Gpart, ldg};
+      const int splits_here = (int)cdiv(rows, rps);
+      dim3 g2((unsigned)cdiv(n_slots, BM), (unsigned)nt, (unsigned)splits_here);
       grad_kernel<<<g2, NT, kGemmSmemBytes, st>>>(gp);
+      ReduceParams rp{d_Gpart, ldg, splits_here, n_slots, d, T, d_lossPart, r0 / BM, cdiv(rows, BM), d_Gred, ldgr, ci > 0 ? 1 : 0};
+      reduce_grad_kernel<<<n_slots, 128, 0, st>>>(rp);
+      reduce_tiles_kernel<<<(unsigned)cdiv(n_active, 32), dim3(32, 8), 0, st>>>(rp);
       launches += 2;
+      ctx->total_launches += 2;
     }
     tock(ctx, launches);
-    KCHECK();
-    ReduceParams rp{d_Gpart, ldg, splits, n_slots, d, d_lossPart, d_gbPart, tiles_total, d_Gred, ldgr};
-    reduce_grad_kernel<<<n_slots, 128, 0, st>>>(rp);
-    reduce_tiles_kernel<<<(unsigned)cdiv(n_slots, 32), dim3(32, 8), 0, st>>>(rp);
     KCHECK();
     if (ctx->comm) { int rc = allreduce(ctx, d_Gred, (size_t)n_slots * ldgr, kNcclFloat64); if (rc) return rc; }
     LbfgsParams lp{d, T, P, ldgr, d_st, d_x, d_g, d_dir, d_gt, d_S, d_Y, d_ys, d_active, d_nactive, d_Gred};
@@ -354,7 +357,7 @@ extern "C" int dml_logreg_sweep(dml_ctx* ctx, const float* X, int64_t n, int d, 
     CU(cudaMemcpyAsync(ctx->h_scalar, d_nactive, sizeof(int), cudaMemcpyDeviceToHost, st));
     CU(cudaStreamSynchronize(st));
     n_active = ctx->h_scalar[0];
-    ctx->total_launches += launches + 5;
+    ctx->total_launches += launches + 3;
     if (++rounds > 200000) return fail(ctx, DML_ERR_LIMIT, "dml_logreg_sweep: round cap hit");
   }
   // results + score pass on every fit's held-out rows
@@ -366,9 +369,9 @@ extern "C" int dml_logreg_sweep(dml_ctx* ctx, const float* X, int64_t n, int d, 
   ctx->total_launches += 1;
   if (correct_out || n_test_out) {
     int rc = run_score(ctx, FWD_SCORE_CLS, X, n, d, ldx, y, nullptr, fold_id, hold_id, d_Wt, ldw, d_bt, d_sel, d_val,
-                       (int)S_max, T, d_lossPart);
+                       (int)S_max, T, d_cntPart);
     if (rc) return rc;
-    reduce_counts_kernel<<<F, 256, 0, st>>>((const int32_t*)d_lossPart, tiles_total, (int)S_max, T, d_correct);
+    reduce_counts_kernel<<<F, 256, 0, st>>>(d_cntPart, tiles_total, (int)S_max, T, d_correct);
     KCHECK();
     if (ctx->comm) { rc = allreduce(ctx, d_correct, F, kNcclInt64); if (rc) return rc; }
     if (correct_out) CU(cudaMemcpyAsync(correct_out, d_correct, sizeof(int64_t) * F, cudaMemcpyDeviceToDevice, st));

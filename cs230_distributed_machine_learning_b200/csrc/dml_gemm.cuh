@@ -21,7 +21,7 @@ namespace dml {
 constexpr int BM = 128, BN = 128, BK = 16, LDS = 132, NT = 256;
 constexpr int ZP = 129;  // pitch of the epilogue tile (odd => conflict-free both ways)
 constexpr int kGemmSmemBytes = 2 * 2 * BK * LDS * 4;                 // A,B double-buffered
-constexpr int kEpiSmemBytes = BM * ZP * 4 + BM * 16 + 4 * 256 * 4;   // Z tile + row meta + red
+constexpr int kEpiSmemBytes = BM * ZP * 4 + BM * 16 + 8192;          // Z tile + row meta + red
 constexpr int kFwdSmemBytes = kEpiSmemBytes > kGemmSmemBytes ? kEpiSmemBytes : kGemmSmemBytes;
 
 // ---- operand loaders ----------------------------------------------------------------
@@ -167,7 +167,7 @@ struct FwdParams {
   const int8_t* fold_id; const int8_t* hold_id;   // row labels (hold_id may be null)
   const int32_t* slot_sel; const int32_t* slot_val; // per slot: which label array, which value is held out
   float* R; int ldr;                                // [rows][ldr], chunk local (FWD_LOGREG)
-  float* lossPart; float* gbPart;                   // [row tiles][n_slots]
+  double* lossPart;                                 // [row tiles][n_slots / T]: fp64, see DESIGN.md "precision"
   int32_t* cntPart; float* ssePart;                 // [row tiles][n_slots] (score modes)
 };
 
@@ -203,7 +203,8 @@ __global__ void __launch_bounds__(NT) fwd_kernel(const FwdParams p) {
   int32_t* rowY = reinterpret_cast<int32_t*>(smem + BM * ZP);
   float* rowYf = reinterpret_cast<float*>(rowY + BM);
   int32_t* rowLab = rowY + 2 * BM;                         // fold | hold<<8
-  float* red = reinterpret_cast<float*>(rowY + 4 * BM);    // [4][256]
+  double* redd = reinterpret_cast<double*>(rowY + 4 * BM); // [512] doubles
+  int* redi = reinterpret_cast<int*>(redd + 512);          // [256] ints
 #pragma unroll
   for (int i = 0; i < 8; ++i)
 #pragma unroll
@@ -223,9 +224,11 @@ __global__ void __launch_bounds__(NT) fwd_kernel(const FwdParams p) {
 
   const int T = p.T;
   if (T == 1) {
-    // thread -> (slot column, half of the rows); running sums stay in registers
+    // thread -> (slot column, half of the rows); running sums stay in registers.  The loss is
+    // summed in fp64: More'-Thuente interpolates on differences of f, and fp32 summation noise
+    // (1e-8 relative) is enough to move the accepted step (DESIGN.md "precision").
     const int c = threadIdx.x & 127, half = threadIdx.x >> 7;
-    float s0 = 0.f, s1 = 0.f; int cnt = 0;
+    double s0 = 0.0; int cnt = 0;
     if (c < slots_here) {
       const int sel = p.slot_sel[slot0 + c], val = p.slot_val[slot0 + c];
       const float b = p.bt[slot0 + c];
@@ -238,34 +241,27 @@ __global__ void __launch_bounds__(NT) fwd_kernel(const FwdParams p) {
           float res = 0.f;
           if (!held) {
             const float yv = (float)rowY[r];
-            s0 += softplus_f(z) - yv * z;
+            s0 += (double)(softplus_f(z) - yv * z);
             res = sigmoid_f(z) - yv;
-            s1 += res;
           }
           Zs[r * ZP + c] = res;
         } else if (MODE == FWD_SCORE_CLS) {
           if (held) cnt += ((z > 0.f) ? 1 : 0) == rowY[r];
         } else {
-          if (held) { const float e = rowYf[r] - z; s0 += e * e; }
+          if (held) { const float e = rowYf[r] - z; s0 += (double)(e * e); }
         }
       }
     } else if (MODE == FWD_LOGREG) {
       for (int r = half * 64; r < half * 64 + 64; ++r) Zs[r * ZP + c] = 0.f;
     }
-    red[threadIdx.x] = s0; red[256 + threadIdx.x] = s1;
-    reinterpret_cast<int*>(red)[512 + threadIdx.x] = cnt;
+    redd[threadIdx.x] = s0;
+    redi[threadIdx.x] = cnt;
     __syncthreads();
     if (threadIdx.x < slots_here) {
       const int64_t o = tile_id * p.n_slots + slot0 + threadIdx.x;
-      if (MODE == FWD_LOGREG) {
-        p.lossPart[o] = red[threadIdx.x] + red[128 + threadIdx.x];
-        p.gbPart[o] = red[256 + threadIdx.x] + red[256 + 128 + threadIdx.x];
-      } else if (MODE == FWD_SCORE_CLS) {
-        const int* ri = reinterpret_cast<int*>(red) + 512;
-        p.cntPart[o] = ri[threadIdx.x] + ri[128 + threadIdx.x];
-      } else {
-        p.ssePart[o] = red[threadIdx.x] + red[128 + threadIdx.x];
-      }
+      if (MODE == FWD_LOGREG) p.lossPart[o] = redd[threadIdx.x] + redd[128 + threadIdx.x];
+      else if (MODE == FWD_SCORE_CLS) p.cntPart[o] = redi[threadIdx.x] + redi[128 + threadIdx.x];
+      else p.ssePart[o] = (float)(redd[threadIdx.x] + redd[128 + threadIdx.x]);
     }
   } else {
     // thread -> (row, group of T consecutive slots = one fit); a warp covers 32 rows of one group
@@ -301,34 +297,22 @@ __global__ void __launch_bounds__(NT) fwd_kernel(const FwdParams p) {
       // one (group, 32-row block) per warp iteration
       const int wslot = it >> 5;  // = g*4 + row block
       if (MODE == FWD_LOGREG) {
-        loss = warp_sum(loss);
-        if ((threadIdx.x & 31) == 0) red[wslot] = loss;
+        const double l = warp_sum((double)loss);
+        if ((threadIdx.x & 31) == 0) redd[wslot] = l;
       } else {
         const unsigned bal = __ballot_sync(0xffffffffu, ok);
-        if ((threadIdx.x & 31) == 0) reinterpret_cast<int*>(red)[wslot] = __popc(bal);
+        if ((threadIdx.x & 31) == 0) redi[wslot] = __popc(bal);
       }
     }
     __syncthreads();
     if (threadIdx.x < groups) {
-      const int64_t o = tile_id * p.n_slots + slot0 + threadIdx.x * T;
       if (MODE == FWD_LOGREG) {
-        const float* q = red + threadIdx.x * 4;
-        p.lossPart[o] = (q[0] + q[1]) + (q[2] + q[3]);
+        const double* q = redd + threadIdx.x * 4;
+        p.lossPart[tile_id * (p.n_slots / T) + slot0 / T + threadIdx.x] = (q[0] + q[1]) + (q[2] + q[3]);
       } else {
-        const int* q = reinterpret_cast<int*>(red) + threadIdx.x * 4;
-        p.cntPart[o] = q[0] + q[1] + q[2] + q[3];
+        const int* q = redi + threadIdx.x * 4;
+        p.cntPart[tile_id * p.n_slots + slot0 + threadIdx.x * T] = q[0] + q[1] + q[2] + q[3];
       }
-    }
-    if (MODE == FWD_LOGREG) {
-      // column sums of R for the intercept gradient
-      const int c = threadIdx.x & 127, half = threadIdx.x >> 7;
-      float s1 = 0.f;
-      if (c < slots_here) for (int r = half * 64; r < half * 64 + 64; ++r) s1 += Zs[r * ZP + c];
-      __syncthreads();
-      red[threadIdx.x] = s1;
-      __syncthreads();
-      if (threadIdx.x < slots_here)
-        p.gbPart[tile_id * p.n_slots + slot0 + threadIdx.x] = red[threadIdx.x] + red[128 + threadIdx.x];
     }
   }
   if (MODE == FWD_LOGREG) {
@@ -345,13 +329,12 @@ __global__ void __launch_bounds__(NT) fwd_kernel(const FwdParams p) {
   }
 }
 
-// ---- gradient kernel: Gpart[split][slot][j] (+)= sum_rows R[row][slot] X[row][j] -------
+// ---- gradient kernel: Gpart[split][slot][j] = sum_rows R[row][slot] [X | 1][row][j] -------
 struct GradParams {
   const float* X; int64_t ldx; int64_t row0; int64_t rows; int d; bool xvec;
   const float* R; int ldr; int n_slots;
   int64_t rows_per_split;
-  float* Gpart; int ldg;  // [splits][n_slots][ldg]
-  int accumulate;         // 0: overwrite, 1: add to what is there (later chunks)
+  float* Gpart; int ldg;  // [splits][n_slots][ldg], ldg >= d + 1 (column d = sum of residuals)
 };
 
 __global__ void __launch_bounds__(NT) grad_kernel(const GradParams p) {
@@ -367,8 +350,9 @@ __global__ void __launch_bounds__(NT) grad_kernel(const GradParams p) {
   if (kb < ke) {
     LoadMN la{p.R + kb * p.ldr + slot0, p.ldr, min(BM, p.ldr - slot0), (int)(ke - kb), true,
               false, nullptr, 0, false, 0, 0, 0, nullptr, nullptr};
-    LoadMN lb{p.X + (p.row0 + kb) * p.ldx + j0, p.ldx, min(BN, p.d - j0), (int)(ke - kb), p.xvec,
-              false, nullptr, 0, false, 0, 0, 0, nullptr, nullptr};
+    // columns: the d features, then a column of ones (intercept gradient = sum of residuals)
+    LoadMN lb{p.X + (p.row0 + kb) * p.ldx + j0, p.ldx, max(0, min(BN, p.d - j0)), (int)(ke - kb), p.xvec,
+              false, nullptr, 0, true, j0, p.d, 0, nullptr, nullptr};
     gemm_mainloop(acc, la, lb, 0, (int)(ke - kb), smem, nullptr, 0);
   }
   float* out = p.Gpart + (int64_t)split * p.n_slots * p.ldg;
@@ -379,10 +363,7 @@ __global__ void __launch_bounds__(NT) grad_kernel(const GradParams p) {
 #pragma unroll
     for (int j = 0; j < 8; ++j) {
       const int c = j0 + acc_col(j);
-      if (c < p.d) {
-        float* q = out + (int64_t)s * p.ldg + c;
-        *q = p.accumulate ? *q + acc[i][j] : acc[i][j];
-      }
+      if (c <= p.d) out[(int64_t)s * p.ldg + c] = acc[i][j];
     }
   }
 }

@@ -317,36 +317,37 @@ __global__ void write_trial_kernel(const TrialParams p) {
   }
 }
 
-// partial sums -> fp64 per-slot record [G(0..d-1), gb, loss]; fixed summation order
+// partial sums -> fp64 per-slot record [G(0..d-1), gb, loss]; fixed summation order.
+// `accumulate` adds to the record (row chunks after the first).
 struct ReduceParams {
-  const float* Gpart; int ldg; int splits; int n_slots; int d;
-  const float* lossPart; const float* gbPart; int64_t n_tiles;
-  double* Gred; int ldgr;
+  const float* Gpart; int ldg; int splits; int n_slots; int d; int T;
+  const double* lossPart; int64_t tile0, n_tiles;
+  double* Gred; int ldgr; int accumulate;
 };
 __global__ void reduce_grad_kernel(const ReduceParams p) {
   const int slot = blockIdx.x;
-  for (int j = threadIdx.x; j < p.d; j += blockDim.x) {
+  for (int j = threadIdx.x; j <= p.d; j += blockDim.x) {
     double acc = 0.0;
     for (int s = 0; s < p.splits; ++s) acc += (double)p.Gpart[((int64_t)s * p.n_slots + slot) * p.ldg + j];
-    p.Gred[(int64_t)slot * p.ldgr + j] = acc;
+    double* q = p.Gred + (int64_t)slot * p.ldgr + j;
+    *q = p.accumulate ? *q + acc : acc;
   }
 }
+// loss of group g (fit) = sum over this chunk's row tiles; block = (32 groups, 8 tile lanes)
 __global__ void reduce_tiles_kernel(const ReduceParams p) {
-  __shared__ double sh[2][8][33];
-  const int slot = blockIdx.x * 32 + threadIdx.x;
-  double a = 0.0, b = 0.0;
-  if (slot < p.n_slots)
-    for (int64_t t = threadIdx.y; t < p.n_tiles; t += 8) {
-      a += (double)p.lossPart[t * p.n_slots + slot];
-      b += (double)p.gbPart[t * p.n_slots + slot];
-    }
-  sh[0][threadIdx.y][threadIdx.x] = a; sh[1][threadIdx.y][threadIdx.x] = b;
+  __shared__ double sh[8][33];
+  const int n_groups = p.n_slots / p.T;
+  const int g = blockIdx.x * 32 + threadIdx.x;
+  double a = 0.0;
+  if (g < n_groups)
+    for (int64_t t = p.tile0 + threadIdx.y; t < p.tile0 + p.n_tiles; t += 8) a += p.lossPart[t * n_groups + g];
+  sh[threadIdx.y][threadIdx.x] = a;
   __syncthreads();
-  if (threadIdx.y == 0 && slot < p.n_slots) {
-    double l = 0.0, gsum = 0.0;
-    for (int i = 0; i < 8; ++i) { l += sh[0][i][threadIdx.x]; gsum += sh[1][i][threadIdx.x]; }
-    p.Gred[(int64_t)slot * p.ldgr + p.d] = gsum;
-    p.Gred[(int64_t)slot * p.ldgr + p.d + 1] = l;
+  if (threadIdx.y == 0 && g < n_groups) {
+    double l = 0.0;
+    for (int i = 0; i < 8; ++i) l += sh[i][threadIdx.x];
+    double* q = p.Gred + (int64_t)g * p.T * p.ldgr + p.d + 1;
+    *q = p.accumulate ? *q + l : l;
   }
 }
 

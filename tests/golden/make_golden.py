@@ -18,7 +18,14 @@ Outputs
   sweep_small.npz          scikit-learn 1.9.0 answers (coef, intercept, n_iter,
                            per-fold correct counts / sse / sst) for small seeded
                            versions of BASELINE.json configs 2-5, produced through
-                           the same ``train_model`` call sequence.
+                           the same ``train_model`` call sequence.  The float32
+                           synthetic values are handed to scikit-learn as float64,
+                           which is what the reference worker does with every
+                           dataset (pd.read_csv -> float64, worker.py:425-429).
+                           scikit-learn's own float32 code path sums the loss in
+                           float32 and lands up to 1e-3 away from its float64
+                           answer on the same values (line-search noise), so it
+                           cannot serve as a 1e-4 parity target for anyone.
 """
 import json
 import os
@@ -158,6 +165,9 @@ def main():
     }
     for name, (kind, n, d, seed, model, cands, cv) in cases.items():
         X, y = make_dataset(kind, n, d, seed=seed)
+        X = X.astype(np.float64)
+        if kind == "regression":
+            y = y.astype(np.float64)
         res = rp.sweep(model, {}, cands, X, y, cv=cv)
         coef = np.stack([np.stack([np.atleast_2d(f["model"].coef_) for f in row]) for row in res["fits"]])
         icpt = np.stack([np.stack([np.atleast_1d(f["model"].intercept_) for f in row]) for row in res["fits"]])

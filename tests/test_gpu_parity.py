@@ -3,6 +3,13 @@
 Bars (BASELINE.json north_star): identical fold labels, per-fold correct counts
 bit-exact except on decision ties, coefficients / scores within 1e-4 relative,
 best candidate identical under sklearn's rule.
+
+The comparison target is scikit-learn fed the same values as float64 -- the
+reference worker's actual path (pd.read_csv -> float64, worker.py:425-429).
+scikit-learn's float32 path is NOT a usable target: it sums the per-sample loss in
+float32, and that noise moves More'-Thuente interpolation steps enough to land up
+to 1e-3 away from scikit-learn's own float64 result on identical values
+(DESIGN.md, "precision").
 """
 import json
 import os
@@ -149,7 +156,7 @@ def test_logreg_ragged_shapes_and_options(solver, n, d, k):
         for i, c in enumerate(cands):
             for f in range(cv):
                 tr, te = fold != f, fold == f
-                m = LogisticRegression(**c).fit(X[tr], y[tr])
+                m = LogisticRegression(**c).fit(X[tr].astype(np.float64), y[tr])
                 if out["n_iter"][i, f] != m.n_iter_[0]:
                     continue
                 assert rel_err(out["coef"][i, f], m.coef_) <= 5 * RTOL, (i, f)
@@ -168,7 +175,7 @@ def test_holdout_fit_equals_train_test_split(solver):
     hold = folds.holdout_labels(len(y), 0.25, 42)
     ds = solver.upload_dataset(X, y, classifier=True)
     out = solver.logreg_sweep(ds, fold, 5, [0.5], [1e-4], [True], [100], hold_id=hold)
-    Xtr, Xte, ytr, yte = train_test_split(X, y, test_size=0.25, random_state=42)
+    Xtr, Xte, ytr, yte = train_test_split(X.astype(np.float64), y, test_size=0.25, random_state=42)
     m = LogisticRegression(C=0.5).fit(Xtr, ytr)
     assert out["coef"].shape == (1, 6, 1, 16)
     assert rel_err(out["coef"][0, 5], m.coef_) <= RTOL
@@ -177,7 +184,7 @@ def test_holdout_fit_equals_train_test_split(solver):
     Xr, yr = make_dataset("regression", 3000, 16, seed=51)
     dr = solver.upload_dataset(Xr, yr, classifier=False)
     outr = solver.ridge_sweep(dr, folds.kfold_labels(3000, 5), 5, [2.0], [True], classifier=False, hold_id=hold)
-    Xtr, Xte, ytr, yte = train_test_split(Xr, yr, test_size=0.25, random_state=42)
+    Xtr, Xte, ytr, yte = train_test_split(Xr.astype(np.float64), yr.astype(np.float64), test_size=0.25, random_state=42)
     mr = Ridge(alpha=2.0).fit(Xtr, ytr)
     assert rel_err(outr["coef"][0, 5], mr.coef_) <= RTOL
     assert outr["sse"][0, 5] == pytest.approx(float(((yte - mr.predict(Xte)) ** 2).sum()), rel=RTOL)
@@ -212,7 +219,7 @@ def test_api_end_to_end_best_params_equal_gridsearchcv():
         grid = {"C": [float(c) for c in np.logspace(-5, 1, 7)]}
         r = m.train(GridSearchCV(LogisticRegression(), grid, cv=5), "syn-bin", wait_for_completion=True)
         assert r["job_status"] == "completed", r
-        gs = GridSearchCV(LogisticRegression(), grid, cv=5).fit(X, y)
+        gs = GridSearchCV(LogisticRegression(), grid, cv=5).fit(X.astype(np.float64), y)
         jr = r["job_result"]
         assert all(res["executor"] == "b200" for res in jr["results"])
         np.testing.assert_allclose(jr["cv_results_"]["mean_test_score"], gs.cv_results_["mean_test_score"], atol=RTOL)
@@ -224,7 +231,7 @@ def test_api_end_to_end_best_params_equal_gridsearchcv():
         gridr = {"alpha": [float(a) for a in np.logspace(-2, 4, 7)]}
         r = m.train(GridSearchCV(Ridge(), gridr, cv=5), "syn-reg", train_params={"test_size": 0.2, "random_state": 1},
                     wait_for_completion=True)
-        gsr = GridSearchCV(Ridge(), gridr, cv=5).fit(Xr, yr)
+        gsr = GridSearchCV(Ridge(), gridr, cv=5).fit(Xr.astype(np.float64), yr.astype(np.float64))
         jr = r["job_result"]
         np.testing.assert_allclose(jr["cv_results_"]["mean_test_score"], gsr.cv_results_["mean_test_score"], rtol=RTOL)
         assert jr["best_params_"] == gsr.best_params_
