@@ -4,10 +4,12 @@
 #include "dml_gemm.cuh"
 #include "dml_lbfgs.cuh"
 #include "dml_ridge.cuh"
+#include "dml_tc.cuh"
 
 #include <dlfcn.h>
 #include <stdarg.h>
 #include <string.h>
+#include <stdlib.h>
 #include <algorithm>
 #include <vector>
 
@@ -53,8 +55,11 @@ struct dml_ctx {
   size_t ev_used = 0;
   cudaEvent_t ev_total[2] = {nullptr, nullptr};
   float total_ms = 0.f, contraction_ms = 0.f; int contraction_launches = 0, total_launches = 0;
-  size_t r_budget = (size_t)2 << 30;  // bytes of residual scratch per row chunk
+  size_t r_budget = (size_t)4 << 30;  // bytes of residual scratch per row chunk
+  int tc_mask_hi = 1;                 // write the masked hi operand back before the MMAs read it
   long long slot_rounds = 0; int rounds = 0;  // sum over rounds of evaluated columns
+  // debug: scratch of the last evaluation (dml_debug_fetch)
+  const void* dbg_ptr[4] = {nullptr, nullptr, nullptr, nullptr}; size_t dbg_bytes[4] = {0, 0, 0, 0};
 };
 
 static int fail(dml_ctx* c, int code, const char* fmt, ...) {
@@ -144,6 +149,7 @@ extern "C" int dml_ctx_create(int device, void* stream, dml_ctx** out) {
                 device, prop.major, prop.minor);
   ctx = new dml_ctx();
   ctx->device = device; ctx->stream = (cudaStream_t)stream; ctx->n_sms = prop.multiProcessorCount;
+  if (const char* e = getenv("DML_TC_MASK_HI")) ctx->tc_mask_hi = atoi(e);
   CU(cudaSetDevice(device));
   CU(cudaHostAlloc(&ctx->h_scalar, 64, cudaHostAllocDefault));
   ctx->ev.resize(2 * 2048);
@@ -199,11 +205,104 @@ extern "C" int dml_last_timing(dml_ctx* ctx, float* total_ms, float* contraction
   return DML_OK;
 }
 
+// Debug aid: copy scratch buffer `which` (0 R/R_hi, 1 R_lo, 2 Gpart, 3 W_hi) of the last evaluation to the host.
+extern "C" int dml_debug_fetch(dml_ctx* ctx, int which, void* dst_host, size_t bytes, size_t* avail) {
+  if (!ctx || which < 0 || which > 3) return DML_ERR_ARG;
+  if (avail) *avail = ctx->dbg_bytes[which];
+  if (dst_host && ctx->dbg_ptr[which]) {
+    CU(cudaMemcpy(dst_host, ctx->dbg_ptr[which], std::min(bytes, ctx->dbg_bytes[which]), cudaMemcpyDeviceToHost));
+  }
+  return DML_OK;
+}
+
 extern "C" int dml_last_counters(dml_ctx* ctx, int64_t* column_rounds, int32_t* rounds) {
   if (!ctx) return DML_ERR_ARG;
   if (column_rounds) *column_rounds = ctx->slot_rounds;
   if (rounds) *rounds = ctx->rounds;
   return DML_OK;
+}
+
+
+// ---- tcgen05 path: tensor maps + dispatch ---------------------------------------------------
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                  const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
+                                  CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+static EncodeTiledFn g_encode = nullptr;
+static int make_map_2d(dml_ctx* ctx, CUtensorMap* m, const void* base, uint64_t inner, uint64_t outer,
+                       uint64_t stride_bytes, uint32_t box_inner, uint32_t box_outer, bool mn_major = false) {
+  if (!g_encode) {
+    void* fn = nullptr;
+    cudaDriverEntryPointQueryResult q;
+    CU(cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &fn, cudaEnableDefault, &q));
+    if (!fn || q != cudaDriverEntryPointSuccess) return fail(ctx, DML_ERR_CUDA, "cuTensorMapEncodeTiled not available");
+    g_encode = (EncodeTiledFn)fn;
+  }
+  cuuint64_t gdim[2] = {inner, outer};
+  cuuint64_t gstr[1] = {stride_bytes};
+  cuuint32_t box[2] = {box_inner, box_outer};
+  cuuint32_t est[2] = {1, 1};
+  const CUresult r = g_encode(m, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, const_cast<void*>(base), gdim, gstr, box, est,
+                              CU_TENSOR_MAP_INTERLEAVE_NONE,
+                              // MN-major tf32 operands need the 128B swizzle with 32-byte atoms
+                              // (UMMA layout SWIZZLE_128B_BASE32B); K-major ones the plain 128B swizzle
+                              mn_major ? CU_TENSOR_MAP_SWIZZLE_128B_ATOM_32B : CU_TENSOR_MAP_SWIZZLE_128B,
+                              CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) return fail(ctx, DML_ERR_CUDA, "cuTensorMapEncodeTiled failed (%d) inner=%llu outer=%llu stride=%llu box=%ux%u",
+                                     (int)r, (unsigned long long)inner, (unsigned long long)outer,
+                                     (unsigned long long)stride_bytes, box_inner, box_outer);
+  return DML_OK;
+}
+// column-block width: the candidate with the least padding, larger on ties
+static int pick_nc(int64_t n_slots) {
+  const int cand[5] = {160, 128, 96, 64, 32};
+  int best = 160; int64_t best_pad = INT64_MAX;
+  for (int c : cand) { const int64_t pad = cdiv(n_slots, c) * c; if (pad < best_pad) { best_pad = pad; best = c; } }
+  return best;
+}
+static bool tc_eligible(const float* X, int64_t ldx, int T) { return T == 1 && ldx % 4 == 0 && aligned16(X); }
+
+template <int NC, int MODE>
+static int launch_tc_fwd_nc(dml_ctx* ctx, int grid, const CUtensorMap& mx, const CUtensorMap& mwh, const CUtensorMap& mwl,
+                            const tc::TcFwdParams& p) {
+  static bool attr_set = false;
+  if (!attr_set) {
+    CU(cudaFuncSetAttribute(tc::tc_fwd_kernel<NC, MODE>, cudaFuncAttributeMaxDynamicSharedMemorySize, tc::FwdSmem<NC>::kBytes));
+    attr_set = true;
+  }
+  tc::tc_fwd_kernel<NC, MODE><<<grid, tc::kFwdThreads, tc::FwdSmem<NC>::kBytes, ctx->stream>>>(mx, mwh, mwl, p);
+  return DML_OK;
+}
+template <int MODE>
+static int launch_tc_fwd(dml_ctx* ctx, int NC, int grid, const CUtensorMap& mx, const CUtensorMap& mwh,
+                         const CUtensorMap& mwl, const tc::TcFwdParams& p) {
+  switch (NC) {
+    case 160: return launch_tc_fwd_nc<160, MODE>(ctx, grid, mx, mwh, mwl, p);
+    case 128: return launch_tc_fwd_nc<128, MODE>(ctx, grid, mx, mwh, mwl, p);
+    case 96: return launch_tc_fwd_nc<96, MODE>(ctx, grid, mx, mwh, mwl, p);
+    case 64: return launch_tc_fwd_nc<64, MODE>(ctx, grid, mx, mwh, mwl, p);
+    default: return launch_tc_fwd_nc<32, MODE>(ctx, grid, mx, mwh, mwl, p);
+  }
+}
+template <int NC>
+static int launch_tc_grad_nc(dml_ctx* ctx, dim3 grid, const CUtensorMap& mx, const CUtensorMap& mrh, const CUtensorMap& mrl,
+                             const tc::TcGradParams& p) {
+  static bool attr_set = false;
+  if (!attr_set) {
+    CU(cudaFuncSetAttribute(tc::tc_grad_kernel<NC>, cudaFuncAttributeMaxDynamicSharedMemorySize, tc::GradSmem<NC>::kBytes));
+    attr_set = true;
+  }
+  tc::tc_grad_kernel<NC><<<grid, tc::kGradThreads, tc::GradSmem<NC>::kBytes, ctx->stream>>>(mx, mrh, mrl, p);
+  return DML_OK;
+}
+static int launch_tc_grad(dml_ctx* ctx, int NC, dim3 grid, const CUtensorMap& mx, const CUtensorMap& mrh,
+                          const CUtensorMap& mrl, const tc::TcGradParams& p) {
+  switch (NC) {
+    case 160: return launch_tc_grad_nc<160>(ctx, grid, mx, mrh, mrl, p);
+    case 128: return launch_tc_grad_nc<128>(ctx, grid, mx, mrh, mrl, p);
+    case 96: return launch_tc_grad_nc<96>(ctx, grid, mx, mrh, mrl, p);
+    case 64: return launch_tc_grad_nc<64>(ctx, grid, mx, mrh, mrl, p);
+    default: return launch_tc_grad_nc<32>(ctx, grid, mx, mrh, mrl, p);
+  }
 }
 
 // ---- shared: one scoring pass over all rows for `n_slots` columns -------------------------
@@ -232,6 +331,148 @@ static int run_score(dml_ctx* ctx, int mode, const float* X, int64_t n, int d, i
 }
 
 // =============================================================================================
+// One batched loss/gradient evaluation for `n_slots` columns: the buffers and the two code paths
+// (tcgen05 3xTF32, or FFMA for shapes the tensor-core path does not take).
+struct EvalCtx {
+  // problem
+  const float* X = nullptr; int64_t n = 0, ldx = 0; int d = 0, T = 1;
+  const int32_t* y = nullptr; const int8_t* fold_id = nullptr; const int8_t* hold_id = nullptr;
+  // plan
+  bool use_tc = false, xvec = false; int NC = 160, nt = 1, tile_n = BN, ldw = 0, ldg = 0, ldgr = 0, splits = 1;
+  int64_t S_max = 0, ldr_max = 0, chunk_rows = 0, rps = 0, tc_rps = 2048, tiles_total = 0;
+  // buffers
+  float *Wt = nullptr, *bt = nullptr, *R = nullptr, *Rlo = nullptr, *Whi = nullptr, *Wlo = nullptr, *Gpart = nullptr;
+  double *lossPart = nullptr, *gbPart = nullptr, *Gred = nullptr; int32_t *sel = nullptr, *val = nullptr, *cntPart = nullptr;
+  CUtensorMap mXf, mXg, mWh, mWl, mRh, mRl;
+
+  void plan(dml_ctx* ctx, int64_t n_groups_max) {
+    ldw = (int)rup(d, 4); ldg = (int)rup(d + 1, 4); ldgr = d + 2;
+    tiles_total = cdiv(n, BM); tile_n = (BN / T) * T;
+    ldr_max = rup(S_max, 4); NC = pick_nc(S_max);
+    // row chunk so that the residual scratch stays within budget
+    chunk_rows = std::max<int64_t>(BM, (int64_t)(ctx->r_budget / (ldr_max * (use_tc ? 8 : 4))) / BM * BM);
+    chunk_rows = std::min<int64_t>(chunk_rows, rup(n, BM));
+    nt = (int)cdiv(d + 1, BN);
+    const int mt_max = (int)cdiv(S_max, BM);
+    // short fp32 accumulation chains (<= 2048 rows), fp64 across splits: keeps the gradient noise
+    // near 1e-7 relative (DESIGN.md "precision"); at least enough splits to fill the machine
+    splits = (int)std::max<int64_t>(cdiv(chunk_rows, 2048),
+                                    std::min<int64_t>(cdiv(2 * ctx->n_sms, (int64_t)mt_max * nt), cdiv(chunk_rows, 256)));
+    rps = rup(cdiv(chunk_rows, splits), 16);
+    splits = (int)cdiv(chunk_rows, rps);
+    if (use_tc) splits = std::max(splits, (int)cdiv(chunk_rows, tc_rps));
+    (void)n_groups_max;
+  }
+  void take(Arena& a, int64_t n_groups_max) {
+    Gred = a.take<double>((size_t)S_max * ldgr);
+    Wt = a.take<float>((size_t)S_max * ldw); bt = a.take<float>(S_max);
+    sel = a.take<int32_t>(S_max); val = a.take<int32_t>(S_max);
+    R = a.take<float>((size_t)chunk_rows * ldr_max);
+    lossPart = a.take<double>((size_t)tiles_total * (use_tc ? 4 * S_max : n_groups_max));
+    cntPart = a.take<int32_t>((size_t)tiles_total * S_max * (use_tc ? 4 : 1));
+    Gpart = a.take<float>((size_t)splits * S_max * ldg);
+    if (use_tc) {
+      Rlo = a.take<float>((size_t)chunk_rows * ldr_max);
+      gbPart = a.take<double>((size_t)tiles_total * S_max * 4);
+      Whi = a.take<float>((size_t)S_max * ldw); Wlo = a.take<float>((size_t)S_max * ldw);
+    }
+  }
+  int make_maps(dml_ctx* ctx) {
+    if (!use_tc) return DML_OK;
+    int rc;
+    if ((rc = make_map_2d(ctx, &mXf, X, d, n, ldx * 4, 32, 128))) return rc;   // forward: 128 rows x 32 features
+    if ((rc = make_map_2d(ctx, &mXg, X, d, n, ldx * 4, 32, 32, true))) return rc;    // gradient: 32 rows x 32 features
+    if ((rc = make_map_2d(ctx, &mWh, Whi, d, S_max, (uint64_t)ldw * 4, 32, NC))) return rc;
+    if ((rc = make_map_2d(ctx, &mWl, Wlo, d, S_max, (uint64_t)ldw * 4, 32, NC))) return rc;
+    if ((rc = make_map_2d(ctx, &mRh, R, ldr_max, chunk_rows, (uint64_t)ldr_max * 4, 32, 32, true))) return rc;
+    if ((rc = make_map_2d(ctx, &mRl, Rlo, ldr_max, chunk_rows, (uint64_t)ldr_max * 4, 32, 32, true))) return rc;
+    return DML_OK;
+  }
+  // Gred[slot] = [sum r x (d), sum r, sum loss] over the training rows of each column
+  int evaluate(dml_ctx* ctx, int n_slots) {
+    cudaStream_t st = ctx->stream;
+    int launches = 0;
+    if (use_tc) {
+      tc::split_weights_kernel<<<(unsigned)cdiv((int64_t)n_slots * ldw, 256), 256, 0, st>>>(Wt, Whi, Wlo, (int64_t)n_slots * ldw);
+      ctx->total_launches += 1;
+    }
+    tick(ctx);
+    for (int64_t r0 = 0, ci = 0; r0 < n; r0 += chunk_rows, ++ci) {
+      const int64_t rows = std::min(chunk_rows, n - r0);
+      if (use_tc) {
+        const int ncb = (int)cdiv(n_slots, NC);
+        tc::TcFwdParams fp{};
+        fp.n_rows_total = n; fp.row0 = r0; fp.rows = rows; fp.d_chunks = (int)cdiv(d, 32);
+        fp.n_slots = n_slots; fp.n_col_blocks = ncb; fp.bt = bt; fp.ycls = y; fp.yreg = nullptr;
+        fp.fold_id = fold_id; fp.hold_id = hold_id; fp.slot_sel = sel; fp.slot_val = val;
+        fp.Rhi = R; fp.Rlo = Rlo; fp.ldr = (int)ldr_max; fp.lossPart = lossPart; fp.gbPart = gbPart;
+        fp.mask_hi = ctx->tc_mask_hi;
+        const int64_t jobs = cdiv(rows, 128) * ncb;
+        int rc = launch_tc_fwd<FWD_LOGREG>(ctx, NC, (int)std::min<int64_t>(jobs, ctx->n_sms), mXf, mWh, mWl, fp);
+        if (rc) return rc;
+        tc::TcGradParams gp{r0, rows, tc_rps, d, n_slots, Gpart, ldg, ctx->tc_mask_hi};
+        const int splits_here = (int)cdiv(rows, tc_rps);
+        rc = launch_tc_grad(ctx, NC, dim3((unsigned)cdiv(d, 128), (unsigned)ncb, (unsigned)splits_here), mXg, mRh, mRl, gp);
+        if (rc) return rc;
+        ReduceParams rp{Gpart, ldg, splits_here, n_slots, d, T, d, nullptr, 0, 0, Gred, ldgr, ci > 0 ? 1 : 0};
+        reduce_grad_kernel<<<n_slots, 128, 0, st>>>(rp);
+        tc::TcReduceParams tr{lossPart, gbPart, (r0 / BM) * 4, cdiv(rows, BM) * 4, n_slots, T, d, Gred, ldgr, ci > 0 ? 1 : 0};
+        tc::tc_reduce_tiles_kernel<<<(unsigned)cdiv(n_slots, 32), dim3(32, 8), 0, st>>>(tr);
+      } else {
+        const int ldr = (int)rup(n_slots, 4);
+        FwdParams fp{};
+        fp.X = X; fp.ldx = ldx; fp.row0 = r0; fp.rows = rows; fp.d = d; fp.xvec = xvec;
+        fp.Wt = Wt; fp.ldw = ldw; fp.wvec = true; fp.bt = bt;
+        fp.n_slots = n_slots; fp.T = T; fp.tile_n = tile_n;
+        fp.ycls = y; fp.yreg = nullptr; fp.fold_id = fold_id; fp.hold_id = hold_id;
+        fp.slot_sel = sel; fp.slot_val = val;
+        fp.R = R; fp.ldr = ldr; fp.lossPart = lossPart;
+        dim3 g1((unsigned)cdiv(rows, BM), (unsigned)cdiv(n_slots, tile_n));
+        fwd_kernel<FWD_LOGREG><<<g1, NT, kFwdSmemBytes, st>>>(fp);
+        GradParams gp{X, ldx, r0, rows, d, xvec, R, ldr, n_slots, rps, Gpart, ldg};
+        const int splits_here = (int)cdiv(rows, rps);
+        dim3 g2((unsigned)cdiv(n_slots, BM), (unsigned)nt, (unsigned)splits_here);
+        grad_kernel<<<g2, NT, kGemmSmemBytes, st>>>(gp);
+        ReduceParams rp{Gpart, ldg, splits_here, n_slots, d, T, d + 1, lossPart, r0 / BM, cdiv(rows, BM), Gred, ldgr, ci > 0 ? 1 : 0};
+        reduce_grad_kernel<<<n_slots, 128, 0, st>>>(rp);
+        reduce_tiles_kernel<<<(unsigned)cdiv(n_slots / T, 32), dim3(32, 8), 0, st>>>(rp);
+      }
+      launches += 2;
+      ctx->total_launches += 4;
+    }
+    tock(ctx, launches);
+    KCHECK();
+    ctx->dbg_ptr[0] = R; ctx->dbg_bytes[0] = (size_t)chunk_rows * ldr_max * 4;
+    ctx->dbg_ptr[1] = Rlo; ctx->dbg_bytes[1] = Rlo ? (size_t)chunk_rows * ldr_max * 4 : 0;
+    ctx->dbg_ptr[2] = Gpart; ctx->dbg_bytes[2] = (size_t)splits * S_max * ldg * 4;
+    ctx->dbg_ptr[3] = Whi; ctx->dbg_bytes[3] = Whi ? (size_t)S_max * ldw * 4 : 0;
+    return DML_OK;
+  }
+  // correct-prediction counts of `n_slots` columns (groups of T) on their held-out rows -> cntPart
+  int score_cls(dml_ctx* ctx, int n_slots, int64_t* n_parts) {
+    cudaStream_t st = ctx->stream;
+    if (use_tc) {
+      tc::split_weights_kernel<<<(unsigned)cdiv((int64_t)n_slots * ldw, 256), 256, 0, st>>>(Wt, Whi, Wlo, (int64_t)n_slots * ldw);
+      tc::TcFwdParams fp{};
+      fp.n_rows_total = n; fp.row0 = 0; fp.rows = n; fp.d_chunks = (int)cdiv(d, 32);
+      fp.n_slots = n_slots; fp.n_col_blocks = (int)cdiv(n_slots, NC); fp.bt = bt; fp.ycls = y;
+      fp.fold_id = fold_id; fp.hold_id = hold_id; fp.slot_sel = sel; fp.slot_val = val;
+      fp.cntPart = cntPart; fp.mask_hi = ctx->tc_mask_hi;
+      const int64_t jobs = tiles_total * fp.n_col_blocks;
+      tick(ctx);
+      int rc = launch_tc_fwd<FWD_SCORE_CLS>(ctx, NC, (int)std::min<int64_t>(jobs, ctx->n_sms), mXf, mWh, mWl, fp);
+      tock(ctx, 1);
+      ctx->total_launches += 2;
+      if (rc) return rc;
+      KCHECK();
+      *n_parts = tiles_total * 4;
+      return DML_OK;
+    }
+    *n_parts = tiles_total;
+    return run_score(ctx, FWD_SCORE_CLS, X, n, d, ldx, y, nullptr, fold_id, hold_id, Wt, ldw, bt, sel, val, n_slots, T, cntPart);
+  }
+};
+
 extern "C" int dml_logreg_sweep(dml_ctx* ctx, const float* X, int64_t n, int d, int64_t ldx,
                                 const int32_t* y, int n_classes,
                                 const int8_t* fold_id, int n_folds, const int8_t* hold_id,
@@ -247,7 +488,6 @@ extern "C" int dml_logreg_sweep(dml_ctx* ctx, const float* X, int64_t n, int d, 
   if (n <= 0 || d <= 0 || ldx < d || n_classes < 2 || n_cand <= 0 || n_folds < 0 || n_folds > 127)
     return fail(ctx, DML_ERR_ARG, "dml_logreg_sweep: bad shape (n=%lld d=%d ldx=%lld classes=%d cand=%d folds=%d)",
                 (long long)n, d, (long long)ldx, n_classes, n_cand, n_folds);
-  (void)use_tensor_cores;
   CU(cudaSetDevice(ctx->device));
   cudaStream_t st = ctx->stream;
   const int T = n_classes == 2 ? 1 : n_classes;
@@ -255,27 +495,18 @@ extern "C" int dml_logreg_sweep(dml_ctx* ctx, const float* X, int64_t n, int d, 
   const int fpc = n_folds + (hold_id ? 1 : 0);
   if (fpc == 0) return fail(ctx, DML_ERR_ARG, "dml_logreg_sweep: no fits requested");
   const int F = n_cand * fpc, P = T * (d + 1);
-  const int64_t S_max = (int64_t)F * T;
-  const int ldw = (int)rup(d, 4), ldg = (int)rup(d + 1, 4), ldgr = d + 2;
-  const int64_t tiles_total = cdiv(n, BM);
-  const int tile_n = (BN / T) * T;
-  if (cdiv(S_max, tile_n) > 65535) return fail(ctx, DML_ERR_LIMIT, "too many columns (%lld)", (long long)S_max);
-  // row chunk so that the residual scratch stays within budget
-  const int64_t ldr_max = rup(S_max, 4);
-  int64_t chunk_rows = std::max<int64_t>(BM, (int64_t)(ctx->r_budget / (ldr_max * 4)) / BM * BM);
-  chunk_rows = std::min<int64_t>(chunk_rows, rup(n, BM));
-  // row splits of the gradient contraction
-  const int mt_max = (int)cdiv(S_max, BM), nt = (int)cdiv(d + 1, BN);
-  // short fp32 accumulation chains (<= 2048 rows), fp64 across splits: keeps the gradient noise
-  // near 1e-7 relative (DESIGN.md "precision"); at least enough splits to fill the machine
-  int splits = (int)std::max<int64_t>(cdiv(chunk_rows, 2048), std::min<int64_t>(cdiv(2 * ctx->n_sms, (int64_t)mt_max * nt), cdiv(chunk_rows, 256)));
-  const int64_t rps = rup(cdiv(chunk_rows, splits), 16);
-  splits = (int)cdiv(chunk_rows, rps);
-  (void)mt_max;
+  EvalCtx ev;
+  ev.X = X; ev.n = n; ev.ldx = ldx; ev.d = d; ev.T = T; ev.y = y; ev.fold_id = fold_id; ev.hold_id = hold_id;
+  ev.S_max = (int64_t)F * T;
+  ev.use_tc = use_tensor_cores != 0 && tc_eligible(X, ldx, T);
+  ev.xvec = (ldx % 4 == 0) && aligned16(X);
+  if (use_tensor_cores == 1 && !ev.use_tc)
+    return fail(ctx, DML_ERR_ARG, "tensor-core path needs a binary problem, ldx %% 4 == 0 and 16-byte aligned X");
+  ev.plan(ctx, F);
+  if (cdiv(ev.S_max, ev.tile_n) > 65535) return fail(ctx, DML_ERR_LIMIT, "too many columns (%lld)", (long long)ev.S_max);
 
-  FitState* d_st; double *d_x, *d_g, *d_dir, *d_gt, *d_S, *d_Y, *d_ys, *d_Gred;
-  int *d_active, *d_nactive; unsigned long long* d_hist; long long* d_correct;
-  float *d_Wt, *d_bt, *d_R, *d_Gpart; double* d_lossPart; int32_t *d_sel, *d_val, *d_i32, *d_cntPart;
+  FitState* d_st; double *d_x, *d_g, *d_dir, *d_gt, *d_S, *d_Y, *d_ys;
+  int *d_active, *d_nactive; unsigned long long* d_hist; long long* d_correct; int32_t* d_i32;
   for (int pass = 0; pass < 2; ++pass) {
     Arena a(pass ? ctx->ws : nullptr);
     d_st = a.take<FitState>(F); d_i32 = a.take<int32_t>(3 * (size_t)F);
@@ -283,17 +514,12 @@ extern "C" int dml_logreg_sweep(dml_ctx* ctx, const float* X, int64_t n, int d, 
     d_dir = a.take<double>((size_t)F * P); d_gt = a.take<double>((size_t)F * P);
     d_S = a.take<double>((size_t)F * kMaxCor * P); d_Y = a.take<double>((size_t)F * kMaxCor * P);
     d_ys = a.take<double>((size_t)F * kMaxCor);
-    d_Gred = a.take<double>((size_t)S_max * ldgr);
     d_active = a.take<int>(F); d_nactive = a.take<int>(4);
     d_hist = a.take<unsigned long long>(512); d_correct = a.take<long long>(F);
-    d_Wt = a.take<float>((size_t)S_max * ldw); d_bt = a.take<float>(S_max);
-    d_sel = a.take<int32_t>(S_max); d_val = a.take<int32_t>(S_max);
-    d_R = a.take<float>((size_t)chunk_rows * ldr_max);
-    d_lossPart = a.take<double>((size_t)tiles_total * F);
-    d_cntPart = a.take<int32_t>((size_t)tiles_total * S_max);
-    d_Gpart = a.take<float>((size_t)splits * S_max * ldg);
+    ev.take(a, F);
     if (!pass) { int rc = ensure_ws(ctx, a.off + 256); if (rc) return rc; }
   }
+  { int rc = ev.make_maps(ctx); if (rc) return rc; }
   timing_begin(ctx);
   CU(cudaMemsetAsync(d_x, 0, sizeof(double) * (size_t)F * P, st));
   CU(cudaMemsetAsync(d_g, 0, sizeof(double) * (size_t)F * P, st));
@@ -304,8 +530,7 @@ extern "C" int dml_logreg_sweep(dml_ctx* ctx, const float* X, int64_t n, int d, 
   int64_t n_total = n;
   if (ctx->comm) {
     int rc = allreduce(ctx, d_hist, 512, kNcclUint64); if (rc) return rc;
-    // total rows = sum of the fold histogram
-    std::vector<unsigned long long> h(256);
+    std::vector<unsigned long long> h(256);   // total rows = sum of the fold histogram
     CU(cudaMemcpyAsync(h.data(), d_hist, 256 * sizeof(unsigned long long), cudaMemcpyDeviceToHost, st));
     CU(cudaStreamSynchronize(st));
     n_total = 0; for (auto v : h) n_total += (int64_t)v;
@@ -313,43 +538,19 @@ extern "C" int dml_logreg_sweep(dml_ctx* ctx, const float* X, int64_t n, int d, 
   InitParams ip{F, n_folds, hold_id ? 1 : 0, fpc, n_total, d_hist, C, tol, fit_intercept, max_iter, d_st, d_active, d_nactive};
   init_fits_kernel<<<(unsigned)cdiv(F, 128), 128, 0, st>>>(ip);
   KCHECK();
-  TrialParams tp{d, T, P, ldw, d_st, d_x, d_dir, d_active, d_nactive, d_Wt, d_bt, d_sel, d_val};
+  TrialParams tp{d, T, P, ev.ldw, d_st, d_x, d_dir, d_active, d_nactive, ev.Wt, ev.bt, ev.sel, ev.val};
   write_trial_kernel<<<F, 128, 0, st>>>(tp);
   KCHECK();
   ctx->total_launches += 3;
 
   int n_active = F, rounds = 0;
-  const bool xvec = (ldx % 4 == 0) && aligned16(X);
   while (n_active > 0) {
-    const int n_slots = n_active * T, ldr = (int)rup(n_slots, 4);
+    const int n_slots = n_active * T;
     ctx->slot_rounds += n_slots; ctx->rounds += 1;
-    int launches = 0;
-    tick(ctx);
-    for (int64_t r0 = 0, ci = 0; r0 < n; r0 += chunk_rows, ++ci) {
-      const int64_t rows = std::min(chunk_rows, n - r0);
-      FwdParams fp{};
-      fp.X = X; fp.ldx = ldx; fp.row0 = r0; fp.rows = rows; fp.d = d; fp.xvec = xvec;
-      fp.Wt = d_Wt; fp.ldw = ldw; fp.wvec = true; fp.bt = d_bt;
-      fp.n_slots = n_slots; fp.T = T; fp.tile_n = tile_n;
-      fp.ycls = y; fp.yreg = nullptr; fp.fold_id = fold_id; fp.hold_id = hold_id;
-      fp.slot_sel = d_sel; fp.slot_val = d_val;
-      fp.R = d_R; fp.ldr = ldr; fp.lossPart = d_lossPart;
-      dim3 g1((unsigned)cdiv(rows, BM), (unsigned)cdiv(n_slots, tile_n));
-      fwd_kernel<FWD_LOGREG><<<g1, NT, kFwdSmemBytes, st>>>(fp);
-      GradParams gp{X, ldx, r0, rows, d, xvec, d_R, ldr, n_slots, rps, d_Gpart, ldg};
-      const int splits_here = (int)cdiv(rows, rps);
-      dim3 g2((unsigned)cdiv(n_slots, BM), (unsigned)nt, (unsigned)splits_here);
-      grad_kernel<<<g2, NT, kGemmSmemBytes, st>>>(gp);
-      ReduceParams rp{d_Gpart, ldg, splits_here, n_slots, d, T, d_lossPart, r0 / BM, cdiv(rows, BM), d_Gred, ldgr, ci > 0 ? 1 : 0};
-      reduce_grad_kernel<<<n_slots, 128, 0, st>>>(rp);
-      reduce_tiles_kernel<<<(unsigned)cdiv(n_active, 32), dim3(32, 8), 0, st>>>(rp);
-      launches += 2;
-      ctx->total_launches += 2;
-    }
-    tock(ctx, launches);
-    KCHECK();
-    if (ctx->comm) { int rc = allreduce(ctx, d_Gred, (size_t)n_slots * ldgr, kNcclFloat64); if (rc) return rc; }
-    LbfgsParams lp{d, T, P, ldgr, d_st, d_x, d_g, d_dir, d_gt, d_S, d_Y, d_ys, d_active, d_nactive, d_Gred};
+    int rc = ev.evaluate(ctx, n_slots);
+    if (rc) return rc;
+    if (ctx->comm) { rc = allreduce(ctx, ev.Gred, (size_t)n_slots * ev.ldgr, kNcclFloat64); if (rc) return rc; }
+    LbfgsParams lp{d, T, P, ev.ldgr, d_st, d_x, d_g, d_dir, d_gt, d_S, d_Y, d_ys, d_active, d_nactive, ev.Gred};
     lbfgs_update_kernel<<<n_active, 256, 0, st>>>(lp);
     compact_kernel<<<1, 1024, 0, st>>>(d_st, F, d_active, d_nactive, d_nactive + 1);
     write_trial_kernel<<<n_active, 128, 0, st>>>(tp);
@@ -357,21 +558,21 @@ extern "C" int dml_logreg_sweep(dml_ctx* ctx, const float* X, int64_t n, int d, 
     CU(cudaMemcpyAsync(ctx->h_scalar, d_nactive, sizeof(int), cudaMemcpyDeviceToHost, st));
     CU(cudaStreamSynchronize(st));
     n_active = ctx->h_scalar[0];
-    ctx->total_launches += launches + 3;
+    ctx->total_launches += 3;
     if (++rounds > 200000) return fail(ctx, DML_ERR_LIMIT, "dml_logreg_sweep: round cap hit");
   }
   // results + score pass on every fit's held-out rows
-  FinalParams fin{F, d, T, P, ldw, d_st, d_x, coef_out, intercept_out, n_iter_out ? n_iter_out : d_i32,
+  FinalParams fin{F, d, T, P, ev.ldw, d_st, d_x, coef_out, intercept_out, n_iter_out ? n_iter_out : d_i32,
                   status_out ? status_out : d_i32 + F, nfev_out ? nfev_out : d_i32 + 2 * F,
-                  d_Wt, d_bt, d_sel, d_val};
+                  ev.Wt, ev.bt, ev.sel, ev.val};
   finalize_kernel<<<F, 128, 0, st>>>(fin);
   KCHECK();
   ctx->total_launches += 1;
   if (correct_out || n_test_out) {
-    int rc = run_score(ctx, FWD_SCORE_CLS, X, n, d, ldx, y, nullptr, fold_id, hold_id, d_Wt, ldw, d_bt, d_sel, d_val,
-                       (int)S_max, T, d_cntPart);
+    int64_t n_parts = 0;
+    int rc = ev.score_cls(ctx, (int)ev.S_max, &n_parts);
     if (rc) return rc;
-    reduce_counts_kernel<<<F, 256, 0, st>>>(d_cntPart, tiles_total, (int)S_max, T, d_correct);
+    reduce_counts_kernel<<<F, 256, 0, st>>>(ev.cntPart, n_parts, (int)ev.S_max, T, d_correct);
     KCHECK();
     if (ctx->comm) { rc = allreduce(ctx, d_correct, F, kNcclInt64); if (rc) return rc; }
     if (correct_out) CU(cudaMemcpyAsync(correct_out, d_correct, sizeof(int64_t) * F, cudaMemcpyDeviceToDevice, st));
@@ -390,6 +591,47 @@ extern "C" int dml_logreg_sweep(dml_ctx* ctx, const float* X, int64_t n, int d, 
   timing_end(ctx);
   CU(cudaStreamSynchronize(st));
   if (rounds_out) *rounds_out = rounds;
+  return DML_OK;
+}
+
+// Loss and gradient sums of given coefficient columns (binary logistic): one batched evaluation.
+extern "C" int dml_logreg_eval(dml_ctx* ctx, const float* X, int64_t n, int d, int64_t ldx, const int32_t* y,
+                               const int8_t* fold_id, const int8_t* hold_id,
+                               const float* W, const float* b, const int32_t* mask_sel, const int32_t* mask_val,
+                               int n_slots, double* out, int use_tensor_cores) {
+  if (!ctx) return DML_ERR_ARG;
+  if (!X || !y || !fold_id || !W || !b || !mask_sel || !mask_val || !out || n <= 0 || d <= 0 || ldx < d || n_slots <= 0)
+    return fail(ctx, DML_ERR_ARG, "dml_logreg_eval: bad argument");
+  CU(cudaSetDevice(ctx->device));
+  cudaStream_t st = ctx->stream;
+  EvalCtx ev;
+  ev.X = X; ev.n = n; ev.ldx = ldx; ev.d = d; ev.T = 1; ev.y = y; ev.fold_id = fold_id; ev.hold_id = hold_id;
+  ev.S_max = n_slots;
+  ev.use_tc = use_tensor_cores != 0 && tc_eligible(X, ldx, 1);
+  ev.xvec = (ldx % 4 == 0) && aligned16(X);
+  if (use_tensor_cores == 1 && !ev.use_tc) return fail(ctx, DML_ERR_ARG, "tensor-core path needs ldx %% 4 == 0 and aligned X");
+  ev.plan(ctx, n_slots);
+  for (int pass = 0; pass < 2; ++pass) {
+    Arena a(pass ? ctx->ws : nullptr);
+    ev.take(a, n_slots);
+    if (!pass) { int rc = ensure_ws(ctx, a.off + 256); if (rc) return rc; }
+  }
+  { int rc = ev.make_maps(ctx); if (rc) return rc; }
+  timing_begin(ctx);
+  CU(cudaMemcpy2DAsync(ev.Wt, (size_t)ev.ldw * 4, W, (size_t)d * 4, (size_t)d * 4, n_slots, cudaMemcpyDeviceToDevice, st));
+  if (ev.ldw > d) {
+    // pad columns are never read by the FFMA path; the TMA path reads them (zero them)
+    CU(cudaMemset2DAsync(ev.Wt + d, (size_t)ev.ldw * 4, 0, (size_t)(ev.ldw - d) * 4, n_slots, st));
+  }
+  CU(cudaMemcpyAsync(ev.bt, b, sizeof(float) * n_slots, cudaMemcpyDeviceToDevice, st));
+  CU(cudaMemcpyAsync(ev.sel, mask_sel, sizeof(int32_t) * n_slots, cudaMemcpyDeviceToDevice, st));
+  CU(cudaMemcpyAsync(ev.val, mask_val, sizeof(int32_t) * n_slots, cudaMemcpyDeviceToDevice, st));
+  int rc = ev.evaluate(ctx, n_slots);
+  if (rc) return rc;
+  if (ctx->comm) { rc = allreduce(ctx, ev.Gred, (size_t)n_slots * ev.ldgr, kNcclFloat64); if (rc) return rc; }
+  CU(cudaMemcpyAsync(out, ev.Gred, sizeof(double) * (size_t)n_slots * ev.ldgr, cudaMemcpyDeviceToDevice, st));
+  timing_end(ctx);
+  CU(cudaStreamSynchronize(st));
   return DML_OK;
 }
 

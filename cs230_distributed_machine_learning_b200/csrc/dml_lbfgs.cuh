@@ -320,13 +320,13 @@ __global__ void write_trial_kernel(const TrialParams p) {
 // partial sums -> fp64 per-slot record [G(0..d-1), gb, loss]; fixed summation order.
 // `accumulate` adds to the record (row chunks after the first).
 struct ReduceParams {
-  const float* Gpart; int ldg; int splits; int n_slots; int d; int T;
+  const float* Gpart; int ldg; int splits; int n_slots; int d; int T; int jcount;  // jcount = d+1 (FFMA path: column d = sum r) or d
   const double* lossPart; int64_t tile0, n_tiles;
   double* Gred; int ldgr; int accumulate;
 };
 __global__ void reduce_grad_kernel(const ReduceParams p) {
   const int slot = blockIdx.x;
-  for (int j = threadIdx.x; j <= p.d; j += blockDim.x) {
+  for (int j = threadIdx.x; j < p.jcount; j += blockDim.x) {
     double acc = 0.0;
     for (int s = 0; s < p.splits; ++s) acc += (double)p.Gpart[((int64_t)s * p.n_slots + slot) * p.ldg + j];
     double* q = p.Gred + (int64_t)slot * p.ldgr + j;

@@ -1,0 +1,533 @@
+// tcgen05 (5th-gen tensor core) path of the sweep: 3xTF32 split-precision contractions
+// with TMA-staged operands and TMEM accumulators, sm_100a only.
+//
+//   tc_fwd_kernel : Z = X W^T for a 128-row tile x NC columns, epilogue in registers:
+//                   loss / residual (written pre-split as R_hi, R_lo) or counts
+//   tc_grad_kernel: G = X^T R for a 128-feature block x NC columns over a row split
+//
+// Split precision: a = a_hi + a_lo with a_hi = a & 0xffffe000 (exactly a TF32 number);
+// a.b ~= a_hi.b_hi + a_hi.b_lo + a_lo.b_hi, three kind::tf32 MMAs into one fp32
+// TMEM accumulator.  The operand derived from X is split inside the kernel (the
+// split is elementwise, so it works on the swizzled stage buffer as it lies); the
+// other operand (W or R) arrives pre-split from the kernel that produced it.
+//
+// Reference call sites these stand in for: the X @ w and X.T @ g products inside
+// every L-BFGS function evaluation of every fit (sklearn/linear_model/_linear_loss.py:216-222,
+// 355-368, reached from aws-prod/worker/worker.py:315,326).
+#pragma once
+#include <cuda.h>
+#include "dml_common.cuh"
+#include "dml_gemm.cuh"
+
+namespace dml {
+namespace tc {
+
+// ---------------------------------------------------------------- PTX wrappers
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+
+__device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count));
+}
+__device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, uint32_t bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive(uint64_t* bar) {
+  asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
+  const uint32_t addr = smem_u32(bar);
+  uint32_t done;
+  do {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+        "selp.u32 %0, 1, 0, p;\n\t}"
+        : "=r"(done) : "r"(addr), "r"(parity) : "memory");
+  } while (!done);
+}
+__device__ __forceinline__ void fence_barrier_init() { asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory"); }
+__device__ __forceinline__ void fence_proxy_async() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
+__device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
+
+__device__ __forceinline__ void tma_load_2d(const CUtensorMap* map, uint64_t* bar, void* dst, int c0, int c1) {
+  asm volatile(
+      "cp.async.bulk.tensor.2d.shared::cluster.global.tile.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];"
+      ::"r"(smem_u32(dst)), "l"(map), "r"(smem_u32(bar)), "r"(c0), "r"(c1) : "memory");
+}
+__device__ __forceinline__ void tmem_alloc(uint32_t* slot, uint32_t cols) {
+  asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(slot)), "r"(cols) : "memory");
+  asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+}
+__device__ __forceinline__ void tmem_dealloc(uint32_t addr, uint32_t cols) {
+  asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(addr), "r"(cols) : "memory");
+}
+__device__ __forceinline__ void umma_tf32(uint32_t tmem_c, uint64_t da, uint64_t db, uint32_t idesc, uint32_t accumulate) {
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "setp.ne.b32 p, %4, 0;\n\t"
+      "tcgen05.mma.cta_group::1.kind::tf32 [%0], %1, %2, %3, p;\n\t}"
+      ::"r"(tmem_c), "l"(da), "l"(db), "r"(idesc), "r"(accumulate) : "memory");
+}
+__device__ __forceinline__ void umma_commit(uint64_t* bar) {
+  asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(bar)) : "memory");
+}
+__device__ __forceinline__ void tmem_ld16(uint32_t taddr, uint32_t (&v)[16]) {
+  asm volatile(
+      "tcgen05.ld.sync.aligned.32x32b.x16.b32 {%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15}, [%16];"
+      : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]),
+        "=r"(v[8]), "=r"(v[9]), "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15])
+      : "r"(taddr));
+}
+__device__ __forceinline__ void tmem_ld_wait() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
+__device__ __forceinline__ bool elect_one() {
+  uint32_t pred;
+  asm volatile("{\n\t.reg .pred p;\n\telect.sync _|p, 0xffffffff;\n\tselp.u32 %0, 1, 0, p;\n\t}" : "=r"(pred));
+  return pred != 0;
+}
+
+// ---------------------------------------------------------------- descriptors
+// Shared-memory matrix descriptor (sm_100 "version 1").
+//   K-major  (layout 2 = SWIZZLE_128B): rows of 128 B (32 tf32 along K), 8-row groups SBO = 1024 B
+//             apart; the K offset inside the swizzle atom is added to the start address.
+//   MN-major (layout 1 = SWIZZLE_128B_BASE32B, the only layout tf32 accepts when transposed): rows
+//             of 128 B (32 tf32 along M/N) stacked along K, 32-byte chunks XOR-ed with (row & 3);
+//             4-row atoms SBO = 512 B apart, the next 32 elements along M/N LBO bytes away.
+//             TMA writes this pattern with CU_TENSOR_MAP_SWIZZLE_128B_ATOM_32B.
+constexpr uint32_t kLayoutSw128 = 2, kLayoutSw128Base32 = 1;
+__device__ __forceinline__ uint64_t smem_desc(uint32_t saddr, uint32_t lbo_bytes, uint32_t sbo_bytes,
+                                              uint32_t layout = kLayoutSw128) {
+  uint64_t d = 0;
+  d |= (uint64_t)((saddr >> 4) & 0x3fff);
+  d |= (uint64_t)((lbo_bytes >> 4) & 0x3fff) << 16;
+  d |= (uint64_t)((sbo_bytes >> 4) & 0x3fff) << 32;
+  d |= (uint64_t)1 << 46;   // descriptor version (Blackwell)
+  d |= (uint64_t)layout << 61;
+  return d;
+}
+// Instruction descriptor: D fp32, A/B tf32, M x N, transposes (MN-major) as flags.
+__host__ __device__ constexpr uint32_t instr_desc_tf32(int M, int N, int a_mn_major, int b_mn_major) {
+  return (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)a_mn_major << 15) | ((uint32_t)b_mn_major << 16) |
+         ((uint32_t)(N >> 3) << 17) | ((uint32_t)(M >> 4) << 24);
+}
+
+constexpr uint32_t kHiMask = 0xffffe000u;
+__device__ __forceinline__ float tf32_hi(float x) { return __uint_as_float(__float_as_uint(x) & kHiMask); }
+
+// split a stage buffer in place: hi <- hi & mask (optional), lo <- x - hi.  `bytes` multiple of 2048.
+__device__ __forceinline__ void split_stage(float* hi, float* lo, int bytes, int tid, int nthreads, bool mask_hi) {
+  float4* h4 = reinterpret_cast<float4*>(hi);
+  float4* l4 = reinterpret_cast<float4*>(lo);
+  const int n4 = bytes >> 4;
+  for (int i = tid; i < n4; i += nthreads) {
+    const float4 x = h4[i];
+    float4 h = make_float4(tf32_hi(x.x), tf32_hi(x.y), tf32_hi(x.z), tf32_hi(x.w));
+    l4[i] = make_float4(x.x - h.x, x.y - h.y, x.z - h.z, x.w - h.w);
+    if (mask_hi) h4[i] = h;
+  }
+}
+
+// ---------------------------------------------------------------- forward kernel
+constexpr int kFwdStages = 3;
+constexpr int kFwdThreads = 320;   // warp 0 TMA, warp 1 MMA, warps 2-5 operand split, warps 6-9 epilogue
+
+struct TcFwdParams {
+  int64_t n_rows_total;      // rows of X visible through the tensor map (for masking the last tile)
+  int64_t row0, rows;        // chunk
+  int d_chunks;              // ceil(d / 32)
+  int n_slots, n_col_blocks;
+  const float* bt;           // [n_slots]
+  const int32_t* ycls; const float* yreg;
+  const int8_t* fold_id; const int8_t* hold_id;
+  const int32_t* slot_sel; const int32_t* slot_val;
+  float* Rhi; float* Rlo; int ldr;       // [chunk rows][ldr]
+  double* lossPart; double* gbPart;      // [row tiles][n_slots]
+  int32_t* cntPart; float* ssePart;      // score modes
+  int mask_hi;
+};
+
+template <int NC>
+struct FwdSmem {
+  static constexpr int kA = 128 * 128;          // 128 rows x 32 tf32
+  static constexpr int kB = NC * 128;
+  static constexpr int kStage = 2 * kA + 2 * kB;
+  static constexpr int kBytes = kFwdStages * kStage + 1024 /*align*/ + 256 /*barriers*/;
+};
+
+template <int NC, int MODE>
+__global__ void __launch_bounds__(kFwdThreads, 1)
+tc_fwd_kernel(const __grid_constant__ CUtensorMap mapX, const __grid_constant__ CUtensorMap mapWhi,
+              const __grid_constant__ CUtensorMap mapWlo, const TcFwdParams p) {
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
+  using L = FwdSmem<NC>;
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + kFwdStages * L::kStage);
+  uint64_t* full = bars;                    // [S] TMA landed
+  uint64_t* split = bars + kFwdStages;      // [S] lo operand written
+  uint64_t* empty = bars + 2 * kFwdStages;  // [S] MMAs that read the stage retired
+  uint64_t* tfull = bars + 3 * kFwdStages;  // [2] accumulator ready
+  uint64_t* tempty = tfull + 2;             // [2] accumulator drained
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tempty + 2);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  constexpr uint32_t kTmemCols = (2 * NC <= 64) ? 64 : (2 * NC <= 128) ? 128 : (2 * NC <= 256) ? 256 : 512;
+  static_assert(2 * NC <= 512 && NC % 16 == 0, "NC");
+
+  if (warp == 0 && lane == 0) {
+    for (int s = 0; s < kFwdStages; ++s) { mbar_init(full + s, 1); mbar_init(split + s, 4); mbar_init(empty + s, 1); }
+    for (int a = 0; a < 2; ++a) { mbar_init(tfull + a, 1); mbar_init(tempty + a, 4); }
+    fence_barrier_init();
+  }
+  if (warp == 1) tmem_alloc(tmem_slot, kTmemCols);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  const int64_t n_row_tiles = (p.rows + 127) / 128;
+  const int64_t n_jobs = n_row_tiles * p.n_col_blocks;
+
+  if (warp == 0) {
+    // ===== TMA producer =====
+    if (lane == 0) {
+      uint32_t it = 0;
+      for (int64_t job = blockIdx.x; job < n_jobs; job += gridDim.x) {
+        const int64_t rt = job / p.n_col_blocks; const int cb = (int)(job % p.n_col_blocks);
+        const int row = (int)(p.row0 + rt * 128), slot = cb * NC;
+        for (int c = 0; c < p.d_chunks; ++c, ++it) {
+          const int s = it % kFwdStages; const uint32_t ph = (it / kFwdStages) & 1;
+          mbar_wait(empty + s, ph ^ 1);
+          uint8_t* st = smem + s * L::kStage;
+          mbar_expect_tx(full + s, L::kA + 2 * L::kB);
+          tma_load_2d(&mapX, full + s, st, c * 32, row);
+          tma_load_2d(&mapWhi, full + s, st + 2 * L::kA, c * 32, slot);
+          tma_load_2d(&mapWlo, full + s, st + 2 * L::kA + L::kB, c * 32, slot);
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ===== MMA issuer =====
+    constexpr uint32_t idesc = instr_desc_tf32(128, NC, 0, 0);
+    uint32_t it = 0, tile = 0;
+    for (int64_t job = blockIdx.x; job < n_jobs; job += gridDim.x, ++tile) {
+      const int acc = tile & 1; const uint32_t aph = (tile >> 1) & 1;
+      mbar_wait(tempty + acc, aph ^ 1);
+      tc_fence_after();
+      const uint32_t tacc = tmem_base + acc * NC;
+      for (int c = 0; c < p.d_chunks; ++c, ++it) {
+        const int s = it % kFwdStages; const uint32_t ph = (it / kFwdStages) & 1;
+        mbar_wait(full + s, ph);
+        mbar_wait(split + s, ph);
+        tc_fence_after();
+        if (elect_one()) {
+          const uint32_t a_hi = smem_u32(smem + s * L::kStage), a_lo = a_hi + L::kA;
+          const uint32_t b_hi = a_hi + 2 * L::kA, b_lo = b_hi + L::kB;
+#pragma unroll
+          for (int k = 0; k < 4; ++k) {
+            const uint64_t dah = smem_desc(a_hi + k * 32, 16, 1024), dal = smem_desc(a_lo + k * 32, 16, 1024);
+            const uint64_t dbh = smem_desc(b_hi + k * 32, 16, 1024), dbl = smem_desc(b_lo + k * 32, 16, 1024);
+            umma_tf32(tacc, dal, dbh, idesc, (c | k) != 0);   // small terms first
+            umma_tf32(tacc, dah, dbl, idesc, 1);
+            umma_tf32(tacc, dah, dbh, idesc, 1);
+          }
+          umma_commit(empty + s);
+          if (c == p.d_chunks - 1) umma_commit(tfull + acc);
+        }
+        __syncwarp();
+      }
+    }
+  } else if (warp < 6) {
+    // ===== operand split: X_lo = X - tf32(X) on the stage buffer as it lies =====
+    const int tid = threadIdx.x - 64;
+    uint32_t it = 0;
+    for (int64_t job = blockIdx.x; job < n_jobs; job += gridDim.x) {
+      for (int c = 0; c < p.d_chunks; ++c, ++it) {
+        const int s = it % kFwdStages; const uint32_t ph = (it / kFwdStages) & 1;
+        mbar_wait(full + s, ph);
+        float* hi = reinterpret_cast<float*>(smem + s * L::kStage);
+        split_stage(hi, hi + L::kA / 4, L::kA, tid, 128, p.mask_hi != 0);
+        fence_proxy_async();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(split + s);
+      }
+    }
+  } else {
+    // ===== epilogue: thread = row of the tile (TMEM lane) =====
+    const int q = warp & 3;                 // TMEM lane quadrant this warp may read
+    const int r = q * 32 + lane;            // row within the tile
+    uint32_t tile = 0;
+    for (int64_t job = blockIdx.x; job < n_jobs; job += gridDim.x, ++tile) {
+      const int64_t rt = job / p.n_col_blocks; const int cb = (int)(job % p.n_col_blocks);
+      const int64_t grow = p.row0 + rt * 128 + r;          // global row
+      const int64_t lrow = rt * 128 + r;                   // row inside the chunk
+      const int64_t tile_id = (p.row0 >> 7) + rt;
+      const int slot0 = cb * NC;
+      const bool valid = grow < p.row0 + p.rows && grow < p.n_rows_total;
+      int yv = 0, lab = 0; float yf = 0.f;
+      if (valid) {
+        if (p.ycls) yv = p.ycls[grow];
+        if (p.yreg) yf = p.yreg[grow];
+        lab = (int)(uint8_t)p.fold_id[grow] | ((p.hold_id ? (int)(uint8_t)p.hold_id[grow] : 0) << 8);
+      }
+      const int acc = tile & 1; const uint32_t aph = (tile >> 1) & 1;
+      mbar_wait(tfull + acc, aph);
+      tc_fence_after();
+      const uint32_t tacc = tmem_base + acc * NC + ((uint32_t)(q * 32) << 16);
+#pragma unroll 1
+      for (int c0 = 0; c0 < NC; c0 += 16) {
+        uint32_t v[16];
+        tmem_ld16(tacc + c0, v);
+        tmem_ld_wait();
+        if (c0 + 16 >= NC) {               // accumulator fully read: hand it back to the MMA warp
+          tc_fence_before();
+          __syncwarp();
+          if (lane == 0) mbar_arrive(tempty + acc);
+        }
+        float rh[16], rl[16];
+#pragma unroll
+        for (int j = 0; j < 16; ++j) {
+          const int slot = slot0 + c0 + j;
+          double ls = 0.0, rs = 0.0; int ok = 0; float res = 0.f;
+          if (slot < p.n_slots && valid) {
+            const int sel = __ldg(p.slot_sel + slot), val = __ldg(p.slot_val + slot);
+            const bool held = ((lab >> (8 * sel)) & 0xff) == val;
+            const float z = __uint_as_float(v[j]) + __ldg(p.bt + slot);
+            if (MODE == FWD_LOGREG) {
+              if (!held) { const float yy = (float)yv; ls = (double)(softplus_f(z) - yy * z); res = sigmoid_f(z) - yy; rs = (double)res; }
+            } else if (MODE == FWD_SCORE_CLS) {
+              if (held) ok = ((z > 0.f) ? 1 : 0) == yv;
+            } else {
+              if (held) { const float e = yf - z; ls = (double)(e * e); }
+            }
+          }
+          if (MODE == FWD_LOGREG) { rh[j] = tf32_hi(res); rl[j] = res - rh[j]; }
+          // column sums over the 32 rows of this warp (fp64), one partial per (tile, quadrant)
+          if (MODE == FWD_SCORE_CLS) {
+            const unsigned bal = __ballot_sync(0xffffffffu, ok);
+            if (lane == 0 && slot < p.n_slots) p.cntPart[(tile_id * 4 + q) * p.n_slots + slot] = __popc(bal);
+          } else {
+            ls = warp_sum(ls);
+            if (MODE == FWD_LOGREG) rs = warp_sum(rs);
+            if (lane == 0 && slot < p.n_slots) {
+              if (MODE == FWD_LOGREG) {
+                p.lossPart[(tile_id * 4 + q) * p.n_slots + slot] = ls;
+                p.gbPart[(tile_id * 4 + q) * p.n_slots + slot] = rs;
+              } else {
+                p.ssePart[(tile_id * 4 + q) * p.n_slots + slot] = (float)ls;
+              }
+            }
+          }
+        }
+        if (MODE == FWD_LOGREG && lrow < ((p.rows + 127) / 128) * 128 && slot0 + c0 < p.ldr) {
+          float4* dh = reinterpret_cast<float4*>(p.Rhi + lrow * p.ldr + slot0 + c0);
+          float4* dl = reinterpret_cast<float4*>(p.Rlo + lrow * p.ldr + slot0 + c0);
+#pragma unroll
+          for (int j = 0; j < 4; ++j) {
+            if (slot0 + c0 + 4 * j < p.ldr) {
+              dh[j] = make_float4(rh[4 * j], rh[4 * j + 1], rh[4 * j + 2], rh[4 * j + 3]);
+              dl[j] = make_float4(rl[4 * j], rl[4 * j + 1], rl[4 * j + 2], rl[4 * j + 3]);
+            }
+          }
+        }
+      }
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) tmem_dealloc(tmem_base, kTmemCols);
+}
+
+// ---------------------------------------------------------------- gradient kernel
+// G[j][slot] = sum over the split's rows of X[row][j] * R[row][slot]
+//   A = X^T : MN-major, per stage 4 TMA boxes [32 rows x 32 features]  (split in kernel)
+//   B = R   : MN-major, per stage NC/32 boxes [32 rows x 32 columns], hi and lo from global
+// Two-level accumulation: the tensor core adds into a TMEM accumulator for at most kChain
+// stages (128 rows, 48 MMAs) -- its fp32 adder truncates, and the bias grows linearly with the
+// chain (measured 1.3e-5 relative after 2048 rows) -- then the drain warps add the TMEM tile
+// into fp32 registers with round-to-nearest while the MMAs fill the other TMEM accumulator.
+constexpr int kGradStages = 3;
+constexpr int kChain = 4;           // stages per TMEM accumulation chain
+constexpr int kGradThreads = 320;   // warp 0 TMA, warp 1 MMA, warps 2-5 operand split, warps 6-9 drain
+
+struct TcGradParams {
+  int64_t row0_x;            // first row of the chunk inside X
+  int64_t rows;              // rows in the chunk (R is chunk-local)
+  int64_t rows_per_split;    // multiple of 32
+  int d, n_slots;
+  float* Gpart; int ldg;     // [splits][n_slots][ldg]
+  int mask_hi;
+};
+
+template <int NC>
+struct GradSmem {
+  static constexpr int kA = 4 * 32 * 128;       // 4 boxes of 32 rows x 128 B
+  static constexpr int kB = (NC / 32) * 32 * 128;
+  static constexpr int kStage = 2 * kA + 2 * kB;
+  static constexpr int kBytes = kGradStages * kStage + 1024 + 256;
+};
+
+template <int NC>
+__global__ void __launch_bounds__(kGradThreads, 1)
+tc_grad_kernel(const __grid_constant__ CUtensorMap mapX, const __grid_constant__ CUtensorMap mapRhi,
+               const __grid_constant__ CUtensorMap mapRlo, const TcGradParams p) {
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
+  using L = GradSmem<NC>;
+  static_assert(NC % 32 == 0 && NC <= 256, "NC");
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + kGradStages * L::kStage);
+  uint64_t* full = bars; uint64_t* split = bars + kGradStages; uint64_t* empty = bars + 2 * kGradStages;
+  uint64_t* tfull = bars + 3 * kGradStages;   // [2]
+  uint64_t* tempty = tfull + 2;               // [2]
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tempty + 2);
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  constexpr uint32_t kTmemCols = 2 * NC <= 64 ? 64 : 2 * NC <= 128 ? 128 : 2 * NC <= 256 ? 256 : 512;
+
+  if (warp == 0 && lane == 0) {
+    for (int s = 0; s < kGradStages; ++s) { mbar_init(full + s, 1); mbar_init(split + s, 4); mbar_init(empty + s, 1); }
+    for (int a = 0; a < 2; ++a) { mbar_init(tfull + a, 1); mbar_init(tempty + a, 4); }
+    fence_barrier_init();
+  }
+  if (warp == 1) tmem_alloc(tmem_slot, kTmemCols);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  const int jb = blockIdx.x, cb = blockIdx.y, sp = blockIdx.z;
+  const int64_t kb = (int64_t)sp * p.rows_per_split;
+  const int64_t ke = min(p.rows, kb + p.rows_per_split);
+  const int n_stages = (int)((ke - kb + 31) / 32);
+  const int n_groups = (n_stages + kChain - 1) / kChain;
+
+  if (warp == 0) {
+    if (lane == 0) {
+      for (int it = 0; it < n_stages; ++it) {
+        const int s = it % kGradStages; const uint32_t ph = (it / kGradStages) & 1;
+        mbar_wait(empty + s, ph ^ 1);
+        uint8_t* st = smem + s * L::kStage;
+        mbar_expect_tx(full + s, L::kA + 2 * L::kB);
+        const int lr = (int)(kb + (int64_t)it * 32);          // row inside the chunk (R)
+        const int xr = (int)(p.row0_x + lr);                   // row inside X
+#pragma unroll
+        for (int b = 0; b < 4; ++b) tma_load_2d(&mapX, full + s, st + b * 4096, jb * 128 + b * 32, xr);
+#pragma unroll
+        for (int b = 0; b < NC / 32; ++b) {
+          tma_load_2d(&mapRhi, full + s, st + 2 * L::kA + b * 4096, cb * NC + b * 32, lr);
+          tma_load_2d(&mapRlo, full + s, st + 2 * L::kA + L::kB + b * 4096, cb * NC + b * 32, lr);
+        }
+      }
+    }
+  } else if (warp == 1) {
+    constexpr uint32_t idesc = instr_desc_tf32(128, NC, 1, 1);
+    for (int g = 0, it = 0; g < n_groups; ++g) {
+      const int acc = g & 1; const uint32_t aph = (g >> 1) & 1;
+      mbar_wait(tempty + acc, aph ^ 1);
+      tc_fence_after();
+      const uint32_t tacc = tmem_base + acc * NC;
+      const int g_end = min(n_stages, (g + 1) * kChain);
+      for (int first = 1; it < g_end; ++it) {
+        const int s = it % kGradStages; const uint32_t ph = (it / kGradStages) & 1;
+        mbar_wait(full + s, ph);
+        mbar_wait(split + s, ph);
+        tc_fence_after();
+        if (elect_one()) {
+          const uint32_t a_hi = smem_u32(smem + s * L::kStage), a_lo = a_hi + L::kA;
+          const uint32_t b_hi = a_hi + 2 * L::kA, b_lo = b_hi + L::kB;
+#pragma unroll
+          for (int k = 0; k < 4; ++k) {   // 8 rows (two 4-row swizzle atoms along K) per MMA
+            const uint64_t dah = smem_desc(a_hi + k * 1024, 4096, 512, kLayoutSw128Base32);
+            const uint64_t dal = smem_desc(a_lo + k * 1024, 4096, 512, kLayoutSw128Base32);
+            const uint64_t dbh = smem_desc(b_hi + k * 1024, 4096, 512, kLayoutSw128Base32);
+            const uint64_t dbl = smem_desc(b_lo + k * 1024, 4096, 512, kLayoutSw128Base32);
+            umma_tf32(tacc, dal, dbh, idesc, (first && k == 0) ? 0u : 1u);
+            umma_tf32(tacc, dah, dbl, idesc, 1);
+            umma_tf32(tacc, dah, dbh, idesc, 1);
+          }
+          umma_commit(empty + s);
+          if (it == g_end - 1) umma_commit(tfull + acc);
+        }
+        __syncwarp();
+        first = 0;
+      }
+    }
+  } else if (warp < 6) {
+    const int tid = threadIdx.x - 64;
+    for (int it = 0; it < n_stages; ++it) {
+      const int s = it % kGradStages; const uint32_t ph = (it / kGradStages) & 1;
+      mbar_wait(full + s, ph);
+      float* hi = reinterpret_cast<float*>(smem + s * L::kStage);
+      split_stage(hi, hi + L::kA / 4, L::kA, tid, 128, p.mask_hi != 0);
+      fence_proxy_async();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(split + s);
+    }
+  } else {
+    // drain: lane = feature index inside the 128-block; fp32 round-to-nearest running sums
+    const int q = warp & 3;
+    const int j = jb * 128 + q * 32 + lane;
+    float sum[NC];
+#pragma unroll
+    for (int c = 0; c < NC; ++c) sum[c] = 0.f;
+    for (int g = 0; g < n_groups; ++g) {
+      const int acc = g & 1; const uint32_t aph = (g >> 1) & 1;
+      mbar_wait(tfull + acc, aph);
+      tc_fence_after();
+      const uint32_t tacc = tmem_base + acc * NC + ((uint32_t)(q * 32) << 16);
+#pragma unroll
+      for (int c0 = 0; c0 < NC; c0 += 16) {
+        uint32_t v[16];
+        tmem_ld16(tacc + c0, v);
+        tmem_ld_wait();
+#pragma unroll
+        for (int c = 0; c < 16; ++c) sum[c0 + c] += __uint_as_float(v[c]);
+      }
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(tempty + acc);
+    }
+    float* out = p.Gpart + (int64_t)sp * p.n_slots * p.ldg;
+#pragma unroll
+    for (int c = 0; c < NC; ++c) {
+      const int slot = cb * NC + c;
+      if (slot < p.n_slots && j < p.d) out[(int64_t)slot * p.ldg + j] = sum[c];
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) tmem_dealloc(tmem_base, kTmemCols);
+}
+
+// ---------------------------------------------------------------- small helpers
+// trial weights -> hi / lo copies for the forward B operand
+__global__ void split_weights_kernel(const float* W, float* Whi, float* Wlo, int64_t n) {
+  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) { const float x = W[i], h = tf32_hi(x); Whi[i] = h; Wlo[i] = x - h; }
+}
+
+// per-(tile, quadrant) fp64 partials -> Gred columns d (sum of residuals) and d+1 (loss)
+struct TcReduceParams {
+  const double* lossPart; const double* gbPart; int64_t part0, n_parts; int n_slots, T, d;
+  double* Gred; int ldgr; int accumulate;
+};
+__global__ void tc_reduce_tiles_kernel(const TcReduceParams p) {
+  __shared__ double sh[2][8][33];
+  const int slot = blockIdx.x * 32 + threadIdx.x;
+  double a = 0.0, b = 0.0;
+  if (slot < p.n_slots)
+    for (int64_t t = p.part0 + threadIdx.y; t < p.part0 + p.n_parts; t += 8) {
+      a += p.lossPart[t * p.n_slots + slot];
+      b += p.gbPart[t * p.n_slots + slot];
+    }
+  sh[0][threadIdx.y][threadIdx.x] = a; sh[1][threadIdx.y][threadIdx.x] = b;
+  __syncthreads();
+  if (threadIdx.y == 0 && slot < p.n_slots) {
+    double l = 0.0, g = 0.0;
+    for (int i = 0; i < 8; ++i) { l += sh[0][i][threadIdx.x]; g += sh[1][i][threadIdx.x]; }
+    double* q = p.Gred + (int64_t)slot * p.ldgr;
+    q[p.d] = p.accumulate ? q[p.d] + g : g;
+    if (slot % p.T == 0) q[p.d + 1] = p.accumulate ? q[p.d + 1] + l : l;
+  }
+}
+
+}  // namespace tc
+}  // namespace dml

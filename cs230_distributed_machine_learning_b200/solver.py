@@ -163,6 +163,23 @@ class SweepSolver:
             out["syy"] = self.to_host(syy).reshape(n_cand, fpc)
         return out
 
+    def logreg_eval(self, ds: DeviceDataset, fold_id, W, b, mask_sel, mask_val, hold_id=None,
+                    use_tensor_cores: int = -1) -> np.ndarray:
+        """Loss / gradient sums of given columns (dml_logreg_eval): (n_slots, d + 2) float64."""
+        W_d = self.to_device(np.ascontiguousarray(W, dtype=np.float32))
+        b_d = self.to_device(np.ascontiguousarray(b, dtype=np.float32))
+        n_slots = W_d.shape[0]
+        sel_d = self.to_device(np.asarray(mask_sel, dtype=np.int32))
+        val_d = self.to_device(np.asarray(mask_val, dtype=np.int32))
+        fold_d = self.to_device(fold_id, torch.int8)
+        hold_d = self.to_device(hold_id, torch.int8) if hold_id is not None else None
+        out = torch.empty((n_slots, ds.d + 2), dtype=torch.float64, device=self.device)
+        rc = self.lib.dml_logreg_eval(self.ctx.handle, _ptr(ds.X), ds.n, ds.d, ds.X.stride(0), _ptr(ds.y_cls),
+                                      _ptr(fold_d), _ptr(hold_d), _ptr(W_d), _ptr(b_d), _ptr(sel_d), _ptr(val_d),
+                                      n_slots, _ptr(out), int(use_tensor_cores))
+        self.ctx.check(rc, "dml_logreg_eval")
+        return self.to_host(out)
+
     def score(self, ds: DeviceDataset, fold_id, W, b, mask_sel, mask_val, T: int, hold_id=None):
         """Counts / squared errors of given coefficients (dml_score)."""
         W_d = self.to_device(np.ascontiguousarray(W, dtype=np.float32))

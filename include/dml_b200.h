@@ -97,6 +97,19 @@ int dml_ridge_sweep(dml_ctx* ctx, const float* X, int64_t n, int d, int64_t ldx,
                     double* sse_out, double* sy_out, double* syy_out,
                     int32_t* info_out, int use_tensor_cores);
 
+/* One batched evaluation of the binary-logistic objective for given coefficient
+ * columns: for column s, over rows i with label[mask_sel[s]][i] != mask_val[s]
+ * (its training rows), out[s] = [ sum_i r_i x_i (d values), sum_i r_i, sum_i loss_i ]
+ * with z = x.w_s + b_s, loss = log(1+e^z) - y z, r = sigmoid(z) - y; fp64, length
+ * d + 2 per column.  This is sklearn's LinearModelLoss.loss_gradient before the
+ * 1/n scaling and the penalty (_linear_loss.py:291-379), i.e. what every L-BFGS
+ * function evaluation inside model.fit (worker.py:315,326) computes, for all
+ * columns at once.  W [n_slots][d], b [n_slots] fp32. */
+int dml_logreg_eval(dml_ctx* ctx, const float* X, int64_t n, int d, int64_t ldx, const int32_t* y,
+                    const int8_t* fold_id, const int8_t* hold_id,
+                    const float* W, const float* b, const int32_t* mask_sel, const int32_t* mask_val,
+                    int n_slots, double* out, int use_tensor_cores);
+
 /* Score given coefficients: per slot (column) s, over rows with
  * label[mask_sel[s]][i] == mask_val[s]: classifier -> correct count of groups of
  * T columns (binary: decision > 0, else first arg-max), regressor -> squared

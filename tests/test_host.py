@@ -198,7 +198,7 @@ def test_cabi_library_exports_every_declared_symbol():
     declared = set(re.findall(r"\b(dml_[a-z0-9_]+)\s*\(", header))
     assert declared >= {"dml_version", "dml_ctx_create", "dml_ctx_destroy", "dml_last_error", "dml_logreg_sweep",
                         "dml_ridge_sweep", "dml_score", "dml_ctx_init_comm", "dml_nccl_unique_id", "dml_last_timing",
-                        "dml_last_counters"}
+                        "dml_last_counters", "dml_logreg_eval"}
     for name in declared:
         assert hasattr(lib, name), name
     assert set(_cabi.SYMBOLS) == declared
