@@ -339,13 +339,14 @@ struct EvalCtx {
   const int32_t* y = nullptr; const int8_t* fold_id = nullptr; const int8_t* hold_id = nullptr;
   // plan
   bool use_tc = false, xvec = false; int NC = 160, nt = 1, tile_n = BN, ldw = 0, ldg = 0, ldgr = 0, splits = 1;
-  int64_t S_max = 0, ldr_max = 0, chunk_rows = 0, rps = 0, tc_rps = 2048, tiles_total = 0;
+  int64_t S_max = 0, ldr_max = 0, chunk_rows = 0, rps = 0, tc_rps = 2048, tiles_total = 0; int ctx_sms = 148;
   // buffers
   float *Wt = nullptr, *bt = nullptr, *R = nullptr, *Rlo = nullptr, *Whi = nullptr, *Wlo = nullptr, *Gpart = nullptr;
   double *lossPart = nullptr, *gbPart = nullptr, *Gred = nullptr; int32_t *sel = nullptr, *val = nullptr, *cntPart = nullptr;
   CUtensorMap mXf, mXg, mWh, mWl, mRh, mRl;
 
   void plan(dml_ctx* ctx, int64_t n_groups_max) {
+    ctx_sms = ctx->n_sms;
     ldw = (int)rup(d, 4); ldg = (int)rup(d + 1, 4); ldgr = d + 2;
     tiles_total = cdiv(n, BM); tile_n = (BN / T) * T;
     ldr_max = rup(S_max, 4); NC = pick_nc(S_max);
@@ -368,12 +369,14 @@ struct EvalCtx {
     Wt = a.take<float>((size_t)S_max * ldw); bt = a.take<float>(S_max);
     sel = a.take<int32_t>(S_max); val = a.take<int32_t>(S_max);
     R = a.take<float>((size_t)chunk_rows * ldr_max);
-    lossPart = a.take<double>((size_t)tiles_total * (use_tc ? 4 * S_max : n_groups_max));
-    cntPart = a.take<int32_t>((size_t)tiles_total * S_max * (use_tc ? 4 : 1));
+    // FFMA path: one partial per row tile; tcgen05 path: one per (CTA, epilogue warp)
+    const size_t tc_parts = (size_t)ctx_sms * 4;
+    lossPart = a.take<double>(use_tc ? tc_parts * S_max : (size_t)tiles_total * n_groups_max);
+    cntPart = a.take<int32_t>(use_tc ? tc_parts * S_max : (size_t)tiles_total * S_max);
     Gpart = a.take<float>((size_t)splits * S_max * ldg);
     if (use_tc) {
       Rlo = a.take<float>((size_t)chunk_rows * ldr_max);
-      gbPart = a.take<double>((size_t)tiles_total * S_max * 4);
+      gbPart = a.take<double>(tc_parts * S_max);
       Whi = a.take<float>((size_t)S_max * ldw); Wlo = a.take<float>((size_t)S_max * ldw);
     }
   }
@@ -408,15 +411,18 @@ struct EvalCtx {
         fp.Rhi = R; fp.Rlo = Rlo; fp.ldr = (int)ldr_max; fp.lossPart = lossPart; fp.gbPart = gbPart;
         fp.mask_hi = ctx->tc_mask_hi;
         const int64_t jobs = cdiv(rows, 128) * ncb;
-        int rc = launch_tc_fwd<FWD_LOGREG>(ctx, NC, (int)std::min<int64_t>(jobs, ctx->n_sms), mXf, mWh, mWl, fp);
+        const int grid = (int)std::min<int64_t>(jobs, ctx->n_sms);
+        CU(cudaMemsetAsync(lossPart, 0, sizeof(double) * (size_t)grid * 4 * n_slots, st));
+        CU(cudaMemsetAsync(gbPart, 0, sizeof(double) * (size_t)grid * 4 * n_slots, st));
+        int rc = launch_tc_fwd<FWD_LOGREG>(ctx, NC, grid, mXf, mWh, mWl, fp);
         if (rc) return rc;
         tc::TcGradParams gp{r0, rows, tc_rps, d, n_slots, Gpart, ldg, ctx->tc_mask_hi};
         const int splits_here = (int)cdiv(rows, tc_rps);
         rc = launch_tc_grad(ctx, NC, dim3((unsigned)cdiv(d, 128), (unsigned)ncb, (unsigned)splits_here), mXg, mRh, mRl, gp);
         if (rc) return rc;
         ReduceParams rp{Gpart, ldg, splits_here, n_slots, d, T, d, nullptr, 0, 0, Gred, ldgr, ci > 0 ? 1 : 0};
-        reduce_grad_kernel<<<n_slots, 128, 0, st>>>(rp);
-        tc::TcReduceParams tr{lossPart, gbPart, (r0 / BM) * 4, cdiv(rows, BM) * 4, n_slots, T, d, Gred, ldgr, ci > 0 ? 1 : 0};
+        reduce_grad_kernel<<<n_slots, 256, 0, st>>>(rp);
+        tc::TcReduceParams tr{lossPart, gbPart, (int64_t)grid * 4, n_slots, T, d, Gred, ldgr, ci > 0 ? 1 : 0};
         tc::tc_reduce_tiles_kernel<<<(unsigned)cdiv(n_slots, 32), dim3(32, 8), 0, st>>>(tr);
       } else {
         const int ldr = (int)rup(n_slots, 4);
@@ -434,7 +440,7 @@ struct EvalCtx {
         dim3 g2((unsigned)cdiv(n_slots, BM), (unsigned)nt, (unsigned)splits_here);
         grad_kernel<<<g2, NT, kGemmSmemBytes, st>>>(gp);
         ReduceParams rp{Gpart, ldg, splits_here, n_slots, d, T, d + 1, lossPart, r0 / BM, cdiv(rows, BM), Gred, ldgr, ci > 0 ? 1 : 0};
-        reduce_grad_kernel<<<n_slots, 128, 0, st>>>(rp);
+        reduce_grad_kernel<<<n_slots, 256, 0, st>>>(rp);
         reduce_tiles_kernel<<<(unsigned)cdiv(n_slots / T, 32), dim3(32, 8), 0, st>>>(rp);
       }
       launches += 2;
@@ -459,13 +465,15 @@ struct EvalCtx {
       fp.fold_id = fold_id; fp.hold_id = hold_id; fp.slot_sel = sel; fp.slot_val = val;
       fp.cntPart = cntPart; fp.mask_hi = ctx->tc_mask_hi;
       const int64_t jobs = tiles_total * fp.n_col_blocks;
+      const int grid = (int)std::min<int64_t>(jobs, ctx->n_sms);
+      CU(cudaMemsetAsync(cntPart, 0, sizeof(int32_t) * (size_t)grid * 4 * n_slots, st));
       tick(ctx);
-      int rc = launch_tc_fwd<FWD_SCORE_CLS>(ctx, NC, (int)std::min<int64_t>(jobs, ctx->n_sms), mXf, mWh, mWl, fp);
+      int rc = launch_tc_fwd<FWD_SCORE_CLS>(ctx, NC, grid, mXf, mWh, mWl, fp);
       tock(ctx, 1);
       ctx->total_launches += 2;
       if (rc) return rc;
       KCHECK();
-      *n_parts = tiles_total * 4;
+      *n_parts = (int64_t)grid * 4;
       return DML_OK;
     }
     *n_parts = tiles_total;

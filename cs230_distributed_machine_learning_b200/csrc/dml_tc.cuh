@@ -141,8 +141,8 @@ struct TcFwdParams {
   const int8_t* fold_id; const int8_t* hold_id;
   const int32_t* slot_sel; const int32_t* slot_val;
   float* Rhi; float* Rlo; int ldr;       // [chunk rows][ldr]
-  double* lossPart; double* gbPart;      // [row tiles][n_slots]
-  int32_t* cntPart; float* ssePart;      // score modes
+  double* lossPart; double* gbPart;      // [gridDim.x * 4][n_slots], zeroed by the caller
+  int32_t* cntPart; double* ssePart;     // score modes, same shape
   int mask_hi;
 };
 
@@ -151,9 +151,32 @@ struct FwdSmem {
   static constexpr int kA = 128 * 128;          // 128 rows x 32 tf32
   static constexpr int kB = NC * 128;
   static constexpr int kStage = 2 * kA + 2 * kB;
-  static constexpr int kBytes = kFwdStages * kStage + 1024 /*align*/ + 256 /*barriers*/;
+  static constexpr int kMeta = 2 * NC * 4;      // per column: bias, packed mask
+  static constexpr int kBytes = kFwdStages * kStage + 1024 /*align*/ + 256 /*barriers*/ + kMeta;
 };
 
+// Sum v[c] over the 32 lanes of the warp for 16 columns with 16 shuffles (recursive halving):
+// lane l ends up with the total of column bfly_col(l); lanes l and l^1 hold the same column.
+__device__ __forceinline__ int bfly_col(int lane) { return ((lane >> 4) & 1) * 8 + ((lane >> 3) & 1) * 4 + ((lane >> 2) & 1) * 2 + ((lane >> 1) & 1); }
+template <class T>
+__device__ __forceinline__ T bfly16(const T (&v)[16], int lane) {
+  T a[8], b[4], c[2], d;
+  bool up = lane & 16;
+#pragma unroll
+  for (int i = 0; i < 8; ++i) { const T keep = up ? v[8 + i] : v[i], send = up ? v[i] : v[8 + i]; a[i] = keep + __shfl_xor_sync(0xffffffffu, send, 16); }
+  up = lane & 8;
+#pragma unroll
+  for (int i = 0; i < 4; ++i) { const T keep = up ? a[4 + i] : a[i], send = up ? a[i] : a[4 + i]; b[i] = keep + __shfl_xor_sync(0xffffffffu, send, 8); }
+  up = lane & 4;
+#pragma unroll
+  for (int i = 0; i < 2; ++i) { const T keep = up ? b[2 + i] : b[i], send = up ? b[i] : b[2 + i]; c[i] = keep + __shfl_xor_sync(0xffffffffu, send, 4); }
+  up = lane & 2;
+  { const T keep = up ? c[1] : c[0], send = up ? c[0] : c[1]; d = keep + __shfl_xor_sync(0xffffffffu, send, 2); }
+  return d + __shfl_xor_sync(0xffffffffu, d, 1);
+}
+
+// Jobs are ordered column block first: every CTA walks the row tiles of one column block (W stays
+// hot in L2, per-column running sums stay in registers) and changes block at most a few times.
 template <int NC, int MODE>
 __global__ void __launch_bounds__(kFwdThreads, 1)
 tc_fwd_kernel(const __grid_constant__ CUtensorMap mapX, const __grid_constant__ CUtensorMap mapWhi,
@@ -168,6 +191,8 @@ tc_fwd_kernel(const __grid_constant__ CUtensorMap mapX, const __grid_constant__ 
   uint64_t* tfull = bars + 3 * kFwdStages;  // [2] accumulator ready
   uint64_t* tempty = tfull + 2;             // [2] accumulator drained
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tempty + 2);
+  float* colBias = reinterpret_cast<float*>(smem + kFwdStages * L::kStage + 256);   // [NC]
+  int* colMask = reinterpret_cast<int*>(colBias + NC);                               // [NC]: sel<<8 | val, -1 = no column
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   constexpr uint32_t kTmemCols = (2 * NC <= 64) ? 64 : (2 * NC <= 128) ? 128 : (2 * NC <= 256) ? 256 : 512;
@@ -192,7 +217,7 @@ tc_fwd_kernel(const __grid_constant__ CUtensorMap mapX, const __grid_constant__ 
     if (lane == 0) {
       uint32_t it = 0;
       for (int64_t job = blockIdx.x; job < n_jobs; job += gridDim.x) {
-        const int64_t rt = job / p.n_col_blocks; const int cb = (int)(job % p.n_col_blocks);
+        const int cb = (int)(job / n_row_tiles); const int64_t rt = job % n_row_tiles;
         const int row = (int)(p.row0 + rt * 128), slot = cb * NC;
         for (int c = 0; c < p.d_chunks; ++c, ++it) {
           const int s = it % kFwdStages; const uint32_t ph = (it / kFwdStages) & 1;
@@ -255,13 +280,43 @@ tc_fwd_kernel(const __grid_constant__ CUtensorMap mapX, const __grid_constant__ 
     // ===== epilogue: thread = row of the tile (TMEM lane) =====
     const int q = warp & 3;                 // TMEM lane quadrant this warp may read
     const int r = q * 32 + lane;            // row within the tile
+    const int et = threadIdx.x - 192;       // 0..127 among the epilogue threads
+    const int mycol = bfly_col(lane);
+    double accA[NC / 16], accB[NC / 16]; int accC[NC / 16];
+#pragma unroll
+    for (int i = 0; i < NC / 16; ++i) { accA[i] = 0.0; accB[i] = 0.0; accC[i] = 0; }
+    int cur_cb = -1;
+    const int64_t part_row = ((int64_t)blockIdx.x * 4 + q) * p.n_slots;
+    auto flush = [&](int cb) {
+      if (cb < 0 || (lane & 1)) return;
+#pragma unroll
+      for (int i = 0; i < NC / 16; ++i) {
+        const int slot = cb * NC + i * 16 + mycol;
+        if (slot < p.n_slots) {
+          if (MODE == FWD_LOGREG) { p.lossPart[part_row + slot] = accA[i]; p.gbPart[part_row + slot] = accB[i]; }
+          else if (MODE == FWD_SCORE_CLS) p.cntPart[part_row + slot] = accC[i];
+          else p.ssePart[part_row + slot] = accA[i];
+        }
+        accA[i] = 0.0; accB[i] = 0.0; accC[i] = 0;
+      }
+    };
     uint32_t tile = 0;
     for (int64_t job = blockIdx.x; job < n_jobs; job += gridDim.x, ++tile) {
-      const int64_t rt = job / p.n_col_blocks; const int cb = (int)(job % p.n_col_blocks);
+      const int cb = (int)(job / n_row_tiles); const int64_t rt = job % n_row_tiles;
+      const int slot0 = cb * NC;
+      if (cb != cur_cb) {
+        flush(cur_cb);
+        cur_cb = cb;
+        asm volatile("bar.sync 1, 128;" ::: "memory");     // everyone is done with the old column metadata
+        for (int c = et; c < NC; c += 128) {
+          const int slot = slot0 + c;
+          colBias[c] = slot < p.n_slots ? __ldg(p.bt + slot) : 0.f;
+          colMask[c] = slot < p.n_slots ? ((__ldg(p.slot_sel + slot) << 8) | (__ldg(p.slot_val + slot) & 0xff)) : -1;
+        }
+        asm volatile("bar.sync 1, 128;" ::: "memory");
+      }
       const int64_t grow = p.row0 + rt * 128 + r;          // global row
       const int64_t lrow = rt * 128 + r;                   // row inside the chunk
-      const int64_t tile_id = (p.row0 >> 7) + rt;
-      const int slot0 = cb * NC;
       const bool valid = grow < p.row0 + p.rows && grow < p.n_rows_total;
       int yv = 0, lab = 0; float yf = 0.f;
       if (valid) {
@@ -269,68 +324,74 @@ tc_fwd_kernel(const __grid_constant__ CUtensorMap mapX, const __grid_constant__ 
         if (p.yreg) yf = p.yreg[grow];
         lab = (int)(uint8_t)p.fold_id[grow] | ((p.hold_id ? (int)(uint8_t)p.hold_id[grow] : 0) << 8);
       }
+      const float yy = (float)yv;
       const int acc = tile & 1; const uint32_t aph = (tile >> 1) & 1;
       mbar_wait(tfull + acc, aph);
       tc_fence_after();
       const uint32_t tacc = tmem_base + acc * NC + ((uint32_t)(q * 32) << 16);
-#pragma unroll 1
-      for (int c0 = 0; c0 < NC; c0 += 16) {
+#pragma unroll
+      for (int ci = 0; ci < NC / 16; ++ci) {
+        const int c0 = ci * 16;
         uint32_t v[16];
         tmem_ld16(tacc + c0, v);
         tmem_ld_wait();
-        if (c0 + 16 >= NC) {               // accumulator fully read: hand it back to the MMA warp
+        if (ci == NC / 16 - 1) {             // accumulator fully read: hand it back to the MMA warp
           tc_fence_before();
           __syncwarp();
           if (lane == 0) mbar_arrive(tempty + acc);
         }
-        float rh[16], rl[16];
+        if (MODE == FWD_LOGREG) {
+          double ls[16], rs[16]; float rh[16], rl[16];
 #pragma unroll
-        for (int j = 0; j < 16; ++j) {
-          const int slot = slot0 + c0 + j;
-          double ls = 0.0, rs = 0.0; int ok = 0; float res = 0.f;
-          if (slot < p.n_slots && valid) {
-            const int sel = __ldg(p.slot_sel + slot), val = __ldg(p.slot_val + slot);
-            const bool held = ((lab >> (8 * sel)) & 0xff) == val;
-            const float z = __uint_as_float(v[j]) + __ldg(p.bt + slot);
-            if (MODE == FWD_LOGREG) {
-              if (!held) { const float yy = (float)yv; ls = (double)(softplus_f(z) - yy * z); res = sigmoid_f(z) - yy; rs = (double)res; }
-            } else if (MODE == FWD_SCORE_CLS) {
-              if (held) ok = ((z > 0.f) ? 1 : 0) == yv;
-            } else {
-              if (held) { const float e = yf - z; ls = (double)(e * e); }
-            }
+          for (int j = 0; j < 16; ++j) {
+            const int m = colMask[c0 + j];
+            const bool train = valid && m >= 0 && ((lab >> (8 * (m >> 8))) & 0xff) != (m & 0xff);
+            const float z = __uint_as_float(v[j]) + colBias[c0 + j];
+            const float e = __expf(-fabsf(z));
+            const float inv = __fdividef(1.f, 1.f + e);
+            const float pr = z >= 0.f ? inv : e * inv;
+            const float res = train ? pr - yy : 0.f;
+            const float lo = train ? fmaxf(z, 0.f) - yy * z + __logf(1.f + e) : 0.f;
+            ls[j] = (double)lo; rs[j] = (double)res;
+            rh[j] = tf32_hi(res); rl[j] = res - rh[j];
           }
-          if (MODE == FWD_LOGREG) { rh[j] = tf32_hi(res); rl[j] = res - rh[j]; }
-          // column sums over the 32 rows of this warp (fp64), one partial per (tile, quadrant)
-          if (MODE == FWD_SCORE_CLS) {
-            const unsigned bal = __ballot_sync(0xffffffffu, ok);
-            if (lane == 0 && slot < p.n_slots) p.cntPart[(tile_id * 4 + q) * p.n_slots + slot] = __popc(bal);
-          } else {
-            ls = warp_sum(ls);
-            if (MODE == FWD_LOGREG) rs = warp_sum(rs);
-            if (lane == 0 && slot < p.n_slots) {
-              if (MODE == FWD_LOGREG) {
-                p.lossPart[(tile_id * 4 + q) * p.n_slots + slot] = ls;
-                p.gbPart[(tile_id * 4 + q) * p.n_slots + slot] = rs;
-              } else {
-                p.ssePart[(tile_id * 4 + q) * p.n_slots + slot] = (float)ls;
+          accA[ci] += bfly16(ls, lane);
+          accB[ci] += bfly16(rs, lane);
+          if (slot0 + c0 < p.ldr) {
+            float4* dh = reinterpret_cast<float4*>(p.Rhi + lrow * p.ldr + slot0 + c0);
+            float4* dl = reinterpret_cast<float4*>(p.Rlo + lrow * p.ldr + slot0 + c0);
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+              if (slot0 + c0 + 4 * j < p.ldr) {
+                dh[j] = make_float4(rh[4 * j], rh[4 * j + 1], rh[4 * j + 2], rh[4 * j + 3]);
+                dl[j] = make_float4(rl[4 * j], rl[4 * j + 1], rl[4 * j + 2], rl[4 * j + 3]);
               }
             }
           }
-        }
-        if (MODE == FWD_LOGREG && lrow < ((p.rows + 127) / 128) * 128 && slot0 + c0 < p.ldr) {
-          float4* dh = reinterpret_cast<float4*>(p.Rhi + lrow * p.ldr + slot0 + c0);
-          float4* dl = reinterpret_cast<float4*>(p.Rlo + lrow * p.ldr + slot0 + c0);
+        } else if (MODE == FWD_SCORE_CLS) {
+          int ok[16];
 #pragma unroll
-          for (int j = 0; j < 4; ++j) {
-            if (slot0 + c0 + 4 * j < p.ldr) {
-              dh[j] = make_float4(rh[4 * j], rh[4 * j + 1], rh[4 * j + 2], rh[4 * j + 3]);
-              dl[j] = make_float4(rl[4 * j], rl[4 * j + 1], rl[4 * j + 2], rl[4 * j + 3]);
-            }
+          for (int j = 0; j < 16; ++j) {
+            const int m = colMask[c0 + j];
+            const bool held = valid && m >= 0 && ((lab >> (8 * (m >> 8))) & 0xff) == (m & 0xff);
+            const float z = __uint_as_float(v[j]) + colBias[c0 + j];
+            ok[j] = (held && (((z > 0.f) ? 1 : 0) == yv)) ? 1 : 0;
           }
+          accC[ci] += bfly16(ok, lane);
+        } else {
+          double se[16];
+#pragma unroll
+          for (int j = 0; j < 16; ++j) {
+            const int m = colMask[c0 + j];
+            const bool held = valid && m >= 0 && ((lab >> (8 * (m >> 8))) & 0xff) == (m & 0xff);
+            const float e = yf - (__uint_as_float(v[j]) + colBias[c0 + j]);
+            se[j] = held ? (double)(e * e) : 0.0;
+          }
+          accA[ci] += bfly16(se, lane);
         }
       }
     }
+    flush(cur_cb);
   }
   tc_fence_before();
   __syncthreads();
@@ -504,9 +565,9 @@ __global__ void split_weights_kernel(const float* W, float* Whi, float* Wlo, int
   if (i < n) { const float x = W[i], h = tf32_hi(x); Whi[i] = h; Wlo[i] = x - h; }
 }
 
-// per-(tile, quadrant) fp64 partials -> Gred columns d (sum of residuals) and d+1 (loss)
+// per-(CTA, warp) fp64 partials [n_parts][n_slots] -> Gred columns d (sum of residuals) and d+1 (loss)
 struct TcReduceParams {
-  const double* lossPart; const double* gbPart; int64_t part0, n_parts; int n_slots, T, d;
+  const double* lossPart; const double* gbPart; int64_t n_parts; int n_slots, T, d;
   double* Gred; int ldgr; int accumulate;
 };
 __global__ void tc_reduce_tiles_kernel(const TcReduceParams p) {
@@ -514,7 +575,7 @@ __global__ void tc_reduce_tiles_kernel(const TcReduceParams p) {
   const int slot = blockIdx.x * 32 + threadIdx.x;
   double a = 0.0, b = 0.0;
   if (slot < p.n_slots)
-    for (int64_t t = p.part0 + threadIdx.y; t < p.part0 + p.n_parts; t += 8) {
+    for (int64_t t = threadIdx.y; t < p.n_parts; t += 8) {
       a += p.lossPart[t * p.n_slots + slot];
       b += p.gbPart[t * p.n_slots + slot];
     }
