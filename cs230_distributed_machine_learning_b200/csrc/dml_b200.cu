@@ -56,7 +56,8 @@ struct dml_ctx {
   cudaEvent_t ev_total[2] = {nullptr, nullptr};
   float total_ms = 0.f, contraction_ms = 0.f; int contraction_launches = 0, total_launches = 0;
   size_t r_budget = (size_t)4 << 30;  // bytes of residual scratch per row chunk
-  int tc_mask_hi = 1;                 // write the masked hi operand back before the MMAs read it
+  int tc_mask_hi = 0;                 // 1 = write the masked hi operand back before the MMAs read it (not needed:
+                                      // kind::tf32 ignores the 13 low mantissa bits, measured identical results)
   long long slot_rounds = 0; int rounds = 0;  // sum over rounds of evaluated columns
   // debug: scratch of the last evaluation (dml_debug_fetch)
   const void* dbg_ptr[4] = {nullptr, nullptr, nullptr, nullptr}; size_t dbg_bytes[4] = {0, 0, 0, 0};
@@ -344,6 +345,7 @@ struct EvalCtx {
   float *Wt = nullptr, *bt = nullptr, *R = nullptr, *Rlo = nullptr, *Whi = nullptr, *Wlo = nullptr, *Gpart = nullptr;
   double *lossPart = nullptr, *gbPart = nullptr, *Gred = nullptr; int32_t *sel = nullptr, *val = nullptr, *cntPart = nullptr;
   CUtensorMap mXf, mXg, mWh, mWl, mRh, mRl;
+  unsigned long long* hist_local = nullptr;   // [512] label histogram of this rank's rows
 
   void plan(dml_ctx* ctx, int64_t n_groups_max) {
     ctx_sms = ctx->n_sms;
@@ -366,6 +368,7 @@ struct EvalCtx {
   }
   void take(Arena& a, int64_t n_groups_max) {
     Gred = a.take<double>((size_t)S_max * ldgr);
+    hist_local = a.take<unsigned long long>(512);
     Wt = a.take<float>((size_t)S_max * ldw); bt = a.take<float>(S_max);
     sel = a.take<int32_t>(S_max); val = a.take<int32_t>(S_max);
     R = a.take<float>((size_t)chunk_rows * ldr_max);
@@ -422,7 +425,8 @@ struct EvalCtx {
         if (rc) return rc;
         ReduceParams rp{Gpart, ldg, splits_here, n_slots, d, T, d, nullptr, 0, 0, Gred, ldgr, ci > 0 ? 1 : 0};
         reduce_grad_kernel<<<n_slots, 256, 0, st>>>(rp);
-        tc::TcReduceParams tr{lossPart, gbPart, (int64_t)grid * 4, n_slots, T, d, Gred, ldgr, ci > 0 ? 1 : 0};
+        tc::TcReduceParams tr{lossPart, gbPart, (int64_t)grid * 4, n_slots, T, d, Gred, ldgr, ci > 0 ? 1 : 0,
+                              hist_local, sel, val, n};
         tc::tc_reduce_tiles_kernel<<<(unsigned)cdiv(n_slots, 32), dim3(32, 8), 0, st>>>(tr);
       } else {
         const int ldr = (int)rup(n_slots, 4);
@@ -532,9 +536,10 @@ extern "C" int dml_logreg_sweep(dml_ctx* ctx, const float* X, int64_t n, int d, 
   CU(cudaMemsetAsync(d_x, 0, sizeof(double) * (size_t)F * P, st));
   CU(cudaMemsetAsync(d_g, 0, sizeof(double) * (size_t)F * P, st));
   CU(cudaMemsetAsync(d_dir, 0, sizeof(double) * (size_t)F * P, st));
-  CU(cudaMemsetAsync(d_hist, 0, sizeof(unsigned long long) * 512, st));
-  label_hist_kernel<<<(unsigned)std::min<int64_t>(cdiv(n, 256), 4 * ctx->n_sms), 256, 0, st>>>(fold_id, hold_id, n, d_hist);
+  CU(cudaMemsetAsync(ev.hist_local, 0, sizeof(unsigned long long) * 512, st));
+  label_hist_kernel<<<(unsigned)std::min<int64_t>(cdiv(n, 256), 4 * ctx->n_sms), 256, 0, st>>>(fold_id, hold_id, n, ev.hist_local);
   KCHECK();
+  CU(cudaMemcpyAsync(d_hist, ev.hist_local, sizeof(unsigned long long) * 512, cudaMemcpyDeviceToDevice, st));
   int64_t n_total = n;
   if (ctx->comm) {
     int rc = allreduce(ctx, d_hist, 512, kNcclUint64); if (rc) return rc;
@@ -634,6 +639,8 @@ extern "C" int dml_logreg_eval(dml_ctx* ctx, const float* X, int64_t n, int d, i
   CU(cudaMemcpyAsync(ev.bt, b, sizeof(float) * n_slots, cudaMemcpyDeviceToDevice, st));
   CU(cudaMemcpyAsync(ev.sel, mask_sel, sizeof(int32_t) * n_slots, cudaMemcpyDeviceToDevice, st));
   CU(cudaMemcpyAsync(ev.val, mask_val, sizeof(int32_t) * n_slots, cudaMemcpyDeviceToDevice, st));
+  CU(cudaMemsetAsync(ev.hist_local, 0, sizeof(unsigned long long) * 512, st));
+  label_hist_kernel<<<(unsigned)std::min<int64_t>(cdiv(n, 256), 4 * ctx->n_sms), 256, 0, st>>>(fold_id, hold_id, n, ev.hist_local);
   int rc = ev.evaluate(ctx, n_slots);
   if (rc) return rc;
   if (ctx->comm) { rc = allreduce(ctx, ev.Gred, (size_t)n_slots * ev.ldgr, kNcclFloat64); if (rc) return rc; }

@@ -129,7 +129,8 @@ __device__ __forceinline__ void split_stage(float* hi, float* lo, int bytes, int
 
 // ---------------------------------------------------------------- forward kernel
 constexpr int kFwdStages = 3;
-constexpr int kFwdThreads = 320;   // warp 0 TMA, warp 1 MMA, warps 2-5 operand split, warps 6-9 epilogue
+constexpr int kFwdThreads = 448;   // warp 0 TMA, warp 1 MMA, warps 2-5 operand split, warps 6-13 epilogue
+constexpr float kLossShift = 0.693147182f;   // ln 2: per-row losses are summed as (loss - ln 2), see below
 
 struct TcFwdParams {
   int64_t n_rows_total;      // rows of X visible through the tensor map (for masking the last tile)
@@ -200,7 +201,7 @@ tc_fwd_kernel(const __grid_constant__ CUtensorMap mapX, const __grid_constant__ 
 
   if (warp == 0 && lane == 0) {
     for (int s = 0; s < kFwdStages; ++s) { mbar_init(full + s, 1); mbar_init(split + s, 4); mbar_init(empty + s, 1); }
-    for (int a = 0; a < 2; ++a) { mbar_init(tfull + a, 1); mbar_init(tempty + a, 4); }
+    for (int a = 0; a < 2; ++a) { mbar_init(tfull + a, 1); mbar_init(tempty + a, 8); }
     fence_barrier_init();
   }
   if (warp == 1) tmem_alloc(tmem_slot, kTmemCols);
@@ -277,22 +278,28 @@ tc_fwd_kernel(const __grid_constant__ CUtensorMap mapX, const __grid_constant__ 
       }
     }
   } else {
-    // ===== epilogue: thread = row of the tile (TMEM lane) =====
+    // ===== epilogue: thread = row of the tile (TMEM lane); two warps per lane quadrant, each
+    // taking every other 16-column chunk.  Column sums over the 32 rows of a warp are formed in
+    // fp32 (the loss shifted by ln 2 so the partial sums stay O(1)) and accumulated in fp64 across
+    // tiles; see DESIGN.md "precision" for why the loss needs this care. =====
     const int q = warp & 3;                 // TMEM lane quadrant this warp may read
+    const int half = (warp - 6) >> 2;       // which chunks: ci % 2 == half
     const int r = q * 32 + lane;            // row within the tile
-    const int et = threadIdx.x - 192;       // 0..127 among the epilogue threads
+    const int et = threadIdx.x - 192;       // 0..255 among the epilogue threads
     const int mycol = bfly_col(lane);
-    double accA[NC / 16], accB[NC / 16]; int accC[NC / 16];
+    constexpr int kMy = (NC / 16 + 1) / 2;  // chunks per warp (upper bound)
+    double accA[kMy], accB[kMy]; int accC[kMy];
 #pragma unroll
-    for (int i = 0; i < NC / 16; ++i) { accA[i] = 0.0; accB[i] = 0.0; accC[i] = 0; }
+    for (int i = 0; i < kMy; ++i) { accA[i] = 0.0; accB[i] = 0.0; accC[i] = 0; }
     int cur_cb = -1;
     const int64_t part_row = ((int64_t)blockIdx.x * 4 + q) * p.n_slots;
     auto flush = [&](int cb) {
       if (cb < 0 || (lane & 1)) return;
 #pragma unroll
-      for (int i = 0; i < NC / 16; ++i) {
-        const int slot = cb * NC + i * 16 + mycol;
-        if (slot < p.n_slots) {
+      for (int i = 0; i < kMy; ++i) {
+        const int ci = 2 * i + half;
+        const int slot = cb * NC + ci * 16 + mycol;
+        if (ci < NC / 16 && slot < p.n_slots) {
           if (MODE == FWD_LOGREG) { p.lossPart[part_row + slot] = accA[i]; p.gbPart[part_row + slot] = accB[i]; }
           else if (MODE == FWD_SCORE_CLS) p.cntPart[part_row + slot] = accC[i];
           else p.ssePart[part_row + slot] = accA[i];
@@ -307,13 +314,13 @@ tc_fwd_kernel(const __grid_constant__ CUtensorMap mapX, const __grid_constant__ 
       if (cb != cur_cb) {
         flush(cur_cb);
         cur_cb = cb;
-        asm volatile("bar.sync 1, 128;" ::: "memory");     // everyone is done with the old column metadata
-        for (int c = et; c < NC; c += 128) {
+        asm volatile("bar.sync 1, 256;" ::: "memory");     // everyone is done with the old column metadata
+        for (int c = et; c < NC; c += 256) {
           const int slot = slot0 + c;
           colBias[c] = slot < p.n_slots ? __ldg(p.bt + slot) : 0.f;
           colMask[c] = slot < p.n_slots ? ((__ldg(p.slot_sel + slot) << 8) | (__ldg(p.slot_val + slot) & 0xff)) : -1;
         }
-        asm volatile("bar.sync 1, 128;" ::: "memory");
+        asm volatile("bar.sync 1, 256;" ::: "memory");
       }
       const int64_t grow = p.row0 + rt * 128 + r;          // global row
       const int64_t lrow = rt * 128 + r;                   // row inside the chunk
@@ -330,18 +337,20 @@ tc_fwd_kernel(const __grid_constant__ CUtensorMap mapX, const __grid_constant__ 
       tc_fence_after();
       const uint32_t tacc = tmem_base + acc * NC + ((uint32_t)(q * 32) << 16);
 #pragma unroll
-      for (int ci = 0; ci < NC / 16; ++ci) {
+      for (int i = 0; i < kMy; ++i) {
+        const int ci = 2 * i + half;
+        if (ci >= NC / 16) break;
         const int c0 = ci * 16;
         uint32_t v[16];
         tmem_ld16(tacc + c0, v);
         tmem_ld_wait();
-        if (ci == NC / 16 - 1) {             // accumulator fully read: hand it back to the MMA warp
+        if (i == kMy - 1 || ci + 2 >= NC / 16) {   // this warp's last read of the accumulator
           tc_fence_before();
           __syncwarp();
           if (lane == 0) mbar_arrive(tempty + acc);
         }
         if (MODE == FWD_LOGREG) {
-          double ls[16], rs[16]; float rh[16], rl[16];
+          float ls[16], rs[16], rl[16];
 #pragma unroll
           for (int j = 0; j < 16; ++j) {
             const int m = colMask[c0 + j];
@@ -350,20 +359,20 @@ tc_fwd_kernel(const __grid_constant__ CUtensorMap mapX, const __grid_constant__ 
             const float e = __expf(-fabsf(z));
             const float inv = __fdividef(1.f, 1.f + e);
             const float pr = z >= 0.f ? inv : e * inv;
-            const float res = train ? pr - yy : 0.f;
-            const float lo = train ? fmaxf(z, 0.f) - yy * z + __logf(1.f + e) : 0.f;
-            ls[j] = (double)lo; rs[j] = (double)res;
-            rh[j] = tf32_hi(res); rl[j] = res - rh[j];
+            rs[j] = train ? pr - yy : 0.f;
+            ls[j] = train ? (fmaxf(z, 0.f) - yy * z) + (__logf(1.f + e) - kLossShift) : 0.f;
           }
-          accA[ci] += bfly16(ls, lane);
-          accB[ci] += bfly16(rs, lane);
+          accA[i] += (double)bfly16(ls, lane);
+          accB[i] += (double)bfly16(rs, lane);
+#pragma unroll
+          for (int j = 0; j < 16; ++j) { const float h = tf32_hi(rs[j]); rl[j] = rs[j] - h; rs[j] = h; }
           if (slot0 + c0 < p.ldr) {
             float4* dh = reinterpret_cast<float4*>(p.Rhi + lrow * p.ldr + slot0 + c0);
             float4* dl = reinterpret_cast<float4*>(p.Rlo + lrow * p.ldr + slot0 + c0);
 #pragma unroll
             for (int j = 0; j < 4; ++j) {
               if (slot0 + c0 + 4 * j < p.ldr) {
-                dh[j] = make_float4(rh[4 * j], rh[4 * j + 1], rh[4 * j + 2], rh[4 * j + 3]);
+                dh[j] = make_float4(rs[4 * j], rs[4 * j + 1], rs[4 * j + 2], rs[4 * j + 3]);
                 dl[j] = make_float4(rl[4 * j], rl[4 * j + 1], rl[4 * j + 2], rl[4 * j + 3]);
               }
             }
@@ -377,17 +386,17 @@ tc_fwd_kernel(const __grid_constant__ CUtensorMap mapX, const __grid_constant__ 
             const float z = __uint_as_float(v[j]) + colBias[c0 + j];
             ok[j] = (held && (((z > 0.f) ? 1 : 0) == yv)) ? 1 : 0;
           }
-          accC[ci] += bfly16(ok, lane);
+          accC[i] += bfly16(ok, lane);
         } else {
-          double se[16];
+          float se[16];
 #pragma unroll
           for (int j = 0; j < 16; ++j) {
             const int m = colMask[c0 + j];
             const bool held = valid && m >= 0 && ((lab >> (8 * (m >> 8))) & 0xff) == (m & 0xff);
             const float e = yf - (__uint_as_float(v[j]) + colBias[c0 + j]);
-            se[j] = held ? (double)(e * e) : 0.0;
+            se[j] = held ? e * e : 0.f;
           }
-          accA[ci] += bfly16(se, lane);
+          accA[i] += (double)bfly16(se, lane);
         }
       }
     }
@@ -569,6 +578,8 @@ __global__ void split_weights_kernel(const float* W, float* Whi, float* Wlo, int
 struct TcReduceParams {
   const double* lossPart; const double* gbPart; int64_t n_parts; int n_slots, T, d;
   double* Gred; int ldgr; int accumulate;
+  // the forward kernel sums (loss - ln 2): add ln 2 * (training rows of the column) back once
+  const unsigned long long* hist_local; const int32_t* sel; const int32_t* val; int64_t n_local;
 };
 __global__ void tc_reduce_tiles_kernel(const TcReduceParams p) {
   __shared__ double sh[2][8][33];
@@ -586,6 +597,8 @@ __global__ void tc_reduce_tiles_kernel(const TcReduceParams p) {
     for (int i = 0; i < 8; ++i) { l += sh[0][i][threadIdx.x]; g += sh[1][i][threadIdx.x]; }
     double* q = p.Gred + (int64_t)slot * p.ldgr;
     q[p.d] = p.accumulate ? q[p.d] + g : g;
+    if (!p.accumulate)
+      l += (double)kLossShift * (double)(p.n_local - (int64_t)p.hist_local[p.sel[slot] * 256 + (p.val[slot] & 0xff)]);
     if (slot % p.T == 0) q[p.d + 1] = p.accumulate ? q[p.d + 1] + l : l;
   }
 }
