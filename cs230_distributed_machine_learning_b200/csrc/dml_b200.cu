@@ -843,3 +843,68 @@ extern "C" int dml_score(dml_ctx* ctx, const float* X, int64_t n, int d, int64_t
   CU(cudaStreamSynchronize(st));
   return DML_OK;
 }
+
+// =============================================================================================
+// Scoring without any allocation.
+//
+// Some callers of this library must not allocate device memory while they run: a worker that
+// was admitted with a fixed device-memory reservation and has handed all of it out already, or
+// a scoring call issued on a side stream while a sweep owns the GPU -- cudaMalloc / cudaFree
+// serialise the whole device and would stall that sweep (and fail outright when the reservation
+// is spent).  dml_score reaches into the ctx arena, which grows with cudaMalloc on demand; this
+// variant keeps its only scratch (per-row-tile partial counts) in the fixed array below, so the
+// call launches kernels and nothing else.  The array is resident on every GPU that loads the
+// library (4 MiB) until the process exits.
+constexpr size_t kStaticScoreInts = (size_t)1 << 20;   // 1 Mi int32 = 4 MiB
+static __device__ __align__(256) int32_t g_score_scratch[kStaticScoreInts];
+// Host code must not hand `g_score_scratch` itself to a kernel: on the host that name is only a
+// stand-in for the symbol.  The device address is looked up once per device, below.
+constexpr int kMaxDevices = 64;
+static int32_t* g_score_scratch_dev[kMaxDevices] = {nullptr};
+
+extern "C" int dml_score_static(int device, void* stream_v, const float* X, int64_t n, int d, int64_t ldx,
+                                const int32_t* y_cls, const int8_t* fold_id, const int8_t* hold_id,
+                                const float* W, const float* b, const int32_t* mask_sel, const int32_t* mask_val,
+                                int n_slots, int T, int64_t* correct_out) {
+  dml_ctx* ctx = nullptr;   // messages go to the context-free slot of dml_last_error(NULL)
+  if (device < 0 || device >= kMaxDevices) return fail(ctx, DML_ERR_ARG, "dml_score_static: device %d out of range", device);
+  if (!X || !y_cls || !fold_id || !W || !b || !mask_sel || !mask_val || !correct_out || n <= 0 || d <= 0 || ldx < d ||
+      n_slots <= 0 || T <= 0 || T > BN || n_slots % T != 0)
+    return fail(ctx, DML_ERR_ARG, "dml_score_static: bad argument");
+  const int64_t tiles = cdiv(n, BM);
+  const int tile_n = (BN / T) * T;
+  if ((size_t)tiles * (size_t)n_slots > kStaticScoreInts)
+    return fail(ctx, DML_ERR_LIMIT,
+                "dml_score_static: ceil(n/128) * n_slots = %lld exceeds the fixed scratch of %llu entries "
+                "(4 MiB); score fewer columns per call or use dml_score",
+                (long long)(tiles * n_slots), (unsigned long long)kStaticScoreInts);
+  if (cdiv(n_slots, tile_n) > 65535) return fail(ctx, DML_ERR_LIMIT, "dml_score_static: too many columns (%d)", n_slots);
+  CU(cudaSetDevice(device));
+  if (!g_score_scratch_dev[device]) {
+    // one-time set-up on this device (no allocation: address lookup + a function attribute)
+    int32_t* ptr = nullptr;
+    CU(cudaGetSymbolAddress((void**)&ptr, g_score_scratch));
+    CU(cudaFuncSetAttribute(fwd_kernel<FWD_SCORE_CLS>, cudaFuncAttributeMaxDynamicSharedMemorySize, kFwdSmemBytes));
+    g_score_scratch_dev[device] = ptr;
+  }
+  int32_t* part = g_score_scratch_dev[device];
+  cudaStream_t st = (cudaStream_t)stream_v;
+  // The array still holds the previous call's partial counts.  Every entry this call reads is
+  // written by it first, but the used part is zeroed anyway so that stale counts can never leak.
+  CU(cudaMemsetAsync(part, 0, sizeof(int32_t) * (size_t)tiles * n_slots, st));
+  FwdParams fp{};
+  fp.X = X; fp.ldx = ldx; fp.row0 = 0; fp.rows = n; fp.d = d;
+  fp.xvec = (ldx % 4 == 0) && aligned16(X);
+  fp.Wt = W; fp.ldw = d; fp.wvec = (d % 4 == 0) && aligned16(W); fp.bt = b;
+  fp.n_slots = n_slots; fp.T = T; fp.tile_n = tile_n;
+  fp.ycls = y_cls; fp.yreg = nullptr; fp.fold_id = fold_id; fp.hold_id = hold_id;
+  fp.slot_sel = mask_sel; fp.slot_val = mask_val;
+  fp.cntPart = part; fp.ssePart = nullptr;
+  dim3 grid((unsigned)tiles, (unsigned)cdiv(n_slots, tile_n));
+  fwd_kernel<FWD_SCORE_CLS><<<grid, NT, kFwdSmemBytes, st>>>(fp);
+  KCHECK();
+  reduce_counts_kernel<<<n_slots / T, 256, 0, st>>>(part, tiles, n_slots, T, (long long*)correct_out);
+  KCHECK();
+  CU(cudaStreamSynchronize(st));
+  return DML_OK;
+}

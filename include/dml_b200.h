@@ -123,6 +123,34 @@ int dml_score(dml_ctx* ctx, const float* X, int64_t n, int d, int64_t ldx,
               const float* W, const float* b, const int32_t* mask_sel, const int32_t* mask_val,
               int n_slots, int T, int64_t* correct_out, double* sse_out);
 
+/* dml_score for classifiers, for callers that cannot allocate device memory at the
+ * time of the call.  It has no counterpart in the reference.
+ *
+ * Who needs it: a worker admitted under a fixed device-memory reservation that is
+ * already fully handed out, or a caller scoring on a side stream while a sweep is
+ * running on the same GPU.  cudaMalloc / cudaFree serialise the device (stalling
+ * the sweep) and fail once the reservation is spent; dml_score may call them
+ * because its scratch lives in a ctx arena that grows on demand.  This entry point
+ * takes no ctx and calls neither: its only scratch, the per-128-row-tile partial
+ * counts, sits in a fixed 4 MiB array inside the library image, present on every
+ * GPU that loads the library for the life of the process.
+ *
+ * Limit: ceil(n / 128) * n_slots <= 1 048 576, else DML_ERR_LIMIT (4) is returned
+ * with a message in dml_last_error(NULL) and nothing is launched.
+ * Arguments and results are those of dml_score (classifier form): W [n_slots][d],
+ * b, mask_sel, mask_val device arrays; correct_out [n_slots / T] int64 on device.
+ * `device` is made current; `stream` is a cudaStream_t (NULL = default stream);
+ * the call returns after the stream has drained, with correct_out valid.
+ * The first call on each device looks up the array's device address and sets a
+ * kernel attribute; make that first call outside of any stream capture.
+ * All calls on a device share the one array and the array keeps the previous
+ * call's contents (the used part is cleared at the start of each call): two
+ * calls that overlap on the same GPU, from any streams or threads, race. */
+int dml_score_static(int device, void* stream, const float* X, int64_t n, int d, int64_t ldx,
+                     const int32_t* y_cls, const int8_t* fold_id, const int8_t* hold_id,
+                     const float* W, const float* b, const int32_t* mask_sel, const int32_t* mask_val,
+                     int n_slots, int T, int64_t* correct_out);
+
 /* Timing of the last sweep on this ctx, measured with CUDA events on the ctx
  * stream: total milliseconds, milliseconds inside the contraction kernels
  * (forward + gradient, or Gram), their launch count, and all launches. */
