@@ -364,17 +364,38 @@ tc_fwd_kernel(const __grid_constant__ CUtensorMap mapX, const __grid_constant__ 
           }
           accA[i] += (double)bfly16(ls, lane);
           accB[i] += (double)bfly16(rs, lane);
+          // 4x4 transpose of float4 inside each group of 4 lanes (rows 4g..4g+3): afterwards lane t
+          // holds float4 #t of rows 4g..4g+3, so the 4 lanes of a group store 64 contiguous bytes
+          // of one row per instruction instead of 16 bytes of four different rows.
+          {
+            const bool o1 = lane & 1, o2 = lane & 2;
+#pragma unroll
+            for (int c1 = 0; c1 < 2; ++c1)
+#pragma unroll
+              for (int e = 0; e < 4; ++e) {
+                const float snd = o1 ? rs[8 * c1 + e] : rs[8 * c1 + 4 + e];
+                const float rcv = __shfl_xor_sync(0xffffffffu, snd, 1);
+                if (o1) rs[8 * c1 + e] = rcv; else rs[8 * c1 + 4 + e] = rcv;
+              }
+#pragma unroll
+            for (int c0 = 0; c0 < 2; ++c0)
+#pragma unroll
+              for (int e = 0; e < 4; ++e) {
+                const float snd = o2 ? rs[4 * c0 + e] : rs[4 * c0 + 8 + e];
+                const float rcv = __shfl_xor_sync(0xffffffffu, snd, 2);
+                if (o2) rs[4 * c0 + e] = rcv; else rs[4 * c0 + 8 + e] = rcv;
+              }
+          }
 #pragma unroll
           for (int j = 0; j < 16; ++j) { const float h = tf32_hi(rs[j]); rl[j] = rs[j] - h; rs[j] = h; }
-          if (slot0 + c0 < p.ldr) {
-            float4* dh = reinterpret_cast<float4*>(p.Rhi + lrow * p.ldr + slot0 + c0);
-            float4* dl = reinterpret_cast<float4*>(p.Rlo + lrow * p.ldr + slot0 + c0);
+          const int tq = lane & 3;                              // which float4 of the 16-column chunk
+          const int64_t lrow4 = rt * 128 + q * 32 + (lane & ~3); // first row of this lane group
+          if (slot0 + c0 + 4 * tq < p.ldr) {
 #pragma unroll
-            for (int j = 0; j < 4; ++j) {
-              if (slot0 + c0 + 4 * j < p.ldr) {
-                dh[j] = make_float4(rs[4 * j], rs[4 * j + 1], rs[4 * j + 2], rs[4 * j + 3]);
-                dl[j] = make_float4(rl[4 * j], rl[4 * j + 1], rl[4 * j + 2], rl[4 * j + 3]);
-              }
+            for (int j = 0; j < 4; ++j) {                       // j = row inside the group
+              const int64_t o = (lrow4 + j) * p.ldr + slot0 + c0 + 4 * tq;
+              *reinterpret_cast<float4*>(p.Rhi + o) = make_float4(rs[4 * j], rs[4 * j + 1], rs[4 * j + 2], rs[4 * j + 3]);
+              *reinterpret_cast<float4*>(p.Rlo + o) = make_float4(rl[4 * j], rl[4 * j + 1], rl[4 * j + 2], rl[4 * j + 3]);
             }
           }
         } else if (MODE == FWD_SCORE_CLS) {

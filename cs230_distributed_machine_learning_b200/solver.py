@@ -41,6 +41,7 @@ class SweepSolver:
         self.lib = self.ctx.lib
         self.h2d_bytes = 0
         self.d2h_bytes = 0
+        self._class_cache: dict[int, tuple] = {}
 
     # ---- plumbing -------------------------------------------------------------------
     def to_device(self, a, dtype=None, pin: bool = False) -> torch.Tensor:
@@ -74,8 +75,12 @@ class SweepSolver:
         if classifier:
             if isinstance(y, torch.Tensor):
                 y = y.cpu().numpy()
-            classes, idx = np.unique(np.asarray(y), return_inverse=True)
-            yc = self.to_device(idx.astype(np.int32), torch.int32)
+            key = id(y)
+            if key not in self._class_cache:      # label encoding of a registered dataset is computed once
+                classes, idx = np.unique(np.asarray(y), return_inverse=True)
+                self._class_cache[key] = (classes, idx.astype(np.int32), y)
+            classes, idx, _ = self._class_cache[key]
+            yc = self.to_device(idx, torch.int32)
             return DeviceDataset(Xd, yc, None, classes, n, d)
         yr = self.to_device(y, torch.float32)
         return DeviceDataset(Xd, None, yr, None, n, d)

@@ -139,6 +139,8 @@ class GpuExecutor:
         self.gpu = gpu
         self.solver = SweepSolver(gpu)
         self.resident: dict[tuple[str, bool], object] = {}
+        self.labels: dict[tuple, np.ndarray] = {}     # host-side row labels, computed once per dataset
+        self.pinned: set[int] = set()
         self.lock = threading.Lock()
 
     def drop_resident(self):
@@ -150,8 +152,35 @@ class GpuExecutor:
         key = (name, classifier)
         if key not in self.resident:   # the reference re-parses the CSV per subtask (worker.py:425)
             X, y = datasets.get_dataset(name)
+            self._pin(X)
             self.resident[key] = self.solver.upload_dataset(X, y, classifier)
         return self.resident[key]
+
+    def _pin(self, X: np.ndarray) -> None:
+        """Page-lock a registered float32 array in place (once), so every later upload is a
+        pinned-memory DMA instead of a staged copy."""
+        import torch
+        if X.dtype != np.float32 or id(X) in self.pinned or not X.flags.c_contiguous:
+            return
+        rc = torch.cuda.cudart().cudaHostRegister(X.ctypes.data, X.nbytes, 0)
+        if int(rc) == 0:
+            self.pinned.add(id(X))
+
+    def row_labels(self, dataset_id: str, classifier: bool, cv: int, n: int, y_host, test_size=None, random_state=None):
+        key = (dataset_id, classifier, cv)
+        if key not in self.labels:
+            if classifier:
+                _, y_idx = np.unique(np.asarray(y_host), return_inverse=True)
+                self.labels[key] = folds.stratified_labels(y_idx, cv)
+            else:
+                self.labels[key] = folds.kfold_labels(n, cv)
+        hold = None
+        if test_size is not None:
+            hkey = (dataset_id, "hold", test_size, random_state)
+            if hkey not in self.labels:
+                self.labels[hkey] = folds.holdout_labels(n, test_size, random_state)
+            hold = self.labels[hkey]
+        return self.labels[key], hold
 
     def run(self, model_type: str, cands: list[dict], train_params: dict, dataset_id: str, model_dir: str) -> list[dict]:
         """cands: [{index, subtask_id, parameters}] -> result dict per candidate (A9 shape)."""
@@ -162,14 +191,8 @@ class GpuExecutor:
             cv = train_params.get("cv", 5)
             if not isinstance(cv, int):
                 raise ValueError("the GPU executor takes an integer cv (un-shuffled (Stratified)KFold)")
-            if classifier:
-                _, y_idx = np.unique(np.asarray(y_host), return_inverse=True)
-                fold = folds.stratified_labels(y_idx, cv)
-            else:
-                fold = folds.kfold_labels(ds.n, cv)
-            hold = None
-            if "test_size" in train_params:
-                hold = folds.holdout_labels(ds.n, train_params["test_size"], train_params.get("random_state"))
+            fold, hold = self.row_labels(dataset_id, classifier, cv, ds.n, y_host, train_params.get("test_size"),
+                                         train_params.get("random_state"))
             P = [c["parameters"] for c in cands]
             fi = [bool(p.get("fit_intercept", True)) for p in P]
             t0 = time.time()

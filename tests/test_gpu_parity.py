@@ -262,3 +262,48 @@ def test_medium_size_properties(solver):
         rows = fold == k
         zz = X[rows] @ a["coef"][i, k, 0] + a["intercept"][i, k, 0]
         assert abs(int(((zz > 0) == y[rows]).sum()) - int(a["correct"][i, k])) <= int((np.abs(zz) < 1e-5).sum())
+
+
+def test_config_shapes_at_moderate_size(solver):
+    """The shapes of BASELINE.json configs 3-5 (d = 512, cv = 10, 10 classes, per-candidate tol /
+    fit_intercept) at sizes the oracle can still spot-check."""
+    from sklearn.linear_model import LogisticRegression, Ridge
+    # config 5 shape: binary, d = 512, cv = 10 (tensor-core path, 4 feature blocks)
+    X, y = make_dataset("binary", 60_000, 512, seed=5)
+    fold = folds.stratified_labels(y, 10)
+    Cs = np.logspace(-6, 2, 16)
+    ds = solver.upload_dataset(X, y, classifier=True)
+    out = solver.logreg_sweep(ds, fold, 10, Cs, [1e-4] * 16, [True] * 16, [100] * 16)
+    assert (out["status"] == 0).all() and (out["n_test"].sum(axis=1) == len(y)).all()
+    for i, k in [(0, 0), (7, 3), (15, 9)]:
+        r = olbfgs.fit_logreg(X[fold != k].astype(np.float64), y[fold != k], 2, C=Cs[i])
+        assert r["n_iter"] == out["n_iter"][i, k]
+        assert rel_err(out["coef"][i, k], r["coef"]) <= RTOL
+        z = X[fold == k].astype(np.float64) @ r["coef"][0] + r["intercept"][0]
+        assert abs(int(((z > 0) == y[fold == k]).sum()) - int(out["correct"][i, k])) <= int((np.abs(z) < 2e-5).sum())
+    # config 4 shape: 10 classes, d = 512, candidates differing in C, tol and fit_intercept
+    X, y = make_dataset("multiclass10", 30_000, 512, seed=4)
+    fold = folds.stratified_labels(y, 5)
+    cands = [(1e-3, 1e-4, True), (1.0, 1e-5, False), (10.0, 1e-3, True), (0.05, 1e-4, False)]
+    ds = solver.upload_dataset(X, y, classifier=True)
+    out = solver.logreg_sweep(ds, fold, 5, [c[0] for c in cands], [c[1] for c in cands], [c[2] for c in cands], [100] * 4)
+    assert out["coef"].shape == (4, 5, 10, 512)
+    for i, k in [(0, 1), (1, 4), (3, 0)]:
+        C_, tol_, fi_ = cands[i]
+        m = LogisticRegression(C=C_, tol=tol_, fit_intercept=fi_).fit(X[fold != k].astype(np.float64), y[fold != k])
+        if m.n_iter_[0] == out["n_iter"][i, k]:
+            assert rel_err(out["coef"][i, k], m.coef_) <= RTOL
+            ties = near_ties(X, m.coef_, m.intercept_, fold == k)
+            assert abs(int((m.predict(X[fold == k].astype(np.float64)) == y[fold == k]).sum()) - int(out["correct"][i, k])) <= ties
+    # config 3 shape: Ridge, d = 512, many alphas, one pass over X for all folds
+    X, y = make_dataset("regression", 100_000, 512, seed=3)
+    kf = folds.kfold_labels(len(y), 5)
+    alphas = np.logspace(-3, 5, 16)
+    ds = solver.upload_dataset(X, y, classifier=False)
+    out = solver.ridge_sweep(ds, kf, 5, alphas, [True] * 16, classifier=False)
+    assert (out["info"] == 0).all()
+    for i, k in [(0, 0), (9, 2), (15, 4)]:
+        m = Ridge(alpha=alphas[i]).fit(X[kf != k].astype(np.float64), y[kf != k].astype(np.float64))
+        assert rel_err(out["coef"][i, k], m.coef_) <= RTOL
+        sse = float(((y[kf == k] - m.predict(X[kf == k].astype(np.float64))) ** 2).sum())
+        assert out["sse"][i, k] == pytest.approx(sse, rel=RTOL)
