@@ -56,6 +56,7 @@ struct dml_ctx {
   cudaEvent_t ev_total[2] = {nullptr, nullptr};
   float total_ms = 0.f, contraction_ms = 0.f; int contraction_launches = 0, total_launches = 0;
   size_t r_budget = (size_t)4 << 30;  // bytes of residual scratch per row chunk
+  int tc_cluster = 2;                 // CTAs per cluster in the forward kernel (W multicast): 1 or 2
   int tc_mask_hi = 0;                 // 1 = write the masked hi operand back before the MMAs read it (not needed:
                                       // kind::tf32 ignores the 13 low mantissa bits, measured identical results)
   long long slot_rounds = 0; int rounds = 0;  // sum over rounds of evaluated columns
@@ -151,6 +152,7 @@ extern "C" int dml_ctx_create(int device, void* stream, dml_ctx** out) {
   ctx = new dml_ctx();
   ctx->device = device; ctx->stream = (cudaStream_t)stream; ctx->n_sms = prop.multiProcessorCount;
   if (const char* e = getenv("DML_TC_MASK_HI")) ctx->tc_mask_hi = atoi(e);
+  if (const char* e = getenv("DML_TC_CLUSTER")) ctx->tc_cluster = atoi(e) == 1 ? 1 : 2;
   CU(cudaSetDevice(device));
   CU(cudaHostAlloc(&ctx->h_scalar, 64, cudaHostAllocDefault));
   ctx->ev.resize(2 * 2048);
@@ -262,27 +264,36 @@ static int pick_nc(int64_t n_slots) {
 }
 static bool tc_eligible(const float* X, int64_t ldx, int T) { return T == 1 && ldx % 4 == 0 && aligned16(X); }
 
-template <int NC, int MODE>
+template <int NC, int MODE, int CL>
 static int launch_tc_fwd_nc(dml_ctx* ctx, int grid, const CUtensorMap& mx, const CUtensorMap& mwh, const CUtensorMap& mwl,
                             const tc::TcFwdParams& p) {
   static bool attr_set = false;
   if (!attr_set) {
-    CU(cudaFuncSetAttribute(tc::tc_fwd_kernel<NC, MODE>, cudaFuncAttributeMaxDynamicSharedMemorySize, tc::FwdSmem<NC>::kBytes));
+    CU(cudaFuncSetAttribute(tc::tc_fwd_kernel<NC, MODE, CL>, cudaFuncAttributeMaxDynamicSharedMemorySize, tc::FwdSmem<NC>::kBytes));
     attr_set = true;
   }
-  tc::tc_fwd_kernel<NC, MODE><<<grid, tc::kFwdThreads, tc::FwdSmem<NC>::kBytes, ctx->stream>>>(mx, mwh, mwl, p);
+  cudaLaunchConfig_t cfg{};
+  cfg.gridDim = dim3((unsigned)grid); cfg.blockDim = dim3(tc::kFwdThreads);
+  cfg.dynamicSmemBytes = tc::FwdSmem<NC>::kBytes; cfg.stream = ctx->stream;
+  cudaLaunchAttribute at[1];
+  at[0].id = cudaLaunchAttributeClusterDimension;
+  at[0].val.clusterDim.x = CL; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = 1;
+  cfg.attrs = at; cfg.numAttrs = 1;
+  CU(cudaLaunchKernelEx(&cfg, tc::tc_fwd_kernel<NC, MODE, CL>, mx, mwh, mwl, p));
   return DML_OK;
 }
+// `cl` = CTAs per cluster (1 or 2); the W maps must have been built with box rows NC / cl
 template <int MODE>
-static int launch_tc_fwd(dml_ctx* ctx, int NC, int grid, const CUtensorMap& mx, const CUtensorMap& mwh,
+static int launch_tc_fwd(dml_ctx* ctx, int NC, int cl, int grid, const CUtensorMap& mx, const CUtensorMap& mwh,
                          const CUtensorMap& mwl, const tc::TcFwdParams& p) {
+#define DML_FWD_CASE(N) case N: return cl == 2 ? launch_tc_fwd_nc<N, MODE, 2>(ctx, grid, mx, mwh, mwl, p) \
+                                               : launch_tc_fwd_nc<N, MODE, 1>(ctx, grid, mx, mwh, mwl, p);
   switch (NC) {
-    case 160: return launch_tc_fwd_nc<160, MODE>(ctx, grid, mx, mwh, mwl, p);
-    case 128: return launch_tc_fwd_nc<128, MODE>(ctx, grid, mx, mwh, mwl, p);
-    case 96: return launch_tc_fwd_nc<96, MODE>(ctx, grid, mx, mwh, mwl, p);
-    case 64: return launch_tc_fwd_nc<64, MODE>(ctx, grid, mx, mwh, mwl, p);
-    default: return launch_tc_fwd_nc<32, MODE>(ctx, grid, mx, mwh, mwl, p);
+    DML_FWD_CASE(160) DML_FWD_CASE(128) DML_FWD_CASE(96) DML_FWD_CASE(64)
+    default: return cl == 2 ? launch_tc_fwd_nc<32, MODE, 2>(ctx, grid, mx, mwh, mwl, p)
+                            : launch_tc_fwd_nc<32, MODE, 1>(ctx, grid, mx, mwh, mwl, p);
   }
+#undef DML_FWD_CASE
 }
 template <int NC>
 static int launch_tc_grad_nc(dml_ctx* ctx, dim3 grid, const CUtensorMap& mx, const CUtensorMap& mrh, const CUtensorMap& mrl,
@@ -339,7 +350,7 @@ struct EvalCtx {
   const float* X = nullptr; int64_t n = 0, ldx = 0; int d = 0, T = 1;
   const int32_t* y = nullptr; const int8_t* fold_id = nullptr; const int8_t* hold_id = nullptr;
   // plan
-  bool use_tc = false, xvec = false; int NC = 160, nt = 1, tile_n = BN, ldw = 0, ldg = 0, ldgr = 0, splits = 1;
+  bool use_tc = false, xvec = false; int cl = 2; int NC = 160, nt = 1, tile_n = BN, ldw = 0, ldg = 0, ldgr = 0, splits = 1;
   int64_t S_max = 0, ldr_max = 0, chunk_rows = 0, rps = 0, tc_rps = 2048, tiles_total = 0; int ctx_sms = 148;
   // buffers
   float *Wt = nullptr, *bt = nullptr, *R = nullptr, *Rlo = nullptr, *Whi = nullptr, *Wlo = nullptr, *Gpart = nullptr;
@@ -349,6 +360,7 @@ struct EvalCtx {
 
   void plan(dml_ctx* ctx, int64_t n_groups_max) {
     ctx_sms = ctx->n_sms;
+    cl = ctx->tc_cluster;
     ldw = (int)rup(d, 4); ldg = (int)rup(d + 1, 4); ldgr = d + 2;
     tiles_total = cdiv(n, BM); tile_n = (BN / T) * T;
     ldr_max = rup(S_max, 4); NC = pick_nc(S_max);
@@ -388,8 +400,8 @@ struct EvalCtx {
     int rc;
     if ((rc = make_map_2d(ctx, &mXf, X, d, n, ldx * 4, 32, 128))) return rc;   // forward: 128 rows x 32 features
     if ((rc = make_map_2d(ctx, &mXg, X, d, n, ldx * 4, 32, 32, true))) return rc;    // gradient: 32 rows x 32 features
-    if ((rc = make_map_2d(ctx, &mWh, Whi, d, S_max, (uint64_t)ldw * 4, 32, NC))) return rc;
-    if ((rc = make_map_2d(ctx, &mWl, Wlo, d, S_max, (uint64_t)ldw * 4, 32, NC))) return rc;
+    if ((rc = make_map_2d(ctx, &mWh, Whi, d, S_max, (uint64_t)ldw * 4, 32, NC / cl))) return rc;
+    if ((rc = make_map_2d(ctx, &mWl, Wlo, d, S_max, (uint64_t)ldw * 4, 32, NC / cl))) return rc;
     if ((rc = make_map_2d(ctx, &mRh, R, ldr_max, chunk_rows, (uint64_t)ldr_max * 4, 32, 32, true))) return rc;
     if ((rc = make_map_2d(ctx, &mRl, Rlo, ldr_max, chunk_rows, (uint64_t)ldr_max * 4, 32, 32, true))) return rc;
     return DML_OK;
@@ -413,11 +425,11 @@ struct EvalCtx {
         fp.fold_id = fold_id; fp.hold_id = hold_id; fp.slot_sel = sel; fp.slot_val = val;
         fp.Rhi = R; fp.Rlo = Rlo; fp.ldr = (int)ldr_max; fp.lossPart = lossPart; fp.gbPart = gbPart;
         fp.mask_hi = ctx->tc_mask_hi;
-        const int64_t jobs = cdiv(rows, 128) * ncb;
-        const int grid = (int)std::min<int64_t>(jobs, ctx->n_sms);
+        const int64_t jobs = cdiv(cdiv(rows, 128), cl) * ncb;      // per cluster
+        const int grid = cl * (int)std::min<int64_t>(jobs, ctx->n_sms / cl);
         CU(cudaMemsetAsync(lossPart, 0, sizeof(double) * (size_t)grid * 4 * n_slots, st));
         CU(cudaMemsetAsync(gbPart, 0, sizeof(double) * (size_t)grid * 4 * n_slots, st));
-        int rc = launch_tc_fwd<FWD_LOGREG>(ctx, NC, grid, mXf, mWh, mWl, fp);
+        int rc = launch_tc_fwd<FWD_LOGREG>(ctx, NC, cl, grid, mXf, mWh, mWl, fp);
         if (rc) return rc;
         tc::TcGradParams gp{r0, rows, tc_rps, d, n_slots, Gpart, ldg, ctx->tc_mask_hi};
         const int splits_here = (int)cdiv(rows, tc_rps);
@@ -468,11 +480,11 @@ struct EvalCtx {
       fp.n_slots = n_slots; fp.n_col_blocks = (int)cdiv(n_slots, NC); fp.bt = bt; fp.ycls = y;
       fp.fold_id = fold_id; fp.hold_id = hold_id; fp.slot_sel = sel; fp.slot_val = val;
       fp.cntPart = cntPart; fp.mask_hi = ctx->tc_mask_hi;
-      const int64_t jobs = tiles_total * fp.n_col_blocks;
-      const int grid = (int)std::min<int64_t>(jobs, ctx->n_sms);
+      const int64_t jobs = cdiv(tiles_total, cl) * fp.n_col_blocks;
+      const int grid = cl * (int)std::min<int64_t>(jobs, ctx->n_sms / cl);
       CU(cudaMemsetAsync(cntPart, 0, sizeof(int32_t) * (size_t)grid * 4 * n_slots, st));
       tick(ctx);
-      int rc = launch_tc_fwd<FWD_SCORE_CLS>(ctx, NC, grid, mXf, mWh, mWl, fp);
+      int rc = launch_tc_fwd<FWD_SCORE_CLS>(ctx, NC, cl, grid, mXf, mWh, mWl, fp);
       tock(ctx, 1);
       ctx->total_launches += 2;
       if (rc) return rc;

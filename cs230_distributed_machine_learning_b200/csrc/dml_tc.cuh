@@ -55,6 +55,20 @@ __device__ __forceinline__ void tma_load_2d(const CUtensorMap* map, uint64_t* ba
       "cp.async.bulk.tensor.2d.shared::cluster.global.tile.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];"
       ::"r"(smem_u32(dst)), "l"(map), "r"(smem_u32(bar)), "r"(c0), "r"(c1) : "memory");
 }
+__device__ __forceinline__ void tma_load_2d_mcast(const CUtensorMap* map, uint64_t* bar, void* dst, int c0, int c1, uint16_t mask) {
+  asm volatile(
+      "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes.multicast::cluster [%0], [%1, {%3, %4}], [%2], %5;"
+      ::"r"(smem_u32(dst)), "l"(map), "r"(smem_u32(bar)), "r"(c0), "r"(c1), "h"(mask) : "memory");
+}
+__device__ __forceinline__ void umma_commit_mcast(uint64_t* bar, uint16_t mask) {
+  asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;"
+               ::"r"(smem_u32(bar)), "h"(mask) : "memory");
+}
+__device__ __forceinline__ uint32_t cluster_ctarank() { uint32_t r; asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r)); return r; }
+__device__ __forceinline__ void cluster_sync_all() {
+  asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory");
+  asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory");
+}
 __device__ __forceinline__ void tmem_alloc(uint32_t* slot, uint32_t cols) {
   asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(slot)), "r"(cols) : "memory");
   asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
@@ -114,22 +128,42 @@ __host__ __device__ constexpr uint32_t instr_desc_tf32(int M, int N, int a_mn_ma
 constexpr uint32_t kHiMask = 0xffffe000u;
 __device__ __forceinline__ float tf32_hi(float x) { return __uint_as_float(__float_as_uint(x) & kHiMask); }
 
-// split a stage buffer in place: hi <- hi & mask (optional), lo <- x - hi.  `bytes` multiple of 2048.
-__device__ __forceinline__ void split_stage(float* hi, float* lo, int bytes, int tid, int nthreads, bool mask_hi) {
-  float4* h4 = reinterpret_cast<float4*>(hi);
-  float4* l4 = reinterpret_cast<float4*>(lo);
+__device__ __forceinline__ float4 lds128(uint32_t a) {
+  float4 v;
+  asm volatile("ld.shared.v4.f32 {%0,%1,%2,%3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "r"(a));
+  return v;
+}
+__device__ __forceinline__ void sts128(uint32_t a, const float4& v) {
+  asm volatile("st.shared.v4.f32 [%0], {%1,%2,%3,%4};" ::"r"(a), "f"(v.x), "f"(v.y), "f"(v.z), "f"(v.w) : "memory");
+}
+__device__ __forceinline__ float lds32f(uint32_t a) { float v; asm volatile("ld.shared.f32 %0, [%1];" : "=f"(v) : "r"(a)); return v; }
+__device__ __forceinline__ uint32_t lds16u(uint32_t a) { uint16_t v; asm volatile("ld.shared.u16 %0, [%1];" : "=h"(v) : "r"(a)); return v; }
+
+// split a stage buffer: lo <- x - (x & mask) (and optionally hi <- x & mask).  `bytes` multiple of
+// 2048; `hi`, `lo` are shared-space addresses.  128 threads, 4 x 16 bytes in flight per thread.
+__device__ __forceinline__ void split_stage(uint32_t hi, uint32_t lo, int bytes, int tid, int nthreads, bool mask_hi) {
   const int n4 = bytes >> 4;
-  for (int i = tid; i < n4; i += nthreads) {
-    const float4 x = h4[i];
-    float4 h = make_float4(tf32_hi(x.x), tf32_hi(x.y), tf32_hi(x.z), tf32_hi(x.w));
-    l4[i] = make_float4(x.x - h.x, x.y - h.y, x.z - h.z, x.w - h.w);
-    if (mask_hi) h4[i] = h;
+  for (int i0 = tid; i0 < n4; i0 += 4 * nthreads) {
+    float4 x[4];
+#pragma unroll
+    for (int u = 0; u < 4; ++u) if (i0 + u * nthreads < n4) x[u] = lds128(hi + (i0 + u * nthreads) * 16);
+#pragma unroll
+    for (int u = 0; u < 4; ++u) {
+      const int i = i0 + u * nthreads;
+      if (i < n4) {
+        const float4 h = make_float4(tf32_hi(x[u].x), tf32_hi(x[u].y), tf32_hi(x[u].z), tf32_hi(x[u].w));
+        sts128(lo + i * 16, make_float4(x[u].x - h.x, x[u].y - h.y, x[u].z - h.z, x[u].w - h.w));
+        if (mask_hi) sts128(hi + i * 16, h);
+      }
+    }
   }
 }
 
 // ---------------------------------------------------------------- forward kernel
 constexpr int kFwdStages = 3;
-constexpr int kFwdThreads = 448;   // warp 0 TMA, warp 1 MMA, warps 2-5 operand split, warps 6-13 epilogue
+constexpr int kFwdEpiGroups = 3;    // epilogue warps per TMEM lane quadrant
+constexpr int kFwdThreads = 192 + 128 * kFwdEpiGroups;   // warp 0 TMA, warp 1 MMA, warps 2-5 operand split, then the epilogue warps
+constexpr int kMaxLabel = 128;      // fold ids 0..126 (+ hold flag) in the held-column tables
 constexpr float kLossShift = 0.693147182f;   // ln 2: per-row losses are summed as (loss - ln 2), see below
 
 struct TcFwdParams {
@@ -152,7 +186,8 @@ struct FwdSmem {
   static constexpr int kA = 128 * 128;          // 128 rows x 32 tf32
   static constexpr int kB = NC * 128;
   static constexpr int kStage = 2 * kA + 2 * kB;
-  static constexpr int kMeta = 2 * NC * 4;      // per column: bias, packed mask
+  // per column: bias; per label value: 16-bit held-column masks, one per 16-column chunk
+  static constexpr int kMeta = NC * 4 + (kMaxLabel + 2) * (NC / 16) * 2 + 64;
   static constexpr int kBytes = kFwdStages * kStage + 1024 /*align*/ + 256 /*barriers*/ + kMeta;
 };
 
@@ -178,7 +213,10 @@ __device__ __forceinline__ T bfly16(const T (&v)[16], int lane) {
 
 // Jobs are ordered column block first: every CTA walks the row tiles of one column block (W stays
 // hot in L2, per-column running sums stay in registers) and changes block at most a few times.
-template <int NC, int MODE>
+// CL = 2: the kernel runs as clusters of two CTAs that work on neighbouring row tiles of the same
+// column block; each CTA fetches half of every W chunk and TMA-multicasts it to both, which halves
+// the L2 -> SM traffic of the operand every row tile re-reads (measured bound of the CL = 1 kernel).
+template <int NC, int MODE, int CL>
 __global__ void __launch_bounds__(kFwdThreads, 1)
 tc_fwd_kernel(const __grid_constant__ CUtensorMap mapX, const __grid_constant__ CUtensorMap mapWhi,
               const __grid_constant__ CUtensorMap mapWlo, const TcFwdParams p) {
@@ -193,32 +231,41 @@ tc_fwd_kernel(const __grid_constant__ CUtensorMap mapX, const __grid_constant__ 
   uint64_t* tempty = tfull + 2;             // [2] accumulator drained
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tempty + 2);
   float* colBias = reinterpret_cast<float*>(smem + kFwdStages * L::kStage + 256);   // [NC]
-  int* colMask = reinterpret_cast<int*>(colBias + NC);                               // [NC]: sel<<8 | val, -1 = no column
+  // heldTab[v][ci] bit j: column ci*16+j holds out the rows whose label equals v (v < kMaxLabel: fold
+  // id; v = kMaxLabel + h: hold flag h), or does not exist.  A row's held columns = OR of two entries.
+  uint16_t* heldTab = reinterpret_cast<uint16_t*>(colBias + NC);                     // [kMaxLabel + 2][NC / 16]
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   constexpr uint32_t kTmemCols = (2 * NC <= 64) ? 64 : (2 * NC <= 128) ? 128 : (2 * NC <= 256) ? 256 : 512;
   static_assert(2 * NC <= 512 && NC % 16 == 0, "NC");
 
   if (warp == 0 && lane == 0) {
-    for (int s = 0; s < kFwdStages; ++s) { mbar_init(full + s, 1); mbar_init(split + s, 4); mbar_init(empty + s, 1); }
-    for (int a = 0; a < 2; ++a) { mbar_init(tfull + a, 1); mbar_init(tempty + a, 8); }
+    for (int s = 0; s < kFwdStages; ++s) { mbar_init(full + s, 1); mbar_init(split + s, 4); mbar_init(empty + s, CL); }
+    for (int a = 0; a < 2; ++a) { mbar_init(tfull + a, 1); mbar_init(tempty + a, 4 * kFwdEpiGroups); }
     fence_barrier_init();
   }
   if (warp == 1) tmem_alloc(tmem_slot, kTmemCols);
   tc_fence_before();
   __syncthreads();
+  if (CL > 1) cluster_sync_all();           // peer barriers are initialised before anyone signals them
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
 
+  // job list of this CTA: (column block, row tile); a cluster takes CL neighbouring row tiles
   const int64_t n_row_tiles = (p.rows + 127) / 128;
-  const int64_t n_jobs = n_row_tiles * p.n_col_blocks;
+  const int crank = CL > 1 ? (int)cluster_ctarank() : 0;
+  const int64_t tiles_per_cb = (n_row_tiles + CL - 1) / CL;      // per cluster member
+  const int64_t n_jobs = tiles_per_cb * p.n_col_blocks;          // jobs per cluster member stream
+  const int64_t job0 = blockIdx.x / CL, job_step = gridDim.x / CL;
+  auto job_cb = [&](int64_t job) { return (int)(job / tiles_per_cb); };
+  auto job_rt = [&](int64_t job) { return (job % tiles_per_cb) * CL + crank; };   // may be == n_row_tiles (dummy tile)
 
   if (warp == 0) {
     // ===== TMA producer =====
     if (lane == 0) {
       uint32_t it = 0;
-      for (int64_t job = blockIdx.x; job < n_jobs; job += gridDim.x) {
-        const int cb = (int)(job / n_row_tiles); const int64_t rt = job % n_row_tiles;
+      for (int64_t job = job0; job < n_jobs; job += job_step) {
+        const int cb = job_cb(job); const int64_t rt = job_rt(job);
         const int row = (int)(p.row0 + rt * 128), slot = cb * NC;
         for (int c = 0; c < p.d_chunks; ++c, ++it) {
           const int s = it % kFwdStages; const uint32_t ph = (it / kFwdStages) & 1;
@@ -226,8 +273,14 @@ tc_fwd_kernel(const __grid_constant__ CUtensorMap mapX, const __grid_constant__ 
           uint8_t* st = smem + s * L::kStage;
           mbar_expect_tx(full + s, L::kA + 2 * L::kB);
           tma_load_2d(&mapX, full + s, st, c * 32, row);
-          tma_load_2d(&mapWhi, full + s, st + 2 * L::kA, c * 32, slot);
-          tma_load_2d(&mapWlo, full + s, st + 2 * L::kA + L::kB, c * 32, slot);
+          if (CL == 1) {
+            tma_load_2d(&mapWhi, full + s, st + 2 * L::kA, c * 32, slot);
+            tma_load_2d(&mapWlo, full + s, st + 2 * L::kA + L::kB, c * 32, slot);
+          } else {
+            constexpr int kHalf = (NC / CL) * 128;               // bytes of this CTA's share of a W chunk
+            tma_load_2d_mcast(&mapWhi, full + s, st + 2 * L::kA + crank * kHalf, c * 32, slot + crank * (NC / CL), (1 << CL) - 1);
+            tma_load_2d_mcast(&mapWlo, full + s, st + 2 * L::kA + L::kB + crank * kHalf, c * 32, slot + crank * (NC / CL), (1 << CL) - 1);
+          }
         }
       }
     }
@@ -235,7 +288,7 @@ tc_fwd_kernel(const __grid_constant__ CUtensorMap mapX, const __grid_constant__ 
     // ===== MMA issuer =====
     constexpr uint32_t idesc = instr_desc_tf32(128, NC, 0, 0);
     uint32_t it = 0, tile = 0;
-    for (int64_t job = blockIdx.x; job < n_jobs; job += gridDim.x, ++tile) {
+    for (int64_t job = job0; job < n_jobs; job += job_step, ++tile) {
       const int acc = tile & 1; const uint32_t aph = (tile >> 1) & 1;
       mbar_wait(tempty + acc, aph ^ 1);
       tc_fence_after();
@@ -256,7 +309,8 @@ tc_fwd_kernel(const __grid_constant__ CUtensorMap mapX, const __grid_constant__ 
             umma_tf32(tacc, dah, dbl, idesc, 1);
             umma_tf32(tacc, dah, dbh, idesc, 1);
           }
-          umma_commit(empty + s);
+          if (CL == 1) umma_commit(empty + s);
+          else umma_commit_mcast(empty + s, (1 << CL) - 1);   // the stage is refilled by both CTAs
           if (c == p.d_chunks - 1) umma_commit(tfull + acc);
         }
         __syncwarp();
@@ -266,40 +320,42 @@ tc_fwd_kernel(const __grid_constant__ CUtensorMap mapX, const __grid_constant__ 
     // ===== operand split: X_lo = X - tf32(X) on the stage buffer as it lies =====
     const int tid = threadIdx.x - 64;
     uint32_t it = 0;
-    for (int64_t job = blockIdx.x; job < n_jobs; job += gridDim.x) {
+    for (int64_t job = job0; job < n_jobs; job += job_step) {
       for (int c = 0; c < p.d_chunks; ++c, ++it) {
         const int s = it % kFwdStages; const uint32_t ph = (it / kFwdStages) & 1;
         mbar_wait(full + s, ph);
-        float* hi = reinterpret_cast<float*>(smem + s * L::kStage);
-        split_stage(hi, hi + L::kA / 4, L::kA, tid, 128, p.mask_hi != 0);
+        const uint32_t hi = smem_u32(smem + s * L::kStage);
+        split_stage(hi, hi + L::kA, L::kA, tid, 128, p.mask_hi != 0);
         fence_proxy_async();
         __syncwarp();
         if (lane == 0) mbar_arrive(split + s);
       }
     }
   } else {
-    // ===== epilogue: thread = row of the tile (TMEM lane); two warps per lane quadrant, each
-    // taking every other 16-column chunk.  Column sums over the 32 rows of a warp are formed in
-    // fp32 (the loss shifted by ln 2 so the partial sums stay O(1)) and accumulated in fp64 across
-    // tiles; see DESIGN.md "precision" for why the loss needs this care. =====
-    const int q = warp & 3;                 // TMEM lane quadrant this warp may read
-    const int half = (warp - 6) >> 2;       // which chunks: ci % 2 == half
-    const int r = q * 32 + lane;            // row within the tile
-    const int et = threadIdx.x - 192;       // 0..255 among the epilogue threads
+    // ===== epilogue: thread = row of the tile (TMEM lane); kFwdEpiGroups warps per lane quadrant,
+    // warp group g taking the 16-column chunks g, g + G, g + 2G, ...  Column sums over the 32 rows of
+    // a warp are formed in fp32 (the loss shifted by ln 2 so the partial sums stay O(1)) and
+    // accumulated in fp64 across tiles; see DESIGN.md "precision" for why the loss needs this care. =====
+    constexpr int G = kFwdEpiGroups, NCH = NC / 16;
+    const int q = warp & 3;                 // TMEM lane quadrant this warp may read ((warp - 6) % 4 == (warp + 2) % 4)
+    const int grp = (warp - 6) >> 2;        // chunk residue of this warp
+    const int qrow = (warp & 3) * 32 + lane; // row within the tile = TMEM lane
+    const int et = threadIdx.x - 192;       // 0 .. 128*G-1 among the epilogue threads
     const int mycol = bfly_col(lane);
-    constexpr int kMy = (NC / 16 + 1) / 2;  // chunks per warp (upper bound)
+    constexpr int kMy = (NCH + G - 1) / G;  // chunks per warp (upper bound)
     double accA[kMy], accB[kMy]; int accC[kMy];
 #pragma unroll
     for (int i = 0; i < kMy; ++i) { accA[i] = 0.0; accB[i] = 0.0; accC[i] = 0; }
     int cur_cb = -1;
     const int64_t part_row = ((int64_t)blockIdx.x * 4 + q) * p.n_slots;
+    const uint32_t bias_s = smem_u32(colBias), held_s = smem_u32(heldTab);
     auto flush = [&](int cb) {
       if (cb < 0 || (lane & 1)) return;
 #pragma unroll
       for (int i = 0; i < kMy; ++i) {
-        const int ci = 2 * i + half;
+        const int ci = G * i + grp;
         const int slot = cb * NC + ci * 16 + mycol;
-        if (ci < NC / 16 && slot < p.n_slots) {
+        if (ci < NCH && slot < p.n_slots) {
           if (MODE == FWD_LOGREG) { p.lossPart[part_row + slot] = accA[i]; p.gbPart[part_row + slot] = accB[i]; }
           else if (MODE == FWD_SCORE_CLS) p.cntPart[part_row + slot] = accC[i];
           else p.ssePart[part_row + slot] = accA[i];
@@ -307,55 +363,72 @@ tc_fwd_kernel(const __grid_constant__ CUtensorMap mapX, const __grid_constant__ 
         accA[i] = 0.0; accB[i] = 0.0; accC[i] = 0;
       }
     };
+    // last chunk this warp reads of every accumulator (-1: none, arrive straight away)
+    int last_ci = -1;
+#pragma unroll
+    for (int i = 0; i < kMy; ++i) if (G * i + grp < NCH) last_ci = G * i + grp;
     uint32_t tile = 0;
-    for (int64_t job = blockIdx.x; job < n_jobs; job += gridDim.x, ++tile) {
-      const int cb = (int)(job / n_row_tiles); const int64_t rt = job % n_row_tiles;
+    for (int64_t job = job0; job < n_jobs; job += job_step, ++tile) {
+      const int cb = job_cb(job); const int64_t rt = job_rt(job);
       const int slot0 = cb * NC;
       if (cb != cur_cb) {
         flush(cur_cb);
         cur_cb = cb;
-        asm volatile("bar.sync 1, 256;" ::: "memory");     // everyone is done with the old column metadata
-        for (int c = et; c < NC; c += 256) {
-          const int slot = slot0 + c;
-          colBias[c] = slot < p.n_slots ? __ldg(p.bt + slot) : 0.f;
-          colMask[c] = slot < p.n_slots ? ((__ldg(p.slot_sel + slot) << 8) | (__ldg(p.slot_val + slot) & 0xff)) : -1;
+        asm volatile("bar.sync 1, %0;" ::"n"(128 * G) : "memory");   // everyone is done with the old column tables
+        for (int c = et; c < NC; c += 128 * G) colBias[c] = slot0 + c < p.n_slots ? __ldg(p.bt + slot0 + c) : 0.f;
+        for (int e = et; e < (kMaxLabel + 2) * NCH; e += 128 * G) {
+          const int v = e / NCH, ci = e % NCH;
+          uint32_t bits = 0;
+          for (int j = 0; j < 16; ++j) {
+            const int slot = slot0 + ci * 16 + j;
+            bool held = true;                                        // a column that does not exist holds out every row
+            if (slot < p.n_slots) {
+              const int sel = __ldg(p.slot_sel + slot), val = __ldg(p.slot_val + slot) & 0xff;
+              held = v < kMaxLabel ? (sel == 0 && val == v) : (sel == 1 && val == v - kMaxLabel);
+            }
+            bits |= (held ? 1u : 0u) << j;
+          }
+          heldTab[e] = (uint16_t)bits;
         }
-        asm volatile("bar.sync 1, 256;" ::: "memory");
+        asm volatile("bar.sync 1, %0;" ::"n"(128 * G) : "memory");
       }
-      const int64_t grow = p.row0 + rt * 128 + r;          // global row
-      const int64_t lrow = rt * 128 + r;                   // row inside the chunk
-      const bool valid = grow < p.row0 + p.rows && grow < p.n_rows_total;
-      int yv = 0, lab = 0; float yf = 0.f;
+      const int64_t grow = p.row0 + rt * 128 + qrow;       // global row
+      const bool valid = rt < n_row_tiles && grow < p.row0 + p.rows && grow < p.n_rows_total;
+      int yv = 0, fold_v = 0, hold_v = 0; float yf = 0.f;
       if (valid) {
         if (p.ycls) yv = p.ycls[grow];
         if (p.yreg) yf = p.yreg[grow];
-        lab = (int)(uint8_t)p.fold_id[grow] | ((p.hold_id ? (int)(uint8_t)p.hold_id[grow] : 0) << 8);
+        fold_v = (int)(uint8_t)p.fold_id[grow] & (kMaxLabel - 1);
+        hold_v = p.hold_id ? ((int)(uint8_t)p.hold_id[grow] & 1) : 0;
       }
       const float yy = (float)yv;
+      const uint32_t held_f = held_s + fold_v * NCH * 2, held_h = held_s + (kMaxLabel + hold_v) * NCH * 2;
       const int acc = tile & 1; const uint32_t aph = (tile >> 1) & 1;
       mbar_wait(tfull + acc, aph);
       tc_fence_after();
       const uint32_t tacc = tmem_base + acc * NC + ((uint32_t)(q * 32) << 16);
+      if (last_ci < 0) { tc_fence_before(); __syncwarp(); if (lane == 0) mbar_arrive(tempty + acc); }
 #pragma unroll
       for (int i = 0; i < kMy; ++i) {
-        const int ci = 2 * i + half;
-        if (ci >= NC / 16) break;
+        const int ci = G * i + grp;
+        if (ci >= NCH) break;
         const int c0 = ci * 16;
         uint32_t v[16];
         tmem_ld16(tacc + c0, v);
         tmem_ld_wait();
-        if (i == kMy - 1 || ci + 2 >= NC / 16) {   // this warp's last read of the accumulator
+        if (ci == last_ci) {                 // this warp's last read of the accumulator
           tc_fence_before();
           __syncwarp();
           if (lane == 0) mbar_arrive(tempty + acc);
         }
+        // bit j set: column c0 + j does not train on (LOGREG) / is scored on (SCORE) this row
+        const uint32_t heldbits = valid ? (lds16u(held_f + ci * 2) | lds16u(held_h + ci * 2)) : 0xffffu;
         if (MODE == FWD_LOGREG) {
           float ls[16], rs[16], rl[16];
 #pragma unroll
           for (int j = 0; j < 16; ++j) {
-            const int m = colMask[c0 + j];
-            const bool train = valid && m >= 0 && ((lab >> (8 * (m >> 8))) & 0xff) != (m & 0xff);
-            const float z = __uint_as_float(v[j]) + colBias[c0 + j];
+            const bool train = !((heldbits >> j) & 1u);
+            const float z = __uint_as_float(v[j]) + lds32f(bias_s + (c0 + j) * 4);
             const float e = __expf(-fabsf(z));
             const float inv = __fdividef(1.f, 1.f + e);
             const float pr = z >= 0.f ? inv : e * inv;
@@ -378,21 +451,21 @@ tc_fwd_kernel(const __grid_constant__ CUtensorMap mapX, const __grid_constant__ 
                 if (o1) rs[8 * c1 + e] = rcv; else rs[8 * c1 + 4 + e] = rcv;
               }
 #pragma unroll
-            for (int c0 = 0; c0 < 2; ++c0)
+            for (int cc = 0; cc < 2; ++cc)
 #pragma unroll
               for (int e = 0; e < 4; ++e) {
-                const float snd = o2 ? rs[4 * c0 + e] : rs[4 * c0 + 8 + e];
+                const float snd = o2 ? rs[4 * cc + e] : rs[4 * cc + 8 + e];
                 const float rcv = __shfl_xor_sync(0xffffffffu, snd, 2);
-                if (o2) rs[4 * c0 + e] = rcv; else rs[4 * c0 + 8 + e] = rcv;
+                if (o2) rs[4 * cc + e] = rcv; else rs[4 * cc + 8 + e] = rcv;
               }
           }
 #pragma unroll
           for (int j = 0; j < 16; ++j) { const float h = tf32_hi(rs[j]); rl[j] = rs[j] - h; rs[j] = h; }
-          const int tq = lane & 3;                              // which float4 of the 16-column chunk
-          const int64_t lrow4 = rt * 128 + q * 32 + (lane & ~3); // first row of this lane group
-          if (slot0 + c0 + 4 * tq < p.ldr) {
+          const int tq = lane & 3;                                // which float4 of the 16-column chunk
+          const int64_t lrow4 = rt * 128 + q * 32 + (lane & ~3);   // first row of this lane group
+          if (rt < n_row_tiles && slot0 + c0 + 4 * tq < p.ldr) {
 #pragma unroll
-            for (int j = 0; j < 4; ++j) {                       // j = row inside the group
+            for (int j = 0; j < 4; ++j) {                         // j = row inside the group
               const int64_t o = (lrow4 + j) * p.ldr + slot0 + c0 + 4 * tq;
               *reinterpret_cast<float4*>(p.Rhi + o) = make_float4(rs[4 * j], rs[4 * j + 1], rs[4 * j + 2], rs[4 * j + 3]);
               *reinterpret_cast<float4*>(p.Rlo + o) = make_float4(rl[4 * j], rl[4 * j + 1], rl[4 * j + 2], rl[4 * j + 3]);
@@ -402,9 +475,8 @@ tc_fwd_kernel(const __grid_constant__ CUtensorMap mapX, const __grid_constant__ 
           int ok[16];
 #pragma unroll
           for (int j = 0; j < 16; ++j) {
-            const int m = colMask[c0 + j];
-            const bool held = valid && m >= 0 && ((lab >> (8 * (m >> 8))) & 0xff) == (m & 0xff);
-            const float z = __uint_as_float(v[j]) + colBias[c0 + j];
+            const bool held = valid && ((heldbits >> j) & 1u) && slot0 + c0 + j < p.n_slots;
+            const float z = __uint_as_float(v[j]) + lds32f(bias_s + (c0 + j) * 4);
             ok[j] = (held && (((z > 0.f) ? 1 : 0) == yv)) ? 1 : 0;
           }
           accC[i] += bfly16(ok, lane);
@@ -412,9 +484,8 @@ tc_fwd_kernel(const __grid_constant__ CUtensorMap mapX, const __grid_constant__ 
           float se[16];
 #pragma unroll
           for (int j = 0; j < 16; ++j) {
-            const int m = colMask[c0 + j];
-            const bool held = valid && m >= 0 && ((lab >> (8 * (m >> 8))) & 0xff) == (m & 0xff);
-            const float e = yf - (__uint_as_float(v[j]) + colBias[c0 + j]);
+            const bool held = valid && ((heldbits >> j) & 1u) && slot0 + c0 + j < p.n_slots;
+            const float e = yf - (__uint_as_float(v[j]) + lds32f(bias_s + (c0 + j) * 4));
             se[j] = held ? e * e : 0.f;
           }
           accA[i] += (double)bfly16(se, lane);
@@ -425,6 +496,7 @@ tc_fwd_kernel(const __grid_constant__ CUtensorMap mapX, const __grid_constant__ 
   }
   tc_fence_before();
   __syncthreads();
+  if (CL > 1) cluster_sync_all();           // no CTA leaves while its peer may still write into it
   if (warp == 1) tmem_dealloc(tmem_base, kTmemCols);
 }
 
@@ -546,8 +618,8 @@ tc_grad_kernel(const __grid_constant__ CUtensorMap mapX, const __grid_constant__
     for (int it = 0; it < n_stages; ++it) {
       const int s = it % kGradStages; const uint32_t ph = (it / kGradStages) & 1;
       mbar_wait(full + s, ph);
-      float* hi = reinterpret_cast<float*>(smem + s * L::kStage);
-      split_stage(hi, hi + L::kA / 4, L::kA, tid, 128, p.mask_hi != 0);
+      const uint32_t hi = smem_u32(smem + s * L::kStage);
+      split_stage(hi, hi + L::kA, L::kA, tid, 128, p.mask_hi != 0);
       fence_proxy_async();
       __syncwarp();
       if (lane == 0) mbar_arrive(split + s);
