@@ -56,6 +56,7 @@ struct dml_ctx {
   cudaEvent_t ev_total[2] = {nullptr, nullptr};
   float total_ms = 0.f, contraction_ms = 0.f; int contraction_launches = 0, total_launches = 0;
   size_t r_budget = (size_t)4 << 30;  // bytes of residual scratch per row chunk
+  int tc_prefetch = 1, tc_prefetch_grad = 8;  // L2 prefetch distances (jobs / stages), 0 = off
   int tc_cluster = 2;                 // CTAs per cluster in the forward kernel (W multicast): 1 or 2
   int tc_mask_hi = 0;                 // 1 = write the masked hi operand back before the MMAs read it (not needed:
                                       // kind::tf32 ignores the 13 low mantissa bits, measured identical results)
@@ -152,6 +153,8 @@ extern "C" int dml_ctx_create(int device, void* stream, dml_ctx** out) {
   ctx = new dml_ctx();
   ctx->device = device; ctx->stream = (cudaStream_t)stream; ctx->n_sms = prop.multiProcessorCount;
   if (const char* e = getenv("DML_TC_MASK_HI")) ctx->tc_mask_hi = atoi(e);
+  if (const char* e = getenv("DML_TC_PREFETCH")) ctx->tc_prefetch = atoi(e);
+  if (const char* e = getenv("DML_TC_PREFETCH_GRAD")) ctx->tc_prefetch_grad = atoi(e);
   if (const char* e = getenv("DML_TC_CLUSTER")) ctx->tc_cluster = atoi(e) == 1 ? 1 : 2;
   CU(cudaSetDevice(device));
   CU(cudaHostAlloc(&ctx->h_scalar, 64, cudaHostAllocDefault));
@@ -424,14 +427,14 @@ struct EvalCtx {
         fp.n_slots = n_slots; fp.n_col_blocks = ncb; fp.bt = bt; fp.ycls = y; fp.yreg = nullptr;
         fp.fold_id = fold_id; fp.hold_id = hold_id; fp.slot_sel = sel; fp.slot_val = val;
         fp.Rhi = R; fp.Rlo = Rlo; fp.ldr = (int)ldr_max; fp.lossPart = lossPart; fp.gbPart = gbPart;
-        fp.mask_hi = ctx->tc_mask_hi;
+        fp.mask_hi = ctx->tc_mask_hi; fp.prefetch_jobs = ctx->tc_prefetch;
         const int64_t jobs = cdiv(cdiv(rows, 128), cl) * ncb;      // per cluster
         const int grid = cl * (int)std::min<int64_t>(jobs, ctx->n_sms / cl);
         CU(cudaMemsetAsync(lossPart, 0, sizeof(double) * (size_t)grid * 4 * n_slots, st));
         CU(cudaMemsetAsync(gbPart, 0, sizeof(double) * (size_t)grid * 4 * n_slots, st));
         int rc = launch_tc_fwd<FWD_LOGREG>(ctx, NC, cl, grid, mXf, mWh, mWl, fp);
         if (rc) return rc;
-        tc::TcGradParams gp{r0, rows, tc_rps, d, n_slots, Gpart, ldg, ctx->tc_mask_hi};
+        tc::TcGradParams gp{r0, rows, tc_rps, d, n_slots, Gpart, ldg, ctx->tc_mask_hi, ctx->tc_prefetch_grad};
         const int splits_here = (int)cdiv(rows, tc_rps);
         rc = launch_tc_grad(ctx, NC, dim3((unsigned)cdiv(d, 128), (unsigned)ncb, (unsigned)splits_here), mXg, mRh, mRl, gp);
         if (rc) return rc;
@@ -479,7 +482,7 @@ struct EvalCtx {
       fp.n_rows_total = n; fp.row0 = 0; fp.rows = n; fp.d_chunks = (int)cdiv(d, 32);
       fp.n_slots = n_slots; fp.n_col_blocks = (int)cdiv(n_slots, NC); fp.bt = bt; fp.ycls = y;
       fp.fold_id = fold_id; fp.hold_id = hold_id; fp.slot_sel = sel; fp.slot_val = val;
-      fp.cntPart = cntPart; fp.mask_hi = ctx->tc_mask_hi;
+      fp.cntPart = cntPart; fp.mask_hi = ctx->tc_mask_hi; fp.prefetch_jobs = ctx->tc_prefetch;
       const int64_t jobs = cdiv(tiles_total, cl) * fp.n_col_blocks;
       const int grid = cl * (int)std::min<int64_t>(jobs, ctx->n_sms / cl);
       CU(cudaMemsetAsync(cntPart, 0, sizeof(int32_t) * (size_t)grid * 4 * n_slots, st));
