@@ -56,7 +56,7 @@ struct dml_ctx {
   cudaEvent_t ev_total[2] = {nullptr, nullptr};
   float total_ms = 0.f, contraction_ms = 0.f; int contraction_launches = 0, total_launches = 0;
   size_t r_budget = (size_t)4 << 30;  // bytes of residual scratch per row chunk
-  int tc_prefetch = 1, tc_prefetch_grad = 8;  // L2 prefetch distances (jobs / stages), 0 = off
+  int tc_prefetch = 0, tc_prefetch_grad = 0;  // L2 prefetch distance of the forward X tiles in jobs (0 = off; measured: no gain, the ring is not latency-bound)
   int tc_cluster = 2;                 // CTAs per cluster in the forward kernel (W multicast): 1 or 2
   int tc_mask_hi = 0;                 // 1 = write the masked hi operand back before the MMAs read it (not needed:
                                       // kind::tf32 ignores the 13 low mantissa bits, measured identical results)
@@ -258,6 +258,25 @@ static int make_map_2d(dml_ctx* ctx, CUtensorMap* m, const void* base, uint64_t 
                                      (unsigned long long)stride_bytes, box_inner, box_outer);
   return DML_OK;
 }
+// 3-D view of a row-major fp32 matrix [rows][ld] as (32 columns, row, 32-column chunk): a box of
+// (32, box_rows, box_chunks) lands in shared memory as [chunk][row][128 B], which is the MN-major
+// operand layout of the gradient kernel.  Columns past `cols` read as zero.
+static int make_map_chunked(dml_ctx* ctx, CUtensorMap* m, const void* base, uint64_t cols, uint64_t rows,
+                            uint64_t stride_bytes, uint32_t box_rows, uint32_t box_chunks) {
+  if (!g_encode) { CUtensorMap tmp; int rc = make_map_2d(ctx, &tmp, base, 32, 1, 128, 32, 1); (void)rc; }
+  if (!g_encode) return fail(ctx, DML_ERR_CUDA, "cuTensorMapEncodeTiled not available");
+  // the chunk dimension cannot clip inside a chunk, so the column extent is rounded up to a chunk;
+  // the caller guarantees that the memory behind it is readable (row pitch >= rounded extent) and zero
+  cuuint64_t gdim[3] = {32, rows, (cols + 31) / 32};
+  cuuint64_t gstr[2] = {stride_bytes, 128};
+  cuuint32_t box[3] = {32, box_rows, box_chunks};
+  cuuint32_t est[3] = {1, 1, 1};
+  const CUresult r = g_encode(m, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 3, const_cast<void*>(base), gdim, gstr, box, est,
+                              CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B_ATOM_32B,
+                              CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) return fail(ctx, DML_ERR_CUDA, "cuTensorMapEncodeTiled(3d) failed (%d)", (int)r);
+  return DML_OK;
+}
 // column-block width: the candidate with the least padding, larger on ties
 static int pick_nc(int64_t n_slots) {
   const int cand[5] = {160, 128, 96, 64, 32};
@@ -366,7 +385,8 @@ struct EvalCtx {
     cl = ctx->tc_cluster;
     ldw = (int)rup(d, 4); ldg = (int)rup(d + 1, 4); ldgr = d + 2;
     tiles_total = cdiv(n, BM); tile_n = (BN / T) * T;
-    ldr_max = rup(S_max, 4); NC = pick_nc(S_max);
+    NC = pick_nc(S_max);
+    ldr_max = use_tc ? cdiv(S_max, NC) * NC : rup(S_max, 4);   // tcgen05: whole column blocks, so 32-column chunks stay inside a row
     // row chunk so that the residual scratch stays within budget
     chunk_rows = std::max<int64_t>(BM, (int64_t)(ctx->r_budget / (ldr_max * (use_tc ? 8 : 4))) / BM * BM);
     chunk_rows = std::min<int64_t>(chunk_rows, rup(n, BM));
@@ -405,8 +425,8 @@ struct EvalCtx {
     if ((rc = make_map_2d(ctx, &mXg, X, d, n, ldx * 4, 32, 32, true))) return rc;    // gradient: 32 rows x 32 features
     if ((rc = make_map_2d(ctx, &mWh, Whi, d, S_max, (uint64_t)ldw * 4, 32, NC / cl))) return rc;
     if ((rc = make_map_2d(ctx, &mWl, Wlo, d, S_max, (uint64_t)ldw * 4, 32, NC / cl))) return rc;
-    if ((rc = make_map_2d(ctx, &mRh, R, ldr_max, chunk_rows, (uint64_t)ldr_max * 4, 32, 32, true))) return rc;
-    if ((rc = make_map_2d(ctx, &mRl, Rlo, ldr_max, chunk_rows, (uint64_t)ldr_max * 4, 32, 32, true))) return rc;
+    if ((rc = make_map_chunked(ctx, &mRh, R, ldr_max, chunk_rows, (uint64_t)ldr_max * 4, 32, NC / 32))) return rc;
+    if ((rc = make_map_chunked(ctx, &mRl, Rlo, ldr_max, chunk_rows, (uint64_t)ldr_max * 4, 32, NC / 32))) return rc;
     return DML_OK;
   }
   // Gred[slot] = [sum r x (d), sum r, sum loss] over the training rows of each column

@@ -55,6 +55,11 @@ __device__ __forceinline__ void tma_load_2d(const CUtensorMap* map, uint64_t* ba
       "cp.async.bulk.tensor.2d.shared::cluster.global.tile.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];"
       ::"r"(smem_u32(dst)), "l"(map), "r"(smem_u32(bar)), "r"(c0), "r"(c1) : "memory");
 }
+__device__ __forceinline__ void tma_load_3d(const CUtensorMap* map, uint64_t* bar, void* dst, int c0, int c1, int c2) {
+  asm volatile(
+      "cp.async.bulk.tensor.3d.shared::cluster.global.tile.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5}], [%2];"
+      ::"r"(smem_u32(dst)), "l"(map), "r"(smem_u32(bar)), "r"(c0), "r"(c1), "r"(c2) : "memory");
+}
 __device__ __forceinline__ void tma_prefetch_2d(const CUtensorMap* map, int c0, int c1) {
   asm volatile("cp.async.bulk.prefetch.tensor.2d.L2.global.tile [%0, {%1, %2}];" ::"l"(map), "r"(c0), "r"(c1) : "memory");
 }
@@ -183,7 +188,7 @@ __device__ __forceinline__ void split_stage(uint32_t hi, uint32_t lo, int bytes,
 
 // ---------------------------------------------------------------- forward kernel
 constexpr int kFwdStages = 3;
-constexpr int kFwdEpiGroups = 3;    // epilogue warps per TMEM lane quadrant
+constexpr int kFwdEpiGroups = 4;    // epilogue warps per TMEM lane quadrant
 // warps 0-3 operand staging, 4 .. 4+4G-1 epilogue, then the TMA producer and the MMA issuer: the SM's warp
 // arbiter favours the highest warp id, and the two single-thread roles must never wait behind the math warps
 constexpr int kFwdThreads = 192 + 128 * kFwdEpiGroups;
@@ -624,23 +629,12 @@ tc_grad_kernel(const __grid_constant__ CUtensorMap mapX, const __grid_constant__
         mbar_expect_tx(full + s, L::kA + 2 * L::kB);
         const int lr = (int)(kb + (int64_t)it * 32);          // row inside the chunk (R)
         const int xr = (int)(p.row0_x + lr);                   // row inside X
-        if (p.prefetch_stages > 0 && it + p.prefetch_stages < n_stages) {
-          const int plr = lr + 32 * p.prefetch_stages;
-#pragma unroll
-          for (int b = 0; b < 4; ++b) tma_prefetch_2d(&mapX, jb * 128 + b * 32, (int)(p.row0_x + plr));
-#pragma unroll
-          for (int b = 0; b < NC / 32; ++b) {
-            tma_prefetch_2d(&mapRhi, cb * NC + b * 32, plr);
-            tma_prefetch_2d(&mapRlo, cb * NC + b * 32, plr);
-          }
-        }
+        // X: four boxes of 32 rows x 32 features (a 2-D map clips at d); R: 3-D view (32 columns, row,
+        // 32-column chunk), one instruction lands [chunk][32 rows][128 B]
 #pragma unroll
         for (int b = 0; b < 4; ++b) tma_load_2d(&mapX, full + s, st + b * 4096, jb * 128 + b * 32, xr);
-#pragma unroll
-        for (int b = 0; b < NC / 32; ++b) {
-          tma_load_2d(&mapRhi, full + s, st + L::kA + b * 4096, cb * NC + b * 32, lr);
-          tma_load_2d(&mapRlo, full + s, st + L::kA + L::kB + b * 4096, cb * NC + b * 32, lr);
-        }
+        tma_load_3d(&mapRhi, full + s, st + L::kA, 0, lr, cb * (NC / 32));
+        tma_load_3d(&mapRlo, full + s, st + L::kA + L::kB, 0, lr, cb * (NC / 32));
       }
     }
   } else if (warp == 9) {
