@@ -278,13 +278,21 @@ static int make_map_chunked(dml_ctx* ctx, CUtensorMap* m, const void* base, uint
   return DML_OK;
 }
 // column-block width: the candidate with the least padding, larger on ties
-static int pick_nc(int64_t n_slots) {
+// (a fit's T columns never straddle a block, so the width must be a multiple of T); 0 = none fits
+static int pick_nc(int64_t n_slots, int T = 1) {
   const int cand[5] = {160, 128, 96, 64, 32};
-  int best = 160; int64_t best_pad = INT64_MAX;
-  for (int c : cand) { const int64_t pad = cdiv(n_slots, c) * c; if (pad < best_pad) { best_pad = pad; best = c; } }
+  int best = 0; int64_t best_pad = INT64_MAX;
+  for (int c : cand) {
+    if (c % T || (T > 1 && c / T > 32)) continue;   // at most 32 fits per column block (epilogue registers)
+    const int64_t pad = cdiv(n_slots, c) * c;
+    if (pad < best_pad) { best_pad = pad; best = c; }
+  }
   return best;
 }
-static bool tc_eligible(const float* X, int64_t ldx, int T) { return T == 1 && ldx % 4 == 0 && aligned16(X); }
+// tcgen05 path: TMA needs 16-byte aligned rows; multinomial fits need a block width divisible by T <= 16
+static bool tc_eligible(const float* X, int64_t ldx, int T) {
+  return ldx % 4 == 0 && aligned16(X) && (T == 1 || (T >= 3 && T <= 16 && pick_nc(1, T) != 0));
+}
 
 template <int NC, int MODE, int CL>
 static int launch_tc_fwd_nc(dml_ctx* ctx, int grid, const CUtensorMap& mx, const CUtensorMap& mwh, const CUtensorMap& mwl,
@@ -379,13 +387,15 @@ struct EvalCtx {
   double *lossPart = nullptr, *gbPart = nullptr, *Gred = nullptr; int32_t *sel = nullptr, *val = nullptr, *cntPart = nullptr;
   CUtensorMap mXf, mXg, mWh, mWl, mRh, mRl;
   unsigned long long* hist_local = nullptr;   // [512] label histogram of this rank's rows
+  // the forward kernel sums (loss - shift) with shift = loss of the zero model: ln 2, or ln T (multinomial)
+  float loss_shift() const { return T == 1 ? 0.693147182f : logf((float)T); }
 
   void plan(dml_ctx* ctx, int64_t n_groups_max) {
     ctx_sms = ctx->n_sms;
     cl = ctx->tc_cluster;
     ldw = (int)rup(d, 4); ldg = (int)rup(d + 1, 4); ldgr = d + 2;
     tiles_total = cdiv(n, BM); tile_n = (BN / T) * T;
-    NC = pick_nc(S_max);
+    NC = pick_nc(S_max, T); if (NC == 0) NC = 160;
     ldr_max = use_tc ? cdiv(S_max, NC) * NC : rup(S_max, 4);   // tcgen05: whole column blocks, so 32-column chunks stay inside a row
     // row chunk so that the residual scratch stays within budget
     chunk_rows = std::max<int64_t>(BM, (int64_t)(ctx->r_budget / (ldr_max * (use_tc ? 8 : 4))) / BM * BM);
@@ -447,12 +457,13 @@ struct EvalCtx {
         fp.n_slots = n_slots; fp.n_col_blocks = ncb; fp.bt = bt; fp.ycls = y; fp.yreg = nullptr;
         fp.fold_id = fold_id; fp.hold_id = hold_id; fp.slot_sel = sel; fp.slot_val = val;
         fp.Rhi = R; fp.Rlo = Rlo; fp.ldr = (int)ldr_max; fp.lossPart = lossPart; fp.gbPart = gbPart;
-        fp.mask_hi = ctx->tc_mask_hi; fp.prefetch_jobs = ctx->tc_prefetch;
+        fp.mask_hi = ctx->tc_mask_hi; fp.prefetch_jobs = ctx->tc_prefetch; fp.T = T; fp.loss_shift = loss_shift();
         const int64_t jobs = cdiv(cdiv(rows, 128), cl) * ncb;      // per cluster
         const int grid = cl * (int)std::min<int64_t>(jobs, ctx->n_sms / cl);
         CU(cudaMemsetAsync(lossPart, 0, sizeof(double) * (size_t)grid * 4 * n_slots, st));
         CU(cudaMemsetAsync(gbPart, 0, sizeof(double) * (size_t)grid * 4 * n_slots, st));
-        int rc = launch_tc_fwd<FWD_LOGREG>(ctx, NC, cl, grid, mXf, mWh, mWl, fp);
+        int rc = T == 1 ? launch_tc_fwd<FWD_LOGREG>(ctx, NC, cl, grid, mXf, mWh, mWl, fp)
+                        : launch_tc_fwd<tc::FWD_LOGREG_MULTI>(ctx, NC, cl, grid, mXf, mWh, mWl, fp);
         if (rc) return rc;
         tc::TcGradParams gp{r0, rows, tc_rps, d, n_slots, Gpart, ldg, ctx->tc_mask_hi, ctx->tc_prefetch_grad};
         const int splits_here = (int)cdiv(rows, tc_rps);
@@ -461,7 +472,7 @@ struct EvalCtx {
         ReduceParams rp{Gpart, ldg, splits_here, n_slots, d, T, d, nullptr, 0, 0, Gred, ldgr, ci > 0 ? 1 : 0};
         reduce_grad_kernel<<<n_slots, 256, 0, st>>>(rp);
         tc::TcReduceParams tr{lossPart, gbPart, (int64_t)grid * 4, n_slots, T, d, Gred, ldgr, ci > 0 ? 1 : 0,
-                              hist_local, sel, val, n};
+                              hist_local, sel, val, n, (double)loss_shift()};
         tc::tc_reduce_tiles_kernel<<<(unsigned)cdiv(n_slots, 32), dim3(32, 8), 0, st>>>(tr);
       } else {
         const int ldr = (int)rup(n_slots, 4);
@@ -502,12 +513,13 @@ struct EvalCtx {
       fp.n_rows_total = n; fp.row0 = 0; fp.rows = n; fp.d_chunks = (int)cdiv(d, 32);
       fp.n_slots = n_slots; fp.n_col_blocks = (int)cdiv(n_slots, NC); fp.bt = bt; fp.ycls = y;
       fp.fold_id = fold_id; fp.hold_id = hold_id; fp.slot_sel = sel; fp.slot_val = val;
-      fp.cntPart = cntPart; fp.mask_hi = ctx->tc_mask_hi; fp.prefetch_jobs = ctx->tc_prefetch;
+      fp.cntPart = cntPart; fp.mask_hi = ctx->tc_mask_hi; fp.prefetch_jobs = ctx->tc_prefetch; fp.T = T; fp.loss_shift = 0.f;
       const int64_t jobs = cdiv(tiles_total, cl) * fp.n_col_blocks;
       const int grid = cl * (int)std::min<int64_t>(jobs, ctx->n_sms / cl);
       CU(cudaMemsetAsync(cntPart, 0, sizeof(int32_t) * (size_t)grid * 4 * n_slots, st));
       tick(ctx);
-      int rc = launch_tc_fwd<FWD_SCORE_CLS>(ctx, NC, cl, grid, mXf, mWh, mWl, fp);
+      int rc = T == 1 ? launch_tc_fwd<FWD_SCORE_CLS>(ctx, NC, cl, grid, mXf, mWh, mWl, fp)
+                      : launch_tc_fwd<tc::FWD_SCORE_MULTI>(ctx, NC, cl, grid, mXf, mWh, mWl, fp);
       tock(ctx, 1);
       ctx->total_launches += 2;
       if (rc) return rc;

@@ -194,7 +194,6 @@ constexpr int kFwdEpiGroups = 4;    // epilogue warps per TMEM lane quadrant
 constexpr int kFwdThreads = 192 + 128 * kFwdEpiGroups;
 constexpr int kFwdTmaWarp = 4 + 4 * kFwdEpiGroups, kFwdMmaWarp = kFwdTmaWarp + 1;
 constexpr int kMaxLabel = 128;      // fold ids 0..126 (+ hold flag) in the held-column tables
-constexpr float kLossShift = 0.693147182f;   // ln 2: per-row losses are summed as (loss - ln 2), see below
 
 struct TcFwdParams {
   int64_t n_rows_total;      // rows of X visible through the tensor map (for masking the last tile)
@@ -210,7 +209,10 @@ struct TcFwdParams {
   int32_t* cntPart; double* ssePart;     // score modes, same shape
   int mask_hi;
   int prefetch_jobs;                     // L2 prefetch distance of the X tiles, in jobs of this CTA (0 = off)
+  int T;                                 // columns per fit (1 = binary; multinomial modes: classes, <= 16)
+  float loss_shift;                      // per-row losses are summed as (loss - loss_shift): ln 2, or ln T
 };
+enum { FWD_LOGREG_MULTI = 3, FWD_SCORE_MULTI = 4 };   // softmax / arg-max over T consecutive columns
 
 template <int NC>
 struct FwdSmem {
@@ -385,6 +387,125 @@ tc_fwd_kernel(const __grid_constant__ CUtensorMap mapX, const __grid_constant__ 
       }
     }
   } else {
+    if constexpr (MODE == FWD_LOGREG_MULTI || MODE == FWD_SCORE_MULTI) {
+      // ===== multinomial epilogue: a fit owns T consecutive columns; warp group g takes the fits
+      // g, g + G, ... of the column block; thread = row.  softmax / first arg-max over the T columns. =====
+      constexpr int G = kFwdEpiGroups;
+      constexpr int kMyF = 32 / G;                          // fits per warp: the host only picks NC / T <= 32
+      const int T = p.T, nfit = NC / T;
+      const int q = warp & 3, grp = (warp - 4) >> 2;
+      const int qrow = q * 32 + lane;
+      const int et = threadIdx.x - 128;
+      const int mycol = bfly_col(lane);
+      double accA[kMyF], accB[kMyF]; int accC[kMyF];
+#pragma unroll
+      for (int i = 0; i < kMyF; ++i) { accA[i] = 0.0; accB[i] = 0.0; accC[i] = 0; }
+      int cur_cb = -1;
+      const int64_t part_row = ((int64_t)blockIdx.x * 4 + q) * p.n_slots;
+      const uint32_t bias_s = smem_u32(colBias), held_s = smem_u32(heldTab);
+      constexpr int NCH = NC / 16;
+      auto flush = [&](int cb) {
+        if (cb < 0) return;
+#pragma unroll
+        for (int i = 0; i < kMyF; ++i) {
+          const int f = G * i + grp;
+          const int slot = cb * NC + f * T;
+          if (f < nfit && slot < p.n_slots) {
+            if (MODE == FWD_LOGREG_MULTI) {
+              if (lane == 0) p.lossPart[part_row + slot] = accA[i];
+              if (!(lane & 1) && mycol < T) p.gbPart[part_row + slot + mycol] = accB[i];
+            } else if (lane == 0) p.cntPart[part_row + slot] = accC[i];
+          }
+          accA[i] = 0.0; accB[i] = 0.0; accC[i] = 0;
+        }
+      };
+      int last_f = -1;
+      for (int i = 0; i < kMyF; ++i) if (G * i + grp < nfit) last_f = G * i + grp;
+      uint32_t tile = 0;
+      for (int64_t job = job0; job < n_jobs; job += job_step, ++tile) {
+        const int cb = job_cb(job); const int64_t rt = job_rt(job);
+        const int slot0 = cb * NC;
+        if (cb != cur_cb) {
+          flush(cur_cb);
+          cur_cb = cb;
+          asm volatile("bar.sync 1, %0;" ::"n"(128 * G) : "memory");
+          for (int c = et; c < NC; c += 128 * G) colBias[c] = slot0 + c < p.n_slots ? __ldg(p.bt + slot0 + c) : 0.f;
+          for (int e = et; e < (kMaxLabel + 2) * NCH; e += 128 * G) {
+            const int v = e / NCH, ci = e % NCH;
+            uint32_t bits = 0;
+            for (int j = 0; j < 16; ++j) {
+              const int slot = slot0 + ci * 16 + j;
+              bool held = true;
+              if (slot < p.n_slots) {
+                const int sel = __ldg(p.slot_sel + slot), val = __ldg(p.slot_val + slot) & 0xff;
+                held = v < kMaxLabel ? (sel == 0 && val == v) : (sel == 1 && val == v - kMaxLabel);
+              }
+              bits |= (held ? 1u : 0u) << j;
+            }
+            heldTab[e] = (uint16_t)bits;
+          }
+          asm volatile("bar.sync 1, %0;" ::"n"(128 * G) : "memory");
+        }
+        const int64_t grow = p.row0 + rt * 128 + qrow;
+        const int64_t lrow = rt * 128 + qrow;
+        const bool valid = rt < n_row_tiles && grow < p.row0 + p.rows && grow < p.n_rows_total;
+        int yv = 0, fold_v = 0, hold_v = 0;
+        if (valid) {
+          yv = p.ycls[grow];
+          fold_v = (int)(uint8_t)p.fold_id[grow] & (kMaxLabel - 1);
+          hold_v = p.hold_id ? ((int)(uint8_t)p.hold_id[grow] & 1) : 0;
+        }
+        const uint32_t held_f = held_s + fold_v * NCH * 2, held_h = held_s + (kMaxLabel + hold_v) * NCH * 2;
+        const int acc = tile & 1; const uint32_t aph = (tile >> 1) & 1;
+        mbar_wait(tfull + acc, aph);
+        tc_fence_after();
+        const uint32_t tacc = tmem_base + acc * NC + ((uint32_t)(q * 32) << 16);
+        if (last_f < 0) { tc_fence_before(); __syncwarp(); if (lane == 0) mbar_arrive(tempty + acc); }
+#pragma unroll
+        for (int i = 0; i < kMyF; ++i) {
+          const int f = G * i + grp;
+          if (f >= nfit) break;
+          const int c0 = f * T;
+          uint32_t v[16];
+          tmem_ld16(tacc + c0, v);           // T <= 16 columns of this fit (the tail of the vector is ignored)
+          tmem_ld_wait();
+          if (f == last_f) { tc_fence_before(); __syncwarp(); if (lane == 0) mbar_arrive(tempty + acc); }
+          const uint32_t hb = valid ? (lds16u(held_f + (c0 >> 4) * 2) | lds16u(held_h + (c0 >> 4) * 2)) : 0xffffu;
+          const bool held = (hb >> (c0 & 15)) & 1u;
+          const bool exists = slot0 + c0 < p.n_slots;
+          float z[16];
+          float m = -INFINITY; int am = 0;
+#pragma unroll
+          for (int c = 0; c < 16; ++c) {
+            z[c] = c < T ? __uint_as_float(v[c]) + lds32f(bias_s + (c0 + c) * 4) : -INFINITY;
+            if (z[c] > m) { m = z[c]; am = c; }
+          }
+          if (MODE == FWD_SCORE_MULTI) {
+            const int ok = (valid && held && exists && am == yv) ? 1 : 0;
+            accC[i] += __popc(__ballot_sync(0xffffffffu, ok));
+          } else {
+            const bool train = valid && !held && exists;
+            float ssum = 0.f, zy = 0.f, rs[16];
+#pragma unroll
+            for (int c = 0; c < 16; ++c) { rs[c] = c < T ? __expf(z[c] - m) : 0.f; ssum += rs[c]; if (c == yv) zy = z[c]; }
+            const float inv = __fdividef(1.f, ssum);
+            const float loss = train ? (__logf(ssum) + m - zy) - p.loss_shift : 0.f;
+#pragma unroll
+            for (int c = 0; c < 16; ++c) rs[c] = (train && c < T) ? rs[c] * inv - (c == yv ? 1.f : 0.f) : 0.f;
+            accA[i] += (double)warp_sum(loss);
+            accB[i] += (double)bfly16(rs, lane);
+            if (rt < n_row_tiles) {
+              float* dh = p.Rhi + lrow * p.ldr + slot0 + c0;
+              float* dl = p.Rlo + lrow * p.ldr + slot0 + c0;
+#pragma unroll
+              for (int c = 0; c < 16; ++c)
+                if (c < T && slot0 + c0 + c < p.ldr) { const float h = tf32_hi(rs[c]); dh[c] = h; dl[c] = rs[c] - h; }
+            }
+          }
+        }
+      }
+      flush(cur_cb);
+    } else {
     // ===== epilogue: thread = row of the tile (TMEM lane); kFwdEpiGroups warps per lane quadrant,
     // warp group g taking the 16-column chunks g, g + G, g + 2G, ...  Column sums over the 32 rows of
     // a warp are formed in fp32 (the loss shifted by ln 2 so the partial sums stay O(1)) and
@@ -486,7 +607,7 @@ tc_fwd_kernel(const __grid_constant__ CUtensorMap mapX, const __grid_constant__ 
             const float inv = __fdividef(1.f, 1.f + e);
             const float pr = z >= 0.f ? inv : e * inv;
             rs[j] = train ? pr - yy : 0.f;
-            ls[j] = train ? (fmaxf(z, 0.f) - yy * z) + (__logf(1.f + e) - kLossShift) : 0.f;
+            ls[j] = train ? (fmaxf(z, 0.f) - yy * z) + (__logf(1.f + e) - p.loss_shift) : 0.f;
           }
           accA[i] += (double)bfly16(ls, lane);
           accB[i] += (double)bfly16(rs, lane);
@@ -546,6 +667,7 @@ tc_fwd_kernel(const __grid_constant__ CUtensorMap mapX, const __grid_constant__ 
       }
     }
     flush(cur_cb);
+    }
   }
   tc_fence_before();
   __syncthreads();
@@ -739,7 +861,7 @@ struct TcReduceParams {
   const double* lossPart; const double* gbPart; int64_t n_parts; int n_slots, T, d;
   double* Gred; int ldgr; int accumulate;
   // the forward kernel sums (loss - ln 2): add ln 2 * (training rows of the column) back once
-  const unsigned long long* hist_local; const int32_t* sel; const int32_t* val; int64_t n_local;
+  const unsigned long long* hist_local; const int32_t* sel; const int32_t* val; int64_t n_local; double loss_shift;
 };
 __global__ void tc_reduce_tiles_kernel(const TcReduceParams p) {
   __shared__ double sh[2][8][33];
@@ -758,7 +880,7 @@ __global__ void tc_reduce_tiles_kernel(const TcReduceParams p) {
     double* q = p.Gred + (int64_t)slot * p.ldgr;
     q[p.d] = p.accumulate ? q[p.d] + g : g;
     if (!p.accumulate)
-      l += (double)kLossShift * (double)(p.n_local - (int64_t)p.hist_local[p.sel[slot] * 256 + (p.val[slot] & 0xff)]);
+      l += p.loss_shift * (double)(p.n_local - (int64_t)p.hist_local[p.sel[slot] * 256 + (p.val[slot] & 0xff)]);
     if (slot % p.T == 0) q[p.d + 1] = p.accumulate ? q[p.d + 1] + l : l;
   }
 }

@@ -50,15 +50,16 @@ def load_case(golden_dir, name):
     return z, meta, X, y
 
 
+@pytest.mark.parametrize("tc", [1, 0], ids=["tcgen05", "ffma"])
 @pytest.mark.parametrize("name", ["cfg2", "cfg5", "cfg4"])
-def test_logreg_sweep_vs_sklearn_fixture(solver, golden_dir, name):
+def test_logreg_sweep_vs_sklearn_fixture(solver, golden_dir, name, tc):
     z, meta, X, y = load_case(golden_dir, name)
     cv, cands = meta["cv"], meta["candidates"]
     fold = folds.stratified_labels(y, cv)
     assert (fold == ofolds.stratified_fold_ids(y, cv)).all()
     ds = solver.upload_dataset(X, y, classifier=True)
     out = solver.logreg_sweep(ds, fold, cv, [c["C"] for c in cands], [c.get("tol", 1e-4) for c in cands],
-                              [c.get("fit_intercept", True) for c in cands], [100] * len(cands))
+                              [c.get("fit_intercept", True) for c in cands], [100] * len(cands), use_tensor_cores=tc)
     want_coef, want_icpt = z[f"{name}_coef"], z[f"{name}_intercept"]
     iter_diff = 0
     for i in range(len(cands)):
