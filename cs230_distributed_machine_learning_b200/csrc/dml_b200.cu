@@ -385,7 +385,7 @@ struct EvalCtx {
   // buffers
   float *Wt = nullptr, *bt = nullptr, *R = nullptr, *Rlo = nullptr, *Whi = nullptr, *Wlo = nullptr, *Gpart = nullptr;
   double *lossPart = nullptr, *gbPart = nullptr, *Gred = nullptr; int32_t *sel = nullptr, *val = nullptr, *cntPart = nullptr;
-  CUtensorMap mXf, mXg, mWh, mWl, mRh, mRl;
+  CUtensorMap mXf, mXf2, mXg, mWh, mWl, mRh, mRl;   // mXf2: forward X box of a 2-CTA cluster member (64 rows)
   unsigned long long* hist_local = nullptr;   // [512] label histogram of this rank's rows
   // the forward kernel sums (loss - shift) with shift = loss of the zero model: ln 2, or ln T (multinomial)
   float loss_shift() const { return T == 1 ? 0.693147182f : logf((float)T); }
@@ -431,10 +431,12 @@ struct EvalCtx {
   int make_maps(dml_ctx* ctx) {
     if (!use_tc) return DML_OK;
     int rc;
-    if ((rc = make_map_2d(ctx, &mXf, X, d, n, ldx * 4, 32, 128))) return rc;   // forward: 128 rows x 32 features
+    // forward X box: 128 rows (or a cluster member's share of them) x 32 features
+    if ((rc = make_map_2d(ctx, &mXf, X, d, n, ldx * 4, 32, 128))) return rc;
+    if ((rc = make_map_2d(ctx, &mXf2, X, d, n, ldx * 4, 32, 64))) return rc;   // forward: 128 rows x 32 features
     if ((rc = make_map_2d(ctx, &mXg, X, d, n, ldx * 4, 32, 32, true))) return rc;    // gradient: 32 rows x 32 features
-    if ((rc = make_map_2d(ctx, &mWh, Whi, d, S_max, (uint64_t)ldw * 4, 32, NC / cl))) return rc;
-    if ((rc = make_map_2d(ctx, &mWl, Wlo, d, S_max, (uint64_t)ldw * 4, 32, NC / cl))) return rc;
+    if ((rc = make_map_2d(ctx, &mWh, Whi, d, S_max, (uint64_t)ldw * 4, 32, NC))) return rc;
+    if ((rc = make_map_2d(ctx, &mWl, Wlo, d, S_max, (uint64_t)ldw * 4, 32, NC))) return rc;
     if ((rc = make_map_chunked(ctx, &mRh, R, ldr_max, chunk_rows, (uint64_t)ldr_max * 4, 32, NC / 32))) return rc;
     if ((rc = make_map_chunked(ctx, &mRl, Rlo, ldr_max, chunk_rows, (uint64_t)ldr_max * 4, 32, NC / 32))) return rc;
     return DML_OK;
@@ -458,12 +460,15 @@ struct EvalCtx {
         fp.fold_id = fold_id; fp.hold_id = hold_id; fp.slot_sel = sel; fp.slot_val = val;
         fp.Rhi = R; fp.Rlo = Rlo; fp.ldr = (int)ldr_max; fp.lossPart = lossPart; fp.gbPart = gbPart;
         fp.mask_hi = ctx->tc_mask_hi; fp.prefetch_jobs = ctx->tc_prefetch; fp.T = T; fp.loss_shift = loss_shift();
-        const int64_t jobs = cdiv(cdiv(rows, 128), cl) * ncb;      // per cluster
-        const int grid = cl * (int)std::min<int64_t>(jobs, ctx->n_sms / cl);
+        // clusters of 2 share each X tile between two column blocks; with an odd number of blocks one
+        // CTA of the last pair would run on empty columns, so small / odd cases run unclustered
+        const int clr = (cl == 2 && ncb >= 2 && (ncb % 2 == 0 || ncb >= 5)) ? 2 : 1;
+        const int64_t jobs = cdiv(rows, 128) * cdiv(ncb, clr);     // per cluster
+        const int grid = clr * (int)std::min<int64_t>(jobs, ctx->n_sms / clr);
         CU(cudaMemsetAsync(lossPart, 0, sizeof(double) * (size_t)grid * 4 * n_slots, st));
         CU(cudaMemsetAsync(gbPart, 0, sizeof(double) * (size_t)grid * 4 * n_slots, st));
-        int rc = T == 1 ? launch_tc_fwd<FWD_LOGREG>(ctx, NC, cl, grid, mXf, mWh, mWl, fp)
-                        : launch_tc_fwd<tc::FWD_LOGREG_MULTI>(ctx, NC, cl, grid, mXf, mWh, mWl, fp);
+        int rc = T == 1 ? launch_tc_fwd<FWD_LOGREG>(ctx, NC, clr, grid, clr == 2 ? mXf2 : mXf, mWh, mWl, fp)
+                        : launch_tc_fwd<tc::FWD_LOGREG_MULTI>(ctx, NC, clr, grid, clr == 2 ? mXf2 : mXf, mWh, mWl, fp);
         if (rc) return rc;
         tc::TcGradParams gp{r0, rows, tc_rps, d, n_slots, Gpart, ldg, ctx->tc_mask_hi, ctx->tc_prefetch_grad};
         const int splits_here = (int)cdiv(rows, tc_rps);
@@ -514,12 +519,14 @@ struct EvalCtx {
       fp.n_slots = n_slots; fp.n_col_blocks = (int)cdiv(n_slots, NC); fp.bt = bt; fp.ycls = y;
       fp.fold_id = fold_id; fp.hold_id = hold_id; fp.slot_sel = sel; fp.slot_val = val;
       fp.cntPart = cntPart; fp.mask_hi = ctx->tc_mask_hi; fp.prefetch_jobs = ctx->tc_prefetch; fp.T = T; fp.loss_shift = 0.f;
-      const int64_t jobs = cdiv(tiles_total, cl) * fp.n_col_blocks;
-      const int grid = cl * (int)std::min<int64_t>(jobs, ctx->n_sms / cl);
+      const int ncb = fp.n_col_blocks;
+      const int clr = (cl == 2 && ncb >= 2 && (ncb % 2 == 0 || ncb >= 5)) ? 2 : 1;
+      const int64_t jobs = tiles_total * cdiv(ncb, clr);
+      const int grid = clr * (int)std::min<int64_t>(jobs, ctx->n_sms / clr);
       CU(cudaMemsetAsync(cntPart, 0, sizeof(int32_t) * (size_t)grid * 4 * n_slots, st));
       tick(ctx);
-      int rc = T == 1 ? launch_tc_fwd<FWD_SCORE_CLS>(ctx, NC, cl, grid, mXf, mWh, mWl, fp)
-                      : launch_tc_fwd<tc::FWD_SCORE_MULTI>(ctx, NC, cl, grid, mXf, mWh, mWl, fp);
+      int rc = T == 1 ? launch_tc_fwd<FWD_SCORE_CLS>(ctx, NC, clr, grid, clr == 2 ? mXf2 : mXf, mWh, mWl, fp)
+                      : launch_tc_fwd<tc::FWD_SCORE_MULTI>(ctx, NC, clr, grid, clr == 2 ? mXf2 : mXf, mWh, mWl, fp);
       tock(ctx, 1);
       ctx->total_launches += 2;
       if (rc) return rc;

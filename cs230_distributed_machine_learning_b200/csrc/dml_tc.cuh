@@ -246,9 +246,9 @@ __device__ __forceinline__ T bfly16(const T (&v)[16], int lane) {
 
 // Jobs are ordered column block first: every CTA walks the row tiles of one column block (W stays
 // hot in L2, per-column running sums stay in registers) and changes block at most a few times.
-// CL = 2: the kernel runs as clusters of two CTAs that work on neighbouring row tiles of the same
-// column block; each CTA fetches half of every W chunk and TMA-multicasts it to both, which halves
-// the L2 -> SM traffic of the operand every row tile re-reads (measured bound of the CL = 1 kernel).
+// CL = 2: the kernel runs as clusters of two CTAs that work on the SAME row tile and on neighbouring
+// column blocks (2k, 2k+1); each CTA fetches half of every X chunk and TMA-multicasts it to both, so
+// X crosses HBM / L2 once per row tile instead of once per (row tile, column block).
 template <int NC, int MODE, int CL>
 __global__ void __launch_bounds__(kFwdThreads, 1)
 tc_fwd_kernel(const __grid_constant__ CUtensorMap mapX, const __grid_constant__ CUtensorMap mapWhi,
@@ -290,11 +290,11 @@ tc_fwd_kernel(const __grid_constant__ CUtensorMap mapX, const __grid_constant__ 
   // job list of this CTA: (column block, row tile); a cluster takes CL neighbouring row tiles
   const int64_t n_row_tiles = (p.rows + 127) / 128;
   const int crank = CL > 1 ? (int)cluster_ctarank() : 0;
-  const int64_t tiles_per_cb = (n_row_tiles + CL - 1) / CL;      // per cluster member
-  const int64_t n_jobs = tiles_per_cb * p.n_col_blocks;          // jobs per cluster member stream
+  const int64_t cb_groups = (p.n_col_blocks + CL - 1) / CL;      // column blocks are dealt out CL at a time
+  const int64_t n_jobs = n_row_tiles * cb_groups;                // jobs per cluster (column-block group major)
   const int64_t job0 = blockIdx.x / CL, job_step = gridDim.x / CL;
-  auto job_cb = [&](int64_t job) { return (int)(job / tiles_per_cb); };
-  auto job_rt = [&](int64_t job) { return (job % tiles_per_cb) * CL + crank; };   // may be == n_row_tiles (dummy tile)
+  auto job_cb = [&](int64_t job) { return (int)(job / n_row_tiles) * CL + crank; };  // may be >= n_col_blocks (no columns)
+  auto job_rt = [&](int64_t job) { return job % n_row_tiles; };
 
   if (warp == kFwdTmaWarp) {
     // ===== TMA producer =====
@@ -314,15 +314,11 @@ tc_fwd_kernel(const __grid_constant__ CUtensorMap mapX, const __grid_constant__ 
           mbar_wait(empty + s, ph ^ 1);
           uint8_t* st = smem + s * L::kStage;
           mbar_expect_tx(full + s, L::kA + 2 * L::kB);
-          tma_load_2d(&mapX, full + s, st, c * 32, row);
-          if (CL == 1) {
-            tma_load_2d(&mapWhi, full + s, st + L::kA, c * 32, slot);
-            tma_load_2d(&mapWlo, full + s, st + L::kA + L::kB, c * 32, slot);
-          } else {
-            constexpr int kHalf = (NC / CL) * 128;               // bytes of this CTA's share of a W chunk
-            tma_load_2d_mcast(&mapWhi, full + s, st + L::kA + crank * kHalf, c * 32, slot + crank * (NC / CL), (1 << CL) - 1);
-            tma_load_2d_mcast(&mapWlo, full + s, st + L::kA + L::kB + crank * kHalf, c * 32, slot + crank * (NC / CL), (1 << CL) - 1);
-          }
+          if (CL == 1) tma_load_2d(&mapX, full + s, st, c * 32, row);
+          else         // this CTA's share of the X chunk (128 / CL rows), delivered to every CTA of the cluster
+            tma_load_2d_mcast(&mapX, full + s, st + crank * (128 / CL) * 128, c * 32, row + crank * (128 / CL), (1 << CL) - 1);
+          tma_load_2d(&mapWhi, full + s, st + L::kA, c * 32, slot);
+          tma_load_2d(&mapWlo, full + s, st + L::kA + L::kB, c * 32, slot);
         }
       }
     }
