@@ -734,7 +734,6 @@ extern "C" int dml_ridge_sweep(dml_ctx* ctx, const float* X, int64_t n, int d, i
                                double* sse_out, double* sy_out, double* syy_out,
                                int32_t* info_out, int use_tensor_cores) {
   if (!ctx) return DML_ERR_ARG;
-  (void)use_tensor_cores;
   if (!X || !fold_id || !alpha || !fit_intercept || !coef_out || !intercept_out || (is_classifier ? !y_cls : !y_reg))
     return fail(ctx, DML_ERR_ARG, "dml_ridge_sweep: NULL argument");
   if (n <= 0 || d <= 0 || ldx < d || n_cand <= 0 || n_folds < 0 || n_folds > 127 || (is_classifier && n_classes < 2))
@@ -749,18 +748,27 @@ extern "C" int dml_ridge_sweep(dml_ctx* ctx, const float* X, int64_t n, int d, i
   const int64_t S_all = (int64_t)F * T, tiles_total = cdiv(n, BM);
   const int tile_n = (BN / T) * T;
   if (cdiv(S_all, tile_n) > 65535) return fail(ctx, DML_ERR_LIMIT, "too many columns (%lld)", (long long)S_all);
-  const int64_t rps = 16384;
+  // tcgen05 Gram: 128 x 128 feature blocks (upper block triangle), long row splits (the drain warps
+  // keep round-to-nearest fp32 sums over 128-row tensor-core chains), first-order moments by a
+  // separate HBM-bound kernel
+  const bool use_tc = use_tensor_cores != 0 && ldx % 4 == 0 && aligned16(X) && n_folds <= 16 && d <= 1024 && T <= 16;
+  if (use_tensor_cores == 1 && !use_tc)
+    return fail(ctx, DML_ERR_ARG, "tensor-core Gram needs ldx %% 4 == 0, aligned X, n_folds <= 16, d <= 1024, <= 16 targets");
+  const int nb = (int)cdiv(d, 128), ldm_tc = nb * 128;
+  const int64_t rps = use_tc ? 32768 : 16384;
   const int splits = (int)cdiv(n, rps);
+  const int64_t xty_rows = 4096; const int xty_chunks = (int)cdiv(n, xty_rows);
   const int gfolds = std::max(n_folds, 2);  // the hold-out pass uses labels {0,1}
   // candidates per solve batch: keep the fp64 systems under ~2 GB
   int cand_chunk = (int)std::max<int64_t>(1, ((int64_t)2 << 30) / ((int64_t)fpc * d * d * 8));
   cand_chunk = std::min(cand_chunk, n_cand);
 
-  float *d_Mpart, *d_Wt, *d_bt; void* d_part; uint16_t* d_bmask;
+  float *d_Mpart, *d_Wt, *d_bt, *d_xty = nullptr; void* d_part; uint16_t* d_bmask;
   double *d_Mfold, *d_Mtot, *d_A, *d_B, *d_mu, *d_stats, *d_sse; int32_t *d_sel, *d_val, *d_info; long long* d_cnt;
   for (int pass = 0; pass < 2; ++pass) {
     Arena a(pass ? ctx->ws : nullptr);
-    d_Mpart = a.take<float>((size_t)gfolds * splits * D * ldm);
+    d_Mpart = a.take<float>(use_tc ? (size_t)gfolds * splits * ldm_tc * ldm_tc : (size_t)gfolds * splits * D * ldm);
+    if (use_tc) d_xty = a.take<float>((size_t)gfolds * xty_chunks * (d + 2) * (1 + T));
     d_Mfold = a.take<double>((size_t)(n_folds + 2) * D * D);
     d_Mtot = a.take<double>((size_t)D * D);
     d_bmask = a.take<uint16_t>((size_t)cdiv(n, 16) + 16);
@@ -774,6 +782,13 @@ extern "C" int dml_ridge_sweep(dml_ctx* ctx, const float* X, int64_t n, int d, i
     d_part = a.take<float>((size_t)tiles_total * S_all);
     if (!pass) { int rc = ensure_ws(ctx, a.off + 256); if (rc) return rc; }
   }
+  CUtensorMap mXg;
+  if (use_tc) { int rc = make_map_2d(ctx, &mXg, X, d, n, ldx * 4, 32, 32, true); if (rc) return rc; }
+  static bool gram_attr = false;
+  if (use_tc && !gram_attr) {
+    CU(cudaFuncSetAttribute(tc::tc_gram_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, tc::GramSmem::kBytes));
+    gram_attr = true;
+  }
   timing_begin(ctx);
   const bool xvec = (ldx % 4 == 0) && aligned16(X);
   CU(cudaMemsetAsync(d_info, 0, sizeof(int32_t) * F, st));
@@ -784,6 +799,25 @@ extern "C" int dml_ridge_sweep(dml_ctx* ctx, const float* X, int64_t n, int d, i
     if (nf == 0) continue;
     const bool use_mask = nf <= 16;
     if (use_mask) { blockmask_kernel<<<(unsigned)cdiv(cdiv(n, 16), 256), 256, 0, st>>>(lab, n, d_bmask); KCHECK(); }
+    double* dst = pass == 0 ? d_Mfold : d_Mfold + (size_t)n_folds * D * D;  // hold pass writes [n_folds], [n_folds+1]
+    if (use_tc) {
+      CU(cudaMemsetAsync(d_Mpart, 0, sizeof(float) * (size_t)nf * splits * ldm_tc * ldm_tc, st));
+      tc::TcGramParams gp{n, rps, d, nb, lab, d_bmask, splits, d_Mpart, ldm_tc};
+      tick(ctx);
+      tc::tc_gram_kernel<<<dim3((unsigned)(nb * (nb + 1) / 2), 1, (unsigned)(nf * splits)), tc::kGramThreads,
+                           tc::GramSmem::kBytes, st>>>(mXg, gp);
+      tock(ctx, 1);
+      KCHECK();
+      tc::XtyParams xp{X, ldx, n, d, T, lab, d_bmask, is_classifier ? nullptr : y_reg, is_classifier ? y_cls : nullptr,
+                       xty_rows, xty_chunks, d_xty};
+      tc::xty_kernel<<<dim3((unsigned)xty_chunks, (unsigned)nf), 256, 0, st>>>(xp);
+      KCHECK();
+      tc::GramReduceParams rp{d_Mpart, splits, nb, ldm_tc, d_xty, xty_chunks, d, T, dst};
+      tc::gram_reduce_kernel<<<dim3((unsigned)cdiv(D, 128), D, nf), 128, 0, st>>>(rp);
+      KCHECK();
+      ctx->total_launches += 5;
+      continue;
+    }
     GramParams gp{X, ldx, n, d, xvec, lab, use_mask ? d_bmask : nullptr, T, is_classifier ? nullptr : y_reg,
                   is_classifier ? y_cls : nullptr, rps, splits, d_Mpart, ldm};
     dim3 grid((unsigned)cdiv(D, BM), (unsigned)cdiv(D, BN), (unsigned)(nf * splits));
@@ -791,7 +825,6 @@ extern "C" int dml_ridge_sweep(dml_ctx* ctx, const float* X, int64_t n, int d, i
     gram_kernel<<<grid, NT, kGemmSmemBytes, st>>>(gp);
     tock(ctx, 1);
     KCHECK();
-    double* dst = pass == 0 ? d_Mfold : d_Mfold + (size_t)n_folds * D * D;  // hold pass writes [n_folds], [n_folds+1]
     reduce_moments_kernel<<<dim3((unsigned)cdiv(D, 128), D, nf), 128, 0, st>>>(d_Mpart, splits, D, ldm, dst);
     KCHECK();
     ctx->total_launches += 3;
@@ -814,7 +847,19 @@ extern "C" int dml_ridge_sweep(dml_ctx* ctx, const float* X, int64_t n, int d, i
     const int nc = std::min(cand_chunk, n_cand - c0), nsys = nc * fpc;
     RidgeSysParams sp{d, T, D, n_folds, has_hold, c0, nc, d_Mfold, d_Mtot, alpha, fit_intercept, d_A, d_B, d_mu};
     ridge_assemble_kernel<<<dim3(32, nsys), 256, 0, st>>>(sp);
-    ridge_cholesky_kernel<<<nsys, 512, d * sizeof(double), st>>>(d_A, d_B, d, T, d_info + c0 * fpc);
+    if (d <= kCholMaxD) {
+      const size_t chol_smem = ((size_t)d * (kCholNB + 1) + 1 + (size_t)kCholNB * (kCholNB + 2)) * sizeof(double);
+      static bool chol_attr = false;
+      if (!chol_attr) {
+        CU(cudaFuncSetAttribute(ridge_cholesky_blocked_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                (int)(((size_t)kCholMaxD * (kCholNB + 1) + 1 + (size_t)kCholNB * (kCholNB + 2)) * sizeof(double))));
+        chol_attr = true;
+      }
+      const int threads = (int)std::min<int64_t>(640, rup(d, 32));
+      ridge_cholesky_blocked_kernel<<<nsys, threads, chol_smem, st>>>(d_A, d_B, d, T, d_info + c0 * fpc);
+    } else {
+      ridge_cholesky_kernel<<<nsys, 512, d * sizeof(double), st>>>(d_A, d_B, d, T, d_info + c0 * fpc);
+    }
     RidgeOutParams op{d, T, n_folds, has_hold, c0, ldw, d_B, d_mu, coef_out, intercept_out, d_Wt, d_bt, d_sel, d_val};
     ridge_output_kernel<<<dim3(nsys, T), 128, 0, st>>>(op);
     KCHECK();

@@ -845,6 +845,294 @@ tc_grad_kernel(const __grid_constant__ CUtensorMap mapX, const __grid_constant__
   if (warp == 9) tmem_dealloc(tmem_base, kTmemCols);
 }
 
+// ---------------------------------------------------------------- Gram kernel (Ridge)
+// Mpart[fold][split][i][c] = sum over the split's rows of that fold of X[row][i] * X[row][c]
+// for a 128 x 128 block (ib, cb), cb >= ib (the moment matrix is symmetric; the reducer mirrors).
+//   A = X^T block ib: staged into tensor memory (hi, lo) with the rows of other folds zeroed
+//   B = X block cb  : four TMA boxes [32 rows x 32 features]; B_lo written to shared memory by
+//                     four extra warps (elementwise on the swizzled buffer)
+// 32-row stages without a row of the fold are skipped by every role (per-16-row presence bits).
+// Replaces the sgemm in sklearn's _solve_cholesky (sklearn/linear_model/_ridge.py:220) for all folds
+// of cross_val_score (worker.py:326/341) in one pass over X.
+constexpr int kGramStages = 3;
+constexpr int kGramThreads = 448;   // warps 0-3 A staging, 4-7 B split, 8-11 drain, 12 TMA, 13 MMA
+constexpr int kGramNC = 128;
+
+struct TcGramParams {
+  int64_t n; int64_t rows_per_split; int d; int n_blocks;   // n_blocks = ceil(d / 128)
+  const int8_t* label; const uint16_t* blockmask;            // presence bits per 16 rows (bit f: fold f occurs)
+  int splits;
+  float* Mpart; int ldm;                                     // [folds][splits][n_blocks*128][ldm], zero-initialised
+};
+struct GramSmem {
+  static constexpr int kA = 4 * 4096, kB = 4 * 4096;
+  static constexpr int kStage = kA + 2 * kB;
+  static constexpr int kBytes = kGramStages * kStage + 1024 + 256;
+};
+
+__global__ void __launch_bounds__(kGramThreads, 1)
+tc_gram_kernel(const __grid_constant__ CUtensorMap mapX, const TcGramParams p) {
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
+  using L = GramSmem;
+  constexpr int NC = kGramNC;
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + kGramStages * L::kStage);
+  uint64_t* full = bars; uint64_t* split = bars + kGramStages; uint64_t* empty = bars + 2 * kGramStages;
+  uint64_t* tfull = bars + 3 * kGramStages; uint64_t* tempty = tfull + 2;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tempty + 2);
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  constexpr uint32_t kTmemCols = 512, kTmemA = 2 * NC;       // 2 x 128 accumulator + 3 x 64 operand columns
+
+  // block pair (ib <= cb) from the linear index
+  int ib = 0, cb = 0;
+  { int t = blockIdx.x; for (ib = 0; ib < p.n_blocks; ++ib) { const int len = p.n_blocks - ib; if (t < len) { cb = ib + t; break; } t -= len; } }
+  const int fold = blockIdx.z / p.splits, sp = blockIdx.z % p.splits;
+  const int64_t kb = (int64_t)sp * p.rows_per_split;
+  const int64_t ke = min(p.n, kb + p.rows_per_split);
+  const int n_stages = (int)((ke - kb + 31) / 32);
+  const uint16_t* bm = p.blockmask + (kb >> 4);
+  const int64_t bm_len = ((p.n + 15) >> 4) - (kb >> 4);
+  auto stage_active = [&](int it) -> bool {
+    unsigned m = bm[2 * it];
+    if (2 * it + 1 < bm_len) m |= bm[2 * it + 1];
+    return (m >> fold) & 1u;
+  };
+  int n_act = 0;
+  for (int it = 0; it < n_stages; ++it) n_act += stage_active(it) ? 1 : 0;
+  if (n_act == 0) return;                                   // nothing of this fold in the split (uniform exit)
+  const int n_groups = (n_act + kChain - 1) / kChain;
+
+  if (warp == 12 && lane == 0) {
+    for (int s = 0; s < kGramStages; ++s) { mbar_init(full + s, 1); mbar_init(split + s, 8); mbar_init(empty + s, 1); }
+    for (int a = 0; a < 2; ++a) { mbar_init(tfull + a, 1); mbar_init(tempty + a, 4); }
+    fence_barrier_init();
+  }
+  if (warp == 13) tmem_alloc(tmem_slot, kTmemCols);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  if (warp == 12) {
+    if (lane == 0) {
+      for (int it = 0, ai = 0; it < n_stages; ++it) {
+        if (!stage_active(it)) continue;
+        const int s = ai % kGramStages; const uint32_t ph = (ai / kGramStages) & 1; ++ai;
+        mbar_wait(empty + s, ph ^ 1);
+        uint8_t* st = smem + s * L::kStage;
+        mbar_expect_tx(full + s, L::kA + L::kB);
+        const int xr = (int)(kb + (int64_t)it * 32);
+#pragma unroll
+        for (int b = 0; b < 4; ++b) {
+          tma_load_2d(&mapX, full + s, st + b * 4096, ib * 128 + b * 32, xr);
+          tma_load_2d(&mapX, full + s, st + L::kA + b * 4096, cb * 128 + b * 32, xr);
+        }
+      }
+    }
+  } else if (warp == 13) {
+    constexpr uint32_t idesc = instr_desc_tf32(128, NC, 0, 1);
+    for (int g = 0, ai = 0; g < n_groups; ++g) {
+      const int acc = g & 1; const uint32_t aph = (g >> 1) & 1;
+      mbar_wait(tempty + acc, aph ^ 1);
+      tc_fence_after();
+      const uint32_t tacc = tmem_base + acc * NC;
+      const int g_end = min(n_act, (g + 1) * kChain);
+      for (int first = 1; ai < g_end; ++ai) {
+        const int s = ai % kGramStages; const uint32_t ph = (ai / kGramStages) & 1;
+        mbar_wait(full + s, ph);
+        mbar_wait(split + s, ph);
+        tc_fence_after();
+        if (elect_one()) {
+          const uint32_t b_hi = smem_u32(smem + s * L::kStage) + L::kA, b_lo = b_hi + L::kB;
+          const uint32_t ta_hi = tmem_base + kTmemA + s * 64, ta_lo = ta_hi + 32;
+#pragma unroll
+          for (int k = 0; k < 4; ++k) {
+            const uint64_t dbh = smem_desc(b_hi + k * 1024, 4096, 512, kLayoutSw128Base32);
+            const uint64_t dbl = smem_desc(b_lo + k * 1024, 4096, 512, kLayoutSw128Base32);
+            umma_tf32_ts(tacc, ta_lo + k * 8, dbh, idesc, (first && k == 0) ? 0u : 1u);
+            umma_tf32_ts(tacc, ta_hi + k * 8, dbl, idesc, 1);
+            umma_tf32_ts(tacc, ta_hi + k * 8, dbh, idesc, 1);
+          }
+          umma_commit(empty + s);
+          if (ai == g_end - 1) umma_commit(tfull + acc);
+        }
+        __syncwarp();
+        first = 0;
+      }
+    }
+  } else if (warp < 4) {
+    // A staging: lane = feature of block ib; rows of other folds (and rows past n) contribute zero
+    const int qd = warp & 3;
+    for (int it = 0, ai = 0; it < n_stages; ++it) {
+      if (!stage_active(it)) continue;
+      const int s = ai % kGramStages; const uint32_t ph = (ai / kGramStages) & 1; ++ai;
+      const int64_t row0 = kb + (int64_t)it * 32;
+      uint32_t keep = 0;                                      // bit k: row k of the stage belongs to the fold
+      { const int64_t r = row0 + lane; const int ok = (r < p.n) && (p.label[r] == fold); keep = __ballot_sync(0xffffffffu, ok); }
+      mbar_wait(full + s, ph);
+      const uint32_t box = smem_u32(smem + s * L::kStage) + qd * 4096;
+      uint32_t hi[32], lo[32];
+#pragma unroll
+      for (int k = 0; k < 32; ++k) {
+        const uint32_t w = lds32u(box + k * 128 + ((((lane >> 3) ^ (k & 3)) << 5) | ((lane & 7) << 2)));
+        hi[k] = ((keep >> k) & 1u) ? w : 0u;
+      }
+#pragma unroll
+      for (int e = 0; e < 32; ++e) { const float x = __uint_as_float(hi[e]); lo[e] = __float_as_uint(x - tf32_hi(x)); }
+      const uint32_t ta = tmem_base + kTmemA + s * 64 + ((uint32_t)(qd * 32) << 16);
+      tmem_st32(ta, hi);
+      tmem_st32(ta + 32, lo);
+      tmem_st_wait();
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(split + s);
+    }
+  } else if (warp < 8) {
+    // B split: lo = x - tf32(x), elementwise on the swizzled tile
+    const int tid = threadIdx.x - 128;
+    for (int it = 0, ai = 0; it < n_stages; ++it) {
+      if (!stage_active(it)) continue;
+      const int s = ai % kGramStages; const uint32_t ph = (ai / kGramStages) & 1; ++ai;
+      mbar_wait(full + s, ph);
+      const uint32_t hi = smem_u32(smem + s * L::kStage) + L::kA;
+      split_stage(hi, hi + L::kB, L::kB, tid, 128, false);
+      fence_proxy_async();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(split + s);
+    }
+  } else if (warp < 12) {
+    const int q = warp & 3;
+    const int i = ib * 128 + q * 32 + lane;
+    float sum[NC];
+#pragma unroll
+    for (int c = 0; c < NC; ++c) sum[c] = 0.f;
+    for (int g = 0; g < n_groups; ++g) {
+      const int acc = g & 1; const uint32_t aph = (g >> 1) & 1;
+      mbar_wait(tfull + acc, aph);
+      tc_fence_after();
+      const uint32_t tacc = tmem_base + acc * NC + ((uint32_t)(q * 32) << 16);
+#pragma unroll
+      for (int c0 = 0; c0 < NC; c0 += 16) {
+        uint32_t v[16];
+        tmem_ld16(tacc + c0, v);
+        tmem_ld_wait();
+#pragma unroll
+        for (int c = 0; c < 16; ++c) sum[c0 + c] += __uint_as_float(v[c]);
+      }
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(tempty + acc);
+    }
+    float* out = p.Mpart + (((int64_t)fold * p.splits + sp) * (p.n_blocks * 128) + i) * p.ldm + cb * 128;
+#pragma unroll
+    for (int c = 0; c < NC; ++c) out[c] = sum[c];
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 13) tmem_dealloc(tmem_base, kTmemCols);
+}
+
+// First-order moments and targets, per fold, HBM-bound: for a chunk of rows and one fold,
+// part[j][0] = sum x_j, part[j][1+t] = sum x_j y_t (j < d); row d: [count, sum y_t ...]; row d+1: [0, sum y_t^2 ...].
+// Y: regression target, or +-1 one-vs-rest columns of the class index (T = 1: class 1 positive).
+struct XtyParams {
+  const float* X; int64_t ldx; int64_t n; int d; int T;
+  const int8_t* label; const uint16_t* blockmask;
+  const float* yreg; const int32_t* ycls;
+  int64_t rows_per_chunk; int chunks;
+  float* part;   // [folds][chunks][d + 2][1 + T]
+};
+__global__ void __launch_bounds__(256) xty_kernel(const XtyParams p) {
+  const int fold = blockIdx.y, ch = blockIdx.x;
+  const int64_t r0 = (int64_t)ch * p.rows_per_chunk, r1 = min(p.n, r0 + p.rows_per_chunk);
+  const int T = p.T, W = 1 + T;
+  constexpr int JMAX = 4, TMAX = 16;                 // d <= 1024, T <= 16 (checked by the host)
+  float ax[JMAX], axy[JMAX][TMAX];
+#pragma unroll
+  for (int a = 0; a < JMAX; ++a) { ax[a] = 0.f;
+#pragma unroll
+    for (int t = 0; t < TMAX; ++t) axy[a][t] = 0.f; }
+  float cnt = 0.f, sy[TMAX], syy[TMAX];
+#pragma unroll
+  for (int t = 0; t < TMAX; ++t) { sy[t] = 0.f; syy[t] = 0.f; }
+  for (int64_t r = r0; r < r1; ++r) {
+    if ((r & 15) == 0 && !((p.blockmask[r >> 4] >> fold) & 1u)) { r += 15; continue; }
+    if (p.label[r] != fold) continue;
+    float yv[TMAX];
+#pragma unroll
+    for (int t = 0; t < TMAX; ++t) {
+      if (t < T) {
+        if (p.yreg) yv[t] = p.yreg[r];
+        else { const int c = p.ycls[r]; yv[t] = (T == 1 ? (c == 1) : (c == t)) ? 1.f : -1.f; }
+      } else yv[t] = 0.f;
+    }
+    const float* xr = p.X + r * p.ldx;
+#pragma unroll
+    for (int a = 0; a < JMAX; ++a) {
+      const int j = threadIdx.x + a * 256;
+      if (j < p.d) {
+        const float x = __ldg(xr + j);
+        ax[a] += x;
+#pragma unroll
+        for (int t = 0; t < TMAX; ++t) if (t < T) axy[a][t] = fmaf(x, yv[t], axy[a][t]);
+      }
+    }
+    if (threadIdx.x == 0) {
+      cnt += 1.f;
+#pragma unroll
+      for (int t = 0; t < TMAX; ++t) if (t < T) { sy[t] += yv[t]; syy[t] = fmaf(yv[t], yv[t], syy[t]); }
+    }
+  }
+  float* out = p.part + ((int64_t)fold * p.chunks + ch) * (p.d + 2) * W;
+#pragma unroll
+  for (int a = 0; a < JMAX; ++a) {
+    const int j = threadIdx.x + a * 256;
+    if (j < p.d) {
+      out[(int64_t)j * W] = ax[a];
+#pragma unroll
+      for (int t = 0; t < TMAX; ++t) if (t < T) out[(int64_t)j * W + 1 + t] = axy[a][t];
+    }
+  }
+  if (threadIdx.x == 0) {
+    out[(int64_t)p.d * W] = cnt; out[(int64_t)(p.d + 1) * W] = 0.f;
+#pragma unroll
+    for (int t = 0; t < TMAX; ++t) if (t < T) { out[(int64_t)p.d * W + 1 + t] = sy[t]; out[(int64_t)(p.d + 1) * W + 1 + t] = syy[t]; }
+  }
+}
+
+// Partials -> Mfold[fold][D][D] (fp64, D = d + T + 1), fixed summation order.
+//   (i, c) with i, c < d   : Gram blocks, mirrored from the computed upper block triangle
+//   (i, d + t), (d + t, i) : X^T Y ; (i, D-1), (D-1, i): column sums; (d+t, d+t): sum y^2; (d+t, D-1): sum y; (D-1, D-1): count
+struct GramReduceParams {
+  const float* Mpart; int splits; int n_blocks; int ldm;
+  const float* xty; int chunks; int d; int T;
+  double* Mfold;
+};
+__global__ void gram_reduce_kernel(const GramReduceParams p) {
+  const int fold = blockIdx.z, i = blockIdx.y;
+  const int c = blockIdx.x * blockDim.x + threadIdx.x;
+  const int D = p.d + p.T + 1, W = 1 + p.T;
+  if (c >= D || i >= D) return;
+  double acc = 0.0;
+  if (i < p.d && c < p.d) {
+    const bool upper = (c >> 7) >= (i >> 7);
+    const int64_t rr = upper ? i : c, cc = upper ? c : i;
+    const int64_t rows = (int64_t)p.n_blocks * 128;
+    for (int s = 0; s < p.splits; ++s) acc += (double)p.Mpart[(((int64_t)fold * p.splits + s) * rows + rr) * p.ldm + cc];
+  } else {
+    // which entry of the xty partial record?
+    int j, k;                                   // record row j (feature, or d = counts/sums, d+1 = squares), column k
+    const int hi = max(i, c), lo = min(i, c);
+    if (lo < p.d) { j = lo; k = (hi == D - 1) ? 0 : 1 + (hi - p.d); }          // X^T 1 or X^T Y
+    else if (hi == D - 1) { j = p.d; k = (lo == D - 1) ? 0 : 1 + (lo - p.d); }  // count or sum y_t
+    else if (hi == lo) { j = p.d + 1; k = 1 + (lo - p.d); }                     // sum y_t^2
+    else { j = -1; k = 0; }                                                      // y_t y_t' cross terms: not used
+    if (j >= 0)
+      for (int s = 0; s < p.chunks; ++s) acc += (double)p.xty[(((int64_t)fold * p.chunks + s) * (p.d + 2) + j) * W + k];
+  }
+  p.Mfold[((int64_t)fold * D + i) * D + c] = acc;
+}
+
 // ---------------------------------------------------------------- small helpers
 // trial weights -> hi / lo copies for the forward B operand
 __global__ void split_weights_kernel(const float* W, float* Whi, float* Wlo, int64_t n) {
