@@ -372,6 +372,55 @@ static int run_score(dml_ctx* ctx, int mode, const float* X, int64_t n, int d, i
   return DML_OK;
 }
 
+// ---- scoring pass on the tensor cores (classifier counts or squared errors) -----------------
+// Wt [n_slots][ldw] fp32 coefficients; Whi/Wlo: scratch of the same shape; part: [n_sms*4][n_slots]
+// int32 (classifier) or double (regressor) partials, summed by reduce_counts / reduce_sse_parts.
+static int run_score_tc(dml_ctx* ctx, int mode, const float* X, int64_t n, int d, int64_t ldx,
+                        const int32_t* ycls, const float* yreg, const int8_t* fold_id, const int8_t* hold_id,
+                        const float* Wt, int ldw, const float* bt, const int32_t* sel, const int32_t* val,
+                        int n_slots, int T, float* Whi, float* Wlo, void* part, int64_t* n_parts) {
+  cudaStream_t st = ctx->stream;
+  const int NC = pick_nc(n_slots, T);
+  if (NC == 0) return fail(ctx, DML_ERR_ARG, "run_score_tc: no column-block width for T=%d", T);
+  CUtensorMap mX, mX2, mWh, mWl;
+  int rc;
+  if ((rc = make_map_2d(ctx, &mX, X, d, n, ldx * 4, 32, 128))) return rc;
+  if ((rc = make_map_2d(ctx, &mX2, X, d, n, ldx * 4, 32, 64))) return rc;
+  if ((rc = make_map_2d(ctx, &mWh, Whi, d, n_slots, (uint64_t)ldw * 4, 32, NC))) return rc;
+  if ((rc = make_map_2d(ctx, &mWl, Wlo, d, n_slots, (uint64_t)ldw * 4, 32, NC))) return rc;
+  tc::split_weights_kernel<<<(unsigned)cdiv((int64_t)n_slots * ldw, 256), 256, 0, st>>>(Wt, Whi, Wlo, (int64_t)n_slots * ldw);
+  tc::TcFwdParams fp{};
+  fp.n_rows_total = n; fp.row0 = 0; fp.rows = n; fp.d_chunks = (int)cdiv(d, 32);
+  fp.n_slots = n_slots; fp.n_col_blocks = (int)cdiv(n_slots, NC); fp.bt = bt; fp.ycls = ycls; fp.yreg = yreg;
+  fp.fold_id = fold_id; fp.hold_id = hold_id; fp.slot_sel = sel; fp.slot_val = val;
+  fp.cntPart = (int32_t*)part; fp.ssePart = (double*)part;
+  fp.mask_hi = ctx->tc_mask_hi; fp.prefetch_jobs = 0; fp.T = T; fp.loss_shift = 0.f;
+  const int ncb = fp.n_col_blocks;
+  const int clr = (ctx->tc_cluster == 2 && ncb >= 2 && (ncb % 2 == 0 || ncb >= 5)) ? 2 : 1;
+  const int64_t jobs = cdiv(n, 128) * cdiv(ncb, clr);
+  const int grid = clr * (int)std::min<int64_t>(jobs, ctx->n_sms / clr);
+  const size_t esz = mode == FWD_SCORE_REG ? sizeof(double) : sizeof(int32_t);
+  CU(cudaMemsetAsync(part, 0, esz * (size_t)grid * 4 * n_slots, st));
+  const CUtensorMap& mx = clr == 2 ? mX2 : mX;
+  tick(ctx);
+  if (mode == FWD_SCORE_REG) rc = launch_tc_fwd<FWD_SCORE_REG>(ctx, NC, clr, grid, mx, mWh, mWl, fp);
+  else if (T == 1) rc = launch_tc_fwd<FWD_SCORE_CLS>(ctx, NC, clr, grid, mx, mWh, mWl, fp);
+  else rc = launch_tc_fwd<tc::FWD_SCORE_MULTI>(ctx, NC, clr, grid, mx, mWh, mWl, fp);
+  tock(ctx, 1);
+  ctx->total_launches += 2;
+  if (rc) return rc;
+  KCHECK();
+  *n_parts = (int64_t)grid * 4;
+  return DML_OK;
+}
+__global__ void reduce_sse_parts_kernel(const double* part, int64_t n_parts, int n_slots, double* sse) {
+  const int slot = blockIdx.x * blockDim.x + threadIdx.x;
+  if (slot >= n_slots) return;
+  double a = 0.0;
+  for (int64_t t = 0; t < n_parts; ++t) a += part[t * n_slots + slot];
+  sse[slot] = a;
+}
+
 // =============================================================================================
 // One batched loss/gradient evaluation for `n_slots` columns: the buffers and the two code paths
 // (tcgen05 3xTF32, or FFMA for shapes the tensor-core path does not take).
@@ -392,6 +441,11 @@ struct EvalCtx {
 
   void plan(dml_ctx* ctx, int64_t n_groups_max) {
     ctx_sms = ctx->n_sms;
+    {  // residual scratch per row chunk: a third of what is free (arena included), at most 16 GB
+      size_t free_b = 0, total_b = 0;
+      if (cudaMemGetInfo(&free_b, &total_b) == cudaSuccess)
+        ctx->r_budget = std::max<size_t>((size_t)1 << 30, std::min<size_t>((size_t)16 << 30, (free_b + ctx->ws_bytes) / 3));
+    }
     cl = ctx->tc_cluster;
     ldw = (int)rup(d, 4); ldg = (int)rup(d + 1, 4); ldgr = d + 2;
     tiles_total = cdiv(n, BM); tile_n = (BN / T) * T;
@@ -760,11 +814,14 @@ extern "C" int dml_ridge_sweep(dml_ctx* ctx, const float* X, int64_t n, int d, i
   const int64_t xty_rows = 4096; const int xty_chunks = (int)cdiv(n, xty_rows);
   const int gfolds = std::max(n_folds, 2);  // the hold-out pass uses labels {0,1}
   // candidates per solve batch: keep the fp64 systems under ~2 GB
-  int cand_chunk = (int)std::max<int64_t>(1, ((int64_t)2 << 30) / ((int64_t)fpc * d * d * 8));
+  int cand_chunk = (int)std::max<int64_t>(1, ((int64_t)2 << 30) / ((int64_t)fpc * d * d * 16));   // A and L^T
   cand_chunk = std::min(cand_chunk, n_cand);
 
-  float *d_Mpart, *d_Wt, *d_bt, *d_xty = nullptr; void* d_part; uint16_t* d_bmask;
-  double *d_Mfold, *d_Mtot, *d_A, *d_B, *d_mu, *d_stats, *d_sse; int32_t *d_sel, *d_val, *d_info; long long* d_cnt;
+  float *d_Mpart, *d_Wt, *d_bt, *d_xty = nullptr, *d_Whi = nullptr, *d_Wlo = nullptr; void* d_part; uint16_t* d_bmask;
+  double* d_part_tc = nullptr;
+  // scoring on the tensor cores needs a column-block width that holds whole fits
+  const bool score_tc = use_tc && (T == 1 || (T >= 3 && pick_nc(1, T) != 0));
+  double *d_Mfold, *d_Mtot, *d_A, *d_AT, *d_B, *d_mu, *d_stats, *d_sse; int32_t *d_sel, *d_val, *d_info; long long* d_cnt;
   for (int pass = 0; pass < 2; ++pass) {
     Arena a(pass ? ctx->ws : nullptr);
     d_Mpart = a.take<float>(use_tc ? (size_t)gfolds * splits * ldm_tc * ldm_tc : (size_t)gfolds * splits * D * ldm);
@@ -773,6 +830,7 @@ extern "C" int dml_ridge_sweep(dml_ctx* ctx, const float* X, int64_t n, int d, i
     d_Mtot = a.take<double>((size_t)D * D);
     d_bmask = a.take<uint16_t>((size_t)cdiv(n, 16) + 16);
     d_A = a.take<double>((size_t)cand_chunk * fpc * d * d);
+    d_AT = a.take<double>((size_t)cand_chunk * fpc * d * d);
     d_B = a.take<double>((size_t)cand_chunk * fpc * T * d);
     d_mu = a.take<double>((size_t)cand_chunk * fpc * (d + T));
     d_Wt = a.take<float>((size_t)S_all * ldw); d_bt = a.take<float>(S_all);
@@ -780,6 +838,10 @@ extern "C" int dml_ridge_sweep(dml_ctx* ctx, const float* X, int64_t n, int d, i
     d_info = a.take<int32_t>(F); d_cnt = a.take<long long>(F);
     d_stats = a.take<double>(4 * 256); d_sse = a.take<double>(S_all);
     d_part = a.take<float>((size_t)tiles_total * S_all);
+    if (score_tc) {
+      d_Whi = a.take<float>((size_t)S_all * ldw); d_Wlo = a.take<float>((size_t)S_all * ldw);
+      d_part_tc = a.take<double>((size_t)ctx->n_sms * 4 * S_all);
+    }
     if (!pass) { int rc = ensure_ws(ctx, a.off + 256); if (rc) return rc; }
   }
   CUtensorMap mXg;
@@ -810,7 +872,13 @@ extern "C" int dml_ridge_sweep(dml_ctx* ctx, const float* X, int64_t n, int d, i
       KCHECK();
       tc::XtyParams xp{X, ldx, n, d, T, lab, d_bmask, is_classifier ? nullptr : y_reg, is_classifier ? y_cls : nullptr,
                        xty_rows, xty_chunks, d_xty};
-      tc::xty_kernel<<<dim3((unsigned)xty_chunks, (unsigned)nf), 256, 0, st>>>(xp);
+      {
+        const dim3 xg((unsigned)xty_chunks, (unsigned)nf);
+        if (d <= 512 && T <= 2) tc::xty_kernel<2, 2><<<xg, 256, 0, st>>>(xp);
+        else if (d <= 512) tc::xty_kernel<2, 16><<<xg, 256, 0, st>>>(xp);
+        else if (T <= 2) tc::xty_kernel<4, 2><<<xg, 256, 0, st>>>(xp);
+        else tc::xty_kernel<4, 16><<<xg, 256, 0, st>>>(xp);
+      }
       KCHECK();
       tc::GramReduceParams rp{d_Mpart, splits, nb, ldm_tc, d_xty, xty_chunks, d, T, dst};
       tc::gram_reduce_kernel<<<dim3((unsigned)cdiv(D, 128), D, nf), 128, 0, st>>>(rp);
@@ -856,7 +924,7 @@ extern "C" int dml_ridge_sweep(dml_ctx* ctx, const float* X, int64_t n, int d, i
         chol_attr = true;
       }
       const int threads = (int)std::min<int64_t>(640, rup(d, 32));
-      ridge_cholesky_blocked_kernel<<<nsys, threads, chol_smem, st>>>(d_A, d_B, d, T, d_info + c0 * fpc);
+      ridge_cholesky_blocked_kernel<<<nsys, threads, chol_smem, st>>>(d_A, d_AT, d_B, d, T, d_info + c0 * fpc);
     } else {
       ridge_cholesky_kernel<<<nsys, 512, d * sizeof(double), st>>>(d_A, d_B, d, T, d_info + c0 * fpc);
     }
@@ -867,16 +935,24 @@ extern "C" int dml_ridge_sweep(dml_ctx* ctx, const float* X, int64_t n, int d, i
   }
   if (info_out) CU(cudaMemcpyAsync(info_out, d_info, sizeof(int32_t) * F, cudaMemcpyDeviceToDevice, st));
   // ---- score every fit on its held-out rows ----
-  int rc = run_score(ctx, is_classifier ? FWD_SCORE_CLS : FWD_SCORE_REG, X, n, d, ldx, y_cls, y_reg, fold_id, hold_id,
-                     d_Wt, ldw, d_bt, d_sel, d_val, (int)S_all, T, d_part);
+  int rc; int64_t n_parts = tiles_total; const void* parts = d_part;
+  if (score_tc) {
+    rc = run_score_tc(ctx, is_classifier ? FWD_SCORE_CLS : FWD_SCORE_REG, X, n, d, ldx, y_cls, y_reg, fold_id, hold_id,
+                      d_Wt, ldw, d_bt, d_sel, d_val, (int)S_all, T, d_Whi, d_Wlo, d_part_tc, &n_parts);
+    parts = d_part_tc;
+  } else {
+    rc = run_score(ctx, is_classifier ? FWD_SCORE_CLS : FWD_SCORE_REG, X, n, d, ldx, y_cls, y_reg, fold_id, hold_id,
+                   d_Wt, ldw, d_bt, d_sel, d_val, (int)S_all, T, d_part);
+  }
   if (rc) return rc;
   if (is_classifier) {
-    reduce_counts_kernel<<<F, 256, 0, st>>>((const int32_t*)d_part, tiles_total, (int)S_all, T, d_cnt);
+    reduce_counts_kernel<<<F, 256, 0, st>>>((const int32_t*)parts, n_parts, (int)S_all, T, d_cnt);
     KCHECK();
     if (ctx->comm) { rc = allreduce(ctx, d_cnt, F, kNcclInt64); if (rc) return rc; }
     if (correct_out) CU(cudaMemcpyAsync(correct_out, d_cnt, sizeof(int64_t) * F, cudaMemcpyDeviceToDevice, st));
   } else {
-    reduce_sse_kernel<<<(unsigned)S_all, 256, 0, st>>>((const float*)d_part, tiles_total, (int)S_all, d_sse);
+    if (score_tc) reduce_sse_parts_kernel<<<(unsigned)cdiv(S_all, 128), 128, 0, st>>>((const double*)parts, n_parts, (int)S_all, d_sse);
+    else reduce_sse_kernel<<<(unsigned)S_all, 256, 0, st>>>((const float*)d_part, tiles_total, (int)S_all, d_sse);
     KCHECK();
     if (ctx->comm) { rc = allreduce(ctx, d_sse, S_all, kNcclFloat64); if (rc) return rc; }
     if (sse_out) CU(cudaMemcpyAsync(sse_out, d_sse, sizeof(double) * S_all, cudaMemcpyDeviceToDevice, st));

@@ -125,7 +125,9 @@ __global__ void __launch_bounds__(512) ridge_cholesky_kernel(double* Aall, doubl
 // factored, and written back once.  Same result as the column-by-column kernel above up to fp64
 // rounding; ~100x less memory traffic (the rank-1 version rewrites the trailing matrix d times).
 constexpr int kCholNB = 32, kCholMaxD = 640;
-__global__ void __launch_bounds__(640) ridge_cholesky_blocked_kernel(double* Aall, double* Ball, int d, int T, int* info) {
+// `ATall` receives L^T (row j of AT = column j of L): with one thread per matrix row, the panel update
+// and the forward substitution walk L by columns, which is contiguous (coalesced) only in L^T.
+__global__ void __launch_bounds__(640) ridge_cholesky_blocked_kernel(double* Aall, double* ATall, double* Ball, int d, int T, int* info) {
   extern __shared__ double sm[];
   constexpr int NB = kCholNB, PP = NB + 1;
   double* P = sm;                     // [d][PP] panel rows k0..d-1
@@ -133,6 +135,7 @@ __global__ void __launch_bounds__(640) ridge_cholesky_blocked_kernel(double* Aal
   __shared__ double piv;
   __shared__ int bad;
   double* A = Aall + (int64_t)blockIdx.x * d * d;
+  double* AT = ATall + (int64_t)blockIdx.x * d * d;
   double* B = Ball + (int64_t)blockIdx.x * T * d;
   const int t = threadIdx.x;
   if (t == 0) bad = 0;
@@ -150,10 +153,10 @@ __global__ void __launch_bounds__(640) ridge_cholesky_blocked_kernel(double* Aal
       }
       __syncthreads();
       if (t < nr) {
-        const double* ar = A + (int64_t)r * d + j0;
-#pragma unroll 4
+        const double* at = AT + (int64_t)j0 * d + r;   // L[r][j0 + jj] = AT[j0 + jj][r]: coalesced over threads
+#pragma unroll 8
         for (int jj = 0; jj < NB; ++jj) {
-          const double a = ar[jj];
+          const double a = at[(int64_t)jj * d];
           const double2* lk = reinterpret_cast<const double2*>(Lk + jj * (NB + 2));
 #pragma unroll
           for (int c2 = 0; c2 < NB / 2; ++c2) { const double2 l = lk[c2]; acc[2 * c2] = fma(a, l.x, acc[2 * c2]); acc[2 * c2 + 1] = fma(a, l.y, acc[2 * c2 + 1]); }
@@ -182,26 +185,29 @@ __global__ void __launch_bounds__(640) ridge_cholesky_blocked_kernel(double* Aal
       __syncthreads();
       if (t > j && t < nr) {
         const double ltj = P[(size_t)t * PP + j];
-        // columns j+1 .. min(t, nc-1) of this row
-        const int cend = min(t, nc - 1);
+        const int cend = min(t, nc - 1);               // columns j+1 .. min(t, nc-1) of this row
         for (int c = j + 1; c <= cend; ++c) P[(size_t)t * PP + c] -= ltj * P[(size_t)c * PP + j];
       }
-      __syncthreads();
     }
+    __syncthreads();
     if (t < nr) {
-      for (int c = 0; c < nc; ++c) if (k0 + c <= r) A[(int64_t)r * d + k0 + c] = P[(size_t)t * PP + c];
+      for (int c = 0; c < nc; ++c) {
+        const double v = (k0 + c <= r) ? P[(size_t)t * PP + c] : 0.0;
+        if (k0 + c <= r) A[(int64_t)r * d + k0 + c] = v;
+        AT[(int64_t)(k0 + c) * d + r] = v;             // coalesced over threads
+      }
     }
     __syncthreads();
   }
   if (t == 0 && bad) atomicExch(info + blockIdx.x, bad);
-  // forward then backward substitution, one right-hand side at a time
+  // forward (columns of L = rows of L^T) then backward (rows of L) substitution, one right-hand side at a time
   for (int tt = 0; tt < T; ++tt) {
     double* b = B + (int64_t)tt * d;
     for (int j = 0; j < d; ++j) {
       if (t == 0) { piv = b[j] / A[(int64_t)j * d + j]; b[j] = piv; }
       __syncthreads();
       const double zj = piv;
-      for (int i = j + 1 + t; i < d; i += blockDim.x) b[i] -= A[(int64_t)i * d + j] * zj;
+      for (int i = j + 1 + t; i < d; i += blockDim.x) b[i] -= AT[(int64_t)j * d + i] * zj;
       __syncthreads();
     }
     for (int j = d - 1; j >= 0; --j) {

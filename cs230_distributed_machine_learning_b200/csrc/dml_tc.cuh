@@ -1042,11 +1042,11 @@ struct XtyParams {
   int64_t rows_per_chunk; int chunks;
   float* part;   // [folds][chunks][d + 2][1 + T]
 };
+template <int JMAX, int TMAX>   // features per thread (d <= 256 * JMAX), targets (T <= TMAX)
 __global__ void __launch_bounds__(256) xty_kernel(const XtyParams p) {
   const int fold = blockIdx.y, ch = blockIdx.x;
   const int64_t r0 = (int64_t)ch * p.rows_per_chunk, r1 = min(p.n, r0 + p.rows_per_chunk);
   const int T = p.T, W = 1 + T;
-  constexpr int JMAX = 4, TMAX = 16;                 // d <= 1024, T <= 16 (checked by the host)
   float ax[JMAX], axy[JMAX][TMAX];
 #pragma unroll
   for (int a = 0; a < JMAX; ++a) { ax[a] = 0.f;
@@ -1055,32 +1055,41 @@ __global__ void __launch_bounds__(256) xty_kernel(const XtyParams p) {
   float cnt = 0.f, sy[TMAX], syy[TMAX];
 #pragma unroll
   for (int t = 0; t < TMAX; ++t) { sy[t] = 0.f; syy[t] = 0.f; }
-  for (int64_t r = r0; r < r1; ++r) {
-    if ((r & 15) == 0 && !((p.blockmask[r >> 4] >> fold) & 1u)) { r += 15; continue; }
-    if (p.label[r] != fold) continue;
-    float yv[TMAX];
+  constexpr int U = 8;                                  // rows in flight per thread (the pass is latency-bound otherwise)
+  for (int64_t r = r0; r < r1; r += U) {                // r0 and the chunk length are multiples of 16
+    if (!((p.blockmask[r >> 4] >> fold) & 1u)) continue;
+    bool in[U]; float xv[U][JMAX];
 #pragma unroll
-    for (int t = 0; t < TMAX; ++t) {
-      if (t < T) {
-        if (p.yreg) yv[t] = p.yreg[r];
-        else { const int c = p.ycls[r]; yv[t] = (T == 1 ? (c == 1) : (c == t)) ? 1.f : -1.f; }
-      } else yv[t] = 0.f;
-    }
-    const float* xr = p.X + r * p.ldx;
+    for (int u = 0; u < U; ++u) in[u] = (r + u < r1) && (p.label[r + u] == fold);
 #pragma unroll
-    for (int a = 0; a < JMAX; ++a) {
-      const int j = threadIdx.x + a * 256;
-      if (j < p.d) {
-        const float x = __ldg(xr + j);
-        ax[a] += x;
+    for (int u = 0; u < U; ++u)
 #pragma unroll
-        for (int t = 0; t < TMAX; ++t) if (t < T) axy[a][t] = fmaf(x, yv[t], axy[a][t]);
+      for (int a = 0; a < JMAX; ++a) {
+        const int j = threadIdx.x + a * 256;
+        xv[u][a] = (in[u] && j < p.d) ? __ldg(p.X + (r + u) * p.ldx + j) : 0.f;
       }
-    }
-    if (threadIdx.x == 0) {
-      cnt += 1.f;
 #pragma unroll
-      for (int t = 0; t < TMAX; ++t) if (t < T) { sy[t] += yv[t]; syy[t] = fmaf(yv[t], yv[t], syy[t]); }
+    for (int u = 0; u < U; ++u) {
+      if (!in[u]) continue;
+      float yv[TMAX];
+#pragma unroll
+      for (int t = 0; t < TMAX; ++t) {
+        if (t < T) {
+          if (p.yreg) yv[t] = p.yreg[r + u];
+          else { const int c = p.ycls[r + u]; yv[t] = (T == 1 ? (c == 1) : (c == t)) ? 1.f : -1.f; }
+        } else yv[t] = 0.f;
+      }
+#pragma unroll
+      for (int a = 0; a < JMAX; ++a) {
+        ax[a] += xv[u][a];
+#pragma unroll
+        for (int t = 0; t < TMAX; ++t) if (t < T) axy[a][t] = fmaf(xv[u][a], yv[t], axy[a][t]);
+      }
+      if (threadIdx.x == 0) {
+        cnt += 1.f;
+#pragma unroll
+        for (int t = 0; t < TMAX; ++t) if (t < T) { sy[t] += yv[t]; syy[t] = fmaf(yv[t], yv[t], syy[t]); }
+      }
     }
   }
   float* out = p.part + ((int64_t)fold * p.chunks + ch) * (p.d + 2) * W;
