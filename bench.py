@@ -35,7 +35,7 @@ METRIC, UNIT = "candidate_fold_fits_per_sec", "fits/s"
 def parse():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--steps", type=int, default=20)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--rows", type=int, default=N_ROWS)       # smaller sizes are for debugging only
@@ -54,44 +54,59 @@ def workload_name(a, n_cand_total):
 
 # ------------------------------------------------------------------------------------------
 class ClockSampler(threading.Thread):
-    """nvidia-smi clocks / throttle reasons during the timed region (B200_PROFILING.md recipe)."""
-    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown,"
-         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
-         "clocks_event_reasons.sw_power_cap")
+    """SM clock and throttle reasons DURING the timed region: NVML every 10 ms (the nvidia-smi query of
+    B200_PROFILING.md, one process per sample, is the fallback when the NVML binding is missing)."""
+    REASONS = {0x4: "sw_power_cap", 0x8: "hw_slowdown", 0x20: "sw_thermal_slowdown", 0x40: "hw_thermal_slowdown"}
 
     def __init__(self, gpu_index: int):
         super().__init__(daemon=True)
-        self.gpu_index, self.stop_ev, self.rows = gpu_index, threading.Event(), []
+        self.gpu_index, self.stop_ev = gpu_index, threading.Event()
+        self.sm, self.mx, self.reasons = [], [], set()
+        try:
+            import pynvml
+            pynvml.nvmlInit()
+            self.nv, self.h = pynvml, pynvml.nvmlDeviceGetHandleByIndex(gpu_index)
+        except Exception:
+            self.nv = None
+
+    def sample(self):
+        if self.nv is not None:
+            nv = self.nv
+            self.sm.append(float(nv.nvmlDeviceGetClockInfo(self.h, nv.NVML_CLOCK_SM)))
+            self.mx.append(float(nv.nvmlDeviceGetMaxClockInfo(self.h, nv.NVML_CLOCK_SM)))
+            try:
+                bits = nv.nvmlDeviceGetCurrentClocksEventReasons(self.h)
+            except Exception:
+                bits = nv.nvmlDeviceGetCurrentClocksThrottleReasons(self.h)
+            for bit, name in self.REASONS.items():
+                if bits & bit:
+                    self.reasons.add(name)
+            return
+        q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+             "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+        out = subprocess.run(["nvidia-smi", f"--query-gpu={q}", "--format=csv,noheader,nounits", "-i",
+                              str(self.gpu_index)], capture_output=True, text=True, timeout=5).stdout
+        r = [c.strip() for c in out.strip().split(",")]
+        self.sm.append(float(r[0])); self.mx.append(float(r[1]))
+        for name, v in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), r[2:]):
+            if v.lower().startswith("active"):
+                self.reasons.add(name)
 
     def run(self):
         while not self.stop_ev.is_set():
             try:
-                out = subprocess.run(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
-                                      "-i", str(self.gpu_index)], capture_output=True, text=True, timeout=5).stdout
-                for line in out.strip().splitlines():
-                    self.rows.append([c.strip() for c in line.split(",")])
+                self.sample()
             except Exception:
                 pass
-            self.stop_ev.wait(0.2)
+            self.stop_ev.wait(0.01 if self.nv is not None else 0.2)
 
     def summary(self):
         self.stop_ev.set()
         self.join(timeout=6)
-        sm, mx, reasons = [], [], set()
-        for r in self.rows:
-            try:
-                sm.append(float(r[1])); mx.append(float(r[2]))
-            except Exception:
-                continue
-            for name, col in (("hw_slowdown", 5), ("hw_thermal_slowdown", 6), ("sw_thermal_slowdown", 7),
-                              ("sw_power_cap", 8)):
-                if len(r) > col and r[col].lower().startswith("active"):
-                    reasons.add(name)
-        sm.sort()
-        # "under load" = samples in the upper half (idle samples between steps excluded)
-        load = sm[len(sm) // 2:] if sm else []
-        return {"sm_mhz": float(np.median(load)) if load else None, "sm_max_mhz": max(mx) if mx else None,
-                "reasons": sorted(reasons), "samples": len(sm)}
+        return {"sm_mhz": float(np.median(self.sm)) if self.sm else None,
+                "sm_max_mhz": max(self.mx) if self.mx else None,
+                "reasons": sorted(self.reasons), "samples": len(self.sm),
+                "source": "nvml" if self.nv is not None else "nvidia-smi"}
 
 
 def measured_peaks():
@@ -103,7 +118,9 @@ def measured_peaks():
 
 
 def measure_tf32_peak(torch):
-    """cuBLAS TF32 GEMM 8192^3, best of 10 (same method as MEASURED_PEAKS.json uses for bf16)."""
+    """cuBLAS TF32 GEMM 8192^3 the way MEASURED_PEAKS.json measures bf16: best of 10 (burst, for a kernel
+    timed alone) and back to back for ~2 s (sustained, under the power cap: the figure that applies to
+    kernels timed inside a long step).  Returns (burst, sustained) in TFLOP/s."""
     old = torch.backends.cuda.matmul.allow_tf32
     torch.backends.cuda.matmul.allow_tf32 = True
     try:
@@ -115,7 +132,15 @@ def measure_tf32_peak(torch):
             e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
             e0.record(); a @ b; e1.record(); torch.cuda.synchronize()
             best = min(best, e0.elapsed_time(e1))
-        return 2 * 8192 ** 3 / (best * 1e-3) / 1e12
+        flops = 2 * 8192 ** 3
+        reps = max(50, int(2000.0 / best))
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(reps):
+            a @ b
+        e1.record(); torch.cuda.synchronize()
+        sustained = flops * reps / (e0.elapsed_time(e1) * 1e-3) / 1e12
+        return flops / (best * 1e-3) / 1e12, sustained
     finally:
         torch.backends.cuda.matmul.allow_tf32 = old
 
@@ -274,7 +299,7 @@ def run_b200(a):
 
     if rank == 0:
         peaks, src = measured_peaks()
-        p_tf32 = measure_tf32_peak(torch)
+        p_burst, p_tf32 = measure_tf32_peak(torch)   # the sweep is a long step: sustained figure
         p3 = p_tf32 / 3.0
         n_tr = a.rows * (CV - 1) / CV
         # algorithmic flops: every column-round is one pass of the training rows through one
@@ -296,7 +321,9 @@ def run_b200(a):
             "roofline": {"bound": "tensor", "achieved": ach, "peak": p3, "unit": "TFLOP/s",
                          "frac": (ach / p3) if ach else None, "traffic": None,
                          "kernel": "forward+gradient contraction pair per batched round",
-                         "peak_source": f"cuBLAS TF32 8192^3 measured in this run = {p_tf32:.1f} TFLOP/s, /3 for 3xTF32",
+                         "peak_source": f"cuBLAS TF32 8192^3 measured in this run, sustained over ~2 s = {p_tf32:.1f} TFLOP/s "
+                                        f"(burst {p_burst:.1f}); /3 for 3xTF32; MEASURED_PEAKS.json has no TF32 entry",
+                         "burst_frac": (ach / (p_burst / 3.0)) if ach else None,
                          "naive_tf32_frac": (ach / p_tf32) if ach else None,
                          "hbm_achieved_gbs": hbm_ach, "hbm_peak_gbs": peaks.get("hbm_gbs"), "hbm_peak_source": src,
                          "kernel_ms_per_step": contraction_ms / a.steps,
