@@ -269,7 +269,9 @@ def run_b200(a):
         from sklearn.model_selection import GridSearchCV
         from cs230_distributed_machine_learning_b200 import worker as wk
         from cs230_distributed_machine_learning_b200.client import LocalBackend, MLTaskManager
-        register_dataset("bench-cfg2", X, y)
+        names = ["bench-cfg2-a", "bench-cfg2-b"]     # a stream of jobs on alternating datasets
+        for nm in names:
+            register_dataset(nm, X, y)
         ds = None
         solver.close()
         del solver
@@ -278,22 +280,46 @@ def run_b200(a):
         mgr = MLTaskManager(backend)
         est = GridSearchCV(LogisticRegression(), {"C": [float(c) for c in Cs]}, cv=CV)
         ex = wk.gpu_executor(local_rank)
-        k_e2e = max(1, min(a.steps, 3))
-        r = mgr.train(est, "bench-cfg2", wait_for_completion=True)      # warm-up (module import, arena)
-        assert r.get("job_status") == "completed", r
+        # the worker may keep 1.5 datasets: the one a job reads plus the next one arriving, so
+        # EVERY job pays the full host->device copy of its X and y inside the timed region
+        ex.max_resident_bytes = int(1.5 * X.nbytes)
+        for nm in names:                                                 # warm-up (module import, arena, labels)
+            r = mgr.train(est, nm, wait_for_completion=True)
+            assert r.get("job_status") == "completed", r
+        k_ser = max(1, min(a.steps, 4))
         barrier()
         t0 = time.perf_counter()
-        h2d0, d2h0 = ex.solver.h2d_bytes, ex.solver.d2h_bytes
-        for _ in range(k_e2e):
-            ex.drop_resident()                      # every step pays the host->device copy of X, y
-            r = mgr.train(est, "bench-cfg2", wait_for_completion=True)
+        for i in range(k_ser):                                           # one job at a time: copy, then sweep
+            r = mgr.train(est, names[i % 2], wait_for_completion=True)
+            assert r["job_status"] == "completed"
+        torch.cuda.synchronize()
+        t_ser = ddist.max_over_ranks(time.perf_counter() - t0, device=dev)
+        k_e2e = max(2, a.steps)
+        barrier()
+        t0 = time.perf_counter()
+        h2d0, d2h0, pf0 = ex.solver.h2d_bytes, ex.solver.d2h_bytes, ex.prefetched
+        for v in ex.stats.values():
+            v.clear()
+        jobs = []
+        for i in range(k_e2e):                                           # the queue holds the next job: its copy
+            resp = mgr.train(est, names[i % 2], wait_for_completion=False)   # runs beside the current sweep
+            assert resp.get("status") == "Training started", resp
+            jobs.append(mgr.job_id)
+        for j in jobs:
+            r = mgr._wait_for_completion(j)
             assert r["job_status"] == "completed"
         torch.cuda.synchronize()
         t_e2e = ddist.max_over_ranks(time.perf_counter() - t0, device=dev)
         e2e = {"value": n_cand_total * CV * k_e2e / t_e2e, "unit": UNIT,
                "h2d_bytes_per_step": (ex.solver.h2d_bytes - h2d0) // k_e2e,
                "d2h_bytes_per_step": (ex.solver.d2h_bytes - d2h0) // k_e2e,
-               "api": "MLTaskManager.train(GridSearchCV(...), wait_for_completion=True)", "steps": k_e2e,
+               "api": "MLTaskManager.train(GridSearchCV(...)) x steps, then _wait_for_completion per job",
+               "steps": k_e2e, "ms_per_step": t_e2e / k_e2e * 1e3,
+               "overlap": "the worker copies job i+1's dataset on a copy stream while job i's sweep runs; "
+                          f"{ex.prefetched - pf0} of {k_e2e} copies were started that way",
+               "one_job_at_a_time": {"value": n_cand_total * CV * k_ser / t_ser, "steps": k_ser,
+                                     "ms_per_step": t_ser / k_ser * 1e3},
+               "per_job_ms": {k: (float(np.mean(v)) if v else None) for k, v in ex.stats.items()},
                "best_params_": r["job_result"]["best_params_"]}
         mgr.close()
 

@@ -532,7 +532,7 @@ struct EvalCtx {
         reduce_grad_kernel<<<n_slots, 256, 0, st>>>(rp);
         tc::TcReduceParams tr{lossPart, gbPart, (int64_t)grid * 4, n_slots, T, d, Gred, ldgr, ci > 0 ? 1 : 0,
                               hist_local, sel, val, n, (double)loss_shift()};
-        tc::tc_reduce_tiles_kernel<<<(unsigned)cdiv(n_slots, 32), dim3(32, 8), 0, st>>>(tr);
+        tc::tc_reduce_tiles_kernel<<<(unsigned)cdiv(n_slots, 32), dim3(32, 32), 0, st>>>(tr);
       } else {
         const int ldr = (int)rup(n_slots, 4);
         FwdParams fp{};
@@ -592,6 +592,14 @@ struct EvalCtx {
     return run_score(ctx, FWD_SCORE_CLS, X, n, d, ldx, y, nullptr, fold_id, hold_id, Wt, ldw, bt, sel, val, n_slots, T, cntPart);
   }
 };
+
+__global__ void fill_n_test_kernel(const unsigned long long* __restrict__ hist, int F, int fpc, int n_folds,
+                                   int64_t* __restrict__ n_test) {
+  const int f = blockIdx.x * blockDim.x + threadIdx.x;
+  if (f >= F) return;
+  const int k = f % fpc;
+  n_test[f] = (int64_t)(k < n_folds ? hist[k] : hist[256 + 1]);
+}
 
 extern "C" int dml_logreg_sweep(dml_ctx* ctx, const float* X, int64_t n, int d, int64_t ldx,
                                 const int32_t* y, int n_classes,
@@ -697,15 +705,9 @@ extern "C" int dml_logreg_sweep(dml_ctx* ctx, const float* X, int64_t n, int d, 
     KCHECK();
     if (ctx->comm) { rc = allreduce(ctx, d_correct, F, kNcclInt64); if (rc) return rc; }
     if (correct_out) CU(cudaMemcpyAsync(correct_out, d_correct, sizeof(int64_t) * F, cudaMemcpyDeviceToDevice, st));
-    if (n_test_out) {
-      // n_test of fit (cand, k) = histogram entry of its mask
-      std::vector<unsigned long long> h(512);
-      CU(cudaMemcpyAsync(h.data(), d_hist, 512 * sizeof(unsigned long long), cudaMemcpyDeviceToHost, st));
-      CU(cudaStreamSynchronize(st));
-      std::vector<int64_t> nt_h(F);
-      for (int f = 0; f < F; ++f) { const int k = f % fpc; nt_h[f] = (int64_t)(k < n_folds ? h[k] : h[256 + 1]); }
-      CU(cudaMemcpyAsync(n_test_out, nt_h.data(), sizeof(int64_t) * F, cudaMemcpyHostToDevice, st));
-      CU(cudaStreamSynchronize(st));
+    if (n_test_out) {   // n_test of fit (cand, k) = histogram entry of its mask
+      fill_n_test_kernel<<<(unsigned)cdiv(F, 256), 256, 0, st>>>(d_hist, F, fpc, n_folds, n_test_out);
+      KCHECK();
     }
     ctx->total_launches += 1;
   }

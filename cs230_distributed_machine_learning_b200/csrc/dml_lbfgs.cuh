@@ -329,15 +329,17 @@ __global__ void reduce_grad_kernel(const ReduceParams p) {
   const int64_t stride = (int64_t)p.n_slots * p.ldg;
   for (int j = threadIdx.x; j < p.jcount; j += blockDim.x) {
     const float* src = p.Gpart + (int64_t)slot * p.ldg + j;
-    double a0 = 0.0, a1 = 0.0, a2 = 0.0, a3 = 0.0;   // fixed association: deterministic
+    double a[8] = {0.0, 0.0, 0.0, 0.0, 0.0, 0.0, 0.0, 0.0};   // 8 independent chains; fixed association: deterministic
     int s = 0;
-    for (; s + 4 <= p.splits; s += 4) {
-      const float v0 = src[(int64_t)(s + 0) * stride], v1 = src[(int64_t)(s + 1) * stride];
-      const float v2 = src[(int64_t)(s + 2) * stride], v3 = src[(int64_t)(s + 3) * stride];
-      a0 += (double)v0; a1 += (double)v1; a2 += (double)v2; a3 += (double)v3;
+    for (; s + 8 <= p.splits; s += 8) {
+      float v[8];
+#pragma unroll
+      for (int u = 0; u < 8; ++u) v[u] = src[(int64_t)(s + u) * stride];
+#pragma unroll
+      for (int u = 0; u < 8; ++u) a[u] += (double)v[u];
     }
-    for (; s < p.splits; ++s) a0 += (double)src[(int64_t)s * stride];
-    const double acc = (a0 + a1) + (a2 + a3);
+    for (; s < p.splits; ++s) a[0] += (double)src[(int64_t)s * stride];
+    const double acc = ((a[0] + a[1]) + (a[2] + a[3])) + ((a[4] + a[5]) + (a[6] + a[7]));
     double* q = p.Gred + (int64_t)slot * p.ldgr + j;
     *q = p.accumulate ? *q + acc : acc;
   }

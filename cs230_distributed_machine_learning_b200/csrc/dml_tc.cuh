@@ -1156,12 +1156,12 @@ struct TcReduceParams {
   // the forward kernel sums (loss - ln 2): add ln 2 * (training rows of the column) back once
   const unsigned long long* hist_local; const int32_t* sel; const int32_t* val; int64_t n_local; double loss_shift;
 };
-__global__ void tc_reduce_tiles_kernel(const TcReduceParams p) {
-  __shared__ double sh[2][8][33];
+__global__ void tc_reduce_tiles_kernel(const TcReduceParams p) {   // block (32 slots, 32 partial lanes)
+  __shared__ double sh[2][32][33];
   const int slot = blockIdx.x * 32 + threadIdx.x;
   double a = 0.0, b = 0.0;
   if (slot < p.n_slots)
-    for (int64_t t = threadIdx.y; t < p.n_parts; t += 8) {
+    for (int64_t t = threadIdx.y; t < p.n_parts; t += 32) {
       a += p.lossPart[t * p.n_slots + slot];
       b += p.gbPart[t * p.n_slots + slot];
     }
@@ -1169,7 +1169,7 @@ __global__ void tc_reduce_tiles_kernel(const TcReduceParams p) {
   __syncthreads();
   if (threadIdx.y == 0 && slot < p.n_slots) {
     double l = 0.0, g = 0.0;
-    for (int i = 0; i < 8; ++i) { l += sh[0][i][threadIdx.x]; g += sh[1][i][threadIdx.x]; }
+    for (int i = 0; i < 32; ++i) { l += sh[0][i][threadIdx.x]; g += sh[1][i][threadIdx.x]; }   // fixed order
     double* q = p.Gred + (int64_t)slot * p.ldgr;
     q[p.d] = p.accumulate ? q[p.d] + g : g;
     if (!p.accumulate)

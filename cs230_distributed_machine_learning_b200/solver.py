@@ -28,6 +28,12 @@ class DeviceDataset:
     classes: np.ndarray | None      # sorted unique labels (sklearn classes_)
     n: int
     d: int
+    ready: object = None            # CUDA event of an upload still in flight on a copy stream
+    copy_events: object = None      # (start, end) events of that upload, for the worker's statistics
+
+    @property
+    def nbytes(self) -> int:
+        return sum(t.numel() * t.element_size() for t in (self.X, self.y_cls, self.y_reg) if t is not None)
 
 
 class SweepSolver:
@@ -41,7 +47,8 @@ class SweepSolver:
         self.lib = self.ctx.lib
         self.h2d_bytes = 0
         self.d2h_bytes = 0
-        self._class_cache: dict[int, tuple] = {}
+        self._class_cache: dict[tuple, tuple] = {}
+        self._param_buf = torch.empty(1 << 16, dtype=torch.uint8, pin_memory=True)
 
     # ---- plumbing -------------------------------------------------------------------
     def to_device(self, a, dtype=None, pin: bool = False) -> torch.Tensor:
@@ -62,28 +69,62 @@ class SweepSolver:
         self.h2d_bytes += t.numel() * t.element_size()
         return t.to(self.device, non_blocking=True)
 
+    def params(self, *arrays):
+        """Small per-candidate arrays handed to the library without a copy engine: they are
+        written into one page-locked buffer, which the device reads in place (pinned host memory
+        is device-addressable under UVA).  A host->device copy here would queue behind a dataset
+        prefetch on the same DMA engine and hold the sweep back for the whole transfer."""
+        arrays = [np.ascontiguousarray(a) for a in arrays]
+        need = sum((a.nbytes + 255) // 256 * 256 for a in arrays)
+        if need > self._param_buf.numel():
+            self._param_buf = torch.empty(2 * need, dtype=torch.uint8, pin_memory=True)
+        host = self._param_buf.numpy()
+        base, off, ptrs = self._param_buf.data_ptr(), 0, []
+        for a in arrays:
+            host[off:off + a.nbytes] = a.view(np.uint8).reshape(-1)
+            ptrs.append(C.c_void_p(base + off))
+            off += (a.nbytes + 255) // 256 * 256
+            self.h2d_bytes += a.nbytes
+        return ptrs
+
     def to_host(self, t: torch.Tensor) -> np.ndarray:
         self.d2h_bytes += t.numel() * t.element_size()
         return t.cpu().numpy()
 
-    def upload_dataset(self, X, y, classifier: bool) -> DeviceDataset:
-        """X (n, d) any float dtype -> fp32 on device; y -> class indices or fp32."""
+    def upload_dataset(self, X, y, classifier: bool, stream=None) -> DeviceDataset:
+        """X (n, d) any float dtype -> fp32 on device; y -> class indices or fp32.
+        With ``stream`` the copies are queued there and ``ready`` holds the event to wait on."""
+        if stream is not None:
+            with torch.cuda.stream(stream):
+                t0 = torch.cuda.Event(enable_timing=True)
+                t0.record(stream)
+                ds = self.upload_dataset(X, y, classifier)
+                ds.ready = torch.cuda.Event(enable_timing=True)
+                ds.ready.record(stream)
+                ds.copy_events = (t0, ds.ready)
+            for t in (ds.X, ds.y_cls, ds.y_reg):
+                if t is not None:
+                    t.record_stream(self.stream)
+            return ds
         Xd = self.to_device(X, torch.float32)
         if Xd.dim() != 2:
             raise ValueError("X must be 2-D")
         n, d = Xd.shape
-        if classifier:
-            if isinstance(y, torch.Tensor):
-                y = y.cpu().numpy()
-            key = id(y)
-            if key not in self._class_cache:      # label encoding of a registered dataset is computed once
+        if isinstance(y, torch.Tensor):
+            y = y.cpu().numpy()
+        key = (id(y), classifier)
+        if key not in self._class_cache:      # label encoding of a registered dataset is computed once,
+            if classifier:                    # into page-locked memory so that its copy is asynchronous
                 classes, idx = np.unique(np.asarray(y), return_inverse=True)
-                self._class_cache[key] = (classes, idx.astype(np.int32), y)
-            classes, idx, _ = self._class_cache[key]
-            yc = self.to_device(idx, torch.int32)
-            return DeviceDataset(Xd, yc, None, classes, n, d)
-        yr = self.to_device(y, torch.float32)
-        return DeviceDataset(Xd, None, yr, None, n, d)
+                enc = torch.from_numpy(idx.astype(np.int32)).pin_memory()
+            else:
+                classes, enc = None, torch.from_numpy(np.ascontiguousarray(y, dtype=np.float32)).pin_memory()
+            self._class_cache[key] = (classes, enc, y)
+        classes, enc, _ = self._class_cache[key]
+        yd = self.to_device(enc)
+        if classifier:
+            return DeviceDataset(Xd, yd, None, classes, n, d)
+        return DeviceDataset(Xd, None, yd, None, n, d)
 
     def init_comm(self, n_ranks: int, rank: int, unique_id: bytes):
         self.ctx.init_comm(n_ranks, rank, unique_id)
@@ -101,10 +142,10 @@ class SweepSolver:
         dev = self.device
         fold_d = self.to_device(fold_id, torch.int8)
         hold_d = self.to_device(hold_id, torch.int8) if hold_id is not None else None
-        C_d = self.to_device(np.asarray(C_vals, dtype=np.float64))
-        tol_d = self.to_device(np.broadcast_to(np.asarray(tol, dtype=np.float64), (n_cand,)).copy())
-        fi_d = self.to_device(np.broadcast_to(np.asarray(fit_intercept, dtype=np.uint8), (n_cand,)).copy())
-        mi_d = self.to_device(np.broadcast_to(np.asarray(max_iter, dtype=np.int32), (n_cand,)).copy())
+        C_p, tol_p, fi_p, mi_p = self.params(
+            np.asarray(C_vals, dtype=np.float64), np.broadcast_to(np.asarray(tol, dtype=np.float64), (n_cand,)),
+            np.broadcast_to(np.asarray(fit_intercept, dtype=np.uint8), (n_cand,)),
+            np.broadcast_to(np.asarray(max_iter, dtype=np.int32), (n_cand,)))
         coef = torch.empty((F, T, ds.d), dtype=torch.float32, device=dev)
         icpt = torch.empty((F, T), dtype=torch.float32, device=dev)
         n_iter = torch.empty(F, dtype=torch.int32, device=dev)
@@ -115,7 +156,7 @@ class SweepSolver:
         rounds = C.c_int32(0)
         rc = self.lib.dml_logreg_sweep(
             self.ctx.handle, _ptr(ds.X), ds.n, ds.d, ds.X.stride(0), _ptr(ds.y_cls), n_classes,
-            _ptr(fold_d), n_folds, _ptr(hold_d), _ptr(C_d), _ptr(tol_d), _ptr(fi_d), _ptr(mi_d), n_cand,
+            _ptr(fold_d), n_folds, _ptr(hold_d), C_p, tol_p, fi_p, mi_p, n_cand,
             _ptr(coef), _ptr(icpt), _ptr(n_iter), _ptr(status), _ptr(nfev), _ptr(correct), _ptr(n_test),
             C.byref(rounds), int(use_tensor_cores))
         self.ctx.check(rc, "dml_logreg_sweep")
@@ -140,8 +181,8 @@ class SweepSolver:
         dev = self.device
         fold_d = self.to_device(fold_id, torch.int8)
         hold_d = self.to_device(hold_id, torch.int8) if hold_id is not None else None
-        a_d = self.to_device(np.asarray(alphas, dtype=np.float64))
-        fi_d = self.to_device(np.broadcast_to(np.asarray(fit_intercept, dtype=np.uint8), (n_cand,)).copy())
+        a_p, fi_p = self.params(np.asarray(alphas, dtype=np.float64),
+                                np.broadcast_to(np.asarray(fit_intercept, dtype=np.uint8), (n_cand,)))
         coef = torch.empty((F, T, ds.d), dtype=torch.float32, device=dev)
         icpt = torch.empty((F, T), dtype=torch.float32, device=dev)
         n_test = torch.empty(F, dtype=torch.int64, device=dev)
@@ -152,7 +193,7 @@ class SweepSolver:
         syy = torch.empty(F, dtype=torch.float64, device=dev) if not classifier else None
         rc = self.lib.dml_ridge_sweep(
             self.ctx.handle, _ptr(ds.X), ds.n, ds.d, ds.X.stride(0), _ptr(ds.y_reg), _ptr(ds.y_cls),
-            n_classes, 1 if classifier else 0, _ptr(fold_d), n_folds, _ptr(hold_d), _ptr(a_d), _ptr(fi_d), n_cand,
+            n_classes, 1 if classifier else 0, _ptr(fold_d), n_folds, _ptr(hold_d), a_p, fi_p, n_cand,
             _ptr(coef), _ptr(icpt), _ptr(correct), _ptr(n_test), _ptr(sse), _ptr(sy), _ptr(syy), _ptr(info),
             int(use_tensor_cores))
         self.ctx.check(rc, "dml_ridge_sweep")

@@ -136,25 +136,71 @@ class GpuExecutor:
 
     def __init__(self, gpu: int = 0):
         from .solver import SweepSolver   # raises without CUDA: no CPU fallback
+        import torch
         self.gpu = gpu
         self.solver = SweepSolver(gpu)
-        self.resident: dict[tuple[str, bool], object] = {}
+        self.resident: dict[tuple[str, bool], object] = {}   # insertion order = least recently used first
         self.labels: dict[tuple, np.ndarray] = {}     # host-side row labels, computed once per dataset
+        self.labels_dev: dict[tuple, object] = {}
         self.pinned: set[int] = set()
         self.lock = threading.Lock()
+        self.res_lock = threading.Lock()              # guards ``resident`` (prefetch runs beside a sweep)
+        self.copy_stream = torch.cuda.Stream(self.solver.device)
+        self.max_resident_bytes = int(0.7 * torch.cuda.get_device_properties(self.solver.device).total_memory)
+        self.in_use: tuple | None = None
+        self.hint: tuple | None = None                # dataset of the next queued task (prefetch_task)
+        self.prefetched = 0
+        self.stats = {"sweep_ms": [], "copy_ms": [], "host_ms": []}   # last jobs: GPU sweep, overlapped copy, wall
 
     def drop_resident(self):
         """Forget device copies (the next job pays the host->device copy again)."""
-        with self.lock:
+        with self.lock, self.res_lock:
             self.resident.clear()
+
+    def _evict(self, incoming: int = 0, keep: tuple | None = None):
+        """Least recently used first; never the dataset a sweep is reading, the one the
+        running task is about to read (``keep``) or a prefetched copy nobody has used yet.
+        The budget is soft: when nothing may go, the new copy is made anyway.  Call under res_lock."""
+        total = sum(v.nbytes for v in self.resident.values()) + incoming
+        for key in list(self.resident):
+            if total <= self.max_resident_bytes:
+                break
+            if key == self.in_use or key == keep or self.resident[key].ready is not None:
+                continue
+            total -= self.resident.pop(key).nbytes
+
+    def prefetch(self, name: str, classifier: bool) -> bool:
+        """Start the host->device copy of a dataset a queued task will need, on the copy
+        stream, while the current sweep runs (the reference parses the CSV again inside
+        every subtask, worker.py:425).  Returns True when a copy was queued."""
+        key = (name, classifier)
+        with self.res_lock:
+            if key in self.resident:
+                return False
+            X, y = datasets.get_dataset(name)
+            if X.dtype != np.float32:
+                return False
+            self._evict(incoming=X.nbytes)
+            self._pin(X)
+            self.resident[key] = self.solver.upload_dataset(X, y, classifier, stream=self.copy_stream)
+            self.prefetched += 1
+            return True
 
     def dataset(self, name: str, classifier: bool):
         key = (name, classifier)
-        if key not in self.resident:   # the reference re-parses the CSV per subtask (worker.py:425)
-            X, y = datasets.get_dataset(name)
-            self._pin(X)
-            self.resident[key] = self.solver.upload_dataset(X, y, classifier)
-        return self.resident[key]
+        with self.res_lock:
+            if key not in self.resident:   # the reference re-parses the CSV per subtask (worker.py:425)
+                X, y = datasets.get_dataset(name)
+                self._evict(incoming=X.nbytes)
+                self._pin(X)
+                self.resident[key] = self.solver.upload_dataset(X, y, classifier)
+            ds = self.resident.pop(key)
+            self.resident[key] = ds        # most recently used
+            self.in_use = key
+        if ds.ready is not None:           # uploaded by prefetch: order the sweep's stream after the copy
+            self.solver.stream.wait_event(ds.ready)
+            ds.ready = None
+        return ds
 
     def _pin(self, X: np.ndarray) -> None:
         """Page-lock a registered float32 array in place (once), so every later upload is a
@@ -180,13 +226,26 @@ class GpuExecutor:
             if hkey not in self.labels:
                 self.labels[hkey] = folds.holdout_labels(n, test_size, random_state)
             hold = self.labels[hkey]
-        return self.labels[key], hold
+        return self._on_device(key), (self._on_device(hkey) if hold is not None else None)
+
+    def _on_device(self, key):
+        """Row labels go to the GPU once per dataset and stay (1 byte per row)."""
+        import torch
+        if key not in self.labels_dev:
+            self.labels_dev[key] = self.solver.to_device(self.labels[key], torch.int8)
+        return self.labels_dev[key]
 
     def run(self, model_type: str, cands: list[dict], train_params: dict, dataset_id: str, model_dir: str) -> list[dict]:
         """cands: [{index, subtask_id, parameters}] -> result dict per candidate (A9 shape)."""
         classifier = model_type != "Ridge"
         with self.lock:
             ds = self.dataset(dataset_id, classifier)
+            hint, self.hint = self.hint, None
+            if hint is not None and hint != (dataset_id, classifier):
+                try:
+                    self.prefetch(*hint)          # the next task's copy runs beside this sweep
+                except Exception:
+                    pass
             X_host, y_host = datasets.get_dataset(dataset_id)
             cv = train_params.get("cv", 5)
             if not isinstance(cv, int):
@@ -204,6 +263,15 @@ class GpuExecutor:
                 out = self.solver.ridge_sweep(ds, fold, cv, [float(p.get("alpha", 1.0)) for p in P], fi,
                                               classifier=classifier, hold_id=hold)
             wall = time.time() - t0
+            if len(self.stats["sweep_ms"]) < 4096:
+                self.stats["sweep_ms"].append(out["timing"]["total_ms"])
+                self.stats["host_ms"].append(wall * 1e3)
+                if ds.copy_events is not None:      # the copy ended before the sweep began (wait_event)
+                    self.stats["copy_ms"].append(ds.copy_events[0].elapsed_time(ds.copy_events[1]))
+                    ds.copy_events = None
+            with self.res_lock:
+                self.in_use = None
+                self._evict()
         n_fits = len(cands) * (cv + (hold is not None))
         results = []
         for i, c in enumerate(cands):
@@ -301,6 +369,43 @@ def train_model(task: dict, gpu: int = 0, model_dir: str = "./models"):
     return ordered
 
 
+def _gpu_block_key(task) -> tuple | None:
+    """(dataset_id, classifier) when the b200 executor would take at least one candidate of the task."""
+    if not isinstance(task, dict) or "model_type" not in task or "dataset_id" not in task:
+        return None
+    try:
+        block = _as_block(task)
+        choice = _executor_choice(block)
+        if choice == "sklearn":
+            return None
+        if not any(gpu_eligible(block["model_type"], c["parameters"])[0] for c in block["candidates"]):
+            return None
+        if choice == "auto" and datasets.get_dataset(block["dataset_id"])[0].dtype != np.float32:
+            return None
+        return (block["dataset_id"], block["model_type"] != "Ridge")
+    except Exception:
+        return None       # a look-ahead never fails a task; the task itself reports the error
+
+
+def prefetch_task(task: dict, gpu: int = 0, current: dict | None = None) -> bool:
+    """Look one message ahead in the worker's queue: arrange for that task's dataset to be
+    copied to the GPU while ``current`` runs.  Only acts when this GPU already has an
+    executor (a b200 block ran before).  When ``current`` is itself a b200 block the copy
+    starts right after it has acquired its own dataset (GpuExecutor.run), so the two never
+    compete for the residency budget; otherwise it starts at once."""
+    ex = _EXECUTORS.get(gpu)
+    key = _gpu_block_key(task) if ex is not None else None
+    if key is None:
+        return False
+    if _gpu_block_key(current) is None:
+        try:
+            return ex.prefetch(*key)
+        except Exception:
+            return False
+    ex.hint = key
+    return True
+
+
 def process_task(task: dict, gpu: int = 0):
     """worker.py:366-387."""
     return train_model(task, gpu=gpu)
@@ -336,6 +441,10 @@ class Worker(threading.Thread):
                 break
             if key != self.worker_id:      # worker.py:185: skip messages keyed to another worker
                 continue
+            with self.queue.mutex:         # look one message ahead: its dataset copy overlaps this task
+                nxt = self.queue.queue[0] if self.queue.queue else None
+            if nxt is not None and nxt[0] == self.worker_id and nxt[1] is not None:
+                prefetch_task(nxt[1], gpu=self.gpu or 0, current=task)
             self.handle(task)
 
     def handle(self, task: dict):

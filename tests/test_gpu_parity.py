@@ -241,6 +241,45 @@ def test_api_end_to_end_best_params_equal_gridsearchcv():
         m.close()
 
 
+def test_queued_jobs_prefetch_their_dataset_and_match_blocking_runs():
+    """Jobs submitted without waiting: the worker starts the next job's host->device copy on its
+    copy stream while the current sweep runs.  Results equal the one-job-at-a-time results exactly."""
+    from sklearn.linear_model import LogisticRegression
+    from sklearn.model_selection import GridSearchCV
+    import cs230_distributed_machine_learning_b200 as pkg
+    from cs230_distributed_machine_learning_b200 import worker as wk
+    data = {}
+    for nm, seed in (("pf-a", 80), ("pf-b", 81)):
+        data[nm] = make_dataset("binary", 20_000, 64, seed=seed)
+        pkg.register_dataset(nm, *data[nm])
+    m = pkg.MLTaskManager("local://1")
+    try:
+        est = GridSearchCV(LogisticRegression(), {"C": [0.001, 0.1, 10.0]}, cv=3)
+        want = {}
+        for nm in data:
+            r = m.train(est, nm, wait_for_completion=True)
+            assert r["job_status"] == "completed", r
+            want[nm] = r["job_result"]["cv_results_"]["mean_test_score"]
+        ex = wk.gpu_executor(0)
+        old_budget, ex.max_resident_bytes = ex.max_resident_bytes, int(1.5 * data["pf-a"][0].nbytes)
+        before = ex.prefetched
+        order = ["pf-a", "pf-b", "pf-a", "pf-b", "pf-a", "pf-b"]
+        jobs = []
+        with ex.lock:                    # hold the first sweep back until every job is queued
+            for nm in order:
+                assert m.train(est, nm, wait_for_completion=False)["status"] == "Training started"
+                jobs.append(m.job_id)
+        for nm, j in zip(order, jobs):
+            r = m._wait_for_completion(j)
+            assert r["job_status"] == "completed", r
+            assert r["job_result"]["cv_results_"]["mean_test_score"] == want[nm]
+        assert ex.prefetched - before >= 4      # every job after the first found its copy already started
+        assert len(ex.resident) <= 2
+        ex.max_resident_bytes = old_budget
+    finally:
+        m.close()
+
+
 def test_medium_size_properties(solver):
     """Size-independent properties at a size the oracle cannot sweep in seconds (200k x 256, 16 C x 5 folds)."""
     X, y = make_dataset("binary", 200_000, 256, seed=2)

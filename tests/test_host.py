@@ -208,3 +208,67 @@ def test_cabi_library_exports_every_declared_symbol():
         h = ctypes.c_void_p()
         assert _cabi.load().dml_ctx_create(0, None, ctypes.byref(h)) != 0   # loud, not a crash
         assert b"CUDA" in _cabi.load().dml_last_error(None) or b"device" in _cabi.load().dml_last_error(None)
+
+
+# ---- dataset prefetch / residency (host logic only; the copies themselves are GPU tests) ----
+from cs230_distributed_machine_learning_b200 import worker as wk  # noqa: E402
+class _FakeDs:
+    def __init__(self, nbytes, ready=None):
+        self.nbytes, self.ready = nbytes, ready
+
+
+def _bare_executor(budget):
+    import threading
+    ex = object.__new__(wk.GpuExecutor)
+    ex.resident, ex.in_use, ex.max_resident_bytes = {}, None, budget
+    ex.res_lock = threading.Lock()
+    return ex
+
+
+def test_resident_eviction_order():
+    ex = _bare_executor(budget=250)
+    ex.resident = {("a", True): _FakeDs(100), ("b", True): _FakeDs(100), ("c", True): _FakeDs(100, ready=object())}
+    ex.in_use = ("a", True)
+    ex._evict()                       # a is being read, c is a prefetched copy nobody used: b goes
+    assert list(ex.resident) == [("a", True), ("c", True)]
+    ex.in_use = None
+    ex._evict(incoming=100, keep=("a", True))   # nothing may go: the budget is soft
+    assert list(ex.resident) == [("a", True), ("c", True)]
+    ex.resident[("c", True)].ready = None
+    ex._evict(incoming=100)           # least recently used first
+    assert list(ex.resident) == [("c", True)]
+
+
+def test_prefetch_task_routes_to_the_executor(monkeypatch):
+    calls = []
+
+    class Fake:
+        hint = None
+
+        def prefetch(self, name, classifier):
+            calls.append((name, classifier))
+            return True
+
+    fake = Fake()
+    monkeypatch.setitem(wk._EXECUTORS, 0, fake)
+    X = np.zeros((8, 2), dtype=np.float32)
+    pkg.register_dataset("pf-now", X, np.arange(8) % 2)
+    pkg.register_dataset("pf-next", X, np.arange(8) % 2)
+    pkg.register_dataset("pf-f64", X.astype(np.float64), np.arange(8) % 2)
+    block = {"model_type": "LogisticRegression", "dataset_id": "pf-next", "train_params": {"cv": 3},
+             "candidates": [{"index": 0, "subtask_id": "s0", "parameters": {"C": 1.0}}]}
+    # nothing on the GPU right now (no current task, or a scikit-learn one): the copy starts at once
+    assert wk.prefetch_task(block, gpu=0)
+    assert wk.prefetch_task(block, gpu=0, current=dict(block, model_type="RandomForestClassifier"))
+    assert calls == [("pf-next", True), ("pf-next", True)] and fake.hint is None
+    # the running task is a b200 block: leave a hint, GpuExecutor.run copies once it holds its own dataset
+    cur = dict(block, model_type="Ridge", dataset_id="pf-now")
+    assert wk.prefetch_task(block, gpu=0, current=cur)
+    assert fake.hint == ("pf-next", True) and len(calls) == 2
+    # tasks the b200 executor would not take are not prefetched
+    assert not wk.prefetch_task(dict(block, model_type="RandomForestClassifier"), gpu=0)
+    assert not wk.prefetch_task(dict(block, train_params={"executor": "sklearn"}), gpu=0)
+    assert not wk.prefetch_task(dict(block, dataset_id="pf-f64"), gpu=0)      # auto keeps float64 on scikit-learn
+    assert not wk.prefetch_task(dict(block, dataset_id="missing"), gpu=0)
+    assert not wk.prefetch_task(block, gpu=1)          # no executor on that GPU yet
+    assert len(calls) == 2
