@@ -179,7 +179,10 @@ class Master:
         job = {"job_id": payload["job_id"], "session_id": session_id, "subtasks": subtasks,
                "results": {}, "failed": {}, "status": "pending", "created_at": time.time(),
                "search_type": details.get("search_type"), "base_params": base, "search_params": search,
-               "metrics": [], "done": threading.Event()}
+               "metrics": [], "done": threading.Event(),
+               # GridSearchCV's refit step (_search.py:1146-1159).  The reference never refits (its
+               # client serialises cv_params.refit and nobody reads it), so it is opt-in here.
+               "refit": bool(payload.get("train_params", {}).get("refit")) and "search_type" in details}
         with self.lock:
             self.jobs[(session_id, payload["job_id"])] = job
         n_gpus = self.n_gpus or max(1, self.scheduler.n_workers())
@@ -195,6 +198,12 @@ class Master:
             if job is None:
                 return
             entries = message["result"] if isinstance(message.get("result"), list) else [message]
+            if message.get("subtask_id") == f"{job['job_id']}-refit":
+                e = entries[0]
+                ok = e.get("status", message.get("status")) == "completed"
+                self._complete(job, job.pop("pending_result"), e.get("result") if ok else None,
+                               None if ok else e.get("error", message.get("error", "failed")))
+                return
             for e in entries:
                 sid = e.get("subtask_id", message.get("subtask_id"))
                 if e.get("status", message.get("status")) == "completed":
@@ -204,8 +213,9 @@ class Master:
             total = len(job["subtasks"])
             finished = len(job["results"]) + len(job["failed"])
             job["status"] = str(len(job["results"]) / total * 100.0)
-            if finished == total:
-                self._finish(job)
+            refit_task = self._finish(job) if finished == total else None
+        if refit_task is not None:
+            self.scheduler.submit(refit_task)
 
     def on_metrics(self, record: dict) -> None:
         with self.lock:
@@ -213,7 +223,8 @@ class Master:
                 if record.get("subtask_id", "").startswith(jid):
                     job["metrics"].append(record)
 
-    def _finish(self, job: dict) -> None:
+    def _finish(self, job: dict) -> dict | None:
+        """All candidates are in: aggregate.  Returns the refit block to submit, if one is due."""
         ordered = []
         for st in job["subtasks"]:
             r = job["results"].get(st["subtask_id"])
@@ -230,6 +241,28 @@ class Master:
             nf = max(len(r.get("cv_scores", [])) for r in ordered)
             scores = [list(r.get("cv_scores", [])) + [float("nan")] * (nf - len(r.get("cv_scores", []))) for r in ordered]
             out.update(build_cv_results(cands, scores))
+        best = out.get("best_index_")
+        if job["refit"] and best is not None and np.isfinite(out["best_score_"]):
+            st = job["subtasks"][best]       # best candidate again, all rows, one more block subtask
+            rid = f"{job['job_id']}-refit"
+            tp = {k: v for k, v in st.get("train_params", {}).items() if k != "test_size"}
+            job["pending_result"] = out
+            return {"subtask_id": rid, "job_id": job["job_id"], "session_id": job["session_id"],
+                    "dataset_id": st["dataset_id"], "model_type": st["model_type"],
+                    "train_params": {**tp, "refit_fit": True},
+                    "candidates": [{"index": best, "subtask_id": rid, "parameters": st["parameters"]}],
+                    "folds": [], "gpu": 0, "partition": "candidates", "n_shards": 1}
+        self._complete(job, out)
+        return None
+
+    def _complete(self, job: dict, out: dict, refit_result: dict | None = None, refit_error: str | None = None) -> None:
+        if refit_result is not None:
+            out["best_estimator_"] = {k: refit_result.get(k) for k in
+                                      ("model_id", "model_path", "coef", "intercept", "parameters", "executor")}
+            out["refit_time_"] = refit_result.get("training_time")
+        elif refit_error is not None:
+            out["refit_error"] = refit_error
+        out["completion_time"] = time.time()
         job["job_result"] = out
         job["status"] = "completed"
         job["done"].set()

@@ -24,6 +24,7 @@ from __future__ import annotations
 
 import inspect
 import os
+import pickle
 import threading
 import time
 import warnings
@@ -84,6 +85,40 @@ def gpu_eligible(model_type: str, params: dict) -> tuple[bool, str]:
     return False, "model type not covered by the GPU path"
 
 
+def fitted_estimator(model_type: str, parameters: dict, coef, intercept, classes=None, n_iter=None):
+    """A scikit-learn estimator carrying coefficients fitted on the GPU, so that the artefact
+    the worker pickles (worker.py:351-356) loads and predicts like the reference's."""
+    est = get_model_instance(model_type, parameters)
+    coef = np.asarray(coef, dtype=np.float64)
+    icpt = np.asarray(intercept, dtype=np.float64)
+    if model_type == "Ridge":
+        est.coef_ = coef.reshape(-1)
+        est.intercept_ = float(icpt.reshape(-1)[0])
+        est.n_features_in_ = est.coef_.shape[0]
+    else:
+        est.coef_ = coef.reshape(-1, coef.shape[-1])
+        est.intercept_ = icpt.reshape(-1)
+        est.n_features_in_ = est.coef_.shape[1]
+        if model_type == "RidgeClassifier":      # older scikit-learn reads classes_ off the fitted binarizer
+            from sklearn.preprocessing import LabelBinarizer
+            est._label_binarizer = LabelBinarizer(pos_label=1, neg_label=-1).fit(np.asarray(classes))
+        try:
+            est.classes_ = np.asarray(classes)
+        except AttributeError:                   # classes_ is a read-only property there
+            pass
+    if n_iter is not None and model_type == "LogisticRegression":
+        est.n_iter_ = np.asarray([int(n_iter)], dtype=np.int32)
+    return est
+
+
+def save_model(model, model_dir: str, model_id: str) -> str:
+    os.makedirs(model_dir, exist_ok=True)
+    path = os.path.join(model_dir, f"{model_id}.pkl")
+    with open(path, "wb") as fh:
+        pickle.dump(model, fh)
+    return path
+
+
 def _executor_choice(task: dict) -> str:
     return str(task.get("train_params", {}).get("executor") or os.environ.get("DML_EXECUTOR", "auto")).lower()
 
@@ -91,7 +126,8 @@ def _executor_choice(task: dict) -> str:
 # ---------------------------------------------------------------------------------------
 # sklearn executor: the reference's body, one candidate at a time
 # ---------------------------------------------------------------------------------------
-def train_candidate_sklearn(model_type: str, parameters: dict, train_params: dict, X, y, subtask_id: str) -> dict:
+def train_candidate_sklearn(model_type: str, parameters: dict, train_params: dict, X, y, subtask_id: str,
+                            model_dir: str | None = None) -> dict:
     """worker.py:289-363 with the SURVEY.md 3.4 repairs (keyword train_test_split
     arguments, optional hold-out, cv from train_params)."""
     from sklearn.base import is_classifier
@@ -101,6 +137,18 @@ def train_candidate_sklearn(model_type: str, parameters: dict, train_params: dic
     model = get_model_instance(model_type, parameters)
     clf = is_classifier(model)
     results = {}
+    if train_params.get("refit_fit"):      # GridSearchCV's refit (_search.py:1146-1159): best params, all rows
+        with warnings.catch_warnings():
+            warnings.simplefilter("ignore", ConvergenceWarning)
+            t0 = time.time()
+            model.fit(X, y)
+            results["training_time"] = time.time() - t0
+        results.update(refit=True, model_id=f"{subtask_id}_model", parameters=parameters, executor="sklearn",
+                       model_path=save_model(model, model_dir, f"{subtask_id}_model") if model_dir else None)
+        if hasattr(model, "coef_"):
+            results["coef"] = np.asarray(model.coef_).tolist()
+            results["intercept"] = np.asarray(model.intercept_).tolist()
+        return results
     with warnings.catch_warnings():
         warnings.simplefilter("ignore", ConvergenceWarning)
         if "test_size" in train_params:
@@ -250,15 +298,24 @@ class GpuExecutor:
             cv = train_params.get("cv", 5)
             if not isinstance(cv, int):
                 raise ValueError("the GPU executor takes an integer cv (un-shuffled (Stratified)KFold)")
-            fold, hold = self.row_labels(dataset_id, classifier, cv, ds.n, y_host, train_params.get("test_size"),
+            refit = bool(train_params.get("refit_fit"))
+            fold, hold = self.row_labels(dataset_id, classifier, cv, ds.n, y_host,
+                                         None if refit else train_params.get("test_size"),
                                          train_params.get("random_state"))
+            if refit:        # the all-rows fit is the "hold-out" fit of an empty hold-out set
+                zkey = (dataset_id, "all-rows")
+                if zkey not in self.labels:
+                    self.labels[zkey] = np.zeros(ds.n, dtype=np.int8)
+                hold = self._on_device(zkey)
             P = [c["parameters"] for c in cands]
             fi = [bool(p.get("fit_intercept", True)) for p in P]
+            if refit and model_type == "LogisticRegression":
+                cv = 0           # only the all-rows column; Ridge keeps its folds (one Gram pass either way)
             t0 = time.time()
             if model_type == "LogisticRegression":
                 out = self.solver.logreg_sweep(
                     ds, fold, cv, [float(p.get("C", 1.0)) for p in P], [float(p.get("tol", 1e-4)) for p in P], fi,
-                    [int(p.get("max_iter", 100)) for p in P], hold_id=hold)
+                    [int(p.get("max_iter", 100)) for p in P], hold_id=hold, want_scores=not refit)
             else:
                 out = self.solver.ridge_sweep(ds, fold, cv, [float(p.get("alpha", 1.0)) for p in P], fi,
                                               classifier=classifier, hold_id=hold)
@@ -276,29 +333,32 @@ class GpuExecutor:
         results = []
         for i, c in enumerate(cands):
             r = {}
-            if classifier:
-                sc = out["correct"][i] / out["n_test"][i]        # float64 count / n_test (A14)
+            if refit:
+                r.update(refit=True, training_time=wall, coef=out["coef"][i][cv].tolist(),
+                         intercept=out["intercept"][i][cv].tolist())
             else:
-                sst = out["syy"][i] - out["sy"][i] ** 2 / out["n_test"][i]
-                sc = 1.0 - out["sse"][i] / sst
-            cvs = sc[:cv]
-            if hold is not None:
                 if classifier:
-                    r["accuracy"] = float(sc[cv])
+                    sc = out["correct"][i] / out["n_test"][i]        # float64 count / n_test (A14)
                 else:
-                    r["r2_score"] = float(sc[cv])
-                    r["mean_squared_error"] = float(out["sse"][i][cv] / out["n_test"][i][cv])
-            r["cv_scores"] = [float(v) for v in cvs]
-            r["mean_cv_score"] = float(np.mean(cvs))
-            r["training_time"] = wall / n_fits
+                    sst = out["syy"][i] - out["sy"][i] ** 2 / out["n_test"][i]
+                    sc = 1.0 - out["sse"][i] / sst
+                cvs = sc[:cv]
+                if hold is not None:
+                    if classifier:
+                        r["accuracy"] = float(sc[cv])
+                    else:
+                        r["r2_score"] = float(sc[cv])
+                        r["mean_squared_error"] = float(out["sse"][i][cv] / out["n_test"][i][cv])
+                r["cv_scores"] = [float(v) for v in cvs]
+                r["mean_cv_score"] = float(np.mean(cvs))
+                r["training_time"] = wall / n_fits
             r["model_id"] = f"{c['subtask_id']}_model"
             r["model_path"] = None
-            if hold is not None and model_dir:
-                os.makedirs(model_dir, exist_ok=True)
-                path = os.path.join(model_dir, f"{r['model_id']}.npz")
-                np.savez(path, coef=out["coef"][i][cv], intercept=out["intercept"][i][cv],
-                         classes=ds.classes if classifier else np.zeros(0), model_type=model_type)
-                r["model_path"] = path
+            if hold is not None and model_dir:      # worker.py:351-356: the fitted model is pickled
+                n_it = out["n_iter"][i][cv] if model_type == "LogisticRegression" else None
+                est = fitted_estimator(model_type, c["parameters"], out["coef"][i][cv], out["intercept"][i][cv],
+                                       ds.classes if classifier else None, n_it)
+                r["model_path"] = save_model(est, model_dir, r["model_id"])
             r["parameters"] = c["parameters"]
             r["executor"] = "b200"
             if model_type == "LogisticRegression":
@@ -357,7 +417,7 @@ def train_model(task: dict, gpu: int = 0, model_dir: str = "./models"):
             entries[c["subtask_id"]] = {"subtask_id": c["subtask_id"], "status": "completed", "result": r}
     for c in on_cpu:
         try:
-            r = train_candidate_sklearn(model_type, c["parameters"], tp, X, y, c["subtask_id"])
+            r = train_candidate_sklearn(model_type, c["parameters"], tp, X, y, c["subtask_id"], model_dir)
             entries[c["subtask_id"]] = {"subtask_id": c["subtask_id"], "status": "completed", "result": r}
         except Exception as e:   # worker.py:264-286: a failing fit is reported, not raised
             if "candidates" not in task:

@@ -241,6 +241,48 @@ def test_api_end_to_end_best_params_equal_gridsearchcv():
         m.close()
 
 
+def test_refit_on_gpu_equals_gridsearchcv_best_estimator(tmp_path, monkeypatch):
+    """train_params {"refit": True}: the best candidate is fitted on ALL rows by the sweep library
+    (one column, empty hold-out set) and pickled as a scikit-learn estimator."""
+    import pickle
+    from sklearn.linear_model import LogisticRegression, Ridge
+    from sklearn.model_selection import GridSearchCV
+    import cs230_distributed_machine_learning_b200 as pkg
+    monkeypatch.chdir(tmp_path)
+    X, y = make_dataset("binary", 12_000, 40, seed=90)
+    pkg.register_dataset("rf-bin", X, y)
+    Xr, yr = make_dataset("regression", 12_000, 40, seed=91)
+    pkg.register_dataset("rf-reg", Xr, yr)
+    m = pkg.MLTaskManager("local://1")
+    try:
+        grid = {"C": [1e-4, 1e-2, 1.0]}
+        r = m.train(GridSearchCV(LogisticRegression(), grid, cv=5), "rf-bin", train_params={"refit": True},
+                    wait_for_completion=True)
+        assert r["job_status"] == "completed", r
+        jr = r["job_result"]
+        gs = GridSearchCV(LogisticRegression(), grid, cv=5).fit(X.astype(np.float64), y)
+        be = jr["best_estimator_"]
+        assert be["executor"] == "b200" and be["parameters"]["C"] == gs.best_params_["C"]
+        assert rel_err(np.asarray(be["coef"]), gs.best_estimator_.coef_) < RTOL
+        assert rel_err(np.asarray(be["intercept"]), gs.best_estimator_.intercept_) < 10 * RTOL
+        with open(be["model_path"], "rb") as fh:
+            est = pickle.load(fh)
+        agree = (est.predict(X.astype(np.float64)) == gs.best_estimator_.predict(X.astype(np.float64))).mean()
+        assert agree > 0.9995                                # decision ties only
+        gridr = {"alpha": [0.1, 10.0, 1000.0]}
+        r = m.train(GridSearchCV(Ridge(), gridr, cv=5), "rf-reg", train_params={"refit": True}, wait_for_completion=True)
+        gsr = GridSearchCV(Ridge(), gridr, cv=5).fit(Xr.astype(np.float64), yr.astype(np.float64))
+        be = r["job_result"]["best_estimator_"]
+        assert be["parameters"]["alpha"] == gsr.best_params_["alpha"]
+        assert rel_err(np.asarray(be["coef"]), gsr.best_estimator_.coef_) < RTOL
+        with open(be["model_path"], "rb") as fh:
+            est = pickle.load(fh)
+        np.testing.assert_allclose(est.predict(Xr[:100].astype(np.float64)),
+                                   gsr.best_estimator_.predict(Xr[:100].astype(np.float64)), rtol=1e-3, atol=1e-3)
+    finally:
+        m.close()
+
+
 def test_queued_jobs_prefetch_their_dataset_and_match_blocking_runs():
     """Jobs submitted without waiting: the worker starts the next job's host->device copy on its
     copy stream while the current sweep runs.  Results equal the one-job-at-a-time results exactly."""

@@ -11,6 +11,7 @@ from sklearn.linear_model import LogisticRegression, RidgeClassifier
 from sklearn.model_selection import GridSearchCV, ParameterSampler, RandomizedSearchCV
 
 import cs230_distributed_machine_learning_b200 as pkg
+from cs230_distributed_machine_learning_b200 import worker as wk
 from cs230_distributed_machine_learning_b200 import _cabi, build, folds, master, scheduler, worker
 from cs230_distributed_machine_learning_b200.client import MLTaskManager, wire
 
@@ -112,6 +113,58 @@ def test_client_config1_iris_known_answers():
         m.close()
 
 
+def test_refit_returns_best_estimator_artefact(tmp_path, monkeypatch):
+    """train_params {"refit": True}: after the search the best candidate is fitted on all rows
+    (GridSearchCV.best_estimator_) and pickled the way the reference pickles its models."""
+    import pickle
+    from sklearn.datasets import load_iris
+    monkeypatch.chdir(tmp_path)
+    X, y = load_iris(return_X_y=True)
+    pkg.register_dataset("iris", X, y)
+    m = MLTaskManager("local://1")
+    try:
+        grid = {"C": [0.1, 1.0, 10.0]}
+        r = m.train(GridSearchCV(LogisticRegression(max_iter=500), grid, cv=5), "iris",
+                    train_params={"refit": True}, wait_for_completion=True)
+        assert r["job_status"] == "completed", r
+        jr = r["job_result"]
+        gs = GridSearchCV(LogisticRegression(max_iter=500), grid, cv=5).fit(X, y)
+        assert jr["best_params_"] == gs.best_params_ and len(jr["results"]) == 3
+        be = jr["best_estimator_"]
+        assert be["parameters"]["C"] == gs.best_params_["C"] and jr["refit_time_"] >= 0
+        np.testing.assert_allclose(be["coef"], gs.best_estimator_.coef_, rtol=1e-12)
+        got = m.download_best_model(m.job_id, be["model_path"], be["model_id"])
+        assert got["status"] == "success"
+        with open(got["model_path"], "rb") as fh:
+            est = pickle.load(fh)
+        assert (est.predict(X) == gs.best_estimator_.predict(X)).all()
+        # without the flag nothing is refitted (the reference never does)
+        r2 = m.train(GridSearchCV(LogisticRegression(max_iter=500), grid, cv=5), "iris", wait_for_completion=True)
+        assert "best_estimator_" not in r2["job_result"]
+    finally:
+        m.close()
+
+
+def test_fitted_estimator_predicts_like_sklearn():
+    """The artefact built from GPU coefficients is a working scikit-learn estimator."""
+    from sklearn.linear_model import Ridge
+    rng = np.random.default_rng(0)
+    X = rng.normal(size=(200, 6))
+    yb = (X[:, 0] + 0.3 * rng.normal(size=200) > 0).astype(int) * 2 + 3      # labels {3, 5}
+    for name, ref in (("LogisticRegression", LogisticRegression(C=0.5).fit(X, yb)),
+                      ("RidgeClassifier", RidgeClassifier(alpha=2.0).fit(X, yb))):
+        est = wk.fitted_estimator(name, ref.get_params(), ref.coef_, ref.intercept_, ref.classes_, 7)
+        assert (est.predict(X) == ref.predict(X)).all() and list(est.classes_) == [3, 5]
+    ym = rng.integers(0, 4, size=200)
+    ref = LogisticRegression().fit(X, ym)
+    est = wk.fitted_estimator("LogisticRegression", ref.get_params(), ref.coef_, ref.intercept_, ref.classes_, 9)
+    np.testing.assert_allclose(est.predict_proba(X), ref.predict_proba(X), rtol=1e-12)
+    yr = X @ rng.normal(size=6) + 1.0
+    ref = Ridge(alpha=0.3).fit(X, yr)
+    est = wk.fitted_estimator("Ridge", ref.get_params(), ref.coef_, ref.intercept_)
+    np.testing.assert_allclose(est.predict(X), ref.predict(X), rtol=1e-12)
+
+
 def test_client_single_estimator_defaults_test_size():
     from sklearn.datasets import load_iris
     X, y = load_iris(return_X_y=True)
@@ -211,7 +264,6 @@ def test_cabi_library_exports_every_declared_symbol():
 
 
 # ---- dataset prefetch / residency (host logic only; the copies themselves are GPU tests) ----
-from cs230_distributed_machine_learning_b200 import worker as wk  # noqa: E402
 class _FakeDs:
     def __init__(self, nbytes, ready=None):
         self.nbytes, self.ready = nbytes, ready
