@@ -38,6 +38,7 @@ SYMBOLS = {
     "dml_score_static": (C.c_int, [C.c_int, C.c_void_p, C.c_void_p, C.c_int64, C.c_int, C.c_int64,
                                    C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p,
                                    C.c_void_p, C.c_int, C.c_int, C.c_void_p]),
+    "dml_last_first_round": (C.c_int, [C.c_void_p, C.POINTER(C.c_float), C.POINTER(C.c_int64)]),
     "dml_last_timing": (C.c_int, [C.c_void_p, C.POINTER(C.c_float), C.POINTER(C.c_float),
                                   C.POINTER(C.c_int32), C.POINTER(C.c_int32)]),
 }
@@ -96,8 +97,11 @@ class Context:
         self.lib.dml_last_timing(self.handle, C.byref(t), C.byref(c), C.byref(cl), C.byref(tl))
         cr, rd = C.c_int64(), C.c_int32()
         self.lib.dml_last_counters(self.handle, C.byref(cr), C.byref(rd))
+        fm, fc = C.c_float(), C.c_int64()
+        self.lib.dml_last_first_round(self.handle, C.byref(fm), C.byref(fc))
         return dict(total_ms=t.value, contraction_ms=c.value, contraction_launches=cl.value,
-                    total_launches=tl.value, column_rounds=cr.value, rounds=rd.value)
+                    total_launches=tl.value, column_rounds=cr.value, rounds=rd.value,
+                    first_round_ms=fm.value, first_round_columns=fc.value)
 
     def close(self):
         if getattr(self, "handle", None):

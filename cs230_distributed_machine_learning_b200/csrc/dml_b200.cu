@@ -56,6 +56,9 @@ struct dml_ctx {
   cudaEvent_t ev_total[2] = {nullptr, nullptr};
   float total_ms = 0.f, contraction_ms = 0.f; int contraction_launches = 0, total_launches = 0;
   size_t r_budget = (size_t)4 << 30;  // bytes of residual scratch per row chunk
+  size_t first_pairs = 0; float first_ms = 0.f; int64_t first_cols = 0;   // round 0 when it ran once per row mask
+  int first_round_once = 1;   // evaluate round 0 once per row mask instead of once per candidate
+  int tc_grad2 = 1;   // gradient contraction on CTA pairs (cta_group::2) when d spans an even number of 128-feature blocks
   int tc_prefetch = 0, tc_prefetch_grad = 0;  // L2 prefetch distance of the forward X tiles in jobs (0 = off; measured: no gain, the ring is not latency-bound)
   int tc_cluster = 2;                 // CTAs per cluster in the forward kernel (W multicast): 1 or 2
   int tc_mask_hi = 0;                 // 1 = write the masked hi operand back before the MMAs read it (not needed:
@@ -112,6 +115,7 @@ static void timing_begin(dml_ctx* ctx) {
   ctx->ev_used = 0; ctx->contraction_launches = 0; ctx->total_launches = 0;
   ctx->slot_rounds = 0; ctx->rounds = 0;
   ctx->total_ms = ctx->contraction_ms = 0.f;
+  ctx->first_pairs = 0; ctx->first_ms = 0.f; ctx->first_cols = 0;
   cudaEventRecord(ctx->ev_total[0], ctx->stream);
 }
 static void timing_end(dml_ctx* ctx) {
@@ -121,7 +125,10 @@ static void timing_end(dml_ctx* ctx) {
   float acc = 0.f;
   for (size_t i = 0; i + 1 < ctx->ev_used; i += 2) {
     float ms = 0.f;
-    if (cudaEventElapsedTime(&ms, ctx->ev[i], ctx->ev[i + 1]) == cudaSuccess) acc += ms;
+    if (cudaEventElapsedTime(&ms, ctx->ev[i], ctx->ev[i + 1]) == cudaSuccess) {
+      acc += ms;
+      if (i / 2 < ctx->first_pairs) ctx->first_ms += ms;
+    }
   }
   ctx->contraction_ms = acc;
 }
@@ -155,6 +162,8 @@ extern "C" int dml_ctx_create(int device, void* stream, dml_ctx** out) {
   if (const char* e = getenv("DML_TC_MASK_HI")) ctx->tc_mask_hi = atoi(e);
   if (const char* e = getenv("DML_TC_PREFETCH")) ctx->tc_prefetch = atoi(e);
   if (const char* e = getenv("DML_TC_PREFETCH_GRAD")) ctx->tc_prefetch_grad = atoi(e);
+  if (const char* e = getenv("DML_TC_GRAD2")) ctx->tc_grad2 = atoi(e);
+  if (const char* e = getenv("DML_FIRST_ROUND_ONCE")) ctx->first_round_once = atoi(e);
   if (const char* e = getenv("DML_TC_CLUSTER")) ctx->tc_cluster = atoi(e) == 1 ? 1 : 2;
   CU(cudaSetDevice(device));
   CU(cudaHostAlloc(&ctx->h_scalar, 64, cudaHostAllocDefault));
@@ -218,6 +227,13 @@ extern "C" int dml_debug_fetch(dml_ctx* ctx, int which, void* dst_host, size_t b
   if (dst_host && ctx->dbg_ptr[which]) {
     CU(cudaMemcpy(dst_host, ctx->dbg_ptr[which], std::min(bytes, ctx->dbg_bytes[which]), cudaMemcpyDeviceToHost));
   }
+  return DML_OK;
+}
+
+extern "C" int dml_last_first_round(dml_ctx* ctx, float* contraction_ms, int64_t* column_rounds) {
+  if (!ctx) return DML_ERR_ARG;
+  if (contraction_ms) *contraction_ms = ctx->first_ms;
+  if (column_rounds) *column_rounds = ctx->first_cols;
   return DML_OK;
 }
 
@@ -347,6 +363,25 @@ static int launch_tc_grad(dml_ctx* ctx, int NC, dim3 grid, const CUtensorMap& mx
   }
 }
 
+// CTA-pair gradient kernel: cluster of two along the feature-block axis, R maps with a one-chunk box
+static int launch_tc_grad2(dml_ctx* ctx, dim3 grid, const CUtensorMap& mx, const CUtensorMap& mrh, const CUtensorMap& mrl,
+                           const tc::TcGradParams& p) {
+  static bool attr_set = false;
+  if (!attr_set) {
+    CU(cudaFuncSetAttribute(tc::tc_grad2_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, tc::Grad2Smem::kBytes));
+    attr_set = true;
+  }
+  cudaLaunchConfig_t cfg{};
+  cfg.gridDim = grid; cfg.blockDim = dim3(tc::kGradThreads);
+  cfg.dynamicSmemBytes = tc::Grad2Smem::kBytes; cfg.stream = ctx->stream;
+  cudaLaunchAttribute at[1];
+  at[0].id = cudaLaunchAttributeClusterDimension;
+  at[0].val.clusterDim.x = 2; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = 1;
+  cfg.attrs = at; cfg.numAttrs = 1;
+  CU(cudaLaunchKernelEx(&cfg, tc::tc_grad2_kernel, mx, mrh, mrl, p));
+  return DML_OK;
+}
+
 // ---- shared: one scoring pass over all rows for `n_slots` columns -------------------------
 struct ScoreBufs { int32_t* cntPart; float* ssePart; };
 static int run_score(dml_ctx* ctx, int mode, const float* X, int64_t n, int d, int64_t ldx,
@@ -434,7 +469,8 @@ struct EvalCtx {
   // buffers
   float *Wt = nullptr, *bt = nullptr, *R = nullptr, *Rlo = nullptr, *Whi = nullptr, *Wlo = nullptr, *Gpart = nullptr;
   double *lossPart = nullptr, *gbPart = nullptr, *Gred = nullptr; int32_t *sel = nullptr, *val = nullptr, *cntPart = nullptr;
-  CUtensorMap mXf, mXf2, mXg, mWh, mWl, mRh, mRl;   // mXf2: forward X box of a 2-CTA cluster member (64 rows)
+  CUtensorMap mXf, mXf2, mXg, mWh, mWl, mRh, mRl, mRh1, mRl1;   // mR?1: one 32-column chunk per box (CTA-pair gradient)
+  bool grad2 = false;   // mXf2: forward X box of a 2-CTA cluster member (64 rows)
   unsigned long long* hist_local = nullptr;   // [512] label histogram of this rank's rows
   // the forward kernel sums (loss - shift) with shift = loss of the zero model: ln 2, or ln T (multinomial)
   float loss_shift() const { return T == 1 ? 0.693147182f : logf((float)T); }
@@ -493,6 +529,11 @@ struct EvalCtx {
     if ((rc = make_map_2d(ctx, &mWl, Wlo, d, S_max, (uint64_t)ldw * 4, 32, NC))) return rc;
     if ((rc = make_map_chunked(ctx, &mRh, R, ldr_max, chunk_rows, (uint64_t)ldr_max * 4, 32, NC / 32))) return rc;
     if ((rc = make_map_chunked(ctx, &mRl, Rlo, ldr_max, chunk_rows, (uint64_t)ldr_max * 4, 32, NC / 32))) return rc;
+    grad2 = ctx->tc_grad2 != 0 && cdiv(d, 128) % 2 == 0;
+    if (grad2) {
+      if ((rc = make_map_chunked(ctx, &mRh1, R, ldr_max, chunk_rows, (uint64_t)ldr_max * 4, 32, 1))) return rc;
+      if ((rc = make_map_chunked(ctx, &mRl1, Rlo, ldr_max, chunk_rows, (uint64_t)ldr_max * 4, 32, 1))) return rc;
+    }
     return DML_OK;
   }
   // Gred[slot] = [sum r x (d), sum r, sum loss] over the training rows of each column
@@ -526,7 +567,11 @@ struct EvalCtx {
         if (rc) return rc;
         tc::TcGradParams gp{r0, rows, tc_rps, d, n_slots, Gpart, ldg, ctx->tc_mask_hi, ctx->tc_prefetch_grad};
         const int splits_here = (int)cdiv(rows, tc_rps);
-        rc = launch_tc_grad(ctx, NC, dim3((unsigned)cdiv(d, 128), (unsigned)ncb, (unsigned)splits_here), mXg, mRh, mRl, gp);
+        if (grad2)
+          rc = launch_tc_grad2(ctx, dim3((unsigned)cdiv(d, 128), (unsigned)cdiv(n_slots, tc::kGrad2NC), (unsigned)splits_here),
+                               mXg, mRh1, mRl1, gp);
+        else
+          rc = launch_tc_grad(ctx, NC, dim3((unsigned)cdiv(d, 128), (unsigned)ncb, (unsigned)splits_here), mXg, mRh, mRl, gp);
         if (rc) return rc;
         ReduceParams rp{Gpart, ldg, splits_here, n_slots, d, T, d, nullptr, 0, 0, Gred, ldgr, ci > 0 ? 1 : 0};
         reduce_grad_kernel<<<n_slots, 256, 0, st>>>(rp);
@@ -592,6 +637,16 @@ struct EvalCtx {
     return run_score(ctx, FWD_SCORE_CLS, X, n, d, ldx, y, nullptr, fold_id, hold_id, Wt, ldw, bt, sel, val, n_slots, T, cntPart);
   }
 };
+
+// Round 0 starts every fit at w = 0, where the loss and gradient sums depend on the row mask only:
+// rows [0, n_unique) of Gred (candidate 0's fits) are copied to the same fits of the other candidates.
+__global__ void broadcast_first_round_kernel(double* __restrict__ Gred, int ldgr, int n_unique, int n_slots) {
+  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  const int64_t total = (int64_t)(n_slots - n_unique) * ldgr;
+  if (i >= total) return;
+  const int64_t slot = n_unique + i / ldgr; const int j = (int)(i % ldgr);
+  Gred[slot * ldgr + j] = Gred[(slot % n_unique) * ldgr + j];
+}
 
 __global__ void fill_n_test_kernel(const unsigned long long* __restrict__ hist, int F, int fpc, int n_folds,
                                    int64_t* __restrict__ n_test) {
@@ -675,10 +730,19 @@ extern "C" int dml_logreg_sweep(dml_ctx* ctx, const float* X, int64_t n, int d, 
   int n_active = F, rounds = 0;
   while (n_active > 0) {
     const int n_slots = n_active * T;
-    ctx->slot_rounds += n_slots; ctx->rounds += 1;
-    int rc = ev.evaluate(ctx, n_slots);
+    // round 0: all coefficients are zero (_logistic.py:439,457), so z = 0 for every column and the sums
+    // differ only by row mask -- evaluate candidate 0's fits (slots are [candidate][fit][class]) and copy
+    const int n_eval = (rounds == 0 && ctx->first_round_once) ? std::min(n_slots, fpc * T) : n_slots;
+    ctx->slot_rounds += n_eval; ctx->rounds += 1;
+    int rc = ev.evaluate(ctx, n_eval);
     if (rc) return rc;
-    if (ctx->comm) { rc = allreduce(ctx, ev.Gred, (size_t)n_slots * ev.ldgr, kNcclFloat64); if (rc) return rc; }
+    if (ctx->comm) { rc = allreduce(ctx, ev.Gred, (size_t)n_eval * ev.ldgr, kNcclFloat64); if (rc) return rc; }
+    if (n_eval < n_slots) {
+      ctx->first_pairs = ctx->ev_used / 2; ctx->first_cols = n_eval;
+      const int64_t total = (int64_t)(n_slots - n_eval) * ev.ldgr;
+      broadcast_first_round_kernel<<<(unsigned)cdiv(total, 256), 256, 0, st>>>(ev.Gred, ev.ldgr, n_eval, n_slots);
+      ctx->total_launches += 1;
+    }
     LbfgsParams lp{d, T, P, ev.ldgr, d_st, d_x, d_g, d_dir, d_gt, d_S, d_Y, d_ys, d_active, d_nactive, ev.Gred};
     lbfgs_update_kernel<<<n_active, 256, 0, st>>>(lp);
     compact_kernel<<<1, 1024, 0, st>>>(d_st, F, d_active, d_nactive, d_nactive + 1);

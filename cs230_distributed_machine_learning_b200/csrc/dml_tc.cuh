@@ -77,6 +77,53 @@ __device__ __forceinline__ void cluster_sync_all() {
   asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory");
   asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory");
 }
+// ---- CTA-pair (cta_group::2) variants: one MMA spans the two SMs of a cluster of two
+__device__ __forceinline__ uint32_t mapa_rank(uint32_t saddr, uint32_t rank) {   // same offset in CTA `rank`
+  uint32_t r; asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(r) : "r"(saddr), "r"(rank)); return r;
+}
+__device__ __forceinline__ void mbar_arrive_cluster(uint32_t cluster_addr) {
+  // default semantics on purpose: the data published here lives in tensor memory and is ordered by the
+  // tcgen05 fences; ".release.cluster" compiles to MEMBAR.ALL.GPU per arrive (measured: the staging warps
+  // then spend a quarter of their time in it)
+  asm volatile("mbarrier.arrive.shared::cluster.b64 _, [%0];" ::"r"(cluster_addr) : "memory");
+}
+__device__ __forceinline__ void mbar_wait_cluster(uint64_t* bar, uint32_t parity) {   // arrivals may come from the peer CTA
+  const uint32_t addr = smem_u32(bar);
+  uint32_t done;
+  do {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+        "selp.u32 %0, 1, 0, p;\n\t}"
+        : "=r"(done) : "r"(addr), "r"(parity) : "memory");
+  } while (!done);
+}
+// the bytes land in this CTA's shared memory, the completion is counted on `bar_cluster_addr` (the leader's barrier)
+__device__ __forceinline__ void tma_load_3d_pair(const CUtensorMap* map, uint32_t bar_cluster_addr, void* dst, int c0, int c1, int c2) {
+  asm volatile(
+      "cp.async.bulk.tensor.3d.cta_group::2.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5}], [%2];"
+      ::"r"(smem_u32(dst)), "l"(map), "r"(bar_cluster_addr), "r"(c0), "r"(c1), "r"(c2) : "memory");
+}
+__device__ __forceinline__ void tmem_alloc_pair(uint32_t* slot, uint32_t cols) {
+  asm volatile("tcgen05.alloc.cta_group::2.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(slot)), "r"(cols) : "memory");
+  asm volatile("tcgen05.relinquish_alloc_permit.cta_group::2.sync.aligned;" ::: "memory");
+}
+__device__ __forceinline__ void tmem_dealloc_pair(uint32_t addr, uint32_t cols) {
+  asm volatile("tcgen05.dealloc.cta_group::2.sync.aligned.b32 %0, %1;" ::"r"(addr), "r"(cols) : "memory");
+}
+// D[256 x N] += A[256 x 8] B[8 x N]: rows 0-127 of A and D in the leader's tensor memory, 128-255 in the
+// peer's (same addresses); columns 0..N/2-1 of B in the leader's shared memory, the rest in the peer's
+__device__ __forceinline__ void umma_tf32_ts_pair(uint32_t tmem_c, uint32_t tmem_a, uint64_t db, uint32_t idesc, uint32_t accumulate) {
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "setp.ne.b32 p, %4, 0;\n\t"
+      "tcgen05.mma.cta_group::2.kind::tf32 [%0], [%1], %2, %3, p;\n\t}"
+      ::"r"(tmem_c), "r"(tmem_a), "l"(db), "r"(idesc), "r"(accumulate) : "memory");
+}
+__device__ __forceinline__ void umma_commit_pair(uint64_t* bar) {   // arrives on `bar` in both CTAs of the pair
+  asm volatile("tcgen05.commit.cta_group::2.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;"
+               ::"r"(smem_u32(bar)), "h"((uint16_t)3) : "memory");
+}
 __device__ __forceinline__ void tmem_alloc(uint32_t* slot, uint32_t cols) {
   asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(slot)), "r"(cols) : "memory");
   asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
@@ -843,6 +890,191 @@ tc_grad_kernel(const __grid_constant__ CUtensorMap mapX, const __grid_constant__
   tc_fence_before();
   __syncthreads();
   if (warp == 9) tmem_dealloc(tmem_base, kTmemCols);
+}
+
+// ---------------------------------------------------------------- gradient kernel, CTA pair
+// Same contraction with cta_group::2 MMAs (M = 256): the two CTAs of a cluster take feature blocks
+// 2k and 2k+1 and share the R operand -- each loads and holds half of the block's columns, so the
+// shared-memory traffic of the B operand (the limiter of the one-CTA kernel) is halved per SM.
+//   leader (rank 0): issues every MMA; its fullB / split / tempty barriers also count the peer's
+//                    TMA bytes, staging warps and drain warps (remote arrives)
+//   both CTAs      : TMA producer (own X boxes -> own fullA; own R half -> the leader's fullB),
+//                    staging warps (X^T hi/lo into own tensor memory), drain warps (own features)
+//   tcgen05.commit multicasts "stage free" and "accumulator full" to both CTAs.
+// Column blocks are 128 wide, the last one 64 when that covers the rest (N/2 must be whole 32-column
+// chunks of the MN-major swizzled layout).  Used when d spans an even number of 128-feature blocks.
+// Three rings so that the look-ahead is set by shared memory, not by tensor memory: X boxes (freed as
+// soon as the staging warps have read them), R halves (freed by the MMAs) and the A slots in tensor
+// memory (four, freed by the MMAs).  Measured with a single 4-stage ring: the MMA warp waited for data
+// a third of the time (HBM latency under load exceeds 4 x 768 clocks).
+constexpr int kGrad2SX = 6, kGrad2SR = 6, kGrad2TA = 4;
+constexpr int kGrad2NC = 128;
+struct Grad2Smem {
+  static constexpr int kA = 4 * 32 * 128;                    // own X boxes of one stage
+  static constexpr int kBh = (kGrad2NC / 2 / 32) * 32 * 128; // own half of R_hi (and of R_lo) of one stage
+  static constexpr int kB = 2 * kBh;
+  static constexpr int kBytes = kGrad2SX * kA + kGrad2SR * kB + 1024 + 512;
+};
+
+__global__ void __launch_bounds__(kGradThreads, 1)
+tc_grad2_kernel(const __grid_constant__ CUtensorMap mapX, const __grid_constant__ CUtensorMap mapRhi,
+                const __grid_constant__ CUtensorMap mapRlo, const TcGradParams p) {
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
+  using L = Grad2Smem;
+  constexpr int SX = kGrad2SX, SR = kGrad2SR, TA = kGrad2TA;
+  uint8_t* smX = smem;
+  uint8_t* smR = smem + SX * L::kA;
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smR + SR * L::kB);
+  uint64_t* fullA = bars; uint64_t* emptyA = fullA + SX;
+  uint64_t* fullB = emptyA + SX; uint64_t* emptyB = fullB + SR;
+  uint64_t* split = emptyB + SR; uint64_t* aempty = split + TA;
+  uint64_t* tfull = aempty + TA;      // [2]
+  uint64_t* tempty = tfull + 2;       // [2]
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tempty + 2);
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const uint32_t rank = cluster_ctarank();
+  const bool leader = rank == 0;
+  constexpr uint32_t kTmemCols = 512, kTmemA = 2 * kGrad2NC;   // two accumulators, then 64 columns of A per slot
+  static_assert(2 * kGrad2NC + TA * 64 <= 512, "tensor memory");
+
+  if (warp == 8 && lane == 0) {
+    for (int s = 0; s < SX; ++s) { mbar_init(fullA + s, 1); mbar_init(emptyA + s, 4); }
+    for (int s = 0; s < SR; ++s) { mbar_init(fullB + s, 1); mbar_init(emptyB + s, 1); }
+    for (int s = 0; s < TA; ++s) { mbar_init(split + s, 8); mbar_init(aempty + s, 1); }
+    for (int a = 0; a < 2; ++a) { mbar_init(tfull + a, 1); mbar_init(tempty + a, 8); }
+    fence_barrier_init();
+  }
+  if (warp == 9) tmem_alloc_pair(tmem_slot, kTmemCols);
+  tc_fence_before();
+  cluster_sync_all();       // barriers of both CTAs initialised before any remote arrive or multicast
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  const int jb = blockIdx.x, cb = blockIdx.y, sp = blockIdx.z;
+  const int col0 = cb * kGrad2NC;
+  const int ncols = min(kGrad2NC, ((p.n_slots - col0 + 63) / 64) * 64);   // columns of this pair's block
+  const int nch = ncols / 64;                                             // 32-column chunks per CTA
+  const int64_t kb = (int64_t)sp * p.rows_per_split;
+  const int64_t ke = min(p.rows, kb + p.rows_per_split);
+  const int n_stages = (int)((ke - kb + 31) / 32);
+  const int n_groups = (n_stages + kChain - 1) / kChain;
+
+  if (warp == 8) {
+    if (lane == 0) {
+      const int chunk0 = col0 / 32 + (int)rank * nch;
+      for (int it = 0; it < n_stages; ++it) {
+        const int sx = it % SX, sr = it % SR;
+        const int lr = (int)(kb + (int64_t)it * 32);
+        const int xr = (int)(p.row0_x + lr);
+        mbar_wait(emptyA + sx, ((it / SX) & 1) ^ 1);
+        uint8_t* ax = smX + sx * L::kA;
+        mbar_expect_tx(fullA + sx, L::kA);
+#pragma unroll
+        for (int b = 0; b < 4; ++b) tma_load_2d(&mapX, fullA + sx, ax + b * 4096, jb * 128 + b * 32, xr);
+        mbar_wait(emptyB + sr, ((it / SR) & 1) ^ 1);
+        uint8_t* br = smR + sr * L::kB;
+        if (leader) mbar_expect_tx(fullB + sr, (uint32_t)(4 * nch * 4096));   // hi + lo halves of both CTAs
+        const uint32_t fb = mapa_rank(smem_u32(fullB + sr), 0);
+        for (int c = 0; c < nch; ++c) {
+          tma_load_3d_pair(&mapRhi, fb, br + c * 4096, 0, lr, chunk0 + c);
+          tma_load_3d_pair(&mapRlo, fb, br + L::kBh + c * 4096, 0, lr, chunk0 + c);
+        }
+      }
+    }
+  } else if (warp == 9) {
+    if (leader) {
+      const uint32_t idesc = instr_desc_tf32(256, ncols, 0, 1);
+      for (int g = 0, it = 0; g < n_groups; ++g) {
+        const int acc = g & 1; const uint32_t aph = (g >> 1) & 1;
+        mbar_wait_cluster(tempty + acc, aph ^ 1);
+        tc_fence_after();
+        const uint32_t tacc = tmem_base + acc * kGrad2NC;
+        const int g_end = min(n_stages, (g + 1) * kChain);
+        for (int first = 1; it < g_end; ++it) {
+          const int sr = it % SR, ta = it % TA;
+          mbar_wait_cluster(fullB + sr, (it / SR) & 1);
+          mbar_wait_cluster(split + ta, (it / TA) & 1);
+          tc_fence_after();
+          if (elect_one()) {
+            const uint32_t b_hi = smem_u32(smR + sr * L::kB), b_lo = b_hi + L::kBh;
+            const uint32_t ta_hi = tmem_base + kTmemA + ta * 64, ta_lo = ta_hi + 32;
+#pragma unroll
+            for (int k = 0; k < 4; ++k) {
+              const uint64_t dbh = smem_desc(b_hi + k * 1024, 4096, 512, kLayoutSw128Base32);
+              const uint64_t dbl = smem_desc(b_lo + k * 1024, 4096, 512, kLayoutSw128Base32);
+              umma_tf32_ts_pair(tacc, ta_lo + k * 8, dbh, idesc, (first && k == 0) ? 0u : 1u);
+              umma_tf32_ts_pair(tacc, ta_hi + k * 8, dbl, idesc, 1);
+              umma_tf32_ts_pair(tacc, ta_hi + k * 8, dbh, idesc, 1);
+            }
+            umma_commit_pair(emptyB + sr);
+            umma_commit_pair(aempty + ta);
+            if (it == g_end - 1) umma_commit_pair(tfull + acc);
+          }
+          __syncwarp();
+          first = 0;
+        }
+      }
+    }
+  } else if (warp < 4) {
+    const int qd = warp & 3;
+    for (int it = 0; it < n_stages; ++it) {
+      const int sx = it % SX, ta = it % TA;
+      mbar_wait(fullA + sx, (it / SX) & 1);
+      const uint32_t box = smem_u32(smX + sx * L::kA) + qd * 4096;
+      uint32_t hi[32], lo[32];
+#pragma unroll
+      for (int k = 0; k < 32; ++k)
+        hi[k] = lds32u(box + k * 128 + ((((lane >> 3) ^ (k & 3)) << 5) | ((lane & 7) << 2)));
+#pragma unroll
+      for (int e = 0; e < 32; ++e) { const float x = __uint_as_float(hi[e]); lo[e] = __float_as_uint(x - tf32_hi(x)); }
+      __syncwarp();
+      if (lane == 0) mbar_arrive(emptyA + sx);              // the box is in registers: the producer may refill it
+      mbar_wait(aempty + ta, ((it / TA) & 1) ^ 1);          // the MMAs that read this A slot are done
+      tc_fence_after();
+      const uint32_t taddr = tmem_base + kTmemA + ta * 64 + ((uint32_t)(qd * 32) << 16);
+      tmem_st32(taddr, hi);
+      tmem_st32(taddr + 32, lo);
+      tmem_st_wait();
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive_cluster(mapa_rank(smem_u32(split + ta), 0));
+    }
+  } else {
+    const int q = warp & 3;
+    const int j = jb * 128 + q * 32 + lane;
+    float sum[kGrad2NC];
+#pragma unroll
+    for (int c = 0; c < kGrad2NC; ++c) sum[c] = 0.f;
+    for (int g = 0; g < n_groups; ++g) {
+      const int acc = g & 1; const uint32_t aph = (g >> 1) & 1;
+      mbar_wait(tfull + acc, aph);
+      tc_fence_after();
+      const uint32_t tacc = tmem_base + acc * kGrad2NC + ((uint32_t)(q * 32) << 16);
+#pragma unroll
+      for (int c0 = 0; c0 < kGrad2NC; c0 += 16) {
+        if (c0 < ncols) {
+          uint32_t v[16];
+          tmem_ld16(tacc + c0, v);
+          tmem_ld_wait();
+#pragma unroll
+          for (int c = 0; c < 16; ++c) sum[c0 + c] += __uint_as_float(v[c]);
+        }
+      }
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive_cluster(mapa_rank(smem_u32(tempty + acc), 0));
+    }
+    float* out = p.Gpart + (int64_t)sp * p.n_slots * p.ldg;
+#pragma unroll
+    for (int c = 0; c < kGrad2NC; ++c) {
+      const int slot = col0 + c;
+      if (c < ncols && slot < p.n_slots && j < p.d) out[(int64_t)slot * p.ldg + j] = sum[c];
+    }
+  }
+  tc_fence_before();
+  cluster_sync_all();       // the peer's shared and tensor memory stay alive until the leader's MMAs are done
+  if (warp == 9) tmem_dealloc_pair(tmem_base, kTmemCols);
 }
 
 // ---------------------------------------------------------------- Gram kernel (Ridge)

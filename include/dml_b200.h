@@ -162,6 +162,15 @@ int dml_last_timing(dml_ctx* ctx, float* total_ms, float* contraction_ms,
  * one column: 4*n_train*d flops), and the number of rounds. */
 int dml_last_counters(dml_ctx* ctx, int64_t* column_rounds, int32_t* rounds);
 
+/* Round 0 of the last logistic sweep.  Every fit starts at w = 0
+ * (sklearn/linear_model/_logistic.py:439,457), where z = 0 for every row and the
+ * loss / gradient sums depend on the row mask only, so the sweep evaluates the
+ * n_folds (+1) masks of one candidate and copies the sums to the others.
+ * Returns the contraction milliseconds and the column count of that round
+ * (both included in dml_last_timing / dml_last_counters); 0, 0 when the round
+ * ran in full (one candidate, or DML_FIRST_ROUND_ONCE=0). */
+int dml_last_first_round(dml_ctx* ctx, float* contraction_ms, int64_t* column_rounds);
+
 #ifdef __cplusplus
 }
 #endif
