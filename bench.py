@@ -24,6 +24,9 @@ import time
 
 import numpy as np
 
+# stdout carries exactly one JSON line: NCCL's own banner / debug output goes to stderr
+os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")
+
 ROOT = os.path.dirname(os.path.abspath(__file__))
 if ROOT not in sys.path:
     sys.path.insert(0, ROOT)
@@ -62,6 +65,7 @@ class ClockSampler(threading.Thread):
         super().__init__(daemon=True)
         self.gpu_index, self.stop_ev = gpu_index, threading.Event()
         self.sm, self.mx, self.reasons = [], [], set()
+        self.watts, self.limit_w = [], None
         try:
             import pynvml
             pynvml.nvmlInit()
@@ -81,6 +85,12 @@ class ClockSampler(threading.Thread):
             for bit, name in self.REASONS.items():
                 if bits & bit:
                     self.reasons.add(name)
+            try:                                     # board power next to the clocks: the sweep runs at the cap
+                self.watts.append(nv.nvmlDeviceGetPowerUsage(self.h) / 1000.0)
+                if self.limit_w is None:
+                    self.limit_w = nv.nvmlDeviceGetEnforcedPowerLimit(self.h) / 1000.0
+            except Exception:
+                pass
             return
         q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
              "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
@@ -106,6 +116,7 @@ class ClockSampler(threading.Thread):
         return {"sm_mhz": float(np.median(self.sm)) if self.sm else None,
                 "sm_max_mhz": max(self.mx) if self.mx else None,
                 "reasons": sorted(self.reasons), "samples": len(self.sm),
+                "power_w": float(np.median(self.watts)) if self.watts else None, "power_limit_w": self.limit_w,
                 "source": "nvml" if self.nv is not None else "nvidia-smi"}
 
 

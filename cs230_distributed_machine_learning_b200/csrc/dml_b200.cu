@@ -274,17 +274,17 @@ static int make_map_2d(dml_ctx* ctx, CUtensorMap* m, const void* base, uint64_t 
                                      (unsigned long long)stride_bytes, box_inner, box_outer);
   return DML_OK;
 }
-// 3-D view of a row-major fp32 matrix [rows][ld] as (32 columns, row, 32-column chunk): a box of
-// (32, box_rows, box_chunks) lands in shared memory as [chunk][row][128 B], which is the MN-major
-// operand layout of the gradient kernel.  Columns past `cols` read as zero.
+// 3-D view (32 columns, row, 32-column chunk) of the residual scratch, which is stored chunk-major
+// ([chunk][row][32 floats]) so that a box of 32 rows is one contiguous 4 KB run in HBM (row-major R made
+// every box 32 separate 128-byte pieces).  A box (32, box_rows, box_chunks) lands in shared memory as
+// [chunk][row][128 B], the MN-major operand layout of the gradient kernels.  Chunks past `cols` read as zero.
 static int make_map_chunked(dml_ctx* ctx, CUtensorMap* m, const void* base, uint64_t cols, uint64_t rows,
-                            uint64_t stride_bytes, uint32_t box_rows, uint32_t box_chunks) {
+                            uint32_t box_rows, uint32_t box_chunks) {
   if (!g_encode) { CUtensorMap tmp; int rc = make_map_2d(ctx, &tmp, base, 32, 1, 128, 32, 1); (void)rc; }
   if (!g_encode) return fail(ctx, DML_ERR_CUDA, "cuTensorMapEncodeTiled not available");
-  // the chunk dimension cannot clip inside a chunk, so the column extent is rounded up to a chunk;
-  // the caller guarantees that the memory behind it is readable (row pitch >= rounded extent) and zero
+  // memory is [chunk][row][32 floats]: rows of a chunk 128 B apart, chunks rows * 128 B apart
   cuuint64_t gdim[3] = {32, rows, (cols + 31) / 32};
-  cuuint64_t gstr[2] = {stride_bytes, 128};
+  cuuint64_t gstr[2] = {128, rows * 128};
   cuuint32_t box[3] = {32, box_rows, box_chunks};
   cuuint32_t est[3] = {1, 1, 1};
   const CUresult r = g_encode(m, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 3, const_cast<void*>(base), gdim, gstr, box, est,
@@ -527,12 +527,12 @@ struct EvalCtx {
     if ((rc = make_map_2d(ctx, &mXg, X, d, n, ldx * 4, 32, 32, true))) return rc;    // gradient: 32 rows x 32 features
     if ((rc = make_map_2d(ctx, &mWh, Whi, d, S_max, (uint64_t)ldw * 4, 32, NC))) return rc;
     if ((rc = make_map_2d(ctx, &mWl, Wlo, d, S_max, (uint64_t)ldw * 4, 32, NC))) return rc;
-    if ((rc = make_map_chunked(ctx, &mRh, R, ldr_max, chunk_rows, (uint64_t)ldr_max * 4, 32, NC / 32))) return rc;
-    if ((rc = make_map_chunked(ctx, &mRl, Rlo, ldr_max, chunk_rows, (uint64_t)ldr_max * 4, 32, NC / 32))) return rc;
+    if ((rc = make_map_chunked(ctx, &mRh, R, ldr_max, chunk_rows, 32, NC / 32))) return rc;
+    if ((rc = make_map_chunked(ctx, &mRl, Rlo, ldr_max, chunk_rows, 32, NC / 32))) return rc;
     grad2 = ctx->tc_grad2 != 0 && cdiv(d, 128) % 2 == 0;
     if (grad2) {
-      if ((rc = make_map_chunked(ctx, &mRh1, R, ldr_max, chunk_rows, (uint64_t)ldr_max * 4, 32, 1))) return rc;
-      if ((rc = make_map_chunked(ctx, &mRl1, Rlo, ldr_max, chunk_rows, (uint64_t)ldr_max * 4, 32, 1))) return rc;
+      if ((rc = make_map_chunked(ctx, &mRh1, R, ldr_max, chunk_rows, 32, 1))) return rc;
+      if ((rc = make_map_chunked(ctx, &mRl1, Rlo, ldr_max, chunk_rows, 32, 1))) return rc;
     }
     return DML_OK;
   }
@@ -553,7 +553,7 @@ struct EvalCtx {
         fp.n_rows_total = n; fp.row0 = r0; fp.rows = rows; fp.d_chunks = (int)cdiv(d, 32);
         fp.n_slots = n_slots; fp.n_col_blocks = ncb; fp.bt = bt; fp.ycls = y; fp.yreg = nullptr;
         fp.fold_id = fold_id; fp.hold_id = hold_id; fp.slot_sel = sel; fp.slot_val = val;
-        fp.Rhi = R; fp.Rlo = Rlo; fp.ldr = (int)ldr_max; fp.lossPart = lossPart; fp.gbPart = gbPart;
+        fp.Rhi = R; fp.Rlo = Rlo; fp.ldr = (int)ldr_max; fp.r_chunk_stride = chunk_rows * 32; fp.lossPart = lossPart; fp.gbPart = gbPart;
         fp.mask_hi = ctx->tc_mask_hi; fp.prefetch_jobs = ctx->tc_prefetch; fp.T = T; fp.loss_shift = loss_shift();
         // clusters of 2 share each X tile between two column blocks; with an odd number of blocks one
         // CTA of the last pair would run on empty columns, so small / odd cases run unclustered

@@ -251,7 +251,8 @@ struct TcFwdParams {
   const int32_t* ycls; const float* yreg;
   const int8_t* fold_id; const int8_t* hold_id;
   const int32_t* slot_sel; const int32_t* slot_val;
-  float* Rhi; float* Rlo; int ldr;       // [chunk rows][ldr]
+  float* Rhi; float* Rlo; int ldr;       // [ldr / 32 column chunks][chunk rows][32]: a chunk's rows are contiguous,
+  int64_t r_chunk_stride;                // so a gradient box (32 rows x 32 columns) is one 4 KB run; stride in floats
   double* lossPart; double* gbPart;      // [gridDim.x * 4][n_slots], zeroed by the caller
   int32_t* cntPart; double* ssePart;     // score modes, same shape
   int mask_hi;
@@ -538,11 +539,14 @@ tc_fwd_kernel(const __grid_constant__ CUtensorMap mapX, const __grid_constant__ 
             accA[i] += (double)warp_sum(loss);
             accB[i] += (double)bfly16(rs, lane);
             if (rt < n_row_tiles) {
-              float* dh = p.Rhi + lrow * p.ldr + slot0 + c0;
-              float* dl = p.Rlo + lrow * p.ldr + slot0 + c0;
 #pragma unroll
-              for (int c = 0; c < 16; ++c)
-                if (c < T && slot0 + c0 + c < p.ldr) { const float h = tf32_hi(rs[c]); dh[c] = h; dl[c] = rs[c] - h; }
+              for (int c = 0; c < 16; ++c) {
+                const int col = slot0 + c0 + c;
+                if (c < T && col < p.ldr) {
+                  const int64_t o = (int64_t)(col >> 5) * p.r_chunk_stride + lrow * 32 + (col & 31);
+                  const float h = tf32_hi(rs[c]); p.Rhi[o] = h; p.Rlo[o] = rs[c] - h;
+                }
+              }
             }
           }
         }
@@ -683,7 +687,8 @@ tc_fwd_kernel(const __grid_constant__ CUtensorMap mapX, const __grid_constant__ 
           if (rt < n_row_tiles && slot0 + c0 + 4 * tq < p.ldr) {
 #pragma unroll
             for (int j = 0; j < 4; ++j) {                         // j = row inside the group
-              const int64_t o = (lrow4 + j) * p.ldr + slot0 + c0 + 4 * tq;
+              const int col = slot0 + c0 + 4 * tq;
+              const int64_t o = (int64_t)(col >> 5) * p.r_chunk_stride + (lrow4 + j) * 32 + (col & 31);
               *reinterpret_cast<float4*>(p.Rhi + o) = make_float4(rs[4 * j], rs[4 * j + 1], rs[4 * j + 2], rs[4 * j + 3]);
               *reinterpret_cast<float4*>(p.Rlo + o) = make_float4(rl[4 * j], rl[4 * j + 1], rl[4 * j + 2], rl[4 * j + 3]);
             }
