@@ -57,6 +57,7 @@ struct dml_ctx {
   float total_ms = 0.f, contraction_ms = 0.f; int contraction_launches = 0, total_launches = 0;
   size_t r_budget = (size_t)4 << 30;  // bytes of residual scratch per row chunk
   size_t first_pairs = 0; float first_ms = 0.f; int64_t first_cols = 0;   // round 0 when it ran once per row mask
+  int fold_skip = 1;          // fold-major column groups, so that row tiles of one fold can skip that fold's columns
   int first_round_once = 1;   // evaluate round 0 once per row mask instead of once per candidate
   int tc_grad2 = 1;   // gradient contraction on CTA pairs (cta_group::2) when d spans an even number of 128-feature blocks
   int tc_prefetch = 0, tc_prefetch_grad = 0;  // L2 prefetch distance of the forward X tiles in jobs (0 = off; measured: no gain, the ring is not latency-bound)
@@ -164,6 +165,7 @@ extern "C" int dml_ctx_create(int device, void* stream, dml_ctx** out) {
   if (const char* e = getenv("DML_TC_PREFETCH_GRAD")) ctx->tc_prefetch_grad = atoi(e);
   if (const char* e = getenv("DML_TC_GRAD2")) ctx->tc_grad2 = atoi(e);
   if (const char* e = getenv("DML_FIRST_ROUND_ONCE")) ctx->first_round_once = atoi(e);
+  if (const char* e = getenv("DML_FOLD_SKIP")) ctx->fold_skip = atoi(e);
   if (const char* e = getenv("DML_TC_CLUSTER")) ctx->tc_cluster = atoi(e) == 1 ? 1 : 2;
   CU(cudaSetDevice(device));
   CU(cudaHostAlloc(&ctx->h_scalar, 64, cudaHostAllocDefault));
@@ -470,7 +472,8 @@ struct EvalCtx {
   float *Wt = nullptr, *bt = nullptr, *R = nullptr, *Rlo = nullptr, *Whi = nullptr, *Wlo = nullptr, *Gpart = nullptr;
   double *lossPart = nullptr, *gbPart = nullptr, *Gred = nullptr; int32_t *sel = nullptr, *val = nullptr, *cntPart = nullptr;
   CUtensorMap mXf, mXf2, mXg, mWh, mWl, mRh, mRl, mRh1, mRl1;   // mR?1: one 32-column chunk per box (CTA-pair gradient)
-  bool grad2 = false;   // mXf2: forward X box of a 2-CTA cluster member (64 rows)
+  bool grad2 = false;
+  const int* gstart = nullptr; int n_groups = 0;   // fold-major column groups of the current list (device), or null   // mXf2: forward X box of a 2-CTA cluster member (64 rows)
   unsigned long long* hist_local = nullptr;   // [512] label histogram of this rank's rows
   // the forward kernel sums (loss - shift) with shift = loss of the zero model: ln 2, or ln T (multinomial)
   float loss_shift() const { return T == 1 ? 0.693147182f : logf((float)T); }
@@ -639,14 +642,19 @@ struct EvalCtx {
 };
 
 // Round 0 starts every fit at w = 0, where the loss and gradient sums depend on the row mask only:
-// rows [0, n_unique) of Gred (candidate 0's fits) are copied to the same fits of the other candidates.
-__global__ void broadcast_first_round_kernel(double* __restrict__ Gred, int ldgr, int n_unique, int n_slots) {
+// `Gu` holds the sums of candidate 0's fits (fit k, class t at row k*T + t); every list entry gets the
+// row of its own fit number within the candidate.
+__global__ void broadcast_first_round_kernel(double* __restrict__ Gred, const double* __restrict__ Gu, int ldgr,
+                                             const int* __restrict__ active_fits, int n_list, int fpc, int T) {
   const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-  const int64_t total = (int64_t)(n_slots - n_unique) * ldgr;
+  const int64_t total = (int64_t)n_list * T * ldgr;
   if (i >= total) return;
-  const int64_t slot = n_unique + i / ldgr; const int j = (int)(i % ldgr);
-  Gred[slot * ldgr + j] = Gred[(slot % n_unique) * ldgr + j];
+  const int64_t slot = i / ldgr; const int j = (int)(i % ldgr);
+  const int fit = active_fits[slot / T];
+  if (fit < 0) return;
+  Gred[i] = Gu[(int64_t)((fit % fpc) * T + (int)(slot % T)) * ldgr + j];
 }
+__global__ void set_int_kernel(int* p, int v) { *p = v; }
 
 __global__ void fill_n_test_kernel(const unsigned long long* __restrict__ hist, int F, int fpc, int n_folds,
                                    int64_t* __restrict__ n_test) {
@@ -680,7 +688,11 @@ extern "C" int dml_logreg_sweep(dml_ctx* ctx, const float* X, int64_t n, int d, 
   const int F = n_cand * fpc, P = T * (d + 1);
   EvalCtx ev;
   ev.X = X; ev.n = n; ev.ldx = ldx; ev.d = d; ev.T = T; ev.y = y; ev.fold_id = fold_id; ev.hold_id = hold_id;
-  ev.S_max = (int64_t)F * T;
+  ev.use_tc = use_tensor_cores != 0 && tc_eligible(X, ldx, T);
+  // fold-major lists pad every fold's group of live fits to 32 columns (binary problems on the tcgen05 path)
+  const int pad_to = (ev.use_tc && T == 1 && ctx->fold_skip) ? 32 : 0;
+  const int F_pad = F + (pad_to ? fpc * pad_to : 0);
+  ev.S_max = (int64_t)F_pad * T;
   ev.use_tc = use_tensor_cores != 0 && tc_eligible(X, ldx, T);
   ev.xvec = (ldx % 4 == 0) && aligned16(X);
   if (use_tensor_cores == 1 && !ev.use_tc)
@@ -689,7 +701,7 @@ extern "C" int dml_logreg_sweep(dml_ctx* ctx, const float* X, int64_t n, int d, 
   if (cdiv(ev.S_max, ev.tile_n) > 65535) return fail(ctx, DML_ERR_LIMIT, "too many columns (%lld)", (long long)ev.S_max);
 
   FitState* d_st; double *d_x, *d_g, *d_dir, *d_gt, *d_S, *d_Y, *d_ys;
-  int *d_active, *d_nactive; unsigned long long* d_hist; long long* d_correct; int32_t* d_i32;
+  int *d_active, *d_nactive, *d_gstart; double* d_Gu; unsigned long long* d_hist; long long* d_correct; int32_t* d_i32;
   for (int pass = 0; pass < 2; ++pass) {
     Arena a(pass ? ctx->ws : nullptr);
     d_st = a.take<FitState>(F); d_i32 = a.take<int32_t>(3 * (size_t)F);
@@ -697,7 +709,8 @@ extern "C" int dml_logreg_sweep(dml_ctx* ctx, const float* X, int64_t n, int d, 
     d_dir = a.take<double>((size_t)F * P); d_gt = a.take<double>((size_t)F * P);
     d_S = a.take<double>((size_t)F * kMaxCor * P); d_Y = a.take<double>((size_t)F * kMaxCor * P);
     d_ys = a.take<double>((size_t)F * kMaxCor);
-    d_active = a.take<int>(F); d_nactive = a.take<int>(4);
+    d_active = a.take<int>(F_pad); d_nactive = a.take<int>(8); d_gstart = a.take<int>(fpc + 1);
+    d_Gu = a.take<double>((size_t)fpc * T * (d + 2));
     d_hist = a.take<unsigned long long>(512); d_correct = a.take<long long>(F);
     ev.take(a, F);
     if (!pass) { int rc = ensure_ws(ctx, a.off + 256); if (rc) return rc; }
@@ -723,36 +736,62 @@ extern "C" int dml_logreg_sweep(dml_ctx* ctx, const float* X, int64_t n, int d, 
   init_fits_kernel<<<(unsigned)cdiv(F, 128), 128, 0, st>>>(ip);
   KCHECK();
   TrialParams tp{d, T, P, ev.ldw, d_st, d_x, d_dir, d_active, d_nactive, ev.Wt, ev.bt, ev.sel, ev.val};
-  write_trial_kernel<<<F, 128, 0, st>>>(tp);
-  KCHECK();
-  ctx->total_launches += 3;
-
-  int n_active = F, rounds = 0;
-  while (n_active > 0) {
-    const int n_slots = n_active * T;
-    // round 0: all coefficients are zero (_logistic.py:439,457), so z = 0 for every column and the sums
-    // differ only by row mask -- evaluate candidate 0's fits (slots are [candidate][fit][class]) and copy
-    const int n_eval = (rounds == 0 && ctx->first_round_once) ? std::min(n_slots, fpc * T) : n_slots;
-    ctx->slot_rounds += n_eval; ctx->rounds += 1;
-    int rc = ev.evaluate(ctx, n_eval);
-    if (rc) return rc;
-    if (ctx->comm) { rc = allreduce(ctx, ev.Gred, (size_t)n_eval * ev.ldgr, kNcclFloat64); if (rc) return rc; }
-    if (n_eval < n_slots) {
-      ctx->first_pairs = ctx->ev_used / 2; ctx->first_cols = n_eval;
-      const int64_t total = (int64_t)(n_slots - n_eval) * ev.ldgr;
-      broadcast_first_round_kernel<<<(unsigned)cdiv(total, 256), 256, 0, st>>>(ev.Gred, ev.ldgr, n_eval, n_slots);
-      ctx->total_launches += 1;
-    }
-    LbfgsParams lp{d, T, P, ev.ldgr, d_st, d_x, d_g, d_dir, d_gt, d_S, d_Y, d_ys, d_active, d_nactive, ev.Gred};
-    lbfgs_update_kernel<<<n_active, 256, 0, st>>>(lp);
-    compact_kernel<<<1, 1024, 0, st>>>(d_st, F, d_active, d_nactive, d_nactive + 1);
-    write_trial_kernel<<<n_active, 128, 0, st>>>(tp);
+  CompactParams cp{d_st, F, fpc, pad_to, d_active, d_nactive, d_gstart, d_nactive + 4};
+  LbfgsParams lp{d, T, P, ev.ldgr, d_st, d_x, d_g, d_dir, d_gt, d_S, d_Y, d_ys, d_active, d_nactive, ev.Gred};
+  ctx->total_launches += 1;
+  int n_list = 0, n_real = 0, rounds = 0;
+  auto next_list = [&]() -> int {      // live fits -> list of the next round; trial weights in that layout
+    compact_groups_kernel<<<1, 1024, 0, st>>>(cp);
+    write_trial_kernel<<<F_pad, 128, 0, st>>>(tp);
     KCHECK();
-    CU(cudaMemcpyAsync(ctx->h_scalar, d_nactive, sizeof(int), cudaMemcpyDeviceToHost, st));
+    CU(cudaMemcpyAsync(ctx->h_scalar, d_nactive + 4, 3 * sizeof(int), cudaMemcpyDeviceToHost, st));
     CU(cudaStreamSynchronize(st));
-    n_active = ctx->h_scalar[0];
-    ctx->total_launches += 3;
-    if (++rounds > 200000) return fail(ctx, DML_ERR_LIMIT, "dml_logreg_sweep: round cap hit");
+    n_list = ctx->h_scalar[0]; n_real = ctx->h_scalar[1];
+    ev.gstart = ctx->h_scalar[2] ? d_gstart : nullptr; ev.n_groups = fpc;
+    ctx->total_launches += 2;
+    return DML_OK;
+  };
+  auto evaluate_list = [&]() -> int {
+    ctx->slot_rounds += (int64_t)n_real * T; ctx->rounds += 1; ++rounds;
+    int rc = ev.evaluate(ctx, n_list * T);
+    if (rc) return rc;
+    if (ctx->comm) rc = allreduce(ctx, ev.Gred, (size_t)n_list * T * ev.ldgr, kNcclFloat64);
+    return rc;
+  };
+  // round 0: all coefficients are zero (_logistic.py:439,457), so z = 0 for every column and the sums
+  // differ only by row mask -- evaluate candidate 0's fits (fits 0 .. fpc-1) and copy the sums
+  if (ctx->first_round_once && n_cand > 1) {
+    set_int_kernel<<<1, 1, 0, st>>>(d_nactive, fpc);
+    write_trial_kernel<<<fpc, 128, 0, st>>>(tp);
+    KCHECK();
+    ev.gstart = nullptr;
+    ctx->slot_rounds += (int64_t)fpc * T; ctx->rounds += 1; ++rounds;
+    int rc = ev.evaluate(ctx, fpc * T);
+    if (rc) return rc;
+    if (ctx->comm) { rc = allreduce(ctx, ev.Gred, (size_t)fpc * T * ev.ldgr, kNcclFloat64); if (rc) return rc; }
+    ctx->first_pairs = ctx->ev_used / 2; ctx->first_cols = (int64_t)fpc * T;
+    CU(cudaMemcpyAsync(d_Gu, ev.Gred, sizeof(double) * (size_t)fpc * T * ev.ldgr, cudaMemcpyDeviceToDevice, st));
+    rc = next_list();
+    if (rc) return rc;
+    const int64_t total = (int64_t)n_list * T * ev.ldgr;
+    broadcast_first_round_kernel<<<(unsigned)cdiv(total, 256), 256, 0, st>>>(ev.Gred, d_Gu, ev.ldgr, d_active, n_list, fpc, T);
+    KCHECK();
+    ctx->total_launches += 4;
+  } else {
+    int rc = next_list();
+    if (rc) return rc;
+    rc = evaluate_list();
+    if (rc) return rc;
+  }
+  while (true) {
+    lbfgs_update_kernel<<<n_list, 256, 0, st>>>(lp);
+    ctx->total_launches += 1;
+    int rc = next_list();
+    if (rc) return rc;
+    if (n_real == 0) break;
+    rc = evaluate_list();
+    if (rc) return rc;
+    if (rounds > 200000) return fail(ctx, DML_ERR_LIMIT, "dml_logreg_sweep: round cap hit");
   }
   // results + score pass on every fit's held-out rows
   FinalParams fin{F, d, T, P, ev.ldw, d_st, d_x, coef_out, intercept_out, n_iter_out ? n_iter_out : d_i32,
@@ -763,9 +802,10 @@ extern "C" int dml_logreg_sweep(dml_ctx* ctx, const float* X, int64_t n, int d, 
   ctx->total_launches += 1;
   if (correct_out || n_test_out) {
     int64_t n_parts = 0;
-    int rc = ev.score_cls(ctx, (int)ev.S_max, &n_parts);
+    ev.gstart = nullptr;
+    int rc = ev.score_cls(ctx, F * T, &n_parts);
     if (rc) return rc;
-    reduce_counts_kernel<<<F, 256, 0, st>>>(ev.cntPart, n_parts, (int)ev.S_max, T, d_correct);
+    reduce_counts_kernel<<<F, 256, 0, st>>>(ev.cntPart, n_parts, F * T, T, d_correct);
     KCHECK();
     if (ctx->comm) { rc = allreduce(ctx, d_correct, F, kNcclInt64); if (rc) return rc; }
     if (correct_out) CU(cudaMemcpyAsync(correct_out, d_correct, sizeof(int64_t) * F, cudaMemcpyDeviceToDevice, st));

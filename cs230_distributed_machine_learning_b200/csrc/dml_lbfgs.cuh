@@ -155,6 +155,7 @@ __global__ void __launch_bounds__(256) lbfgs_update_kernel(const LbfgsParams p) 
   const int a = blockIdx.x;
   if (a >= *p.n_active) return;
   const int fit = p.active_fits[a];
+  if (fit < 0) return;                 // padding entry of a fold-major list (compact_groups_kernel)
   FitState s = p.st[fit];
   const int d = p.d, T = p.T, P = p.P, D1 = d + 1;
   double* x = p.x + (int64_t)fit * P;
@@ -294,6 +295,81 @@ __global__ void compact_kernel(const FitState* st, int n_fits, int* active_fits,
   if (threadIdx.x == 0) { *n_active = base; *n_active_host = base; }
 }
 
+// Live fits -> list for the next round.  With `pad_to` > 0 the list is fold-major: the fits of fold
+// (or hold-out split) k, in candidate order, then -1 entries up to a multiple of `pad_to`; group k
+// occupies list positions [gstart[k], gstart[k+1]).  A row tile whose rows all sit in fold k trains
+// none of group k's columns, so the contraction kernels skip that column range for it.  The padded
+// form is used while it costs at most an eighth more columns than the dense list; otherwise (and
+// with pad_to == 0) the list is dense in fit order and gstart[0] = -1 (no column ranges).  One block.
+struct CompactParams {
+  const FitState* st; int n_fits, fpc, pad_to;
+  int* active_fits;
+  int* counts;        // [0] list length (n_active of the next round), [1] live fits, [2] 1 = fold-major padded
+  int* gstart;        // [fpc + 1]
+  int* counts_host;   // copy of counts[0..2] the host reads
+};
+__global__ void compact_groups_kernel(const CompactParams p) {
+  __shared__ int cnt[128], start[129], warp_tot[32], base, grouped;
+  const int lane = threadIdx.x & 31, w = threadIdx.x >> 5, nw = blockDim.x >> 5;
+  for (int k = threadIdx.x; k < p.fpc; k += blockDim.x) cnt[k] = 0;
+  __syncthreads();
+  for (int f = threadIdx.x; f < p.n_fits; f += blockDim.x)
+    if (p.st[f].active != 0) atomicAdd(&cnt[f % p.fpc], 1);
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    int dense = 0, padded = 0;
+    start[0] = 0;
+    for (int k = 0; k < p.fpc; ++k) {
+      dense += cnt[k];
+      if (p.pad_to > 0) padded += (cnt[k] + p.pad_to - 1) / p.pad_to * p.pad_to;
+      start[k + 1] = padded;
+    }
+    grouped = (p.pad_to > 0 && dense > 0 && padded * 8 <= ((dense + 31) / 32 * 32) * 9) ? 1 : 0;
+    base = 0;
+    p.counts[0] = grouped ? padded : dense; p.counts[1] = dense; p.counts[2] = grouped;
+    p.counts_host[0] = p.counts[0]; p.counts_host[1] = dense; p.counts_host[2] = grouped;
+    for (int k = 0; k <= p.fpc; ++k) p.gstart[k] = grouped ? start[k] : -1;
+  }
+  __syncthreads();
+  if (!grouped) {                       // dense, fit order
+    for (int f0 = 0; f0 < p.n_fits; f0 += blockDim.x) {
+      const int f = f0 + threadIdx.x;
+      const int flag = (f < p.n_fits) ? (p.st[f].active != 0) : 0;
+      const unsigned bal = __ballot_sync(0xffffffffu, flag);
+      if (lane == 0) warp_tot[w] = __popc(bal);
+      __syncthreads();
+      int off = base;
+      for (int i = 0; i < w; ++i) off += warp_tot[i];
+      if (flag) p.active_fits[off + __popc(bal & ((1u << lane) - 1))] = f;
+      __syncthreads();
+      if (threadIdx.x == 0) { int t = 0; for (int i = 0; i < nw; ++i) t += warp_tot[i]; base += t; }
+      __syncthreads();
+    }
+    return;
+  }
+  const int n_cand = p.n_fits / p.fpc;
+  for (int k = 0; k < p.fpc; ++k) {
+    if (threadIdx.x == 0) base = start[k];
+    __syncthreads();
+    for (int c0 = 0; c0 < n_cand; c0 += blockDim.x) {
+      const int c = c0 + threadIdx.x;
+      const int f = c * p.fpc + k;
+      const int flag = (c < n_cand) ? (p.st[f].active != 0) : 0;
+      const unsigned bal = __ballot_sync(0xffffffffu, flag);
+      if (lane == 0) warp_tot[w] = __popc(bal);
+      __syncthreads();
+      int off = base;
+      for (int i = 0; i < w; ++i) off += warp_tot[i];
+      if (flag) p.active_fits[off + __popc(bal & ((1u << lane) - 1))] = f;
+      __syncthreads();
+      if (threadIdx.x == 0) { int t = 0; for (int i = 0; i < nw; ++i) t += warp_tot[i]; base += t; }
+      __syncthreads();
+    }
+    for (int i = start[k] + cnt[k] + threadIdx.x; i < start[k + 1]; i += blockDim.x) p.active_fits[i] = -1;
+    __syncthreads();
+  }
+}
+
 // trial point of every active fit, rounded to fp32, in the layout the contraction kernels read
 struct TrialParams {
   int d, T, P, ldw;
@@ -305,6 +381,14 @@ __global__ void write_trial_kernel(const TrialParams p) {
   const int a = blockIdx.x;
   if (a >= *p.n_active) return;
   const int fit = p.active_fits[a], D1 = p.d + 1;
+  if (fit < 0) {                       // padding entry: zero weights, mask -1 = "holds out every row"
+    for (int idx = threadIdx.x; idx < p.P; idx += blockDim.x) {
+      const int t = idx / D1, j = idx - t * D1, slot = a * p.T + t;
+      if (j < p.d) p.Wt[(int64_t)slot * p.ldw + j] = 0.f;
+      else { p.bt[slot] = 0.f; p.slot_sel[slot] = -1; p.slot_val[slot] = 0; }
+    }
+    return;
+  }
   const FitState& s = p.st[fit];
   const double stp = s.phase == 0 ? 0.0 : s.stp;
   const double* x = p.x + (int64_t)fit * p.P;

@@ -482,7 +482,7 @@ tc_fwd_kernel(const __grid_constant__ CUtensorMap mapX, const __grid_constant__ 
               bool held = true;
               if (slot < p.n_slots) {
                 const int sel = __ldg(p.slot_sel + slot), val = __ldg(p.slot_val + slot) & 0xff;
-                held = v < kMaxLabel ? (sel == 0 && val == v) : (sel == 1 && val == v - kMaxLabel);
+                held = sel < 0 || (v < kMaxLabel ? (sel == 0 && val == v) : (sel == 1 && val == v - kMaxLabel));   // mask -1: padding column
               }
               bits |= (held ? 1u : 0u) << j;
             }
@@ -605,7 +605,7 @@ tc_fwd_kernel(const __grid_constant__ CUtensorMap mapX, const __grid_constant__ 
             bool held = true;                                        // a column that does not exist holds out every row
             if (slot < p.n_slots) {
               const int sel = __ldg(p.slot_sel + slot), val = __ldg(p.slot_val + slot) & 0xff;
-              held = v < kMaxLabel ? (sel == 0 && val == v) : (sel == 1 && val == v - kMaxLabel);
+              held = sel < 0 || (v < kMaxLabel ? (sel == 0 && val == v) : (sel == 1 && val == v - kMaxLabel));   // mask -1: padding column
             }
             bits |= (held ? 1u : 0u) << j;
           }
@@ -1409,7 +1409,7 @@ __global__ void tc_reduce_tiles_kernel(const TcReduceParams p) {   // block (32 
     for (int i = 0; i < 32; ++i) { l += sh[0][i][threadIdx.x]; g += sh[1][i][threadIdx.x]; }   // fixed order
     double* q = p.Gred + (int64_t)slot * p.ldgr;
     q[p.d] = p.accumulate ? q[p.d] + g : g;
-    if (!p.accumulate)
+    if (!p.accumulate && p.sel[slot] >= 0)     // (a padding column has mask -1 and no rows)
       l += p.loss_shift * (double)(p.n_local - (int64_t)p.hist_local[p.sel[slot] * 256 + (p.val[slot] & 0xff)]);
     if (slot % p.T == 0) q[p.d + 1] = p.accumulate ? q[p.d + 1] + l : l;
   }
