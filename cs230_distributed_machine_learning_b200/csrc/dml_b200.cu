@@ -473,7 +473,7 @@ struct EvalCtx {
   double *lossPart = nullptr, *gbPart = nullptr, *Gred = nullptr; int32_t *sel = nullptr, *val = nullptr, *cntPart = nullptr;
   CUtensorMap mXf, mXf2, mXg, mWh, mWl, mRh, mRl, mRh1, mRl1;   // mR?1: one 32-column chunk per box (CTA-pair gradient)
   bool grad2 = false;
-  const int* gstart = nullptr; int n_groups = 0;   // fold-major column groups of the current list (device), or null   // mXf2: forward X box of a 2-CTA cluster member (64 rows)
+  const int* gstart = nullptr; int n_groups = 0; uint8_t* tile_fold = nullptr;   // fold-major column groups of the current list (device), or null   // mXf2: forward X box of a 2-CTA cluster member (64 rows)
   unsigned long long* hist_local = nullptr;   // [512] label histogram of this rank's rows
   // the forward kernel sums (loss - shift) with shift = loss of the zero model: ln 2, or ln T (multinomial)
   float loss_shift() const { return T == 1 ? 0.693147182f : logf((float)T); }
@@ -506,6 +506,7 @@ struct EvalCtx {
   }
   void take(Arena& a, int64_t n_groups_max) {
     Gred = a.take<double>((size_t)S_max * ldgr);
+    tile_fold = a.take<uint8_t>((size_t)cdiv(n, 128) + 16);
     hist_local = a.take<unsigned long long>(512);
     Wt = a.take<float>((size_t)S_max * ldw); bt = a.take<float>(S_max);
     sel = a.take<int32_t>(S_max); val = a.take<int32_t>(S_max);
@@ -558,6 +559,7 @@ struct EvalCtx {
         fp.fold_id = fold_id; fp.hold_id = hold_id; fp.slot_sel = sel; fp.slot_val = val;
         fp.Rhi = R; fp.Rlo = Rlo; fp.ldr = (int)ldr_max; fp.r_chunk_stride = chunk_rows * 32; fp.lossPart = lossPart; fp.gbPart = gbPart;
         fp.mask_hi = ctx->tc_mask_hi; fp.prefetch_jobs = ctx->tc_prefetch; fp.T = T; fp.loss_shift = loss_shift();
+        fp.tile_fold = tile_fold; fp.gstart = gstart; fp.n_groups = n_groups;
         // clusters of 2 share each X tile between two column blocks; with an odd number of blocks one
         // CTA of the last pair would run on empty columns, so small / odd cases run unclustered
         const int clr = (cl == 2 && ncb >= 2 && (ncb % 2 == 0 || ncb >= 5)) ? 2 : 1;
@@ -655,6 +657,20 @@ __global__ void broadcast_first_round_kernel(double* __restrict__ Gred, const do
   Gred[i] = Gu[(int64_t)((fit % fpc) * T + (int)(slot % T)) * ldgr + j];
 }
 __global__ void set_int_kernel(int* p, int v) { *p = v; }
+// tile_fold[t] = fold id shared by all rows of the 128-row tile t, or 255 when the tile mixes folds
+__global__ void tile_fold_kernel(const int8_t* __restrict__ fold_id, int64_t n, uint8_t* __restrict__ tile_fold) {
+  const int64_t t = (int64_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+  const int lane = threadIdx.x & 31;
+  if (t * 128 >= n) return;
+  const int first = (int)(uint8_t)fold_id[t * 128];
+  bool same = true;
+  for (int i = lane; i < 128; i += 32) {
+    const int64_t r = t * 128 + i;
+    if (r < n && (int)(uint8_t)fold_id[r] != first) same = false;
+  }
+  same = __all_sync(0xffffffffu, same);
+  if (lane == 0) tile_fold[t] = same ? (uint8_t)first : (uint8_t)255;
+}
 
 __global__ void fill_n_test_kernel(const unsigned long long* __restrict__ hist, int F, int fpc, int n_folds,
                                    int64_t* __restrict__ n_test) {
@@ -724,6 +740,11 @@ extern "C" int dml_logreg_sweep(dml_ctx* ctx, const float* X, int64_t n, int d, 
   label_hist_kernel<<<(unsigned)std::min<int64_t>(cdiv(n, 256), 4 * ctx->n_sms), 256, 0, st>>>(fold_id, hold_id, n, ev.hist_local);
   KCHECK();
   CU(cudaMemcpyAsync(d_hist, ev.hist_local, sizeof(unsigned long long) * 512, cudaMemcpyDeviceToDevice, st));
+  if (pad_to) {
+    tile_fold_kernel<<<(unsigned)cdiv(cdiv(n, 128), 8), 256, 0, st>>>(fold_id, n, ev.tile_fold);
+    KCHECK();
+    ctx->total_launches += 1;
+  }
   int64_t n_total = n;
   if (ctx->comm) {
     int rc = allreduce(ctx, d_hist, 512, kNcclUint64); if (rc) return rc;
@@ -747,7 +768,7 @@ extern "C" int dml_logreg_sweep(dml_ctx* ctx, const float* X, int64_t n, int d, 
     CU(cudaMemcpyAsync(ctx->h_scalar, d_nactive + 4, 3 * sizeof(int), cudaMemcpyDeviceToHost, st));
     CU(cudaStreamSynchronize(st));
     n_list = ctx->h_scalar[0]; n_real = ctx->h_scalar[1];
-    ev.gstart = ctx->h_scalar[2] ? d_gstart : nullptr; ev.n_groups = fpc;
+    ev.gstart = ctx->h_scalar[2] ? d_gstart : nullptr; ev.n_groups = n_folds;   // only CV folds own row tiles (group n_folds = hold-out split)
     ctx->total_launches += 2;
     return DML_OK;
   };

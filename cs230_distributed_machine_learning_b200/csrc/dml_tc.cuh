@@ -251,6 +251,10 @@ struct TcFwdParams {
   const int32_t* ycls; const float* yreg;
   const int8_t* fold_id; const int8_t* hold_id;
   const int32_t* slot_sel; const int32_t* slot_val;
+  // fold-aware skipping (binary training mode): tile_fold[t] = the fold id shared by all rows of global row
+  // tile t (255: mixed); gstart[k] .. gstart[k+1] = the columns of fold k's fits (multiples of 32).  A tile of
+  // fold k trains none of them: no MMAs, no epilogue math for that column range.  gstart == nullptr: off.
+  const uint8_t* tile_fold; const int* gstart; int n_groups;
   float* Rhi; float* Rlo; int ldr;       // [ldr / 32 column chunks][chunk rows][32]: a chunk's rows are contiguous,
   int64_t r_chunk_stride;                // so a gradient box (32 rows x 32 columns) is one 4 KB run; stride in floats
   double* lossPart; double* gbPart;      // [gridDim.x * 4][n_slots], zeroed by the caller
@@ -343,6 +347,15 @@ tc_fwd_kernel(const __grid_constant__ CUtensorMap mapX, const __grid_constant__ 
   const int64_t job0 = blockIdx.x / CL, job_step = gridDim.x / CL;
   auto job_cb = [&](int64_t job) { return (int)(job / n_row_tiles) * CL + crank; };  // may be >= n_col_blocks (no columns)
   auto job_rt = [&](int64_t job) { return job % n_row_tiles; };
+  // block-local column range [sa, sb) that the rows of this tile do not train (empty: sa == sb == 0)
+  auto hole_of = [&](int cb, int64_t rt, int& sa, int& sb) {
+    sa = 0; sb = 0;
+    if (MODE != FWD_LOGREG || p.gstart == nullptr) return;
+    const int k = p.tile_fold[p.row0 / 128 + rt];
+    if (k >= p.n_groups) return;
+    const int lo = max(p.gstart[k], cb * NC) - cb * NC, hi = min(p.gstart[k + 1], cb * NC + NC) - cb * NC;
+    if (hi > lo) { sa = lo; sb = hi; }
+  };
 
   if (warp == kFwdTmaWarp) {
     // ===== TMA producer =====
@@ -372,10 +385,13 @@ tc_fwd_kernel(const __grid_constant__ CUtensorMap mapX, const __grid_constant__ 
     }
   } else if (warp == kFwdMmaWarp) {
     // ===== MMA issuer =====
-    constexpr uint32_t idesc = instr_desc_tf32(128, NC, 0, 0);
     uint32_t it = 0, tile = 0;
     for (int64_t job = job0; job < n_jobs; job += job_step, ++tile) {
       const int acc = tile & 1; const uint32_t aph = (tile >> 1) & 1;
+      int sa, sb;
+      hole_of(job_cb(job), job_rt(job), sa, sb);
+      // column ranges [0, sa) and [sb, NC); without a hole the first one is empty
+      const uint32_t idesc_a = instr_desc_tf32(128, sa, 0, 0), idesc_b = instr_desc_tf32(128, NC - sb, 0, 0);
       mbar_wait(tempty + acc, aph ^ 1);
       tc_fence_after();
       const uint32_t tacc = tmem_base + acc * NC;
@@ -387,12 +403,24 @@ tc_fwd_kernel(const __grid_constant__ CUtensorMap mapX, const __grid_constant__ 
         if (elect_one()) {
           const uint32_t b_hi = smem_u32(smem + s * L::kStage) + L::kA, b_lo = b_hi + L::kB;
           const uint32_t ta_hi = tmem_base + kTmemA + s * 64, ta_lo = ta_hi + 32;
+          if (sa > 0) {
 #pragma unroll
-          for (int k = 0; k < 4; ++k) {
-            const uint64_t dbh = smem_desc(b_hi + k * 32, 16, 1024), dbl = smem_desc(b_lo + k * 32, 16, 1024);
-            umma_tf32_ts(tacc, ta_lo + k * 8, dbh, idesc, (c | k) != 0);   // small terms first
-            umma_tf32_ts(tacc, ta_hi + k * 8, dbl, idesc, 1);
-            umma_tf32_ts(tacc, ta_hi + k * 8, dbh, idesc, 1);
+            for (int k = 0; k < 4; ++k) {
+              const uint64_t dbh = smem_desc(b_hi + k * 32, 16, 1024), dbl = smem_desc(b_lo + k * 32, 16, 1024);
+              umma_tf32_ts(tacc, ta_lo + k * 8, dbh, idesc_a, (c | k) != 0);   // small terms first
+              umma_tf32_ts(tacc, ta_hi + k * 8, dbl, idesc_a, 1);
+              umma_tf32_ts(tacc, ta_hi + k * 8, dbh, idesc_a, 1);
+            }
+          }
+          if (sb < NC) {
+            const uint32_t off = (uint32_t)sb * 128;       // W rows are 128 B apart (8-row swizzle atoms: sb % 8 == 0)
+#pragma unroll
+            for (int k = 0; k < 4; ++k) {
+              const uint64_t dbh = smem_desc(b_hi + off + k * 32, 16, 1024), dbl = smem_desc(b_lo + off + k * 32, 16, 1024);
+              umma_tf32_ts(tacc + sb, ta_lo + k * 8, dbh, idesc_b, (c | k) != 0);
+              umma_tf32_ts(tacc + sb, ta_hi + k * 8, dbl, idesc_b, 1);
+              umma_tf32_ts(tacc + sb, ta_hi + k * 8, dbh, idesc_b, 1);
+            }
           }
           if (CL == 1) umma_commit(empty + s);
           else umma_commit_mcast(empty + s, (1 << CL) - 1);   // the stage is refilled by both CTAs
@@ -625,6 +653,8 @@ tc_fwd_kernel(const __grid_constant__ CUtensorMap mapX, const __grid_constant__ 
       const float yy = (float)yv;
       const uint32_t held_f = held_s + fold_v * NCH * 2, held_h = held_s + (kMaxLabel + hold_v) * NCH * 2;
       const int acc = tile & 1; const uint32_t aph = (tile >> 1) & 1;
+      int sa, sb;
+      hole_of(cb, rt, sa, sb);
       mbar_wait(tfull + acc, aph);
       tc_fence_after();
       const uint32_t tacc = tmem_base + acc * NC + ((uint32_t)(q * 32) << 16);
@@ -634,13 +664,30 @@ tc_fwd_kernel(const __grid_constant__ CUtensorMap mapX, const __grid_constant__ 
         const int ci = G * i + grp;
         if (ci >= NCH) break;
         const int c0 = ci * 16;
+        const bool in_hole = MODE == FWD_LOGREG && c0 >= sa && c0 + 16 <= sb;   // no row of this tile trains these columns
         uint32_t v[16];
-        tmem_ld16(tacc + c0, v);
-        tmem_ld_wait();
+        if (!in_hole) {
+          tmem_ld16(tacc + c0, v);
+          tmem_ld_wait();
+        }
         if (ci == last_ci) {                 // this warp's last read of the accumulator
           tc_fence_before();
           __syncwarp();
           if (lane == 0) mbar_arrive(tempty + acc);
+        }
+        if (in_hole) {                       // residuals are zero there; the MMAs never wrote these TMEM columns
+          const int tq = lane & 3;
+          const int64_t lrow4 = rt * 128 + q * 32 + (lane & ~3);
+          const int col = slot0 + c0 + 4 * tq;
+          if (rt < n_row_tiles && col < p.ldr) {
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+              const int64_t o = (int64_t)(col >> 5) * p.r_chunk_stride + (lrow4 + j) * 32 + (col & 31);
+              *reinterpret_cast<float4*>(p.Rhi + o) = make_float4(0.f, 0.f, 0.f, 0.f);
+              *reinterpret_cast<float4*>(p.Rlo + o) = make_float4(0.f, 0.f, 0.f, 0.f);
+            }
+          }
+          continue;
         }
         // bit j set: column c0 + j does not train on (LOGREG) / is scored on (SCORE) this row
         const uint32_t heldbits = valid ? (lds16u(held_f + ci * 2) | lds16u(held_h + ci * 2)) : 0xffffu;
