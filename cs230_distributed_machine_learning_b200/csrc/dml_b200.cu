@@ -59,7 +59,6 @@ struct dml_ctx {
   size_t first_pairs = 0; float first_ms = 0.f; int64_t first_cols = 0;   // round 0 when it ran once per row mask
   int fold_skip = 1;          // fold-major column groups, so that row tiles of one fold can skip that fold's columns
   int first_round_once = 1;   // evaluate round 0 once per row mask instead of once per candidate
-  int tc_grad2 = 1;   // gradient contraction on CTA pairs (cta_group::2) when d spans an even number of 128-feature blocks
   int tc_prefetch = 0, tc_prefetch_grad = 0;  // L2 prefetch distance of the forward X tiles in jobs (0 = off; measured: no gain, the ring is not latency-bound)
   int tc_cluster = 2;                 // CTAs per cluster in the forward kernel (W multicast): 1 or 2
   int tc_mask_hi = 0;                 // 1 = write the masked hi operand back before the MMAs read it (not needed:
@@ -163,7 +162,6 @@ extern "C" int dml_ctx_create(int device, void* stream, dml_ctx** out) {
   if (const char* e = getenv("DML_TC_MASK_HI")) ctx->tc_mask_hi = atoi(e);
   if (const char* e = getenv("DML_TC_PREFETCH")) ctx->tc_prefetch = atoi(e);
   if (const char* e = getenv("DML_TC_PREFETCH_GRAD")) ctx->tc_prefetch_grad = atoi(e);
-  if (const char* e = getenv("DML_TC_GRAD2")) ctx->tc_grad2 = atoi(e);
   if (const char* e = getenv("DML_FIRST_ROUND_ONCE")) ctx->first_round_once = atoi(e);
   if (const char* e = getenv("DML_FOLD_SKIP")) ctx->fold_skip = atoi(e);
   if (const char* e = getenv("DML_TC_CLUSTER")) ctx->tc_cluster = atoi(e) == 1 ? 1 : 2;
@@ -343,44 +341,22 @@ static int launch_tc_fwd(dml_ctx* ctx, int NC, int cl, int grid, const CUtensorM
   }
 #undef DML_FWD_CASE
 }
-template <int NC>
-static int launch_tc_grad_nc(dml_ctx* ctx, dim3 grid, const CUtensorMap& mx, const CUtensorMap& mrh, const CUtensorMap& mrl,
-                             const tc::TcGradParams& p) {
-  static bool attr_set = false;
-  if (!attr_set) {
-    CU(cudaFuncSetAttribute(tc::tc_grad_kernel<NC>, cudaFuncAttributeMaxDynamicSharedMemorySize, tc::GradSmem<NC>::kBytes));
-    attr_set = true;
-  }
-  tc::tc_grad_kernel<NC><<<grid, tc::kGradThreads, tc::GradSmem<NC>::kBytes, ctx->stream>>>(mx, mrh, mrl, p);
-  return DML_OK;
-}
-static int launch_tc_grad(dml_ctx* ctx, int NC, dim3 grid, const CUtensorMap& mx, const CUtensorMap& mrh,
-                          const CUtensorMap& mrl, const tc::TcGradParams& p) {
-  switch (NC) {
-    case 160: return launch_tc_grad_nc<160>(ctx, grid, mx, mrh, mrl, p);
-    case 128: return launch_tc_grad_nc<128>(ctx, grid, mx, mrh, mrl, p);
-    case 96: return launch_tc_grad_nc<96>(ctx, grid, mx, mrh, mrl, p);
-    case 64: return launch_tc_grad_nc<64>(ctx, grid, mx, mrh, mrl, p);
-    default: return launch_tc_grad_nc<32>(ctx, grid, mx, mrh, mrl, p);
-  }
-}
-
-// CTA-pair gradient kernel: cluster of two along the feature-block axis, R maps with a one-chunk box
-static int launch_tc_grad2(dml_ctx* ctx, dim3 grid, const CUtensorMap& mx, const CUtensorMap& mrh, const CUtensorMap& mrl,
-                           const tc::TcGradParams& p) {
+// gradient kernel on CTA pairs: cluster of two along the feature-block axis (an odd block count leaves
+// the last pair's second CTA on zero-filled features), R map with a one-chunk box
+static int launch_tc_grad2(dml_ctx* ctx, dim3 grid, const CUtensorMap& mx, const CUtensorMap& mr, const tc::TcGradParams& p) {
   static bool attr_set = false;
   if (!attr_set) {
     CU(cudaFuncSetAttribute(tc::tc_grad2_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, tc::Grad2Smem::kBytes));
     attr_set = true;
   }
   cudaLaunchConfig_t cfg{};
-  cfg.gridDim = grid; cfg.blockDim = dim3(tc::kGradThreads);
+  cfg.gridDim = grid; cfg.blockDim = dim3(tc::kGrad2Threads);
   cfg.dynamicSmemBytes = tc::Grad2Smem::kBytes; cfg.stream = ctx->stream;
   cudaLaunchAttribute at[1];
   at[0].id = cudaLaunchAttributeClusterDimension;
   at[0].val.clusterDim.x = 2; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = 1;
   cfg.attrs = at; cfg.numAttrs = 1;
-  CU(cudaLaunchKernelEx(&cfg, tc::tc_grad2_kernel, mx, mrh, mrl, p));
+  CU(cudaLaunchKernelEx(&cfg, tc::tc_grad2_kernel, mx, mr, p));
   return DML_OK;
 }
 
@@ -469,10 +445,9 @@ struct EvalCtx {
   bool use_tc = false, xvec = false; int cl = 2; int NC = 160, nt = 1, tile_n = BN, ldw = 0, ldg = 0, ldgr = 0, splits = 1;
   int64_t S_max = 0, ldr_max = 0, chunk_rows = 0, rps = 0, tc_rps = 2048, tiles_total = 0; int ctx_sms = 148;
   // buffers
-  float *Wt = nullptr, *bt = nullptr, *R = nullptr, *Rlo = nullptr, *Whi = nullptr, *Wlo = nullptr, *Gpart = nullptr;
+  float *Wt = nullptr, *bt = nullptr, *R = nullptr, *Whi = nullptr, *Wlo = nullptr, *Gpart = nullptr;
   double *lossPart = nullptr, *gbPart = nullptr, *Gred = nullptr; int32_t *sel = nullptr, *val = nullptr, *cntPart = nullptr;
-  CUtensorMap mXf, mXf2, mXg, mWh, mWl, mRh, mRl, mRh1, mRl1;   // mR?1: one 32-column chunk per box (CTA-pair gradient)
-  bool grad2 = false;
+  CUtensorMap mXf, mXf2, mXg, mWh, mWl, mR1;   // mR1: residuals, one 32-column chunk x 32 rows per box
   const int* gstart = nullptr; int n_groups = 0; uint8_t* tile_fold = nullptr;   // fold-major column groups of the current list (device), or null   // mXf2: forward X box of a 2-CTA cluster member (64 rows)
   unsigned long long* hist_local = nullptr;   // [512] label histogram of this rank's rows
   // the forward kernel sums (loss - shift) with shift = loss of the zero model: ln 2, or ln T (multinomial)
@@ -491,7 +466,7 @@ struct EvalCtx {
     NC = pick_nc(S_max, T); if (NC == 0) NC = 160;
     ldr_max = use_tc ? cdiv(S_max, NC) * NC : rup(S_max, 4);   // tcgen05: whole column blocks, so 32-column chunks stay inside a row
     // row chunk so that the residual scratch stays within budget
-    chunk_rows = std::max<int64_t>(BM, (int64_t)(ctx->r_budget / (ldr_max * (use_tc ? 8 : 4))) / BM * BM);
+    chunk_rows = std::max<int64_t>(BM, (int64_t)(ctx->r_budget / (ldr_max * 4)) / BM * BM);
     chunk_rows = std::min<int64_t>(chunk_rows, rup(n, BM));
     nt = (int)cdiv(d + 1, BN);
     const int mt_max = (int)cdiv(S_max, BM);
@@ -517,7 +492,6 @@ struct EvalCtx {
     cntPart = a.take<int32_t>(use_tc ? tc_parts * S_max : (size_t)tiles_total * S_max);
     Gpart = a.take<float>((size_t)splits * S_max * ldg);
     if (use_tc) {
-      Rlo = a.take<float>((size_t)chunk_rows * ldr_max);
       gbPart = a.take<double>(tc_parts * S_max);
       Whi = a.take<float>((size_t)S_max * ldw); Wlo = a.take<float>((size_t)S_max * ldw);
     }
@@ -531,13 +505,7 @@ struct EvalCtx {
     if ((rc = make_map_2d(ctx, &mXg, X, d, n, ldx * 4, 32, 32, true))) return rc;    // gradient: 32 rows x 32 features
     if ((rc = make_map_2d(ctx, &mWh, Whi, d, S_max, (uint64_t)ldw * 4, 32, NC))) return rc;
     if ((rc = make_map_2d(ctx, &mWl, Wlo, d, S_max, (uint64_t)ldw * 4, 32, NC))) return rc;
-    if ((rc = make_map_chunked(ctx, &mRh, R, ldr_max, chunk_rows, 32, NC / 32))) return rc;
-    if ((rc = make_map_chunked(ctx, &mRl, Rlo, ldr_max, chunk_rows, 32, NC / 32))) return rc;
-    grad2 = ctx->tc_grad2 != 0 && cdiv(d, 128) % 2 == 0;
-    if (grad2) {
-      if ((rc = make_map_chunked(ctx, &mRh1, R, ldr_max, chunk_rows, 32, 1))) return rc;
-      if ((rc = make_map_chunked(ctx, &mRl1, Rlo, ldr_max, chunk_rows, 32, 1))) return rc;
-    }
+    if ((rc = make_map_chunked(ctx, &mR1, R, ldr_max, chunk_rows, 32, 1))) return rc;
     return DML_OK;
   }
   // Gred[slot] = [sum r x (d), sum r, sum loss] over the training rows of each column
@@ -557,7 +525,7 @@ struct EvalCtx {
         fp.n_rows_total = n; fp.row0 = r0; fp.rows = rows; fp.d_chunks = (int)cdiv(d, 32);
         fp.n_slots = n_slots; fp.n_col_blocks = ncb; fp.bt = bt; fp.ycls = y; fp.yreg = nullptr;
         fp.fold_id = fold_id; fp.hold_id = hold_id; fp.slot_sel = sel; fp.slot_val = val;
-        fp.Rhi = R; fp.Rlo = Rlo; fp.ldr = (int)ldr_max; fp.r_chunk_stride = chunk_rows * 32; fp.lossPart = lossPart; fp.gbPart = gbPart;
+        fp.R = R; fp.ldr = (int)ldr_max; fp.r_chunk_stride = chunk_rows * 32; fp.lossPart = lossPart; fp.gbPart = gbPart;
         fp.mask_hi = ctx->tc_mask_hi; fp.prefetch_jobs = ctx->tc_prefetch; fp.T = T; fp.loss_shift = loss_shift();
         fp.tile_fold = tile_fold; fp.gstart = gstart; fp.n_groups = n_groups;
         // clusters of 2 share each X tile between two column blocks; with an odd number of blocks one
@@ -572,11 +540,8 @@ struct EvalCtx {
         if (rc) return rc;
         tc::TcGradParams gp{r0, rows, tc_rps, d, n_slots, Gpart, ldg, ctx->tc_mask_hi, ctx->tc_prefetch_grad};
         const int splits_here = (int)cdiv(rows, tc_rps);
-        if (grad2)
-          rc = launch_tc_grad2(ctx, dim3((unsigned)cdiv(d, 128), (unsigned)cdiv(n_slots, tc::kGrad2NC), (unsigned)splits_here),
-                               mXg, mRh1, mRl1, gp);
-        else
-          rc = launch_tc_grad(ctx, NC, dim3((unsigned)cdiv(d, 128), (unsigned)ncb, (unsigned)splits_here), mXg, mRh, mRl, gp);
+        rc = launch_tc_grad2(ctx, dim3((unsigned)(2 * cdiv(cdiv(d, 128), 2)), (unsigned)cdiv(n_slots, tc::kGrad2NC), (unsigned)splits_here),
+                             mXg, mR1, gp);
         if (rc) return rc;
         ReduceParams rp{Gpart, ldg, splits_here, n_slots, d, T, d, nullptr, 0, 0, Gred, ldgr, ci > 0 ? 1 : 0};
         reduce_grad_kernel<<<n_slots, 256, 0, st>>>(rp);
@@ -608,7 +573,7 @@ struct EvalCtx {
     tock(ctx, launches);
     KCHECK();
     ctx->dbg_ptr[0] = R; ctx->dbg_bytes[0] = (size_t)chunk_rows * ldr_max * 4;
-    ctx->dbg_ptr[1] = Rlo; ctx->dbg_bytes[1] = Rlo ? (size_t)chunk_rows * ldr_max * 4 : 0;
+    ctx->dbg_ptr[1] = nullptr; ctx->dbg_bytes[1] = 0;
     ctx->dbg_ptr[2] = Gpart; ctx->dbg_bytes[2] = (size_t)splits * S_max * ldg * 4;
     ctx->dbg_ptr[3] = Whi; ctx->dbg_bytes[3] = Whi ? (size_t)S_max * ldw * 4 : 0;
     return DML_OK;

@@ -255,7 +255,7 @@ struct TcFwdParams {
   // tile t (255: mixed); gstart[k] .. gstart[k+1] = the columns of fold k's fits (multiples of 32).  A tile of
   // fold k trains none of them: no MMAs, no epilogue math for that column range.  gstart == nullptr: off.
   const uint8_t* tile_fold; const int* gstart; int n_groups;
-  float* Rhi; float* Rlo; int ldr;       // [ldr / 32 column chunks][chunk rows][32]: a chunk's rows are contiguous,
+  float* R; int ldr;                     // fp32 residuals, [ldr / 32 column chunks][chunk rows][32]: a chunk's rows are contiguous,
   int64_t r_chunk_stride;                // so a gradient box (32 rows x 32 columns) is one 4 KB run; stride in floats
   double* lossPart; double* gbPart;      // [gridDim.x * 4][n_slots], zeroed by the caller
   int32_t* cntPart; double* ssePart;     // score modes, same shape
@@ -272,7 +272,7 @@ struct FwdSmem {
   static constexpr int kB = NC * 128;
   static constexpr int kStage = kA + 2 * kB;
   // per column: bias; per label value: 16-bit held-column masks, one per 16-column chunk
-  static constexpr int kMeta = NC * 4 + (kMaxLabel + 2) * (NC / 16) * 2 + 64;
+  static constexpr int kMeta = NC * 4 + (kMaxLabel + 2) * (NC / 16) * 2 + (kMaxLabel + 2) * 4 + 64;   // + column-group starts
   static constexpr int kBytes = kFwdStages * kStage + 1024 /*align*/ + 256 /*barriers*/ + kMeta;
 };
 
@@ -319,6 +319,7 @@ tc_fwd_kernel(const __grid_constant__ CUtensorMap mapX, const __grid_constant__ 
   // heldTab[v][ci] bit j: column ci*16+j holds out the rows whose label equals v (v < kMaxLabel: fold
   // id; v = kMaxLabel + h: hold flag h), or does not exist.  A row's held columns = OR of two entries.
   uint16_t* heldTab = reinterpret_cast<uint16_t*>(colBias + NC);                     // [kMaxLabel + 2][NC / 16]
+  int* gsTab = reinterpret_cast<int*>(heldTab + (kMaxLabel + 2) * (NC / 16));        // [n_groups + 1] copy of p.gstart
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   // tensor memory: two accumulators of NC columns, then per stage 32 columns of X_hi and 32 of X_lo
@@ -333,6 +334,8 @@ tc_fwd_kernel(const __grid_constant__ CUtensorMap mapX, const __grid_constant__ 
     fence_barrier_init();
   }
   if (warp == kFwdMmaWarp) tmem_alloc(tmem_slot, kTmemCols);
+  const bool holes = MODE == FWD_LOGREG && p.gstart != nullptr;
+  if (holes) for (int i = threadIdx.x; i <= p.n_groups; i += blockDim.x) gsTab[i] = p.gstart[i];
   tc_fence_before();
   __syncthreads();
   if (CL > 1) cluster_sync_all();           // peer barriers are initialised before anyone signals them
@@ -347,13 +350,13 @@ tc_fwd_kernel(const __grid_constant__ CUtensorMap mapX, const __grid_constant__ 
   const int64_t job0 = blockIdx.x / CL, job_step = gridDim.x / CL;
   auto job_cb = [&](int64_t job) { return (int)(job / n_row_tiles) * CL + crank; };  // may be >= n_col_blocks (no columns)
   auto job_rt = [&](int64_t job) { return job % n_row_tiles; };
-  // block-local column range [sa, sb) that the rows of this tile do not train (empty: sa == sb == 0)
-  auto hole_of = [&](int cb, int64_t rt, int& sa, int& sb) {
+  // block-local column range [sa, sb) that a tile whose rows all sit in fold k does not train
+  // (empty: sa == sb == 0); k = 255: the tile mixes folds
+  auto tile_k = [&](int64_t rt) -> int { return holes ? (int)p.tile_fold[p.row0 / 128 + rt] : 255; };
+  auto hole_of = [&](int cb, int k, int& sa, int& sb) {
     sa = 0; sb = 0;
-    if (MODE != FWD_LOGREG || p.gstart == nullptr) return;
-    const int k = p.tile_fold[p.row0 / 128 + rt];
-    if (k >= p.n_groups) return;
-    const int lo = max(p.gstart[k], cb * NC) - cb * NC, hi = min(p.gstart[k + 1], cb * NC + NC) - cb * NC;
+    if (!holes || k >= p.n_groups) return;
+    const int lo = max(gsTab[k], cb * NC) - cb * NC, hi = min(gsTab[k + 1], cb * NC + NC) - cb * NC;
     if (hi > lo) { sa = lo; sb = hi; }
   };
 
@@ -386,10 +389,12 @@ tc_fwd_kernel(const __grid_constant__ CUtensorMap mapX, const __grid_constant__ 
   } else if (warp == kFwdMmaWarp) {
     // ===== MMA issuer =====
     uint32_t it = 0, tile = 0;
+    int k_next = job0 < n_jobs ? tile_k(job_rt(job0)) : 255;
     for (int64_t job = job0; job < n_jobs; job += job_step, ++tile) {
       const int acc = tile & 1; const uint32_t aph = (tile >> 1) & 1;
       int sa, sb;
-      hole_of(job_cb(job), job_rt(job), sa, sb);
+      hole_of(job_cb(job), k_next, sa, sb);
+      if (job + job_step < n_jobs) k_next = tile_k(job_rt(job + job_step));   // in flight while this tile's MMAs are issued
       // column ranges [0, sa) and [sb, NC); without a hole the first one is empty
       const uint32_t idesc_a = instr_desc_tf32(128, sa, 0, 0), idesc_b = instr_desc_tf32(128, NC - sb, 0, 0);
       mbar_wait(tempty + acc, aph ^ 1);
@@ -572,7 +577,7 @@ tc_fwd_kernel(const __grid_constant__ CUtensorMap mapX, const __grid_constant__ 
                 const int col = slot0 + c0 + c;
                 if (c < T && col < p.ldr) {
                   const int64_t o = (int64_t)(col >> 5) * p.r_chunk_stride + lrow * 32 + (col & 31);
-                  const float h = tf32_hi(rs[c]); p.Rhi[o] = h; p.Rlo[o] = rs[c] - h;
+                  p.R[o] = rs[c];
                 }
               }
             }
@@ -644,6 +649,7 @@ tc_fwd_kernel(const __grid_constant__ CUtensorMap mapX, const __grid_constant__ 
       const int64_t grow = p.row0 + rt * 128 + qrow;       // global row
       const bool valid = rt < n_row_tiles && grow < p.row0 + p.rows && grow < p.n_rows_total;
       int yv = 0, fold_v = 0, hold_v = 0; float yf = 0.f;
+      const int kf = tile_k(rt);                           // independent of the row loads below: one latency
       if (valid) {
         if (p.ycls) yv = p.ycls[grow];
         if (p.yreg) yf = p.yreg[grow];
@@ -653,8 +659,13 @@ tc_fwd_kernel(const __grid_constant__ CUtensorMap mapX, const __grid_constant__ 
       const float yy = (float)yv;
       const uint32_t held_f = held_s + fold_v * NCH * 2, held_h = held_s + (kMaxLabel + hold_v) * NCH * 2;
       const int acc = tile & 1; const uint32_t aph = (tile >> 1) & 1;
-      int sa, sb;
-      hole_of(cb, rt, sa, sb);
+      uint32_t hole_mask = 0;                  // bit ci: no row of this tile trains the columns of chunk ci
+      {
+        int sa, sb;
+        hole_of(cb, kf, sa, sb);
+#pragma unroll
+        for (int ci = 0; ci < NCH; ++ci) if (ci * 16 >= sa && ci * 16 + 16 <= sb) hole_mask |= 1u << ci;
+      }
       mbar_wait(tfull + acc, aph);
       tc_fence_after();
       const uint32_t tacc = tmem_base + acc * NC + ((uint32_t)(q * 32) << 16);
@@ -664,8 +675,8 @@ tc_fwd_kernel(const __grid_constant__ CUtensorMap mapX, const __grid_constant__ 
         const int ci = G * i + grp;
         if (ci >= NCH) break;
         const int c0 = ci * 16;
-        const bool in_hole = MODE == FWD_LOGREG && c0 >= sa && c0 + 16 <= sb;   // no row of this tile trains these columns
-        uint32_t v[16];
+        const bool in_hole = MODE == FWD_LOGREG && ((hole_mask >> ci) & 1u);   // residuals are zero there; the MMAs
+        uint32_t v[16];                                                         // never wrote these TMEM columns
         if (!in_hole) {
           tmem_ld16(tacc + c0, v);
           tmem_ld_wait();
@@ -675,40 +686,29 @@ tc_fwd_kernel(const __grid_constant__ CUtensorMap mapX, const __grid_constant__ 
           __syncwarp();
           if (lane == 0) mbar_arrive(tempty + acc);
         }
-        if (in_hole) {                       // residuals are zero there; the MMAs never wrote these TMEM columns
-          const int tq = lane & 3;
-          const int64_t lrow4 = rt * 128 + q * 32 + (lane & ~3);
-          const int col = slot0 + c0 + 4 * tq;
-          if (rt < n_row_tiles && col < p.ldr) {
-#pragma unroll
-            for (int j = 0; j < 4; ++j) {
-              const int64_t o = (int64_t)(col >> 5) * p.r_chunk_stride + (lrow4 + j) * 32 + (col & 31);
-              *reinterpret_cast<float4*>(p.Rhi + o) = make_float4(0.f, 0.f, 0.f, 0.f);
-              *reinterpret_cast<float4*>(p.Rlo + o) = make_float4(0.f, 0.f, 0.f, 0.f);
-            }
-          }
-          continue;
-        }
         // bit j set: column c0 + j does not train on (LOGREG) / is scored on (SCORE) this row
         const uint32_t heldbits = valid ? (lds16u(held_f + ci * 2) | lds16u(held_h + ci * 2)) : 0xffffu;
         if (MODE == FWD_LOGREG) {
-          float ls[16], rs[16], rl[16];
+          float ls[16], rs[16];
+          if (in_hole) {
 #pragma unroll
-          for (int j = 0; j < 16; ++j) {
-            const bool train = !((heldbits >> j) & 1u);
-            const float z = __uint_as_float(v[j]) + lds32f(bias_s + (c0 + j) * 4);
-            const float e = __expf(-fabsf(z));
-            const float inv = __fdividef(1.f, 1.f + e);
-            const float pr = z >= 0.f ? inv : e * inv;
-            rs[j] = train ? pr - yy : 0.f;
-            ls[j] = train ? (fmaxf(z, 0.f) - yy * z) + (__logf(1.f + e) - p.loss_shift) : 0.f;
-          }
-          accA[i] += (double)bfly16(ls, lane);
-          accB[i] += (double)bfly16(rs, lane);
-          // 4x4 transpose of float4 inside each group of 4 lanes (rows 4g..4g+3): afterwards lane t
-          // holds float4 #t of rows 4g..4g+3, so the 4 lanes of a group store 64 contiguous bytes
-          // of one row per instruction instead of 16 bytes of four different rows.
-          {
+            for (int j = 0; j < 16; ++j) rs[j] = 0.f;
+          } else {
+#pragma unroll
+            for (int j = 0; j < 16; ++j) {
+              const bool train = !((heldbits >> j) & 1u);
+              const float z = __uint_as_float(v[j]) + lds32f(bias_s + (c0 + j) * 4);
+              const float e = __expf(-fabsf(z));
+              const float inv = __fdividef(1.f, 1.f + e);
+              const float pr = z >= 0.f ? inv : e * inv;
+              rs[j] = train ? pr - yy : 0.f;
+              ls[j] = train ? (fmaxf(z, 0.f) - yy * z) + (__logf(1.f + e) - p.loss_shift) : 0.f;
+            }
+            accA[i] += (double)bfly16(ls, lane);
+            accB[i] += (double)bfly16(rs, lane);
+            // 4x4 transpose of float4 inside each group of 4 lanes (rows 4g..4g+3): afterwards lane t
+            // holds float4 #t of rows 4g..4g+3, so the 4 lanes of a group store 64 contiguous bytes
+            // of one row per instruction instead of 16 bytes of four different rows.
             const bool o1 = lane & 1, o2 = lane & 2;
 #pragma unroll
             for (int c1 = 0; c1 < 2; ++c1)
@@ -727,8 +727,6 @@ tc_fwd_kernel(const __grid_constant__ CUtensorMap mapX, const __grid_constant__ 
                 if (o2) rs[4 * cc + e] = rcv; else rs[4 * cc + 8 + e] = rcv;
               }
           }
-#pragma unroll
-          for (int j = 0; j < 16; ++j) { const float h = tf32_hi(rs[j]); rl[j] = rs[j] - h; rs[j] = h; }
           const int tq = lane & 3;                                // which float4 of the 16-column chunk
           const int64_t lrow4 = rt * 128 + q * 32 + (lane & ~3);   // first row of this lane group
           if (rt < n_row_tiles && slot0 + c0 + 4 * tq < p.ldr) {
@@ -736,8 +734,7 @@ tc_fwd_kernel(const __grid_constant__ CUtensorMap mapX, const __grid_constant__ 
             for (int j = 0; j < 4; ++j) {                         // j = row inside the group
               const int col = slot0 + c0 + 4 * tq;
               const int64_t o = (int64_t)(col >> 5) * p.r_chunk_stride + (lrow4 + j) * 32 + (col & 31);
-              *reinterpret_cast<float4*>(p.Rhi + o) = make_float4(rs[4 * j], rs[4 * j + 1], rs[4 * j + 2], rs[4 * j + 3]);
-              *reinterpret_cast<float4*>(p.Rlo + o) = make_float4(rl[4 * j], rl[4 * j + 1], rl[4 * j + 2], rl[4 * j + 3]);
+              *reinterpret_cast<float4*>(p.R + o) = make_float4(rs[4 * j], rs[4 * j + 1], rs[4 * j + 2], rs[4 * j + 3]);
             }
           }
         } else if (MODE == FWD_SCORE_CLS) {
@@ -771,17 +768,14 @@ tc_fwd_kernel(const __grid_constant__ CUtensorMap mapX, const __grid_constant__ 
 }
 
 // ---------------------------------------------------------------- gradient kernel
-// G[j][slot] = sum over the split's rows of X[row][j] * R[row][slot]
-//   A = X^T : MN-major, per stage 4 TMA boxes [32 rows x 32 features]  (split in kernel)
-//   B = R   : MN-major, per stage NC/32 boxes [32 rows x 32 columns], hi and lo from global
-// Two-level accumulation: the tensor core adds into a TMEM accumulator for at most kChain
-// stages (128 rows, 48 MMAs) -- its fp32 adder truncates, and the bias grows linearly with the
-// chain (measured 1.3e-5 relative after 2048 rows) -- then the drain warps add the TMEM tile
-// into fp32 registers with round-to-nearest while the MMAs fill the other TMEM accumulator.
-constexpr int kGradStages = 3;
+// G[j][slot] = sum over the split's rows of X[row][j] * R[row][slot]: A = X^T (features = TMEM lanes,
+// gathered column-wise from the TMA tile and written to tensor memory as hi / lo), B = R (MN-major,
+// UMMA layout SWIZZLE_128B_BASE32B + TMA SWIZZLE_128B_ATOM_32B, the only layout tf32 accepts
+// transposed).  Two-level accumulation: the tensor core's fp32 accumulator truncates, so chains stay
+// short (kChain stages = 128 rows, measured 1.3e-5 relative after 2048 rows in one chain) and the drain
+// warps add each finished TMEM tile into fp32 registers with round-to-nearest while the MMAs fill the
+// other accumulator.
 constexpr int kChain = 4;           // stages per TMEM accumulation chain
-constexpr int kGradThreads = 320;   // warps 0-3 operand staging, 4-7 drain, 8 TMA producer, 9 MMA issuer (highest id = highest priority)
-
 struct TcGradParams {
   int64_t row0_x;            // first row of the chunk inside X
   int64_t rows;              // rows in the chunk (R is chunk-local)
@@ -791,158 +785,6 @@ struct TcGradParams {
   int mask_hi;
   int prefetch_stages;       // L2 prefetch distance of the operand boxes, in 32-row stages (0 = off)
 };
-
-template <int NC>
-struct GradSmem {
-  static constexpr int kA = 4 * 32 * 128;       // 4 boxes of 32 rows x 128 B (TMA landing zone; A goes to TMEM)
-  static constexpr int kB = (NC / 32) * 32 * 128;
-  static constexpr int kStage = kA + 2 * kB;
-  static constexpr int kBytes = kGradStages * kStage + 1024 + 256;
-};
-
-template <int NC>
-__global__ void __launch_bounds__(kGradThreads, 1)
-tc_grad_kernel(const __grid_constant__ CUtensorMap mapX, const __grid_constant__ CUtensorMap mapRhi,
-               const __grid_constant__ CUtensorMap mapRlo, const TcGradParams p) {
-  extern __shared__ uint8_t smem_raw[];
-  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
-  using L = GradSmem<NC>;
-  static_assert(NC % 32 == 0 && NC <= 256, "NC");
-  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + kGradStages * L::kStage);
-  uint64_t* full = bars; uint64_t* split = bars + kGradStages; uint64_t* empty = bars + 2 * kGradStages;
-  uint64_t* tfull = bars + 3 * kGradStages;   // [2]
-  uint64_t* tempty = tfull + 2;               // [2]
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tempty + 2);
-  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  // tensor memory: two accumulators of NC columns, then per stage 32 columns of X^T_hi and 32 of X^T_lo
-  constexpr uint32_t kTmemUse = 2 * NC + kGradStages * 64;
-  constexpr uint32_t kTmemCols = kTmemUse <= 256 ? 256 : 512;
-  constexpr uint32_t kTmemA = 2 * NC;
-  static_assert(kTmemUse <= 512, "NC");
-
-  if (warp == 8 && lane == 0) {
-    for (int s = 0; s < kGradStages; ++s) { mbar_init(full + s, 1); mbar_init(split + s, 4); mbar_init(empty + s, 1); }
-    for (int a = 0; a < 2; ++a) { mbar_init(tfull + a, 1); mbar_init(tempty + a, 4); }
-    fence_barrier_init();
-  }
-  if (warp == 9) tmem_alloc(tmem_slot, kTmemCols);
-  tc_fence_before();
-  __syncthreads();
-  tc_fence_after();
-  const uint32_t tmem_base = *tmem_slot;
-
-  const int jb = blockIdx.x, cb = blockIdx.y, sp = blockIdx.z;
-  const int64_t kb = (int64_t)sp * p.rows_per_split;
-  const int64_t ke = min(p.rows, kb + p.rows_per_split);
-  const int n_stages = (int)((ke - kb + 31) / 32);
-  const int n_groups = (n_stages + kChain - 1) / kChain;
-
-  if (warp == 8) {
-    if (lane == 0) {
-      for (int it = 0; it < n_stages; ++it) {
-        const int s = it % kGradStages; const uint32_t ph = (it / kGradStages) & 1;
-        mbar_wait(empty + s, ph ^ 1);
-        uint8_t* st = smem + s * L::kStage;
-        mbar_expect_tx(full + s, L::kA + 2 * L::kB);
-        const int lr = (int)(kb + (int64_t)it * 32);          // row inside the chunk (R)
-        const int xr = (int)(p.row0_x + lr);                   // row inside X
-        // X: four boxes of 32 rows x 32 features (a 2-D map clips at d); R: 3-D view (32 columns, row,
-        // 32-column chunk), one instruction lands [chunk][32 rows][128 B]
-#pragma unroll
-        for (int b = 0; b < 4; ++b) tma_load_2d(&mapX, full + s, st + b * 4096, jb * 128 + b * 32, xr);
-        tma_load_3d(&mapRhi, full + s, st + L::kA, 0, lr, cb * (NC / 32));
-        tma_load_3d(&mapRlo, full + s, st + L::kA + L::kB, 0, lr, cb * (NC / 32));
-      }
-    }
-  } else if (warp == 9) {
-    constexpr uint32_t idesc = instr_desc_tf32(128, NC, 0, 1);   // A from TMEM (lanes = features), B = R MN-major
-    for (int g = 0, it = 0; g < n_groups; ++g) {
-      const int acc = g & 1; const uint32_t aph = (g >> 1) & 1;
-      mbar_wait(tempty + acc, aph ^ 1);
-      tc_fence_after();
-      const uint32_t tacc = tmem_base + acc * NC;
-      const int g_end = min(n_stages, (g + 1) * kChain);
-      for (int first = 1; it < g_end; ++it) {
-        const int s = it % kGradStages; const uint32_t ph = (it / kGradStages) & 1;
-        mbar_wait(full + s, ph);
-        mbar_wait(split + s, ph);
-        tc_fence_after();
-        if (elect_one()) {
-          const uint32_t b_hi = smem_u32(smem + s * L::kStage) + L::kA, b_lo = b_hi + L::kB;
-          const uint32_t ta_hi = tmem_base + kTmemA + s * 64, ta_lo = ta_hi + 32;
-#pragma unroll
-          for (int k = 0; k < 4; ++k) {   // 8 rows (two 4-row swizzle atoms along K) per MMA
-            const uint64_t dbh = smem_desc(b_hi + k * 1024, 4096, 512, kLayoutSw128Base32);
-            const uint64_t dbl = smem_desc(b_lo + k * 1024, 4096, 512, kLayoutSw128Base32);
-            umma_tf32_ts(tacc, ta_lo + k * 8, dbh, idesc, (first && k == 0) ? 0u : 1u);
-            umma_tf32_ts(tacc, ta_hi + k * 8, dbl, idesc, 1);
-            umma_tf32_ts(tacc, ta_hi + k * 8, dbh, idesc, 1);
-          }
-          umma_commit(empty + s);
-          if (it == g_end - 1) umma_commit(tfull + acc);
-        }
-        __syncwarp();
-        first = 0;
-      }
-    }
-  } else if (warp < 4) {
-    // operand staging: thread = feature of the 128-block = TMEM lane; it gathers its feature over the
-    // 32 rows of the stage (a column of the TMA tile; 32-byte-atom swizzle: chunk (lane>>3) ^ (row&3))
-    // and writes X^T_hi (raw words) and X^T_lo into tensor memory, where the MMAs read A from.
-    const int qd = warp & 3;
-    for (int it = 0; it < n_stages; ++it) {
-      const int s = it % kGradStages; const uint32_t ph = (it / kGradStages) & 1;
-      mbar_wait(full + s, ph);
-      const uint32_t box = smem_u32(smem + s * L::kStage) + qd * 4096;
-      uint32_t hi[32], lo[32];
-#pragma unroll
-      for (int k = 0; k < 32; ++k)
-        hi[k] = lds32u(box + k * 128 + ((((lane >> 3) ^ (k & 3)) << 5) | ((lane & 7) << 2)));
-#pragma unroll
-      for (int e = 0; e < 32; ++e) { const float x = __uint_as_float(hi[e]); lo[e] = __float_as_uint(x - tf32_hi(x)); }
-      const uint32_t ta = tmem_base + kTmemA + s * 64 + ((uint32_t)(qd * 32) << 16);
-      tmem_st32(ta, hi);
-      tmem_st32(ta + 32, lo);
-      tmem_st_wait();
-      tc_fence_before();
-      __syncwarp();
-      if (lane == 0) mbar_arrive(split + s);
-    }
-  } else {
-    // drain: lane = feature index inside the 128-block; fp32 round-to-nearest running sums
-    const int q = warp & 3;
-    const int j = jb * 128 + q * 32 + lane;
-    float sum[NC];
-#pragma unroll
-    for (int c = 0; c < NC; ++c) sum[c] = 0.f;
-    for (int g = 0; g < n_groups; ++g) {
-      const int acc = g & 1; const uint32_t aph = (g >> 1) & 1;
-      mbar_wait(tfull + acc, aph);
-      tc_fence_after();
-      const uint32_t tacc = tmem_base + acc * NC + ((uint32_t)(q * 32) << 16);
-#pragma unroll
-      for (int c0 = 0; c0 < NC; c0 += 16) {
-        uint32_t v[16];
-        tmem_ld16(tacc + c0, v);
-        tmem_ld_wait();
-#pragma unroll
-        for (int c = 0; c < 16; ++c) sum[c0 + c] += __uint_as_float(v[c]);
-      }
-      tc_fence_before();
-      __syncwarp();
-      if (lane == 0) mbar_arrive(tempty + acc);
-    }
-    float* out = p.Gpart + (int64_t)sp * p.n_slots * p.ldg;
-#pragma unroll
-    for (int c = 0; c < NC; ++c) {
-      const int slot = cb * NC + c;
-      if (slot < p.n_slots && j < p.d) out[(int64_t)slot * p.ldg + j] = sum[c];
-    }
-  }
-  tc_fence_before();
-  __syncthreads();
-  if (warp == 9) tmem_dealloc(tmem_base, kTmemCols);
-}
 
 // ---------------------------------------------------------------- gradient kernel, CTA pair
 // Same contraction with cta_group::2 MMAs (M = 256): the two CTAs of a cluster take feature blocks
@@ -961,16 +803,21 @@ tc_grad_kernel(const __grid_constant__ CUtensorMap mapX, const __grid_constant__
 // a third of the time (HBM latency under load exceeds 4 x 768 clocks).
 constexpr int kGrad2SX = 6, kGrad2SR = 6, kGrad2TA = 4;
 constexpr int kGrad2NC = 128;
+// warps 0-3 X staging, 4-7 drain, 8-9 R_lo split, 10 TMA producer, 11 MMA issuer
+constexpr int kGrad2Threads = 384, kGrad2SplitWarp = 8, kGrad2TmaWarp = 10, kGrad2MmaWarp = 11;
 struct Grad2Smem {
   static constexpr int kA = 4 * 32 * 128;                    // own X boxes of one stage
-  static constexpr int kBh = (kGrad2NC / 2 / 32) * 32 * 128; // own half of R_hi (and of R_lo) of one stage
+  static constexpr int kBh = (kGrad2NC / 2 / 32) * 32 * 128; // own half of R (fp32; read as R_hi) and of R_lo
   static constexpr int kB = 2 * kBh;
   static constexpr int kBytes = kGrad2SX * kA + kGrad2SR * kB + 1024 + 512;
 };
 
-__global__ void __launch_bounds__(kGradThreads, 1)
-tc_grad2_kernel(const __grid_constant__ CUtensorMap mapX, const __grid_constant__ CUtensorMap mapRhi,
-                const __grid_constant__ CUtensorMap mapRlo, const TcGradParams p) {
+// R is the fp32 residual as the forward kernel left it: the MMAs read it as R_hi (kind::tf32 ignores the
+// 13 low mantissa bits) and two warps per CTA write R_lo = R - tf32(R) next to it in shared memory, so
+// the residual crosses HBM once in each direction instead of twice.
+__global__ void __launch_bounds__(kGrad2Threads, 1)
+tc_grad2_kernel(const __grid_constant__ CUtensorMap mapX, const __grid_constant__ CUtensorMap mapR,
+                const TcGradParams p) {
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
   using L = Grad2Smem;
@@ -979,7 +826,9 @@ tc_grad2_kernel(const __grid_constant__ CUtensorMap mapX, const __grid_constant_
   uint8_t* smR = smem + SX * L::kA;
   uint64_t* bars = reinterpret_cast<uint64_t*>(smR + SR * L::kB);
   uint64_t* fullA = bars; uint64_t* emptyA = fullA + SX;
-  uint64_t* fullB = emptyA + SX; uint64_t* emptyB = fullB + SR;
+  uint64_t* fullR = emptyA + SX;      // own R half landed (local)
+  uint64_t* bsplit = fullR + SR;      // leader: R_lo of both CTAs written (4 remote/local arrives)
+  uint64_t* emptyB = bsplit + SR;
   uint64_t* split = emptyB + SR; uint64_t* aempty = split + TA;
   uint64_t* tfull = aempty + TA;      // [2]
   uint64_t* tempty = tfull + 2;       // [2]
@@ -990,14 +839,14 @@ tc_grad2_kernel(const __grid_constant__ CUtensorMap mapX, const __grid_constant_
   constexpr uint32_t kTmemCols = 512, kTmemA = 2 * kGrad2NC;   // two accumulators, then 64 columns of A per slot
   static_assert(2 * kGrad2NC + TA * 64 <= 512, "tensor memory");
 
-  if (warp == 8 && lane == 0) {
+  if (warp == kGrad2TmaWarp && lane == 0) {
     for (int s = 0; s < SX; ++s) { mbar_init(fullA + s, 1); mbar_init(emptyA + s, 4); }
-    for (int s = 0; s < SR; ++s) { mbar_init(fullB + s, 1); mbar_init(emptyB + s, 1); }
+    for (int s = 0; s < SR; ++s) { mbar_init(fullR + s, 1); mbar_init(bsplit + s, 4); mbar_init(emptyB + s, 1); }
     for (int s = 0; s < TA; ++s) { mbar_init(split + s, 8); mbar_init(aempty + s, 1); }
     for (int a = 0; a < 2; ++a) { mbar_init(tfull + a, 1); mbar_init(tempty + a, 8); }
     fence_barrier_init();
   }
-  if (warp == 9) tmem_alloc_pair(tmem_slot, kTmemCols);
+  if (warp == kGrad2MmaWarp) tmem_alloc_pair(tmem_slot, kTmemCols);
   tc_fence_before();
   cluster_sync_all();       // barriers of both CTAs initialised before any remote arrive or multicast
   tc_fence_after();
@@ -1012,7 +861,7 @@ tc_grad2_kernel(const __grid_constant__ CUtensorMap mapX, const __grid_constant_
   const int n_stages = (int)((ke - kb + 31) / 32);
   const int n_groups = (n_stages + kChain - 1) / kChain;
 
-  if (warp == 8) {
+  if (warp == kGrad2TmaWarp) {
     if (lane == 0) {
       const int chunk0 = col0 / 32 + (int)rank * nch;
       for (int it = 0; it < n_stages; ++it) {
@@ -1026,15 +875,11 @@ tc_grad2_kernel(const __grid_constant__ CUtensorMap mapX, const __grid_constant_
         for (int b = 0; b < 4; ++b) tma_load_2d(&mapX, fullA + sx, ax + b * 4096, jb * 128 + b * 32, xr);
         mbar_wait(emptyB + sr, ((it / SR) & 1) ^ 1);
         uint8_t* br = smR + sr * L::kB;
-        if (leader) mbar_expect_tx(fullB + sr, (uint32_t)(4 * nch * 4096));   // hi + lo halves of both CTAs
-        const uint32_t fb = mapa_rank(smem_u32(fullB + sr), 0);
-        for (int c = 0; c < nch; ++c) {
-          tma_load_3d_pair(&mapRhi, fb, br + c * 4096, 0, lr, chunk0 + c);
-          tma_load_3d_pair(&mapRlo, fb, br + L::kBh + c * 4096, 0, lr, chunk0 + c);
-        }
+        mbar_expect_tx(fullR + sr, (uint32_t)(nch * 4096));
+        for (int c = 0; c < nch; ++c) tma_load_3d(&mapR, fullR + sr, br + c * 4096, 0, lr, chunk0 + c);
       }
     }
-  } else if (warp == 9) {
+  } else if (warp == kGrad2MmaWarp) {
     if (leader) {
       const uint32_t idesc = instr_desc_tf32(256, ncols, 0, 1);
       for (int g = 0, it = 0; g < n_groups; ++g) {
@@ -1045,7 +890,7 @@ tc_grad2_kernel(const __grid_constant__ CUtensorMap mapX, const __grid_constant_
         const int g_end = min(n_stages, (g + 1) * kChain);
         for (int first = 1; it < g_end; ++it) {
           const int sr = it % SR, ta = it % TA;
-          mbar_wait_cluster(fullB + sr, (it / SR) & 1);
+          mbar_wait_cluster(bsplit + sr, (it / SR) & 1);
           mbar_wait_cluster(split + ta, (it / TA) & 1);
           tc_fence_after();
           if (elect_one()) {
@@ -1067,6 +912,23 @@ tc_grad2_kernel(const __grid_constant__ CUtensorMap mapX, const __grid_constant_
           first = 0;
         }
       }
+    }
+  } else if (warp >= kGrad2SplitWarp && warp < kGrad2TmaWarp) {
+    // R_lo = R - tf32(R), elementwise on the swizzled tile (position-preserving): each of the two warps
+    // takes half of the CTA's nch * 4 KB; then the buffer is handed to the async proxy (the MMAs)
+    const int half = warp - kGrad2SplitWarp;
+    for (int it = 0; it < n_stages; ++it) {
+      const int sr = it % SR;
+      mbar_wait(fullR + sr, (it / SR) & 1);
+      const uint32_t hi_s = smem_u32(smR + sr * L::kB), lo_s = hi_s + L::kBh;
+      const int n16 = nch * 256;                       // 16-byte pieces in the CTA's half
+      for (int i = half * 32 + lane; i < n16; i += 64) {
+        const float4 v = lds128(hi_s + i * 16);
+        sts128(lo_s + i * 16, make_float4(v.x - tf32_hi(v.x), v.y - tf32_hi(v.y), v.z - tf32_hi(v.z), v.w - tf32_hi(v.w)));
+      }
+      fence_proxy_async();
+      __syncwarp();
+      if (lane == 0) mbar_arrive_cluster(mapa_rank(smem_u32(bsplit + sr), 0));
     }
   } else if (warp < 4) {
     const int qd = warp & 3;
@@ -1126,7 +988,7 @@ tc_grad2_kernel(const __grid_constant__ CUtensorMap mapX, const __grid_constant_
   }
   tc_fence_before();
   cluster_sync_all();       // the peer's shared and tensor memory stay alive until the leader's MMAs are done
-  if (warp == 9) tmem_dealloc_pair(tmem_base, kTmemCols);
+  if (warp == kGrad2MmaWarp) tmem_dealloc_pair(tmem_base, kTmemCols);
 }
 
 // ---------------------------------------------------------------- Gram kernel (Ridge)
