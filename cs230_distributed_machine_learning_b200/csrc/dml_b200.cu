@@ -57,6 +57,10 @@ struct dml_ctx {
   float total_ms = 0.f, contraction_ms = 0.f; int contraction_launches = 0, total_launches = 0;
   size_t r_budget = (size_t)4 << 30;  // bytes of residual scratch per row chunk
   size_t first_pairs = 0; float first_ms = 0.f; int64_t first_cols = 0;   // round 0 when it ran once per row mask
+  // the gradient kernel can skip 64-column segments too (DML_GRAD_SKIP=1).  Measured on config 2: per launch
+  // 0.85 ms against 0.76 ms (N = 64 MMAs cost more than half an N = 128 one) but a third less HBM traffic and
+  // tensor work, and the same sustained sweep time at the power cap -- so it is off by default.
+  int grad_skip = 0;
   int fold_skip = 1;          // fold-major column groups, so that row tiles of one fold can skip that fold's columns
   int first_round_once = 1;   // evaluate round 0 once per row mask instead of once per candidate
   int tc_prefetch = 0, tc_prefetch_grad = 0;  // L2 prefetch distance of the forward X tiles in jobs (0 = off; measured: no gain, the ring is not latency-bound)
@@ -164,6 +168,7 @@ extern "C" int dml_ctx_create(int device, void* stream, dml_ctx** out) {
   if (const char* e = getenv("DML_TC_PREFETCH_GRAD")) ctx->tc_prefetch_grad = atoi(e);
   if (const char* e = getenv("DML_FIRST_ROUND_ONCE")) ctx->first_round_once = atoi(e);
   if (const char* e = getenv("DML_FOLD_SKIP")) ctx->fold_skip = atoi(e);
+  if (const char* e = getenv("DML_GRAD_SKIP")) ctx->grad_skip = atoi(e);
   if (const char* e = getenv("DML_TC_CLUSTER")) ctx->tc_cluster = atoi(e) == 1 ? 1 : 2;
   CU(cudaSetDevice(device));
   CU(cudaHostAlloc(&ctx->h_scalar, 64, cudaHostAllocDefault));
@@ -527,7 +532,7 @@ struct EvalCtx {
         fp.fold_id = fold_id; fp.hold_id = hold_id; fp.slot_sel = sel; fp.slot_val = val;
         fp.R = R; fp.ldr = (int)ldr_max; fp.r_chunk_stride = chunk_rows * 32; fp.lossPart = lossPart; fp.gbPart = gbPart;
         fp.mask_hi = ctx->tc_mask_hi; fp.prefetch_jobs = ctx->tc_prefetch; fp.T = T; fp.loss_shift = loss_shift();
-        fp.tile_fold = tile_fold; fp.gstart = gstart; fp.n_groups = n_groups;
+        fp.tile_fold = tile_fold; fp.gstart = gstart; fp.n_groups = n_groups; fp.grad_skips = ctx->grad_skip;
         // clusters of 2 share each X tile between two column blocks; with an odd number of blocks one
         // CTA of the last pair would run on empty columns, so small / odd cases run unclustered
         const int clr = (cl == 2 && ncb >= 2 && (ncb % 2 == 0 || ncb >= 5)) ? 2 : 1;
@@ -538,7 +543,8 @@ struct EvalCtx {
         int rc = T == 1 ? launch_tc_fwd<FWD_LOGREG>(ctx, NC, clr, grid, clr == 2 ? mXf2 : mXf, mWh, mWl, fp)
                         : launch_tc_fwd<tc::FWD_LOGREG_MULTI>(ctx, NC, clr, grid, clr == 2 ? mXf2 : mXf, mWh, mWl, fp);
         if (rc) return rc;
-        tc::TcGradParams gp{r0, rows, tc_rps, d, n_slots, Gpart, ldg, ctx->tc_mask_hi, ctx->tc_prefetch_grad};
+        tc::TcGradParams gp{r0, rows, tc_rps, d, n_slots, Gpart, ldg, ctx->tc_mask_hi, ctx->tc_prefetch_grad,
+                            tile_fold, ctx->grad_skip ? gstart : nullptr, n_groups};
         const int splits_here = (int)cdiv(rows, tc_rps);
         rc = launch_tc_grad2(ctx, dim3((unsigned)(2 * cdiv(cdiv(d, 128), 2)), (unsigned)cdiv(n_slots, tc::kGrad2NC), (unsigned)splits_here),
                              mXg, mR1, gp);

@@ -255,6 +255,7 @@ struct TcFwdParams {
   // tile t (255: mixed); gstart[k] .. gstart[k+1] = the columns of fold k's fits (multiples of 32).  A tile of
   // fold k trains none of them: no MMAs, no epilogue math for that column range.  gstart == nullptr: off.
   const uint8_t* tile_fold; const int* gstart; int n_groups;
+  int grad_skips;                        // the gradient kernel skips whole 64-column segments of a hole: nothing to store there
   float* R; int ldr;                     // fp32 residuals, [ldr / 32 column chunks][chunk rows][32]: a chunk's rows are contiguous,
   int64_t r_chunk_stride;                // so a gradient box (32 rows x 32 columns) is one 4 KB run; stride in floats
   double* lossPart; double* gbPart;      // [gridDim.x * 4][n_slots], zeroed by the caller
@@ -659,12 +660,18 @@ tc_fwd_kernel(const __grid_constant__ CUtensorMap mapX, const __grid_constant__ 
       const float yy = (float)yv;
       const uint32_t held_f = held_s + fold_v * NCH * 2, held_h = held_s + (kMaxLabel + hold_v) * NCH * 2;
       const int acc = tile & 1; const uint32_t aph = (tile >> 1) & 1;
-      uint32_t hole_mask = 0;                  // bit ci: no row of this tile trains the columns of chunk ci
+      // bit ci of hole_mask: no row of this tile trains the columns of chunk ci (no math, residual zero);
+      // bit ci + 16: the gradient kernel skips the chunk's 64-column segment as well, so nothing is stored
+      uint32_t hole_mask = 0;
       {
         int sa, sb;
         hole_of(cb, kf, sa, sb);
 #pragma unroll
-        for (int ci = 0; ci < NCH; ++ci) if (ci * 16 >= sa && ci * 16 + 16 <= sb) hole_mask |= 1u << ci;
+        for (int ci = 0; ci < NCH; ++ci)
+          if (ci * 16 >= sa && ci * 16 + 16 <= sb) {
+            const int seg = ((slot0 + ci * 16) & ~63) - slot0;       // block-local start of the 64-column segment
+            hole_mask |= (p.grad_skips && seg >= sa && seg + 64 <= sb) ? (0x10001u << ci) : (1u << ci);
+          }
       }
       mbar_wait(tfull + acc, aph);
       tc_fence_after();
@@ -686,6 +693,7 @@ tc_fwd_kernel(const __grid_constant__ CUtensorMap mapX, const __grid_constant__ 
           __syncwarp();
           if (lane == 0) mbar_arrive(tempty + acc);
         }
+        if (MODE == FWD_LOGREG && ((hole_mask >> (ci + 16)) & 1u)) continue;
         // bit j set: column c0 + j does not train on (LOGREG) / is scored on (SCORE) this row
         const uint32_t heldbits = valid ? (lds16u(held_f + ci * 2) | lds16u(held_h + ci * 2)) : 0xffffu;
         if (MODE == FWD_LOGREG) {
@@ -784,6 +792,9 @@ struct TcGradParams {
   float* Gpart; int ldg;     // [splits][n_slots][ldg]
   int mask_hi;
   int prefetch_stages;       // L2 prefetch distance of the operand boxes, in 32-row stages (0 = off)
+  // fold-aware skipping (see TcFwdParams): a 128-row chain whose rows all sit in fold k contributes
+  // nothing to fold k's columns; 64-column segments inside that group are not loaded or multiplied
+  const uint8_t* tile_fold; const int* gstart; int n_groups;
 };
 
 // ---------------------------------------------------------------- gradient kernel, CTA pair
@@ -809,12 +820,18 @@ struct Grad2Smem {
   static constexpr int kA = 4 * 32 * 128;                    // own X boxes of one stage
   static constexpr int kBh = (kGrad2NC / 2 / 32) * 32 * 128; // own half of R (fp32; read as R_hi) and of R_lo
   static constexpr int kB = 2 * kBh;
-  static constexpr int kBytes = kGrad2SX * kA + kGrad2SR * kB + 1024 + 512;
+  static constexpr int kBytes = kGrad2SX * kA + kGrad2SR * kB + 1024 + 512 + (kMaxLabel + 2) * 4 + 64;   // + column-group starts, chain fold ids
 };
 
 // R is the fp32 residual as the forward kernel left it: the MMAs read it as R_hi (kind::tf32 ignores the
 // 13 low mantissa bits) and two warps per CTA write R_lo = R - tf32(R) next to it in shared memory, so
 // the residual crosses HBM once in each direction instead of twice.
+// A chain = 4 stages = one 128-row tile of X.  Normally the leader holds the first half of the block's
+// columns, the peer the second half, and one N = ncols MMA covers the block.  A column block is also two
+// 64-column segments: when all rows of the chain sit in fold k and a segment lies inside fold k's column
+// group, that segment is skipped for the chain by every role (no TMA, no split, no MMA, nothing added by
+// the drain warps); the other segment is then loaded interleaved (leader: its even 32-column chunk, peer:
+// the odd one) and multiplied by N = 64 MMAs, which keeps the accumulator columns in natural order.
 __global__ void __launch_bounds__(kGrad2Threads, 1)
 tc_grad2_kernel(const __grid_constant__ CUtensorMap mapX, const __grid_constant__ CUtensorMap mapR,
                 const TcGradParams p) {
@@ -833,6 +850,8 @@ tc_grad2_kernel(const __grid_constant__ CUtensorMap mapX, const __grid_constant_
   uint64_t* tfull = aempty + TA;      // [2]
   uint64_t* tempty = tfull + 2;       // [2]
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tempty + 2);
+  int* gsTab = reinterpret_cast<int*>(tmem_slot + 2);        // [n_groups + 1] copy of p.gstart
+  uint8_t* tfTab = reinterpret_cast<uint8_t*>(gsTab + kMaxLabel + 2);   // [<= 64] fold id of each chain's row tile
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const uint32_t rank = cluster_ctarank();
   const bool leader = rank == 0;
@@ -847,24 +866,42 @@ tc_grad2_kernel(const __grid_constant__ CUtensorMap mapX, const __grid_constant_
     fence_barrier_init();
   }
   if (warp == kGrad2MmaWarp) tmem_alloc_pair(tmem_slot, kTmemCols);
+  const int jb = blockIdx.x, cb = blockIdx.y, sp = blockIdx.z;
+  const int col0 = cb * kGrad2NC;
+  const int ncols = min(kGrad2NC, ((p.n_slots - col0 + 63) / 64) * 64);   // columns of this pair's block
+  const int nseg = ncols / 64;                                            // 64-column segments = chunks per CTA
+  const int64_t kb = (int64_t)sp * p.rows_per_split;
+  const int64_t ke = min(p.rows, kb + p.rows_per_split);
+  const int n_stages = (int)((ke - kb + 31) / 32);
+  const int n_groups = (n_stages + kChain - 1) / kChain;
+  const bool holes = p.gstart != nullptr && n_groups <= 64;
+  if (holes) {              // the tables every role consults once per chain live in shared memory
+    for (int i = threadIdx.x; i <= p.n_groups; i += blockDim.x) gsTab[i] = p.gstart[i];
+    for (int i = threadIdx.x; i < n_groups; i += blockDim.x) tfTab[i] = p.tile_fold[(p.row0_x + kb) / 128 + i];
+  }
   tc_fence_before();
   cluster_sync_all();       // barriers of both CTAs initialised before any remote arrive or multicast
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
 
-  const int jb = blockIdx.x, cb = blockIdx.y, sp = blockIdx.z;
-  const int col0 = cb * kGrad2NC;
-  const int ncols = min(kGrad2NC, ((p.n_slots - col0 + 63) / 64) * 64);   // columns of this pair's block
-  const int nch = ncols / 64;                                             // 32-column chunks per CTA
-  const int64_t kb = (int64_t)sp * p.rows_per_split;
-  const int64_t ke = min(p.rows, kb + p.rows_per_split);
-  const int n_stages = (int)((ke - kb + 31) / 32);
-  const int n_groups = (n_stages + kChain - 1) / kChain;
+  // bit s set: segment s is skipped for chain g (rows_per_split and row0_x are multiples of 128)
+  auto skip_of = [&](int g) -> uint32_t {
+    if (!holes) return 0u;
+    const int k = tfTab[g];
+    if (k >= p.n_groups) return 0u;
+    uint32_t m = 0;
+    for (int sg = 0; sg < nseg; ++sg) {
+      const int c = col0 + sg * 64;
+      if (c >= gsTab[k] && c + 64 <= gsTab[k + 1]) m |= 1u << sg;
+    }
+    return m;
+  };
 
   if (warp == kGrad2TmaWarp) {
     if (lane == 0) {
-      const int chunk0 = col0 / 32 + (int)rank * nch;
+      uint32_t skip = 0;
       for (int it = 0; it < n_stages; ++it) {
+        if (it % kChain == 0) skip = skip_of(it / kChain);
         const int sx = it % SX, sr = it % SR;
         const int lr = (int)(kb + (int64_t)it * 32);
         const int xr = (int)(p.row0_x + lr);
@@ -875,15 +912,28 @@ tc_grad2_kernel(const __grid_constant__ CUtensorMap mapX, const __grid_constant_
         for (int b = 0; b < 4; ++b) tma_load_2d(&mapX, fullA + sx, ax + b * 4096, jb * 128 + b * 32, xr);
         mbar_wait(emptyB + sr, ((it / SR) & 1) ^ 1);
         uint8_t* br = smR + sr * L::kB;
-        mbar_expect_tx(fullR + sr, (uint32_t)(nch * 4096));
-        for (int c = 0; c < nch; ++c) tma_load_3d(&mapR, fullR + sr, br + c * 4096, 0, lr, chunk0 + c);
+        if (skip == 0) {           // whole block: this CTA's half = nseg consecutive chunks
+          mbar_expect_tx(fullR + sr, (uint32_t)(nseg * 4096));
+          for (int c = 0; c < nseg; ++c) tma_load_3d(&mapR, fullR + sr, br + c * 4096, 0, lr, col0 / 32 + (int)rank * nseg + c);
+        } else {                   // segments: chunk (2 sg + rank) of the block, at position sg
+          int n_load = 0;
+          for (int sg = 0; sg < nseg; ++sg) if (!((skip >> sg) & 1u)) ++n_load;
+          if (n_load == 0) mbar_arrive(fullR + sr);
+          else {
+            mbar_expect_tx(fullR + sr, (uint32_t)(n_load * 4096));
+            for (int sg = 0; sg < nseg; ++sg)
+              if (!((skip >> sg) & 1u)) tma_load_3d(&mapR, fullR + sr, br + sg * 4096, 0, lr, col0 / 32 + 2 * sg + (int)rank);
+          }
+        }
       }
     }
   } else if (warp == kGrad2MmaWarp) {
     if (leader) {
-      const uint32_t idesc = instr_desc_tf32(256, ncols, 0, 1);
+      constexpr uint32_t idesc_seg = instr_desc_tf32(256, 64, 0, 1);
+      const uint32_t idesc_all = instr_desc_tf32(256, ncols, 0, 1);
       for (int g = 0, it = 0; g < n_groups; ++g) {
         const int acc = g & 1; const uint32_t aph = (g >> 1) & 1;
+        const uint32_t skip = skip_of(g);
         mbar_wait_cluster(tempty + acc, aph ^ 1);
         tc_fence_after();
         const uint32_t tacc = tmem_base + acc * kGrad2NC;
@@ -894,15 +944,30 @@ tc_grad2_kernel(const __grid_constant__ CUtensorMap mapX, const __grid_constant_
           mbar_wait_cluster(split + ta, (it / TA) & 1);
           tc_fence_after();
           if (elect_one()) {
-            const uint32_t b_hi = smem_u32(smR + sr * L::kB), b_lo = b_hi + L::kBh;
             const uint32_t ta_hi = tmem_base + kTmemA + ta * 64, ta_lo = ta_hi + 32;
+            const uint32_t b0 = smem_u32(smR + sr * L::kB);
+            if (skip == 0) {
 #pragma unroll
-            for (int k = 0; k < 4; ++k) {
-              const uint64_t dbh = smem_desc(b_hi + k * 1024, 4096, 512, kLayoutSw128Base32);
-              const uint64_t dbl = smem_desc(b_lo + k * 1024, 4096, 512, kLayoutSw128Base32);
-              umma_tf32_ts_pair(tacc, ta_lo + k * 8, dbh, idesc, (first && k == 0) ? 0u : 1u);
-              umma_tf32_ts_pair(tacc, ta_hi + k * 8, dbl, idesc, 1);
-              umma_tf32_ts_pair(tacc, ta_hi + k * 8, dbh, idesc, 1);
+              for (int k = 0; k < 4; ++k) {
+                const uint64_t dbh = smem_desc(b0 + k * 1024, 4096, 512, kLayoutSw128Base32);
+                const uint64_t dbl = smem_desc(b0 + L::kBh + k * 1024, 4096, 512, kLayoutSw128Base32);
+                umma_tf32_ts_pair(tacc, ta_lo + k * 8, dbh, idesc_all, (first && k == 0) ? 0u : 1u);
+                umma_tf32_ts_pair(tacc, ta_hi + k * 8, dbl, idesc_all, 1);
+                umma_tf32_ts_pair(tacc, ta_hi + k * 8, dbh, idesc_all, 1);
+              }
+            } else {
+              for (int sg = 0; sg < nseg; ++sg) {
+                if ((skip >> sg) & 1u) continue;
+                const uint32_t b_hi = b0 + sg * 4096, b_lo = b_hi + L::kBh;
+#pragma unroll
+                for (int k = 0; k < 4; ++k) {
+                  const uint64_t dbh = smem_desc(b_hi + k * 1024, 4096, 512, kLayoutSw128Base32);
+                  const uint64_t dbl = smem_desc(b_lo + k * 1024, 4096, 512, kLayoutSw128Base32);
+                  umma_tf32_ts_pair(tacc + sg * 64, ta_lo + k * 8, dbh, idesc_seg, (first && k == 0) ? 0u : 1u);
+                  umma_tf32_ts_pair(tacc + sg * 64, ta_hi + k * 8, dbl, idesc_seg, 1);
+                  umma_tf32_ts_pair(tacc + sg * 64, ta_hi + k * 8, dbh, idesc_seg, 1);
+                }
+              }
             }
             umma_commit_pair(emptyB + sr);
             umma_commit_pair(aempty + ta);
@@ -915,16 +980,22 @@ tc_grad2_kernel(const __grid_constant__ CUtensorMap mapX, const __grid_constant_
     }
   } else if (warp >= kGrad2SplitWarp && warp < kGrad2TmaWarp) {
     // R_lo = R - tf32(R), elementwise on the swizzled tile (position-preserving): each of the two warps
-    // takes half of the CTA's nch * 4 KB; then the buffer is handed to the async proxy (the MMAs)
+    // takes half of every loaded 4 KB chunk; then the buffer is handed to the async proxy (the MMAs)
     const int half = warp - kGrad2SplitWarp;
+    uint32_t skip = 0;
     for (int it = 0; it < n_stages; ++it) {
+      if (it % kChain == 0) skip = skip_of(it / kChain);
       const int sr = it % SR;
       mbar_wait(fullR + sr, (it / SR) & 1);
       const uint32_t hi_s = smem_u32(smR + sr * L::kB), lo_s = hi_s + L::kBh;
-      const int n16 = nch * 256;                       // 16-byte pieces in the CTA's half
-      for (int i = half * 32 + lane; i < n16; i += 64) {
-        const float4 v = lds128(hi_s + i * 16);
-        sts128(lo_s + i * 16, make_float4(v.x - tf32_hi(v.x), v.y - tf32_hi(v.y), v.z - tf32_hi(v.z), v.w - tf32_hi(v.w)));
+      for (int sg = 0; sg < nseg; ++sg) {
+        if ((skip >> sg) & 1u) continue;
+#pragma unroll
+        for (int u = 0; u < 4; ++u) {
+          const int i = sg * 256 + half * 128 + u * 32 + lane;       // 16-byte piece of the chunk
+          const float4 v = lds128(hi_s + i * 16);
+          sts128(lo_s + i * 16, make_float4(v.x - tf32_hi(v.x), v.y - tf32_hi(v.y), v.z - tf32_hi(v.z), v.w - tf32_hi(v.w)));
+        }
       }
       fence_proxy_async();
       __syncwarp();
@@ -962,12 +1033,13 @@ tc_grad2_kernel(const __grid_constant__ CUtensorMap mapX, const __grid_constant_
     for (int c = 0; c < kGrad2NC; ++c) sum[c] = 0.f;
     for (int g = 0; g < n_groups; ++g) {
       const int acc = g & 1; const uint32_t aph = (g >> 1) & 1;
+      const uint32_t skip = skip_of(g);
       mbar_wait(tfull + acc, aph);
       tc_fence_after();
       const uint32_t tacc = tmem_base + acc * kGrad2NC + ((uint32_t)(q * 32) << 16);
 #pragma unroll
       for (int c0 = 0; c0 < kGrad2NC; c0 += 16) {
-        if (c0 < ncols) {
+        if (c0 < ncols && !((skip >> (c0 / 64)) & 1u)) {
           uint32_t v[16];
           tmem_ld16(tacc + c0, v);
           tmem_ld_wait();
