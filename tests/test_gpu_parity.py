@@ -322,6 +322,30 @@ def test_queued_jobs_prefetch_their_dataset_and_match_blocking_runs():
         m.close()
 
 
+@pytest.mark.parametrize("env", [{"DML_FOLD_SKIP": "0"}, {"DML_GRAD_SKIP": "1"}, {"DML_FIRST_ROUND_ONCE": "0"}],
+                         ids=["no-fold-skip", "grad-skip", "full-round-0"])
+def test_skipping_knobs_do_not_change_results(solver, monkeypatch, env):
+    """Fold-aware column skipping and the round-0 shortcut only remove work whose result is zero or
+    known: every switch setting gives the same iterates (compared with the default context)."""
+    from cs230_distributed_machine_learning_b200.solver import SweepSolver
+    X, y = make_dataset("binary", 60_000, 256, seed=12)
+    fold = folds.stratified_labels(y, 5)
+    Cs = np.logspace(-5, 1, 70)           # 70 candidates: groups of 70 -> padded to 96, several column blocks
+    args = ([1e-4] * 70, [True] * 70, [100] * 70)
+    ds = solver.upload_dataset(X, y, classifier=True)
+    want = solver.logreg_sweep(ds, fold, 5, Cs, *args)
+    for k, v in env.items():
+        monkeypatch.setenv(k, v)
+    other = SweepSolver(0)
+    try:
+        ds2 = other.upload_dataset(X, y, classifier=True)
+        got = other.logreg_sweep(ds2, fold, 5, Cs, *args)
+    finally:
+        other.close()
+    assert (got["n_iter"] == want["n_iter"]).all() and (got["correct"] == want["correct"]).all()
+    np.testing.assert_allclose(got["coef"], want["coef"], rtol=1e-6, atol=1e-9)
+
+
 def test_medium_size_properties(solver):
     """Size-independent properties at a size the oracle cannot sweep in seconds (200k x 256, 16 C x 5 folds)."""
     X, y = make_dataset("binary", 200_000, 256, seed=2)
