@@ -702,15 +702,28 @@ tc_fwd_kernel(const __grid_constant__ CUtensorMap mapX, const __grid_constant__ 
 #pragma unroll
             for (int j = 0; j < 16; ++j) rs[j] = 0.f;
           } else {
+            // most (tile, chunk) pairs hold out nothing: every row of a one-fold tile trains every column
+            // of the other folds -- that case runs without the per-element selects
+            if (__all_sync(0xffffffffu, heldbits == 0u)) {
 #pragma unroll
-            for (int j = 0; j < 16; ++j) {
-              const bool train = !((heldbits >> j) & 1u);
-              const float z = __uint_as_float(v[j]) + lds32f(bias_s + (c0 + j) * 4);
-              const float e = __expf(-fabsf(z));
-              const float inv = __fdividef(1.f, 1.f + e);
-              const float pr = z >= 0.f ? inv : e * inv;
-              rs[j] = train ? pr - yy : 0.f;
-              ls[j] = train ? (fmaxf(z, 0.f) - yy * z) + (__logf(1.f + e) - p.loss_shift) : 0.f;
+              for (int j = 0; j < 16; ++j) {
+                const float z = __uint_as_float(v[j]) + lds32f(bias_s + (c0 + j) * 4);
+                const float e = __expf(-fabsf(z));
+                const float inv = __fdividef(1.f, 1.f + e);
+                rs[j] = (z >= 0.f ? inv : e * inv) - yy;
+                ls[j] = (fmaxf(z, 0.f) - yy * z) + (__logf(1.f + e) - p.loss_shift);
+              }
+            } else {
+#pragma unroll
+              for (int j = 0; j < 16; ++j) {
+                const bool train = !((heldbits >> j) & 1u);
+                const float z = __uint_as_float(v[j]) + lds32f(bias_s + (c0 + j) * 4);
+                const float e = __expf(-fabsf(z));
+                const float inv = __fdividef(1.f, 1.f + e);
+                const float pr = z >= 0.f ? inv : e * inv;
+                rs[j] = train ? pr - yy : 0.f;
+                ls[j] = train ? (fmaxf(z, 0.f) - yy * z) + (__logf(1.f + e) - p.loss_shift) : 0.f;
+              }
             }
             accA[i] += (double)bfly16(ls, lane);
             accB[i] += (double)bfly16(rs, lane);
