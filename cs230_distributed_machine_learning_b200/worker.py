@@ -43,7 +43,8 @@ MODEL_IMPORTS = {   # worker.py:36-57 plus the two north-star models (SURVEY.md 
     "LinearRegression": "sklearn.linear_model", "Ridge": "sklearn.linear_model",
     "RidgeClassifier": "sklearn.linear_model",
 }
-GPU_MODELS = ("LogisticRegression", "Ridge", "RidgeClassifier")
+GPU_MODELS = ("LogisticRegression", "Ridge", "RidgeClassifier", "LinearRegression")
+REGRESSORS = ("Ridge", "LinearRegression")     # KFold + R^2 (sklearn check_cv / default scorer)
 
 
 def get_model_instance(algorithm_name: str, parameters: dict):
@@ -82,6 +83,10 @@ def gpu_eligible(model_type: str, params: dict) -> tuple[bool, str]:
         if not (isinstance(a, (int, float)) and np.isfinite(a) and a >= 0):
             return False, "alpha must be a finite scalar"
         return True, ""
+    if model_type == "LinearRegression":      # ordinary least squares = the Ridge normal equations with alpha = 0
+        if p.get("positive"):
+            return False, "positive=True"
+        return True, ""
     return False, "model type not covered by the GPU path"
 
 
@@ -91,7 +96,7 @@ def fitted_estimator(model_type: str, parameters: dict, coef, intercept, classes
     est = get_model_instance(model_type, parameters)
     coef = np.asarray(coef, dtype=np.float64)
     icpt = np.asarray(intercept, dtype=np.float64)
-    if model_type == "Ridge":
+    if model_type in REGRESSORS:
         est.coef_ = coef.reshape(-1)
         est.intercept_ = float(icpt.reshape(-1)[0])
         est.n_features_in_ = est.coef_.shape[0]
@@ -285,7 +290,7 @@ class GpuExecutor:
 
     def run(self, model_type: str, cands: list[dict], train_params: dict, dataset_id: str, model_dir: str) -> list[dict]:
         """cands: [{index, subtask_id, parameters}] -> result dict per candidate (A9 shape)."""
-        classifier = model_type != "Ridge"
+        classifier = model_type not in REGRESSORS
         with self.lock:
             ds = self.dataset(dataset_id, classifier)
             hint, self.hint = self.hint, None
@@ -317,8 +322,8 @@ class GpuExecutor:
                     ds, fold, cv, [float(p.get("C", 1.0)) for p in P], [float(p.get("tol", 1e-4)) for p in P], fi,
                     [int(p.get("max_iter", 100)) for p in P], hold_id=hold, want_scores=not refit)
             else:
-                out = self.solver.ridge_sweep(ds, fold, cv, [float(p.get("alpha", 1.0)) for p in P], fi,
-                                              classifier=classifier, hold_id=hold)
+                alphas = [0.0 if model_type == "LinearRegression" else float(p.get("alpha", 1.0)) for p in P]
+                out = self.solver.ridge_sweep(ds, fold, cv, alphas, fi, classifier=classifier, hold_id=hold)
             wall = time.time() - t0
             if len(self.stats["sweep_ms"]) < 4096:
                 self.stats["sweep_ms"].append(out["timing"]["total_ms"])
@@ -442,7 +447,7 @@ def _gpu_block_key(task) -> tuple | None:
             return None
         if choice == "auto" and datasets.get_dataset(block["dataset_id"])[0].dtype != np.float32:
             return None
-        return (block["dataset_id"], block["model_type"] != "Ridge")
+        return (block["dataset_id"], block["model_type"] not in REGRESSORS)
     except Exception:
         return None       # a look-ahead never fails a task; the task itself reports the error
 

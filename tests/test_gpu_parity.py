@@ -283,6 +283,29 @@ def test_refit_on_gpu_equals_gridsearchcv_best_estimator(tmp_path, monkeypatch):
         m.close()
 
 
+def test_linear_regression_is_ridge_with_alpha_zero():
+    """LinearRegression on the b200 executor: the Ridge normal equations with alpha = 0."""
+    from sklearn.linear_model import LinearRegression
+    from sklearn.model_selection import GridSearchCV
+    import cs230_distributed_machine_learning_b200 as pkg
+    X, y = make_dataset("regression", 20_000, 48, seed=95)
+    pkg.register_dataset("lin-reg", X, y)
+    m = pkg.MLTaskManager("local://1")
+    try:
+        grid = {"fit_intercept": [True, False]}
+        r = m.train(GridSearchCV(LinearRegression(), grid, cv=5), "lin-reg", train_params={"refit": True},
+                    wait_for_completion=True)
+        assert r["job_status"] == "completed", r
+        jr = r["job_result"]
+        assert all(res["executor"] == "b200" for res in jr["results"])
+        gs = GridSearchCV(LinearRegression(), grid, cv=5).fit(X.astype(np.float64), y.astype(np.float64))
+        np.testing.assert_allclose(jr["cv_results_"]["mean_test_score"], gs.cv_results_["mean_test_score"], rtol=RTOL)
+        assert jr["best_params_"] == gs.best_params_
+        assert rel_err(np.asarray(jr["best_estimator_"]["coef"]), gs.best_estimator_.coef_) < RTOL
+    finally:
+        m.close()
+
+
 def test_queued_jobs_prefetch_their_dataset_and_match_blocking_runs():
     """Jobs submitted without waiting: the worker starts the next job's host->device copy on its
     copy stream while the current sweep runs.  Results equal the one-job-at-a-time results exactly."""
