@@ -24,8 +24,26 @@ import time
 
 import numpy as np
 
-# stdout carries exactly one JSON line: NCCL's own banner / debug output goes to stderr
+# stdout carries exactly one JSON line.  Native libraries print there too (NCCL's version banner), so the
+# process keeps a private copy of the original stdout for that line and points fd 1 at stderr.
 os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")
+_RESULT_FD = None
+
+
+def _claim_stdout():
+    global _RESULT_FD
+    if _RESULT_FD is None:
+        sys.stdout.flush()
+        _RESULT_FD = os.dup(1)
+        os.dup2(2, 1)
+
+
+def emit(line: dict):
+    data = (json.dumps(line) + "\n").encode()
+    if _RESULT_FD is None:
+        sys.stdout.write(data.decode()); sys.stdout.flush()
+    else:
+        os.write(_RESULT_FD, data)
 
 ROOT = os.path.dirname(os.path.abspath(__file__))
 if ROOT not in sys.path:
@@ -197,14 +215,14 @@ def run_reference(a):
     v = fits / t
     sample_txt = (f"{per_step} of {len(Cs_all)} candidates x {CV} folds per step at full n={a.rows}, "
                   f"{workers if per_step > 1 else 1} process(es), BLAS threads left at default")
-    print(json.dumps({
+    emit({
         "impl": "reference", "metric": METRIC, "value": v, "unit": UNIT, "n_gpus": a.gpus, "steps": a.steps,
         "warmup": a.warmup, "ms_per_step": t / a.steps * 1e3, "higher_is_better": True, "scaling": "weak",
         "vs_baseline": None, "dtype": "f32", "data": "synthetic",
         "config": {"workload": workload_name(a, len(Cs_all)), "l2": "inputs larger than L2"},
         "cpu_baseline": {"value": v, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample_txt},
         "e2e": {"value": v, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
-        "gpu_launches": 0}))
+        "gpu_launches": 0})
 
 
 # ------------------------------------------------------------------------------------------
@@ -384,13 +402,14 @@ def run_b200(a):
             line["cpu_baseline"] = {"value": len(sample) * CV / t, "unit": UNIT, "cores": cores, "kind": "port",
                                     "sample": f"{len(sample)} of {len(Cs_all)} candidates x {CV} folds at full "
                                               f"n={a.rows}, serial fits as in worker.py:326, BLAS on all cores"}
-        print(json.dumps(line))
+        emit(line)
     if world > 1:
         dist.destroy_process_group()
 
 
 if __name__ == "__main__":
     a = parse()
+    _claim_stdout()
     if a.impl == "reference":
         run_reference(a)
     else:
