@@ -62,6 +62,10 @@ struct dml_ctx {
   // tensor work, and the same sustained sweep time at the power cap -- so it is off by default.
   int grad_skip = 0;
   int fold_skip = 1;          // fold-major column groups, so that row tiles of one fold can skip that fold's columns
+  // gradient kernel: cross terms of the 3xTF32 product as bf16 MMAs over a K-concatenated operand
+  // (DML_CROSS_BF16=1).  Measured on config 2: same accuracy (G within 1e-6 of fp64), tensor pipe 60 % -> 43 %
+  // busy, launch time unchanged (the kernel is bound by the MMA warp's issue path, not by the pipe): off.
+  int cross_bf16 = 0;
   int first_round_once = 1;   // evaluate round 0 once per row mask instead of once per candidate
   int tc_prefetch = 0, tc_prefetch_grad = 0;  // L2 prefetch distance of the forward X tiles in jobs (0 = off; measured: no gain, the ring is not latency-bound)
   int tc_cluster = 2;                 // CTAs per cluster in the forward kernel (W multicast): 1 or 2
@@ -169,6 +173,7 @@ extern "C" int dml_ctx_create(int device, void* stream, dml_ctx** out) {
   if (const char* e = getenv("DML_FIRST_ROUND_ONCE")) ctx->first_round_once = atoi(e);
   if (const char* e = getenv("DML_FOLD_SKIP")) ctx->fold_skip = atoi(e);
   if (const char* e = getenv("DML_GRAD_SKIP")) ctx->grad_skip = atoi(e);
+  if (const char* e = getenv("DML_CROSS_BF16")) ctx->cross_bf16 = atoi(e);
   if (const char* e = getenv("DML_TC_CLUSTER")) ctx->tc_cluster = atoi(e) == 1 ? 1 : 2;
   CU(cudaSetDevice(device));
   CU(cudaHostAlloc(&ctx->h_scalar, 64, cudaHostAllocDefault));
@@ -544,7 +549,7 @@ struct EvalCtx {
                         : launch_tc_fwd<tc::FWD_LOGREG_MULTI>(ctx, NC, clr, grid, clr == 2 ? mXf2 : mXf, mWh, mWl, fp);
         if (rc) return rc;
         tc::TcGradParams gp{r0, rows, tc_rps, d, n_slots, Gpart, ldg, ctx->tc_mask_hi, ctx->tc_prefetch_grad,
-                            tile_fold, ctx->grad_skip ? gstart : nullptr, n_groups};
+                            tile_fold, ctx->grad_skip ? gstart : nullptr, n_groups, ctx->cross_bf16};
         const int splits_here = (int)cdiv(rows, tc_rps);
         rc = launch_tc_grad2(ctx, dim3((unsigned)(2 * cdiv(cdiv(d, 128), 2)), (unsigned)cdiv(n_slots, tc::kGrad2NC), (unsigned)splits_here),
                              mXg, mR1, gp);

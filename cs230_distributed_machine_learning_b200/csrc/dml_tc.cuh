@@ -120,6 +120,14 @@ __device__ __forceinline__ void umma_tf32_ts_pair(uint32_t tmem_c, uint32_t tmem
       "tcgen05.mma.cta_group::2.kind::tf32 [%0], [%1], %2, %3, p;\n\t}"
       ::"r"(tmem_c), "r"(tmem_a), "l"(db), "r"(idesc), "r"(accumulate) : "memory");
 }
+// bf16 operands (A: tensor memory, two K-adjacent elements per 32-bit column; B: shared memory), fp32 accumulate
+__device__ __forceinline__ void umma_bf16_ts_pair(uint32_t tmem_c, uint32_t tmem_a, uint64_t db, uint32_t idesc, uint32_t accumulate) {
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "setp.ne.b32 p, %4, 0;\n\t"
+      "tcgen05.mma.cta_group::2.kind::f16 [%0], [%1], %2, %3, p;\n\t}"
+      ::"r"(tmem_c), "r"(tmem_a), "l"(db), "r"(idesc), "r"(accumulate) : "memory");
+}
 __device__ __forceinline__ void umma_commit_pair(uint64_t* bar) {   // arrives on `bar` in both CTAs of the pair
   asm volatile("tcgen05.commit.cta_group::2.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;"
                ::"r"(smem_u32(bar)), "h"((uint16_t)3) : "memory");
@@ -197,6 +205,17 @@ __device__ __forceinline__ uint64_t smem_desc(uint32_t saddr, uint32_t lbo_bytes
 __host__ __device__ constexpr uint32_t instr_desc_tf32(int M, int N, int a_mn_major, int b_mn_major) {
   return (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)a_mn_major << 15) | ((uint32_t)b_mn_major << 16) |
          ((uint32_t)(N >> 3) << 17) | ((uint32_t)(M >> 4) << 24);
+}
+
+// D fp32, A/B bf16
+__host__ __device__ constexpr uint32_t instr_desc_bf16(int M, int N, int a_mn_major, int b_mn_major) {
+  return (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)a_mn_major << 15) | ((uint32_t)b_mn_major << 16) |
+         ((uint32_t)(N >> 3) << 17) | ((uint32_t)(M >> 4) << 24);
+}
+__device__ __forceinline__ uint32_t pack_bf16(float lo_k, float hi_k) {   // element k in the low half, k + 1 in the high half
+  uint32_t r;
+  asm("cvt.rn.bf16x2.f32 %0, %1, %2;" : "=r"(r) : "f"(hi_k), "f"(lo_k));
+  return r;
 }
 
 constexpr uint32_t kHiMask = 0xffffe000u;
@@ -808,6 +827,9 @@ struct TcGradParams {
   // fold-aware skipping (see TcFwdParams): a 128-row chain whose rows all sit in fold k contributes
   // nothing to fold k's columns; 64-column segments inside that group are not loaded or multiplied
   const uint8_t* tile_fold; const int* gstart; int n_groups;
+  // cross terms x_lo r_hi + x_hi r_lo as bf16 MMAs over a K-concatenated operand (128-column blocks only):
+  // 8 MMAs per 32-row stage instead of 12; a cross term is 2^-11 of the product and bf16 keeps 8 bits of it
+  int cross_bf16;
 };
 
 // ---------------------------------------------------------------- gradient kernel, CTA pair
@@ -910,6 +932,8 @@ tc_grad2_kernel(const __grid_constant__ CUtensorMap mapX, const __grid_constant_
     return m;
   };
 
+  const bool use_bf = p.cross_bf16 != 0 && nseg == 2;   // only chains without a skipped segment take this form
+
   if (warp == kGrad2TmaWarp) {
     if (lane == 0) {
       uint32_t skip = 0;
@@ -941,9 +965,14 @@ tc_grad2_kernel(const __grid_constant__ CUtensorMap mapX, const __grid_constant_
       }
     }
   } else if (warp == kGrad2MmaWarp) {
+    // The whole warp runs the loop and one elected lane issues: with a single-lane branch around the loop
+    // the compiler cannot keep descriptors in uniform registers and the launch takes 1.16 ms instead of 0.78.
     if (leader) {
       constexpr uint32_t idesc_seg = instr_desc_tf32(256, 64, 0, 1);
-      const uint32_t idesc_all = instr_desc_tf32(256, ncols, 0, 1);
+      const uint32_t idesc_all = instr_desc_tf32(256, ncols, 0, 1), idesc_bf = instr_desc_bf16(256, ncols, 0, 1);
+      // descriptors of stage slot 0; a slot / K step / lo buffer adds a constant to the address field
+      const uint64_t dR0 = smem_desc(smem_u32(smR), 4096, 512, kLayoutSw128Base32);
+      const uint64_t dB0 = smem_desc(smem_u32(smR) + L::kBh, 8192, 1024, kLayoutSw128);
       for (int g = 0, it = 0; g < n_groups; ++g) {
         const int acc = g & 1; const uint32_t aph = (g >> 1) & 1;
         const uint32_t skip = skip_of(g);
@@ -951,34 +980,38 @@ tc_grad2_kernel(const __grid_constant__ CUtensorMap mapX, const __grid_constant_
         tc_fence_after();
         const uint32_t tacc = tmem_base + acc * kGrad2NC;
         const int g_end = min(n_stages, (g + 1) * kChain);
-        for (int first = 1; it < g_end; ++it) {
+        for (uint32_t first = 0; it < g_end; ++it, first = 1) {
           const int sr = it % SR, ta = it % TA;
           mbar_wait_cluster(bsplit + sr, (it / SR) & 1);
           mbar_wait_cluster(split + ta, (it / TA) & 1);
           tc_fence_after();
           if (elect_one()) {
             const uint32_t ta_hi = tmem_base + kTmemA + ta * 64, ta_lo = ta_hi + 32;
-            const uint32_t b0 = smem_u32(smR + sr * L::kB);
-            if (skip == 0) {
+            const uint64_t dh = dR0 + (uint64_t)((sr * L::kB) >> 4), dl = dh + (L::kBh >> 4);
+            if (skip == 0 && use_bf) {
+              // B' = [bf16(R) rows 0-31 ; bf16(R_lo) rows 32-63], 64 columns per CTA, MN-major SWIZZLE_128B;
+              // A' = [x_lo | x_hi] as bf16 pairs in columns 32..63 of the slot: 16 K values per MMA
+              const uint64_t db = dB0 + (uint64_t)((sr * L::kB) >> 4);
+#pragma unroll
+              for (int j = 0; j < 4; ++j) umma_bf16_ts_pair(tacc, ta_lo + j * 8, db + j * (2048 >> 4), idesc_bf, j == 0 ? first : 1u);
+#pragma unroll
+              for (int k = 0; k < 4; ++k) umma_tf32_ts_pair(tacc, ta_hi + k * 8, dh + k * (1024 >> 4), idesc_all, 1);
+            } else if (skip == 0) {
 #pragma unroll
               for (int k = 0; k < 4; ++k) {
-                const uint64_t dbh = smem_desc(b0 + k * 1024, 4096, 512, kLayoutSw128Base32);
-                const uint64_t dbl = smem_desc(b0 + L::kBh + k * 1024, 4096, 512, kLayoutSw128Base32);
-                umma_tf32_ts_pair(tacc, ta_lo + k * 8, dbh, idesc_all, (first && k == 0) ? 0u : 1u);
-                umma_tf32_ts_pair(tacc, ta_hi + k * 8, dbl, idesc_all, 1);
-                umma_tf32_ts_pair(tacc, ta_hi + k * 8, dbh, idesc_all, 1);
+                umma_tf32_ts_pair(tacc, ta_lo + k * 8, dh + k * (1024 >> 4), idesc_all, k == 0 ? first : 1u);
+                umma_tf32_ts_pair(tacc, ta_hi + k * 8, dl + k * (1024 >> 4), idesc_all, 1);
+                umma_tf32_ts_pair(tacc, ta_hi + k * 8, dh + k * (1024 >> 4), idesc_all, 1);
               }
             } else {
               for (int sg = 0; sg < nseg; ++sg) {
                 if ((skip >> sg) & 1u) continue;
-                const uint32_t b_hi = b0 + sg * 4096, b_lo = b_hi + L::kBh;
+                const uint64_t sh = dh + sg * (4096 >> 4), sl = dl + sg * (4096 >> 4);
 #pragma unroll
                 for (int k = 0; k < 4; ++k) {
-                  const uint64_t dbh = smem_desc(b_hi + k * 1024, 4096, 512, kLayoutSw128Base32);
-                  const uint64_t dbl = smem_desc(b_lo + k * 1024, 4096, 512, kLayoutSw128Base32);
-                  umma_tf32_ts_pair(tacc + sg * 64, ta_lo + k * 8, dbh, idesc_seg, (first && k == 0) ? 0u : 1u);
-                  umma_tf32_ts_pair(tacc + sg * 64, ta_hi + k * 8, dbl, idesc_seg, 1);
-                  umma_tf32_ts_pair(tacc + sg * 64, ta_hi + k * 8, dbh, idesc_seg, 1);
+                  umma_tf32_ts_pair(tacc + sg * 64, ta_lo + k * 8, sh + k * (1024 >> 4), idesc_seg, k == 0 ? first : 1u);
+                  umma_tf32_ts_pair(tacc + sg * 64, ta_hi + k * 8, sl + k * (1024 >> 4), idesc_seg, 1);
+                  umma_tf32_ts_pair(tacc + sg * 64, ta_hi + k * 8, sh + k * (1024 >> 4), idesc_seg, 1);
                 }
               }
             }
@@ -987,7 +1020,6 @@ tc_grad2_kernel(const __grid_constant__ CUtensorMap mapX, const __grid_constant_
             if (it == g_end - 1) umma_commit_pair(tfull + acc);
           }
           __syncwarp();
-          first = 0;
         }
       }
     }
@@ -1001,6 +1033,26 @@ tc_grad2_kernel(const __grid_constant__ CUtensorMap mapX, const __grid_constant_
       const int sr = it % SR;
       mbar_wait(fullR + sr, (it / SR) & 1);
       const uint32_t hi_s = smem_u32(smR + sr * L::kB), lo_s = hi_s + L::kBh;
+      if (use_bf && skip == 0) {
+        // unit = (row k, 8 columns): 32 source bytes (one swizzled sub-chunk of the TMA tile) -> 16 bytes of
+        // bf16(R) in row k and 16 bytes of bf16(R - tf32(R)) in row 32 + k of the bf16 tile
+#pragma unroll
+        for (int u4 = 0; u4 < 4; ++u4) {
+          const int u = u4 * 64 + half * 32 + lane, k = u >> 3, c8 = u & 7;
+          const uint32_t src = hi_s + (c8 >> 2) * 4096 + k * 128 + (((c8 & 3) ^ (k & 3)) << 5);
+          const float4 a = lds128(src), b = lds128(src + 16);
+          float4 h, l;
+          h.x = __uint_as_float(pack_bf16(a.x, a.y)); h.y = __uint_as_float(pack_bf16(a.z, a.w));
+          h.z = __uint_as_float(pack_bf16(b.x, b.y)); h.w = __uint_as_float(pack_bf16(b.z, b.w));
+          l.x = __uint_as_float(pack_bf16(a.x - tf32_hi(a.x), a.y - tf32_hi(a.y)));
+          l.y = __uint_as_float(pack_bf16(a.z - tf32_hi(a.z), a.w - tf32_hi(a.w)));
+          l.z = __uint_as_float(pack_bf16(b.x - tf32_hi(b.x), b.y - tf32_hi(b.y)));
+          l.w = __uint_as_float(pack_bf16(b.z - tf32_hi(b.z), b.w - tf32_hi(b.w)));
+          const uint32_t dst = lo_s + k * 128 + ((c8 ^ (k & 7)) << 4);
+          sts128(dst, h);
+          sts128(dst + 32 * 128, l);
+        }
+      } else
       for (int sg = 0; sg < nseg; ++sg) {
         if ((skip >> sg) & 1u) continue;
 #pragma unroll
@@ -1016,6 +1068,7 @@ tc_grad2_kernel(const __grid_constant__ CUtensorMap mapX, const __grid_constant_
     }
   } else if (warp < 4) {
     const int qd = warp & 3;
+    uint32_t sk = 0;
     for (int it = 0; it < n_stages; ++it) {
       const int sx = it % SX, ta = it % TA;
       mbar_wait(fullA + sx, (it / SX) & 1);
@@ -1032,7 +1085,17 @@ tc_grad2_kernel(const __grid_constant__ CUtensorMap mapX, const __grid_constant_
       tc_fence_after();
       const uint32_t taddr = tmem_base + kTmemA + ta * 64 + ((uint32_t)(qd * 32) << 16);
       tmem_st32(taddr, hi);
-      tmem_st32(taddr + 32, lo);
+      if (use_bf && (it % kChain == 0 ? (sk = skip_of(it / kChain)) : sk) == 0) {
+        uint32_t pk[32];       // columns 32..47: x_lo as bf16 pairs (K order), 48..63: x as bf16 pairs
+#pragma unroll
+        for (int e = 0; e < 16; ++e) {
+          pk[e] = pack_bf16(__uint_as_float(lo[2 * e]), __uint_as_float(lo[2 * e + 1]));
+          pk[16 + e] = pack_bf16(__uint_as_float(hi[2 * e]), __uint_as_float(hi[2 * e + 1]));
+        }
+        tmem_st32(taddr + 32, pk);
+      } else {
+        tmem_st32(taddr + 32, lo);
+      }
       tmem_st_wait();
       tc_fence_before();
       __syncwarp();

@@ -7,7 +7,7 @@ from cs230_distributed_machine_learning_b200.solver import SweepSolver
 
 s = SweepSolver(0)
 rng = np.random.default_rng(0)
-for (n, d, K, wscale) in [(256, 32, 32, 0.0), (256, 32, 32, 0.3), (1000, 64, 20, 0.3), (4096, 256, 160, 0.1), (5000, 100, 37, 0.2)]:
+for (n, d, K, wscale) in [(256, 32, 32, 0.0), (256, 32, 32, 0.3), (1000, 64, 20, 0.3), (4096, 256, 160, 0.1), (5000, 100, 37, 0.2), (8192, 256, 256, 0.1)]:
     X, y = make_dataset("binary", n, d, seed=9)
     fold = folds.stratified_labels(y, 5)
     ds = s.upload_dataset(X, y, classifier=True)
