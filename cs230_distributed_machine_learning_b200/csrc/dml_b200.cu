@@ -444,6 +444,58 @@ __global__ void reduce_sse_parts_kernel(const double* part, int64_t n_parts, int
   sse[slot] = a;
 }
 
+// Forward pass of round 0 without a GEMM (binary problems, at most 32 columns): every coefficient is zero,
+// so z = 0, p = 1/2 and the residual of a training row is 1/2 - y -- exactly what the tcgen05 kernel
+// computes there (ex2(0) = 1, rcp(2) = 1/2, lg2(2) = 1, so loss - ln 2 = 0).  Writes the chunk-major residual
+// scratch (one 32-column chunk) and per-block column sums of r.
+struct ZeroRoundParams {
+  int64_t row0, rows; const int32_t* y; const int8_t* fold_id; const int8_t* hold_id;
+  const int32_t* sel; const int32_t* val; int n_slots;
+  float* R; double* gbPart;   // R: [rows][32] (chunk 0); gbPart: [gridDim.x][n_slots]
+};
+__global__ void __launch_bounds__(256) zero_round_kernel(const ZeroRoundParams p) {
+  __shared__ int s_sel[32], s_val[32];
+  __shared__ float s_red[8][32];
+  if (threadIdx.x < 32) {
+    s_sel[threadIdx.x] = threadIdx.x < p.n_slots ? p.sel[threadIdx.x] : -1;
+    s_val[threadIdx.x] = threadIdx.x < p.n_slots ? (p.val[threadIdx.x] & 0xff) : 0;
+  }
+  __syncthreads();
+  float part[32];
+#pragma unroll
+  for (int c = 0; c < 32; ++c) part[c] = 0.f;
+  for (int64_t row = (int64_t)blockIdx.x * 256 + threadIdx.x; row < p.rows; row += (int64_t)gridDim.x * 256) {
+    const int64_t g = p.row0 + row;
+    const float base = 0.5f - (float)p.y[g];
+    const int fv = (int)(uint8_t)p.fold_id[g], hv = p.hold_id ? ((int)(uint8_t)p.hold_id[g] & 1) : 0;
+    float out[32];
+#pragma unroll
+    for (int c = 0; c < 32; ++c) {
+      const int sl = s_sel[c];
+      const bool held = sl < 0 || (sl == 0 ? fv == s_val[c] : hv == s_val[c]);
+      out[c] = held ? 0.f : base;
+      part[c] += out[c];            // multiples of 1/2: exact
+    }
+    float4* dst = reinterpret_cast<float4*>(p.R + row * 32);
+#pragma unroll
+    for (int q = 0; q < 8; ++q) dst[q] = make_float4(out[4 * q], out[4 * q + 1], out[4 * q + 2], out[4 * q + 3]);
+  }
+  const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+#pragma unroll
+  for (int c = 0; c < 32; ++c) {
+    float v = part[c];
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    if (lane == 0) s_red[w][c] = v;
+  }
+  __syncthreads();
+  if (threadIdx.x < p.n_slots) {
+    double a = 0.0;
+    for (int i = 0; i < 8; ++i) a += (double)s_red[i][threadIdx.x];
+    p.gbPart[(int64_t)blockIdx.x * p.n_slots + threadIdx.x] = a;
+  }
+}
+
 // =============================================================================================
 // One batched loss/gradient evaluation for `n_slots` columns: the buffers and the two code paths
 // (tcgen05 3xTF32, or FFMA for shapes the tensor-core path does not take).
@@ -519,7 +571,8 @@ struct EvalCtx {
     return DML_OK;
   }
   // Gred[slot] = [sum r x (d), sum r, sum loss] over the training rows of each column
-  int evaluate(dml_ctx* ctx, int n_slots) {
+  // zero_w: every coefficient of the evaluated columns is zero (round 0)
+  int evaluate(dml_ctx* ctx, int n_slots, bool zero_w = false) {
     cudaStream_t st = ctx->stream;
     int launches = 0;
     if (use_tc) {
@@ -545,8 +598,17 @@ struct EvalCtx {
         const int grid = clr * (int)std::min<int64_t>(jobs, ctx->n_sms / clr);
         CU(cudaMemsetAsync(lossPart, 0, sizeof(double) * (size_t)grid * 4 * n_slots, st));
         CU(cudaMemsetAsync(gbPart, 0, sizeof(double) * (size_t)grid * 4 * n_slots, st));
-        int rc = T == 1 ? launch_tc_fwd<FWD_LOGREG>(ctx, NC, clr, grid, clr == 2 ? mXf2 : mXf, mWh, mWl, fp)
-                        : launch_tc_fwd<tc::FWD_LOGREG_MULTI>(ctx, NC, clr, grid, clr == 2 ? mXf2 : mXf, mWh, mWl, fp);
+        int rc = DML_OK;
+        int64_t n_parts = (int64_t)grid * 4;
+        if (zero_w && T == 1 && n_slots <= 32 && ctx->first_round_once) {
+          const int zgrid = (int)std::min<int64_t>(cdiv(rows, 256), 4 * ctx->n_sms);
+          ZeroRoundParams zp{r0, rows, y, fold_id, hold_id, sel, val, n_slots, R, gbPart};
+          zero_round_kernel<<<zgrid, 256, 0, st>>>(zp);
+          n_parts = zgrid;
+        } else {
+          rc = T == 1 ? launch_tc_fwd<FWD_LOGREG>(ctx, NC, clr, grid, clr == 2 ? mXf2 : mXf, mWh, mWl, fp)
+                      : launch_tc_fwd<tc::FWD_LOGREG_MULTI>(ctx, NC, clr, grid, clr == 2 ? mXf2 : mXf, mWh, mWl, fp);
+        }
         if (rc) return rc;
         tc::TcGradParams gp{r0, rows, tc_rps, d, n_slots, Gpart, ldg, ctx->tc_mask_hi, ctx->tc_prefetch_grad,
                             tile_fold, ctx->grad_skip ? gstart : nullptr, n_groups, ctx->cross_bf16};
@@ -556,7 +618,7 @@ struct EvalCtx {
         if (rc) return rc;
         ReduceParams rp{Gpart, ldg, splits_here, n_slots, d, T, d, nullptr, 0, 0, Gred, ldgr, ci > 0 ? 1 : 0};
         reduce_grad_kernel<<<n_slots, 256, 0, st>>>(rp);
-        tc::TcReduceParams tr{lossPart, gbPart, (int64_t)grid * 4, n_slots, T, d, Gred, ldgr, ci > 0 ? 1 : 0,
+        tc::TcReduceParams tr{lossPart, gbPart, n_parts, n_slots, T, d, Gred, ldgr, ci > 0 ? 1 : 0,
                               hist_local, sel, val, n, (double)loss_shift()};
         tc::tc_reduce_tiles_kernel<<<(unsigned)cdiv(n_slots, 32), dim3(32, 32), 0, st>>>(tr);
       } else {
@@ -763,7 +825,7 @@ extern "C" int dml_logreg_sweep(dml_ctx* ctx, const float* X, int64_t n, int d, 
     KCHECK();
     ev.gstart = nullptr;
     ctx->slot_rounds += (int64_t)fpc * T; ctx->rounds += 1; ++rounds;
-    int rc = ev.evaluate(ctx, fpc * T);
+    int rc = ev.evaluate(ctx, fpc * T, true);
     if (rc) return rc;
     if (ctx->comm) { rc = allreduce(ctx, ev.Gred, (size_t)fpc * T * ev.ldgr, kNcclFloat64); if (rc) return rc; }
     ctx->first_pairs = ctx->ev_used / 2; ctx->first_cols = (int64_t)fpc * T;
