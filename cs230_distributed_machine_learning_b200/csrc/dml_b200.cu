@@ -230,7 +230,7 @@ extern "C" int dml_last_timing(dml_ctx* ctx, float* total_ms, float* contraction
   return DML_OK;
 }
 
-// Debug aid: copy scratch buffer `which` (0 R/R_hi, 1 R_lo, 2 Gpart, 3 W_hi) of the last evaluation to the host.
+// Debug aid: copy scratch buffer `which` (0 R (chunk-major on the tcgen05 path), 2 Gpart, 3 W_hi) of the last evaluation to the host.
 extern "C" int dml_debug_fetch(dml_ctx* ctx, int which, void* dst_host, size_t bytes, size_t* avail) {
   if (!ctx || which < 0 || which > 3) return DML_ERR_ARG;
   if (avail) *avail = ctx->dbg_bytes[which];

@@ -1,15 +1,16 @@
 // tcgen05 (5th-gen tensor core) path of the sweep: 3xTF32 split-precision contractions
 // with TMA-staged operands and TMEM accumulators, sm_100a only.
 //
-//   tc_fwd_kernel : Z = X W^T for a 128-row tile x NC columns, epilogue in registers:
-//                   loss / residual (written pre-split as R_hi, R_lo) or counts
-//   tc_grad_kernel: G = X^T R for a 128-feature block x NC columns over a row split
+//   tc_fwd_kernel  : Z = X W^T for a 128-row tile x NC columns, epilogue in registers:
+//                    loss / residual (one fp32 array R) or counts
+//   tc_grad2_kernel: G = X^T R for two 128-feature blocks x 128 columns over a row split, on CTA pairs
+//   tc_gram_kernel : per-fold X^T X blocks for Ridge
 //
 // Split precision: a = a_hi + a_lo with a_hi = a & 0xffffe000 (exactly a TF32 number);
 // a.b ~= a_hi.b_hi + a_hi.b_lo + a_lo.b_hi, three kind::tf32 MMAs into one fp32
-// TMEM accumulator.  The operand derived from X is split inside the kernel (the
-// split is elementwise, so it works on the swizzled stage buffer as it lies); the
-// other operand (W or R) arrives pre-split from the kernel that produced it.
+// TMEM accumulator.  The operand derived from X is split inside the kernel and staged
+// in tensor memory; W arrives pre-split (split_weights_kernel), R is split inside the
+// gradient kernel (the split is elementwise, so it works on the swizzled tile as it lies).
 //
 // Reference call sites these stand in for: the X @ w and X.T @ g products inside
 // every L-BFGS function evaluation of every fit (sklearn/linear_model/_linear_loss.py:216-222,
@@ -835,7 +836,7 @@ struct TcGradParams {
 // ---------------------------------------------------------------- gradient kernel, CTA pair
 // Same contraction with cta_group::2 MMAs (M = 256): the two CTAs of a cluster take feature blocks
 // 2k and 2k+1 and share the R operand -- each loads and holds half of the block's columns, so the
-// shared-memory traffic of the B operand (the limiter of the one-CTA kernel) is halved per SM.
+// shared-memory traffic of the B operand is halved per SM.
 //   leader (rank 0): issues every MMA; its fullB / split / tempty barriers also count the peer's
 //                    TMA bytes, staging warps and drain warps (remote arrives)
 //   both CTAs      : TMA producer (own X boxes -> own fullA; own R half -> the leader's fullB),

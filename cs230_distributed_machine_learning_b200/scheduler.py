@@ -20,6 +20,13 @@ import uuid
 HEARTBEAT_TIMEOUT_S = 10.0   # scheduler_service.py:214
 
 
+def _task_fits(task: dict) -> int:
+    """Work of a subtask in candidate-fold fits (a legacy subtask is one candidate, all folds)."""
+    cv = task.get("train_params", {}).get("cv", 5)
+    folds = len(task["folds"]) if task.get("folds") else (cv if isinstance(cv, int) else 5)
+    return max(1, len(task.get("candidates", [0])) * max(1, folds))
+
+
 class Scheduler:
     def __init__(self):
         self.lock = threading.Lock()
@@ -84,7 +91,15 @@ class Scheduler:
         for wid in ids:                       # the block names its GPU
             if gpu is not None and self.workers[wid]["gpu"] == gpu:
                 return wid
-        return min(ids, key=lambda w: (len(self.workers[w]["inflight"]), w))   # least loaded
+        # scheduler_service.py:173-191: minimise load/speed + est/speed; "speed" is the fits/s this worker
+        # reported on its last blocks (publish_metrics), work is counted in candidate-fold fits
+        est = _task_fits(task)
+
+        def cost(w):
+            rec = self.workers[w]
+            load = sum(_task_fits(t) for t in rec["inflight"].values())
+            return ((load + est) / rec.get("speed", 1.0), w)
+        return min(ids, key=cost)
 
     # topics "result" / "metrics"
     def publish_result(self, worker_id: str, message: dict) -> None:
@@ -97,6 +112,12 @@ class Scheduler:
             self.master.on_result(message)
 
     def publish_metrics(self, record: dict) -> None:
+        fps = record.get("fits_per_sec")
+        if fps:                               # speed factor of the placement rule: moving average of measured fits/s
+            with self.lock:
+                w = self.workers.get(record.get("worker_id"))
+                if w is not None:
+                    w["speed"] = 0.5 * w["speed"] + 0.5 * float(fps) if "speed" in w else float(fps)
         if self.master is not None:
             self.master.on_metrics(record)
 
@@ -127,4 +148,4 @@ class Scheduler:
     def workers_view(self) -> dict:      # GET /workers
         with self.lock:
             return {wid: {"gpu": w["gpu"], "inflight": len(w["inflight"]), "done": w["done"],
-                          "last_seen": w["last_seen"]} for wid, w in self.workers.items()}
+                          "last_seen": w["last_seen"], "speed": w.get("speed")} for wid, w in self.workers.items()}

@@ -206,6 +206,30 @@ def test_scheduler_contract_and_requeue():
     assert s.unsubscribe(w0)["status"] == "unsubscribed" and s.n_workers() == 0
 
 
+def test_scheduler_places_by_measured_speed():
+    """scheduler_service.py:173-191: a task without a GPU goes to the worker with the least
+    (queued fits + its own fits) / measured fits per second."""
+    s = scheduler.Scheduler()
+
+    class M:
+        def on_result(self, msg): pass
+        def on_metrics(self, rec): pass
+    s.attach_master(M())
+    fast = s.subscribe(1000, "h", gpu=0)["worker_id"]
+    slow = s.subscribe(1000, "h", gpu=1)["worker_id"]
+    s.publish_metrics({"worker_id": fast, "subtask_id": "x", "fits_per_sec": 20000.0})
+    s.publish_metrics({"worker_id": slow, "subtask_id": "y", "fits_per_sec": 5.0})
+    view = s.workers_view()
+    assert view[fast]["speed"] == 20000.0 and view[slow]["speed"] == 5.0
+    blk = lambda i: {"subtask_id": f"b{i}", "candidates": [{}] * 64, "folds": [0, 1, 2, 3, 4]}
+    assert [s.submit(blk(i)) for i in range(4)] == [fast] * 4          # 4 x 320 fits queued is still cheaper there
+    s.publish_metrics({"worker_id": fast, "subtask_id": "x", "fits_per_sec": 10000.0})
+    assert s.workers_view()[fast]["speed"] == 15000.0                   # moving average
+    # equal speeds: the shorter queue wins
+    s.workers[slow]["speed"] = 15000.0
+    assert s.submit(blk(9)) == slow
+
+
 def test_gpu_eligibility_rules():
     ok = worker.gpu_eligible
     assert ok("LogisticRegression", {"C": 1.0, "solver": "lbfgs"})[0]
