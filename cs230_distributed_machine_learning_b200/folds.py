@@ -30,7 +30,18 @@ def stratified_labels(y_idx: np.ndarray, n_folds: int) -> np.ndarray:
     """
     y_idx = np.asarray(y_idx)
     n = y_idx.shape[0]
-    _, first, inv = np.unique(y_idx, return_index=True, return_inverse=True)
+    if y_idx.dtype.kind in "iu" and n and 0 <= int(y_idx.min()) and int(y_idx.max()) < (1 << 16):
+        # small non-negative integers (the worker's label encoding): counting instead of sorting
+        inv = y_idx.astype(np.intp, copy=False)
+        span = int(y_idx.max()) + 1
+        first = np.full(span, n, dtype=np.intp)
+        first[inv[::-1]] = np.arange(n - 1, -1, -1, dtype=np.intp)     # duplicates: the last write = smallest index
+        present = np.nonzero(first < n)[0]
+        remap = np.zeros(span, dtype=np.intp)
+        remap[present] = np.arange(present.shape[0])
+        inv, first = remap[inv], first[present]
+    else:
+        _, first, inv = np.unique(y_idx, return_index=True, return_inverse=True)
     n_classes = first.shape[0]
     counts = np.bincount(inv, minlength=n_classes)
     if np.all(n_folds > counts):
@@ -45,8 +56,8 @@ def stratified_labels(y_idx: np.ndarray, n_folds: int) -> np.ndarray:
         # rows of class k occupy positions [starts[k], starts[k]+cnt[k]) of the sorted
         # label vector; position p goes to fold p % n_folds, so the quota of fold f is
         # the number of such p with p % n_folds == f
-        pos = np.arange(starts[k], starts[k] + cnt[k])
-        quota = np.bincount(pos % n_folds, minlength=n_folds)
+        f = np.arange(n_folds)
+        quota = cnt[k] // n_folds + (((f - starts[k]) % n_folds) < (cnt[k] % n_folds))
         out[enc == k] = np.repeat(np.arange(n_folds, dtype=np.int8), quota)
     return out
 

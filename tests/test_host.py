@@ -230,6 +230,27 @@ def test_scheduler_places_by_measured_speed():
     assert s.submit(blk(9)) == slow
 
 
+@pytest.mark.parametrize("kind", ["binary", "strings", "many", "sorted"])
+def test_fold_labels_equal_sklearn_splitters(kind):
+    """The int8 row labels the kernels take = the un-shuffled (Stratified)KFold of cross_val_score(cv=int)."""
+    from sklearn.model_selection import KFold, StratifiedKFold
+    from cs230_distributed_machine_learning_b200 import folds as pf
+    rng = np.random.default_rng(3)
+    n = 1237
+    y = {"binary": rng.integers(0, 2, n), "strings": rng.choice(np.array(["b", "a", "c"]), n, p=[0.6, 0.3, 0.1]),
+         "many": rng.integers(0, 37, n) * 3 - 5, "sorted": np.sort(rng.integers(0, 4, n))}[kind]
+    for nf in (2, 5, 7):
+        want = np.empty(n, dtype=np.int8)
+        for i, (_, te) in enumerate(StratifiedKFold(nf).split(y, y)):
+            want[te] = i
+        _, idx = np.unique(y, return_inverse=True)
+        assert (pf.stratified_labels(idx, nf) == want).all()
+        assert (pf.stratified_labels(y, nf) == want).all()
+        for i, (_, te) in enumerate(KFold(nf).split(y)):
+            want[te] = i
+        assert (pf.kfold_labels(n, nf) == want).all()
+
+
 def test_gpu_eligibility_rules():
     ok = worker.gpu_eligible
     assert ok("LogisticRegression", {"C": 1.0, "solver": "lbfgs"})[0]
