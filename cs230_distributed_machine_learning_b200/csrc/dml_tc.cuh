@@ -1094,7 +1094,7 @@ tc_grad2_kernel(const __grid_constant__ CUtensorMap mapX, const __grid_constant_
           pk[16 + e] = pack_bf16(__uint_as_float(hi[2 * e]), __uint_as_float(hi[2 * e + 1]));
         }
         tmem_st32(taddr + 32, pk);
-      } else if (p.mask_hi != 77) {      // (77: timing experiment without the lo store -- wrong results)
+      } else {
         tmem_st32(taddr + 32, lo);
       }
       tmem_st_wait();
