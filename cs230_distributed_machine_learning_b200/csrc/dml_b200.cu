@@ -67,6 +67,7 @@ struct dml_ctx {
   // busy, launch time unchanged (the kernel is bound by the MMA warp's issue path, not by the pipe): off.
   int cross_bf16 = 0;
   int first_round_once = 1;   // evaluate round 0 once per row mask instead of once per candidate
+  int tc_rps = 8192;          // most rows per gradient split (DML_TC_RPS, multiple of 128 in 2048..8192)
   int tc_prefetch = 0, tc_prefetch_grad = 0;  // L2 prefetch distance of the forward X tiles in jobs (0 = off; measured: no gain, the ring is not latency-bound)
   int tc_cluster = 2;                 // CTAs per cluster in the forward kernel (W multicast): 1 or 2
   int tc_mask_hi = 0;                 // 1 = write the masked hi operand back before the MMAs read it (not needed:
@@ -174,6 +175,7 @@ extern "C" int dml_ctx_create(int device, void* stream, dml_ctx** out) {
   if (const char* e = getenv("DML_FOLD_SKIP")) ctx->fold_skip = atoi(e);
   if (const char* e = getenv("DML_GRAD_SKIP")) ctx->grad_skip = atoi(e);
   if (const char* e = getenv("DML_CROSS_BF16")) ctx->cross_bf16 = atoi(e);
+  if (const char* e = getenv("DML_TC_RPS")) { const int v = atoi(e); if (v >= 2048 && v <= 8192 && v % 128 == 0) ctx->tc_rps = v; }
   if (const char* e = getenv("DML_TC_CLUSTER")) ctx->tc_cluster = atoi(e) == 1 ? 1 : 2;
   CU(cudaSetDevice(device));
   CU(cudaHostAlloc(&ctx->h_scalar, 64, cudaHostAllocDefault));
@@ -505,7 +507,7 @@ struct EvalCtx {
   const int32_t* y = nullptr; const int8_t* fold_id = nullptr; const int8_t* hold_id = nullptr;
   // plan
   bool use_tc = false, xvec = false; int cl = 2; int NC = 160, nt = 1, tile_n = BN, ldw = 0, ldg = 0, ldgr = 0, splits = 1;
-  int64_t S_max = 0, ldr_max = 0, chunk_rows = 0, rps = 0, tc_rps = 2048, tiles_total = 0; int ctx_sms = 148;
+  int64_t S_max = 0, ldr_max = 0, chunk_rows = 0, rps = 0, tc_rps = 2048, tc_rps_max = 8192, tiles_total = 0; int ctx_sms = 148;
   // buffers
   float *Wt = nullptr, *bt = nullptr, *R = nullptr, *Whi = nullptr, *Wlo = nullptr, *Gpart = nullptr;
   double *lossPart = nullptr, *gbPart = nullptr, *Gred = nullptr; int32_t *sel = nullptr, *val = nullptr, *cntPart = nullptr;
@@ -522,7 +524,7 @@ struct EvalCtx {
       if (cudaMemGetInfo(&free_b, &total_b) == cudaSuccess)
         ctx->r_budget = std::max<size_t>((size_t)1 << 30, std::min<size_t>((size_t)16 << 30, (free_b + ctx->ws_bytes) / 3));
     }
-    cl = ctx->tc_cluster;
+    cl = ctx->tc_cluster; tc_rps_max = ctx->tc_rps;
     ldw = (int)rup(d, 4); ldg = (int)rup(d + 1, 4); ldgr = d + 2;
     tiles_total = cdiv(n, BM); tile_n = (BN / T) * T;
     NC = pick_nc(S_max, T); if (NC == 0) NC = 160;
@@ -610,9 +612,15 @@ struct EvalCtx {
                       : launch_tc_fwd<tc::FWD_LOGREG_MULTI>(ctx, NC, clr, grid, clr == 2 ? mXf2 : mXf, mWh, mWl, fp);
         }
         if (rc) return rc;
-        tc::TcGradParams gp{r0, rows, tc_rps, d, n_slots, Gpart, ldg, ctx->tc_mask_hi, ctx->tc_prefetch_grad,
+        // rows per split: the scratch is planned for 2048 (tc_rps); longer splits mean fewer CTAs (each pays
+        // its pipeline fill and drain) and fewer partial gradients to reduce, as long as two waves of CTA
+        // pairs remain.  Measured on config 2: 2048 / 4096 / 8192 rows -> 0.81 / 0.73 / 0.69 ms per launch.
+        const int64_t pair_blocks = cdiv(n_slots, tc::kGrad2NC) * cdiv(cdiv(d, 128), 2);
+        const int64_t min_splits = cdiv((int64_t)ctx->n_sms, pair_blocks);            // 2 waves of n_sms / 2 pairs
+        const int64_t rps_here = std::min<int64_t>(tc_rps_max, std::max<int64_t>(tc_rps, (rows / min_splits) / 128 * 128));
+        tc::TcGradParams gp{r0, rows, rps_here, d, n_slots, Gpart, ldg, ctx->tc_mask_hi, ctx->tc_prefetch_grad,
                             tile_fold, ctx->grad_skip ? gstart : nullptr, n_groups, ctx->cross_bf16};
-        const int splits_here = (int)cdiv(rows, tc_rps);
+        const int splits_here = (int)cdiv(rows, rps_here);
         rc = launch_tc_grad2(ctx, dim3((unsigned)(2 * cdiv(cdiv(d, 128), 2)), (unsigned)cdiv(n_slots, tc::kGrad2NC), (unsigned)splits_here),
                              mXg, mR1, gp);
         if (rc) return rc;
