@@ -69,7 +69,7 @@ struct dml_ctx {
   int first_round_once = 1;   // evaluate round 0 once per row mask instead of once per candidate
   int tc_rps = 8192;          // most rows per gradient split (DML_TC_RPS, multiple of 128 in 2048..8192)
   int tc_prefetch = 0, tc_prefetch_grad = 0;  // L2 prefetch distance of the forward X tiles in jobs (0 = off; measured: no gain, the ring is not latency-bound)
-  int tc_cluster = 2;                 // CTAs per cluster in the forward kernel (W multicast): 1 or 2
+  int tc_cluster = 2;                 // CTAs per cluster in the forward kernel (X tiles multicast): 1 or 2
   int tc_mask_hi = 0;                 // 1 = write the masked hi operand back before the MMAs read it (not needed:
                                       // kind::tf32 ignores the 13 low mantissa bits, measured identical results)
   long long slot_rounds = 0; int rounds = 0;  // sum over rounds of evaluated columns
@@ -322,6 +322,17 @@ static bool tc_eligible(const float* X, int64_t ldx, int T) {
   return ldx % 4 == 0 && aligned16(X) && (T == 1 || (T >= 3 && T <= 16 && pick_nc(1, T) != 0));
 }
 
+// CTAs per cluster of the forward kernel.  With 2 the X tiles are loaded with TMA multicast, and
+// TMA multicast loads here read only this GPU's memory, since on B200 a TMA multicast load from
+// another GPU's memory hung the GPU.  X is the caller's pointer: unless the driver says it is device
+// memory of the context's own GPU, the kernel runs unclustered and every CTA loads its own tiles.
+static int fwd_cluster(dml_ctx* ctx, const void* X) {
+  if (ctx->tc_cluster != 2) return 1;
+  cudaPointerAttributes at{};
+  if (cudaPointerGetAttributes(&at, X) != cudaSuccess) { cudaGetLastError(); return 1; }
+  return (at.type == cudaMemoryTypeDevice && at.device == ctx->device) ? 2 : 1;
+}
+
 template <int NC, int MODE, int CL>
 static int launch_tc_fwd_nc(dml_ctx* ctx, int grid, const CUtensorMap& mx, const CUtensorMap& mwh, const CUtensorMap& mwl,
                             const tc::TcFwdParams& p) {
@@ -421,7 +432,7 @@ static int run_score_tc(dml_ctx* ctx, int mode, const float* X, int64_t n, int d
   fp.cntPart = (int32_t*)part; fp.ssePart = (double*)part;
   fp.mask_hi = ctx->tc_mask_hi; fp.prefetch_jobs = 0; fp.T = T; fp.loss_shift = 0.f;
   const int ncb = fp.n_col_blocks;
-  const int clr = (ctx->tc_cluster == 2 && ncb >= 2 && (ncb % 2 == 0 || ncb >= 5)) ? 2 : 1;
+  const int clr = (fwd_cluster(ctx, X) == 2 && ncb >= 2 && (ncb % 2 == 0 || ncb >= 5)) ? 2 : 1;
   const int64_t jobs = cdiv(n, 128) * cdiv(ncb, clr);
   const int grid = clr * (int)std::min<int64_t>(jobs, ctx->n_sms / clr);
   const size_t esz = mode == FWD_SCORE_REG ? sizeof(double) : sizeof(int32_t);
@@ -524,7 +535,7 @@ struct EvalCtx {
       if (cudaMemGetInfo(&free_b, &total_b) == cudaSuccess)
         ctx->r_budget = std::max<size_t>((size_t)1 << 30, std::min<size_t>((size_t)16 << 30, (free_b + ctx->ws_bytes) / 3));
     }
-    cl = ctx->tc_cluster; tc_rps_max = ctx->tc_rps;
+    cl = fwd_cluster(ctx, X); tc_rps_max = ctx->tc_rps;
     ldw = (int)rup(d, 4); ldg = (int)rup(d + 1, 4); ldgr = d + 2;
     tiles_total = cdiv(n, BM); tile_n = (BN / T) * T;
     NC = pick_nc(S_max, T); if (NC == 0) NC = 160;
