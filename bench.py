@@ -75,7 +75,7 @@ def workload_name(a, n_cand_total):
 
 # ------------------------------------------------------------------------------------------
 class ClockSampler(threading.Thread):
-    """SM clock and throttle reasons DURING the timed region: NVML every 10 ms (the nvidia-smi query of
+    """SM clock and throttle reasons DURING the timed region: NVML every 20 ms (the nvidia-smi query of
     B200_PROFILING.md, one process per sample, is the fallback when the NVML binding is missing)."""
     REASONS = {0x4: "sw_power_cap", 0x8: "hw_slowdown", 0x20: "sw_thermal_slowdown", 0x40: "hw_thermal_slowdown"}
 
@@ -126,7 +126,7 @@ class ClockSampler(threading.Thread):
                 self.sample()
             except Exception:
                 pass
-            self.stop_ev.wait(0.01 if self.nv is not None else 0.2)
+            self.stop_ev.wait(0.02 if self.nv is not None else 0.2)
 
     def summary(self):
         self.stop_ev.set()

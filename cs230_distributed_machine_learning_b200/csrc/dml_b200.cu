@@ -54,6 +54,8 @@ struct dml_ctx {
   std::vector<cudaEvent_t> ev;  // pairs
   size_t ev_used = 0;
   cudaEvent_t ev_total[2] = {nullptr, nullptr};
+  cudaEvent_t ev_round[2] = {nullptr, nullptr};   // read-back of a round's list counts (the host runs one round ahead)
+  int round_ahead = 1;                             // DML_ROUND_AHEAD=0: wait for every round's counts before sizing the next
   float total_ms = 0.f, contraction_ms = 0.f; int contraction_launches = 0, total_launches = 0;
   size_t r_budget = (size_t)4 << 30;  // bytes of residual scratch per row chunk
   size_t first_pairs = 0; float first_ms = 0.f; int64_t first_cols = 0;   // round 0 when it ran once per row mask
@@ -175,6 +177,7 @@ extern "C" int dml_ctx_create(int device, void* stream, dml_ctx** out) {
   if (const char* e = getenv("DML_FOLD_SKIP")) ctx->fold_skip = atoi(e);
   if (const char* e = getenv("DML_GRAD_SKIP")) ctx->grad_skip = atoi(e);
   if (const char* e = getenv("DML_CROSS_BF16")) ctx->cross_bf16 = atoi(e);
+  if (const char* e = getenv("DML_ROUND_AHEAD")) ctx->round_ahead = atoi(e);
   if (const char* e = getenv("DML_TC_RPS")) { const int v = atoi(e); if (v >= 2048 && v <= 8192 && v % 128 == 0) ctx->tc_rps = v; }
   if (const char* e = getenv("DML_TC_CLUSTER")) ctx->tc_cluster = atoi(e) == 1 ? 1 : 2;
   CU(cudaSetDevice(device));
@@ -183,6 +186,8 @@ extern "C" int dml_ctx_create(int device, void* stream, dml_ctx** out) {
   for (auto& ev : ctx->ev) CU(cudaEventCreate(&ev));
   CU(cudaEventCreate(&ctx->ev_total[0]));
   CU(cudaEventCreate(&ctx->ev_total[1]));
+  CU(cudaEventCreateWithFlags(&ctx->ev_round[0], cudaEventDisableTiming));
+  CU(cudaEventCreateWithFlags(&ctx->ev_round[1], cudaEventDisableTiming));
   CU(cudaFuncSetAttribute(fwd_kernel<FWD_LOGREG>, cudaFuncAttributeMaxDynamicSharedMemorySize, kFwdSmemBytes));
   CU(cudaFuncSetAttribute(fwd_kernel<FWD_SCORE_CLS>, cudaFuncAttributeMaxDynamicSharedMemorySize, kFwdSmemBytes));
   CU(cudaFuncSetAttribute(fwd_kernel<FWD_SCORE_REG>, cudaFuncAttributeMaxDynamicSharedMemorySize, kFwdSmemBytes));
@@ -199,6 +204,8 @@ extern "C" void dml_ctx_destroy(dml_ctx* ctx) {
   if (ctx->h_scalar) cudaFreeHost(ctx->h_scalar);
   for (auto& ev : ctx->ev) cudaEventDestroy(ev);
   cudaEventDestroy(ctx->ev_total[0]); cudaEventDestroy(ctx->ev_total[1]);
+  if (ctx->ev_round[0]) cudaEventDestroy(ctx->ev_round[0]);
+  if (ctx->ev_round[1]) cudaEventDestroy(ctx->ev_round[1]);
   delete ctx;
 }
 
@@ -523,7 +530,8 @@ struct EvalCtx {
   float *Wt = nullptr, *bt = nullptr, *R = nullptr, *Whi = nullptr, *Wlo = nullptr, *Gpart = nullptr;
   double *lossPart = nullptr, *gbPart = nullptr, *Gred = nullptr; int32_t *sel = nullptr, *val = nullptr, *cntPart = nullptr;
   CUtensorMap mXf, mXf2, mXg, mWh, mWl, mR1;   // mR1: residuals, one 32-column chunk x 32 rows per box
-  const int* gstart = nullptr; int n_groups = 0; uint8_t* tile_fold = nullptr;   // fold-major column groups of the current list (device), or null   // mXf2: forward X box of a 2-CTA cluster member (64 rows)
+  const int* gstart = nullptr; int n_groups = 0; uint8_t* tile_fold = nullptr;
+  const int* n_list_dev = nullptr;   // device count of live list entries (n_slots passed to evaluate is then an upper bound)   // fold-major column groups of the current list (device), or null   // mXf2: forward X box of a 2-CTA cluster member (64 rows)
   unsigned long long* hist_local = nullptr;   // [512] label histogram of this rank's rows
   // the forward kernel sums (loss - shift) with shift = loss of the zero model: ln 2, or ln T (multinomial)
   float loss_shift() const { return T == 1 ? 0.693147182f : logf((float)T); }
@@ -604,6 +612,7 @@ struct EvalCtx {
         fp.R = R; fp.ldr = (int)ldr_max; fp.r_chunk_stride = chunk_rows * 32; fp.lossPart = lossPart; fp.gbPart = gbPart;
         fp.mask_hi = ctx->tc_mask_hi; fp.prefetch_jobs = ctx->tc_prefetch; fp.T = T; fp.loss_shift = loss_shift();
         fp.tile_fold = tile_fold; fp.gstart = gstart; fp.n_groups = n_groups; fp.grad_skips = ctx->grad_skip;
+        fp.n_list_dev = n_list_dev;
         // clusters of 2 share each X tile between two column blocks; with an odd number of blocks one
         // CTA of the last pair would run on empty columns, so small / odd cases run unclustered
         const int clr = (cl == 2 && ncb >= 2 && (ncb % 2 == 0 || ncb >= 5)) ? 2 : 1;
@@ -630,15 +639,15 @@ struct EvalCtx {
         const int64_t min_splits = cdiv((int64_t)ctx->n_sms, pair_blocks);            // 2 waves of n_sms / 2 pairs
         const int64_t rps_here = std::min<int64_t>(tc_rps_max, std::max<int64_t>(tc_rps, (rows / min_splits) / 128 * 128));
         tc::TcGradParams gp{r0, rows, rps_here, d, n_slots, Gpart, ldg, ctx->tc_mask_hi, ctx->tc_prefetch_grad,
-                            tile_fold, ctx->grad_skip ? gstart : nullptr, n_groups, ctx->cross_bf16};
+                            tile_fold, ctx->grad_skip ? gstart : nullptr, n_groups, ctx->cross_bf16, n_list_dev, T};
         const int splits_here = (int)cdiv(rows, rps_here);
         rc = launch_tc_grad2(ctx, dim3((unsigned)(2 * cdiv(cdiv(d, 128), 2)), (unsigned)cdiv(n_slots, tc::kGrad2NC), (unsigned)splits_here),
                              mXg, mR1, gp);
         if (rc) return rc;
-        ReduceParams rp{Gpart, ldg, splits_here, n_slots, d, T, d, nullptr, 0, 0, Gred, ldgr, ci > 0 ? 1 : 0};
+        ReduceParams rp{Gpart, ldg, splits_here, n_slots, d, T, d, nullptr, 0, 0, Gred, ldgr, ci > 0 ? 1 : 0, n_list_dev};
         reduce_grad_kernel<<<n_slots, 256, 0, st>>>(rp);
         tc::TcReduceParams tr{lossPart, gbPart, n_parts, n_slots, T, d, Gred, ldgr, ci > 0 ? 1 : 0,
-                              hist_local, sel, val, n, (double)loss_shift()};
+                              hist_local, sel, val, n, (double)loss_shift(), n_list_dev};
         tc::tc_reduce_tiles_kernel<<<(unsigned)cdiv(n_slots, 32), dim3(32, 32), 0, st>>>(tr);
       } else {
         const int ldr = (int)rup(n_slots, 4);
@@ -655,7 +664,7 @@ struct EvalCtx {
         const int splits_here = (int)cdiv(rows, rps);
         dim3 g2((unsigned)cdiv(n_slots, BM), (unsigned)nt, (unsigned)splits_here);
         grad_kernel<<<g2, NT, kGemmSmemBytes, st>>>(gp);
-        ReduceParams rp{Gpart, ldg, splits_here, n_slots, d, T, d + 1, lossPart, r0 / BM, cdiv(rows, BM), Gred, ldgr, ci > 0 ? 1 : 0};
+        ReduceParams rp{Gpart, ldg, splits_here, n_slots, d, T, d + 1, lossPart, r0 / BM, cdiv(rows, BM), Gred, ldgr, ci > 0 ? 1 : 0, nullptr};
         reduce_grad_kernel<<<n_slots, 256, 0, st>>>(rp);
         reduce_tiles_kernel<<<(unsigned)cdiv(n_slots / T, 32), dim3(32, 8), 0, st>>>(rp);
       }
@@ -810,6 +819,7 @@ extern "C" int dml_logreg_sweep(dml_ctx* ctx, const float* X, int64_t n, int d, 
     CU(cudaStreamSynchronize(st));
     n_total = 0; for (auto v : h) n_total += (int64_t)v;
   }
+  CU(cudaMemsetAsync(d_nactive, 0, 8 * sizeof(int), st));
   InitParams ip{F, n_folds, hold_id ? 1 : 0, fpc, n_total, d_hist, C, tol, fit_intercept, max_iter, d_st, d_active, d_nactive};
   init_fits_kernel<<<(unsigned)cdiv(F, 128), 128, 0, st>>>(ip);
   KCHECK();
@@ -861,15 +871,48 @@ extern "C" int dml_logreg_sweep(dml_ctx* ctx, const float* X, int64_t n, int d, 
     rc = evaluate_list();
     if (rc) return rc;
   }
-  while (true) {
-    lbfgs_update_kernel<<<n_list, 256, 0, st>>>(lp);
-    ctx->total_launches += 1;
-    int rc = next_list();
-    if (rc) return rc;
-    if (n_real == 0) break;
-    rc = evaluate_list();
-    if (rc) return rc;
-    if (rounds > 200000) return fail(ctx, DML_ERR_LIMIT, "dml_logreg_sweep: round cap hit");
+  if (!(ev.use_tc && ctx->round_ahead)) {
+    while (true) {
+      lbfgs_update_kernel<<<n_list, 256, 0, st>>>(lp);
+      ctx->total_launches += 1;
+      int rc = next_list();
+      if (rc) return rc;
+      if (n_real == 0) break;
+      rc = evaluate_list();
+      if (rc) return rc;
+      if (rounds > 200000) return fail(ctx, DML_ERR_LIMIT, "dml_logreg_sweep: round cap hit");
+    }
+  } else {
+    // The host runs one round ahead of the GPU.  List k+1 (made by the k-th compaction) is evaluated with grids
+    // sized from the length of list k -- the newest length whose read-back is certain to have arrived without
+    // waiting -- and the kernels take the true length from device memory (EvalCtx::n_list_dev).  A list never
+    // grows (compact_groups_kernel keeps a dense list dense), so that length is an upper bound.  The sweep ends
+    // one read-back late, after one round of kernels that find an empty list.
+    ev.n_list_dev = d_nactive;
+    ev.gstart = pad_to ? d_gstart : nullptr; ev.n_groups = n_folds;   // the device table says whether the list is grouped
+    int bound = n_list;
+    for (int k = 0;; ++k) {
+      lbfgs_update_kernel<<<bound, 256, 0, st>>>(lp);
+      compact_groups_kernel<<<1, 1024, 0, st>>>(cp);
+      write_trial_kernel<<<F_pad, 128, 0, st>>>(tp);
+      KCHECK();
+      int* h_next = ctx->h_scalar + 4 * ((k + 1) & 1);
+      CU(cudaMemcpyAsync(h_next, d_nactive + 4, 3 * sizeof(int), cudaMemcpyDeviceToHost, st));
+      CU(cudaEventRecord(ctx->ev_round[(k + 1) & 1], st));
+      ctx->total_launches += 3;
+      if (k >= 1) {            // counts of list k: the list whose evaluation was queued in the previous iteration
+        CU(cudaEventSynchronize(ctx->ev_round[k & 1]));
+        const int* h = ctx->h_scalar + 4 * (k & 1);
+        if (h[1] == 0) break;
+        ctx->slot_rounds += (int64_t)h[1] * T; ctx->rounds += 1; ++rounds;
+        bound = h[0];
+      }
+      int rc = ev.evaluate(ctx, bound * T);
+      if (rc) return rc;
+      if (ctx->comm) { rc = allreduce(ctx, ev.Gred, (size_t)bound * T * ev.ldgr, kNcclFloat64); if (rc) return rc; }
+      if (rounds > 200000) return fail(ctx, DML_ERR_LIMIT, "dml_logreg_sweep: round cap hit");
+    }
+    ev.n_list_dev = nullptr;
   }
   // results + score pass on every fit's held-out rows
   FinalParams fin{F, d, T, P, ev.ldw, d_st, d_x, coef_out, intercept_out, n_iter_out ? n_iter_out : d_i32,

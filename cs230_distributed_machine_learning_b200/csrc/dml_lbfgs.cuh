@@ -304,7 +304,8 @@ __global__ void compact_kernel(const FitState* st, int n_fits, int* active_fits,
 struct CompactParams {
   const FitState* st; int n_fits, fpc, pad_to;
   int* active_fits;
-  int* counts;        // [0] list length (n_active of the next round), [1] live fits, [2] 1 = fold-major padded
+  int* counts;        // [0] list length (n_active of the next round), [1] live fits, [2] 1 = fold-major padded,
+                      // [3] the list has been dense once (zeroed by the caller at the start of a sweep)
   int* gstart;        // [fpc + 1]
   int* counts_host;   // copy of counts[0..2] the host reads
 };
@@ -325,6 +326,10 @@ __global__ void compact_groups_kernel(const CompactParams p) {
       start[k + 1] = padded;
     }
     grouped = (p.pad_to > 0 && dense > 0 && padded * 8 <= ((dense + 31) / 32 * 32) * 9) ? 1 : 0;
+    // once dense, always dense: a list must never get longer from one round to the next (the host sizes
+    // a round's grids from the previous list's length); counts[3] remembers the switch for the sweep
+    if (p.counts[3]) grouped = 0;
+    if (!grouped) p.counts[3] = 1;
     base = 0;
     p.counts[0] = grouped ? padded : dense; p.counts[1] = dense; p.counts[2] = grouped;
     p.counts_host[0] = p.counts[0]; p.counts_host[1] = dense; p.counts_host[2] = grouped;
@@ -407,9 +412,11 @@ struct ReduceParams {
   const float* Gpart; int ldg; int splits; int n_slots; int d; int T; int jcount;  // jcount = d+1 (FFMA path: column d = sum r) or d
   const double* lossPart; int64_t tile0, n_tiles;
   double* Gred; int ldgr; int accumulate;
+  const int* n_list_dev;   // live columns = *n_list_dev * T when set (n_slots: upper bound and pitch)
 };
 __global__ void reduce_grad_kernel(const ReduceParams p) {
   const int slot = blockIdx.x;
+  if (p.n_list_dev && slot >= *p.n_list_dev * p.T) return;
   const int64_t stride = (int64_t)p.n_slots * p.ldg;
   for (int j = threadIdx.x; j < p.jcount; j += blockDim.x) {
     const float* src = p.Gpart + (int64_t)slot * p.ldg + j;

@@ -274,6 +274,10 @@ struct TcFwdParams {
   // fold k trains none of them: no MMAs, no epilogue math for that column range.  gstart == nullptr: off.
   const uint8_t* tile_fold; const int* gstart; int n_groups;
   int grad_skips;                        // the gradient kernel skips whole 64-column segments of a hole: nothing to store there
+  // n_slots is the host's upper bound (and the pitch of the partial-sum arrays); when n_list_dev is set the
+  // live columns are *n_list_dev * T <= n_slots, read on the device, so that the host can size a round's grids
+  // before it has read back the list length the previous round produced
+  const int* n_list_dev;
   float* R; int ldr;                     // fp32 residuals, [ldr / 32 column chunks][chunk rows][32]: a chunk's rows are contiguous,
   int64_t r_chunk_stride;                // so a gradient box (32 rows x 32 columns) is one 4 KB run; stride in floats
   double* lossPart; double* gbPart;      // [gridDim.x * 4][n_slots], zeroed by the caller
@@ -364,7 +368,9 @@ tc_fwd_kernel(const __grid_constant__ CUtensorMap mapX, const __grid_constant__ 
   // job list of this CTA: (column block, row tile); a cluster takes CL neighbouring row tiles
   const int64_t n_row_tiles = (p.rows + 127) / 128;
   const int crank = CL > 1 ? (int)cluster_ctarank() : 0;
-  const int64_t cb_groups = (p.n_col_blocks + CL - 1) / CL;      // column blocks are dealt out CL at a time
+  const int n_live = p.n_list_dev ? min(p.n_slots, *p.n_list_dev * p.T) : p.n_slots;
+  const int ncb_live = p.n_list_dev ? (n_live + NC - 1) / NC : p.n_col_blocks;
+  const int64_t cb_groups = (ncb_live + CL - 1) / CL;            // column blocks are dealt out CL at a time
   const int64_t n_jobs = n_row_tiles * cb_groups;                // jobs per cluster (column-block group major)
   const int64_t job0 = blockIdx.x / CL, job_step = gridDim.x / CL;
   auto job_cb = [&](int64_t job) { return (int)(job / n_row_tiles) * CL + crank; };  // may be >= n_col_blocks (no columns)
@@ -525,14 +531,14 @@ tc_fwd_kernel(const __grid_constant__ CUtensorMap mapX, const __grid_constant__ 
           flush(cur_cb);
           cur_cb = cb;
           asm volatile("bar.sync 1, %0;" ::"n"(128 * G) : "memory");
-          for (int c = et; c < NC; c += 128 * G) colBias[c] = slot0 + c < p.n_slots ? __ldg(p.bt + slot0 + c) : 0.f;
+          for (int c = et; c < NC; c += 128 * G) colBias[c] = slot0 + c < n_live ? __ldg(p.bt + slot0 + c) : 0.f;
           for (int e = et; e < (kMaxLabel + 2) * NCH; e += 128 * G) {
             const int v = e / NCH, ci = e % NCH;
             uint32_t bits = 0;
             for (int j = 0; j < 16; ++j) {
               const int slot = slot0 + ci * 16 + j;
               bool held = true;
-              if (slot < p.n_slots) {
+              if (slot < n_live) {
                 const int sel = __ldg(p.slot_sel + slot), val = __ldg(p.slot_val + slot) & 0xff;
                 held = sel < 0 || (v < kMaxLabel ? (sel == 0 && val == v) : (sel == 1 && val == v - kMaxLabel));   // mask -1: padding column
               }
@@ -568,7 +574,7 @@ tc_fwd_kernel(const __grid_constant__ CUtensorMap mapX, const __grid_constant__ 
           if (f == last_f) { tc_fence_before(); __syncwarp(); if (lane == 0) mbar_arrive(tempty + acc); }
           const uint32_t hb = valid ? (lds16u(held_f + (c0 >> 4) * 2) | lds16u(held_h + (c0 >> 4) * 2)) : 0xffffu;
           const bool held = (hb >> (c0 & 15)) & 1u;
-          const bool exists = slot0 + c0 < p.n_slots;
+          const bool exists = slot0 + c0 < n_live;
           float z[16];
           float m = -INFINITY; int am = 0;
 #pragma unroll
@@ -648,14 +654,14 @@ tc_fwd_kernel(const __grid_constant__ CUtensorMap mapX, const __grid_constant__ 
         flush(cur_cb);
         cur_cb = cb;
         asm volatile("bar.sync 1, %0;" ::"n"(128 * G) : "memory");   // everyone is done with the old column tables
-        for (int c = et; c < NC; c += 128 * G) colBias[c] = slot0 + c < p.n_slots ? __ldg(p.bt + slot0 + c) : 0.f;
+        for (int c = et; c < NC; c += 128 * G) colBias[c] = slot0 + c < n_live ? __ldg(p.bt + slot0 + c) : 0.f;
         for (int e = et; e < (kMaxLabel + 2) * NCH; e += 128 * G) {
           const int v = e / NCH, ci = e % NCH;
           uint32_t bits = 0;
           for (int j = 0; j < 16; ++j) {
             const int slot = slot0 + ci * 16 + j;
             bool held = true;                                        // a column that does not exist holds out every row
-            if (slot < p.n_slots) {
+            if (slot < n_live) {
               const int sel = __ldg(p.slot_sel + slot), val = __ldg(p.slot_val + slot) & 0xff;
               held = sel < 0 || (v < kMaxLabel ? (sel == 0 && val == v) : (sel == 1 && val == v - kMaxLabel));   // mask -1: padding column
             }
@@ -829,6 +835,7 @@ struct TcGradParams {
   // cross terms x_lo r_hi + x_hi r_lo as bf16 MMAs over a K-concatenated operand (128-column blocks only):
   // 8 MMAs per 32-row stage instead of 12; a cross term is 2^-11 of the product and bf16 keeps 8 bits of it
   int cross_bf16;
+  const int* n_list_dev; int list_T;   // live columns = *n_list_dev * list_T (see TcFwdParams); n_slots stays the pitch
 };
 
 // ---------------------------------------------------------------- gradient kernel, CTA pair
@@ -891,6 +898,9 @@ tc_grad2_kernel(const __grid_constant__ CUtensorMap mapX, const __grid_constant_
   const bool leader = rank == 0;
   constexpr uint32_t kTmemCols = 512, kTmemA = 2 * kGrad2NC;   // two accumulators, then 64 columns of A per slot
   static_assert(2 * kGrad2NC + TA * 64 <= 512, "tensor memory");
+  // a column block past the live columns (the host sized the grid from an upper bound): both CTAs of the
+  // pair share blockIdx.y and leave before anything is set up
+  if (p.n_list_dev && (int)blockIdx.y * kGrad2NC >= min(p.n_slots, *p.n_list_dev * p.list_T)) return;
 
   if (warp == kGrad2TmaWarp && lane == 0) {
     for (int s = 0; s < SX; ++s) { mbar_init(fullA + s, 1); mbar_init(emptyA + s, 4); }
@@ -902,7 +912,8 @@ tc_grad2_kernel(const __grid_constant__ CUtensorMap mapX, const __grid_constant_
   if (warp == kGrad2MmaWarp) tmem_alloc_pair(tmem_slot, kTmemCols);
   const int jb = blockIdx.x, cb = blockIdx.y, sp = blockIdx.z;
   const int col0 = cb * kGrad2NC;
-  const int ncols = min(kGrad2NC, ((p.n_slots - col0 + 63) / 64) * 64);   // columns of this pair's block
+  const int n_live = p.n_list_dev ? min(p.n_slots, *p.n_list_dev * p.list_T) : p.n_slots;
+  const int ncols = min(kGrad2NC, max(0, ((n_live - col0 + 63) / 64) * 64));   // columns of this pair's block
   const int nseg = ncols / 64;                                            // 64-column segments = chunks per CTA
   const int64_t kb = (int64_t)sp * p.rows_per_split;
   const int64_t ke = min(p.rows, kb + p.rows_per_split);
@@ -1130,7 +1141,7 @@ tc_grad2_kernel(const __grid_constant__ CUtensorMap mapX, const __grid_constant_
 #pragma unroll
     for (int c = 0; c < kGrad2NC; ++c) {
       const int slot = col0 + c;
-      if (c < ncols && slot < p.n_slots && j < p.d) out[(int64_t)slot * p.ldg + j] = sum[c];
+      if (c < ncols && slot < n_live && j < p.d) out[(int64_t)slot * p.ldg + j] = sum[c];
     }
   }
   tc_fence_before();
@@ -1448,19 +1459,21 @@ struct TcReduceParams {
   double* Gred; int ldgr; int accumulate;
   // the forward kernel sums (loss - ln 2): add ln 2 * (training rows of the column) back once
   const unsigned long long* hist_local; const int32_t* sel; const int32_t* val; int64_t n_local; double loss_shift;
+  const int* n_list_dev;   // live columns = *n_list_dev * T when set (n_slots: upper bound and pitch)
 };
 __global__ void tc_reduce_tiles_kernel(const TcReduceParams p) {   // block (32 slots, 32 partial lanes)
+  const int n_live = p.n_list_dev ? min(p.n_slots, *p.n_list_dev * p.T) : p.n_slots;
   __shared__ double sh[2][32][33];
   const int slot = blockIdx.x * 32 + threadIdx.x;
   double a = 0.0, b = 0.0;
-  if (slot < p.n_slots)
+  if (slot < n_live)
     for (int64_t t = threadIdx.y; t < p.n_parts; t += 32) {
       a += p.lossPart[t * p.n_slots + slot];
       b += p.gbPart[t * p.n_slots + slot];
     }
   sh[0][threadIdx.y][threadIdx.x] = a; sh[1][threadIdx.y][threadIdx.x] = b;
   __syncthreads();
-  if (threadIdx.y == 0 && slot < p.n_slots) {
+  if (threadIdx.y == 0 && slot < n_live) {
     double l = 0.0, g = 0.0;
     for (int i = 0; i < 32; ++i) { l += sh[0][i][threadIdx.x]; g += sh[1][i][threadIdx.x]; }   // fixed order
     double* q = p.Gred + (int64_t)slot * p.ldgr;
