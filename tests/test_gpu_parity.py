@@ -345,8 +345,9 @@ def test_queued_jobs_prefetch_their_dataset_and_match_blocking_runs():
         m.close()
 
 
-@pytest.mark.parametrize("env", [{"DML_FOLD_SKIP": "0"}, {"DML_GRAD_SKIP": "1"}, {"DML_FIRST_ROUND_ONCE": "0"}],
-                         ids=["no-fold-skip", "grad-skip", "full-round-0"])
+@pytest.mark.parametrize("env", [{"DML_FOLD_SKIP": "0"}, {"DML_GRAD_SKIP": "1"}, {"DML_FIRST_ROUND_ONCE": "0"},
+                                 {"DML_ROUND_AHEAD": "0"}],
+                         ids=["no-fold-skip", "grad-skip", "full-round-0", "no-round-ahead"])
 def test_skipping_knobs_do_not_change_results(solver, monkeypatch, env):
     """Fold-aware column skipping and the round-0 shortcut only remove work whose result is zero or
     known: every switch setting gives the same iterates (compared with the default context)."""
