@@ -146,29 +146,31 @@ class SweepSolver:
             np.asarray(C_vals, dtype=np.float64), np.broadcast_to(np.asarray(tol, dtype=np.float64), (n_cand,)),
             np.broadcast_to(np.asarray(fit_intercept, dtype=np.uint8), (n_cand,)),
             np.broadcast_to(np.asarray(max_iter, dtype=np.int32), (n_cand,)))
-        coef = torch.empty((F, T, ds.d), dtype=torch.float32, device=dev)
-        icpt = torch.empty((F, T), dtype=torch.float32, device=dev)
-        n_iter = torch.empty(F, dtype=torch.int32, device=dev)
-        status = torch.empty(F, dtype=torch.int32, device=dev)
-        nfev = torch.empty(F, dtype=torch.int32, device=dev)
-        correct = torch.empty(F, dtype=torch.int64, device=dev) if want_scores else None
-        n_test = torch.empty(F, dtype=torch.int64, device=dev) if want_scores else None
+        # every result lives in ONE device buffer (64-bit fields first), so a sweep ends with one
+        # device->host copy instead of seven
+        fields = [("correct", np.int64, (F,)), ("n_test", np.int64, (F,))] if want_scores else []
+        fields += [("coef", np.float32, (F, T, ds.d)), ("intercept", np.float32, (F, T)),
+                   ("n_iter", np.int32, (F,)), ("status", np.int32, (F,)), ("nfev", np.int32, (F,))]
+        offs, total = {}, 0
+        for name, dt, shape in fields:
+            offs[name] = total
+            total += (int(np.prod(shape)) * np.dtype(dt).itemsize + 15) // 16 * 16
+        buf = torch.empty(total, dtype=torch.uint8, device=dev)
+        base = buf.data_ptr()
+        ptr = lambda name: C.c_void_p(base + offs[name]) if name in offs else C.c_void_p(None)
         rounds = C.c_int32(0)
         rc = self.lib.dml_logreg_sweep(
             self.ctx.handle, _ptr(ds.X), ds.n, ds.d, ds.X.stride(0), _ptr(ds.y_cls), n_classes,
             _ptr(fold_d), n_folds, _ptr(hold_d), C_p, tol_p, fi_p, mi_p, n_cand,
-            _ptr(coef), _ptr(icpt), _ptr(n_iter), _ptr(status), _ptr(nfev), _ptr(correct), _ptr(n_test),
+            ptr("coef"), ptr("intercept"), ptr("n_iter"), ptr("status"), ptr("nfev"), ptr("correct"), ptr("n_test"),
             C.byref(rounds), int(use_tensor_cores))
         self.ctx.check(rc, "dml_logreg_sweep")
-        out = dict(coef=self.to_host(coef).reshape(n_cand, fpc, T, ds.d),
-                   intercept=self.to_host(icpt).reshape(n_cand, fpc, T),
-                   n_iter=self.to_host(n_iter).reshape(n_cand, fpc),
-                   status=self.to_host(status).reshape(n_cand, fpc),
-                   nfev=self.to_host(nfev).reshape(n_cand, fpc),
-                   rounds=int(rounds.value), timing=self.ctx.last_timing())
-        if want_scores:
-            out["correct"] = self.to_host(correct).reshape(n_cand, fpc)
-            out["n_test"] = self.to_host(n_test).reshape(n_cand, fpc)
+        host = self.to_host(buf)
+        out = dict(rounds=int(rounds.value), timing=self.ctx.last_timing())
+        for name, dt, shape in fields:
+            n_el = int(np.prod(shape))
+            a = host[offs[name]:offs[name] + n_el * np.dtype(dt).itemsize].view(dt)
+            out[name] = a.reshape((n_cand, fpc) + tuple(shape[1:]))
         return out
 
     def ridge_sweep(self, ds: DeviceDataset, fold_id, n_folds: int, alphas, fit_intercept, classifier: bool,
