@@ -199,6 +199,14 @@ def run_reference(a):
         return
     from cs230_distributed_machine_learning_b200 import make_dataset
     cores = os.cpu_count() or 1
+    # the reference gets every host thread: torchrun exports OMP_NUM_THREADS=1 to its ranks, which would pin
+    # this process's BLAS (already loaded) and the joblib workers' to one thread
+    os.environ.pop("OMP_NUM_THREADS", None)
+    try:
+        from threadpoolctl import threadpool_limits
+        threadpool_limits(limits=cores)
+    except Exception:
+        pass
     X, y = make_dataset("binary", a.rows, a.features, seed=SEED)
     Cs_all = np.logspace(-6, 2, a.candidates * a.gpus)
     # calibrate on one candidate (5 fits, BLAS on all cores), then size the step to ~8 s
