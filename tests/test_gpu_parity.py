@@ -354,8 +354,11 @@ def test_skipping_knobs_do_not_change_results(solver, monkeypatch, env):
     from cs230_distributed_machine_learning_b200.solver import SweepSolver
     X, y = make_dataset("binary", 60_000, 256, seed=12)
     fold = folds.stratified_labels(y, 5)
-    Cs = np.logspace(-5, 1, 70)           # 70 candidates: groups of 70 -> padded to 96, several column blocks
-    args = ([1e-4] * 70, [True] * 70, [100] * 70)
+    # 64 candidates: every fold's group of fits is 64 columns, so the default context runs the fold-major
+    # padded layout with column-range skipping (and falls back to the dense list as fits finish), while
+    # DML_FOLD_SKIP=0 runs the dense fit-major list throughout
+    Cs = np.logspace(-5, 1, 64)
+    args = ([1e-4] * 64, [True] * 64, [100] * 64)
     ds = solver.upload_dataset(X, y, classifier=True)
     want = solver.logreg_sweep(ds, fold, 5, Cs, *args)
     for k, v in env.items():
@@ -368,6 +371,13 @@ def test_skipping_knobs_do_not_change_results(solver, monkeypatch, env):
         other.close()
     assert (got["n_iter"] == want["n_iter"]).all() and (got["correct"] == want["correct"]).all()
     np.testing.assert_allclose(got["coef"], want["coef"], rtol=1e-6, atol=1e-9)
+    if "DML_FOLD_SKIP" in env:       # and the grouped layout itself against scikit-learn (float64), three fits
+        from sklearn.linear_model import LogisticRegression
+        X64 = X.astype(np.float64)
+        for i, f in ((5, 0), (33, 2), (60, 4)):
+            m = LogisticRegression(C=float(Cs[i])).fit(X64[fold != f], y[fold != f])
+            if m.n_iter_[0] == want["n_iter"][i, f]:
+                assert rel_err(want["coef"][i, f], m.coef_) < RTOL, (i, f)
 
 
 def test_medium_size_properties(solver):
