@@ -380,6 +380,29 @@ def test_skipping_knobs_do_not_change_results(solver, monkeypatch, env):
                 assert rel_err(want["coef"][i, f], m.coef_) < RTOL, (i, f)
 
 
+def test_grouped_layout_with_holdout_column_group(solver, monkeypatch):
+    """Fold-major layout when every candidate also has a hold-out fit: the hold-out group (rows chosen by
+    a permutation, never a whole tile) must not be skipped anywhere.  Compared with the dense layout."""
+    from cs230_distributed_machine_learning_b200.solver import SweepSolver
+    X, y = make_dataset("binary", 30_000, 128, seed=14)
+    fold = folds.stratified_labels(y, 3)
+    hold = folds.holdout_labels(len(y), 0.25, 7)
+    Cs = np.logspace(-4, 1, 32)
+    args = ([1e-4] * 32, [True] * 32, [100] * 32)
+    ds = solver.upload_dataset(X, y, classifier=True)
+    want = solver.logreg_sweep(ds, fold, 3, Cs, *args, hold_id=hold)
+    monkeypatch.setenv("DML_FOLD_SKIP", "0")
+    other = SweepSolver(0)
+    try:
+        got = other.logreg_sweep(other.upload_dataset(X, y, classifier=True), fold, 3, Cs, *args, hold_id=hold)
+    finally:
+        other.close()
+    assert want["coef"].shape == (32, 4, 1, 128)
+    assert (got["n_iter"] == want["n_iter"]).all() and (got["correct"] == want["correct"]).all()
+    assert (got["n_test"] == want["n_test"]).all() and want["n_test"][0, 3] == hold.sum()
+    np.testing.assert_allclose(got["coef"], want["coef"], rtol=1e-6, atol=1e-9)
+
+
 def test_medium_size_properties(solver):
     """Size-independent properties at a size the oracle cannot sweep in seconds (200k x 256, 16 C x 5 folds)."""
     X, y = make_dataset("binary", 200_000, 256, seed=2)
