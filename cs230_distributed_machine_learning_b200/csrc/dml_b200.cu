@@ -531,6 +531,7 @@ struct EvalCtx {
   double *lossPart = nullptr, *gbPart = nullptr, *Gred = nullptr; int32_t *sel = nullptr, *val = nullptr, *cntPart = nullptr;
   CUtensorMap mXf, mXf2, mXg, mWh, mWl, mR1;   // mR1: residuals, one 32-column chunk x 32 rows per box
   const int* gstart = nullptr; int n_groups = 0; uint8_t* tile_fold = nullptr;
+  int hold_group = 0;                // scoring: column group n_groups belongs to the hold-out fits
   const int* n_list_dev = nullptr;   // device count of live list entries (n_slots passed to evaluate is then an upper bound)   // fold-major column groups of the current list (device), or null   // mXf2: forward X box of a 2-CTA cluster member (64 rows)
   unsigned long long* hist_local = nullptr;   // [512] label histogram of this rank's rows
   // the forward kernel sums (loss - shift) with shift = loss of the zero model: ln 2, or ln T (multinomial)
@@ -689,6 +690,7 @@ struct EvalCtx {
       fp.n_slots = n_slots; fp.n_col_blocks = (int)cdiv(n_slots, NC); fp.bt = bt; fp.ycls = y;
       fp.fold_id = fold_id; fp.hold_id = hold_id; fp.slot_sel = sel; fp.slot_val = val;
       fp.cntPart = cntPart; fp.mask_hi = ctx->tc_mask_hi; fp.prefetch_jobs = ctx->tc_prefetch; fp.T = T; fp.loss_shift = 0.f;
+      fp.tile_fold = tile_fold; fp.gstart = gstart; fp.n_groups = n_groups; fp.hold_group = hold_group;
       const int ncb = fp.n_col_blocks;
       const int clr = (cl == 2 && ncb >= 2 && (ncb % 2 == 0 || ncb >= 5)) ? 2 : 1;
       const int64_t jobs = tiles_total * cdiv(ncb, clr);
@@ -723,6 +725,10 @@ __global__ void broadcast_first_round_kernel(double* __restrict__ Gred, const do
   Gred[i] = Gu[(int64_t)((fit % fpc) * T + (int)(slot % T)) * ldgr + j];
 }
 __global__ void set_int_kernel(int* p, int v) { *p = v; }
+// column groups of the fold-major score layout: group k = [k * npad, (k + 1) * npad)
+__global__ void score_groups_kernel(int* gstart, int n_groups, int npad) {
+  if ((int)threadIdx.x <= n_groups) gstart[threadIdx.x] = (int)threadIdx.x * npad;
+}
 // tile_fold[t] = fold id shared by all rows of the 128-row tile t, or 255 when the tile mixes folds
 __global__ void tile_fold_kernel(const int8_t* __restrict__ fold_id, int64_t n, uint8_t* __restrict__ tile_fold) {
   const int64_t t = (int64_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
@@ -914,19 +920,31 @@ extern "C" int dml_logreg_sweep(dml_ctx* ctx, const float* X, int64_t n, int d, 
     }
     ev.n_list_dev = nullptr;
   }
-  // results + score pass on every fit's held-out rows
+  // results + score pass on every fit's held-out rows.  With fold-major score columns (binary problems on
+  // the tcgen05 path, at least two folds) a row tile of fold k only multiplies and counts group k's columns
+  // and the hold-out group's: a fifth of the work at cv = 5.
+  const int npad = (pad_to && n_folds >= 2) ? (int)rup(n_cand, 32) : 0;
+  const int n_score = npad ? fpc * npad : F * T;
+  if (npad) {      // padding columns: zero weights, mask -1 (no row is scored on them)
+    CU(cudaMemsetAsync(ev.Wt, 0, sizeof(float) * (size_t)n_score * ev.ldw, st));
+    CU(cudaMemsetAsync(ev.bt, 0, sizeof(float) * (size_t)n_score, st));
+    CU(cudaMemsetAsync(ev.sel, 0xff, sizeof(int32_t) * (size_t)n_score, st));
+    CU(cudaMemsetAsync(ev.val, 0, sizeof(int32_t) * (size_t)n_score, st));
+    score_groups_kernel<<<1, 160, 0, st>>>(d_gstart, fpc, npad);
+  }
   FinalParams fin{F, d, T, P, ev.ldw, d_st, d_x, coef_out, intercept_out, n_iter_out ? n_iter_out : d_i32,
                   status_out ? status_out : d_i32 + F, nfev_out ? nfev_out : d_i32 + 2 * F,
-                  ev.Wt, ev.bt, ev.sel, ev.val};
+                  ev.Wt, ev.bt, ev.sel, ev.val, fpc, npad};
   finalize_kernel<<<F, 128, 0, st>>>(fin);
   KCHECK();
   ctx->total_launches += 1;
   if (correct_out || n_test_out) {
     int64_t n_parts = 0;
+    ev.gstart = npad ? d_gstart : nullptr; ev.n_groups = n_folds; ev.hold_group = hold_id ? 1 : 0;
+    int rc = ev.score_cls(ctx, n_score, &n_parts);
     ev.gstart = nullptr;
-    int rc = ev.score_cls(ctx, F * T, &n_parts);
     if (rc) return rc;
-    reduce_counts_kernel<<<F, 256, 0, st>>>(ev.cntPart, n_parts, F * T, T, d_correct);
+    reduce_counts_kernel<<<F, 256, 0, st>>>(ev.cntPart, n_parts, n_score, T, d_correct, fpc, npad);
     KCHECK();
     if (ctx->comm) { rc = allreduce(ctx, d_correct, F, kNcclInt64); if (rc) return rc; }
     if (correct_out) CU(cudaMemcpyAsync(correct_out, d_correct, sizeof(int64_t) * F, cudaMemcpyDeviceToDevice, st));

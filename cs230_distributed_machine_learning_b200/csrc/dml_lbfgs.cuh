@@ -500,16 +500,24 @@ struct FinalParams {
   const FitState* st; const double* x;
   float* coef; float* icpt; int32_t* n_iter; int32_t* status; int32_t* nfev;
   float* Wt; float* bt; int32_t* slot_sel; int32_t* slot_val;  // score-pass operands (all fits)
+  // score-pass column of fit (cand, k): fit-major cand * fpc + k when npad == 0, else fold-major
+  // k * npad + cand (npad = candidates rounded up to 32; the caller presets the padding columns), so that
+  // a row tile of fold k only needs the column range of group k
+  int fpc, npad;
 };
+__device__ __forceinline__ int score_slot(int fit, int fpc, int npad) {
+  return npad ? (fit % fpc) * npad + fit / fpc : fit;
+}
 __global__ void finalize_kernel(const FinalParams p) {
   const int fit = blockIdx.x, D1 = p.d + 1;
   const FitState& s = p.st[fit];
   const double* x = p.x + (int64_t)fit * p.P;
   for (int idx = threadIdx.x; idx < p.P; idx += blockDim.x) {
     const int t = idx / D1, j = idx - t * D1, slot = fit * p.T + t;
+    const int ss = score_slot(fit, p.fpc, p.npad) * p.T + t;
     const float v = (float)x[idx];   // coef_ is cast to X.dtype (_logistic.py:702-712)
-    if (j < p.d) { p.coef[(int64_t)slot * p.d + j] = v; p.Wt[(int64_t)slot * p.ldw + j] = v; }
-    else { p.icpt[slot] = v; p.bt[slot] = v; p.slot_sel[slot] = s.mask_sel; p.slot_val[slot] = s.mask_val; }
+    if (j < p.d) { p.coef[(int64_t)slot * p.d + j] = v; p.Wt[(int64_t)ss * p.ldw + j] = v; }
+    else { p.icpt[slot] = v; p.bt[ss] = v; p.slot_sel[ss] = s.mask_sel; p.slot_val[ss] = s.mask_val; }
   }
   if (threadIdx.x == 0) {
     p.n_iter[fit] = min(s.nit, s.max_iter);   // sklearn/utils/optimize.py:405-460
@@ -519,11 +527,13 @@ __global__ void finalize_kernel(const FinalParams p) {
 }
 
 // score partials -> totals
-__global__ void reduce_counts_kernel(const int32_t* cntPart, int64_t n_tiles, int n_slots, int T, long long* correct) {
+__global__ void reduce_counts_kernel(const int32_t* cntPart, int64_t n_tiles, int n_slots, int T, long long* correct,
+                                     int fpc = 1, int npad = 0) {
   __shared__ long long sh[256];
   const int fit = blockIdx.x;
+  const int col = score_slot(fit, fpc, npad) * T;
   long long a = 0;
-  for (int64_t t = threadIdx.x; t < n_tiles; t += blockDim.x) a += cntPart[t * n_slots + fit * T];
+  for (int64_t t = threadIdx.x; t < n_tiles; t += blockDim.x) a += cntPart[t * n_slots + col];
   sh[threadIdx.x] = a;
   __syncthreads();
   for (int o = blockDim.x / 2; o > 0; o >>= 1) { if (threadIdx.x < o) sh[threadIdx.x] += sh[threadIdx.x + o]; __syncthreads(); }

@@ -273,6 +273,7 @@ struct TcFwdParams {
   // tile t (255: mixed); gstart[k] .. gstart[k+1] = the columns of fold k's fits (multiples of 32).  A tile of
   // fold k trains none of them: no MMAs, no epilogue math for that column range.  gstart == nullptr: off.
   const uint8_t* tile_fold; const int* gstart; int n_groups;
+  int hold_group;                        // scoring mode: group n_groups holds the hold-out fits (scored on rows of every tile)
   int grad_skips;                        // the gradient kernel skips whole 64-column segments of a hole: nothing to store there
   // n_slots is the host's upper bound (and the pitch of the partial-sum arrays); when n_list_dev is set the
   // live columns are *n_list_dev * T <= n_slots, read on the device, so that the host can size a round's grids
@@ -357,8 +358,8 @@ tc_fwd_kernel(const __grid_constant__ CUtensorMap mapX, const __grid_constant__ 
     fence_barrier_init();
   }
   if (warp == kFwdMmaWarp) tmem_alloc(tmem_slot, kTmemCols);
-  const bool holes = MODE == FWD_LOGREG && p.gstart != nullptr;
-  if (holes) for (int i = threadIdx.x; i <= p.n_groups; i += blockDim.x) gsTab[i] = p.gstart[i];
+  const bool holes = (MODE == FWD_LOGREG || MODE == FWD_SCORE_CLS) && p.gstart != nullptr;
+  if (holes) for (int i = threadIdx.x; i <= p.n_groups + (MODE == FWD_SCORE_CLS ? p.hold_group : 0); i += blockDim.x) gsTab[i] = p.gstart[i];
   tc_fence_before();
   __syncthreads();
   if (CL > 1) cluster_sync_all();           // peer barriers are initialised before anyone signals them
@@ -378,11 +379,25 @@ tc_fwd_kernel(const __grid_constant__ CUtensorMap mapX, const __grid_constant__ 
   // block-local column range [sa, sb) that a tile whose rows all sit in fold k does not train
   // (empty: sa == sb == 0); k = 255: the tile mixes folds
   auto tile_k = [&](int64_t rt) -> int { return holes ? (int)p.tile_fold[p.row0 / 128 + rt] : 255; };
-  auto hole_of = [&](int cb, int k, int& sa, int& sb) {
-    sa = 0; sb = 0;
+  // The two block-local column ranges [a0, b0) and [a1, b1) a tile needs when all its rows sit in fold k:
+  // training mode: everything but fold k's group (the rows train none of its columns);
+  // scoring mode : fold k's group (only its fits are scored on these rows) and the hold-out group.
+  // Any other tile, or a list without groups: [0, 0) and [0, NC).
+  auto ranges_of = [&](int cb, int k, int& a0, int& b0, int& a1, int& b1) {
+    a0 = 0; b0 = 0; a1 = 0; b1 = NC;
     if (!holes || k >= p.n_groups) return;
-    const int lo = max(gsTab[k], cb * NC) - cb * NC, hi = min(gsTab[k + 1], cb * NC + NC) - cb * NC;
-    if (hi > lo) { sa = lo; sb = hi; }
+    auto clip = [&](int g, int& lo, int& hi) {
+      lo = max(gsTab[g], cb * NC) - cb * NC; hi = min(gsTab[g + 1], cb * NC + NC) - cb * NC;
+      if (hi <= lo) { lo = 0; hi = 0; }
+    };
+    int lo, hi;
+    clip(k, lo, hi);
+    if (MODE == FWD_LOGREG) {
+      if (hi > lo) { b0 = lo; a1 = hi; }
+    } else {
+      a0 = lo; b0 = hi; a1 = 0; b1 = 0;
+      if (p.hold_group) clip(p.n_groups, a1, b1);
+    }
   };
 
   if (warp == kFwdTmaWarp) {
@@ -417,11 +432,10 @@ tc_fwd_kernel(const __grid_constant__ CUtensorMap mapX, const __grid_constant__ 
     int k_next = job0 < n_jobs ? tile_k(job_rt(job0)) : 255;
     for (int64_t job = job0; job < n_jobs; job += job_step, ++tile) {
       const int acc = tile & 1; const uint32_t aph = (tile >> 1) & 1;
-      int sa, sb;
-      hole_of(job_cb(job), k_next, sa, sb);
+      int a0, b0, a1, b1;
+      ranges_of(job_cb(job), k_next, a0, b0, a1, b1);
       if (job + job_step < n_jobs) k_next = tile_k(job_rt(job + job_step));   // in flight while this tile's MMAs are issued
-      // column ranges [0, sa) and [sb, NC); without a hole the first one is empty
-      const uint32_t idesc_a = instr_desc_tf32(128, sa, 0, 0), idesc_b = instr_desc_tf32(128, NC - sb, 0, 0);
+      const uint32_t idesc_a = instr_desc_tf32(128, b0 - a0, 0, 0), idesc_b = instr_desc_tf32(128, b1 - a1, 0, 0);
       mbar_wait(tempty + acc, aph ^ 1);
       tc_fence_after();
       const uint32_t tacc = tmem_base + acc * NC;
@@ -433,23 +447,24 @@ tc_fwd_kernel(const __grid_constant__ CUtensorMap mapX, const __grid_constant__ 
         if (elect_one()) {
           const uint32_t b_hi = smem_u32(smem + s * L::kStage) + L::kA, b_lo = b_hi + L::kB;
           const uint32_t ta_hi = tmem_base + kTmemA + s * 64, ta_lo = ta_hi + 32;
-          if (sa > 0) {
-#pragma unroll
-            for (int k = 0; k < 4; ++k) {
-              const uint64_t dbh = smem_desc(b_hi + k * 32, 16, 1024), dbl = smem_desc(b_lo + k * 32, 16, 1024);
-              umma_tf32_ts(tacc, ta_lo + k * 8, dbh, idesc_a, (c | k) != 0);   // small terms first
-              umma_tf32_ts(tacc, ta_hi + k * 8, dbl, idesc_a, 1);
-              umma_tf32_ts(tacc, ta_hi + k * 8, dbh, idesc_a, 1);
-            }
-          }
-          if (sb < NC) {
-            const uint32_t off = (uint32_t)sb * 128;       // W rows are 128 B apart (8-row swizzle atoms: sb % 8 == 0)
+          if (b0 > a0) {
+            const uint32_t off = (uint32_t)a0 * 128;       // W rows are 128 B apart (8-row swizzle atoms: a0 % 8 == 0)
 #pragma unroll
             for (int k = 0; k < 4; ++k) {
               const uint64_t dbh = smem_desc(b_hi + off + k * 32, 16, 1024), dbl = smem_desc(b_lo + off + k * 32, 16, 1024);
-              umma_tf32_ts(tacc + sb, ta_lo + k * 8, dbh, idesc_b, (c | k) != 0);
-              umma_tf32_ts(tacc + sb, ta_hi + k * 8, dbl, idesc_b, 1);
-              umma_tf32_ts(tacc + sb, ta_hi + k * 8, dbh, idesc_b, 1);
+              umma_tf32_ts(tacc + a0, ta_lo + k * 8, dbh, idesc_a, (c | k) != 0);   // small terms first
+              umma_tf32_ts(tacc + a0, ta_hi + k * 8, dbl, idesc_a, 1);
+              umma_tf32_ts(tacc + a0, ta_hi + k * 8, dbh, idesc_a, 1);
+            }
+          }
+          if (b1 > a1) {
+            const uint32_t off = (uint32_t)a1 * 128;
+#pragma unroll
+            for (int k = 0; k < 4; ++k) {
+              const uint64_t dbh = smem_desc(b_hi + off + k * 32, 16, 1024), dbl = smem_desc(b_lo + off + k * 32, 16, 1024);
+              umma_tf32_ts(tacc + a1, ta_lo + k * 8, dbh, idesc_b, (c | k) != 0);
+              umma_tf32_ts(tacc + a1, ta_hi + k * 8, dbl, idesc_b, 1);
+              umma_tf32_ts(tacc + a1, ta_hi + k * 8, dbh, idesc_b, 1);
             }
           }
           if (CL == 1) umma_commit(empty + s);
@@ -684,18 +699,25 @@ tc_fwd_kernel(const __grid_constant__ CUtensorMap mapX, const __grid_constant__ 
       const float yy = (float)yv;
       const uint32_t held_f = held_s + fold_v * NCH * 2, held_h = held_s + (kMaxLabel + hold_v) * NCH * 2;
       const int acc = tile & 1; const uint32_t aph = (tile >> 1) & 1;
-      // bit ci of hole_mask: no row of this tile trains the columns of chunk ci (no math, residual zero);
-      // bit ci + 16: the gradient kernel skips the chunk's 64-column segment as well, so nothing is stored
+      // Training mode: bit ci of hole_mask = no row of this tile trains the columns of chunk ci (no math, residual
+      // zero); bit ci + 16 = the gradient kernel skips the chunk's 64-column segment as well, so nothing is stored.
+      // Scoring mode: bit ci = none of the chunk's columns is scored on this tile's rows (nothing to count).
       uint32_t hole_mask = 0;
       {
-        int sa, sb;
-        hole_of(cb, kf, sa, sb);
+        int a0, b0, a1, b1;
+        ranges_of(cb, kf, a0, b0, a1, b1);
 #pragma unroll
-        for (int ci = 0; ci < NCH; ++ci)
-          if (ci * 16 >= sa && ci * 16 + 16 <= sb) {
-            const int seg = ((slot0 + ci * 16) & ~63) - slot0;       // block-local start of the 64-column segment
-            hole_mask |= (p.grad_skips && seg >= sa && seg + 64 <= sb) ? (0x10001u << ci) : (1u << ci);
+        for (int ci = 0; ci < NCH; ++ci) {
+          const int c = ci * 16;
+          if (MODE == FWD_LOGREG) {
+            if (c >= b0 && c + 16 <= a1) {          // inside the hole [b0, a1)
+              const int seg = ((slot0 + c) & ~63) - slot0;       // block-local start of the 64-column segment
+              hole_mask |= (p.grad_skips && seg >= b0 && seg + 64 <= a1) ? (0x10001u << ci) : (1u << ci);
+            }
+          } else if (MODE == FWD_SCORE_CLS) {
+            if (!((c >= a0 && c + 16 <= b0) || (c >= a1 && c + 16 <= b1))) hole_mask |= 1u << ci;
           }
+        }
       }
       mbar_wait(tfull + acc, aph);
       tc_fence_after();
@@ -706,7 +728,7 @@ tc_fwd_kernel(const __grid_constant__ CUtensorMap mapX, const __grid_constant__ 
         const int ci = G * i + grp;
         if (ci >= NCH) break;
         const int c0 = ci * 16;
-        const bool in_hole = MODE == FWD_LOGREG && ((hole_mask >> ci) & 1u);   // residuals are zero there; the MMAs
+        const bool in_hole = (MODE == FWD_LOGREG || MODE == FWD_SCORE_CLS) && ((hole_mask >> ci) & 1u);   // the MMAs
         uint32_t v[16];                                                         // never wrote these TMEM columns
         if (!in_hole) {
           tmem_ld16(tacc + c0, v);
@@ -718,6 +740,7 @@ tc_fwd_kernel(const __grid_constant__ CUtensorMap mapX, const __grid_constant__ 
           if (lane == 0) mbar_arrive(tempty + acc);
         }
         if (MODE == FWD_LOGREG && ((hole_mask >> (ci + 16)) & 1u)) continue;
+        if (MODE == FWD_SCORE_CLS && ((hole_mask >> ci) & 1u)) continue;
         // bit j set: column c0 + j does not train on (LOGREG) / is scored on (SCORE) this row
         const uint32_t heldbits = valid ? (lds16u(held_f + ci * 2) | lds16u(held_h + ci * 2)) : 0xffffu;
         if (MODE == FWD_LOGREG) {
