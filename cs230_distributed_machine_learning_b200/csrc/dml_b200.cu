@@ -58,6 +58,7 @@ struct dml_ctx {
   int round_ahead = 1;                             // DML_ROUND_AHEAD=0: wait for every round's counts before sizing the next
   float total_ms = 0.f, contraction_ms = 0.f; int contraction_launches = 0, total_launches = 0;
   size_t r_budget = (size_t)4 << 30;  // bytes of residual scratch per row chunk
+  bool r_budget_known = false;
   size_t first_pairs = 0; float first_ms = 0.f; int64_t first_cols = 0;   // round 0 when it ran once per row mask
   // the gradient kernel can skip 64-column segments too (DML_GRAD_SKIP=1).  Measured on config 2: per launch
   // 0.85 ms against 0.76 ms (N = 64 MMAs cost more than half an N = 128 one) but a third less HBM traffic and
@@ -539,10 +540,13 @@ struct EvalCtx {
 
   void plan(dml_ctx* ctx, int64_t n_groups_max) {
     ctx_sms = ctx->n_sms;
-    {  // residual scratch per row chunk: a third of what is free (arena included), at most 16 GB
+    if (!ctx->r_budget_known) {
+      // residual scratch per row chunk: a third of what is free (arena included), at most 16 GB.  Asked once
+      // per context: cudaMemGetInfo goes to the kernel driver and takes milliseconds on some hosts.
       size_t free_b = 0, total_b = 0;
       if (cudaMemGetInfo(&free_b, &total_b) == cudaSuccess)
         ctx->r_budget = std::max<size_t>((size_t)1 << 30, std::min<size_t>((size_t)16 << 30, (free_b + ctx->ws_bytes) / 3));
+      ctx->r_budget_known = true;
     }
     cl = fwd_cluster(ctx, X); tc_rps_max = ctx->tc_rps;
     ldw = (int)rup(d, 4); ldg = (int)rup(d + 1, 4); ldgr = d + 2;
