@@ -422,7 +422,8 @@ static int run_score(dml_ctx* ctx, int mode, const float* X, int64_t n, int d, i
 static int run_score_tc(dml_ctx* ctx, int mode, const float* X, int64_t n, int d, int64_t ldx,
                         const int32_t* ycls, const float* yreg, const int8_t* fold_id, const int8_t* hold_id,
                         const float* Wt, int ldw, const float* bt, const int32_t* sel, const int32_t* val,
-                        int n_slots, int T, float* Whi, float* Wlo, void* part, int64_t* n_parts) {
+                        int n_slots, int T, float* Whi, float* Wlo, void* part, int64_t* n_parts,
+                        const uint8_t* tile_fold = nullptr, const int* gstart = nullptr, int n_groups = 0, int hold_group = 0) {
   cudaStream_t st = ctx->stream;
   const int NC = pick_nc(n_slots, T);
   if (NC == 0) return fail(ctx, DML_ERR_ARG, "run_score_tc: no column-block width for T=%d", T);
@@ -439,6 +440,7 @@ static int run_score_tc(dml_ctx* ctx, int mode, const float* X, int64_t n, int d
   fp.fold_id = fold_id; fp.hold_id = hold_id; fp.slot_sel = sel; fp.slot_val = val;
   fp.cntPart = (int32_t*)part; fp.ssePart = (double*)part;
   fp.mask_hi = ctx->tc_mask_hi; fp.prefetch_jobs = 0; fp.T = T; fp.loss_shift = 0.f;
+  fp.tile_fold = tile_fold; fp.gstart = gstart; fp.n_groups = n_groups; fp.hold_group = hold_group;
   const int ncb = fp.n_col_blocks;
   const int clr = (fwd_cluster(ctx, X) == 2 && ncb >= 2 && (ncb % 2 == 0 || ncb >= 5)) ? 2 : 1;
   const int64_t jobs = cdiv(n, 128) * cdiv(ncb, clr);
@@ -457,12 +459,15 @@ static int run_score_tc(dml_ctx* ctx, int mode, const float* X, int64_t n, int d
   *n_parts = (int64_t)grid * 4;
   return DML_OK;
 }
-__global__ void reduce_sse_parts_kernel(const double* part, int64_t n_parts, int n_slots, double* sse) {
-  const int slot = blockIdx.x * blockDim.x + threadIdx.x;
-  if (slot >= n_slots) return;
+// sse[fit] = sum of the partials of the fit's score column (n_cols columns per partial row; see score_slot)
+__global__ void reduce_sse_parts_kernel(const double* part, int64_t n_parts, int n_cols, double* sse,
+                                        int n_fits, int fpc, int npad) {
+  const int fit = blockIdx.x * blockDim.x + threadIdx.x;
+  if (fit >= n_fits) return;
+  const int col = score_slot(fit, fpc, npad);
   double a = 0.0;
-  for (int64_t t = 0; t < n_parts; ++t) a += part[t * n_slots + slot];
-  sse[slot] = a;
+  for (int64_t t = 0; t < n_parts; ++t) a += part[t * n_cols + col];
+  sse[fit] = a;
 }
 
 // Forward pass of round 0 without a GEMM (binary problems, at most 32 columns): every coefficient is zero,
@@ -1070,6 +1075,10 @@ extern "C" int dml_ridge_sweep(dml_ctx* ctx, const float* X, int64_t n, int d, i
   double* d_part_tc = nullptr;
   // scoring on the tensor cores needs a column-block width that holds whole fits
   const bool score_tc = use_tc && (T == 1 || (T >= 3 && pick_nc(1, T) != 0));
+  // fold-major score columns (see dml_logreg_sweep): group k = the fits that hold out fold k, padded to 32
+  const int npad = (score_tc && T == 1 && ctx->fold_skip && n_folds >= 2) ? (int)rup(n_cand, 32) : 0;
+  const int64_t S_score = npad ? (int64_t)fpc * npad : S_all;
+  uint8_t* d_tfold = nullptr; int* d_gs = nullptr;
   double *d_Mfold, *d_Mtot, *d_A, *d_AT, *d_B, *d_mu, *d_stats, *d_sse; int32_t *d_sel, *d_val, *d_info; long long* d_cnt;
   for (int pass = 0; pass < 2; ++pass) {
     Arena a(pass ? ctx->ws : nullptr);
@@ -1082,14 +1091,15 @@ extern "C" int dml_ridge_sweep(dml_ctx* ctx, const float* X, int64_t n, int d, i
     d_AT = a.take<double>((size_t)cand_chunk * fpc * d * d);
     d_B = a.take<double>((size_t)cand_chunk * fpc * T * d);
     d_mu = a.take<double>((size_t)cand_chunk * fpc * (d + T));
-    d_Wt = a.take<float>((size_t)S_all * ldw); d_bt = a.take<float>(S_all);
-    d_sel = a.take<int32_t>(S_all); d_val = a.take<int32_t>(S_all);
+    d_Wt = a.take<float>((size_t)S_score * ldw); d_bt = a.take<float>(S_score);
+    d_sel = a.take<int32_t>(S_score); d_val = a.take<int32_t>(S_score);
+    d_tfold = a.take<uint8_t>((size_t)cdiv(n, 128) + 16); d_gs = a.take<int>(fpc + 1);
     d_info = a.take<int32_t>(F); d_cnt = a.take<long long>(F);
     d_stats = a.take<double>(4 * 256); d_sse = a.take<double>(S_all);
     d_part = a.take<float>((size_t)tiles_total * S_all);
     if (score_tc) {
-      d_Whi = a.take<float>((size_t)S_all * ldw); d_Wlo = a.take<float>((size_t)S_all * ldw);
-      d_part_tc = a.take<double>((size_t)ctx->n_sms * 4 * S_all);
+      d_Whi = a.take<float>((size_t)S_score * ldw); d_Wlo = a.take<float>((size_t)S_score * ldw);
+      d_part_tc = a.take<double>((size_t)ctx->n_sms * 4 * S_score);
     }
     if (!pass) { int rc = ensure_ws(ctx, a.off + 256); if (rc) return rc; }
   }
@@ -1159,6 +1169,15 @@ extern "C" int dml_ridge_sweep(dml_ctx* ctx, const float* X, int64_t n, int d, i
     return fail(ctx, DML_ERR_ARG, "dml_ridge_sweep: n_folds must be >= 2");
   }
   KCHECK();
+  if (npad) {      // score layout: padding columns (zero weights, mask -1), group starts, fold id of every row tile
+    CU(cudaMemsetAsync(d_Wt, 0, sizeof(float) * (size_t)S_score * ldw, st));
+    CU(cudaMemsetAsync(d_bt, 0, sizeof(float) * (size_t)S_score, st));
+    CU(cudaMemsetAsync(d_sel, 0xff, sizeof(int32_t) * (size_t)S_score, st));
+    CU(cudaMemsetAsync(d_val, 0, sizeof(int32_t) * (size_t)S_score, st));
+    score_groups_kernel<<<1, 160, 0, st>>>(d_gs, fpc, npad);
+    tile_fold_kernel<<<(unsigned)cdiv(cdiv(n, 128), 8), 256, 0, st>>>(fold_id, n, d_tfold);
+    KCHECK();
+  }
   // ---- batched solves ----
   for (int c0 = 0; c0 < n_cand; c0 += cand_chunk) {
     const int nc = std::min(cand_chunk, n_cand - c0), nsys = nc * fpc;
@@ -1177,7 +1196,7 @@ extern "C" int dml_ridge_sweep(dml_ctx* ctx, const float* X, int64_t n, int d, i
     } else {
       ridge_cholesky_kernel<<<nsys, 512, d * sizeof(double), st>>>(d_A, d_B, d, T, d_info + c0 * fpc);
     }
-    RidgeOutParams op{d, T, n_folds, has_hold, c0, ldw, d_B, d_mu, coef_out, intercept_out, d_Wt, d_bt, d_sel, d_val};
+    RidgeOutParams op{d, T, n_folds, has_hold, c0, ldw, d_B, d_mu, coef_out, intercept_out, d_Wt, d_bt, d_sel, d_val, npad};
     ridge_output_kernel<<<dim3(nsys, T), 128, 0, st>>>(op);
     KCHECK();
     ctx->total_launches += 3;
@@ -1187,7 +1206,8 @@ extern "C" int dml_ridge_sweep(dml_ctx* ctx, const float* X, int64_t n, int d, i
   int rc; int64_t n_parts = tiles_total; const void* parts = d_part;
   if (score_tc) {
     rc = run_score_tc(ctx, is_classifier ? FWD_SCORE_CLS : FWD_SCORE_REG, X, n, d, ldx, y_cls, y_reg, fold_id, hold_id,
-                      d_Wt, ldw, d_bt, d_sel, d_val, (int)S_all, T, d_Whi, d_Wlo, d_part_tc, &n_parts);
+                      d_Wt, ldw, d_bt, d_sel, d_val, (int)S_score, T, d_Whi, d_Wlo, d_part_tc, &n_parts,
+                      npad ? d_tfold : nullptr, npad ? d_gs : nullptr, n_folds, has_hold);
     parts = d_part_tc;
   } else {
     rc = run_score(ctx, is_classifier ? FWD_SCORE_CLS : FWD_SCORE_REG, X, n, d, ldx, y_cls, y_reg, fold_id, hold_id,
@@ -1195,12 +1215,12 @@ extern "C" int dml_ridge_sweep(dml_ctx* ctx, const float* X, int64_t n, int d, i
   }
   if (rc) return rc;
   if (is_classifier) {
-    reduce_counts_kernel<<<F, 256, 0, st>>>((const int32_t*)parts, n_parts, (int)S_all, T, d_cnt);
+    reduce_counts_kernel<<<F, 256, 0, st>>>((const int32_t*)parts, n_parts, (int)(score_tc ? S_score : S_all), T, d_cnt, fpc, npad);
     KCHECK();
     if (ctx->comm) { rc = allreduce(ctx, d_cnt, F, kNcclInt64); if (rc) return rc; }
     if (correct_out) CU(cudaMemcpyAsync(correct_out, d_cnt, sizeof(int64_t) * F, cudaMemcpyDeviceToDevice, st));
   } else {
-    if (score_tc) reduce_sse_parts_kernel<<<(unsigned)cdiv(S_all, 128), 128, 0, st>>>((const double*)parts, n_parts, (int)S_all, d_sse);
+    if (score_tc) reduce_sse_parts_kernel<<<(unsigned)cdiv(S_all, 128), 128, 0, st>>>((const double*)parts, n_parts, (int)S_score, d_sse, (int)S_all, fpc, npad);
     else reduce_sse_kernel<<<(unsigned)S_all, 256, 0, st>>>((const float*)d_part, tiles_total, (int)S_all, d_sse);
     KCHECK();
     if (ctx->comm) { rc = allreduce(ctx, d_sse, S_all, kNcclFloat64); if (rc) return rc; }

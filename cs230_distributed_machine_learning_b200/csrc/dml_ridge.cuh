@@ -226,27 +226,29 @@ struct RidgeOutParams {
   const double* B; const double* mu;
   float* coef; float* icpt;        // [n_cand][fits_per_cand][T][d], [..][T]
   float* Wt; float* bt; int32_t* slot_sel; int32_t* slot_val;   // all fits
+  int npad;                        // score-pass column of a fit: see score_slot (0 = fit-major)
 };
 __global__ void ridge_output_kernel(const RidgeOutParams p) {
   __shared__ double red[33];
   const int fits_per_cand = p.n_folds + p.has_hold;
   const int sys = blockIdx.x, t = blockIdx.y, k = sys % fits_per_cand;
   const int fit = p.cand0 * fits_per_cand + sys, slot = fit * p.T + t;
+  const int ss = score_slot(fit, fits_per_cand, p.npad) * p.T + t;
   const double* w = p.B + ((int64_t)sys * p.T + t) * p.d;
   const double* mu = p.mu + (int64_t)sys * (p.d + p.T);
   double dot = 0.0;
   for (int j = threadIdx.x; j < p.d; j += blockDim.x) {
     const float v = (float)w[j];   // coef_ keeps X.dtype
     p.coef[(int64_t)slot * p.d + j] = v;
-    p.Wt[(int64_t)slot * p.ldw + j] = v;
+    p.Wt[(int64_t)ss * p.ldw + j] = v;
     dot += mu[j] * w[j];
   }
   dot = block_reduce<false>(dot, red);
   if (threadIdx.x == 0) {
     const float b = (float)(mu[p.d + t] - dot);
-    p.icpt[slot] = b; p.bt[slot] = b;
-    p.slot_sel[slot] = (k < p.n_folds) ? 0 : 1;
-    p.slot_val[slot] = (k < p.n_folds) ? k : 1;
+    p.icpt[slot] = b; p.bt[ss] = b;
+    p.slot_sel[ss] = (k < p.n_folds) ? 0 : 1;
+    p.slot_val[ss] = (k < p.n_folds) ? k : 1;
   }
 }
 

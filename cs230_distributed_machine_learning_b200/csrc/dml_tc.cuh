@@ -358,8 +358,9 @@ tc_fwd_kernel(const __grid_constant__ CUtensorMap mapX, const __grid_constant__ 
     fence_barrier_init();
   }
   if (warp == kFwdMmaWarp) tmem_alloc(tmem_slot, kTmemCols);
-  const bool holes = (MODE == FWD_LOGREG || MODE == FWD_SCORE_CLS) && p.gstart != nullptr;
-  if (holes) for (int i = threadIdx.x; i <= p.n_groups + (MODE == FWD_SCORE_CLS ? p.hold_group : 0); i += blockDim.x) gsTab[i] = p.gstart[i];
+  constexpr bool kScoreBin = MODE == FWD_SCORE_CLS || MODE == FWD_SCORE_REG;
+  const bool holes = (MODE == FWD_LOGREG || kScoreBin) && p.gstart != nullptr;
+  if (holes) for (int i = threadIdx.x; i <= p.n_groups + (kScoreBin ? p.hold_group : 0); i += blockDim.x) gsTab[i] = p.gstart[i];
   tc_fence_before();
   __syncthreads();
   if (CL > 1) cluster_sync_all();           // peer barriers are initialised before anyone signals them
@@ -714,7 +715,7 @@ tc_fwd_kernel(const __grid_constant__ CUtensorMap mapX, const __grid_constant__ 
               const int seg = ((slot0 + c) & ~63) - slot0;       // block-local start of the 64-column segment
               hole_mask |= (p.grad_skips && seg >= b0 && seg + 64 <= a1) ? (0x10001u << ci) : (1u << ci);
             }
-          } else if (MODE == FWD_SCORE_CLS) {
+          } else if (kScoreBin) {
             if (!((c >= a0 && c + 16 <= b0) || (c >= a1 && c + 16 <= b1))) hole_mask |= 1u << ci;
           }
         }
@@ -728,7 +729,7 @@ tc_fwd_kernel(const __grid_constant__ CUtensorMap mapX, const __grid_constant__ 
         const int ci = G * i + grp;
         if (ci >= NCH) break;
         const int c0 = ci * 16;
-        const bool in_hole = (MODE == FWD_LOGREG || MODE == FWD_SCORE_CLS) && ((hole_mask >> ci) & 1u);   // the MMAs
+        const bool in_hole = (MODE == FWD_LOGREG || kScoreBin) && ((hole_mask >> ci) & 1u);   // the MMAs
         uint32_t v[16];                                                         // never wrote these TMEM columns
         if (!in_hole) {
           tmem_ld16(tacc + c0, v);
@@ -740,7 +741,7 @@ tc_fwd_kernel(const __grid_constant__ CUtensorMap mapX, const __grid_constant__ 
           if (lane == 0) mbar_arrive(tempty + acc);
         }
         if (MODE == FWD_LOGREG && ((hole_mask >> (ci + 16)) & 1u)) continue;
-        if (MODE == FWD_SCORE_CLS && ((hole_mask >> ci) & 1u)) continue;
+        if (kScoreBin && ((hole_mask >> ci) & 1u)) continue;
         // bit j set: column c0 + j does not train on (LOGREG) / is scored on (SCORE) this row
         const uint32_t heldbits = valid ? (lds16u(held_f + ci * 2) | lds16u(held_h + ci * 2)) : 0xffffu;
         if (MODE == FWD_LOGREG) {
