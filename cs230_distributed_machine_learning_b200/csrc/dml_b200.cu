@@ -69,6 +69,7 @@ struct dml_ctx {
   // (DML_CROSS_BF16=1).  Measured on config 2: same accuracy (G within 1e-6 of fp64), tensor pipe 60 % -> 43 %
   // busy, launch time unchanged (the kernel is bound by the MMA warp's issue path, not by the pipe): off.
   int cross_bf16 = 0;
+  int gb_in_grad = 1;         // sum r per column in the gradient kernel instead of the forward epilogue (DML_GB_IN_GRAD=0: forward)
   int first_round_once = 1;   // evaluate round 0 once per row mask instead of once per candidate
   int tc_rps = 8192;          // most rows per gradient split (DML_TC_RPS, multiple of 128 in 2048..8192)
   int tc_prefetch = 0, tc_prefetch_grad = 0;  // L2 prefetch distance of the forward X tiles in jobs (0 = off; measured: no gain, the ring is not latency-bound)
@@ -179,6 +180,7 @@ extern "C" int dml_ctx_create(int device, void* stream, dml_ctx** out) {
   if (const char* e = getenv("DML_GRAD_SKIP")) ctx->grad_skip = atoi(e);
   if (const char* e = getenv("DML_CROSS_BF16")) ctx->cross_bf16 = atoi(e);
   if (const char* e = getenv("DML_ROUND_AHEAD")) ctx->round_ahead = atoi(e);
+  if (const char* e = getenv("DML_GB_IN_GRAD")) ctx->gb_in_grad = atoi(e);
   if (const char* e = getenv("DML_TC_RPS")) { const int v = atoi(e); if (v >= 2048 && v <= 8192 && v % 128 == 0) ctx->tc_rps = v; }
   if (const char* e = getenv("DML_TC_CLUSTER")) ctx->tc_cluster = atoi(e) == 1 ? 1 : 2;
   CU(cudaSetDevice(device));
@@ -490,15 +492,19 @@ __global__ void __launch_bounds__(256) zero_round_kernel(const ZeroRoundParams p
   float part[32];
 #pragma unroll
   for (int c = 0; c < 32; ++c) part[c] = 0.f;
-  for (int64_t row = (int64_t)blockIdx.x * 256 + threadIdx.x; row < p.rows; row += (int64_t)gridDim.x * 256) {
-    const int64_t g = p.row0 + row;
+  // rows up to the next multiple of 128 are written too (zeros): the gradient kernel reads whole 32-row
+  // stages and sums the residuals it reads
+  const int64_t rows_pad = (p.rows + 127) / 128 * 128;
+  for (int64_t row = (int64_t)blockIdx.x * 256 + threadIdx.x; row < rows_pad; row += (int64_t)gridDim.x * 256) {
+    const bool live = row < p.rows;
+    const int64_t g = p.row0 + (live ? row : 0);
     const float base = 0.5f - (float)p.y[g];
     const int fv = (int)(uint8_t)p.fold_id[g], hv = p.hold_id ? ((int)(uint8_t)p.hold_id[g] & 1) : 0;
     float out[32];
 #pragma unroll
     for (int c = 0; c < 32; ++c) {
       const int sl = s_sel[c];
-      const bool held = sl < 0 || (sl == 0 ? fv == s_val[c] : hv == s_val[c]);
+      const bool held = !live || sl < 0 || (sl == 0 ? fv == s_val[c] : hv == s_val[c]);
       out[c] = held ? 0.f : base;
       part[c] += out[c];            // multiples of 1/2: exact
     }
@@ -534,7 +540,7 @@ struct EvalCtx {
   int64_t S_max = 0, ldr_max = 0, chunk_rows = 0, rps = 0, tc_rps = 2048, tc_rps_max = 8192, tiles_total = 0; int ctx_sms = 148;
   // buffers
   float *Wt = nullptr, *bt = nullptr, *R = nullptr, *Whi = nullptr, *Wlo = nullptr, *Gpart = nullptr;
-  double *lossPart = nullptr, *gbPart = nullptr, *Gred = nullptr; int32_t *sel = nullptr, *val = nullptr, *cntPart = nullptr;
+  double *lossPart = nullptr, *gbPart = nullptr, *Gred = nullptr, *gb2 = nullptr; int32_t *sel = nullptr, *val = nullptr, *cntPart = nullptr;
   CUtensorMap mXf, mXf2, mXg, mWh, mWl, mR1;   // mR1: residuals, one 32-column chunk x 32 rows per box
   const int* gstart = nullptr; int n_groups = 0; uint8_t* tile_fold = nullptr;
   int hold_group = 0;                // scoring: column group n_groups belongs to the hold-out fits
@@ -586,6 +592,7 @@ struct EvalCtx {
     Gpart = a.take<float>((size_t)splits * S_max * ldg);
     if (use_tc) {
       gbPart = a.take<double>(tc_parts * S_max);
+      gb2 = a.take<double>((size_t)splits * S_max);
       Whi = a.take<float>((size_t)S_max * ldw); Wlo = a.take<float>((size_t)S_max * ldw);
     }
   }
@@ -623,6 +630,10 @@ struct EvalCtx {
         fp.mask_hi = ctx->tc_mask_hi; fp.prefetch_jobs = ctx->tc_prefetch; fp.T = T; fp.loss_shift = loss_shift();
         fp.tile_fold = tile_fold; fp.gstart = gstart; fp.n_groups = n_groups; fp.grad_skips = ctx->grad_skip;
         fp.n_list_dev = n_list_dev;
+        // sum r per column: by the gradient kernel's split warps for binary problems (not with segment skipping or
+        // bf16 cross terms, whose tile layouts differ), else by the forward epilogue
+        const bool gb_grad = T == 1 && !ctx->grad_skip && !ctx->cross_bf16 && ctx->gb_in_grad;
+        fp.gb_in_grad = gb_grad ? 1 : 0;
         // clusters of 2 share each X tile between two column blocks; with an odd number of blocks one
         // CTA of the last pair would run on empty columns, so small / odd cases run unclustered
         const int clr = (cl == 2 && ncb >= 2 && (ncb % 2 == 0 || ncb >= 5)) ? 2 : 1;
@@ -649,7 +660,8 @@ struct EvalCtx {
         const int64_t min_splits = cdiv((int64_t)ctx->n_sms, pair_blocks);            // 2 waves of n_sms / 2 pairs
         const int64_t rps_here = std::min<int64_t>(tc_rps_max, std::max<int64_t>(tc_rps, (rows / min_splits) / 128 * 128));
         tc::TcGradParams gp{r0, rows, rps_here, d, n_slots, Gpart, ldg, ctx->tc_mask_hi, ctx->tc_prefetch_grad,
-                            tile_fold, ctx->grad_skip ? gstart : nullptr, n_groups, ctx->cross_bf16, n_list_dev, T};
+                            tile_fold, ctx->grad_skip ? gstart : nullptr, n_groups, ctx->cross_bf16, n_list_dev, T,
+                            gb_grad ? gb2 : nullptr};
         const int splits_here = (int)cdiv(rows, rps_here);
         rc = launch_tc_grad2(ctx, dim3((unsigned)(2 * cdiv(cdiv(d, 128), 2)), (unsigned)cdiv(n_slots, tc::kGrad2NC), (unsigned)splits_here),
                              mXg, mR1, gp);
@@ -657,7 +669,7 @@ struct EvalCtx {
         ReduceParams rp{Gpart, ldg, splits_here, n_slots, d, T, d, nullptr, 0, 0, Gred, ldgr, ci > 0 ? 1 : 0, n_list_dev};
         reduce_grad_kernel<<<n_slots, 256, 0, st>>>(rp);
         tc::TcReduceParams tr{lossPart, gbPart, n_parts, n_slots, T, d, Gred, ldgr, ci > 0 ? 1 : 0,
-                              hist_local, sel, val, n, (double)loss_shift(), n_list_dev};
+                              hist_local, sel, val, n, (double)loss_shift(), n_list_dev, gb_grad ? gb2 : nullptr, splits_here};
         tc::tc_reduce_tiles_kernel<<<(unsigned)cdiv(n_slots, 32), dim3(32, 32), 0, st>>>(tr);
       } else {
         const int ldr = (int)rup(n_slots, 4);

@@ -279,6 +279,7 @@ struct TcFwdParams {
   // live columns are *n_list_dev * T <= n_slots, read on the device, so that the host can size a round's grids
   // before it has read back the list length the previous round produced
   const int* n_list_dev;
+  int gb_in_grad;                        // the gradient kernel sums r per column (TcGradParams::gb2): no butterfly for it here
   float* R; int ldr;                     // fp32 residuals, [ldr / 32 column chunks][chunk rows][32]: a chunk's rows are contiguous,
   int64_t r_chunk_stride;                // so a gradient box (32 rows x 32 columns) is one 4 KB run; stride in floats
   double* lossPart; double* gbPart;      // [gridDim.x * 4][n_slots], zeroed by the caller
@@ -774,7 +775,7 @@ tc_fwd_kernel(const __grid_constant__ CUtensorMap mapX, const __grid_constant__ 
               }
             }
             accA[i] += (double)bfly16(ls, lane);
-            accB[i] += (double)bfly16(rs, lane);
+            if (!p.gb_in_grad) accB[i] += (double)bfly16(rs, lane);
             // 4x4 transpose of float4 inside each group of 4 lanes (rows 4g..4g+3): afterwards lane t
             // holds float4 #t of rows 4g..4g+3, so the 4 lanes of a group store 64 contiguous bytes
             // of one row per instruction instead of 16 bytes of four different rows.
@@ -860,6 +861,10 @@ struct TcGradParams {
   // 8 MMAs per 32-row stage instead of 12; a cross term is 2^-11 of the product and bf16 keeps 8 bits of it
   int cross_bf16;
   const int* n_list_dev; int list_T;   // live columns = *n_list_dev * list_T (see TcFwdParams); n_slots stays the pitch
+  // column sums of R over the split's rows, [splits][n_slots] doubles (sum r = the intercept's gradient): the
+  // split warps read every residual anyway, which saves the forward epilogue one 16-column butterfly per chunk.
+  // Written by the first feature-block pair only; null = off (the forward kernel sums r itself).
+  double* gb2;
 };
 
 // ---------------------------------------------------------------- gradient kernel, CTA pair
@@ -885,7 +890,7 @@ struct Grad2Smem {
   static constexpr int kA = 4 * 32 * 128;                    // own X boxes of one stage
   static constexpr int kBh = (kGrad2NC / 2 / 32) * 32 * 128; // own half of R (fp32; read as R_hi) and of R_lo
   static constexpr int kB = 2 * kBh;
-  static constexpr int kBytes = kGrad2SX * kA + kGrad2SR * kB + 1024 + 512 + (kMaxLabel + 2) * 4 + 64;   // + column-group starts, chain fold ids
+  static constexpr int kBytes = kGrad2SX * kA + kGrad2SR * kB + 1024 + 512 + (kMaxLabel + 2) * 4 + 64 + 4096 + 16;   // + column-group starts, chain fold ids, column-sum staging
 };
 
 // R is the fp32 residual as the forward kernel left it: the MMAs read it as R_hi (kind::tf32 ignores the
@@ -917,6 +922,7 @@ tc_grad2_kernel(const __grid_constant__ CUtensorMap mapX, const __grid_constant_
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tempty + 2);
   int* gsTab = reinterpret_cast<int*>(tmem_slot + 2);        // [n_groups + 1] copy of p.gstart
   uint8_t* tfTab = reinterpret_cast<uint8_t*>(gsTab + kMaxLabel + 2);   // [<= 64] fold id of each chain's row tile
+  double* gsm = reinterpret_cast<double*>((reinterpret_cast<uintptr_t>(tfTab + 64) + 15) & ~(uintptr_t)15);   // [2][32][8] column-sum staging
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const uint32_t rank = cluster_ctarank();
   const bool leader = rank == 0;
@@ -1062,8 +1068,17 @@ tc_grad2_kernel(const __grid_constant__ CUtensorMap mapX, const __grid_constant_
     // takes half of every loaded 4 KB chunk; then the buffer is handed to the async proxy (the MMAs)
     const int half = warp - kGrad2SplitWarp;
     uint32_t skip = 0;
+    // column sums of R (p.gb2): a lane always meets the same four columns of a chunk -- its 16-byte slot is
+    // lane & 7 and the 32-byte swizzle of the tile depends on row & 3 = (lane >> 3) & 3 for all of its rows
+    const bool want_gb = p.gb2 != nullptr && blockIdx.x < 2;
+    double gs[2][4] = {{0.0, 0.0, 0.0, 0.0}, {0.0, 0.0, 0.0, 0.0}};
+    float fs[2][4] = {{0.f, 0.f, 0.f, 0.f}, {0.f, 0.f, 0.f, 0.f}};   // fp32 over one chain (16 values), fp64 across chains
     for (int it = 0; it < n_stages; ++it) {
-      if (it % kChain == 0) skip = skip_of(it / kChain);
+      if (it % kChain == 0) {
+        skip = skip_of(it / kChain);
+#pragma unroll
+        for (int q = 0; q < 8; ++q) { gs[q >> 2][q & 3] += (double)fs[q >> 2][q & 3]; fs[q >> 2][q & 3] = 0.f; }
+      }
       const int sr = it % SR;
       mbar_wait(fullR + sr, (it / SR) & 1);
       const uint32_t hi_s = smem_u32(smR + sr * L::kB), lo_s = hi_s + L::kBh;
@@ -1094,11 +1109,32 @@ tc_grad2_kernel(const __grid_constant__ CUtensorMap mapX, const __grid_constant_
           const int i = sg * 256 + half * 128 + u * 32 + lane;       // 16-byte piece of the chunk
           const float4 v = lds128(hi_s + i * 16);
           sts128(lo_s + i * 16, make_float4(v.x - tf32_hi(v.x), v.y - tf32_hi(v.y), v.z - tf32_hi(v.z), v.w - tf32_hi(v.w)));
+          if (want_gb) {
+            if (sg == 0) { fs[0][0] += v.x; fs[0][1] += v.y; fs[0][2] += v.z; fs[0][3] += v.w; }
+            else         { fs[1][0] += v.x; fs[1][1] += v.y; fs[1][2] += v.z; fs[1][3] += v.w; }
+          }
         }
       }
       fence_proxy_async();
       __syncwarp();
       if (lane == 0) mbar_arrive_cluster(mapa_rank(smem_u32(bsplit + sr), 0));
+    }
+    if (want_gb) {      // 8 lanes (4 per warp) hold partial sums of each column: add them in a fixed order
+#pragma unroll
+      for (int sg = 0; sg < 2; ++sg)
+#pragma unroll
+        for (int c = 0; c < 4; ++c) gsm[(half * 32 + lane) * 8 + sg * 4 + c] = gs[sg][c] + (double)fs[sg][c];
+      asm volatile("bar.sync 2, 64;" ::: "memory");
+      const int x = half * 32 + lane;                  // column of this CTA's half: chunk x / 32, column x % 32
+      if (x < nseg * 32) {
+        const int sg = x >> 5, cg = (x & 31) >> 2, cc = x & 3;
+        double a = 0.0;
+        for (int h = 0; h < 2; ++h)
+          for (int l = 0; l < 32; ++l)
+            if ((((((l & 7) >> 1) ^ ((l >> 3) & 3)) << 1) | (l & 1)) == cg) a += gsm[(h * 32 + l) * 8 + sg * 4 + cc];
+        const int slot = col0 + ((int)rank * nseg + sg) * 32 + (x & 31);     // the CTA holds chunks rank * nseg + sg
+        if (slot < p.n_slots) p.gb2[(int64_t)sp * p.n_slots + slot] = a;
+      }
     }
   } else if (warp < 4) {
     const int qd = warp & 3;
@@ -1484,17 +1520,20 @@ struct TcReduceParams {
   // the forward kernel sums (loss - ln 2): add ln 2 * (training rows of the column) back once
   const unsigned long long* hist_local; const int32_t* sel; const int32_t* val; int64_t n_local; double loss_shift;
   const int* n_list_dev;   // live columns = *n_list_dev * T when set (n_slots: upper bound and pitch)
+  const double* gb2; int gb2_splits;   // sum r per (gradient split, column) from tc_grad2_kernel, or null (then gbPart)
 };
 __global__ void tc_reduce_tiles_kernel(const TcReduceParams p) {   // block (32 slots, 32 partial lanes)
   const int n_live = p.n_list_dev ? min(p.n_slots, *p.n_list_dev * p.T) : p.n_slots;
   __shared__ double sh[2][32][33];
   const int slot = blockIdx.x * 32 + threadIdx.x;
   double a = 0.0, b = 0.0;
-  if (slot < n_live)
+  if (slot < n_live) {
     for (int64_t t = threadIdx.y; t < p.n_parts; t += 32) {
       a += p.lossPart[t * p.n_slots + slot];
-      b += p.gbPart[t * p.n_slots + slot];
+      if (!p.gb2) b += p.gbPart[t * p.n_slots + slot];
     }
+    if (p.gb2) for (int t = threadIdx.y; t < p.gb2_splits; t += 32) b += p.gb2[(int64_t)t * p.n_slots + slot];
+  }
   sh[0][threadIdx.y][threadIdx.x] = a; sh[1][threadIdx.y][threadIdx.x] = b;
   __syncthreads();
   if (threadIdx.y == 0 && slot < n_live) {
