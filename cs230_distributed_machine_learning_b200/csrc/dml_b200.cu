@@ -69,6 +69,7 @@ struct dml_ctx {
   // (DML_CROSS_BF16=1).  Measured on config 2: same accuracy (G within 1e-6 of fp64), tensor pipe 60 % -> 43 %
   // busy, launch time unchanged (the kernel is bound by the MMA warp's issue path, not by the pipe): off.
   int cross_bf16 = 0;
+  int grad_zero_fill = 1;     // hole chunks of R: not stored by the forward kernel, zero-filled (not read) by the gradient kernel
   int gb_in_grad = 1;         // sum r per column in the gradient kernel instead of the forward epilogue (DML_GB_IN_GRAD=0: forward)
   int first_round_once = 1;   // evaluate round 0 once per row mask instead of once per candidate
   int tc_rps = 8192;          // most rows per gradient split (DML_TC_RPS, multiple of 128 in 2048..8192)
@@ -181,6 +182,7 @@ extern "C" int dml_ctx_create(int device, void* stream, dml_ctx** out) {
   if (const char* e = getenv("DML_CROSS_BF16")) ctx->cross_bf16 = atoi(e);
   if (const char* e = getenv("DML_ROUND_AHEAD")) ctx->round_ahead = atoi(e);
   if (const char* e = getenv("DML_GB_IN_GRAD")) ctx->gb_in_grad = atoi(e);
+  if (const char* e = getenv("DML_GRAD_ZERO_FILL")) ctx->grad_zero_fill = atoi(e);
   if (const char* e = getenv("DML_TC_RPS")) { const int v = atoi(e); if (v >= 2048 && v <= 8192 && v % 128 == 0) ctx->tc_rps = v; }
   if (const char* e = getenv("DML_TC_CLUSTER")) ctx->tc_cluster = atoi(e) == 1 ? 1 : 2;
   CU(cudaSetDevice(device));
@@ -628,7 +630,8 @@ struct EvalCtx {
         fp.fold_id = fold_id; fp.hold_id = hold_id; fp.slot_sel = sel; fp.slot_val = val;
         fp.R = R; fp.ldr = (int)ldr_max; fp.r_chunk_stride = chunk_rows * 32; fp.lossPart = lossPart; fp.gbPart = gbPart;
         fp.mask_hi = ctx->tc_mask_hi; fp.prefetch_jobs = ctx->tc_prefetch; fp.T = T; fp.loss_shift = loss_shift();
-        fp.tile_fold = tile_fold; fp.gstart = gstart; fp.n_groups = n_groups; fp.grad_skips = ctx->grad_skip;
+        fp.tile_fold = tile_fold; fp.gstart = gstart; fp.n_groups = n_groups;
+        fp.grad_skips = ctx->grad_skip ? 1 : (ctx->grad_zero_fill ? 2 : 0);
         fp.n_list_dev = n_list_dev;
         // sum r per column: by the gradient kernel's split warps for binary problems (not with segment skipping or
         // bf16 cross terms, whose tile layouts differ), else by the forward epilogue
@@ -660,7 +663,8 @@ struct EvalCtx {
         const int64_t min_splits = cdiv((int64_t)ctx->n_sms, pair_blocks);            // 2 waves of n_sms / 2 pairs
         const int64_t rps_here = std::min<int64_t>(tc_rps_max, std::max<int64_t>(tc_rps, (rows / min_splits) / 128 * 128));
         tc::TcGradParams gp{r0, rows, rps_here, d, n_slots, Gpart, ldg, ctx->tc_mask_hi, ctx->tc_prefetch_grad,
-                            tile_fold, ctx->grad_skip ? gstart : nullptr, n_groups, ctx->cross_bf16, n_list_dev, T,
+                            tile_fold, (ctx->grad_skip || ctx->grad_zero_fill) ? gstart : nullptr, n_groups, ctx->grad_skip,
+                            ctx->cross_bf16, n_list_dev, T,
                             gb_grad ? gb2 : nullptr};
         const int splits_here = (int)cdiv(rows, rps_here);
         rc = launch_tc_grad2(ctx, dim3((unsigned)(2 * cdiv(cdiv(d, 128), 2)), (unsigned)cdiv(n_slots, tc::kGrad2NC), (unsigned)splits_here),

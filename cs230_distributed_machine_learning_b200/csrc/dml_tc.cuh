@@ -274,7 +274,8 @@ struct TcFwdParams {
   // fold k trains none of them: no MMAs, no epilogue math for that column range.  gstart == nullptr: off.
   const uint8_t* tile_fold; const int* gstart; int n_groups;
   int hold_group;                        // scoring mode: group n_groups holds the hold-out fits (scored on rows of every tile)
-  int grad_skips;                        // the gradient kernel skips whole 64-column segments of a hole: nothing to store there
+  int grad_skips;                        // what the gradient kernel leaves unread of a hole, so nothing is stored there:
+                                         // 1 = whole 64-column segments, 2 = 32-column chunks (TcGradParams::seg_skip)
   // n_slots is the host's upper bound (and the pitch of the partial-sum arrays); when n_list_dev is set the
   // live columns are *n_list_dev * T <= n_slots, read on the device, so that the host can size a round's grids
   // before it has read back the list length the previous round produced
@@ -714,7 +715,10 @@ tc_fwd_kernel(const __grid_constant__ CUtensorMap mapX, const __grid_constant__ 
           if (MODE == FWD_LOGREG) {
             if (c >= b0 && c + 16 <= a1) {          // inside the hole [b0, a1)
               const int seg = ((slot0 + c) & ~63) - slot0;       // block-local start of the 64-column segment
-              hole_mask |= (p.grad_skips && seg >= b0 && seg + 64 <= a1) ? (0x10001u << ci) : (1u << ci);
+              const int ch = ((slot0 + c) & ~31) - slot0;        // ... and of its 32-column chunk
+              const bool unread = p.grad_skips == 1 ? (seg >= b0 && seg + 64 <= a1)
+                                : p.grad_skips == 2 ? (ch >= b0 && ch + 32 <= a1) : false;
+              hole_mask |= unread ? (0x10001u << ci) : (1u << ci);
             }
           } else if (kScoreBin) {
             if (!((c >= a0 && c + 16 <= b0) || (c >= a1 && c + 16 <= b1))) hole_mask |= 1u << ci;
@@ -857,6 +861,11 @@ struct TcGradParams {
   // fold-aware skipping (see TcFwdParams): a 128-row chain whose rows all sit in fold k contributes
   // nothing to fold k's columns; 64-column segments inside that group are not loaded or multiplied
   const uint8_t* tile_fold; const int* gstart; int n_groups;
+  // with gstart set: seg_skip = 1 skips whole 64-column segments as described above (N = 64 MMAs); 0 keeps the
+  // N = ncols MMAs and only leaves the 32-column chunks of the hole unread -- their TMA load is aimed past the
+  // end of the residual array, which fills the shared-memory tile with zeros without touching HBM, and the
+  // forward kernel does not store them (TcFwdParams::grad_skips = 2)
+  int seg_skip;
   // cross terms x_lo r_hi + x_hi r_lo as bf16 MMAs over a K-concatenated operand (128-column blocks only):
   // 8 MMAs per 32-row stage instead of 12; a cross term is 2^-11 of the product and bf16 keeps 8 bits of it
   int cross_bf16;
@@ -961,7 +970,7 @@ tc_grad2_kernel(const __grid_constant__ CUtensorMap mapX, const __grid_constant_
 
   // bit s set: segment s is skipped for chain g (rows_per_split and row0_x are multiples of 128)
   auto skip_of = [&](int g) -> uint32_t {
-    if (!holes) return 0u;
+    if (!holes || !p.seg_skip) return 0u;
     const int k = tfTab[g];
     if (k >= p.n_groups) return 0u;
     uint32_t m = 0;
@@ -972,11 +981,25 @@ tc_grad2_kernel(const __grid_constant__ CUtensorMap mapX, const __grid_constant_
     return m;
   };
 
+  // bit c set: chunk c of this CTA's half lies inside the column group of chain g's fold (zero-filled, not read)
+  auto zero_of = [&](int g) -> uint32_t {
+    if (!holes || p.seg_skip) return 0u;
+    const int k = tfTab[g];
+    if (k >= p.n_groups) return 0u;
+    uint32_t m = 0;
+    for (int c = 0; c < nseg; ++c) {
+      const int col = col0 + ((int)rank * nseg + c) * 32;
+      if (col >= gsTab[k] && col + 32 <= gsTab[k + 1]) m |= 1u << c;
+    }
+    return m;
+  };
+  constexpr int kPastEnd = 1 << 20;   // chunk coordinate beyond every residual array
+
   const bool use_bf = p.cross_bf16 != 0 && nseg == 2;   // only chains without a skipped segment take this form
 
   if (warp == kGrad2TmaWarp) {
     if (lane == 0) {
-      uint32_t skip = 0;
+      uint32_t skip = 0, zfill = 0;
       for (int it = 0; it < n_stages; ++it) {
         if (it % kChain == 0) skip = skip_of(it / kChain);
         const int sx = it % SX, sr = it % SR;
@@ -990,8 +1013,10 @@ tc_grad2_kernel(const __grid_constant__ CUtensorMap mapX, const __grid_constant_
         mbar_wait(emptyB + sr, ((it / SR) & 1) ^ 1);
         uint8_t* br = smR + sr * L::kB;
         if (skip == 0) {           // whole block: this CTA's half = nseg consecutive chunks
+          if (it % kChain == 0) zfill = zero_of(it / kChain);
           mbar_expect_tx(fullR + sr, (uint32_t)(nseg * 4096));
-          for (int c = 0; c < nseg; ++c) tma_load_3d(&mapR, fullR + sr, br + c * 4096, 0, lr, col0 / 32 + (int)rank * nseg + c);
+          for (int c = 0; c < nseg; ++c)
+            tma_load_3d(&mapR, fullR + sr, br + c * 4096, 0, lr, ((zfill >> c) & 1u) ? kPastEnd : col0 / 32 + (int)rank * nseg + c);
         } else {                   // segments: chunk (2 sg + rank) of the block, at position sg
           int n_load = 0;
           for (int sg = 0; sg < nseg; ++sg) if (!((skip >> sg) & 1u)) ++n_load;

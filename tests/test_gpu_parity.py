@@ -346,8 +346,8 @@ def test_queued_jobs_prefetch_their_dataset_and_match_blocking_runs():
 
 
 @pytest.mark.parametrize("env", [{"DML_FOLD_SKIP": "0"}, {"DML_GRAD_SKIP": "1"}, {"DML_FIRST_ROUND_ONCE": "0"},
-                                 {"DML_ROUND_AHEAD": "0"}, {"DML_GB_IN_GRAD": "0"}],
-                         ids=["no-fold-skip", "grad-skip", "full-round-0", "no-round-ahead", "gb-in-forward"])
+                                 {"DML_ROUND_AHEAD": "0"}, {"DML_GB_IN_GRAD": "0"}, {"DML_GRAD_ZERO_FILL": "0"}],
+                         ids=["no-fold-skip", "grad-skip", "full-round-0", "no-round-ahead", "gb-in-forward", "no-zero-fill"])
 def test_skipping_knobs_do_not_change_results(solver, monkeypatch, env):
     """Fold-aware column skipping and the round-0 shortcut only remove work whose result is zero or
     known: every switch setting gives the same iterates (compared with the default context)."""
