@@ -64,7 +64,8 @@ def create_subtasks(job_config: dict) -> list[dict]:
             for i, params in enumerate(combos)]
 
 
-def create_blocks(subtasks: list[dict], n_gpus: int = 1, partition: str = "candidates") -> list[dict]:
+def create_blocks(subtasks: list[dict], n_gpus: int = 1, partition: str = "candidates",
+                  cost: list[float] | None = None) -> list[dict]:
     """Regroup per-candidate subtasks into per-GPU block subtasks.
 
     A block keeps the subtask keys and adds ``candidates`` [{index, subtask_id,
@@ -73,6 +74,12 @@ def create_blocks(subtasks: list[dict], n_gpus: int = 1, partition: str = "candi
     "rows": every GPU gets all candidates and a row shard (needs one process per
     GPU with NCCL, see bench.py).  A block with a single candidate and all folds is
     the legacy subtask.
+
+    ``cost`` (one predicted number of batched rounds per candidate, ``IterationModel``)
+    replaces the round-robin deal by longest-first dealing: candidates sorted by cost,
+    each to the GPU with the least work so far.  A GPU's sweep time follows the sum of
+    its columns' rounds, and a randomized search enumerates candidates in draw order,
+    where round-robin leaves that sum to chance.
     """
     if not subtasks:
         return []
@@ -80,9 +87,13 @@ def create_blocks(subtasks: list[dict], n_gpus: int = 1, partition: str = "candi
     first = subtasks[0]
     cv = first.get("train_params", {}).get("cv", 5)
     blocks = []
+    deal = deal_by_cost(cost, n_gpus) if (cost is not None and partition == "candidates") else None
     for g in range(n_gpus):
-        mine = subtasks[g::n_gpus] if partition == "candidates" else subtasks
-        own = [i for i in range(len(subtasks))][g::n_gpus] if partition == "candidates" else list(range(len(subtasks)))
+        if partition != "candidates":
+            own = list(range(len(subtasks)))
+        else:
+            own = deal[g] if deal is not None else list(range(len(subtasks)))[g::n_gpus]
+        mine = [subtasks[i] for i in own]
         blocks.append({
             "subtask_id": f"{first['job_id']}-block-{g + 1}",
             "job_id": first["job_id"], "session_id": first["session_id"], "dataset_id": first["dataset_id"],
@@ -93,6 +104,79 @@ def create_blocks(subtasks: list[dict], n_gpus: int = 1, partition: str = "candi
             "gpu": g, "partition": partition, "n_shards": n_gpus if partition == "rows" else 1,
         })
     return blocks
+
+
+def deal_by_cost(cost: list[float], n_gpus: int) -> list[list[int]]:
+    """Longest-processing-time dealing: indices by falling cost (ties: enumeration order), each to
+    the least-loaded GPU (ties: lowest GPU).  Every GPU gets at least one candidate when there are
+    enough; each GPU's list comes back in enumeration order."""
+    order = sorted(range(len(cost)), key=lambda i: (-float(cost[i]), i))
+    load = [0.0] * n_gpus
+    own: list[list[int]] = [[] for _ in range(n_gpus)]
+    for i in order:
+        g = min(range(n_gpus), key=lambda k: (-1.0 if not own[k] else load[k], k))
+        own[g].append(i)
+        load[g] += max(float(cost[i]), 0.0)
+    return [sorted(o) for o in own]
+
+
+class IterationModel:
+    """Predicted batched rounds of one candidate: the scheduler's runtime estimate for this path.
+
+    The reference predicts a subtask's runtime with a GBRT over dataset and model features
+    (scheduler_service.py:40-84) and places by ``load/speed + est/speed`` (:173-191).  On the GPU a
+    block's time follows the sum over its columns of L-BFGS rounds (every round streams X once for
+    the columns still live), so the quantity to predict is ``n_iter_`` per candidate.  It rises with
+    log10(C) and with -log10(tol); Ridge-family candidates are direct solves (cost 1).  Finished jobs
+    report ``n_iter`` per fold (worker result dict): per (model, dataset) the model keeps the mean
+    rounds seen at each (log10 C, log10 tol) and interpolates in log10 C among the observations with
+    the nearest tol; before any observation it uses a fixed monotone rule, which is enough for the
+    ordering that longest-first dealing needs.
+    """
+
+    def __init__(self):
+        self.seen: dict[tuple[str, str], dict[tuple[float, float], tuple[float, int]]] = {}
+
+    @staticmethod
+    def _key(params: dict) -> tuple[float, float]:
+        c = float(params.get("C", 1.0) or 1.0)
+        tol = float(params.get("tol", 1e-4) or 1e-4)
+        return (float(np.log10(max(c, 1e-300))), float(np.log10(max(tol, 1e-300))))
+
+    @staticmethod
+    def prior(lc: float, lt: float, max_iter: float) -> float:
+        # 1 round when the penalty dominates, about one more round per decade of C above 1e-6 and
+        # a quarter more per decade of tol below 1e-4 (the shape measured on configs 2 and 4)
+        return float(min(max_iter, max(1.0, (1.0 + max(0.0, lc + 6.0)) * (1.0 + 0.25 * max(0.0, -4.0 - lt)))))
+
+    def predict(self, model_type: str, dataset_id: str, params: dict) -> float:
+        if model_type != "LogisticRegression":
+            return 1.0
+        lc, lt = self._key(params)
+        max_iter = float(params.get("max_iter", 100) or 100)
+        obs = self.seen.get((model_type, dataset_id))
+        if not obs:
+            return self.prior(lc, lt, max_iter)
+        tol_near = min({k[1] for k in obs}, key=lambda t: abs(t - lt))
+        pts = sorted((k[0], v[0]) for k, v in obs.items() if k[1] == tol_near)
+        est = float(np.interp(lc, [p[0] for p in pts], [p[1] for p in pts]))
+        # outside the observed range of C follow the prior's slope from the nearest observation
+        edge = pts[0] if lc < pts[0][0] else pts[-1] if lc > pts[-1][0] else None
+        if edge is not None:
+            est = edge[1] + self.prior(lc, lt, 1e9) - self.prior(edge[0], lt, 1e9)
+        return float(min(max_iter, max(1.0, est)))
+
+    def observe(self, model_type: str, dataset_id: str, params: dict, n_iter) -> None:
+        if model_type != "LogisticRegression" or n_iter is None:
+            return
+        it = np.asarray(n_iter, dtype=np.float64).ravel()
+        it = it[np.isfinite(it)]
+        if it.size == 0:
+            return
+        tab = self.seen.setdefault((model_type, dataset_id), {})
+        k = self._key(params)
+        mean, cnt = tab.get(k, (0.0, 0))
+        tab[k] = ((mean * cnt + float(it.mean())) / (cnt + 1), cnt + 1)
 
 
 # --------------------------------------------------------------------------------------
@@ -150,6 +234,7 @@ class Master:
         self.sessions: set[str] = set()
         self.jobs: dict[tuple[str, str], dict] = {}
         self.lock = threading.Lock()
+        self.iterations = IterationModel()      # rounds per candidate, learnt from finished jobs
         scheduler.attach_master(self)
 
     # /create_session
@@ -186,7 +271,9 @@ class Master:
         with self.lock:
             self.jobs[(session_id, payload["job_id"])] = job
         n_gpus = self.n_gpus or max(1, self.scheduler.n_workers())
-        for block in create_blocks(subtasks, n_gpus=n_gpus, partition=self.partition):
+        with self.lock:
+            cost = [self.iterations.predict(st["model_type"], st["dataset_id"], st["parameters"]) for st in subtasks]
+        for block in create_blocks(subtasks, n_gpus=n_gpus, partition=self.partition, cost=cost):
             self.scheduler.submit(block)       # topic "tasks"
         return {"status": "Training started", "job_id": payload["job_id"], "total_subtasks": len(subtasks)}
 
@@ -233,6 +320,8 @@ class Master:
                 r = {"cv_scores": [float("nan")] * (cv if isinstance(cv, int) else 5),
                      "mean_cv_score": float("nan"), "parameters": st["parameters"],
                      "error": job["failed"].get(st["subtask_id"])}
+            else:
+                self.iterations.observe(st["model_type"], st["dataset_id"], st["parameters"], r.get("n_iter"))
             ordered.append(r)
         out = {"results": ordered, "best_result": aggregate_results(ordered), "completion_time": time.time()}
         if job["search_type"]:

@@ -369,3 +369,45 @@ def test_prefetch_task_routes_to_the_executor(monkeypatch):
     assert not wk.prefetch_task(dict(block, dataset_id="missing"), gpu=0)
     assert not wk.prefetch_task(block, gpu=1)          # no executor on that GPU yet
     assert len(calls) == 2
+
+
+def test_blocks_dealt_by_predicted_rounds():
+    """a randomized search enumerates candidates in draw order; dealing by the predicted
+    rounds balances the GPUs' column-rounds where round-robin leaves them to chance."""
+    rng = np.random.default_rng(0)
+    Cs = rng.permutation(np.logspace(-6, 2, 64))
+    subtasks = [{"subtask_id": f"j-subtask-{i + 1}", "job_id": "j", "session_id": "s", "dataset_id": "d",
+                 "model_type": "LogisticRegression", "parameters": {"C": float(c)}, "train_params": {"cv": 5}}
+                for i, c in enumerate(Cs)]
+    model = master.IterationModel()
+    cost = [model.predict("LogisticRegression", "d", st["parameters"]) for st in subtasks]
+    assert all(a <= b for a, b in zip(sorted(cost), sorted(cost)[1:])) and min(cost) >= 1.0
+    assert np.argsort(Cs, kind="stable").tolist() == np.argsort(cost, kind="stable").tolist()   # monotone in C
+    for n_gpus in (2, 4, 8):
+        dealt = master.create_blocks(subtasks, n_gpus=n_gpus, cost=cost)
+        robin = master.create_blocks(subtasks, n_gpus=n_gpus)
+        assert sorted(c["index"] for b in dealt for c in b["candidates"]) == list(range(64))
+        for b in dealt:
+            idx = [c["index"] for c in b["candidates"]]
+            assert idx == sorted(idx) and all(c["parameters"] == subtasks[c["index"]]["parameters"] for c in b["candidates"])
+        load = lambda blocks: [sum(cost[c["index"]] for c in b["candidates"]) for b in blocks]
+        assert max(load(dealt)) <= max(load(robin)) + 1e-9
+        assert max(load(dealt)) - min(load(dealt)) <= max(cost)            # LPT bound
+    # Ridge-family candidates are direct solves: equal cost, equal block sizes
+    assert model.predict("Ridge", "d", {"alpha": 3.0}) == 1.0
+    sizes = sorted(len(o) for o in master.deal_by_cost([1.0] * 10, 4))
+    assert sizes == [2, 2, 3, 3]
+
+
+def test_iteration_model_learns_from_results():
+    model = master.IterationModel()
+    before = model.predict("LogisticRegression", "d", {"C": 1.0})
+    for c, it in ((1e-4, [2, 2, 3]), (1e-2, [4, 4, 4]), (1.0, [9, 9, 9]), (1e2, [12, 12, 12])):
+        model.observe("LogisticRegression", "d", {"C": c}, it)
+    assert model.predict("LogisticRegression", "d", {"C": 1.0}) == 9.0 != before
+    assert model.predict("LogisticRegression", "d", {"C": 0.1}) == pytest.approx(6.5)        # interpolated in log10 C
+    assert model.predict("LogisticRegression", "d", {"C": 1e3}) > 12.0                       # prior's slope past the edge
+    assert model.predict("LogisticRegression", "d", {"C": 1e3, "max_iter": 10}) == 10.0
+    assert model.predict("LogisticRegression", "other", {"C": 1.0}) == before                # per dataset
+    model.observe("LogisticRegression", "d", {"C": 1.0}, [11, 11, 11])
+    assert model.predict("LogisticRegression", "d", {"C": 1.0}) == 10.0                      # running mean
