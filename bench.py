@@ -407,10 +407,11 @@ def run_b200(a):
                          "frac": (ach / p3) if ach else None,
                          # DRAM bytes of one forward + one gradient launch (ncu --set full, dram__bytes_read.sum +
                          # dram__bytes_write.sum, profiles/r01_ncu_full_n1_fwd_grad2.csv): only known for config 2
-                         "traffic": 4.67e9 if (a.rows, a.features, a.candidates) == (1_000_000, 256, 64) else None,
-                         "traffic_note": "bytes per full-width round (forward 1.03 GB read + 1.24 GB written, gradient "
-                                         "2.36 GB read); algorithmic: X once per kernel (2 x 1.02 GB) + fp32 residuals "
-                                         "once each way (2 x 1.28 GB for 320 columns) = 4.61 GB",
+                         "traffic": 4.20e9 if (a.rows, a.features, a.candidates) == (1_000_000, 256, 64) else None,
+                         "traffic_note": "bytes per full-width round (forward 1.03 GB read + 0.98 GB written, gradient "
+                                         "2.15 GB read + 0.04 GB written); algorithmic: X once per kernel (2 x 1.02 GB) + "
+                                         "fp32 residuals of the training rows once each way (2 x 1.02 GB for 320 columns, "
+                                         "4 of 5 folds) = 4.10 GB",
                          "kernel": "forward+gradient contraction pair per batched round",
                          "peak_source": f"cuBLAS TF32 8192^3 measured in this run, sustained over ~2 s = {p_tf32:.1f} TFLOP/s "
                                         f"(burst {p_burst:.1f}); /3 for 3xTF32; MEASURED_PEAKS.json has no TF32 entry",
