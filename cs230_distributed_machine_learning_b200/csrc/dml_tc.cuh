@@ -322,6 +322,9 @@ __device__ __forceinline__ T bfly16(const T (&v)[16], int lane) {
   return d + __shfl_xor_sync(0xffffffffu, d, 1);
 }
 
+// arr[i] += val for a run-time i < n with arr kept in registers: n predicated adds with compile-time indices
+#define DML_ACC_N(arr, n, val) do { const auto v_ = (val); _Pragma("unroll") for (int k_ = 0; k_ < (n); ++k_) if (k_ == i) arr[k_] += v_; } while (0)
+
 // Jobs are ordered column block first: every CTA walks the row tiles of one column block (W stays
 // hot in L2, per-column running sums stay in registers) and changes block at most a few times.
 // CL = 2: the kernel runs as clusters of two CTAs that work on the SAME row tile and on neighbouring
@@ -581,7 +584,7 @@ tc_fwd_kernel(const __grid_constant__ CUtensorMap mapX, const __grid_constant__ 
         tc_fence_after();
         const uint32_t tacc = tmem_base + acc * NC + ((uint32_t)(q * 32) << 16);
         if (last_f < 0) { tc_fence_before(); __syncwarp(); if (lane == 0) mbar_arrive(tempty + acc); }
-#pragma unroll
+#pragma unroll 1      // rolled for the same reason as the binary epilogue's chunk loop below (8 fits x 16 classes unrolled: 178 KB of SASS)
         for (int i = 0; i < kMyF; ++i) {
           const int f = G * i + grp;
           if (f >= nfit) break;
@@ -602,7 +605,7 @@ tc_fwd_kernel(const __grid_constant__ CUtensorMap mapX, const __grid_constant__ 
           }
           if (MODE == FWD_SCORE_MULTI) {
             const int ok = (valid && held && exists && am == yv) ? 1 : 0;
-            accC[i] += __popc(__ballot_sync(0xffffffffu, ok));
+            DML_ACC_N(accC, kMyF, __popc(__ballot_sync(0xffffffffu, ok)));
           } else {
             const bool train = valid && !held && exists;
             float ssum = 0.f, zy = 0.f, rs[16];
@@ -612,8 +615,8 @@ tc_fwd_kernel(const __grid_constant__ CUtensorMap mapX, const __grid_constant__ 
             const float loss = train ? (__logf(ssum) + m - zy) - p.loss_shift : 0.f;
 #pragma unroll
             for (int c = 0; c < 16; ++c) rs[c] = (train && c < T) ? rs[c] * inv - (c == yv ? 1.f : 0.f) : 0.f;
-            accA[i] += (double)warp_sum(loss);
-            accB[i] += (double)bfly16(rs, lane);
+            DML_ACC_N(accA, kMyF, (double)warp_sum(loss));
+            DML_ACC_N(accB, kMyF, (double)bfly16(rs, lane));
             if (rt < n_row_tiles) {
 #pragma unroll
               for (int c = 0; c < 16; ++c) {
@@ -729,7 +732,12 @@ tc_fwd_kernel(const __grid_constant__ CUtensorMap mapX, const __grid_constant__ 
       tc_fence_after();
       const uint32_t tacc = tmem_base + acc * NC + ((uint32_t)(q * 32) << 16);
       if (last_ci < 0) { tc_fence_before(); __syncwarp(); if (lane == 0) mbar_arrive(tempty + acc); }
-#pragma unroll
+      // The chunk loop stays rolled: unrolled, the body of one tile was 80 KB of SASS (3 chunks x two 16-element
+      // paths), the epilogue warps missed the instruction cache on every pass ("no instruction" was the second
+      // stall reason) and no chunk overlaps the next anyway (each starts with a tcgen05.ld wait).  The per-chunk
+      // accumulators stay in registers: DML_ACC adds under a predicate with a compile-time index.
+#define DML_ACC(arr, val) DML_ACC_N(arr, kMy, val)
+#pragma unroll 1
       for (int i = 0; i < kMy; ++i) {
         const int ci = G * i + grp;
         if (ci >= NCH) break;
@@ -778,8 +786,8 @@ tc_fwd_kernel(const __grid_constant__ CUtensorMap mapX, const __grid_constant__ 
                 ls[j] = train ? (fmaxf(z, 0.f) - yy * z) + (__logf(1.f + e) - p.loss_shift) : 0.f;
               }
             }
-            accA[i] += (double)bfly16(ls, lane);
-            if (!p.gb_in_grad) accB[i] += (double)bfly16(rs, lane);
+            DML_ACC(accA, (double)bfly16(ls, lane));
+            if (!p.gb_in_grad) DML_ACC(accB, (double)bfly16(rs, lane));
             // 4x4 transpose of float4 inside each group of 4 lanes (rows 4g..4g+3): afterwards lane t
             // holds float4 #t of rows 4g..4g+3, so the 4 lanes of a group store 64 contiguous bytes
             // of one row per instruction instead of 16 bytes of four different rows.
@@ -819,7 +827,7 @@ tc_fwd_kernel(const __grid_constant__ CUtensorMap mapX, const __grid_constant__ 
             const float z = __uint_as_float(v[j]) + lds32f(bias_s + (c0 + j) * 4);
             ok[j] = (held && (((z > 0.f) ? 1 : 0) == yv)) ? 1 : 0;
           }
-          accC[i] += bfly16(ok, lane);
+          DML_ACC(accC, bfly16(ok, lane));
         } else {
           float se[16];
 #pragma unroll
@@ -828,10 +836,12 @@ tc_fwd_kernel(const __grid_constant__ CUtensorMap mapX, const __grid_constant__ 
             const float e = yf - (__uint_as_float(v[j]) + lds32f(bias_s + (c0 + j) * 4));
             se[j] = held ? e * e : 0.f;
           }
-          accA[i] += (double)bfly16(se, lane);
+          DML_ACC(accA, (double)bfly16(se, lane));
         }
       }
     }
+#undef DML_ACC
+#undef DML_ACC_N
     flush(cur_cb);
     }
   }
