@@ -228,6 +228,14 @@ __device__ __forceinline__ float4 lds128(uint32_t a) {
 __device__ __forceinline__ void sts128(uint32_t a, const float4& v) {
   asm volatile("st.shared.v4.f32 [%0], {%1,%2,%3,%4};" ::"r"(a), "f"(v.x), "f"(v.y), "f"(v.z), "f"(v.w) : "memory");
 }
+// e^x for x <= 0 as one FMUL and one MUFU: __expf without -ftz wraps the MUFU in a range test and two predicated
+// multiplies (3 of the ~16 instructions per element of the logistic epilogue) to keep results below 2^-126, which
+// no consumer here can see (1 + e, e / (1 + e) - y and log(1 + e) are the same fp32 numbers with e flushed to 0)
+__device__ __forceinline__ float exp_ftz(float x) {
+  float y;
+  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x * 1.4426950408889634f));
+  return y;
+}
 __device__ __forceinline__ float lds32f(uint32_t a) { float v; asm volatile("ld.shared.f32 %0, [%1];" : "=f"(v) : "r"(a)); return v; }
 __device__ __forceinline__ uint32_t lds16u(uint32_t a) { uint16_t v; asm volatile("ld.shared.u16 %0, [%1];" : "=h"(v) : "r"(a)); return v; }
 
@@ -610,7 +618,7 @@ tc_fwd_kernel(const __grid_constant__ CUtensorMap mapX, const __grid_constant__ 
             const bool train = valid && !held && exists;
             float ssum = 0.f, zy = 0.f, rs[16];
 #pragma unroll
-            for (int c = 0; c < 16; ++c) { rs[c] = c < T ? __expf(z[c] - m) : 0.f; ssum += rs[c]; if (c == yv) zy = z[c]; }
+            for (int c = 0; c < 16; ++c) { rs[c] = c < T ? exp_ftz(z[c] - m) : 0.f; ssum += rs[c]; if (c == yv) zy = z[c]; }
             const float inv = __fdividef(1.f, ssum);
             const float loss = train ? (__logf(ssum) + m - zy) - p.loss_shift : 0.f;
 #pragma unroll
@@ -769,7 +777,7 @@ tc_fwd_kernel(const __grid_constant__ CUtensorMap mapX, const __grid_constant__ 
 #pragma unroll
               for (int j = 0; j < 16; ++j) {
                 const float z = __uint_as_float(v[j]) + lds32f(bias_s + (c0 + j) * 4);
-                const float e = __expf(-fabsf(z));
+                const float e = exp_ftz(-fabsf(z));
                 const float inv = __fdividef(1.f, 1.f + e);
                 rs[j] = (z >= 0.f ? inv : e * inv) - yy;
                 ls[j] = (fmaxf(z, 0.f) - yy * z) + (__logf(1.f + e) - p.loss_shift);
@@ -779,7 +787,7 @@ tc_fwd_kernel(const __grid_constant__ CUtensorMap mapX, const __grid_constant__ 
               for (int j = 0; j < 16; ++j) {
                 const bool train = !((heldbits >> j) & 1u);
                 const float z = __uint_as_float(v[j]) + lds32f(bias_s + (c0 + j) * 4);
-                const float e = __expf(-fabsf(z));
+                const float e = exp_ftz(-fabsf(z));
                 const float inv = __fdividef(1.f, 1.f + e);
                 const float pr = z >= 0.f ? inv : e * inv;
                 rs[j] = train ? pr - yy : 0.f;
