@@ -138,7 +138,7 @@ def train_candidate_sklearn(model_type: str, parameters: dict, train_params: dic
     from sklearn.base import is_classifier
     from sklearn.exceptions import ConvergenceWarning
     from sklearn.metrics import accuracy_score, mean_squared_error, r2_score
-    from sklearn.model_selection import cross_val_score, train_test_split
+    from sklearn.model_selection import cross_validate, train_test_split
     model = get_model_instance(model_type, parameters)
     clf = is_classifier(model)
     results = {}
@@ -169,9 +169,14 @@ def train_candidate_sklearn(model_type: str, parameters: dict, train_params: dic
                 results["r2_score"] = float(r2_score(yte, pred))
                 results["mean_squared_error"] = float(mean_squared_error(yte, pred))
         t0 = time.time()
-        scores = cross_val_score(model, X, y, cv=train_params.get("cv", 5), scoring="accuracy" if clf else "r2",
-                                 error_score="raise")
+        # cross_val_score (worker.py:326,341) is cross_validate()["test_score"]; the fitted fold models come back too
+        # so that the result can say how many L-BFGS iterations each fold took (master.IterationModel)
+        cvr = cross_validate(model, X, y, cv=train_params.get("cv", 5), scoring="accuracy" if clf else "r2",
+                             error_score="raise", return_estimator=True)
+        scores = cvr["test_score"]
         results.setdefault("training_time", (time.time() - t0) / max(1, len(scores)))
+        if model_type == "LogisticRegression":
+            results["n_iter"] = [int(np.max(e.n_iter_)) for e in cvr["estimator"]]
     results["cv_scores"] = scores.tolist()
     results["mean_cv_score"] = float(scores.mean())
     results["model_id"] = f"{subtask_id}_model"

@@ -419,3 +419,26 @@ def test_iteration_model_learns_from_results():
     assert model.predict("LogisticRegression", "other", {"C": 1.0}) == before                # per dataset
     model.observe("LogisticRegression", "d", {"C": 1.0}, [11, 11, 11])
     assert model.predict("LogisticRegression", "d", {"C": 1.0}) == 10.0                      # running mean
+
+
+def test_master_learns_rounds_from_a_finished_job():
+    """After one job on a dataset the splitter deals the next job's candidates by the rounds the first one
+    reported (results carry n_iter on both executors)."""
+    from sklearn.datasets import load_iris
+    X, y = load_iris(return_X_y=True)
+    pkg.register_dataset("iris-rounds", X, y)
+    m = MLTaskManager("local://1")
+    try:
+        model = m.master.iterations
+        flat = model.predict("LogisticRegression", "iris-rounds", {"C": 0.01})
+        assert model.predict("LogisticRegression", "iris-rounds", {"C": 100.0}) == flat
+        gs = GridSearchCV(LogisticRegression(max_iter=500), {"C": [0.01, 1.0, 100.0]}, cv=5)
+        m.train(gs, "iris-rounds")
+        r = m._wait_for_completion(m.job_id)
+        assert r["job_status"] == "completed"
+        want = [float(np.mean(res["n_iter"])) for res in r["job_result"]["results"]]
+        got = [model.predict("LogisticRegression", "iris-rounds", {"C": c, "max_iter": 500}) for c in (0.01, 1.0, 100.0)]
+        assert got == want and want[0] < want[2]                     # weak penalty on iris: many more iterations
+        assert model.predict("LogisticRegression", "iris", {"C": 100.0}) == flat          # other datasets: still the prior
+    finally:
+        m.close()
