@@ -34,6 +34,7 @@ SYMBOLS = {
                             C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p,
                             C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p,
                             C.c_int, C.c_int, C.c_void_p, C.c_void_p]),
+    "dml_last_cluster": (C.c_int, [C.c_void_p]),
     "dml_last_counters": (C.c_int, [C.c_void_p, C.POINTER(C.c_int64), C.POINTER(C.c_int32)]),
     "dml_score_static": (C.c_int, [C.c_int, C.c_void_p, C.c_void_p, C.c_int64, C.c_int, C.c_int64,
                                    C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p,
@@ -101,7 +102,8 @@ class Context:
         self.lib.dml_last_first_round(self.handle, C.byref(fm), C.byref(fc))
         return dict(total_ms=t.value, contraction_ms=c.value, contraction_launches=cl.value,
                     total_launches=tl.value, column_rounds=cr.value, rounds=rd.value,
-                    first_round_ms=fm.value, first_round_columns=fc.value)
+                    first_round_ms=fm.value, first_round_columns=fc.value,
+                    cluster=int(self.lib.dml_last_cluster(self.handle)))
 
     def close(self):
         if getattr(self, "handle", None):

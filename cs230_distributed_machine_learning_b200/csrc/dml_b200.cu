@@ -78,6 +78,7 @@ struct dml_ctx {
   int tc_mask_hi = 0;                 // 1 = write the masked hi operand back before the MMAs read it (not needed:
                                       // kind::tf32 ignores the 13 low mantissa bits, measured identical results)
   long long slot_rounds = 0; int rounds = 0;  // sum over rounds of evaluated columns
+  int last_cluster = 1;                       // what fwd_cluster decided for the last call's X (dml_last_cluster)
   // debug: scratch of the last evaluation (dml_debug_fetch)
   const void* dbg_ptr[4] = {nullptr, nullptr, nullptr, nullptr}; size_t dbg_bytes[4] = {0, 0, 0, 0};
 };
@@ -261,6 +262,8 @@ extern "C" int dml_last_first_round(dml_ctx* ctx, float* contraction_ms, int64_t
   return DML_OK;
 }
 
+extern "C" int dml_last_cluster(dml_ctx* ctx) { return ctx ? ctx->last_cluster : 0; }
+
 extern "C" int dml_last_counters(dml_ctx* ctx, int64_t* column_rounds, int32_t* rounds) {
   if (!ctx) return DML_ERR_ARG;
   if (column_rounds) *column_rounds = ctx->slot_rounds;
@@ -336,14 +339,55 @@ static bool tc_eligible(const float* X, int64_t ldx, int T) {
 
 // CTAs per cluster of the forward kernel.  With 2 the X tiles are loaded with TMA multicast, and
 // TMA multicast loads here read only this GPU's memory, since on B200 a TMA multicast load from
-// another GPU's memory hung the GPU.  X is the caller's pointer: unless the driver says it is device
-// memory of the context's own GPU, the kernel runs unclustered and every CTA loads its own tiles.
-static int fwd_cluster(dml_ctx* ctx, const void* X) {
-  if (ctx->tc_cluster != 2) return 1;
-  cudaPointerAttributes at{};
-  if (cudaPointerGetAttributes(&at, X) != cudaSuccess) { cudaGetLastError(); return 1; }
-  return (at.type == cudaMemoryTypeDevice && at.device == ctx->device) ? 2 : 1;
+// another GPU's memory hung the GPU.  X is the caller's pointer: unless the driver says that the whole
+// range the tensor map covers is device memory of the context's own GPU, the kernel runs unclustered
+// and every CTA loads its own tiles (plain TMA loads).
+// The tensor map covers [X, X + bytes), so the proof has to hold for every byte of that range, not
+// for the first one: the range must lie inside ONE allocation made with cudaMalloc / cuMemAlloc on
+// the context's GPU (such an allocation is device memory of a single GPU from end to end).  Memory
+// mapped with cuMemMap (a virtual range can stitch together handles of several GPUs), pool
+// allocations, IPC imports from a peer, managed and host memory, a range that straddles two
+// allocations, or any failed query all take the unclustered kernel.
+typedef CUresult (*PtrGetAttrFn)(void*, CUpointer_attribute, CUdeviceptr);
+typedef CUresult (*MemGetRangeFn)(CUdeviceptr*, size_t*, CUdeviceptr);
+static bool range_is_own_device_allocation(dml_ctx* ctx, const void* p, size_t bytes) {
+  static PtrGetAttrFn get_attr = nullptr;
+  static MemGetRangeFn get_range = nullptr;
+  if (!get_attr || !get_range) {
+    void* f1 = nullptr; void* f2 = nullptr;
+    cudaDriverEntryPointQueryResult q1, q2;
+    if (cudaGetDriverEntryPoint("cuPointerGetAttribute", &f1, cudaEnableDefault, &q1) != cudaSuccess ||
+        cudaGetDriverEntryPoint("cuMemGetAddressRange", &f2, cudaEnableDefault, &q2) != cudaSuccess ||
+        q1 != cudaDriverEntryPointSuccess || q2 != cudaDriverEntryPointSuccess || !f1 || !f2) {
+      cudaGetLastError();
+      return false;
+    }
+    get_attr = (PtrGetAttrFn)f1; get_range = (MemGetRangeFn)f2;
+  }
+  if (!p || bytes == 0) return false;
+  const CUdeviceptr first = (CUdeviceptr)(uintptr_t)p, last = first + bytes - 1;
+  if (last < first) return false;
+  for (CUdeviceptr q : {first, last}) {
+    cudaPointerAttributes at{};
+    if (cudaPointerGetAttributes(&at, (const void*)(uintptr_t)q) != cudaSuccess) { cudaGetLastError(); return false; }
+    if (at.type != cudaMemoryTypeDevice || at.device != ctx->device) return false;
+    unsigned int mtype = 0; int ordinal = -1; int legacy_ipc = 0;
+    if (get_attr(&mtype, CU_POINTER_ATTRIBUTE_MEMORY_TYPE, q) != CUDA_SUCCESS || mtype != CU_MEMORYTYPE_DEVICE) return false;
+    if (get_attr(&ordinal, CU_POINTER_ATTRIBUTE_DEVICE_ORDINAL, q) != CUDA_SUCCESS || ordinal != ctx->device) return false;
+    // true only for cuMemAlloc / cudaMalloc allocations: not for cuMemMap'd ranges, not for pool memory
+    if (get_attr(&legacy_ipc, CU_POINTER_ATTRIBUTE_IS_LEGACY_CUDA_IPC_CAPABLE, q) != CUDA_SUCCESS || !legacy_ipc) return false;
+  }
+  CUdeviceptr base = 0, base2 = 0; size_t size = 0, size2 = 0;
+  if (get_range(&base, &size, first) != CUDA_SUCCESS || get_range(&base2, &size2, last) != CUDA_SUCCESS) return false;
+  if (base != base2 || size != size2) return false;              // first and last byte in the same allocation
+  return first >= base && last - base < size;
 }
+// `bytes` = extent of the X tensor map: ((n - 1) * ldx + d) floats.
+static int fwd_cluster(dml_ctx* ctx, const void* X, size_t bytes) {
+  ctx->last_cluster = (ctx->tc_cluster == 2 && range_is_own_device_allocation(ctx, X, bytes)) ? 2 : 1;
+  return ctx->last_cluster;
+}
+static inline size_t x_extent_bytes(int64_t n, int d, int64_t ldx) { return ((size_t)(n - 1) * (size_t)ldx + (size_t)d) * sizeof(float); }
 
 template <int NC, int MODE, int CL>
 static int launch_tc_fwd_nc(dml_ctx* ctx, int grid, const CUtensorMap& mx, const CUtensorMap& mwh, const CUtensorMap& mwl,
@@ -446,7 +490,7 @@ static int run_score_tc(dml_ctx* ctx, int mode, const float* X, int64_t n, int d
   fp.mask_hi = ctx->tc_mask_hi; fp.prefetch_jobs = 0; fp.T = T; fp.loss_shift = 0.f;
   fp.tile_fold = tile_fold; fp.gstart = gstart; fp.n_groups = n_groups; fp.hold_group = hold_group;
   const int ncb = fp.n_col_blocks;
-  const int clr = (fwd_cluster(ctx, X) == 2 && ncb >= 2 && (ncb % 2 == 0 || ncb >= 5)) ? 2 : 1;
+  const int clr = (fwd_cluster(ctx, X, x_extent_bytes(n, d, ldx)) == 2 && ncb >= 2 && (ncb % 2 == 0 || ncb >= 5)) ? 2 : 1;
   const int64_t jobs = cdiv(n, 128) * cdiv(ncb, clr);
   const int grid = clr * (int)std::min<int64_t>(jobs, ctx->n_sms / clr);
   const size_t esz = mode == FWD_SCORE_REG ? sizeof(double) : sizeof(int32_t);
@@ -561,7 +605,7 @@ struct EvalCtx {
         ctx->r_budget = std::max<size_t>((size_t)1 << 30, std::min<size_t>((size_t)16 << 30, (free_b + ctx->ws_bytes) / 3));
       ctx->r_budget_known = true;
     }
-    cl = fwd_cluster(ctx, X); tc_rps_max = ctx->tc_rps;
+    cl = fwd_cluster(ctx, X, x_extent_bytes(n, d, ldx)); tc_rps_max = ctx->tc_rps;
     ldw = (int)rup(d, 4); ldg = (int)rup(d + 1, 4); ldgr = d + 2;
     tiles_total = cdiv(n, BM); tile_n = (BN / T) * T;
     NC = pick_nc(S_max, T); if (NC == 0) NC = 160;

@@ -162,6 +162,13 @@ int dml_last_timing(dml_ctx* ctx, float* total_ms, float* contraction_ms,
  * one column: 4*n_train*d flops), and the number of rounds. */
 int dml_last_counters(dml_ctx* ctx, int64_t* column_rounds, int32_t* rounds);
 
+/* CTAs per cluster the forward / scoring kernel of the last call ran with: 2 = the X tiles were
+ * shared by TMA multicast between two column blocks, which the library only does after the driver
+ * confirmed that the whole range [X, X + ((n-1)*ldx + d)*4) lies inside one cudaMalloc allocation
+ * of the context's own GPU; 1 = every CTA loaded its own tiles (any other kind of pointer).
+ * Diagnostic only; no counterpart in the reference. */
+int dml_last_cluster(dml_ctx* ctx);
+
 /* Round 0 of the last logistic sweep.  Every fit starts at w = 0
  * (sklearn/linear_model/_logistic.py:439,457), where z = 0 for every row and the
  * loss / gradient sums depend on the row mask only, so the sweep evaluates the
