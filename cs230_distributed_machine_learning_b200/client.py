@@ -60,7 +60,8 @@ def wire(payload):
 class LocalBackend:
     """Master + scheduler + worker threads in this process."""
 
-    def __init__(self, n_gpus: int | None = None, partition: str = "candidates", gpus: list[int] | None = None):
+    def __init__(self, n_gpus: int | None = None, partition: str = "candidates", gpus: list[int] | None = None,
+                 monitor_interval: float | None = 15.0):
         if gpus is not None:
             n_gpus = len(gpus)
         if n_gpus is None:
@@ -74,8 +75,11 @@ class LocalBackend:
         self.workers = [Worker(self.scheduler, gpu=g, slot=i) for i, g in enumerate(gpus or range(n_gpus))]
         for w in self.workers:
             w.start()
+        if monitor_interval:       # scheduler_service.py:205-225: dead-worker check every 15 s
+            self.scheduler.start_monitor(monitor_interval)
 
     def shutdown(self):
+        self.scheduler.stop_monitor()
         for w in self.workers:
             w.shutdown()
 

@@ -11,6 +11,8 @@
 #include <string.h>
 #include <stdlib.h>
 #include <algorithm>
+#include <atomic>
+#include <mutex>
 #include <vector>
 
 using namespace dml;
@@ -41,6 +43,18 @@ struct NcclApi {
 };
 static NcclApi g_nccl;
 static char g_create_err[512] = "";
+
+// cudaFuncSetAttribute acts on the current device's copy of a kernel, and one process may hold a ctx on
+// every GPU (worker.py runs one Worker thread per GPU): the opt-ins for more than 48 KB of dynamic shared
+// memory are therefore remembered per device.  Setting an attribute twice is harmless, so a flag that
+// two threads race to set needs no lock.
+constexpr int kMaxDevices = 64;
+struct DeviceOnce {
+  std::atomic<bool> done[kMaxDevices];
+  DeviceOnce() { for (auto& d : done) d.store(false); }
+  bool test(int dev) const { return dev >= 0 && dev < kMaxDevices && done[dev].load(std::memory_order_acquire); }
+  void set(int dev) { if (dev >= 0 && dev < kMaxDevices) done[dev].store(true, std::memory_order_release); }
+};
 
 struct dml_ctx {
   int device = 0;
@@ -392,10 +406,10 @@ static inline size_t x_extent_bytes(int64_t n, int d, int64_t ldx) { return ((si
 template <int NC, int MODE, int CL>
 static int launch_tc_fwd_nc(dml_ctx* ctx, int grid, const CUtensorMap& mx, const CUtensorMap& mwh, const CUtensorMap& mwl,
                             const tc::TcFwdParams& p) {
-  static bool attr_set = false;
-  if (!attr_set) {
+  static DeviceOnce attr_set;
+  if (!attr_set.test(ctx->device)) {
     CU(cudaFuncSetAttribute(tc::tc_fwd_kernel<NC, MODE, CL>, cudaFuncAttributeMaxDynamicSharedMemorySize, tc::FwdSmem<NC>::kBytes));
-    attr_set = true;
+    attr_set.set(ctx->device);
   }
   cudaLaunchConfig_t cfg{};
   cfg.gridDim = dim3((unsigned)grid); cfg.blockDim = dim3(tc::kFwdThreads);
@@ -423,10 +437,10 @@ static int launch_tc_fwd(dml_ctx* ctx, int NC, int cl, int grid, const CUtensorM
 // gradient kernel on CTA pairs: cluster of two along the feature-block axis (an odd block count leaves
 // the last pair's second CTA on zero-filled features), R map with a one-chunk box
 static int launch_tc_grad2(dml_ctx* ctx, dim3 grid, const CUtensorMap& mx, const CUtensorMap& mr, const tc::TcGradParams& p) {
-  static bool attr_set = false;
-  if (!attr_set) {
+  static DeviceOnce attr_set;
+  if (!attr_set.test(ctx->device)) {
     CU(cudaFuncSetAttribute(tc::tc_grad2_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, tc::Grad2Smem::kBytes));
-    attr_set = true;
+    attr_set.set(ctx->device);
   }
   cudaLaunchConfig_t cfg{};
   cfg.gridDim = grid; cfg.blockDim = dim3(tc::kGrad2Threads);
@@ -1165,10 +1179,10 @@ extern "C" int dml_ridge_sweep(dml_ctx* ctx, const float* X, int64_t n, int d, i
   }
   CUtensorMap mXg;
   if (use_tc) { int rc = make_map_2d(ctx, &mXg, X, d, n, ldx * 4, 32, 32, true); if (rc) return rc; }
-  static bool gram_attr = false;
-  if (use_tc && !gram_attr) {
+  static DeviceOnce gram_attr;
+  if (use_tc && !gram_attr.test(ctx->device)) {
     CU(cudaFuncSetAttribute(tc::tc_gram_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, tc::GramSmem::kBytes));
-    gram_attr = true;
+    gram_attr.set(ctx->device);
   }
   timing_begin(ctx);
   const bool xvec = (ldx % 4 == 0) && aligned16(X);
@@ -1245,11 +1259,11 @@ extern "C" int dml_ridge_sweep(dml_ctx* ctx, const float* X, int64_t n, int d, i
     ridge_assemble_kernel<<<dim3(32, nsys), 256, 0, st>>>(sp);
     if (d <= kCholMaxD) {
       const size_t chol_smem = ((size_t)d * (kCholNB + 1) + 1 + (size_t)kCholNB * (kCholNB + 2)) * sizeof(double);
-      static bool chol_attr = false;
-      if (!chol_attr) {
+      static DeviceOnce chol_attr;
+      if (!chol_attr.test(ctx->device)) {
         CU(cudaFuncSetAttribute(ridge_cholesky_blocked_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                 (int)(((size_t)kCholMaxD * (kCholNB + 1) + 1 + (size_t)kCholNB * (kCholNB + 2)) * sizeof(double))));
-        chol_attr = true;
+        chol_attr.set(ctx->device);
       }
       const int threads = (int)std::min<int64_t>(640, rup(d, 32));
       ridge_cholesky_blocked_kernel<<<nsys, threads, chol_smem, st>>>(d_A, d_AT, d_B, d, T, d_info + c0 * fpc);
@@ -1319,26 +1333,45 @@ extern "C" int dml_score(dml_ctx* ctx, const float* X, int64_t n, int d, int64_t
   CU(cudaSetDevice(ctx->device));
   cudaStream_t st = ctx->stream;
   const int64_t tiles_total = cdiv(n, BM);
+  const bool cls = y_cls != nullptr && correct_out != nullptr;
+  if (!cls && (!sse_out || !y_reg)) return fail(ctx, DML_ERR_ARG, "dml_score: regression scoring needs y_reg and sse_out");
+  // tensor-core scoring (the kernel the sweeps use) whenever the shape allows: TMA needs 16-byte aligned
+  // rows of X; the coefficients are copied into a padded scratch copy, so W may have any d
+  const bool use_tc = tc_eligible(X, ldx, T) && (cls || T == 1);
+  const int ldw = use_tc ? (int)rup(d, 4) : d;
   void* d_part; long long* d_cnt; double* d_sse;
+  float *d_Wt = nullptr, *d_Whi = nullptr, *d_Wlo = nullptr;
   for (int pass = 0; pass < 2; ++pass) {
     Arena a(pass ? ctx->ws : nullptr);
-    d_part = a.take<float>((size_t)tiles_total * n_slots);
+    if (use_tc) {
+      d_part = a.take<double>((size_t)ctx->n_sms * 4 * n_slots);
+      d_Wt = a.take<float>((size_t)n_slots * ldw); d_Whi = a.take<float>((size_t)n_slots * ldw); d_Wlo = a.take<float>((size_t)n_slots * ldw);
+    } else {
+      d_part = a.take<float>((size_t)tiles_total * n_slots);
+    }
     d_cnt = a.take<long long>(n_slots); d_sse = a.take<double>(n_slots);
     if (!pass) { int rc = ensure_ws(ctx, a.off + 256); if (rc) return rc; }
   }
   timing_begin(ctx);
-  const bool cls = y_cls != nullptr && correct_out != nullptr;
-  int rc = run_score(ctx, cls ? FWD_SCORE_CLS : FWD_SCORE_REG, X, n, d, ldx, y_cls, y_reg, fold_id, hold_id,
-                     W, d, b, mask_sel, mask_val, n_slots, T, d_part);
+  int rc; int64_t n_parts = tiles_total;
+  if (use_tc) {
+    if (ldw > d) CU(cudaMemsetAsync(d_Wt, 0, sizeof(float) * (size_t)n_slots * ldw, st));
+    CU(cudaMemcpy2DAsync(d_Wt, (size_t)ldw * 4, W, (size_t)d * 4, (size_t)d * 4, n_slots, cudaMemcpyDeviceToDevice, st));
+    rc = run_score_tc(ctx, cls ? FWD_SCORE_CLS : FWD_SCORE_REG, X, n, d, ldx, y_cls, y_reg, fold_id, hold_id,
+                      d_Wt, ldw, b, mask_sel, mask_val, n_slots, T, d_Whi, d_Wlo, d_part, &n_parts);
+  } else {
+    rc = run_score(ctx, cls ? FWD_SCORE_CLS : FWD_SCORE_REG, X, n, d, ldx, y_cls, y_reg, fold_id, hold_id,
+                   W, d, b, mask_sel, mask_val, n_slots, T, d_part);
+  }
   if (rc) return rc;
   if (cls) {
-    reduce_counts_kernel<<<n_slots / T, 256, 0, st>>>((const int32_t*)d_part, tiles_total, n_slots, T, d_cnt);
+    reduce_counts_kernel<<<n_slots / T, 256, 0, st>>>((const int32_t*)d_part, n_parts, n_slots, T, d_cnt);
     KCHECK();
     if (ctx->comm) { rc = allreduce(ctx, d_cnt, n_slots / T, kNcclInt64); if (rc) return rc; }
     CU(cudaMemcpyAsync(correct_out, d_cnt, sizeof(int64_t) * (n_slots / T), cudaMemcpyDeviceToDevice, st));
   } else {
-    if (!sse_out || !y_reg) return fail(ctx, DML_ERR_ARG, "dml_score: regression scoring needs y_reg and sse_out");
-    reduce_sse_kernel<<<n_slots, 256, 0, st>>>((const float*)d_part, tiles_total, n_slots, d_sse);
+    if (use_tc) reduce_sse_parts_kernel<<<(unsigned)cdiv(n_slots, 128), 128, 0, st>>>((const double*)d_part, n_parts, n_slots, d_sse, n_slots, 1, 0);
+    else reduce_sse_kernel<<<n_slots, 256, 0, st>>>((const float*)d_part, tiles_total, n_slots, d_sse);
     KCHECK();
     if (ctx->comm) { rc = allreduce(ctx, d_sse, n_slots, kNcclFloat64); if (rc) return rc; }
     CU(cudaMemcpyAsync(sse_out, d_sse, sizeof(double) * n_slots, cudaMemcpyDeviceToDevice, st));
@@ -1363,8 +1396,8 @@ constexpr size_t kStaticScoreInts = (size_t)1 << 20;   // 1 Mi int32 = 4 MiB
 static __device__ __align__(256) int32_t g_score_scratch[kStaticScoreInts];
 // Host code must not hand `g_score_scratch` itself to a kernel: on the host that name is only a
 // stand-in for the symbol.  The device address is looked up once per device, below.
-constexpr int kMaxDevices = 64;
 static int32_t* g_score_scratch_dev[kMaxDevices] = {nullptr};
+static std::mutex g_score_scratch_mu;   // two threads may make the first call on a device at the same time
 
 extern "C" int dml_score_static(int device, void* stream_v, const float* X, int64_t n, int d, int64_t ldx,
                                 const int32_t* y_cls, const int8_t* fold_id, const int8_t* hold_id,
@@ -1384,14 +1417,18 @@ extern "C" int dml_score_static(int device, void* stream_v, const float* X, int6
                 (long long)(tiles * n_slots), (unsigned long long)kStaticScoreInts);
   if (cdiv(n_slots, tile_n) > 65535) return fail(ctx, DML_ERR_LIMIT, "dml_score_static: too many columns (%d)", n_slots);
   CU(cudaSetDevice(device));
-  if (!g_score_scratch_dev[device]) {
-    // one-time set-up on this device (no allocation: address lookup + a function attribute)
-    int32_t* ptr = nullptr;
-    CU(cudaGetSymbolAddress((void**)&ptr, g_score_scratch));
-    CU(cudaFuncSetAttribute(fwd_kernel<FWD_SCORE_CLS>, cudaFuncAttributeMaxDynamicSharedMemorySize, kFwdSmemBytes));
-    g_score_scratch_dev[device] = ptr;
+  int32_t* part = nullptr;
+  {
+    std::lock_guard<std::mutex> guard(g_score_scratch_mu);
+    if (!g_score_scratch_dev[device]) {
+      // one-time set-up on this device (no allocation: address lookup + a function attribute)
+      int32_t* ptr = nullptr;
+      CU(cudaGetSymbolAddress((void**)&ptr, g_score_scratch));
+      CU(cudaFuncSetAttribute(fwd_kernel<FWD_SCORE_CLS>, cudaFuncAttributeMaxDynamicSharedMemorySize, kFwdSmemBytes));
+      g_score_scratch_dev[device] = ptr;
+    }
+    part = g_score_scratch_dev[device];
   }
-  int32_t* part = g_score_scratch_dev[device];
   cudaStream_t st = (cudaStream_t)stream_v;
   // The array still holds the previous call's partial counts.  Every entry this call reads is
   // written by it first, but the used part is zeroed anyway so that stale counts can never leak.

@@ -72,16 +72,32 @@ __global__ void ridge_assemble_kernel(const RidgeSysParams p) {
 
 // In-place lower Cholesky of A (row-major, only the lower triangle is read/written),
 // then L L^T W = B for T right-hand sides.  One block per system.
+// A pivot (squared diagonal entry of L before the square root) below kRidgePivotTol times the largest
+// diagonal entry of A marks the system as numerically rank-deficient: the Gram matrix is accumulated at
+// fp32 / 3xTF32 accuracy (about 1e-7 of its diagonal), so such a pivot is mostly noise and the solution
+// is not the one LAPACK gives scikit-learn in float64 (which, for LinearRegression, is the minimum-norm
+// lstsq solution, and for Ridge falls back to SVD on LinAlgError, _ridge.py:753-761).  Reported as
+// info = -(j + 1); the worker re-runs such candidates on the scikit-learn executor.
+constexpr double kRidgePivotTol = 1e-4;
+__device__ __forceinline__ double max_diag(const double* A, int d, double* red) {
+  double m = 0.0;
+  for (int j = threadIdx.x; j < d; j += blockDim.x) m = fmax(m, fabs(A[(int64_t)j * d + j]));
+  return block_reduce<true>(m, red);
+}
 __global__ void __launch_bounds__(512) ridge_cholesky_kernel(double* Aall, double* Ball, int d, int T, int* info) {
   extern __shared__ double colj[];  // [d]
   __shared__ double piv;
+  __shared__ double red[33];
   double* A = Aall + (int64_t)blockIdx.x * d * d;
   double* B = Ball + (int64_t)blockIdx.x * T * d;
   const int nw = blockDim.x >> 5, w = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const double small = kRidgePivotTol * max_diag(A, d, red);
+  int weak = 0;
   for (int j = 0; j < d; ++j) {
     if (threadIdx.x == 0) {
       const double a = A[(int64_t)j * d + j];
       if (!(a > 0.0)) atomicExch(info + blockIdx.x, j + 1);  // not positive definite
+      else if (a < small && !weak) weak = j + 1;
       piv = sqrt(a > 0.0 ? a : 1.0);
     }
     __syncthreads();
@@ -100,6 +116,7 @@ __global__ void __launch_bounds__(512) ridge_cholesky_kernel(double* Aall, doubl
     }
     __syncthreads();
   }
+  if (threadIdx.x == 0 && weak && info[blockIdx.x] == 0) info[blockIdx.x] = -weak;
   // forward then backward substitution, one right-hand side at a time
   for (int t = 0; t < T; ++t) {
     double* b = B + (int64_t)t * d;
@@ -133,12 +150,14 @@ __global__ void __launch_bounds__(640) ridge_cholesky_blocked_kernel(double* Aal
   double* P = sm;                     // [d][PP] panel rows k0..d-1
   double* Lk = sm + (((size_t)d * PP + 1) & ~(size_t)1);   // [NB][NB+2] staged rows of L (16-byte aligned): Lk[jj][c] = L[k0 + c][j0 + jj]
   __shared__ double piv;
-  __shared__ int bad;
+  __shared__ int bad, weak;
+  __shared__ double red[33];
   double* A = Aall + (int64_t)blockIdx.x * d * d;
   double* AT = ATall + (int64_t)blockIdx.x * d * d;
   double* B = Ball + (int64_t)blockIdx.x * T * d;
   const int t = threadIdx.x;
-  if (t == 0) bad = 0;
+  if (t == 0) { bad = 0; weak = 0; }
+  const double small = kRidgePivotTol * max_diag(A, d, red);
   for (int k0 = 0; k0 < d; k0 += NB) {
     const int nc = min(NB, d - k0), nr = d - k0;
     const int r = k0 + t;                              // this thread's row (valid when t < nr)
@@ -174,6 +193,7 @@ __global__ void __launch_bounds__(640) ridge_cholesky_blocked_kernel(double* Aal
       if (t == 0) {
         const double a = P[(size_t)j * PP + j];
         if (!(a > 0.0)) { bad = k0 + j + 1; }
+        else if (a < small && !weak) weak = k0 + j + 1;
         piv = sqrt(a > 0.0 ? a : 1.0);
       }
       __syncthreads();
@@ -199,7 +219,7 @@ __global__ void __launch_bounds__(640) ridge_cholesky_blocked_kernel(double* Aal
     }
     __syncthreads();
   }
-  if (t == 0 && bad) atomicExch(info + blockIdx.x, bad);
+  if (t == 0 && (bad || weak)) atomicExch(info + blockIdx.x, bad ? bad : -weak);
   // Blocked substitution, one right-hand side at a time: the vector lives in shared memory, a 32 x 32
   // diagonal block is solved by one warp with shuffles, and every thread then updates its own row with the
   // 32 new unknowns (coalesced reads of L^T going forward, of L going backward).  Two block barriers per 32

@@ -15,6 +15,7 @@ import threading
 import numpy as np
 
 _REGISTRY: dict[str, tuple[np.ndarray, np.ndarray]] = {}
+_VERSION: dict[str, int] = {}      # bumped by every registration: device copies and row labels are cached per version
 _LOCK = threading.Lock()
 
 
@@ -25,6 +26,15 @@ def register_dataset(name: str, X, y) -> None:
         X = X.astype(np.float64)
     with _LOCK:
         _REGISTRY[name] = (X, np.asarray(y))
+        _VERSION[name] = _VERSION.get(name, 0) + 1
+
+
+def dataset_version(name: str) -> int:
+    """How many times ``name`` has been registered.  The reference re-reads the CSV for every subtask
+    (worker.py:425) and so always sees current data; the GPU executor keeps device copies across jobs
+    and drops them when this number changes."""
+    with _LOCK:
+        return _VERSION.get(name, 0)
 
 
 def get_dataset(name: str):

@@ -65,15 +65,19 @@ def create_subtasks(job_config: dict) -> list[dict]:
 
 
 def create_blocks(subtasks: list[dict], n_gpus: int = 1, partition: str = "candidates",
-                  cost: list[float] | None = None) -> list[dict]:
+                  cost: list[float] | None = None, extra_train_params: dict | None = None) -> list[dict]:
     """Regroup per-candidate subtasks into per-GPU block subtasks.
 
     A block keeps the subtask keys and adds ``candidates`` [{index, subtask_id,
     parameters}], ``folds``, ``gpu`` and ``partition``.  "candidates": GPU g gets
     candidates g, g+G, g+2G, ... (round-robin spreads slow large-C columns);
-    "rows": every GPU gets all candidates and a row shard (needs one process per
-    GPU with NCCL, see bench.py).  A block with a single candidate and all folds is
-    the legacy subtask.
+    "rows": every GPU gets all candidates and row shard ``shard`` of ``n_shards``
+    (dist.row_slice); the workers run the sweep together and the library sums
+    gradients / moments / counts over NCCL (worker.train_model).  A block with a
+    single candidate and all folds is the legacy subtask.  ``extra_train_params``
+    (the search's ``scoring`` / ``return_train_score``, which the reference client
+    serialises under cv_params and nobody reads, core.py:123-130) is merged into the
+    block's ``train_params``; the per-candidate subtasks stay as the reference makes them.
 
     ``cost`` (one predicted number of batched rounds per candidate, ``IterationModel``)
     replaces the round-robin deal by longest-first dealing: candidates sorted by cost,
@@ -97,11 +101,14 @@ def create_blocks(subtasks: list[dict], n_gpus: int = 1, partition: str = "candi
         blocks.append({
             "subtask_id": f"{first['job_id']}-block-{g + 1}",
             "job_id": first["job_id"], "session_id": first["session_id"], "dataset_id": first["dataset_id"],
-            "model_type": first["model_type"], "train_params": copy.deepcopy(first.get("train_params", {})),
+            "model_type": first["model_type"],
+            "train_params": {**copy.deepcopy(first.get("train_params", {})), **(extra_train_params or {}),
+                             **({"shard_group": f"{n_gpus}gpus"} if partition == "rows" else {})},
             "candidates": [{"index": i, "subtask_id": s["subtask_id"], "parameters": s["parameters"]}
                            for i, s in zip(own, mine)],
             "folds": list(range(cv)) if isinstance(cv, int) else cv,
             "gpu": g, "partition": partition, "n_shards": n_gpus if partition == "rows" else 1,
+            "shard": g if partition == "rows" else 0,
         })
     return blocks
 
@@ -195,8 +202,9 @@ def _nan_if_none(v):
     return np.nan if v is None else float(v)
 
 
-def build_cv_results(candidates: list[dict], fold_scores) -> dict:
-    """cv_results_-style dict + best_* (sklearn _search.py:1208-1294, 862-874)."""
+def build_cv_results(candidates: list[dict], fold_scores, train_scores=None) -> dict:
+    """cv_results_-style dict + best_* (sklearn _search.py:1208-1294, 862-874).  ``train_scores``
+    (return_train_score=True) adds split{k}_train_score / mean_train_score / std_train_score."""
     a = np.asarray(fold_scores, dtype=np.float64)
     n_cand, n_folds = a.shape
     mean = np.average(a, axis=1)
@@ -210,6 +218,12 @@ def build_cv_results(candidates: list[dict], fold_scores) -> dict:
     res = {f"split{k}_test_score": a[:, k].tolist() for k in range(n_folds)}
     res.update(mean_test_score=mean.tolist(), std_test_score=std.tolist(), rank_test_score=rank.tolist(),
                params=candidates)
+    if train_scores is not None:
+        t = np.asarray(train_scores, dtype=np.float64)
+        tm = np.average(t, axis=1)
+        res.update({f"split{k}_train_score": t[:, k].tolist() for k in range(t.shape[1])})
+        res.update(mean_train_score=tm.tolist(),
+                   std_train_score=np.sqrt(np.average((t - tm[:, None]) ** 2, axis=1)).tolist())
     keys = sorted({k for c in candidates for k in c})
     for k in keys:
         res[f"param_{k}"] = [c.get(k) for c in candidates]
@@ -230,6 +244,7 @@ class Master:
         self.sessions: set[str] = set()
         self.jobs: dict[tuple[str, str], dict] = {}
         self.lock = threading.Lock()
+        self.submit_lock = threading.Lock()
         self.iterations = IterationModel()      # rounds per candidate, learnt from finished jobs
         scheduler.attach_master(self)
 
@@ -269,8 +284,19 @@ class Master:
         n_gpus = self.n_gpus or max(1, self.scheduler.n_workers())
         with self.lock:
             cost = [self.iterations.predict(st["model_type"], st["dataset_id"], st["parameters"]) for st in subtasks]
-        for block in create_blocks(subtasks, n_gpus=n_gpus, partition=self.partition, cost=cost):
-            self.scheduler.submit(block)       # topic "tasks"
+        cvp = details.get("hyperparameters", {}).get("cv_params", {}) if "search_type" in details else {}
+        extra = {}
+        if cvp.get("scoring") is not None:
+            extra["scoring"] = cvp["scoring"]
+        if cvp.get("return_train_score"):
+            extra["return_train_score"] = True
+        partition = payload.get("train_params", {}).get("partition", self.partition)
+        blocks = create_blocks(subtasks, n_gpus=n_gpus, partition=partition, cost=cost, extra_train_params=extra)
+        # one step for all blocks of a job: the workers of a row-sharded job meet in collectives, so every
+        # worker's queue must hold the jobs' blocks in the same order
+        with self.submit_lock:
+            for block in blocks:
+                self.scheduler.submit(block)       # topic "tasks"
         return {"status": "Training started", "job_id": payload["job_id"], "total_subtasks": len(subtasks)}
 
     # topic "result" consumer (task_handler.py:18-123)
@@ -278,25 +304,42 @@ class Master:
         key = (message.get("session_id"), message.get("job_id"))
         with self.lock:
             job = self.jobs.get(key) or next((j for (s, jid), j in self.jobs.items() if jid == message.get("job_id")), None)
-            if job is None:
-                return
+            if job is None or job["status"] == "completed":
+                return          # at-least-once delivery: a requeued block may report a finished job again
             entries = message["result"] if isinstance(message.get("result"), list) else [message]
             if message.get("subtask_id") == f"{job['job_id']}-refit":
+                if not entries or "pending_result" not in job:
+                    return
                 e = entries[0]
                 ok = e.get("status", message.get("status")) == "completed"
                 self._complete(job, job.pop("pending_result"), e.get("result") if ok else None,
                                None if ok else e.get("error", message.get("error", "failed")))
                 return
+            if job.get("aggregated"):
+                return          # all candidates are in and the refit is under way
+            known = {st["subtask_id"] for st in job["subtasks"]}
+            fresh = 0
             for e in entries:
                 sid = e.get("subtask_id", message.get("subtask_id"))
+                if sid not in known or sid in job["results"]:
+                    continue    # not a candidate of this job (a block id), or already recorded (another shard / a rerun)
+                fresh += 1
                 if e.get("status", message.get("status")) == "completed":
                     job["results"][sid] = e.get("result", e)
+                    job["failed"].pop(sid, None)
                 else:
                     job["failed"][sid] = e.get("error", message.get("error", "failed"))
+            if isinstance(message.get("result"), list) and message.get("status") == "failed" and not entries:
+                for sid in known - set(job["results"]):
+                    job["failed"][sid] = message.get("error", "failed")
+                    fresh += 1
             total = len(job["subtasks"])
             finished = len(job["results"]) + len(job["failed"])
             job["status"] = str(len(job["results"]) / total * 100.0)
-            refit_task = self._finish(job) if finished == total else None
+            refit_task = None
+            if fresh and finished == total:
+                job["aggregated"] = True
+                refit_task = self._finish(job)
         if refit_task is not None:
             self.scheduler.submit(refit_task)
 
@@ -325,7 +368,10 @@ class Master:
             cands = [{k: st["parameters"][k] for k in keys if k in st["parameters"]} for st in job["subtasks"]]
             nf = max(len(r.get("cv_scores", [])) for r in ordered)
             scores = [list(r.get("cv_scores", [])) + [float("nan")] * (nf - len(r.get("cv_scores", []))) for r in ordered]
-            out.update(build_cv_results(cands, scores))
+            train = None
+            if all("train_scores" in r or "error" in r for r in ordered) and any("train_scores" in r for r in ordered):
+                train = [list(r.get("train_scores", [])) + [float("nan")] * (nf - len(r.get("train_scores", []))) for r in ordered]
+            out.update(build_cv_results(cands, scores, train))
         best = out.get("best_index_")
         if job["refit"] and best is not None and np.isfinite(out["best_score_"]):
             st = job["subtasks"][best]       # best candidate again, all rows, one more block subtask

@@ -33,6 +33,10 @@ class Scheduler:
         self.workers: dict[str, dict] = {}
         self.master = None
         self.backlog: list[dict] = []
+        self.mailbox: dict[str, bytes] = {}
+        self.mail_cv = threading.Condition()
+        self.monitor = None
+        self.monitor_stop = threading.Event()
 
     def attach_master(self, master) -> None:
         self.master = master
@@ -144,6 +148,38 @@ class Scheduler:
             t = dict(t)
             t.pop("gpu", None)               # any surviving GPU may take it
             self.submit(t)
+
+    # side channel between the workers of one job (Redis in the reference's deployment): the worker of row
+    # shard 0 posts the 128-byte ncclUniqueId of a new communicator, the other shards' workers wait for it
+    def exchange(self, key: str, payload: bytes | None = None, timeout: float = 120.0) -> bytes:
+        with self.mail_cv:
+            if payload is not None:
+                self.mailbox[key] = payload
+                self.mail_cv.notify_all()
+                return payload
+            if not self.mail_cv.wait_for(lambda: key in self.mailbox, timeout):
+                raise TimeoutError(f"nothing was posted under {key!r} within {timeout} s")
+            return self.mailbox[key]
+
+    # monitor loop (scheduler_service.py:205-225): every `interval` seconds drop workers whose last
+    # heartbeat is older than HEARTBEAT_TIMEOUT_S and hand their tasks to the survivors
+    def start_monitor(self, interval: float = 15.0) -> None:
+        if self.monitor is not None:
+            return
+        self.monitor_stop.clear()
+
+        def loop():
+            while not self.monitor_stop.wait(interval):
+                try:
+                    self.reap_dead_workers()
+                except Exception:
+                    pass
+        self.monitor = threading.Thread(target=loop, daemon=True, name="scheduler-monitor")
+        self.monitor.start()
+
+    def stop_monitor(self) -> None:
+        self.monitor_stop.set()
+        self.monitor = None
 
     def workers_view(self) -> dict:      # GET /workers
         with self.lock:

@@ -91,14 +91,16 @@ class SweepSolver:
         self.d2h_bytes += t.numel() * t.element_size()
         return t.cpu().numpy()
 
-    def upload_dataset(self, X, y, classifier: bool, stream=None) -> DeviceDataset:
+    def upload_dataset(self, X, y, classifier: bool, stream=None, classes=None) -> DeviceDataset:
         """X (n, d) any float dtype -> fp32 on device; y -> class indices or fp32.
-        With ``stream`` the copies are queued there and ``ready`` holds the event to wait on."""
+        With ``stream`` the copies are queued there and ``ready`` holds the event to wait on.
+        ``classes`` (sorted unique labels of the WHOLE dataset) is for row shards: a shard may miss a
+        class, and every rank must number the classes alike."""
         if stream is not None:
             with torch.cuda.stream(stream):
                 t0 = torch.cuda.Event(enable_timing=True)
                 t0.record(stream)
-                ds = self.upload_dataset(X, y, classifier)
+                ds = self.upload_dataset(X, y, classifier, classes=classes)
                 ds.ready = torch.cuda.Event(enable_timing=True)
                 ds.ready.record(stream)
                 ds.copy_events = (t0, ds.ready)
@@ -112,9 +114,13 @@ class SweepSolver:
         n, d = Xd.shape
         if isinstance(y, torch.Tensor):
             y = y.cpu().numpy()
-        key = (id(y), classifier)
+        key = (id(y), classifier, None if classes is None else len(classes))
         if key not in self._class_cache:      # label encoding of a registered dataset is computed once,
-            if classifier:                    # into page-locked memory so that its copy is asynchronous
+            if classifier and classes is not None:
+                classes = np.asarray(classes)
+                idx = np.searchsorted(classes, np.asarray(y))
+                enc = torch.from_numpy(idx.astype(np.int32)).pin_memory()
+            elif classifier:                  # into page-locked memory so that its copy is asynchronous
                 classes, idx = np.unique(np.asarray(y), return_inverse=True)
                 enc = torch.from_numpy(idx.astype(np.int32)).pin_memory()
             else:
@@ -245,6 +251,12 @@ class SweepSolver:
                                 _ptr(val_d), n_slots, T, _ptr(correct), _ptr(sse))
         self.ctx.check(rc, "dml_score")
         return self.to_host(correct) if cls else self.to_host(sse)
+
+    def score_all_rows(self, ds: DeviceDataset, fold_id, W, b, T: int):
+        """Counts (classifier) or squared errors (regressor) of every column over ALL rows of the dataset:
+        the columns select the hold label with value 0, and without a hold array every row carries 0."""
+        n_slots = np.asarray(W).shape[0]
+        return self.score(ds, fold_id, W, b, np.ones(n_slots, np.int32), np.zeros(n_slots, np.int32), T, hold_id=None)
 
     def close(self):
         self.ctx.close()

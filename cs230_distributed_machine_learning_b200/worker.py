@@ -23,6 +23,7 @@ candidate to "b200" exactly when the model/solver is covered and X is float32.
 from __future__ import annotations
 
 import inspect
+import logging
 import os
 import pickle
 import threading
@@ -34,6 +35,9 @@ import numpy as np
 from . import datasets, folds
 
 HEARTBEAT_INTERVAL_S = 5.0   # worker.py:33
+log = logging.getLogger("dml_b200.worker")
+# scorers the GPU path forms from the sums its scoring pass produces (cv_params.scoring, core.py:123-130)
+GPU_SCORINGS = {True: (None, "accuracy"), False: (None, "r2", "neg_mean_squared_error")}
 
 MODEL_IMPORTS = {   # worker.py:36-57 plus the two north-star models
     "RandomForestClassifier": "sklearn.ensemble", "RandomForestRegressor": "sklearn.ensemble",
@@ -171,9 +175,13 @@ def train_candidate_sklearn(model_type: str, parameters: dict, train_params: dic
         t0 = time.time()
         # cross_val_score (worker.py:326,341) is cross_validate()["test_score"]; the fitted fold models come back too
         # so that the result can say how many L-BFGS iterations each fold took (master.IterationModel)
-        cvr = cross_validate(model, X, y, cv=train_params.get("cv", 5), scoring="accuracy" if clf else "r2",
-                             error_score="raise", return_estimator=True)
+        cvr = cross_validate(model, X, y, cv=train_params.get("cv", 5),
+                             scoring=train_params.get("scoring") or ("accuracy" if clf else "r2"),
+                             error_score="raise", return_estimator=True,
+                             return_train_score=bool(train_params.get("return_train_score")))
         scores = cvr["test_score"]
+        if "train_score" in cvr:
+            results["train_scores"] = [float(v) for v in cvr["train_score"]]
         results.setdefault("training_time", (time.time() - t0) / max(1, len(scores)))
         if model_type == "LogisticRegression":
             results["n_iter"] = [int(np.max(e.n_iter_)) for e in cvr["estimator"]]
@@ -197,7 +205,9 @@ class GpuExecutor:
         import torch
         self.gpu = gpu
         self.solver = SweepSolver(gpu)
-        self.resident: dict[tuple[str, bool], object] = {}   # insertion order = least recently used first
+        self.resident: dict[tuple, object] = {}       # (name, classifier[, shard, n_shards]); insertion order = LRU first
+        self.versions: dict[str, int] = {}            # datasets.dataset_version() the cached copies belong to
+        self.shard_solvers: dict[tuple[int, int], object] = {}   # (n_shards, shard) -> SweepSolver with an NCCL comm
         self.labels: dict[tuple, np.ndarray] = {}     # host-side row labels, computed once per dataset
         self.labels_dev: dict[tuple, object] = {}
         self.pinned: set[int] = set()
@@ -227,12 +237,24 @@ class GpuExecutor:
                 continue
             total -= self.resident.pop(key).nbytes
 
+    def _check_version(self, name: str) -> None:
+        """A name registered again is a new dataset: drop its device copies and row labels
+        (the reference re-reads the CSV for every subtask, worker.py:425).  Call under res_lock."""
+        v = datasets.dataset_version(name)
+        if self.versions.get(name) == v:
+            return
+        for cache in (self.resident, self.labels, self.labels_dev):
+            for key in [k for k in cache if k[0] == name]:
+                del cache[key]
+        self.versions[name] = v
+
     def prefetch(self, name: str, classifier: bool) -> bool:
         """Start the host->device copy of a dataset a queued task will need, on the copy
         stream, while the current sweep runs (the reference parses the CSV again inside
         every subtask, worker.py:425).  Returns True when a copy was queued."""
         key = (name, classifier)
         with self.res_lock:
+            self._check_version(name)
             if key in self.resident:
                 return False
             X, y = datasets.get_dataset(name)
@@ -244,21 +266,50 @@ class GpuExecutor:
             self.prefetched += 1
             return True
 
-    def dataset(self, name: str, classifier: bool):
-        key = (name, classifier)
+    def dataset(self, name: str, classifier: bool, shard: tuple[int, int] | None = None, solver=None):
+        """Device copy of a registered dataset; ``shard`` = (index, count) keeps only that row slice
+        (dist.row_slice) on this GPU, with the class numbering of the whole dataset."""
+        key = (name, classifier) if shard is None else (name, classifier, shard[0], shard[1])
+        solver = solver or self.solver
         with self.res_lock:
+            self._check_version(name)
             if key not in self.resident:   # the reference re-parses the CSV per subtask (worker.py:425)
                 X, y = datasets.get_dataset(name)
-                self._evict(incoming=X.nbytes)
-                self._pin(X)
-                self.resident[key] = self.solver.upload_dataset(X, y, classifier)
+                if shard is not None:
+                    from .dist import row_slice
+                    lo, hi = row_slice(X.shape[0], shard[1], shard[0])
+                    classes = np.unique(np.asarray(y)) if classifier else None
+                    X, y = X[lo:hi], np.asarray(y)[lo:hi]
+                    self._evict(incoming=X.nbytes)
+                    self.resident[key] = solver.upload_dataset(X, y, classifier, classes=classes)
+                else:
+                    self._evict(incoming=X.nbytes)
+                    self._pin(X)
+                    self.resident[key] = solver.upload_dataset(X, y, classifier)
             ds = self.resident.pop(key)
             self.resident[key] = ds        # most recently used
             self.in_use = key
         if ds.ready is not None:           # uploaded by prefetch: order the sweep's stream after the copy
-            self.solver.stream.wait_event(ds.ready)
+            solver.stream.wait_event(ds.ready)
             ds.ready = None
         return ds
+
+    def shard_solver(self, n_shards: int, shard: int, exchange, group: str):
+        """The SweepSolver of this GPU for row-sharded blocks: its own context, joined to an NCCL
+        communicator of ``n_shards`` ranks (dml_ctx_init_comm).  Created on the first row-sharded block;
+        ``exchange(key, payload)`` is the side channel that carries shard 0's 128-byte ncclUniqueId to the
+        other workers (Scheduler.exchange here; Redis in the reference's deployment).  Collective: every
+        worker of the shard set must get here, which the master guarantees by queueing a job's blocks to
+        all workers in one step."""
+        key = (n_shards, shard)
+        if key not in self.shard_solvers:
+            from . import _cabi
+            from .solver import SweepSolver
+            sv = SweepSolver(self.gpu)
+            uid = exchange(f"nccl-uid/{group}/{n_shards}", _cabi.nccl_unique_id() if shard == 0 else None)
+            sv.init_comm(n_shards, shard, uid)
+            self.shard_solvers[key] = sv
+        return self.shard_solvers[key]
 
     def _pin(self, X: np.ndarray) -> None:
         """Page-lock a registered float32 array in place (once), so every later upload is a
@@ -270,7 +321,10 @@ class GpuExecutor:
         if int(rc) == 0:
             self.pinned.add(id(X))
 
-    def row_labels(self, dataset_id: str, classifier: bool, cv: int, n: int, y_host, test_size=None, random_state=None):
+    def row_labels(self, dataset_id: str, classifier: bool, cv: int, n: int, y_host, test_size=None, random_state=None,
+                   shard: tuple[int, int] | None = None, solver=None):
+        """Fold labels (and hold-out labels) of the WHOLE dataset, computed once on the host; the device
+        copy holds this GPU's rows of them (all, or its row shard)."""
         key = (dataset_id, classifier, cv)
         if key not in self.labels:
             if classifier:
@@ -284,51 +338,75 @@ class GpuExecutor:
             if hkey not in self.labels:
                 self.labels[hkey] = folds.holdout_labels(n, test_size, random_state)
             hold = self.labels[hkey]
-        return self._on_device(key), (self._on_device(hkey) if hold is not None else None)
+        return self._on_device(key, shard, solver), (self._on_device(hkey, shard, solver) if hold is not None else None)
 
-    def _on_device(self, key):
+    def _on_device(self, key, shard: tuple[int, int] | None = None, solver=None):
         """Row labels go to the GPU once per dataset and stay (1 byte per row)."""
         import torch
-        if key not in self.labels_dev:
-            self.labels_dev[key] = self.solver.to_device(self.labels[key], torch.int8)
-        return self.labels_dev[key]
+        dkey = key if shard is None else key + ("shard",) + tuple(shard)
+        if dkey not in self.labels_dev:
+            lab = self.labels[key]
+            if shard is not None:
+                from .dist import row_slice
+                lo, hi = row_slice(len(lab), shard[1], shard[0])
+                lab = lab[lo:hi]
+            self.labels_dev[dkey] = (solver or self.solver).to_device(lab, torch.int8)
+        return self.labels_dev[dkey]
 
-    def run(self, model_type: str, cands: list[dict], train_params: dict, dataset_id: str, model_dir: str) -> list[dict]:
-        """cands: [{index, subtask_id, parameters}] -> result dict per candidate (A9 shape)."""
+    def run(self, model_type: str, cands: list[dict], train_params: dict, dataset_id: str, model_dir: str,
+            shard: tuple[int, int] | None = None, exchange=None) -> list[dict]:
+        """cands: [{index, subtask_id, parameters}] -> result dict per candidate (A9 shape).
+
+        ``shard`` = (index, count): this GPU holds rows dist.row_slice(n, count, index) and the sweep runs
+        together with the other shards' workers, the library summing gradients / moments / counts over NCCL
+        (SURVEY.md 8e-2); every shard returns the same, complete results."""
         classifier = model_type not in REGRESSORS
         with self.lock:
-            ds = self.dataset(dataset_id, classifier)
+            X_host, y_host = datasets.get_dataset(dataset_id)
+            n_total = X_host.shape[0]
+            solver = self.solver
+            if shard is not None:
+                if exchange is None:
+                    raise ValueError("a row-sharded block needs the scheduler's exchange channel")
+                solver = self.shard_solver(shard[1], shard[0], exchange, group=str(train_params.get("shard_group", "default")))
+            ds = self.dataset(dataset_id, classifier, shard, solver)
             hint, self.hint = self.hint, None
-            if hint is not None and hint != (dataset_id, classifier):
+            if hint is not None and hint != (dataset_id, classifier) and shard is None:
                 try:
                     self.prefetch(*hint)          # the next task's copy runs beside this sweep
                 except Exception:
                     pass
-            X_host, y_host = datasets.get_dataset(dataset_id)
             cv = train_params.get("cv", 5)
             if not isinstance(cv, int):
                 raise ValueError("the GPU executor takes an integer cv (un-shuffled (Stratified)KFold)")
             refit = bool(train_params.get("refit_fit"))
-            fold, hold = self.row_labels(dataset_id, classifier, cv, ds.n, y_host,
+            fold, hold = self.row_labels(dataset_id, classifier, cv, n_total, y_host,
                                          None if refit else train_params.get("test_size"),
-                                         train_params.get("random_state"))
+                                         train_params.get("random_state"), shard, solver)
             if refit:        # the all-rows fit is the "hold-out" fit of an empty hold-out set
                 zkey = (dataset_id, "all-rows")
                 if zkey not in self.labels:
-                    self.labels[zkey] = np.zeros(ds.n, dtype=np.int8)
-                hold = self._on_device(zkey)
+                    self.labels[zkey] = np.zeros(n_total, dtype=np.int8)
+                hold = self._on_device(zkey, shard, solver)
             P = [c["parameters"] for c in cands]
             fi = [bool(p.get("fit_intercept", True)) for p in P]
             if refit and model_type == "LogisticRegression":
                 cv = 0           # only the all-rows column; Ridge keeps its folds (one Gram pass either way)
             t0 = time.time()
             if model_type == "LogisticRegression":
-                out = self.solver.logreg_sweep(
+                out = solver.logreg_sweep(
                     ds, fold, cv, [float(p.get("C", 1.0)) for p in P], [float(p.get("tol", 1e-4)) for p in P], fi,
                     [int(p.get("max_iter", 100)) for p in P], hold_id=hold, want_scores=not refit)
             else:
                 alphas = [0.0 if model_type == "LinearRegression" else float(p.get("alpha", 1.0)) for p in P]
-                out = self.solver.ridge_sweep(ds, fold, cv, alphas, fi, classifier=classifier, hold_id=hold)
+                out = solver.ridge_sweep(ds, fold, cv, alphas, fi, classifier=classifier, hold_id=hold)
+            train_all = None
+            if train_params.get("return_train_score") and not refit and cv > 0:
+                # counts / squared errors of every CV fit over ALL rows; minus the test rows = the training rows
+                T = out["coef"].shape[2]
+                W = out["coef"][:, :cv].reshape(-1, out["coef"].shape[3])
+                b = out["intercept"][:, :cv].reshape(-1)
+                train_all = solver.score_all_rows(ds, fold, W, b, T).reshape(len(cands), cv)
             wall = time.time() - t0
             if len(self.stats["sweep_ms"]) < 4096:
                 self.stats["sweep_ms"].append(out["timing"]["total_ms"])
@@ -340,9 +418,17 @@ class GpuExecutor:
                 self.in_use = None
                 self._evict()
         n_fits = len(cands) * (cv + (hold is not None))
+        scoring = train_params.get("scoring")
         results = []
         for i, c in enumerate(cands):
             r = {}
+            info = out.get("info")
+            if info is not None and np.any(info[i] != 0):
+                # the Cholesky factorisation met a non-positive or negligible pivot (dml_ridge_sweep, info_out):
+                # scikit-learn answers such systems with lstsq / SVD; the caller re-runs the candidate there
+                results.append({"rerun_on_sklearn": f"rank-deficient normal equations (info={info[i].tolist()})",
+                                "parameters": c["parameters"]})
+                continue
             if refit:
                 r.update(refit=True, training_time=wall, coef=out["coef"][i][cv].tolist(),
                          intercept=out["intercept"][i][cv].tolist())
@@ -352,25 +438,41 @@ class GpuExecutor:
                 else:
                     sst = out["syy"][i] - out["sy"][i] ** 2 / out["n_test"][i]
                     sc = 1.0 - out["sse"][i] / sst
+                    if scoring == "neg_mean_squared_error":
+                        sc = -out["sse"][i] / out["n_test"][i]
                 cvs = sc[:cv]
                 if hold is not None:
                     if classifier:
-                        r["accuracy"] = float(sc[cv])
+                        r["accuracy"] = float(out["correct"][i][cv] / out["n_test"][i][cv])
                     else:
-                        r["r2_score"] = float(sc[cv])
+                        sst_h = out["syy"][i][cv] - out["sy"][i][cv] ** 2 / out["n_test"][i][cv]
+                        r["r2_score"] = float(1.0 - out["sse"][i][cv] / sst_h)
                         r["mean_squared_error"] = float(out["sse"][i][cv] / out["n_test"][i][cv])
                 r["cv_scores"] = [float(v) for v in cvs]
                 r["mean_cv_score"] = float(np.mean(cvs))
                 r["training_time"] = wall / n_fits
+                if train_all is not None:
+                    n_tr = n_total - out["n_test"][i][:cv]
+                    if classifier:
+                        tr = (train_all[i] - out["correct"][i][:cv]) / n_tr
+                    else:
+                        sse_tr = train_all[i] - out["sse"][i][:cv]
+                        sy_tr = out["sy"][i][:cv].sum() - out["sy"][i][:cv]
+                        syy_tr = out["syy"][i][:cv].sum() - out["syy"][i][:cv]
+                        tr = (-sse_tr / n_tr) if scoring == "neg_mean_squared_error" else \
+                            (1.0 - sse_tr / (syy_tr - sy_tr ** 2 / n_tr))
+                    r["train_scores"] = [float(v) for v in tr]
             r["model_id"] = f"{c['subtask_id']}_model"
             r["model_path"] = None
-            if hold is not None and model_dir:      # worker.py:351-356: the fitted model is pickled
+            if hold is not None and model_dir and (shard is None or shard[0] == 0):   # worker.py:351-356: the fitted model is pickled
                 n_it = out["n_iter"][i][cv] if model_type == "LogisticRegression" else None
                 est = fitted_estimator(model_type, c["parameters"], out["coef"][i][cv], out["intercept"][i][cv],
                                        ds.classes if classifier else None, n_it)
                 r["model_path"] = save_model(est, model_dir, r["model_id"])
             r["parameters"] = c["parameters"]
             r["executor"] = "b200"
+            if shard is not None:
+                r["row_shards"] = shard[1]
             if model_type == "LogisticRegression":
                 r["n_iter"] = [int(v) for v in out["n_iter"][i]]
                 r["fit_status"] = [int(v) for v in out["status"][i]]
@@ -402,9 +504,14 @@ def _as_block(task: dict) -> dict:
     return t
 
 
-def train_model(task: dict, gpu: int = 0, model_dir: str = "./models"):
+def train_model(task: dict, gpu: int = 0, model_dir: str = "./models", exchange=None):
     """worker.py:289.  Returns the reference's result dict for a legacy subtask, or a
-    list of {subtask_id, status, result|error} for a block subtask."""
+    list of {subtask_id, status, result|error} for a block subtask.
+
+    A block with ``partition == "rows"`` and ``n_shards > 1`` is one of n_shards identical blocks, one per
+    GPU: this worker keeps row shard ``block["shard"]`` and runs the sweep together with the others
+    (``exchange`` = the scheduler's side channel for the NCCL id).  Every shard computes the complete
+    results; only shard 0 reports them, the others report an empty list."""
     block = _as_block(task)
     model_type = block["model_type"]
     tp = block.get("train_params", {})
@@ -412,22 +519,48 @@ def train_model(task: dict, gpu: int = 0, model_dir: str = "./models"):
     choice = _executor_choice(block)
     if choice not in ("auto", "b200", "sklearn"):
         raise ValueError(f"unknown executor {choice!r}")
+    shard = None
+    if block.get("partition") == "rows" and int(block.get("n_shards", 1)) > 1:
+        shard = (int(block.get("shard", block.get("gpu", 0))), int(block["n_shards"]))
+        if choice == "sklearn":
+            raise ValueError("row shards exist on the b200 executor only")
+    classifier = model_type not in REGRESSORS
+    scoring_ok = tp.get("scoring") in GPU_SCORINGS[classifier]
     on_gpu, on_cpu = [], []
     for c in block["candidates"]:
         ok, why = gpu_eligible(model_type, c["parameters"])
-        if choice == "b200" and not ok:
+        if ok and not scoring_ok:
+            ok, why = False, f"scoring={tp.get('scoring')!r}"
+        if ok and choice == "auto" and X.dtype != np.float32:
+            ok, why = False, f"X is {X.dtype}: float64 problems are computed in float64 by scikit-learn"
+        if (choice == "b200" or shard is not None) and not ok:
             raise ValueError(f"executor 'b200' cannot run {model_type}({why})")
-        if choice == "sklearn" or not ok or (choice == "auto" and X.dtype != np.float32):
+        if choice == "sklearn" or not ok:
+            if choice == "auto":       # never silent: say which candidate leaves the GPU path and why
+                log.warning("candidate %s (%s) runs on the scikit-learn executor: %s", c["subtask_id"], model_type, why)
+            c = dict(c, why=why if choice == "auto" else "executor='sklearn'")
             on_cpu.append(c)
         else:
             on_gpu.append(c)
     entries = {}
     if on_gpu:
-        for c, r in zip(on_gpu, gpu_executor(gpu).run(model_type, on_gpu, tp, block["dataset_id"], model_dir)):
-            entries[c["subtask_id"]] = {"subtask_id": c["subtask_id"], "status": "completed", "result": r}
+        got = gpu_executor(gpu).run(model_type, on_gpu, tp, block["dataset_id"], model_dir, shard=shard, exchange=exchange)
+        for c, r in zip(on_gpu, got):
+            if "rerun_on_sklearn" in r:
+                if shard is not None:
+                    raise ValueError(f"row-sharded block: {r['rerun_on_sklearn']}")
+                log.warning("candidate %s (%s) re-runs on the scikit-learn executor: %s", c["subtask_id"], model_type,
+                            r["rerun_on_sklearn"])
+                on_cpu.append(dict(c, why=r["rerun_on_sklearn"], rerouted=True))
+            else:
+                entries[c["subtask_id"]] = {"subtask_id": c["subtask_id"], "status": "completed", "result": r}
     for c in on_cpu:
         try:
             r = train_candidate_sklearn(model_type, c["parameters"], tp, X, y, c["subtask_id"], model_dir)
+            if c.get("rerouted"):
+                r["rerouted"] = c["why"]
+            elif choice == "auto":
+                r["executor_reason"] = c["why"]
             entries[c["subtask_id"]] = {"subtask_id": c["subtask_id"], "status": "completed", "result": r}
         except Exception as e:   # worker.py:264-286: a failing fit is reported, not raised
             if "candidates" not in task:
@@ -436,6 +569,8 @@ def train_model(task: dict, gpu: int = 0, model_dir: str = "./models"):
     ordered = [entries[c["subtask_id"]] for c in block["candidates"]]
     if "candidates" not in task:
         return ordered[0]["result"]
+    if shard is not None and shard[0] != 0:
+        return []                   # shard 0 reports for the set
     return ordered
 
 
@@ -448,6 +583,8 @@ def _gpu_block_key(task) -> tuple | None:
         choice = _executor_choice(block)
         if choice == "sklearn":
             return None
+        if block.get("partition") == "rows" and int(block.get("n_shards", 1)) > 1:
+            return None   # a row-sharded block uploads its own slice; nothing to copy ahead
         if not any(gpu_eligible(block["model_type"], c["parameters"])[0] for c in block["candidates"]):
             return None
         if choice == "auto" and datasets.get_dataset(block["dataset_id"])[0].dtype != np.float32:
@@ -476,9 +613,9 @@ def prefetch_task(task: dict, gpu: int = 0, current: dict | None = None) -> bool
     return True
 
 
-def process_task(task: dict, gpu: int = 0):
+def process_task(task: dict, gpu: int = 0, exchange=None):
     """worker.py:366-387."""
-    return train_model(task, gpu=gpu)
+    return train_model(task, gpu=gpu, exchange=exchange)
 
 
 class Worker(threading.Thread):
@@ -525,7 +662,7 @@ class Worker(threading.Thread):
         except Exception:
             psutil, cpu0, mem0 = None, 0.0, 0.0
         try:
-            result = process_task(task, gpu=self.gpu or 0)
+            result = process_task(task, gpu=self.gpu or 0, exchange=getattr(self.scheduler, "exchange", None))
             message = {"subtask_id": task["subtask_id"], "job_id": task["job_id"], "session_id": task.get("session_id"),
                        "status": "completed", "result": result}
         except Exception as e:

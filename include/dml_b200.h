@@ -87,7 +87,12 @@ int dml_logreg_sweep(dml_ctx* ctx, const float* X, int64_t n, int d, int64_t ldx
  *   classifier: correct_out / n_test_out as above (sse/sy/syy may be NULL)
  *   regressor : sse_out = sum (y - yhat)^2, sy_out = sum y, syy_out = sum y^2 over
  *               the held-out rows (fp64); R^2 = 1 - sse / (syy - sy^2 / n_test)
- *   info_out  [n_fits] int32: 0 ok, j+1 = pivot j not positive (system skipped) */
+ *   info_out  [n_fits] int32: 0 ok; j+1 = pivot j of the Cholesky factorisation was not positive (the
+ *               coefficients of that fit are meaningless); -(j+1) = pivot j was below 1e-4 of the largest
+ *               diagonal entry, i.e. the system is rank-deficient at the accuracy of the fp32 Gram matrix
+ *               and the result is not the one LAPACK gives scikit-learn in float64 (min-norm lstsq for
+ *               LinearRegression, SVD fallback for Ridge, _ridge.py:753-761).  A caller should hand fits
+ *               with info != 0 to the scikit-learn executor (worker.py does). */
 int dml_ridge_sweep(dml_ctx* ctx, const float* X, int64_t n, int d, int64_t ldx,
                     const float* y_reg, const int32_t* y_cls, int n_classes, int is_classifier,
                     const int8_t* fold_id, int n_folds, const int8_t* hold_id,

@@ -5,10 +5,13 @@ Some users of the library run it where a cudaMalloc at call time is not an optio
 a side stream while a sweep owns the GPU (cudaMalloc/cudaFree would serialise the
 device).  dml_score_static keeps its scratch in a fixed array inside the library,
 so it only launches kernels.  This file checks, through the C ABI, that it returns
-exactly what dml_score returns (integer counts: the tolerance is zero), twice in a
-row on different problems -- the second call finds the first call's leftovers in
-the shared array -- and that a request larger than the fixed array is refused with
-a message instead of being run.  It is collected last (file name) so a failure
+what dml_score returns and what a float64 numpy recount of the same predictions
+gives (integer counts: they may differ only by rows whose decision value is within
+1e-5 of a tie, and the number of such rows is the tolerance -- dml_score runs on the
+tensor cores in 3xTF32, this entry point on CUDA cores in fp32), twice in a row on
+different problems -- the second call finds the first call's leftovers in the shared
+array and must return the very same integers -- and that a request larger than the
+fixed array is refused with a message instead of being run.  It is collected last (file name) so a failure
 here cannot hide the result of any other test, and it needs nothing from the
 tests before it: it passes alone in a fresh process as well.
 """
@@ -57,12 +60,28 @@ def test_static_scratch_scoring_equals_dml_score_twice_in_a_row(solver):
         sel = np.zeros(n_slots, np.int32)
         val = np.repeat(np.arange(n_slots // T) % cv, T).astype(np.int32)
         want = solver.score(ds, fold, W, b, sel, val, T=T)           # existing entry point (ctx arena)
+        # float64 recount on the host: the anchor for both entry points
+        z = X.astype(np.float64) @ W.T.astype(np.float64) + b.astype(np.float64)
+        exact = np.zeros(n_slots // T, np.int64)
+        slack = np.zeros(n_slots // T, np.int64)
+        for g in range(n_slots // T):
+            rows = fold == val[g * T]
+            zz = z[rows][:, g * T:(g + 1) * T]
+            if T == 1:
+                exact[g] = int(((zz[:, 0] > 0).astype(np.int64) == y[rows]).sum())
+                slack[g] = int((np.abs(zz[:, 0]) < 1e-5).sum())
+            else:
+                exact[g] = int((zz.argmax(axis=1) == y[rows]).sum())
+                top = np.sort(zz, axis=1)
+                slack[g] = int(((top[:, -1] - top[:, -2]) < 1e-5).sum())
         rc, got = _score_static(ds, fold_d, W, b, sel, val, T)
         assert rc == 0, _cabi.load().dml_last_error(None)
-        np.testing.assert_array_equal(got, want)                      # integer counts: exact
+        assert (np.abs(got - exact) <= slack).all(), (got, exact, slack)        # against numpy
+        assert (np.abs(got - want) <= slack).all(), (got, want, slack)          # against dml_score
+        assert (np.abs(want - exact) <= slack).all(), (want, exact, slack)
         rc, again = _score_static(ds, fold_d, W, b, sel, val, T)      # same call on a dirty array
         assert rc == 0
-        np.testing.assert_array_equal(again, want)
+        np.testing.assert_array_equal(again, got)                     # leftovers of the first call do not leak
 
 
 def test_static_scratch_limit_is_enforced(solver):

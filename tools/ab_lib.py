@@ -1,4 +1,4 @@
-"""Manual A/B helper (not a pytest file): python tests/ab_lib.py STEPS LIB_A.so LIB_B.so ...
+"""Manual A/B helper (not a pytest file): python tools/ab_lib.py STEPS LIB_A.so LIB_B.so ...
 Compares builds of the library: copies each file over libdml_b200.so in turn (interleaved twice), runs
 bench.py --no-e2e --no-cpu-baseline and prints one line per run; the last file stays in place."""
 import json, os, shutil, subprocess, sys

@@ -1,4 +1,4 @@
-"""Manual A/B helper (not a pytest file): python tests/ab_run.py STEPS VAR=a,b [VAR2=c,d] ...
+"""Manual A/B helper (not a pytest file): python tools/ab_run.py STEPS VAR=a,b [VAR2=c,d] ...
 Runs bench.py --no-e2e --no-cpu-baseline once per value (interleaved twice) and prints one line each."""
 import json, os, subprocess, sys
 steps = sys.argv[1]

@@ -1,5 +1,5 @@
 """Manual timing (not a pytest file): BASELINE.json config 5 (binary, 256 C x 10 folds, 16M x 512) ROW-SHARDED
-over the GPUs of one box.  torchrun --nproc-per-node N tests/cfg5_rows.py [rows]
+over the GPUs of one box.  torchrun --nproc-per-node N tools/cfg5_rows.py [rows]
 Every rank generates its own row slice on its GPU (device data of the named shape), the ranks share one NCCL
 communicator inside the library (dml_ctx_init_comm) and each calls the same sweep on its slice."""
 import os, sys, time

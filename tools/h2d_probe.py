@@ -1,5 +1,5 @@
 """Manual probe (not a pytest file): host->device bandwidth of each rank alone and of all ranks at once.
-torchrun --nproc-per-node N tests/h2d_probe.py"""
+torchrun --nproc-per-node N tools/h2d_probe.py"""
 import os, time, torch, torch.distributed as dist
 rank, world = int(os.environ.get("RANK", 0)), int(os.environ.get("WORLD_SIZE", 1))
 torch.cuda.set_device(int(os.environ.get("LOCAL_RANK", 0)))
