@@ -35,6 +35,7 @@ SYMBOLS = {
                             C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p,
                             C.c_int, C.c_int, C.c_void_p, C.c_void_p]),
     "dml_last_cluster": (C.c_int, [C.c_void_p]),
+    "dml_last_comm": (C.c_int, [C.c_void_p, C.POINTER(C.c_float), C.POINTER(C.c_int32), C.POINTER(C.c_double)]),
     "dml_last_counters": (C.c_int, [C.c_void_p, C.POINTER(C.c_int64), C.POINTER(C.c_int32)]),
     "dml_score_static": (C.c_int, [C.c_int, C.c_void_p, C.c_void_p, C.c_int64, C.c_int, C.c_int64,
                                    C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p,
@@ -100,7 +101,10 @@ class Context:
         self.lib.dml_last_counters(self.handle, C.byref(cr), C.byref(rd))
         fm, fc = C.c_float(), C.c_int64()
         self.lib.dml_last_first_round(self.handle, C.byref(fm), C.byref(fc))
-        return dict(total_ms=t.value, contraction_ms=c.value, contraction_launches=cl.value,
+        cm, cc, cb = C.c_float(), C.c_int32(), C.c_double()
+        self.lib.dml_last_comm(self.handle, C.byref(cm), C.byref(cc), C.byref(cb))
+        return dict(allreduce_ms=cm.value, allreduce_calls=cc.value, allreduce_bytes=cb.value,
+                    total_ms=t.value, contraction_ms=c.value, contraction_launches=cl.value,
                     total_launches=tl.value, column_rounds=cr.value, rounds=rd.value,
                     first_round_ms=fm.value, first_round_columns=fc.value,
                     cluster=int(self.lib.dml_last_cluster(self.handle)))

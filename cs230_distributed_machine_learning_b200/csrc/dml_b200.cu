@@ -64,6 +64,8 @@ struct dml_ctx {
   int n_sms = 148;
   char err[512] = "";
   ncclComm_t comm = nullptr; int n_ranks = 1, rank = 0;
+  std::vector<cudaEvent_t> ev_comm; size_t ev_comm_used = 0;   // pairs around each ncclAllReduce of the last call
+  float comm_ms = 0.f; int comm_calls = 0; double comm_bytes = 0.0;
   // timing of the last sweep
   std::vector<cudaEvent_t> ev;  // pairs
   size_t ev_used = 0;
@@ -145,6 +147,7 @@ static void timing_begin(dml_ctx* ctx) {
   ctx->slot_rounds = 0; ctx->rounds = 0;
   ctx->total_ms = ctx->contraction_ms = 0.f;
   ctx->first_pairs = 0; ctx->first_ms = 0.f; ctx->first_cols = 0;
+  ctx->ev_comm_used = 0; ctx->comm_ms = 0.f; ctx->comm_calls = 0; ctx->comm_bytes = 0.0;
   cudaEventRecord(ctx->ev_total[0], ctx->stream);
 }
 static void timing_end(dml_ctx* ctx) {
@@ -160,12 +163,20 @@ static void timing_end(dml_ctx* ctx) {
     }
   }
   ctx->contraction_ms = acc;
+  for (size_t i = 0; i + 1 < ctx->ev_comm_used; i += 2) {
+    float ms = 0.f;
+    if (cudaEventElapsedTime(&ms, ctx->ev_comm[i], ctx->ev_comm[i + 1]) == cudaSuccess) ctx->comm_ms += ms;
+  }
 }
 
 static int allreduce(dml_ctx* ctx, void* buf, size_t count, int dtype) {
   if (!ctx->comm) return DML_OK;
+  const bool timed = ctx->ev_comm_used + 2 <= ctx->ev_comm.size();
+  if (timed) cudaEventRecord(ctx->ev_comm[ctx->ev_comm_used], ctx->stream);
   const int rc = g_nccl.AllReduce(buf, buf, count, dtype, kNcclSum, ctx->comm, ctx->stream);
   if (rc != 0) return fail(ctx, DML_ERR_NCCL, "ncclAllReduce failed: %s", g_nccl.GetErrorString ? g_nccl.GetErrorString(rc) : "?");
+  if (timed) { cudaEventRecord(ctx->ev_comm[ctx->ev_comm_used + 1], ctx->stream); ctx->ev_comm_used += 2; }
+  ctx->comm_calls += 1; ctx->comm_bytes += (double)count * 8.0;   // every reduced type here is 8 bytes wide
   return DML_OK;
 }
 
@@ -223,6 +234,7 @@ extern "C" void dml_ctx_destroy(dml_ctx* ctx) {
   if (ctx->ws) cudaFree(ctx->ws);
   if (ctx->h_scalar) cudaFreeHost(ctx->h_scalar);
   for (auto& ev : ctx->ev) cudaEventDestroy(ev);
+  for (auto& ev : ctx->ev_comm) cudaEventDestroy(ev);
   cudaEventDestroy(ctx->ev_total[0]); cudaEventDestroy(ctx->ev_total[1]);
   if (ctx->ev_round[0]) cudaEventDestroy(ctx->ev_round[0]);
   if (ctx->ev_round[1]) cudaEventDestroy(ctx->ev_round[1]);
@@ -246,6 +258,16 @@ extern "C" int dml_ctx_init_comm(dml_ctx* ctx, int n_ranks, int rank, const void
   const int rc = g_nccl.CommInitRank(&ctx->comm, n_ranks, id, rank);
   if (rc != 0) return fail(ctx, DML_ERR_NCCL, "ncclCommInitRank failed: %s", g_nccl.GetErrorString ? g_nccl.GetErrorString(rc) : "?");
   ctx->n_ranks = n_ranks; ctx->rank = rank;
+  ctx->ev_comm.resize(2 * 512);
+  for (auto& ev : ctx->ev_comm) CU(cudaEventCreate(&ev));
+  return DML_OK;
+}
+
+extern "C" int dml_last_comm(dml_ctx* ctx, float* allreduce_ms, int32_t* allreduce_calls, double* allreduce_bytes) {
+  if (!ctx) return DML_ERR_ARG;
+  if (allreduce_ms) *allreduce_ms = ctx->comm_ms;
+  if (allreduce_calls) *allreduce_calls = ctx->comm_calls;
+  if (allreduce_bytes) *allreduce_bytes = ctx->comm_bytes;
   return DML_OK;
 }
 

@@ -81,3 +81,41 @@ def make_dataset(kind: str, n: int, d: int, seed: int, chunk: int = 1 << 18):
             t = xc.astype(np.float64) @ w + 0.5 * rng.standard_normal(b - a)
             y[a:b] = t if kind == "regression" else (t > 0)
     return X, y
+
+
+CHUNK_ROWS = 1 << 18
+
+
+def make_dataset_rows(kind: str, n: int, d: int, seed: int, lo: int = 0, hi: int | None = None, threads: int = 4):
+    """Rows [lo, hi) of a synthetic dataset whose bytes depend only on (kind, n, d, seed): chunk c (2^18 rows)
+    is drawn from ``default_rng([seed, c])`` and the planted weights from ``default_rng([seed, 2**31 - 1])``,
+    so any row range can be produced on its own -- by the rank that owns the row shard (BASELINE.json config
+    5: 16M x 512 is 32.8 GB, no rank ever holds all of it on the host) or by an oracle checking a slice.
+    Same distributions as ``make_dataset``, different stream.  lo must be chunk-aligned."""
+    from concurrent.futures import ThreadPoolExecutor
+    hi = n if hi is None else hi
+    if lo % CHUNK_ROWS:
+        raise ValueError("lo must be a multiple of CHUNK_ROWS")
+    multi = kind.startswith("multiclass")
+    k = int(kind[len("multiclass"):] or 10) if multi else 0
+    rw = np.random.default_rng([seed, 2 ** 31 - 1])
+    W = rw.standard_normal((d, k)) / np.sqrt(d) if multi else rw.standard_normal(d) / np.sqrt(d)
+    X = np.empty((hi - lo, d), dtype=np.float32)
+    y = np.empty(hi - lo, dtype=np.float32 if kind == "regression" else np.int32)
+
+    def fill(c):
+        a, full = c * CHUNK_ROWS, min(n, (c + 1) * CHUNK_ROWS)     # the whole chunk is drawn (the stream position of
+        b = min(hi, full)                                           # the noise depends on it), then cut to [lo, hi)
+        rng = np.random.default_rng([seed, c])
+        xc = rng.standard_normal((full - a, d), dtype=np.float32)
+        X[a - lo:b - lo] = xc[:b - a]
+        if multi:
+            yc = np.argmax(xc.astype(np.float64) @ W + rng.gumbel(size=(full - a, k)), axis=1)
+        else:
+            t = xc.astype(np.float64) @ W + 0.5 * rng.standard_normal(full - a)
+            yc = t if kind == "regression" else (t > 0)
+        y[a - lo:b - lo] = yc[:b - a]
+    chunks = range(lo // CHUNK_ROWS, -(-hi // CHUNK_ROWS))
+    with ThreadPoolExecutor(max(1, threads)) as pool:
+        list(pool.map(fill, chunks))
+    return X, y

@@ -59,3 +59,19 @@ def max_over_ranks(value: float, device=None) -> float:
     if dist.is_initialized() and dist.get_world_size() > 1:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
     return float(t.item())
+
+
+def replicate_rows(X: np.ndarray, device, group, rank: int, world: int) -> torch.Tensor:
+    """A full copy of ``X`` on ``device`` of every rank, moving each row over the host link once in total:
+    rank r copies rows [r * per, (r + 1) * per) (per = ceil(n / world)) from its host array and one
+    all-gather completes the replicas (NCCL over NVLink on the GPU box, gloo in the CPU tests).
+    Collective over ``group``; every rank must hold the same ``X``."""
+    n, d = X.shape
+    per = -(-n // world)
+    full = torch.empty((per * world, d), dtype=torch.float32, device=device)
+    lo, hi = min(n, rank * per), min(n, (rank + 1) * per)
+    stage = torch.zeros((per, d), dtype=torch.float32, device=device)
+    if hi > lo:
+        stage[:hi - lo].copy_(torch.from_numpy(X[lo:hi]), non_blocking=True)
+    dist.all_gather_into_tensor(full.view(-1), stage.view(-1), group=group)
+    return full[:n]

@@ -85,3 +85,34 @@ def holdout_labels(n: int, test_size, random_state) -> np.ndarray:
     lab = np.zeros(n, dtype=np.int8)
     lab[perm[:n_test]] = 1
     return lab
+
+
+def stratified_labels_slice(y_local: np.ndarray, before: np.ndarray, total: np.ndarray, first_seen: np.ndarray,
+                            n_folds: int) -> np.ndarray:
+    """``stratified_labels`` for a row shard, without the other shards' labels (row-sharded sweeps whose
+    dataset never exists in one place, BASELINE.json config 5).
+
+    y_local    class indices 0..K-1 of this shard's rows, in row order
+    before[k]  members of class k in the rows that precede this shard
+    total[k]   members of class k in the whole dataset
+    first_seen[k]  global row index of the first member of class k (classes are numbered by first
+               appearance, _split.py:774-842)
+    The j-th member (0-based, in row order) of a class gets the fold whose block of that class's quota
+    contains j -- exactly what the un-sharded routine assigns."""
+    y_local = np.asarray(y_local).astype(np.intp, copy=False)
+    K = len(total)
+    order = np.empty(K, dtype=np.int64)
+    order[np.argsort(np.asarray(first_seen), kind="stable")] = np.arange(K)   # class -> id by first appearance
+    cnt = np.zeros(K, dtype=np.int64)
+    cnt[order] = np.asarray(total, dtype=np.int64)                            # counts in first-appearance numbering
+    starts = np.concatenate(([0], np.cumsum(cnt)[:-1]))
+    out = np.empty(y_local.shape[0], dtype=np.int8)
+    f = np.arange(n_folds)
+    for k in range(K):
+        e = order[k]
+        quota = cnt[e] // n_folds + (((f - starts[e]) % n_folds) < (cnt[e] % n_folds))
+        edges = np.cumsum(quota)
+        rows = np.nonzero(y_local == k)[0]
+        j = int(before[k]) + np.arange(rows.shape[0])
+        out[rows] = np.searchsorted(edges, j, side="right").astype(np.int8)
+    return out

@@ -91,7 +91,20 @@ class SweepSolver:
         self.d2h_bytes += t.numel() * t.element_size()
         return t.cpu().numpy()
 
-    def upload_dataset(self, X, y, classifier: bool, stream=None, classes=None) -> DeviceDataset:
+    def upload_replicated(self, X: np.ndarray, replica) -> torch.Tensor:
+        """X for a GPU that is one of ``world`` replicas of the same dataset on one box (candidate blocks,
+        one process per GPU): this rank copies rows [rank * per, (rank + 1) * per) over its own PCIe link and
+        the replicas complete each other with one NCCL all-gather over NVLink, so the host side moves the
+        dataset once instead of ``world`` times.  Collective: every rank of ``group`` must upload the same
+        dataset in the same order.  ``replica`` = (process group, rank, world)."""
+        from .dist import replicate_rows
+        group, rank, world = replica
+        n = X.shape[0]
+        per = -(-n // world)
+        self.h2d_bytes += max(0, min(n, (rank + 1) * per) - min(n, rank * per)) * X.shape[1] * 4
+        return replicate_rows(X, self.device, group, rank, world)
+
+    def upload_dataset(self, X, y, classifier: bool, stream=None, classes=None, replica=None) -> DeviceDataset:
         """X (n, d) any float dtype -> fp32 on device; y -> class indices or fp32.
         With ``stream`` the copies are queued there and ``ready`` holds the event to wait on.
         ``classes`` (sorted unique labels of the WHOLE dataset) is for row shards: a shard may miss a
@@ -100,7 +113,7 @@ class SweepSolver:
             with torch.cuda.stream(stream):
                 t0 = torch.cuda.Event(enable_timing=True)
                 t0.record(stream)
-                ds = self.upload_dataset(X, y, classifier, classes=classes)
+                ds = self.upload_dataset(X, y, classifier, classes=classes, replica=replica)
                 ds.ready = torch.cuda.Event(enable_timing=True)
                 ds.ready.record(stream)
                 ds.copy_events = (t0, ds.ready)
@@ -108,7 +121,10 @@ class SweepSolver:
                 if t is not None:
                     t.record_stream(self.stream)
             return ds
-        Xd = self.to_device(X, torch.float32)
+        if replica is not None and isinstance(X, np.ndarray) and X.dtype == np.float32 and X.ndim == 2 and replica[2] > 1:
+            Xd = self.upload_replicated(X, replica)
+        else:
+            Xd = self.to_device(X, torch.float32)
         if Xd.dim() != 2:
             raise ValueError("X must be 2-D")
         n, d = Xd.shape

@@ -207,6 +207,7 @@ class GpuExecutor:
         self.solver = SweepSolver(gpu)
         self.resident: dict[tuple, object] = {}       # (name, classifier[, shard, n_shards]); insertion order = LRU first
         self.versions: dict[str, int] = {}            # datasets.dataset_version() the cached copies belong to
+        self.replica = None                           # (process group, rank, world): see SweepSolver.upload_replicated
         self.shard_solvers: dict[tuple[int, int], object] = {}   # (n_shards, shard) -> SweepSolver with an NCCL comm
         self.labels: dict[tuple, np.ndarray] = {}     # host-side row labels, computed once per dataset
         self.labels_dev: dict[tuple, object] = {}
@@ -262,7 +263,7 @@ class GpuExecutor:
                 return False
             self._evict(incoming=X.nbytes)
             self._pin(X)
-            self.resident[key] = self.solver.upload_dataset(X, y, classifier, stream=self.copy_stream)
+            self.resident[key] = self.solver.upload_dataset(X, y, classifier, stream=self.copy_stream, replica=self.replica)
             self.prefetched += 1
             return True
 
@@ -285,7 +286,7 @@ class GpuExecutor:
                 else:
                     self._evict(incoming=X.nbytes)
                     self._pin(X)
-                    self.resident[key] = solver.upload_dataset(X, y, classifier)
+                    self.resident[key] = solver.upload_dataset(X, y, classifier, replica=self.replica)
             ds = self.resident.pop(key)
             self.resident[key] = ds        # most recently used
             self.in_use = key

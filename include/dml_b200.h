@@ -167,6 +167,11 @@ int dml_last_timing(dml_ctx* ctx, float* total_ms, float* contraction_ms,
  * one column: 4*n_train*d flops), and the number of rounds. */
 int dml_last_counters(dml_ctx* ctx, int64_t* column_rounds, int32_t* rounds);
 
+/* Row-sharded mode: time spent in the ncclAllReduce calls of the last sweep on this ctx (CUDA events
+ * around each call on the ctx stream; up to 512 calls are timed), their number and the bytes reduced.
+ * The reference has no collective; diagnostic only. */
+int dml_last_comm(dml_ctx* ctx, float* allreduce_ms, int32_t* allreduce_calls, double* allreduce_bytes);
+
 /* CTAs per cluster the forward / scoring kernel of the last call ran with: 2 = the X tiles were
  * shared by TMA multicast between two column blocks, which the library only does after the driver
  * confirmed that the whole range [X, X + ((n-1)*ldx + d)*4) lies inside one cudaMalloc allocation

@@ -23,6 +23,10 @@ def _worker(rank, world, port, q):
     full = ddist.gather_candidates(local, n_cand, world, rank, ["correct", "coef"])
     blob = ddist.broadcast_bytes(bytes(range(128)) if rank == 0 else None, 128)
     mx = ddist.max_over_ranks(float(rank + 1))
+    # replicas completing each other: every rank copies its own row slice, one all-gather does the rest
+    X = np.random.default_rng(3).standard_normal((1001, 7)).astype(np.float32)
+    rep = ddist.replicate_rows(X, "cpu", dist.group.WORLD, rank, world)
+    assert rep.shape == (1001, 7) and (rep.numpy() == X).all()
     if rank == 0:
         q.put((full["correct"].tolist(), full["coef"][:, 0, 0].tolist(), list(blob) == list(range(128)), mx))
     else:

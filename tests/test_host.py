@@ -442,3 +442,162 @@ def test_master_learns_rounds_from_a_finished_job():
         assert model.predict("LogisticRegression", "iris", {"C": 100.0}) == flat          # other datasets: still the prior
     finally:
         m.close()
+
+
+# ---------------------------------------------------------------------------------------------------
+# round 2: row-shard blocks, at-least-once delivery, live failure detection, scoring / train scores
+# ---------------------------------------------------------------------------------------------------
+def _subtasks(n, cv=5):
+    return [{"subtask_id": f"j-subtask-{i + 1}", "job_id": "j", "session_id": "s", "dataset_id": "d",
+             "model_type": "LogisticRegression", "parameters": {"C": 10.0 ** i}, "train_params": {"cv": cv}}
+            for i in range(n)]
+
+
+def test_row_partition_blocks_carry_shard_and_all_candidates():
+    blocks = master.create_blocks(_subtasks(5), n_gpus=4, partition="rows",
+                                  extra_train_params={"scoring": "accuracy", "return_train_score": True})
+    assert [b["gpu"] for b in blocks] == [0, 1, 2, 3] and [b["shard"] for b in blocks] == [0, 1, 2, 3]
+    assert all(b["n_shards"] == 4 and b["partition"] == "rows" and len(b["candidates"]) == 5 for b in blocks)
+    assert all(b["train_params"]["scoring"] == "accuracy" and b["train_params"]["return_train_score"] for b in blocks)
+    assert len({b["train_params"]["shard_group"] for b in blocks}) == 1
+    cand = master.create_blocks(_subtasks(5), n_gpus=4)
+    assert all(b["n_shards"] == 1 and b["shard"] == 0 and "shard_group" not in b["train_params"] for b in cand)
+    assert sorted(c["index"] for b in cand for c in b["candidates"]) == list(range(5))
+
+
+def test_master_accepts_one_result_per_shard_set_and_ignores_reruns():
+    """Row shards: every block names all candidates, shard 0 reports them, the others report nothing.  A block
+    that runs twice (requeue of a worker that was slow, not dead) must not finish the job twice."""
+    s = scheduler.Scheduler()
+    m = master.Master(s, n_gpus=2, partition="rows")
+    sid = m.create_session()["session_id"]
+    pkg.register_dataset("rows-host", np.zeros((8, 2), np.float32), np.arange(8) % 2)
+    est = {"model_type": "LogisticRegression", "search_type": "GridSearchCV",
+           "hyperparameters": {"base_estimator_params": {}, "search_params": {"param_grid": {"C": [0.1, 1.0, 10.0]}},
+                               "cv_params": {"cv": 2, "refit": True}}}
+    r = m.train(sid, {"job_id": "jr", "session_id": sid, "dataset_id": "rows-host", "model_details": est,
+                      "train_params": {"refit": True}})
+    assert r["status"] == "Training started" and len(s.backlog) == 2      # no worker yet: both shard blocks wait
+    blocks = list(s.backlog)
+    assert [b["shard"] for b in blocks] == [0, 1]
+    entries = [{"subtask_id": c["subtask_id"], "status": "completed",
+                "result": {"cv_scores": [0.5 + 0.1 * i, 0.5], "mean_cv_score": 0.5 + 0.05 * i, "parameters": c["parameters"],
+                           "n_iter": [3, 3]}} for i, c in enumerate(blocks[0]["candidates"])]
+    finished = []
+    orig = m._finish
+    m._finish = lambda job: (finished.append(1), orig(job))[1]
+    m.on_result({"subtask_id": blocks[1]["subtask_id"], "job_id": "jr", "session_id": sid, "status": "completed", "result": []})
+    assert m.check_status(sid, "jr")["job_status"] in ("pending", "0.0")
+    m.on_result({"subtask_id": blocks[0]["subtask_id"], "job_id": "jr", "session_id": sid, "status": "completed", "result": entries})
+    m.on_result({"subtask_id": blocks[0]["subtask_id"], "job_id": "jr", "session_id": sid, "status": "completed", "result": entries})
+    m.on_result({"subtask_id": blocks[1]["subtask_id"], "job_id": "jr", "session_id": sid, "status": "completed", "result": []})
+    assert finished == [1]                                                 # aggregated exactly once
+    refits = [t for t in s.backlog if t["subtask_id"] == "jr-refit"]
+    assert len(refits) == 1 and refits[0]["candidates"][0]["parameters"]["C"] == 10.0
+    done = {"subtask_id": "jr-refit", "job_id": "jr", "session_id": sid, "status": "completed",
+            "result": [{"subtask_id": "jr-refit", "status": "completed", "result": {"coef": [[1.0, 2.0]], "intercept": [0.0]}}]}
+    m.on_result(done)
+    m.on_result(done)                                                      # a second refit report: no KeyError, no change
+    st = m.check_status(sid, "jr")
+    assert st["job_status"] == "completed" and st["job_result"]["best_params_"] == {"C": 10.0}
+
+
+def test_scheduler_exchange_is_a_rendezvous():
+    import threading
+    s = scheduler.Scheduler()
+    got = []
+    t = threading.Thread(target=lambda: got.append(s.exchange("k")))
+    t.start()
+    s.exchange("k", b"\x01" * 128)
+    t.join(5)
+    assert got == [b"\x01" * 128]
+    with pytest.raises(TimeoutError):
+        s.exchange("never", timeout=0.05)
+
+
+def test_monitor_thread_requeues_the_blocks_of_a_worker_that_stops_heartbeating(monkeypatch):
+    """scheduler_service.py:205-247 live: a worker dies mid-job (no unsubscribe, no heartbeat); the monitor loop of
+    the LocalBackend notices after HEARTBEAT_TIMEOUT_S and hands its block to the surviving worker."""
+    import time
+    from cs230_distributed_machine_learning_b200.client import LocalBackend, MLTaskManager
+    from sklearn.linear_model import LogisticRegression
+    from sklearn.model_selection import GridSearchCV
+    monkeypatch.setattr(scheduler, "HEARTBEAT_TIMEOUT_S", 0.3)
+    monkeypatch.setattr(worker, "HEARTBEAT_INTERVAL_S", 0.05)
+    rng = np.random.default_rng(5)
+    X = rng.standard_normal((300, 4)); y = (X[:, 0] + 0.3 * rng.standard_normal(300) > 0).astype(int)
+    pkg.register_dataset("mon-f64", X, y)                                  # float64: the scikit-learn executor (CPU test)
+    backend = LocalBackend(n_gpus=2, monitor_interval=0.1)
+    victim = backend.workers[1]
+    victim.handle = lambda task: time.sleep(3600)                          # takes its block and never answers
+    victim._heartbeat = lambda: None
+    orig_hb = backend.scheduler.heartbeat
+    backend.scheduler.heartbeat = lambda wid: {"status": "dropped"} if wid == victim.worker_id else orig_hb(wid)
+    mgr = MLTaskManager(backend)
+    try:
+        r = mgr.train(GridSearchCV(LogisticRegression(), {"C": [0.1, 1.0, 10.0, 100.0]}, cv=3), "mon-f64",
+                      wait_for_completion=False)
+        assert r["status"] == "Training started"
+        st = mgr._wait_for_completion(mgr.job_id, timeout=30)
+        assert st.get("job_status") == "completed", st
+        assert len(st["job_result"]["results"]) == 4 and victim.worker_id not in backend.scheduler.workers_view()
+        want = GridSearchCV(LogisticRegression(), {"C": [0.1, 1.0, 10.0, 100.0]}, cv=3).fit(X, y)
+        assert st["job_result"]["best_params_"] == want.best_params_
+    finally:
+        backend.scheduler.stop_monitor()
+        for w in backend.workers:
+            if w is not victim:
+                w.shutdown()
+
+
+def test_scoring_string_and_train_scores_through_the_api_equal_gridsearchcv():
+    """cv_params.scoring / return_train_score (core.py:123-130) reach the executor; here the scikit-learn one."""
+    from sklearn.linear_model import Ridge
+    from sklearn.model_selection import GridSearchCV
+    rng = np.random.default_rng(6)
+    X = rng.standard_normal((400, 5)); y = X @ rng.standard_normal(5) + 0.2 * rng.standard_normal(400)
+    pkg.register_dataset("score-f64", X, y)
+    m = pkg.MLTaskManager("local://1")
+    try:
+        est = GridSearchCV(Ridge(), {"alpha": [0.1, 10.0, 1000.0]}, cv=4, scoring="neg_mean_squared_error",
+                           return_train_score=True)
+        r = m.train(est, "score-f64", wait_for_completion=True)
+        assert r["job_status"] == "completed", r
+        res, want = r["job_result"]["cv_results_"], est.fit(X, y).cv_results_
+        for k in ("mean_test_score", "mean_train_score", "split2_train_score", "std_train_score"):
+            np.testing.assert_allclose(res[k], want[k], rtol=1e-9)
+        assert r["job_result"]["best_params_"] == est.best_params_
+    finally:
+        m.close()
+
+
+def test_dataset_version_changes_on_reregistration():
+    from cs230_distributed_machine_learning_b200 import datasets
+    v0 = datasets.dataset_version("ver-x")
+    pkg.register_dataset("ver-x", np.zeros((4, 2), np.float32), np.zeros(4))
+    pkg.register_dataset("ver-x", np.ones((4, 2), np.float32), np.zeros(4))
+    assert datasets.dataset_version("ver-x") == v0 + 2
+
+
+def test_stratified_labels_of_a_row_shard_equal_the_unsharded_labels():
+    rng = np.random.default_rng(0)
+    for K, n, nf in [(2, 10007, 10), (3, 5000, 5), (4, 999, 7)]:
+        y = rng.integers(0, K, n)
+        if K == 3:
+            y[:50] = 2                                        # first-appearance order differs from value order
+        full = folds.stratified_labels(y, nf)
+        total = np.bincount(y, minlength=K)
+        first = np.array([np.nonzero(y == k)[0][0] for k in range(K)])
+        cuts = [0, n // 3, n // 3 * 2 + 5, n]
+        got = np.concatenate([folds.stratified_labels_slice(y[a:b], np.bincount(y[:a], minlength=K), total, first, nf)
+                              for a, b in zip(cuts, cuts[1:])])
+        assert (got == full).all()
+
+
+def test_chunk_seeded_generator_gives_any_row_range_on_its_own():
+    from cs230_distributed_machine_learning_b200.datasets import CHUNK_ROWS, make_dataset_rows
+    n = 2 * CHUNK_ROWS + 1000
+    X, y = make_dataset_rows("binary", n, 8, 5)
+    X2, y2 = make_dataset_rows("binary", n, 8, 5, lo=CHUNK_ROWS, hi=CHUNK_ROWS + 77)
+    assert (X2 == X[CHUNK_ROWS:CHUNK_ROWS + 77]).all() and (y2 == y[CHUNK_ROWS:CHUNK_ROWS + 77]).all()
+    assert abs(float(y.mean()) - 0.5) < 0.01 and abs(float(X.std()) - 1.0) < 0.01
