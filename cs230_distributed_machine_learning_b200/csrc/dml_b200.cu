@@ -628,6 +628,7 @@ struct EvalCtx {
   int hold_group = 0;                // scoring: column group n_groups belongs to the hold-out fits
   const int* n_list_dev = nullptr;   // device count of live list entries (n_slots passed to evaluate is then an upper bound)   // fold-major column groups of the current list (device), or null   // mXf2: forward X box of a 2-CTA cluster member (64 rows)
   unsigned long long* hist_local = nullptr;   // [512] label histogram of this rank's rows
+  bool weighted = false; float* cwS = nullptr; double* swS = nullptr;   // class weights per column (write_trial_kernel)
   // the forward kernel sums (loss - shift) with shift = loss of the zero model: ln 2, or ln T (multinomial)
   float loss_shift() const { return T == 1 ? 0.693147182f : logf((float)T); }
 
@@ -666,6 +667,7 @@ struct EvalCtx {
     hist_local = a.take<unsigned long long>(512);
     Wt = a.take<float>((size_t)S_max * ldw); bt = a.take<float>(S_max);
     sel = a.take<int32_t>(S_max); val = a.take<int32_t>(S_max);
+    if (weighted) { cwS = a.take<float>(2 * (size_t)S_max); swS = a.take<double>(S_max); }
     R = a.take<float>((size_t)chunk_rows * ldr_max);
     // FFMA path: one partial per row tile; tcgen05 path: one per (CTA, epilogue warp)
     const size_t tc_parts = (size_t)ctx_sms * 4;
@@ -713,6 +715,7 @@ struct EvalCtx {
         fp.tile_fold = tile_fold; fp.gstart = gstart; fp.n_groups = n_groups;
         fp.grad_skips = ctx->grad_skip ? 1 : (ctx->grad_zero_fill ? 2 : 0);
         fp.n_list_dev = n_list_dev;
+        fp.cw = weighted ? cwS : nullptr;
         // sum r per column: by the gradient kernel's split warps for binary problems (not with segment skipping or
         // bf16 cross terms, whose tile layouts differ), else by the forward epilogue
         const bool gb_grad = T == 1 && !ctx->grad_skip && !ctx->cross_bf16 && ctx->gb_in_grad;
@@ -726,7 +729,7 @@ struct EvalCtx {
         CU(cudaMemsetAsync(gbPart, 0, sizeof(double) * (size_t)grid * 4 * n_slots, st));
         int rc = DML_OK;
         int64_t n_parts = (int64_t)grid * 4;
-        if (zero_w && T == 1 && n_slots <= 32 && ctx->first_round_once) {
+        if (zero_w && T == 1 && n_slots <= 32 && ctx->first_round_once && !weighted) {
           const int zgrid = (int)std::min<int64_t>(cdiv(rows, 256), 4 * ctx->n_sms);
           ZeroRoundParams zp{r0, rows, y, fold_id, hold_id, sel, val, n_slots, R, gbPart};
           zero_round_kernel<<<zgrid, 256, 0, st>>>(zp);
@@ -753,7 +756,8 @@ struct EvalCtx {
         ReduceParams rp{Gpart, ldg, splits_here, n_slots, d, T, d, nullptr, 0, 0, Gred, ldgr, ci > 0 ? 1 : 0, n_list_dev};
         reduce_grad_kernel<<<n_slots, 256, 0, st>>>(rp);
         tc::TcReduceParams tr{lossPart, gbPart, n_parts, n_slots, T, d, Gred, ldgr, ci > 0 ? 1 : 0,
-                              hist_local, sel, val, n, (double)loss_shift(), n_list_dev, gb_grad ? gb2 : nullptr, splits_here};
+                              hist_local, sel, val, n, (double)loss_shift(), n_list_dev, gb_grad ? gb2 : nullptr, splits_here,
+                              weighted ? swS : nullptr};
         tc::tc_reduce_tiles_kernel<<<(unsigned)cdiv(n_slots, 32), dim3(32, 32), 0, st>>>(tr);
       } else {
         const int ldr = (int)rup(n_slots, 4);
@@ -764,6 +768,7 @@ struct EvalCtx {
         fp.ycls = y; fp.yreg = nullptr; fp.fold_id = fold_id; fp.hold_id = hold_id;
         fp.slot_sel = sel; fp.slot_val = val;
         fp.R = R; fp.ldr = ldr; fp.lossPart = lossPart;
+        fp.cw = weighted ? cwS : nullptr;
         dim3 g1((unsigned)cdiv(rows, BM), (unsigned)cdiv(n_slots, tile_n));
         fwd_kernel<FWD_LOGREG><<<g1, NT, kFwdSmemBytes, st>>>(fp);
         GradParams gp{X, ldx, r0, rows, d, xvec, R, ldr, n_slots, rps, Gpart, ldg};
@@ -857,15 +862,15 @@ __global__ void fill_n_test_kernel(const unsigned long long* __restrict__ hist, 
   n_test[f] = (int64_t)(k < n_folds ? hist[k] : hist[256 + 1]);
 }
 
-extern "C" int dml_logreg_sweep(dml_ctx* ctx, const float* X, int64_t n, int d, int64_t ldx,
-                                const int32_t* y, int n_classes,
-                                const int8_t* fold_id, int n_folds, const int8_t* hold_id,
-                                const double* C, const double* tol, const uint8_t* fit_intercept,
-                                const int32_t* max_iter, int n_cand,
-                                float* coef_out, float* intercept_out,
-                                int32_t* n_iter_out, int32_t* status_out, int32_t* nfev_out,
-                                int64_t* correct_out, int64_t* n_test_out,
-                                int32_t* rounds_out, int use_tensor_cores) {
+static int logreg_sweep_impl(dml_ctx* ctx, const float* X, int64_t n, int d, int64_t ldx,
+                             const int32_t* y, int n_classes,
+                             const int8_t* fold_id, int n_folds, const int8_t* hold_id,
+                             const double* C, const double* tol, const uint8_t* fit_intercept,
+                             const int32_t* max_iter, int n_cand, const double* class_weight,
+                             float* coef_out, float* intercept_out,
+                             int32_t* n_iter_out, int32_t* status_out, int32_t* nfev_out,
+                             int64_t* correct_out, int64_t* n_test_out,
+                             int32_t* rounds_out, int use_tensor_cores) {
   if (!ctx) return DML_ERR_ARG;
   if (!X || !y || !fold_id || !C || !tol || !fit_intercept || !max_iter || !coef_out || !intercept_out)
     return fail(ctx, DML_ERR_ARG, "dml_logreg_sweep: NULL argument");
@@ -882,6 +887,7 @@ extern "C" int dml_logreg_sweep(dml_ctx* ctx, const float* X, int64_t n, int d, 
   EvalCtx ev;
   ev.X = X; ev.n = n; ev.ldx = ldx; ev.d = d; ev.T = T; ev.y = y; ev.fold_id = fold_id; ev.hold_id = hold_id;
   ev.use_tc = use_tensor_cores != 0 && tc_eligible(X, ldx, T);
+  ev.weighted = class_weight != nullptr;
   // fold-major lists pad every fold's group of live fits to 32 columns (binary problems on the tcgen05 path)
   const int pad_to = (ev.use_tc && T == 1 && ctx->fold_skip) ? 32 : 0;
   const int F_pad = F + (pad_to ? fpc * pad_to : 0);
@@ -895,6 +901,8 @@ extern "C" int dml_logreg_sweep(dml_ctx* ctx, const float* X, int64_t n, int d, 
 
   FitState* d_st; double *d_x, *d_g, *d_dir, *d_gt, *d_S, *d_Y, *d_ys;
   int *d_active, *d_nactive, *d_gstart; double* d_Gu; unsigned long long* d_hist; long long* d_correct; int32_t* d_i32;
+  unsigned long long *d_hfc_loc = nullptr, *d_hfc = nullptr; float* d_cwfit = nullptr; double *d_swloc = nullptr, *d_swglob = nullptr;
+  const int KC = n_classes;
   for (int pass = 0; pass < 2; ++pass) {
     Arena a(pass ? ctx->ws : nullptr);
     d_st = a.take<FitState>(F); d_i32 = a.take<int32_t>(3 * (size_t)F);
@@ -905,6 +913,10 @@ extern "C" int dml_logreg_sweep(dml_ctx* ctx, const float* X, int64_t n, int d, 
     d_active = a.take<int>(F_pad); d_nactive = a.take<int>(8); d_gstart = a.take<int>(fpc + 1);
     d_Gu = a.take<double>((size_t)fpc * T * (d + 2));
     d_hist = a.take<unsigned long long>(512); d_correct = a.take<long long>(F);
+    if (class_weight) {
+      d_hfc_loc = a.take<unsigned long long>(512 * (size_t)KC); d_hfc = a.take<unsigned long long>(512 * (size_t)KC);
+      d_cwfit = a.take<float>((size_t)F * KC); d_swloc = a.take<double>(F); d_swglob = a.take<double>(F);
+    }
     ev.take(a, F);
     if (!pass) { int rc = ensure_ws(ctx, a.off + 256); if (rc) return rc; }
   }
@@ -930,11 +942,23 @@ extern "C" int dml_logreg_sweep(dml_ctx* ctx, const float* X, int64_t n, int d, 
     CU(cudaStreamSynchronize(st));
     n_total = 0; for (auto v : h) n_total += (int64_t)v;
   }
+  if (class_weight) {      // weighted training-row counts per fit, on this rank (loss shift) and over all ranks (1 / sum s_i)
+    CU(cudaMemsetAsync(d_hfc_loc, 0, sizeof(unsigned long long) * 512 * (size_t)KC, st));
+    label_class_hist_kernel<<<(unsigned)std::min<int64_t>(cdiv(n, 256), 2 * ctx->n_sms), 256, 0, st>>>(fold_id, hold_id, y, n, KC, d_hfc_loc);
+    KCHECK();
+    CU(cudaMemcpyAsync(d_hfc, d_hfc_loc, sizeof(unsigned long long) * 512 * (size_t)KC, cudaMemcpyDeviceToDevice, st));
+    if (ctx->comm) { int rc = allreduce(ctx, d_hfc, 512 * (size_t)KC, kNcclUint64); if (rc) return rc; }
+    fit_weights_kernel<<<(unsigned)cdiv(F, 128), 128, 0, st>>>(class_weight, F, fpc, n_folds, KC, d_hfc_loc, d_hfc, d_cwfit, d_swloc, d_swglob);
+    KCHECK();
+    ctx->total_launches += 2;
+  }
   CU(cudaMemsetAsync(d_nactive, 0, 8 * sizeof(int), st));
-  InitParams ip{F, n_folds, hold_id ? 1 : 0, fpc, n_total, d_hist, C, tol, fit_intercept, max_iter, d_st, d_active, d_nactive};
+  InitParams ip{F, n_folds, hold_id ? 1 : 0, fpc, n_total, d_hist, C, tol, fit_intercept, max_iter, d_st, d_active, d_nactive,
+                class_weight ? d_swglob : nullptr};
   init_fits_kernel<<<(unsigned)cdiv(F, 128), 128, 0, st>>>(ip);
   KCHECK();
-  TrialParams tp{d, T, P, ev.ldw, d_st, d_x, d_dir, d_active, d_nactive, ev.Wt, ev.bt, ev.sel, ev.val};
+  TrialParams tp{d, T, P, ev.ldw, d_st, d_x, d_dir, d_active, d_nactive, ev.Wt, ev.bt, ev.sel, ev.val,
+                 class_weight ? d_cwfit : nullptr, KC, d_swloc, ev.cwS, ev.swS};
   CompactParams cp{d_st, F, fpc, pad_to, d_active, d_nactive, d_gstart, d_nactive + 4};
   LbfgsParams lp{d, T, P, ev.ldgr, d_st, d_x, d_g, d_dir, d_gt, d_S, d_Y, d_ys, d_active, d_nactive, ev.Gred};
   ctx->total_launches += 1;
@@ -959,7 +983,7 @@ extern "C" int dml_logreg_sweep(dml_ctx* ctx, const float* X, int64_t n, int d, 
   };
   // round 0: all coefficients are zero (_logistic.py:439,457), so z = 0 for every column and the sums
   // differ only by row mask -- evaluate candidate 0's fits (fits 0 .. fpc-1) and copy the sums
-  if (ctx->first_round_once && n_cand > 1) {
+  if (ctx->first_round_once && n_cand > 1 && !class_weight) {
     set_int_kernel<<<1, 1, 0, st>>>(d_nactive, fpc);
     write_trial_kernel<<<fpc, 128, 0, st>>>(tp);
     KCHECK();
@@ -1063,6 +1087,35 @@ extern "C" int dml_logreg_sweep(dml_ctx* ctx, const float* X, int64_t n, int d, 
   CU(cudaStreamSynchronize(st));
   if (rounds_out) *rounds_out = rounds;
   return DML_OK;
+}
+
+extern "C" int dml_logreg_sweep(dml_ctx* ctx, const float* X, int64_t n, int d, int64_t ldx,
+                                const int32_t* y, int n_classes,
+                                const int8_t* fold_id, int n_folds, const int8_t* hold_id,
+                                const double* C, const double* tol, const uint8_t* fit_intercept,
+                                const int32_t* max_iter, int n_cand,
+                                float* coef_out, float* intercept_out,
+                                int32_t* n_iter_out, int32_t* status_out, int32_t* nfev_out,
+                                int64_t* correct_out, int64_t* n_test_out,
+                                int32_t* rounds_out, int use_tensor_cores) {
+  return logreg_sweep_impl(ctx, X, n, d, ldx, y, n_classes, fold_id, n_folds, hold_id, C, tol, fit_intercept, max_iter, n_cand,
+                           nullptr, coef_out, intercept_out, n_iter_out, status_out, nfev_out, correct_out, n_test_out,
+                           rounds_out, use_tensor_cores);
+}
+
+extern "C" int dml_logreg_sweep_weighted(dml_ctx* ctx, const float* X, int64_t n, int d, int64_t ldx,
+                                         const int32_t* y, int n_classes,
+                                         const int8_t* fold_id, int n_folds, const int8_t* hold_id,
+                                         const double* C, const double* tol, const uint8_t* fit_intercept,
+                                         const int32_t* max_iter, int n_cand, const double* class_weight,
+                                         float* coef_out, float* intercept_out,
+                                         int32_t* n_iter_out, int32_t* status_out, int32_t* nfev_out,
+                                         int64_t* correct_out, int64_t* n_test_out,
+                                         int32_t* rounds_out, int use_tensor_cores) {
+  if (ctx && !class_weight) return fail(ctx, DML_ERR_ARG, "dml_logreg_sweep_weighted: class_weight is NULL");
+  return logreg_sweep_impl(ctx, X, n, d, ldx, y, n_classes, fold_id, n_folds, hold_id, C, tol, fit_intercept, max_iter, n_cand,
+                           class_weight, coef_out, intercept_out, n_iter_out, status_out, nfev_out, correct_out, n_test_out,
+                           rounds_out, use_tensor_cores);
 }
 
 // Loss and gradient sums of given coefficient columns (binary logistic): one batched evaluation.

@@ -169,6 +169,11 @@ struct FwdParams {
   float* R; int ldr;                                // [rows][ldr], chunk local (FWD_LOGREG)
   double* lossPart;                                 // [row tiles][n_slots / T]: fp64, see DESIGN.md "precision"
   int32_t* cntPart; float* ssePart;                 // [row tiles][n_slots] (score modes)
+  // class weights (FWD_LOGREG; null = unweighted): cw[slot][2]; binary: the weights of class 0 and class 1 for
+  // the column's fit; multinomial: cw[slot][0] = weight of class (slot % T) of the fit that owns the column.
+  // A row's loss and residual are multiplied by the weight of its class (sklearn _logistic.py:
+  // sample_weight = class_weight_[y], _linear_loss.py:291-379).
+  const float* cw;
 };
 
 __device__ __forceinline__ float softplus_f(float z) {  // log(1 + e^z), stable
@@ -241,8 +246,9 @@ __global__ void __launch_bounds__(NT) fwd_kernel(const FwdParams p) {
           float res = 0.f;
           if (!held) {
             const float yv = (float)rowY[r];
-            s0 += (double)(softplus_f(z) - yv * z);
-            res = sigmoid_f(z) - yv;
+            const float sw = p.cw ? p.cw[(int64_t)(slot0 + c) * 2 + rowY[r]] : 1.f;
+            s0 += (double)(sw * (softplus_f(z) - yv * z));
+            res = sw * (sigmoid_f(z) - yv);
           }
           Zs[r * ZP + c] = res;
         } else if (MODE == FWD_SCORE_CLS) {
@@ -281,9 +287,10 @@ __global__ void __launch_bounds__(NT) fwd_kernel(const FwdParams p) {
           float s = 0.f;
           for (int c = 0; c < T; ++c) s += expf(zr[c] - m);
           const int yv = rowY[r];
-          loss = logf(s) + m - zr[yv];
+          const float sw = p.cw ? p.cw[(int64_t)(slot0 + c0 + yv) * 2] : 1.f;
+          loss = sw * (logf(s) + m - zr[yv]);
           const float inv = 1.f / s;
-          for (int c = 0; c < T; ++c) zr[c] = expf(zr[c] - m) * inv - (c == yv ? 1.f : 0.f);
+          for (int c = 0; c < T; ++c) zr[c] = sw * (expf(zr[c] - m) * inv - (c == yv ? 1.f : 0.f));
         } else {
           for (int c = 0; c < T; ++c) zr[c] = 0.f;
         }

@@ -381,11 +381,25 @@ struct TrialParams {
   const FitState* st; const double *x, *dir;
   const int* active_fits; const int* n_active;
   float* Wt; float* bt; int32_t* slot_sel; int32_t* slot_val;
+  // class weights (null = unweighted): cw_fit [n_fits][K] -> per-slot table cwS [slots][2] the forward kernels
+  // read (binary: weights of class 0 / 1; multinomial: [slot][0] = weight of class slot % T), and
+  // swS[slot] = weighted count of this rank's training rows of the fit (sw_loc), for the loss shift
+  const float* cw_fit; int K; const double* sw_loc; float* cwS; double* swS;
 };
 __global__ void write_trial_kernel(const TrialParams p) {
   const int a = blockIdx.x;
   if (a >= *p.n_active) return;
   const int fit = p.active_fits[a], D1 = p.d + 1;
+  if (p.cw_fit && threadIdx.x < p.T) {
+    const int slot = a * p.T + threadIdx.x;
+    if (fit < 0) { p.cwS[2 * slot] = 1.f; p.cwS[2 * slot + 1] = 1.f; p.swS[slot] = 0.0; }
+    else {
+      const float* w = p.cw_fit + (int64_t)fit * p.K;
+      if (p.T == 1) { p.cwS[2 * slot] = w[0]; p.cwS[2 * slot + 1] = w[1]; }
+      else { p.cwS[2 * slot] = w[threadIdx.x]; p.cwS[2 * slot + 1] = 1.f; }
+      p.swS[slot] = p.sw_loc[fit];
+    }
+  }
   if (fit < 0) {                       // padding entry: zero weights, mask -1 = "holds out every row"
     for (int idx = threadIdx.x; idx < p.P; idx += blockDim.x) {
       const int t = idx / D1, j = idx - t * D1, slot = a * p.T + t;
@@ -466,12 +480,45 @@ __global__ void label_hist_kernel(const int8_t* fold_id, const int8_t* hold_id, 
   for (int i = threadIdx.x; i < 512; i += blockDim.x) if (sh[i]) atomicAdd(&hist[i], (unsigned long long)sh[i]);
 }
 
+// (label value, class) histogram for class weights: hist[(sel * 256 + value) * K + class]
+__global__ void label_class_hist_kernel(const int8_t* fold_id, const int8_t* hold_id, const int32_t* y, int64_t n, int K,
+                                        unsigned long long* hist) {
+  for (int64_t r = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; r < n; r += (int64_t)gridDim.x * blockDim.x) {
+    const int c = y[r];
+    atomicAdd(&hist[(int64_t)(uint8_t)fold_id[r] * K + c], 1ull);
+    if (hold_id) atomicAdd(&hist[(int64_t)(256 + (uint8_t)hold_id[r]) * K + c], 1ull);
+  }
+}
+// sw[fit] = sum over classes of class_weight[fit][class] * (training rows of that class), from a (label value,
+// class) histogram: this rank's rows (sw_loc) or all ranks' (sw_glob).  Also narrows the weights to fp32 (cw_fit).
+// One thread per fit.
+__global__ void fit_weights_kernel(const double* class_weight, int n_fits, int fpc, int n_folds, int K,
+                                   const unsigned long long* hist_loc, const unsigned long long* hist_glob,
+                                   float* cw_fit, double* sw_loc, double* sw_glob) {
+  const int f = blockIdx.x * blockDim.x + threadIdx.x;
+  if (f >= n_fits) return;
+  const int k = f % fpc;
+  const int64_t held = (k < n_folds) ? (int64_t)k * K : (int64_t)(256 + 1) * K;
+  double a = 0.0, b = 0.0;
+  for (int c = 0; c < K; ++c) {
+    const double w = class_weight[(int64_t)f * K + c];
+    cw_fit[(int64_t)f * K + c] = (float)w;
+    unsigned long long tl = 0, tg = 0;
+    for (int v = 0; v < 256; ++v) { tl += hist_loc[(int64_t)v * K + c]; tg += hist_glob[(int64_t)v * K + c]; }
+    // the weight the kernels apply is the fp32 one
+    a += (double)(float)w * (double)(tl - hist_loc[held + c]);
+    b += (double)(float)w * (double)(tg - hist_glob[held + c]);
+  }
+  sw_loc[f] = a; sw_glob[f] = b;
+}
+
 struct InitParams {
   int n_fits, n_folds, has_hold, fits_per_cand;
   int64_t n_total;                 // rows over all ranks
   const unsigned long long* hist;  // summed over ranks
   const double* C; const double* tol; const uint8_t* fit_icpt; const int32_t* max_iter;  // per candidate
   FitState* st; int* active_fits; int* n_active;
+  const double* sw_glob;           // class weights: weighted training-row count per fit (null = unweighted)
 };
 // fit index = cand*fits_per_cand + k ; k < n_folds: CV fold k held out ; k == n_folds: hold-out split
 __global__ void init_fits_kernel(const InitParams p) {
@@ -484,7 +531,9 @@ __global__ void init_fits_kernel(const InitParams p) {
   s.mask_sel = (k < p.n_folds) ? 0 : 1;
   s.mask_val = (k < p.n_folds) ? k : 1;
   const double n_te = (double)p.hist[s.mask_sel * 256 + s.mask_val];
-  const double n_tr = (double)p.n_total - n_te;
+  // with sample weights the objective is sum(s_i loss_i) / sum(s_i) + l2/2 |w|^2, l2 = 1 / (C sum(s_i))
+  // (_linear_loss.py:340-361, _logistic.py:580 with sw_sum)
+  const double n_tr = p.sw_glob ? p.sw_glob[f] : (double)p.n_total - n_te;
   s.inv_ntr = 1.0 / n_tr;
   s.l2 = 1.0 / (p.C[cand] * n_tr);   // _logistic.py:580
   s.tol = p.tol[cand];

@@ -297,6 +297,9 @@ struct TcFwdParams {
   int prefetch_jobs;                     // L2 prefetch distance of the X tiles, in jobs of this CTA (0 = off)
   int T;                                 // columns per fit (1 = binary; multinomial modes: classes, <= 16)
   float loss_shift;                      // per-row losses are summed as (loss - loss_shift): ln 2, or ln T
+  // class weights (training modes; null = unweighted), [n_slots][2] as in FwdParams::cw: a row's (loss - shift)
+  // and residual are multiplied by the weight of its class
+  const float* cw;
 };
 enum { FWD_LOGREG_MULTI = 3, FWD_SCORE_MULTI = 4 };   // softmax / arg-max over T consecutive columns
 
@@ -306,7 +309,7 @@ struct FwdSmem {
   static constexpr int kB = NC * 128;
   static constexpr int kStage = kA + 2 * kB;
   // per column: bias; per label value: 16-bit held-column masks, one per 16-column chunk
-  static constexpr int kMeta = NC * 4 + (kMaxLabel + 2) * (NC / 16) * 2 + (kMaxLabel + 2) * 4 + 64;   // + column-group starts
+  static constexpr int kMeta = NC * 4 + (kMaxLabel + 2) * (NC / 16) * 2 + (kMaxLabel + 2) * 4 + 64 + NC * 8;   // + column-group starts, class weights
   static constexpr int kBytes = kFwdStages * kStage + 1024 /*align*/ + 256 /*barriers*/ + kMeta;
 };
 
@@ -357,6 +360,7 @@ tc_fwd_kernel(const __grid_constant__ CUtensorMap mapX, const __grid_constant__ 
   // id; v = kMaxLabel + h: hold flag h), or does not exist.  A row's held columns = OR of two entries.
   uint16_t* heldTab = reinterpret_cast<uint16_t*>(colBias + NC);                     // [kMaxLabel + 2][NC / 16]
   int* gsTab = reinterpret_cast<int*>(heldTab + (kMaxLabel + 2) * (NC / 16));        // [n_groups + 1] copy of p.gstart
+  float* colCw = reinterpret_cast<float*>((reinterpret_cast<uintptr_t>(gsTab + kMaxLabel + 2) + 7) & ~(uintptr_t)7);   // [NC][2] class weights
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   // tensor memory: two accumulators of NC columns, then per stage 32 columns of X_hi and 32 of X_lo
@@ -561,6 +565,7 @@ tc_fwd_kernel(const __grid_constant__ CUtensorMap mapX, const __grid_constant__ 
           cur_cb = cb;
           asm volatile("bar.sync 1, %0;" ::"n"(128 * G) : "memory");
           for (int c = et; c < NC; c += 128 * G) colBias[c] = slot0 + c < n_live ? __ldg(p.bt + slot0 + c) : 0.f;
+          if (p.cw) for (int c = et; c < NC; c += 128 * G) colCw[2 * c] = slot0 + c < n_live ? __ldg(p.cw + (int64_t)(slot0 + c) * 2) : 1.f;
           for (int e = et; e < (kMaxLabel + 2) * NCH; e += 128 * G) {
             const int v = e / NCH, ci = e % NCH;
             uint32_t bits = 0;
@@ -619,10 +624,11 @@ tc_fwd_kernel(const __grid_constant__ CUtensorMap mapX, const __grid_constant__ 
             float ssum = 0.f, zy = 0.f, rs[16];
 #pragma unroll
             for (int c = 0; c < 16; ++c) { rs[c] = c < T ? exp_ftz(z[c] - m) : 0.f; ssum += rs[c]; if (c == yv) zy = z[c]; }
+            const float sw = (p.cw && train) ? colCw[2 * (c0 + yv)] : 1.f;      // weight of the row's class for this fit
             const float inv = __fdividef(1.f, ssum);
-            const float loss = train ? (__logf(ssum) + m - zy) - p.loss_shift : 0.f;
+            const float loss = train ? sw * ((__logf(ssum) + m - zy) - p.loss_shift) : 0.f;
 #pragma unroll
-            for (int c = 0; c < 16; ++c) rs[c] = (train && c < T) ? rs[c] * inv - (c == yv ? 1.f : 0.f) : 0.f;
+            for (int c = 0; c < 16; ++c) rs[c] = (train && c < T) ? sw * (rs[c] * inv - (c == yv ? 1.f : 0.f)) : 0.f;
             DML_ACC_N(accA, kMyF, (double)warp_sum(loss));
             DML_ACC_N(accB, kMyF, (double)bfly16(rs, lane));
             if (rt < n_row_tiles) {
@@ -684,6 +690,8 @@ tc_fwd_kernel(const __grid_constant__ CUtensorMap mapX, const __grid_constant__ 
         cur_cb = cb;
         asm volatile("bar.sync 1, %0;" ::"n"(128 * G) : "memory");   // everyone is done with the old column tables
         for (int c = et; c < NC; c += 128 * G) colBias[c] = slot0 + c < n_live ? __ldg(p.bt + slot0 + c) : 0.f;
+        if (MODE == FWD_LOGREG && p.cw)
+          for (int c = et; c < 2 * NC; c += 128 * G) colCw[c] = slot0 + (c >> 1) < n_live ? __ldg(p.cw + (int64_t)slot0 * 2 + c) : 1.f;
         for (int e = et; e < (kMaxLabel + 2) * NCH; e += 128 * G) {
           const int v = e / NCH, ci = e % NCH;
           uint32_t bits = 0;
@@ -793,6 +801,11 @@ tc_fwd_kernel(const __grid_constant__ CUtensorMap mapX, const __grid_constant__ 
                 rs[j] = train ? pr - yy : 0.f;
                 ls[j] = train ? (fmaxf(z, 0.f) - yy * z) + (__logf(1.f + e) - p.loss_shift) : 0.f;
               }
+            }
+            if (p.cw) {                      // class weights: the row's class picks one of the column's two weights
+              const uint32_t cw_s = smem_u32(colCw) + (uint32_t)(c0 * 8 + yv * 4);
+#pragma unroll
+              for (int j = 0; j < 16; ++j) { const float sw = lds32f(cw_s + j * 8); rs[j] *= sw; ls[j] *= sw; }
             }
             DML_ACC(accA, (double)bfly16(ls, lane));
             if (!p.gb_in_grad) DML_ACC(accB, (double)bfly16(rs, lane));
@@ -1564,6 +1577,7 @@ struct TcReduceParams {
   const unsigned long long* hist_local; const int32_t* sel; const int32_t* val; int64_t n_local; double loss_shift;
   const int* n_list_dev;   // live columns = *n_list_dev * T when set (n_slots: upper bound and pitch)
   const double* gb2; int gb2_splits;   // sum r per (gradient split, column) from tc_grad2_kernel, or null (then gbPart)
+  const double* sw_slot;               // class weights: weighted count of this rank's training rows per column, or null
 };
 __global__ void tc_reduce_tiles_kernel(const TcReduceParams p) {   // block (32 slots, 32 partial lanes)
   const int n_live = p.n_list_dev ? min(p.n_slots, *p.n_list_dev * p.T) : p.n_slots;
@@ -1585,7 +1599,8 @@ __global__ void tc_reduce_tiles_kernel(const TcReduceParams p) {   // block (32 
     double* q = p.Gred + (int64_t)slot * p.ldgr;
     q[p.d] = p.accumulate ? q[p.d] + g : g;
     if (!p.accumulate && p.sel[slot] >= 0)     // (a padding column has mask -1 and no rows)
-      l += p.loss_shift * (double)(p.n_local - (int64_t)p.hist_local[p.sel[slot] * 256 + (p.val[slot] & 0xff)]);
+      l += p.loss_shift * (p.sw_slot ? p.sw_slot[slot]
+                                     : (double)(p.n_local - (int64_t)p.hist_local[p.sel[slot] * 256 + (p.val[slot] & 0xff)]));
     if (slot % p.T == 0) q[p.d + 1] = p.accumulate ? q[p.d + 1] + l : l;
   }
 }

@@ -153,9 +153,10 @@ class SweepSolver:
 
     # ---- sweeps ---------------------------------------------------------------------
     def logreg_sweep(self, ds: DeviceDataset, fold_id, n_folds: int, C_vals, tol, fit_intercept, max_iter,
-                     hold_id=None, use_tensor_cores: int = -1, want_scores: bool = True):
+                     hold_id=None, use_tensor_cores: int = -1, want_scores: bool = True, class_weight=None):
         """All candidates x (n_folds CV fits [+ hold-out fit]).  Returns dict of numpy arrays
-        shaped [n_cand, fits_per_cand, ...]."""
+        shaped [n_cand, fits_per_cand, ...].  ``class_weight``: (n_cand, fits_per_cand, n_classes) weights of
+        each class for each fit (dml_logreg_sweep_weighted), or None."""
         n_cand = len(C_vals)
         n_classes = int(len(ds.classes))
         T = 1 if n_classes == 2 else n_classes
@@ -181,11 +182,22 @@ class SweepSolver:
         base = buf.data_ptr()
         ptr = lambda name: C.c_void_p(base + offs[name]) if name in offs else C.c_void_p(None)
         rounds = C.c_int32(0)
-        rc = self.lib.dml_logreg_sweep(
-            self.ctx.handle, _ptr(ds.X), ds.n, ds.d, ds.X.stride(0), _ptr(ds.y_cls), n_classes,
-            _ptr(fold_d), n_folds, _ptr(hold_d), C_p, tol_p, fi_p, mi_p, n_cand,
-            ptr("coef"), ptr("intercept"), ptr("n_iter"), ptr("status"), ptr("nfev"), ptr("correct"), ptr("n_test"),
-            C.byref(rounds), int(use_tensor_cores))
+        if class_weight is None:
+            rc = self.lib.dml_logreg_sweep(
+                self.ctx.handle, _ptr(ds.X), ds.n, ds.d, ds.X.stride(0), _ptr(ds.y_cls), n_classes,
+                _ptr(fold_d), n_folds, _ptr(hold_d), C_p, tol_p, fi_p, mi_p, n_cand,
+                ptr("coef"), ptr("intercept"), ptr("n_iter"), ptr("status"), ptr("nfev"), ptr("correct"), ptr("n_test"),
+                C.byref(rounds), int(use_tensor_cores))
+        else:
+            cw = np.ascontiguousarray(class_weight, dtype=np.float64)
+            if cw.shape != (n_cand, fpc, n_classes):
+                raise ValueError(f"class_weight must have shape {(n_cand, fpc, n_classes)}, got {cw.shape}")
+            cw_d = self.to_device(cw)      # (the pinned parameter buffer is in use by C_p .. mi_p)
+            rc = self.lib.dml_logreg_sweep_weighted(
+                self.ctx.handle, _ptr(ds.X), ds.n, ds.d, ds.X.stride(0), _ptr(ds.y_cls), n_classes,
+                _ptr(fold_d), n_folds, _ptr(hold_d), C_p, tol_p, fi_p, mi_p, n_cand, _ptr(cw_d),
+                ptr("coef"), ptr("intercept"), ptr("n_iter"), ptr("status"), ptr("nfev"), ptr("correct"), ptr("n_test"),
+                C.byref(rounds), int(use_tensor_cores))
         self.ctx.check(rc, "dml_logreg_sweep")
         host = self.to_host(buf)
         out = dict(rounds=int(rounds.value), timing=self.ctx.last_timing())

@@ -72,8 +72,11 @@ def gpu_eligible(model_type: str, params: dict) -> tuple[bool, str]:
             return False, f"penalty={p.get('penalty')!r}"
         if p.get("l1_ratio", 0.0) not in (0, 0.0, None):
             return False, "l1_ratio != 0"
-        if p.get("class_weight") is not None or p.get("dual") or p.get("warm_start"):
-            return False, "class_weight/dual/warm_start"
+        cw = p.get("class_weight")
+        if cw is not None and not (cw == "balanced" or isinstance(cw, dict)):
+            return False, f"class_weight={cw!r}"
+        if p.get("dual") or p.get("warm_start"):
+            return False, "dual/warm_start"
         c = p.get("C", 1.0)
         if not (isinstance(c, (int, float)) and np.isfinite(c) and c > 0):
             return False, "C must be finite and positive"
@@ -92,6 +95,37 @@ def gpu_eligible(model_type: str, params: dict) -> tuple[bool, str]:
             return False, "positive=True"
         return True, ""
     return False, "model type not covered by the GPU path"
+
+
+def class_weight_table(params: list[dict], classes, y_idx, fold, hold, cv: int):
+    """Weights of each class for every fit (candidate, k): what scikit-learn derives inside each fit from
+    ``class_weight`` and the fit's own training labels (sklearn/utils/class_weight.py: "balanced" =
+    n_train / (n_classes * bincount(y_train)); a dict maps class label -> weight, missing labels weigh 1).
+    Returns (n_cand, cv + (hold is not None), n_classes) float64, or None when no candidate sets class_weight.
+    Dict keys are matched by value or by their string form (a JSON round trip turns them into strings)."""
+    if all(p.get("class_weight") is None for p in params):
+        return None
+    K = len(classes)
+    total = np.bincount(y_idx, minlength=K).astype(np.float64)
+    train_counts = [total - np.bincount(y_idx[fold == k], minlength=K) for k in range(cv)]
+    if hold is not None:
+        train_counts.append(total - np.bincount(y_idx[hold == 1], minlength=K))
+    out = np.ones((len(params), len(train_counts), K), dtype=np.float64)
+    for i, p in enumerate(params):
+        cw = p.get("class_weight")
+        if cw is None:
+            continue
+        if cw == "balanced":
+            for k, cnt in enumerate(train_counts):
+                present = cnt > 0
+                out[i, k, present] = cnt.sum() / (present.sum() * cnt[present])
+        else:
+            lookup = {str(k): float(v) for k, v in cw.items()}
+            unknown = set(lookup) - {str(c) for c in classes}
+            if unknown:
+                raise ValueError(f"class_weight names labels that are not in y: {sorted(unknown)}")
+            out[i, :, :] = np.array([lookup.get(str(c), 1.0) for c in classes])[None, :]
+    return out
 
 
 def fitted_estimator(model_type: str, parameters: dict, coef, intercept, classes=None, n_iter=None):
@@ -395,9 +429,21 @@ class GpuExecutor:
                 cv = 0           # only the all-rows column; Ridge keeps its folds (one Gram pass either way)
             t0 = time.time()
             if model_type == "LogisticRegression":
+                cw = None
+                if any(p.get("class_weight") is not None for p in P):
+                    ykey = (dataset_id, "y-index")
+                    if ykey not in self.labels:
+                        self.labels[ykey] = np.unique(np.asarray(y_host), return_inverse=True)[1].astype(np.int64)
+                    hold_host = None
+                    if refit:
+                        hold_host = self.labels[(dataset_id, "all-rows")]
+                    elif train_params.get("test_size") is not None:
+                        hold_host = self.labels[(dataset_id, "hold", train_params.get("test_size"), train_params.get("random_state"))]
+                    fold_host = self.labels[(dataset_id, classifier, train_params.get("cv", 5))]
+                    cw = class_weight_table(P, ds.classes, self.labels[ykey], fold_host, hold_host, cv)
                 out = solver.logreg_sweep(
                     ds, fold, cv, [float(p.get("C", 1.0)) for p in P], [float(p.get("tol", 1e-4)) for p in P], fi,
-                    [int(p.get("max_iter", 100)) for p in P], hold_id=hold, want_scores=not refit)
+                    [int(p.get("max_iter", 100)) for p in P], hold_id=hold, want_scores=not refit, class_weight=cw)
             else:
                 alphas = [0.0 if model_type == "LinearRegression" else float(p.get("alpha", 1.0)) for p in P]
                 out = solver.ridge_sweep(ds, fold, cv, alphas, fi, classifier=classifier, hold_id=hold)

@@ -8,7 +8,11 @@
  *
  * Conventions
  *  - plain C, no C++/torch types; every array argument is a caller-owned DEVICE
- *    pointer (cudaMalloc / torch.Tensor.data_ptr()) unless marked "host";
+ *    pointer (cudaMalloc / torch.Tensor.data_ptr()) unless marked "host".  The small
+ *    per-candidate arrays (C, tol, fit_intercept, max_iter, alpha, class_weight) only
+ *    have to be device-ACCESSIBLE: page-locked host memory works through unified
+ *    addressing, and this repository's binding passes them that way so that no copy
+ *    queues behind a dataset upload;
  *  - row-major X with leading dimension ldx (floats); labels are class indices
  *    0..n_classes-1 in the order of sklearn's classes_ (sorted unique y);
  *  - fold_id[i] in 0..n_folds-1 is the CV fold whose TEST set holds row i
@@ -18,8 +22,10 @@
  *  - fits are ordered [candidate][k], k = 0..n_folds-1 the CV fits, then (when
  *    hold_id != NULL) k = n_folds the hold-out fit; fits_per_cand = n_folds +
  *    (hold_id != NULL);
- *  - calls are synchronous with respect to the ctx stream on return (outputs are
- *    valid), return 0 on success, and leave a message in dml_last_error otherwise;
+ *  - work is issued on the ctx stream (so a caller can order it after copies it
+ *    queued on that stream, as worker.py does with a prefetched dataset) and every
+ *    call returns after that work has finished: outputs are valid on return; 0 on
+ *    success, otherwise a code and a message in dml_last_error;
  *  - one ctx per (process, GPU); a ctx is not re-entrant; scratch memory comes
  *    from an arena owned by the ctx and released by dml_ctx_destroy.
  */
@@ -77,6 +83,24 @@ int dml_logreg_sweep(dml_ctx* ctx, const float* X, int64_t n, int d, int64_t ldx
                      int32_t* n_iter_out, int32_t* status_out, int32_t* nfev_out,
                      int64_t* correct_out, int64_t* n_test_out,
                      int32_t* rounds_out, int use_tensor_cores);
+
+/* dml_logreg_sweep with class weights (LogisticRegression(class_weight=dict | "balanced"), which the reference's
+ * client serialises with the other estimator parameters, core.py:96-150, and scikit-learn turns into
+ * sample_weight = class_weight_[y], _logistic.py).  class_weight [n_fits][n_classes] float64, device-accessible:
+ * the weight of each class for fit (candidate, k) -- "balanced" depends on the training fold, so the caller
+ * supplies it per fit: n_train / (n_classes * count of the class in the fit's training rows).  A row's loss and
+ * gradient contribution are multiplied by the weight of its class; the objective is sum(s_i loss_i) / sum(s_i)
+ * + |w|^2 / (2 C sum(s_i)) (_linear_loss.py:291-379).  Scoring is unweighted accuracy, as cross_val_score's
+ * default scorer.  Everything else as dml_logreg_sweep. */
+int dml_logreg_sweep_weighted(dml_ctx* ctx, const float* X, int64_t n, int d, int64_t ldx,
+                              const int32_t* y, int n_classes,
+                              const int8_t* fold_id, int n_folds, const int8_t* hold_id,
+                              const double* C, const double* tol, const uint8_t* fit_intercept,
+                              const int32_t* max_iter, int n_cand, const double* class_weight,
+                              float* coef_out, float* intercept_out,
+                              int32_t* n_iter_out, int32_t* status_out, int32_t* nfev_out,
+                              int64_t* correct_out, int64_t* n_test_out,
+                              int32_t* rounds_out, int use_tensor_cores);
 
 /* Ridge (is_classifier = 0, y_reg used) / RidgeClassifier (is_classifier = 1,
  * y_cls used, targets +-1) with solver "cholesky", every alpha and fold from one

@@ -163,14 +163,20 @@ def test_logreg_ragged_shapes_and_options(solver, n, d, k):
                 tr, te = fold != f, fold == f
                 m = LogisticRegression(**c).fit(X[tr].astype(np.float64), y[tr])
                 if out["n_iter"][i, f] != m.n_iter_[0]:
-                    skipped += 1      # stopped one iterate apart: counted and capped below, never silently passed
+                    # stopped at another iterate (candidate 1 asks for tol = 1e-6, at the noise level of fp32 gradients
+                    # on a few hundred rows): counted and capped below, and still held to a bound -- both runs are
+                    # then within the stopping tolerance of the same optimum
+                    skipped += 1
+                    assert abs(int(out["n_iter"][i, f]) - int(m.n_iter_[0])) <= 3, (i, f, out["n_iter"][i, f], m.n_iter_[0])
+                    assert rel_err(out["coef"][i, f], m.coef_) <= 2e-2, (i, f)
                     continue
                 compared += 1
                 assert rel_err(out["coef"][i, f], m.coef_) <= 5 * RTOL, (i, f)
                 ties = near_ties(X, m.coef_, m.intercept_, te, eps=1e-4)
                 assert abs(int(out["correct"][i, f]) - int((m.predict(X[te]) == y[te]).sum())) <= ties
                 assert out["n_test"][i, f] == te.sum()
-    assert compared >= 1 and skipped <= 1, f"{skipped} of {compared + skipped} fits stopped at a different iterate"
+    print(f"ragged {n}x{d} k={k}: {compared} fits compared at equal n_iter, {skipped} at another iterate")
+    assert compared >= 6 and skipped <= 3, f"{skipped} of {compared + skipped} fits stopped at a different iterate"
     assert (out["n_iter"][2] <= 3).all() and (out["status"][2] == 1).all()   # cap reached -> status 1
     assert (out["intercept"][1] == 0).all()
 
@@ -640,3 +646,60 @@ def test_two_contexts_in_one_process_run_tensor_core_sweeps():
     np.testing.assert_array_equal(res[0][0]["coef"], res[1][0]["coef"])
     np.testing.assert_array_equal(res[0][0]["correct"], res[1][0]["correct"])
     np.testing.assert_array_equal(res[0][1]["coef"], res[1][1]["coef"])
+
+
+@pytest.mark.parametrize("tc", [1, 0], ids=["tcgen05", "ffma"])
+@pytest.mark.parametrize("kind,n,d", [("binary", 12_000, 32), ("multiclass4", 12_000, 32)])
+def test_class_weight_vs_sklearn(solver, kind, n, d, tc):
+    """LogisticRegression(class_weight="balanced" | dict): per-row weights by class inside the forward epilogue,
+    1 / sum(weights) in the optimiser.  Against scikit-learn on float64 with the same class_weight."""
+    from sklearn.linear_model import LogisticRegression
+    from cs230_distributed_machine_learning_b200 import worker as wk
+    X, y = make_dataset(kind, n, d, seed=61)
+    if kind == "binary":                    # make the classes unbalanced so that "balanced" is not a no-op
+        keep = (y == 0) | (np.arange(n) % 3 == 0)
+        X, y = np.ascontiguousarray(X[keep]), y[keep]
+    classes = np.unique(y)
+    cv = 3
+    fold = folds.stratified_labels(y, cv)
+    dict_cw = {int(c): 1.0 + 0.7 * i for i, c in enumerate(classes)}
+    cands = [dict(C=0.5, class_weight="balanced"), dict(C=0.01, class_weight=dict_cw), dict(C=1.0)]
+    table = wk.class_weight_table(cands, classes, np.searchsorted(classes, y), fold, None, cv)
+    ds = solver.upload_dataset(X, y, classifier=True)
+    out = solver.logreg_sweep(ds, fold, cv, [c["C"] for c in cands], [1e-4] * 3, [True] * 3, [100] * 3,
+                              class_weight=table, use_tensor_cores=tc)
+    X64 = X.astype(np.float64)
+    compared = 0
+    for i, c in enumerate(cands):
+        for k in range(cv):
+            tr, te = fold != k, fold == k
+            m = LogisticRegression(**c).fit(X64[tr], y[tr])
+            if m.n_iter_[0] != out["n_iter"][i, k]:
+                continue
+            compared += 1
+            assert rel_err(out["coef"][i, k], m.coef_) <= RTOL, (i, k)
+            assert np.abs(out["intercept"][i, k] - m.intercept_).max() <= RTOL * max(1.0, np.abs(m.coef_).max())
+            ties = near_ties(X, m.coef_, m.intercept_, te)
+            assert abs(int(out["correct"][i, k]) - int((m.predict(X64[te]) == y[te]).sum())) <= ties, (i, k)
+    assert compared >= 8, f"only {compared} of 9 fits stopped at scikit-learn's iterate"
+
+
+def test_class_weight_through_the_api():
+    from sklearn.linear_model import LogisticRegression
+    from sklearn.model_selection import GridSearchCV
+    import cs230_distributed_machine_learning_b200 as pkg
+    X, y = make_dataset("binary", 9000, 24, seed=62)
+    keep = (y == 1) | (np.arange(len(y)) % 4 == 0)
+    X, y = np.ascontiguousarray(X[keep]), y[keep]
+    pkg.register_dataset("cw-bin", X, y)
+    m = pkg.MLTaskManager("local://1")
+    try:
+        grid = {"C": [0.01, 1.0], "class_weight": [None, "balanced", {0: 3.0, 1: 1.0}]}
+        r = m.train(GridSearchCV(LogisticRegression(), grid, cv=5), "cw-bin", wait_for_completion=True)
+        assert r["job_status"] == "completed", r
+        jr = r["job_result"]
+        assert all(res["executor"] == "b200" for res in jr["results"]), [res.get("executor_reason") for res in jr["results"]]
+        gs = GridSearchCV(LogisticRegression(), grid, cv=5).fit(X.astype(np.float64), y)
+        np.testing.assert_allclose(jr["cv_results_"]["mean_test_score"], gs.cv_results_["mean_test_score"], atol=RTOL)
+    finally:
+        m.close()

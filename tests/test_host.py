@@ -255,7 +255,9 @@ def test_gpu_eligibility_rules():
     ok = worker.gpu_eligible
     assert ok("LogisticRegression", {"C": 1.0, "solver": "lbfgs"})[0]
     assert not ok("LogisticRegression", {"solver": "liblinear"})[0]
-    assert not ok("LogisticRegression", {"class_weight": "balanced"})[0]
+    assert ok("LogisticRegression", {"class_weight": "balanced"})[0] and ok("LogisticRegression", {"class_weight": {"0": 2.0}})[0]
+    assert not ok("LogisticRegression", {"class_weight": [1.0, 2.0]})[0]
+    assert not ok("RidgeClassifier", {"class_weight": "balanced"})[0]
     assert not ok("LogisticRegression", {"l1_ratio": 0.5})[0]
     assert ok("Ridge", {"alpha": 1.0})[0] and not ok("Ridge", {"solver": "sag"})[0]
     assert ok("RidgeClassifier", {})[0] and not ok("RandomForestClassifier", {})[0]
@@ -601,3 +603,22 @@ def test_chunk_seeded_generator_gives_any_row_range_on_its_own():
     X2, y2 = make_dataset_rows("binary", n, 8, 5, lo=CHUNK_ROWS, hi=CHUNK_ROWS + 77)
     assert (X2 == X[CHUNK_ROWS:CHUNK_ROWS + 77]).all() and (y2 == y[CHUNK_ROWS:CHUNK_ROWS + 77]).all()
     assert abs(float(y.mean()) - 0.5) < 0.01 and abs(float(X.std()) - 1.0) < 0.01
+
+
+def test_class_weight_table_equals_sklearn_compute_class_weight():
+    from sklearn.utils.class_weight import compute_class_weight
+    rng = np.random.default_rng(0)
+    y = rng.choice([0, 1, 2], 500, p=[.6, .3, .1])
+    fold = folds.stratified_labels(y, 5)
+    hold = folds.holdout_labels(500, .2, 1)
+    t = worker.class_weight_table([{"class_weight": "balanced"}, {"class_weight": {"0": 2.0, "2": 0.5}}, {}],
+                                  np.array([0, 1, 2]), y, fold, hold, 5)
+    assert t.shape == (3, 6, 3)
+    for k in range(5):
+        np.testing.assert_allclose(t[0, k], compute_class_weight("balanced", classes=np.array([0, 1, 2]), y=y[fold != k]))
+    np.testing.assert_allclose(t[0, 5], compute_class_weight("balanced", classes=np.array([0, 1, 2]), y=y[hold != 1]))
+    np.testing.assert_allclose(t[1, 3], [2, 1, .5])
+    assert (t[2] == 1).all()
+    assert worker.class_weight_table([{}, {}], np.array([0, 1]), y % 2, fold, None, 5) is None
+    with pytest.raises(ValueError):
+        worker.class_weight_table([{"class_weight": {"7": 1.0}}], np.array([0, 1, 2]), y, fold, None, 5)
