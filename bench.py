@@ -518,7 +518,9 @@ def roofline_logreg(cfg, acc, ms_total, steps, fits_local, T, p_tf32, p_burst, p
 def roofline_ridge(cfg, acc, ms_total, steps, n_alpha, p_tf32, p_burst, peaks, src):
     n, d, cv, T = cfg["n"], cfg["d"], cfg["cv"], 1
     p3 = p_tf32 / 3.0
-    gram = 2.0 * n * d * (d + T)            # moments once for all folds (the kernel computes the upper block triangle: half of d^2)
+    # moments once for all folds; the kernel exploits symmetry (upper block triangle), so the d^2 term is halved
+    # as SURVEY.md 8d prescribes: n d^2 for X^T X + 2 n d T for X^T Y
+    gram = float(n) * d * d + 2.0 * n * d * T
     solves = cv * n_alpha * (d ** 3 / 3.0 + 2.0 * d * d * T)
     score = 2.0 * n * d * n_alpha * T       # every row is a test row of exactly one fold, for every alpha
     flops_step = gram + solves + score
@@ -529,9 +531,9 @@ def roofline_ridge(cfg, acc, ms_total, steps, n_alpha, p_tf32, p_burst, peaks, s
             "frac_step": ach_step / p3, "achieved_step": ach_step,
             "kernel": "Gram (tc_gram_kernel) + scoring pass; frac: their CUDA-event time only; frac_step: Gram + fp64 solves + "
                       "scoring over the whole step",
-            "flops_note": "2 n d (d+T) for the moments (symmetry is exploited: the kernel multiplies the upper block triangle, "
-                          "i.e. about half of the d^2 term, and is credited the full SURVEY.md 8d figure) + "
-                          "cv * n_alpha * (d^3/3 + 2 d^2 T) fp64 solve flops + 2 n d n_alpha T scoring",
+            "flops_note": "n d^2 + 2 n d T for the moments (symmetry is exploited -- the kernel multiplies the upper block "
+                          "triangle -- so the d^2 term of SURVEY.md 8d is halved) + cv * n_alpha * (d^3/3 + 2 d^2 T) fp64 "
+                          "solve flops + 2 n d n_alpha T scoring",
             "traffic": None, "traffic_algorithmic": 2.0 * n * d * 4,
             "peak_source": f"cuBLAS TF32 8192^3 sustained = {p_tf32:.1f} TFLOP/s (burst {p_burst:.1f}); /3 for 3xTF32",
             "hbm_achieved_gbs": 2.0 * n * d * 4 * steps / sec / 1e9 if sec > 0 else None, "hbm_peak_gbs": peaks.get("hbm_gbs"),
@@ -801,7 +803,7 @@ def api_probe(n_gpus: int):
             means[label] = np.asarray(jr["cv_results_"]["mean_test_score"])
             blocks = {m["subtask_id"] for m in mgr._api_request(f"metrics/{mgr.session_id}/{mgr.job_id}", "get")}
             rec[label] = {"ms_per_job_resident": dt * 1e3, "fits_per_s": 320 / dt, "blocks": len(blocks),
-                          "best_params_": jr["best_params_"], "executors": sorted({x["executor"] for x in jr["results"]}),
+                          "best_params_": jr["best_params_"], "executors": sorted({x.get("executor", "failed: " + str(x.get("error"))[:200]) for x in jr["results"]}),
                           "row_shards": sorted({x.get("row_shards", 1) for x in jr["results"]})}
         finally:
             mgr.close()

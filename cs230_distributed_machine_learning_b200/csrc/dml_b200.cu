@@ -80,6 +80,7 @@ struct dml_ctx {
   // 0.85 ms against 0.76 ms (N = 64 MMAs cost more than half an N = 128 one) but a third less HBM traffic and
   // tensor work, and the same sustained sweep time at the power cap -- so it is off by default.
   int grad_skip = 0;
+  int score_by_group = 1;     // scoring pass: a one-fold row tile only visits its own fold's column blocks (DML_SCORE_BY_GROUP=0: every block)
   int fold_skip = 1;          // fold-major column groups, so that row tiles of one fold can skip that fold's columns
   // gradient kernel: cross terms of the 3xTF32 product as bf16 MMAs over a K-concatenated operand
   // (DML_CROSS_BF16=1).  Measured on config 2: same accuracy (G within 1e-6 of fp64), tensor pipe 60 % -> 43 %
@@ -204,6 +205,7 @@ extern "C" int dml_ctx_create(int device, void* stream, dml_ctx** out) {
   if (const char* e = getenv("DML_TC_PREFETCH_GRAD")) ctx->tc_prefetch_grad = atoi(e);
   if (const char* e = getenv("DML_FIRST_ROUND_ONCE")) ctx->first_round_once = atoi(e);
   if (const char* e = getenv("DML_FOLD_SKIP")) ctx->fold_skip = atoi(e);
+  if (const char* e = getenv("DML_SCORE_BY_GROUP")) ctx->score_by_group = atoi(e);
   if (const char* e = getenv("DML_GRAD_SKIP")) ctx->grad_skip = atoi(e);
   if (const char* e = getenv("DML_CROSS_BF16")) ctx->cross_bf16 = atoi(e);
   if (const char* e = getenv("DML_ROUND_AHEAD")) ctx->round_ahead = atoi(e);
@@ -501,47 +503,91 @@ static int run_score(dml_ctx* ctx, int mode, const float* X, int64_t n, int d, i
 }
 
 // ---- scoring pass on the tensor cores (classifier counts or squared errors) -----------------
-// Wt [n_slots][ldw] fp32 coefficients; Whi/Wlo: scratch of the same shape; part: [n_sms*4][n_slots]
-// int32 (classifier) or double (regressor) partials, summed by reduce_counts / reduce_sse_parts.
-static int run_score_tc(dml_ctx* ctx, int mode, const float* X, int64_t n, int d, int64_t ldx,
-                        const int32_t* ycls, const float* yreg, const int8_t* fold_id, const int8_t* hold_id,
-                        const float* Wt, int ldw, const float* bt, const int32_t* sel, const int32_t* val,
-                        int n_slots, int T, float* Whi, float* Wlo, void* part, int64_t* n_parts,
-                        const uint8_t* tile_fold = nullptr, const int* gstart = nullptr, int n_groups = 0, int hold_group = 0) {
+// Launches the scoring kernel(s) for prepared parameters `fp` (labels, masks, bias, groups): builds the tensor
+// maps, zeroes `part` ([<= 2 * n_sms * 4][n_slots] entries of `esz` bytes) and returns the number of partial rows.
+// With fold-major column groups of width `group_width` (> 0, a multiple of 32) the pass runs by group: a row tile
+// of one fold only meets its own group's blocks (tc_fwd_kernel, score_bpg), X is read once; a second small launch
+// covers the tiles that mix folds.
+static int score_launches(dml_ctx* ctx, int mode, int T, const float* X, int64_t n, int d, int64_t ldx,
+                          const float* Whi, const float* Wlo, int ldw, int n_slots, tc::TcFwdParams fp,
+                          int group_width, void* part, size_t esz, int64_t* n_parts) {
   cudaStream_t st = ctx->stream;
-  const int NC = pick_nc(n_slots, T);
-  if (NC == 0) return fail(ctx, DML_ERR_ARG, "run_score_tc: no column-block width for T=%d", T);
+  int NC = pick_nc(n_slots, T);
+  if (NC == 0) return fail(ctx, DML_ERR_ARG, "scoring: no column-block width for T=%d", T);
+  const bool by_group = ctx->score_by_group && T == 1 && group_width > 0 && fp.gstart != nullptr && fp.tile_fold != nullptr && mode != tc::FWD_SCORE_MULTI;
+  if (by_group) { const int cand[5] = {160, 128, 96, 64, 32}; for (int c : cand) if (group_width % c == 0) { NC = c; break; } }
   CUtensorMap mX, mX2, mWh, mWl;
   int rc;
   if ((rc = make_map_2d(ctx, &mX, X, d, n, ldx * 4, 32, 128))) return rc;
   if ((rc = make_map_2d(ctx, &mX2, X, d, n, ldx * 4, 32, 64))) return rc;
   if ((rc = make_map_2d(ctx, &mWh, Whi, d, n_slots, (uint64_t)ldw * 4, 32, NC))) return rc;
   if ((rc = make_map_2d(ctx, &mWl, Wlo, d, n_slots, (uint64_t)ldw * 4, 32, NC))) return rc;
-  tc::split_weights_kernel<<<(unsigned)cdiv((int64_t)n_slots * ldw, 256), 256, 0, st>>>(Wt, Whi, Wlo, (int64_t)n_slots * ldw);
-  tc::TcFwdParams fp{};
   fp.n_rows_total = n; fp.row0 = 0; fp.rows = n; fp.d_chunks = (int)cdiv(d, 32);
-  fp.n_slots = n_slots; fp.n_col_blocks = (int)cdiv(n_slots, NC); fp.bt = bt; fp.ycls = ycls; fp.yreg = yreg;
-  fp.fold_id = fold_id; fp.hold_id = hold_id; fp.slot_sel = sel; fp.slot_val = val;
-  fp.cntPart = (int32_t*)part; fp.ssePart = (double*)part;
-  fp.mask_hi = ctx->tc_mask_hi; fp.prefetch_jobs = 0; fp.T = T; fp.loss_shift = 0.f;
-  fp.tile_fold = tile_fold; fp.gstart = gstart; fp.n_groups = n_groups; fp.hold_group = hold_group;
+  fp.n_slots = n_slots; fp.n_col_blocks = (int)cdiv(n_slots, NC); fp.T = T; fp.loss_shift = 0.f;
+  fp.mask_hi = ctx->tc_mask_hi; fp.prefetch_jobs = 0;
   const int ncb = fp.n_col_blocks;
+  const int64_t tiles = cdiv(n, 128);
+  auto launch = [&](int clr, int grid, const tc::TcFwdParams& q) -> int {
+    const CUtensorMap& mx = clr == 2 ? mX2 : mX;
+    if (mode == FWD_SCORE_REG) return launch_tc_fwd<FWD_SCORE_REG>(ctx, NC, clr, grid, mx, mWh, mWl, q);
+    if (T == 1) return launch_tc_fwd<FWD_SCORE_CLS>(ctx, NC, clr, grid, mx, mWh, mWl, q);
+    return launch_tc_fwd<tc::FWD_SCORE_MULTI>(ctx, NC, clr, grid, mx, mWh, mWl, q);
+  };
+  if (by_group) {
+    fp.score_bpg = group_width / NC;
+    const int64_t jobs0 = tiles * fp.score_bpg * (1 + (fp.hold_group ? 1 : 0)), jobs1 = tiles * ncb;
+    const int grid0 = (int)std::min<int64_t>(jobs0, ctx->n_sms), grid1 = (int)std::min<int64_t>(jobs1, ctx->n_sms);
+    CU(cudaMemsetAsync(part, 0, esz * (size_t)(grid0 + grid1) * 4 * n_slots, st));
+    tick(ctx);
+    fp.score_phase = 0;
+    rc = launch(1, grid0, fp);
+    if (!rc) {
+      tc::TcFwdParams q = fp;
+      q.score_phase = 1;
+      if (q.cntPart) q.cntPart += (size_t)grid0 * 4 * n_slots;
+      if (q.ssePart) q.ssePart += (size_t)grid0 * 4 * n_slots;
+      rc = launch(1, grid1, q);
+    }
+    tock(ctx, 2);
+    ctx->total_launches += 2;
+    if (rc) return rc;
+    KCHECK();
+    *n_parts = (int64_t)(grid0 + grid1) * 4;
+    return DML_OK;
+  }
+  fp.score_bpg = 0; fp.score_phase = 0;
   const int clr = (fwd_cluster(ctx, X, x_extent_bytes(n, d, ldx)) == 2 && ncb >= 2 && (ncb % 2 == 0 || ncb >= 5)) ? 2 : 1;
-  const int64_t jobs = cdiv(n, 128) * cdiv(ncb, clr);
+  const int64_t jobs = tiles * cdiv(ncb, clr);
   const int grid = clr * (int)std::min<int64_t>(jobs, ctx->n_sms / clr);
-  const size_t esz = mode == FWD_SCORE_REG ? sizeof(double) : sizeof(int32_t);
   CU(cudaMemsetAsync(part, 0, esz * (size_t)grid * 4 * n_slots, st));
-  const CUtensorMap& mx = clr == 2 ? mX2 : mX;
   tick(ctx);
-  if (mode == FWD_SCORE_REG) rc = launch_tc_fwd<FWD_SCORE_REG>(ctx, NC, clr, grid, mx, mWh, mWl, fp);
-  else if (T == 1) rc = launch_tc_fwd<FWD_SCORE_CLS>(ctx, NC, clr, grid, mx, mWh, mWl, fp);
-  else rc = launch_tc_fwd<tc::FWD_SCORE_MULTI>(ctx, NC, clr, grid, mx, mWh, mWl, fp);
+  rc = launch(clr, grid, fp);
   tock(ctx, 1);
-  ctx->total_launches += 2;
+  ctx->total_launches += 1;
   if (rc) return rc;
   KCHECK();
   *n_parts = (int64_t)grid * 4;
   return DML_OK;
+}
+// Wt [n_slots][ldw] fp32 coefficients; Whi/Wlo: scratch of the same shape; part: [<= 2 * n_sms * 4][n_slots]
+// int32 (classifier) or double (regressor) partials, summed by reduce_counts / reduce_sse_parts.
+static int run_score_tc(dml_ctx* ctx, int mode, const float* X, int64_t n, int d, int64_t ldx,
+                        const int32_t* ycls, const float* yreg, const int8_t* fold_id, const int8_t* hold_id,
+                        const float* Wt, int ldw, const float* bt, const int32_t* sel, const int32_t* val,
+                        int n_slots, int T, float* Whi, float* Wlo, void* part, int64_t* n_parts,
+                        const uint8_t* tile_fold = nullptr, const int* gstart = nullptr, int n_groups = 0, int hold_group = 0,
+                        int group_width = 0) {
+  cudaStream_t st = ctx->stream;
+  tc::split_weights_kernel<<<(unsigned)cdiv((int64_t)n_slots * ldw, 256), 256, 0, st>>>(Wt, Whi, Wlo, (int64_t)n_slots * ldw);
+  ctx->total_launches += 1;
+  tc::TcFwdParams fp{};
+  fp.bt = bt; fp.ycls = ycls; fp.yreg = yreg;
+  fp.fold_id = fold_id; fp.hold_id = hold_id; fp.slot_sel = sel; fp.slot_val = val;
+  fp.cntPart = (int32_t*)part; fp.ssePart = (double*)part;
+  fp.tile_fold = tile_fold; fp.gstart = gstart; fp.n_groups = n_groups; fp.hold_group = hold_group;
+  const int m = (mode == FWD_SCORE_REG) ? FWD_SCORE_REG : (T == 1 ? FWD_SCORE_CLS : tc::FWD_SCORE_MULTI);
+  return score_launches(ctx, m, T, X, n, d, ldx, Whi, Wlo, ldw, n_slots, fp, group_width, part,
+                        mode == FWD_SCORE_REG ? sizeof(double) : sizeof(int32_t), n_parts);
 }
 // sse[fit] = sum of the partials of the fit's score column (n_cols columns per partial row; see score_slot)
 __global__ void reduce_sse_parts_kernel(const double* part, int64_t n_parts, int n_cols, double* sse,
@@ -672,7 +718,7 @@ struct EvalCtx {
     // FFMA path: one partial per row tile; tcgen05 path: one per (CTA, epilogue warp)
     const size_t tc_parts = (size_t)ctx_sms * 4;
     lossPart = a.take<double>(use_tc ? tc_parts * S_max : (size_t)tiles_total * n_groups_max);
-    cntPart = a.take<int32_t>(use_tc ? tc_parts * S_max : (size_t)tiles_total * S_max);
+    cntPart = a.take<int32_t>(use_tc ? 2 * tc_parts * S_max : (size_t)tiles_total * S_max);   // scoring may run as two launches
     Gpart = a.take<float>((size_t)splits * S_max * ldg);
     if (use_tc) {
       gbPart = a.take<double>(tc_parts * S_max);
@@ -791,30 +837,18 @@ struct EvalCtx {
     return DML_OK;
   }
   // correct-prediction counts of `n_slots` columns (groups of T) on their held-out rows -> cntPart
-  int score_cls(dml_ctx* ctx, int n_slots, int64_t* n_parts) {
+  int score_cls(dml_ctx* ctx, int n_slots, int64_t* n_parts, int group_width = 0) {
     cudaStream_t st = ctx->stream;
     if (use_tc) {
       tc::split_weights_kernel<<<(unsigned)cdiv((int64_t)n_slots * ldw, 256), 256, 0, st>>>(Wt, Whi, Wlo, (int64_t)n_slots * ldw);
+      ctx->total_launches += 1;
       tc::TcFwdParams fp{};
-      fp.n_rows_total = n; fp.row0 = 0; fp.rows = n; fp.d_chunks = (int)cdiv(d, 32);
-      fp.n_slots = n_slots; fp.n_col_blocks = (int)cdiv(n_slots, NC); fp.bt = bt; fp.ycls = y;
+      fp.bt = bt; fp.ycls = y;
       fp.fold_id = fold_id; fp.hold_id = hold_id; fp.slot_sel = sel; fp.slot_val = val;
-      fp.cntPart = cntPart; fp.mask_hi = ctx->tc_mask_hi; fp.prefetch_jobs = ctx->tc_prefetch; fp.T = T; fp.loss_shift = 0.f;
+      fp.cntPart = cntPart;
       fp.tile_fold = tile_fold; fp.gstart = gstart; fp.n_groups = n_groups; fp.hold_group = hold_group;
-      const int ncb = fp.n_col_blocks;
-      const int clr = (cl == 2 && ncb >= 2 && (ncb % 2 == 0 || ncb >= 5)) ? 2 : 1;
-      const int64_t jobs = tiles_total * cdiv(ncb, clr);
-      const int grid = clr * (int)std::min<int64_t>(jobs, ctx->n_sms / clr);
-      CU(cudaMemsetAsync(cntPart, 0, sizeof(int32_t) * (size_t)grid * 4 * n_slots, st));
-      tick(ctx);
-      int rc = T == 1 ? launch_tc_fwd<FWD_SCORE_CLS>(ctx, NC, clr, grid, clr == 2 ? mXf2 : mXf, mWh, mWl, fp)
-                      : launch_tc_fwd<tc::FWD_SCORE_MULTI>(ctx, NC, clr, grid, clr == 2 ? mXf2 : mXf, mWh, mWl, fp);
-      tock(ctx, 1);
-      ctx->total_launches += 2;
-      if (rc) return rc;
-      KCHECK();
-      *n_parts = (int64_t)grid * 4;
-      return DML_OK;
+      return score_launches(ctx, T == 1 ? (int)FWD_SCORE_CLS : (int)tc::FWD_SCORE_MULTI, T, X, n, d, ldx, Whi, Wlo, ldw, n_slots, fp,
+                            group_width, cntPart, sizeof(int32_t), n_parts);
     }
     *n_parts = tiles_total;
     return run_score(ctx, FWD_SCORE_CLS, X, n, d, ldx, y, nullptr, fold_id, hold_id, Wt, ldw, bt, sel, val, n_slots, T, cntPart);
@@ -878,6 +912,7 @@ static int logreg_sweep_impl(dml_ctx* ctx, const float* X, int64_t n, int d, int
     return fail(ctx, DML_ERR_ARG, "dml_logreg_sweep: bad shape (n=%lld d=%d ldx=%lld classes=%d cand=%d folds=%d)",
                 (long long)n, d, (long long)ldx, n_classes, n_cand, n_folds);
   CU(cudaSetDevice(ctx->device));
+  cudaGetLastError();      // an error another library left pending on this thread is not this call's
   cudaStream_t st = ctx->stream;
   const int T = n_classes == 2 ? 1 : n_classes;
   if (T > BN) return fail(ctx, DML_ERR_LIMIT, "n_classes %d > %d not supported", n_classes, BN);
@@ -1070,7 +1105,7 @@ static int logreg_sweep_impl(dml_ctx* ctx, const float* X, int64_t n, int d, int
   if (correct_out || n_test_out) {
     int64_t n_parts = 0;
     ev.gstart = npad ? d_gstart : nullptr; ev.n_groups = n_folds; ev.hold_group = hold_id ? 1 : 0;
-    int rc = ev.score_cls(ctx, n_score, &n_parts);
+    int rc = ev.score_cls(ctx, n_score, &n_parts, npad);
     ev.gstart = nullptr;
     if (rc) return rc;
     reduce_counts_kernel<<<F, 256, 0, st>>>(ev.cntPart, n_parts, n_score, T, d_correct, fpc, npad);
@@ -1162,16 +1197,26 @@ extern "C" int dml_logreg_eval(dml_ctx* ctx, const float* X, int64_t n, int d, i
 }
 
 // =============================================================================================
-// per-fit statistics of the held-out targets, fp64, deterministic: one block per label value
-__global__ void target_stats_kernel(const float* y, const int8_t* label, int64_t n, double* sy, double* syy) {
+// per-fit statistics of the held-out targets, fp64, deterministic: kStatSlices blocks per label value, each over a
+// contiguous slice of the rows, partial sums combined in slice order
+constexpr int kStatSlices = 64;
+__global__ void target_stats_kernel(const float* y, const int8_t* label, int64_t n, double* part /*[labels][slices][2]*/) {
   __shared__ double red[33];
-  const int want = blockIdx.x;
+  const int want = blockIdx.x, sl = blockIdx.y;
+  const int64_t per = (n + kStatSlices - 1) / kStatSlices, r0 = sl * per, r1 = min(n, r0 + per);
   double a = 0.0, b = 0.0;
-  for (int64_t r = threadIdx.x; r < n; r += blockDim.x)
+  for (int64_t r = r0 + threadIdx.x; r < r1; r += blockDim.x)
     if (label[r] == want) { const double v = (double)y[r]; a += v; b += v * v; }
   a = block_reduce<false>(a, red);
   b = block_reduce<false>(b, red);
-  if (threadIdx.x == 0) { sy[want] = a; syy[want] = b; }
+  if (threadIdx.x == 0) { part[((int64_t)want * kStatSlices + sl) * 2] = a; part[((int64_t)want * kStatSlices + sl) * 2 + 1] = b; }
+}
+__global__ void target_stats_sum_kernel(const double* part, double* sy, double* syy) {
+  const int want = blockIdx.x;
+  if (threadIdx.x != 0) return;
+  double a = 0.0, b = 0.0;
+  for (int sl = 0; sl < kStatSlices; ++sl) { a += part[((int64_t)want * kStatSlices + sl) * 2]; b += part[((int64_t)want * kStatSlices + sl) * 2 + 1]; }
+  sy[want] = a; syy[want] = b;
 }
 __global__ void expand_stats_kernel(const double* sy_l, const double* syy_l, const double* sy_h, const double* syy_h,
                                     int n_fits, int fpc, int n_folds, double* sy, double* syy) {
@@ -1196,6 +1241,7 @@ extern "C" int dml_ridge_sweep(dml_ctx* ctx, const float* X, int64_t n, int d, i
   if (n <= 0 || d <= 0 || ldx < d || n_cand <= 0 || n_folds < 0 || n_folds > 127 || (is_classifier && n_classes < 2))
     return fail(ctx, DML_ERR_ARG, "dml_ridge_sweep: bad shape");
   CU(cudaSetDevice(ctx->device));
+  cudaGetLastError();
   cudaStream_t st = ctx->stream;
   const int T = is_classifier ? (n_classes == 2 ? 1 : n_classes) : 1;
   if (T > BN) return fail(ctx, DML_ERR_LIMIT, "n_classes %d > %d not supported", n_classes, BN);
@@ -1228,7 +1274,7 @@ extern "C" int dml_ridge_sweep(dml_ctx* ctx, const float* X, int64_t n, int d, i
   const int npad = (score_tc && T == 1 && ctx->fold_skip && n_folds >= 2) ? (int)rup(n_cand, 32) : 0;
   const int64_t S_score = npad ? (int64_t)fpc * npad : S_all;
   uint8_t* d_tfold = nullptr; int* d_gs = nullptr;
-  double *d_Mfold, *d_Mtot, *d_A, *d_AT, *d_B, *d_mu, *d_stats, *d_sse; int32_t *d_sel, *d_val, *d_info; long long* d_cnt;
+  double *d_Mfold, *d_Mtot, *d_A, *d_AT, *d_B, *d_mu, *d_stats, *d_sse, *d_statpart; int32_t *d_sel, *d_val, *d_info; long long* d_cnt;
   for (int pass = 0; pass < 2; ++pass) {
     Arena a(pass ? ctx->ws : nullptr);
     d_Mpart = a.take<float>(use_tc ? (size_t)gfolds * splits * ldm_tc * ldm_tc : (size_t)gfolds * splits * D * ldm);
@@ -1245,10 +1291,11 @@ extern "C" int dml_ridge_sweep(dml_ctx* ctx, const float* X, int64_t n, int d, i
     d_tfold = a.take<uint8_t>((size_t)cdiv(n, 128) + 16); d_gs = a.take<int>(fpc + 1);
     d_info = a.take<int32_t>(F); d_cnt = a.take<long long>(F);
     d_stats = a.take<double>(4 * 256); d_sse = a.take<double>(S_all);
+    d_statpart = a.take<double>(256 * (size_t)kStatSlices * 2);
     d_part = a.take<float>((size_t)tiles_total * S_all);
     if (score_tc) {
       d_Whi = a.take<float>((size_t)S_score * ldw); d_Wlo = a.take<float>((size_t)S_score * ldw);
-      d_part_tc = a.take<double>((size_t)ctx->n_sms * 4 * S_score);
+      d_part_tc = a.take<double>((size_t)ctx->n_sms * 8 * S_score);
     }
     if (!pass) { int rc = ensure_ws(ctx, a.off + 256); if (rc) return rc; }
   }
@@ -1340,7 +1387,7 @@ extern "C" int dml_ridge_sweep(dml_ctx* ctx, const float* X, int64_t n, int d, i
                                 (int)(((size_t)kCholMaxD * (kCholNB + 1) + 1 + (size_t)kCholNB * (kCholNB + 2)) * sizeof(double))));
         chol_attr.set(ctx->device);
       }
-      const int threads = (int)std::min<int64_t>(640, rup(d, 32));
+      const int threads = (int)std::min<int64_t>(512, rup(d, 32));
       ridge_cholesky_blocked_kernel<<<nsys, threads, chol_smem, st>>>(d_A, d_AT, d_B, d, T, d_info + c0 * fpc);
     } else {
       ridge_cholesky_kernel<<<nsys, 512, d * sizeof(double), st>>>(d_A, d_B, d, T, d_info + c0 * fpc);
@@ -1356,7 +1403,7 @@ extern "C" int dml_ridge_sweep(dml_ctx* ctx, const float* X, int64_t n, int d, i
   if (score_tc) {
     rc = run_score_tc(ctx, is_classifier ? FWD_SCORE_CLS : FWD_SCORE_REG, X, n, d, ldx, y_cls, y_reg, fold_id, hold_id,
                       d_Wt, ldw, d_bt, d_sel, d_val, (int)S_score, T, d_Whi, d_Wlo, d_part_tc, &n_parts,
-                      npad ? d_tfold : nullptr, npad ? d_gs : nullptr, n_folds, has_hold);
+                      npad ? d_tfold : nullptr, npad ? d_gs : nullptr, n_folds, has_hold, npad);
     parts = d_part_tc;
   } else {
     rc = run_score(ctx, is_classifier ? FWD_SCORE_CLS : FWD_SCORE_REG, X, n, d, ldx, y_cls, y_reg, fold_id, hold_id,
@@ -1375,8 +1422,12 @@ extern "C" int dml_ridge_sweep(dml_ctx* ctx, const float* X, int64_t n, int d, i
     if (ctx->comm) { rc = allreduce(ctx, d_sse, S_all, kNcclFloat64); if (rc) return rc; }
     if (sse_out) CU(cudaMemcpyAsync(sse_out, d_sse, sizeof(double) * S_all, cudaMemcpyDeviceToDevice, st));
     if (sy_out || syy_out) {
-      target_stats_kernel<<<n_folds, 1024, 0, st>>>(y_reg, fold_id, n, d_stats, d_stats + 256);
-      if (has_hold) target_stats_kernel<<<2, 1024, 0, st>>>(y_reg, hold_id, n, d_stats + 512, d_stats + 768);
+      target_stats_kernel<<<dim3(n_folds, kStatSlices), 256, 0, st>>>(y_reg, fold_id, n, d_statpart);
+      target_stats_sum_kernel<<<n_folds, 32, 0, st>>>(d_statpart, d_stats, d_stats + 256);
+      if (has_hold) {
+        target_stats_kernel<<<dim3(2, kStatSlices), 256, 0, st>>>(y_reg, hold_id, n, d_statpart);
+        target_stats_sum_kernel<<<2, 32, 0, st>>>(d_statpart, d_stats + 512, d_stats + 768);
+      }
       KCHECK();
       if (ctx->comm) { rc = allreduce(ctx, d_stats, 1024, kNcclFloat64); if (rc) return rc; }
       expand_stats_kernel<<<(unsigned)cdiv(F, 128), 128, 0, st>>>(d_stats, d_stats + 256, d_stats + 512, d_stats + 768,
@@ -1406,6 +1457,7 @@ extern "C" int dml_score(dml_ctx* ctx, const float* X, int64_t n, int d, int64_t
       n_slots % T != 0 || T > BN || (!y_cls && !y_reg))
     return fail(ctx, DML_ERR_ARG, "dml_score: bad argument");
   CU(cudaSetDevice(ctx->device));
+  cudaGetLastError();
   cudaStream_t st = ctx->stream;
   const int64_t tiles_total = cdiv(n, BM);
   const bool cls = y_cls != nullptr && correct_out != nullptr;
@@ -1419,7 +1471,7 @@ extern "C" int dml_score(dml_ctx* ctx, const float* X, int64_t n, int d, int64_t
   for (int pass = 0; pass < 2; ++pass) {
     Arena a(pass ? ctx->ws : nullptr);
     if (use_tc) {
-      d_part = a.take<double>((size_t)ctx->n_sms * 4 * n_slots);
+      d_part = a.take<double>((size_t)ctx->n_sms * 8 * n_slots);
       d_Wt = a.take<float>((size_t)n_slots * ldw); d_Whi = a.take<float>((size_t)n_slots * ldw); d_Wlo = a.take<float>((size_t)n_slots * ldw);
     } else {
       d_part = a.take<float>((size_t)tiles_total * n_slots);

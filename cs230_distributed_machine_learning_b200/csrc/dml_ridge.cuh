@@ -141,10 +141,10 @@ __global__ void __launch_bounds__(512) ridge_cholesky_kernel(double* Aall, doubl
 // updated with all previously factored columns (each thread owns one row and streams it from L2),
 // factored, and written back once.  Same result as the column-by-column kernel above up to fp64
 // rounding; ~100x less memory traffic (the rank-1 version rewrites the trailing matrix d times).
-constexpr int kCholNB = 32, kCholMaxD = 640;
+constexpr int kCholNB = 32, kCholMaxD = 512;
 // `ATall` receives L^T (row j of AT = column j of L): with one thread per matrix row, the panel update
 // and the forward substitution walk L by columns, which is contiguous (coalesced) only in L^T.
-__global__ void __launch_bounds__(640) ridge_cholesky_blocked_kernel(double* Aall, double* ATall, double* Ball, int d, int T, int* info) {
+__global__ void __launch_bounds__(512) ridge_cholesky_blocked_kernel(double* Aall, double* ATall, double* Ball, int d, int T, int* info) {
   extern __shared__ double sm[];
   constexpr int NB = kCholNB, PP = NB + 1;
   double* P = sm;                     // [d][PP] panel rows k0..d-1
@@ -152,6 +152,8 @@ __global__ void __launch_bounds__(640) ridge_cholesky_blocked_kernel(double* Aal
   __shared__ double piv;
   __shared__ int bad, weak;
   __shared__ double red[33];
+  __shared__ double invD[kCholNB];
+  __shared__ double colj[kCholNB];
   double* A = Aall + (int64_t)blockIdx.x * d * d;
   double* AT = ATall + (int64_t)blockIdx.x * d * d;
   double* B = Ball + (int64_t)blockIdx.x * T * d;
@@ -161,53 +163,130 @@ __global__ void __launch_bounds__(640) ridge_cholesky_blocked_kernel(double* Aal
   for (int k0 = 0; k0 < d; k0 += NB) {
     const int nc = min(NB, d - k0), nr = d - k0;
     const int r = k0 + t;                              // this thread's row (valid when t < nr)
-    double acc[NB];
+    // Panel update P = A[k0:, k0:k0+nc] - L[k0:, :k0] L[k0:k0+nc, :k0]^T with a 4-row x 8-column register tile per
+    // thread (row group t / 4, column group t % 4).  One row per thread with all 32 columns re-read the whole
+    // staged 32 x 32 block of L from shared memory for every row: 16 LDS.128 per 32 DFMA, which bound the kernel
+    // by shared-memory return bandwidth at a tenth of the fp64 rate (ncu, config 3); the tile needs 4.
+    const int rg = t >> 2, cg = t & 3;
+    const int r0 = k0 + 4 * rg;                        // first of this thread's four rows
+    const bool tile_on = 4 * rg < nr;
+    double acc[4][8];
 #pragma unroll
-    for (int c = 0; c < NB; ++c) acc[c] = 0.0;
+    for (int i = 0; i < 4; ++i)
+#pragma unroll
+      for (int c = 0; c < 8; ++c) acc[i][c] = 0.0;
+    // rows past the matrix read row d - 1 again (their results are dropped)
+    const int ri0 = min(r0, d - 1), ri1 = min(r0 + 1, d - 1), ri2 = min(r0 + 2, d - 1), ri3 = min(r0 + 3, d - 1);
+    // the 32 x 32 block of L each step needs is fetched one step ahead (registers), so that its L2 / DRAM latency
+    // runs under the previous step's FMAs instead of between two barriers (ncu: a fifth of the kernel sat there)
+    constexpr int kStage = 4;                          // elements per thread: covers NB * NB with >= 256 threads
+    double nxt[kStage];
+    auto fetch = [&](int j0) {
+#pragma unroll
+      for (int u = 0; u < kStage; ++u) {
+        const int e = t + u * blockDim.x, c = e / NB, jj = e % NB;      // coalesced along jj
+        nxt[u] = (e < NB * NB && c < nc) ? A[(int64_t)(k0 + c) * d + j0 + jj] : 0.0;
+      }
+    };
+    const bool ahead = blockDim.x * kStage >= NB * NB;       // small systems (< 256 threads) stage the block directly
+    if (ahead && k0 > 0) fetch(0);
     for (int j0 = 0; j0 < k0; j0 += NB) {
       __syncthreads();
-      for (int e = t; e < NB * NB; e += blockDim.x) {
-        const int c = e / NB, jj = e % NB;             // coalesced along jj
-        Lk[jj * (NB + 2) + c] = (c < nc) ? A[(int64_t)(k0 + c) * d + j0 + jj] : 0.0;
+      if (ahead) {
+#pragma unroll
+        for (int u = 0; u < kStage; ++u) {
+          const int e = t + u * blockDim.x;
+          if (e < NB * NB) Lk[(e % NB) * (NB + 2) + e / NB] = nxt[u];
+        }
+      } else {
+        for (int e = t; e < NB * NB; e += blockDim.x) {
+          const int c = e / NB, jj = e % NB;
+          Lk[jj * (NB + 2) + c] = (c < nc) ? A[(int64_t)(k0 + c) * d + j0 + jj] : 0.0;
+        }
       }
       __syncthreads();
-      if (t < nr) {
-        const double* at = AT + (int64_t)j0 * d + r;   // L[r][j0 + jj] = AT[j0 + jj][r]: coalesced over threads
-#pragma unroll 8
+      if (ahead && j0 + NB < k0) fetch(j0 + NB);
+      if (tile_on) {
+        const double* at = AT + (int64_t)j0 * d;       // L[r][j0 + jj] = AT[j0 + jj][r]: consecutive rows are contiguous
+#pragma unroll 4
         for (int jj = 0; jj < NB; ++jj) {
-          const double a = at[(int64_t)jj * d];
-          const double2* lk = reinterpret_cast<const double2*>(Lk + jj * (NB + 2));
+          const double* col = at + (int64_t)jj * d;
+          const double a0 = col[ri0], a1 = col[ri1], a2 = col[ri2], a3 = col[ri3];
+          const double2* lk = reinterpret_cast<const double2*>(Lk + jj * (NB + 2) + 8 * cg);
+          const double2 l01 = lk[0], l23 = lk[1], l45 = lk[2], l67 = lk[3];
+          const double l[8] = {l01.x, l01.y, l23.x, l23.y, l45.x, l45.y, l67.x, l67.y};
 #pragma unroll
-          for (int c2 = 0; c2 < NB / 2; ++c2) { const double2 l = lk[c2]; acc[2 * c2] = fma(a, l.x, acc[2 * c2]); acc[2 * c2 + 1] = fma(a, l.y, acc[2 * c2 + 1]); }
+          for (int c = 0; c < 8; ++c) {
+            acc[0][c] = fma(a0, l[c], acc[0][c]); acc[1][c] = fma(a1, l[c], acc[1][c]);
+            acc[2][c] = fma(a2, l[c], acc[2][c]); acc[3][c] = fma(a3, l[c], acc[3][c]);
+          }
         }
       }
     }
     __syncthreads();
-    if (t < nr) {
+    if (tile_on) {
 #pragma unroll
-      for (int c = 0; c < NB; ++c) if (c < nc) P[(size_t)t * PP + c] = A[(int64_t)r * d + k0 + c] - acc[c];
+      for (int i = 0; i < 4; ++i) {
+        const int row = r0 + i;
+        if (row < d) {
+#pragma unroll
+          for (int c = 0; c < 8; ++c) {
+            const int cc = 8 * cg + c;
+            if (cc < nc) P[(size_t)(row - k0) * PP + cc] = A[(int64_t)row * d + k0 + cc] - acc[i][c];
+          }
+        }
+      }
     }
     __syncthreads();
-    // factor the nc x nc diagonal block (rows 0..nc-1 of the panel) and solve the rows below, column by column
-    for (int j = 0; j < nc; ++j) {
-      if (t == 0) {
-        const double a = P[(size_t)j * PP + j];
-        if (!(a > 0.0)) { bad = k0 + j + 1; }
-        else if (a < small && !weak) weak = k0 + j + 1;
-        piv = sqrt(a > 0.0 ? a : 1.0);
+    // Factor the panel.  (A) warp 0 factors the nc x nc diagonal block with one row per lane in registers and
+    // lane-to-lane shuffles; (B) every other row is an independent forward substitution against that block,
+    // done by the row's thread in registers.  The column-by-column form this replaces (two block barriers and a
+    // serial shared-memory update loop per column) kept 14 of 16 warps at a barrier (ncu: 57 % of the samples).
+    if (t < 32) {
+      double a[NB];
+#pragma unroll
+      for (int c = 0; c < NB; ++c) a[c] = (t < nc && c <= t) ? P[(size_t)t * PP + c] : 0.0;
+#pragma unroll
+      for (int j = 0; j < NB; ++j) {
+        const double ajj = __shfl_sync(0xffffffffu, a[j], j);
+        if (j < nc) {
+          if (t == 0) {
+            if (!(ajj > 0.0)) bad = k0 + j + 1;
+            else if (ajj < small && !weak) weak = k0 + j + 1;
+          }
+          // one reciprocal square root instead of a square root and a division on the critical path of the step
+          const double rs = rsqrt(ajj > 0.0 ? ajj : 1.0);
+          a[j] = (t == j) ? (ajj > 0.0 ? ajj * rs : 1.0) : (t > j ? a[j] * rs : 0.0);
+          colj[t] = a[j];                                              // column j of L, for every lane to read
+          __syncwarp();
+#pragma unroll
+          for (int c = j + 1; c < NB; ++c) if (c <= t) a[c] = fma(-a[j], colj[c], a[c]);
+          __syncwarp();
+        }
       }
-      __syncthreads();
-      const double pj = piv;
-      if (t >= j && t < nr) {
-        double v = (t == j) ? pj : P[(size_t)t * PP + j] / pj;
-        P[(size_t)t * PP + j] = v;
+      if (t < nc) {
+#pragma unroll
+        for (int c = 0; c < NB; ++c) if (c <= t) P[(size_t)t * PP + c] = a[c];
+#pragma unroll
+        for (int c = 0; c < NB; ++c) if (c == t) invD[t] = 1.0 / a[c];
       }
-      __syncthreads();
-      if (t > j && t < nr) {
-        const double ltj = P[(size_t)t * PP + j];
-        const int cend = min(t, nc - 1);               // columns j+1 .. min(t, nc-1) of this row
-        for (int c = j + 1; c <= cend; ++c) P[(size_t)t * PP + c] -= ltj * P[(size_t)c * PP + j];
+    }
+    __syncthreads();
+    if (t >= nc && t < nr) {
+      double x[NB];
+#pragma unroll
+      for (int c = 0; c < NB; ++c) x[c] = (c < nc) ? P[(size_t)t * PP + c] : 0.0;
+#pragma unroll
+      for (int j = 0; j < NB; ++j) {
+        if (j < nc) {
+          double sacc = x[j];
+#pragma unroll
+          for (int c = 0; c < j; ++c) sacc = fma(-x[c], P[(size_t)j * PP + c], sacc);   // L_d[j][c]: one address per warp
+          x[j] = sacc * invD[j];
+        }
       }
+#pragma unroll
+      for (int c = 0; c < NB; ++c) if (c < nc) P[(size_t)t * PP + c] = x[c];
     }
     __syncthreads();
     if (t < nr) {

@@ -282,6 +282,12 @@ struct TcFwdParams {
   // fold k trains none of them: no MMAs, no epilogue math for that column range.  gstart == nullptr: off.
   const uint8_t* tile_fold; const int* gstart; int n_groups;
   int hold_group;                        // scoring mode: group n_groups holds the hold-out fits (scored on rows of every tile)
+  // Scoring with fold-major column groups of equal width that is a multiple of the block width NC
+  // (score_bpg = blocks per group > 0; clusters of one): a row tile whose rows all sit in fold k only visits
+  // the score_bpg blocks of group k (and those of the hold-out group), so X is streamed ONCE for all
+  // columns instead of once per pair of column blocks.  score_phase 0: those tiles; score_phase 1: the few
+  // tiles that mix folds, against every block.  Both launches skip the other's tiles.
+  int score_bpg, score_phase;
   int grad_skips;                        // what the gradient kernel leaves unread of a hole, so nothing is stored there:
                                          // 1 = whole 64-column segments, 2 = 32-column chunks (TcGradParams::seg_skip)
   // n_slots is the host's upper bound (and the pitch of the partial-sum arrays); when n_list_dev is set the
@@ -390,10 +396,21 @@ tc_fwd_kernel(const __grid_constant__ CUtensorMap mapX, const __grid_constant__ 
   const int n_live = p.n_list_dev ? min(p.n_slots, *p.n_list_dev * p.T) : p.n_slots;
   const int ncb_live = p.n_list_dev ? (n_live + NC - 1) / NC : p.n_col_blocks;
   const int64_t cb_groups = (ncb_live + CL - 1) / CL;            // column blocks are dealt out CL at a time
-  const int64_t n_jobs = n_row_tiles * cb_groups;                // jobs per cluster (column-block group major)
+  constexpr bool kScoreAny = MODE == FWD_SCORE_CLS || MODE == FWD_SCORE_REG;
+  const bool by_group = kScoreAny && CL == 1 && p.score_bpg > 0 && p.gstart != nullptr;
+  const int64_t n_jobs = by_group ? n_row_tiles * (p.score_phase == 0 ? p.score_bpg * (1 + (p.hold_group ? 1 : 0)) : ncb_live)
+                                  : n_row_tiles * cb_groups;     // jobs per cluster (column-block group major)
   const int64_t job0 = blockIdx.x / CL, job_step = gridDim.x / CL;
-  auto job_cb = [&](int64_t job) { return (int)(job / n_row_tiles) * CL + crank; };  // may be >= n_col_blocks (no columns)
   auto job_rt = [&](int64_t job) { return job % n_row_tiles; };
+  // column block of a job; -1 = nothing to do for this job in this launch (every role skips it)
+  auto job_cb = [&](int64_t job) -> int {
+    if (!by_group) return (int)(job / n_row_tiles) * CL + crank;                     // may be >= n_col_blocks (no columns)
+    const int j = (int)(job / n_row_tiles);
+    const int k = (int)p.tile_fold[p.row0 / 128 + job % n_row_tiles];
+    if (p.score_phase == 1) return k >= p.n_groups ? j : -1;
+    if (k >= p.n_groups) return -1;
+    return j < p.score_bpg ? k * p.score_bpg + j : p.n_groups * p.score_bpg + (j - p.score_bpg);
+  };
   // block-local column range [sa, sb) that a tile whose rows all sit in fold k does not train
   // (empty: sa == sb == 0); k = 255: the tile mixes folds
   auto tile_k = [&](int64_t rt) -> int { return holes ? (int)p.tile_fold[p.row0 / 128 + rt] : 255; };
@@ -424,6 +441,7 @@ tc_fwd_kernel(const __grid_constant__ CUtensorMap mapX, const __grid_constant__ 
       uint32_t it = 0;
       for (int64_t job = job0; job < n_jobs; job += job_step) {
         const int cb = job_cb(job); const int64_t rt = job_rt(job);
+        if (cb < 0) continue;
         const int row = (int)(p.row0 + rt * 128), slot = cb * NC;
         // L2 prefetch distance: X comes from HBM (latency the 3-stage ring cannot cover by itself),
         // so the tile this CTA will need `kPf` jobs from now is pulled into L2 chunk by chunk
@@ -448,11 +466,15 @@ tc_fwd_kernel(const __grid_constant__ CUtensorMap mapX, const __grid_constant__ 
     // ===== MMA issuer =====
     uint32_t it = 0, tile = 0;
     int k_next = job0 < n_jobs ? tile_k(job_rt(job0)) : 255;
-    for (int64_t job = job0; job < n_jobs; job += job_step, ++tile) {
-      const int acc = tile & 1; const uint32_t aph = (tile >> 1) & 1;
-      int a0, b0, a1, b1;
-      ranges_of(job_cb(job), k_next, a0, b0, a1, b1);
+    for (int64_t job = job0; job < n_jobs; job += job_step) {
+      const int cb_j = job_cb(job);
+      const int k_here = k_next;
       if (job + job_step < n_jobs) k_next = tile_k(job_rt(job + job_step));   // in flight while this tile's MMAs are issued
+      if (cb_j < 0) continue;
+      const int acc = tile & 1; const uint32_t aph = (tile >> 1) & 1;
+      ++tile;
+      int a0, b0, a1, b1;
+      ranges_of(cb_j, k_here, a0, b0, a1, b1);
       const uint32_t idesc_a = instr_desc_tf32(128, b0 - a0, 0, 0), idesc_b = instr_desc_tf32(128, b1 - a1, 0, 0);
       mbar_wait(tempty + acc, aph ^ 1);
       tc_fence_after();
@@ -499,6 +521,7 @@ tc_fwd_kernel(const __grid_constant__ CUtensorMap mapX, const __grid_constant__ 
     const int rq = (warp & 3) * 32 + lane;      // a warp may only touch the 32 TMEM lanes of its quadrant
     uint32_t it = 0;
     for (int64_t job = job0; job < n_jobs; job += job_step) {
+      if (job_cb(job) < 0) continue;
       for (int c = 0; c < p.d_chunks; ++c, ++it) {
         const int s = it % kFwdStages; const uint32_t ph = (it / kFwdStages) & 1;
         mbar_wait(full + s, ph);
@@ -682,8 +705,10 @@ tc_fwd_kernel(const __grid_constant__ CUtensorMap mapX, const __grid_constant__ 
 #pragma unroll
     for (int i = 0; i < kMy; ++i) if (G * i + grp < NCH) last_ci = G * i + grp;
     uint32_t tile = 0;
-    for (int64_t job = job0; job < n_jobs; job += job_step, ++tile) {
+    for (int64_t job = job0; job < n_jobs; job += job_step) {
       const int cb = job_cb(job); const int64_t rt = job_rt(job);
+      if (cb < 0) continue;
+      const uint32_t tile_now = tile++;
       const int slot0 = cb * NC;
       if (cb != cur_cb) {
         flush(cur_cb);
@@ -720,7 +745,7 @@ tc_fwd_kernel(const __grid_constant__ CUtensorMap mapX, const __grid_constant__ 
       }
       const float yy = (float)yv;
       const uint32_t held_f = held_s + fold_v * NCH * 2, held_h = held_s + (kMaxLabel + hold_v) * NCH * 2;
-      const int acc = tile & 1; const uint32_t aph = (tile >> 1) & 1;
+      const int acc = tile_now & 1; const uint32_t aph = (tile_now >> 1) & 1;
       // Training mode: bit ci of hole_mask = no row of this tile trains the columns of chunk ci (no math, residual
       // zero); bit ci + 16 = the gradient kernel skips the chunk's 64-column segment as well, so nothing is stored.
       // Scoring mode: bit ci = none of the chunk's columns is scored on this tile's rows (nothing to count).

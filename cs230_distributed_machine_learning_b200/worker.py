@@ -245,7 +245,6 @@ class GpuExecutor:
         self.shard_solvers: dict[tuple[int, int], object] = {}   # (n_shards, shard) -> SweepSolver with an NCCL comm
         self.labels: dict[tuple, np.ndarray] = {}     # host-side row labels, computed once per dataset
         self.labels_dev: dict[tuple, object] = {}
-        self.pinned: set[int] = set()
         self.lock = threading.Lock()
         self.res_lock = threading.Lock()              # guards ``resident`` (prefetch runs beside a sweep)
         self.copy_stream = torch.cuda.Stream(self.solver.device)
@@ -347,14 +346,23 @@ class GpuExecutor:
         return self.shard_solvers[key]
 
     def _pin(self, X: np.ndarray) -> None:
-        """Page-lock a registered float32 array in place (once), so every later upload is a
-        pinned-memory DMA instead of a staged copy."""
+        """Page-lock a registered float32 array in place (once per process: the executors of all GPUs share the
+        host array), so every later upload is a pinned-memory DMA instead of a staged copy."""
         import torch
-        if X.dtype != np.float32 or id(X) in self.pinned or not X.flags.c_contiguous:
+        if X.dtype != np.float32 or not X.flags.c_contiguous:
             return
-        rc = torch.cuda.cudart().cudaHostRegister(X.ctypes.data, X.nbytes, 0)
-        if int(rc) == 0:
-            self.pinned.add(id(X))
+        with _PIN_LOCK:
+            if id(X) in _PINNED:
+                return
+            rt = torch.cuda.cudart()
+            rc = rt.cudaHostRegister(X.ctypes.data, X.nbytes, 0)
+            if int(rc) == 0:
+                _PINNED.add(id(X))
+            else:                       # e.g. already registered by someone else: not an error for us; do not
+                try:                    # leave it pending for the next cudaGetLastError of this thread
+                    rt.cudaGetLastError()
+                except Exception:
+                    pass
 
     def row_labels(self, dataset_id: str, classifier: bool, cv: int, n: int, y_host, test_size=None, random_state=None,
                    shard: tuple[int, int] | None = None, solver=None):
@@ -528,6 +536,8 @@ class GpuExecutor:
         return results
 
 
+_PINNED: set[int] = set()           # id() of registered arrays that are page-locked, process-wide
+_PIN_LOCK = threading.Lock()
 _EXECUTORS: dict[int, GpuExecutor] = {}
 _EXEC_LOCK = threading.Lock()
 

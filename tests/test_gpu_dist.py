@@ -59,6 +59,8 @@ def test_row_shard_blocks_through_master_and_workers_match_one_gpu():
         finally:
             m.close()
     one, rows, cand = got["one"], got["rows"], got["cand"]
+    for label, (a, b) in got.items():          # a failed candidate carries its error: show it instead of a NaN score
+        assert not [x["error"] for x in a["results"] + b["results"] if x.get("error")], label
     assert all(x["executor"] == "b200" and x["row_shards"] == n_gpus for x in rows[0]["results"])
     for other in (rows, cand):
         assert other[0]["cv_results_"]["mean_test_score"] == one[0]["cv_results_"]["mean_test_score"]     # counts are exact
