@@ -801,8 +801,14 @@ def api_probe(n_gpus: int):
             assert r.get("job_status") == "completed", r
             jr = r["job_result"]
             means[label] = np.asarray(jr["cv_results_"]["mean_test_score"])
-            blocks = {m["subtask_id"] for m in mgr._api_request(f"metrics/{mgr.session_id}/{mgr.job_id}", "get")}
+            recs = mgr._api_request(f"metrics/{mgr.session_id}/{mgr.job_id}", "get")
+            blocks = {m["subtask_id"] for m in recs}
+            from cs230_distributed_machine_learning_b200 import worker as wk
+            block_ms = [round((m["finished_at"] - m["started_at"]) * 1e3, 2) for m in recs]
+            sweep_ms = {g: round(ex.stats["sweep_ms"][-1], 2) for g, ex in wk._EXECUTORS.items() if ex.stats["sweep_ms"]}
+            host_ms = {g: round(ex.stats["host_ms"][-1], 2) for g, ex in wk._EXECUTORS.items() if ex.stats["host_ms"]}
             rec[label] = {"ms_per_job_resident": dt * 1e3, "fits_per_s": 320 / dt, "blocks": len(blocks),
+                          "block_wall_ms": block_ms, "last_sweep_gpu_ms": sweep_ms, "last_sweep_host_ms": host_ms,
                           "best_params_": jr["best_params_"], "executors": sorted({x.get("executor", "failed: " + str(x.get("error"))[:200]) for x in jr["results"]}),
                           "row_shards": sorted({x.get("row_shards", 1) for x in jr["results"]})}
         finally:
@@ -944,8 +950,15 @@ def run_b200(a):
         del sv_rows
         torch.cuda.empty_cache()
         env.barrier()
+        # The other ranks wait on the host (a key in the rendezvous store), not in an NCCL barrier: a pending NCCL
+        # kernel spins on their GPUs and the probe's sweeps would share the SMs with it (measured: 31 ms per job
+        # instead of 9).
+        store = dist.distributed_c10d._get_default_store()
         if rank == 0:
             extras["api_all_gpus"] = run_api_probe_subprocess(world)
+            store.set("dml-bench-api-probe-done", "1")
+        else:
+            store.wait(["dml-bench-api-probe-done"])
         env.barrier()
         deadline.cancel()
         if rank == 0:
