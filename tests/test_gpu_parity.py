@@ -703,3 +703,26 @@ def test_class_weight_through_the_api():
         np.testing.assert_allclose(jr["cv_results_"]["mean_test_score"], gs.cv_results_["mean_test_score"], atol=RTOL)
     finally:
         m.close()
+
+
+def test_reregistered_dataset_name_is_uploaded_again():
+    """The executor keeps device copies and row labels per dataset NAME across jobs; registering the name again
+    (new rows, new labels, another row count) must invalidate them -- the reference re-reads the CSV for every
+    subtask (worker.py:425) and so always trains on current data."""
+    from sklearn.linear_model import LogisticRegression
+    from sklearn.model_selection import GridSearchCV
+    import cs230_distributed_machine_learning_b200 as pkg
+    m = pkg.MLTaskManager("local://1")
+    try:
+        grid = {"C": [0.01, 1.0]}
+        for n, seed in ((6000, 101), (9000, 102)):
+            X, y = make_dataset("binary", n, 24, seed=seed)
+            pkg.register_dataset("same-name", X, y)
+            r = m.train(GridSearchCV(LogisticRegression(), grid, cv=4), "same-name", train_params={"test_size": 0.25, "random_state": 0},
+                        wait_for_completion=True)
+            assert r["job_status"] == "completed", r
+            gs = GridSearchCV(LogisticRegression(), grid, cv=4).fit(X.astype(np.float64), y)
+            np.testing.assert_allclose(r["job_result"]["cv_results_"]["mean_test_score"], gs.cv_results_["mean_test_score"], atol=RTOL)
+            assert all(res["executor"] == "b200" for res in r["job_result"]["results"])
+    finally:
+        m.close()
