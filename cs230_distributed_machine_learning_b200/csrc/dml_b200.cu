@@ -1378,18 +1378,20 @@ extern "C" int dml_ridge_sweep(dml_ctx* ctx, const float* X, int64_t n, int d, i
   for (int c0 = 0; c0 < n_cand; c0 += cand_chunk) {
     const int nc = std::min(cand_chunk, n_cand - c0), nsys = nc * fpc;
     RidgeSysParams sp{d, T, D, n_folds, has_hold, c0, nc, d_Mfold, d_Mtot, alpha, fit_intercept, d_A, d_B, d_mu};
-    ridge_assemble_kernel<<<dim3(32, nsys), 256, 0, st>>>(sp);
-    if (d <= kCholMaxD) {
-      const size_t chol_smem = ((size_t)d * (kCholNB + 1) + 1 + (size_t)kCholNB * (kCholNB + 2)) * sizeof(double);
+    if (d <= kCholMaxD) {      // the blocked kernel forms the systems itself from the moments (RidgeFused)
+      const size_t chol_doubles = (size_t)kCholMaxD * (kCholNB + 1) + 1 + (size_t)kCholNB * (kCholNB + 2) + kCholMaxD + BN + 2;
+      const size_t chol_smem = ((size_t)d * (kCholNB + 1) + 1 + (size_t)kCholNB * (kCholNB + 2) + d + T + 2) * sizeof(double);
       static DeviceOnce chol_attr;
       if (!chol_attr.test(ctx->device)) {
         CU(cudaFuncSetAttribute(ridge_cholesky_blocked_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                (int)(((size_t)kCholMaxD * (kCholNB + 1) + 1 + (size_t)kCholNB * (kCholNB + 2)) * sizeof(double))));
+                                (int)(chol_doubles * sizeof(double))));
         chol_attr.set(ctx->device);
       }
       const int threads = (int)std::min<int64_t>(512, rup(d, 32));
-      ridge_cholesky_blocked_kernel<<<nsys, threads, chol_smem, st>>>(d_A, d_AT, d_B, d, T, d_info + c0 * fpc);
+      RidgeFused rf{d_Mfold, d_Mtot, alpha, fit_intercept, D, n_folds, has_hold, c0, d_mu};
+      ridge_cholesky_blocked_kernel<<<nsys, threads, chol_smem, st>>>(d_A, d_AT, d_B, d, T, d_info + c0 * fpc, rf);
     } else {
+      ridge_assemble_kernel<<<dim3(32, nsys), 256, 0, st>>>(sp);
       ridge_cholesky_kernel<<<nsys, 512, d * sizeof(double), st>>>(d_A, d_B, d, T, d_info + c0 * fpc);
     }
     RidgeOutParams op{d, T, n_folds, has_hold, c0, ldw, d_B, d_mu, coef_out, intercept_out, d_Wt, d_bt, d_sel, d_val, npad};

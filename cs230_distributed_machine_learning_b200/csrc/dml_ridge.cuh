@@ -144,12 +144,22 @@ __global__ void __launch_bounds__(512) ridge_cholesky_kernel(double* Aall, doubl
 constexpr int kCholNB = 32, kCholMaxD = 512;
 // `ATall` receives L^T (row j of AT = column j of L): with one thread per matrix row, the panel update
 // and the forward substitution walk L by columns, which is contiguous (coalesced) only in L^T.
-__global__ void __launch_bounds__(512) ridge_cholesky_blocked_kernel(double* Aall, double* ATall, double* Ball, int d, int T, int* info) {
+// With `f.Mtot` set the kernel forms the centred normal equations itself while it reads them (the entries of A and
+// of the right-hand sides are each read once), straight from the fold moments that all systems of a fold share and
+// that stay in L2, instead of reading a matrix ridge_assemble_kernel wrote to HBM for every system: same numbers
+// (same expression, fp64), one kernel and 3 MB of traffic per system less.
+struct RidgeFused {
+  const double* Mfold; const double* Mtot; const double* alpha; const uint8_t* fit_icpt;
+  int D, n_folds, has_hold, cand0;
+  double* mu;             // [systems][d + T], written here (ridge_output_kernel reads it)
+};
+__global__ void __launch_bounds__(512) ridge_cholesky_blocked_kernel(double* Aall, double* ATall, double* Ball, int d, int T, int* info,
+                                                                     const RidgeFused f) {
   extern __shared__ double sm[];
   constexpr int NB = kCholNB, PP = NB + 1;
   double* P = sm;                     // [d][PP] panel rows k0..d-1
   double* Lk = sm + (((size_t)d * PP + 1) & ~(size_t)1);   // [NB][NB+2] staged rows of L (16-byte aligned): Lk[jj][c] = L[k0 + c][j0 + jj]
-  __shared__ double piv;
+  double* mus = Lk + NB * (NB + 2);   // [d + T] training-fold means (fused form)
   __shared__ int bad, weak;
   __shared__ double red[33];
   __shared__ double invD[kCholNB];
@@ -159,7 +169,33 @@ __global__ void __launch_bounds__(512) ridge_cholesky_blocked_kernel(double* Aal
   double* B = Ball + (int64_t)blockIdx.x * T * d;
   const int t = threadIdx.x;
   if (t == 0) { bad = 0; weak = 0; }
-  const double small = kRidgePivotTol * max_diag(A, d, red);
+  const bool fused = f.Mtot != nullptr;
+  const int D = f.D;
+  const double* Mf = nullptr; double n_tr = 0.0, alpha = 0.0; bool ic = false;
+  if (fused) {
+    const int fpc = f.n_folds + f.has_hold, cand = f.cand0 + blockIdx.x / fpc, k = blockIdx.x % fpc;
+    Mf = f.Mfold + (int64_t)k * D * D;
+    n_tr = f.Mtot[(int64_t)(D - 1) * D + (D - 1)] - Mf[(int64_t)(D - 1) * D + (D - 1)];
+    alpha = f.alpha[cand]; ic = f.fit_icpt[cand] != 0;
+    for (int c = t; c < d + T; c += blockDim.x) {
+      const double mc = (f.Mtot[(int64_t)c * D + (D - 1)] - Mf[(int64_t)c * D + (D - 1)]) / n_tr;
+      mus[c] = mc;
+      f.mu[(int64_t)blockIdx.x * (d + T) + c] = ic ? mc : 0.0;
+    }
+    __syncthreads();
+  }
+  // entry (i, c) of [A | B]: c < d is A, c = d + target is a right-hand side (ridge_assemble_kernel's expression)
+  auto entry = [&](int i, int c) -> double {
+    double v = f.Mtot[(int64_t)i * D + c] - Mf[(int64_t)i * D + c];
+    if (ic) v -= n_tr * mus[i] * mus[c];
+    return (i == c) ? v + alpha : v;
+  };
+  double md = 0.0;
+  if (fused) {
+    for (int j = t; j < d; j += blockDim.x) md = fmax(md, fabs(entry(j, j)));
+    md = block_reduce<true>(md, red);
+  } else md = max_diag(A, d, red);
+  const double small = kRidgePivotTol * md;
   for (int k0 = 0; k0 < d; k0 += NB) {
     const int nc = min(NB, d - k0), nr = d - k0;
     const int r = k0 + t;                              // this thread's row (valid when t < nr)
@@ -232,7 +268,7 @@ __global__ void __launch_bounds__(512) ridge_cholesky_blocked_kernel(double* Aal
 #pragma unroll
           for (int c = 0; c < 8; ++c) {
             const int cc = 8 * cg + c;
-            if (cc < nc) P[(size_t)(row - k0) * PP + cc] = A[(int64_t)row * d + k0 + cc] - acc[i][c];
+            if (cc < nc) P[(size_t)(row - k0) * PP + cc] = (fused ? entry(row, k0 + cc) : A[(int64_t)row * d + k0 + cc]) - acc[i][c];
           }
         }
       }
@@ -309,7 +345,7 @@ __global__ void __launch_bounds__(512) ridge_cholesky_blocked_kernel(double* Aal
   const int lane = t & 31;
   for (int tt = 0; tt < T; ++tt) {
     double* b = B + (int64_t)tt * d;
-    for (int i = t; i < d; i += blockDim.x) bs[i] = b[i];
+    for (int i = t; i < d; i += blockDim.x) bs[i] = fused ? entry(i, d + tt) : b[i];
     for (int k0 = 0; k0 < d; k0 += NB) {            // forward: L z = b
       const int nc = min(NB, d - k0);
       __syncthreads();

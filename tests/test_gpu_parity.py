@@ -726,3 +726,36 @@ def test_reregistered_dataset_name_is_uploaded_again():
             assert all(res["executor"] == "b200" for res in r["job_result"]["results"])
     finally:
         m.close()
+
+
+def test_scoring_and_train_scores_on_the_b200_executor():
+    """cv_params.scoring / return_train_score (core.py:123-130) on float32 data: the scores come from the sums of
+    the GPU scoring pass (test rows) and of one more scoring call over all rows (training rows = all - test)."""
+    from sklearn.linear_model import LogisticRegression, Ridge, RidgeClassifier
+    from sklearn.model_selection import GridSearchCV
+    import cs230_distributed_machine_learning_b200 as pkg
+    Xr, yr = make_dataset("regression", 20_000, 40, seed=111)
+    pkg.register_dataset("sc-reg", Xr, yr)
+    X, y = make_dataset("binary", 20_000, 40, seed=112)
+    pkg.register_dataset("sc-bin", X, y)
+    Xm, ym = make_dataset("multiclass4", 12_000, 24, seed=113)
+    pkg.register_dataset("sc-multi", Xm, ym)
+    m = pkg.MLTaskManager("local://1")
+    try:
+        cases = [("sc-reg", Ridge(), {"alpha": [0.1, 100.0, 1e4]}, "neg_mean_squared_error", Xr, yr.astype(np.float64)),
+                 ("sc-reg", Ridge(), {"alpha": [0.1, 100.0, 1e4]}, "r2", Xr, yr.astype(np.float64)),
+                 ("sc-bin", LogisticRegression(), {"C": [1e-3, 1.0]}, "accuracy", X, y),
+                 ("sc-bin", RidgeClassifier(), {"alpha": [1.0, 1e3]}, None, X, y),
+                 ("sc-multi", LogisticRegression(), {"C": [1e-2, 1.0]}, None, Xm, ym)]
+        for name, est, grid, scoring, Xh, yh in cases:
+            gs = GridSearchCV(est, grid, cv=4, scoring=scoring, return_train_score=True)
+            r = m.train(gs, name, wait_for_completion=True)
+            assert r["job_status"] == "completed", r
+            jr = r["job_result"]
+            assert all(res["executor"] == "b200" for res in jr["results"]), [res.get("executor_reason") for res in jr["results"]]
+            want = gs.fit(Xh.astype(np.float64), yh).cv_results_
+            for key in ("mean_test_score", "mean_train_score", "split1_train_score", "std_train_score"):
+                np.testing.assert_allclose(jr["cv_results_"][key], want[key], rtol=2 * RTOL, atol=2 * RTOL, err_msg=f"{name} {scoring} {key}")
+            assert jr["best_params_"] == gs.best_params_
+    finally:
+        m.close()
