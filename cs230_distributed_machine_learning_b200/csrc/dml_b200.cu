@@ -3,8 +3,8 @@
 #include "dml_common.cuh"
 #include "dml_gemm.cuh"
 #include "dml_lbfgs.cuh"
-#include "dml_ridge.cuh"
 #include "dml_tc.cuh"
+#include "dml_ridge.cuh"
 
 #include <dlfcn.h>
 #include <stdarg.h>
@@ -1379,8 +1379,8 @@ extern "C" int dml_ridge_sweep(dml_ctx* ctx, const float* X, int64_t n, int d, i
     const int nc = std::min(cand_chunk, n_cand - c0), nsys = nc * fpc;
     RidgeSysParams sp{d, T, D, n_folds, has_hold, c0, nc, d_Mfold, d_Mtot, alpha, fit_intercept, d_A, d_B, d_mu};
     if (d <= kCholMaxD) {      // the blocked kernel forms the systems itself from the moments (RidgeFused)
-      const size_t chol_doubles = (size_t)kCholMaxD * (kCholNB + 1) + 1 + (size_t)kCholNB * (kCholNB + 2) + kCholMaxD + BN + 2;
-      const size_t chol_smem = ((size_t)d * (kCholNB + 1) + 1 + (size_t)kCholNB * (kCholNB + 2) + d + T + 2) * sizeof(double);
+      const size_t chol_doubles = (size_t)kCholMaxD * (kCholNB + 1) + 1 + (size_t)kCholNB * (kCholNB + 2) + kCholMaxD + BN + 2 + 16 * (size_t)kCholMaxD;
+      const size_t chol_smem = ((size_t)d * (kCholNB + 1) + 1 + (size_t)kCholNB * (kCholNB + 2) + d + T + 2 + 16 * (size_t)d) * sizeof(double);   // + ring of 4 x 4 rows
       static DeviceOnce chol_attr;
       if (!chol_attr.test(ctx->device)) {
         CU(cudaFuncSetAttribute(ridge_cholesky_blocked_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
@@ -1389,7 +1389,14 @@ extern "C" int dml_ridge_sweep(dml_ctx* ctx, const float* X, int64_t n, int d, i
       }
       const int threads = (int)std::min<int64_t>(512, rup(d, 32));
       RidgeFused rf{d_Mfold, d_Mtot, alpha, fit_intercept, D, n_folds, has_hold, c0, d_mu};
-      ridge_cholesky_blocked_kernel<<<nsys, threads, chol_smem, st>>>(d_A, d_AT, d_B, d, T, d_info + c0 * fpc, rf);
+      long long* d_prof = getenv("DML_CHOL_PROF") ? (long long*)d_statpart : nullptr;   // (scratch that is free at this point)
+      ridge_cholesky_blocked_kernel<<<nsys, threads, chol_smem, st>>>(d_A, d_AT, d_B, d, T, d_info + c0 * fpc, rf, 1, d_prof);
+      if (d_prof) {
+        long long h[6];
+        CU(cudaMemcpyAsync(h, d_prof, sizeof(h), cudaMemcpyDeviceToHost, st));
+        CU(cudaStreamSynchronize(st));
+        fprintf(stderr, "chol block 0 clocks: update %lld form %lld diag %lld rows %lld writeback %lld solves %lld\n", h[0], h[1], h[2], h[3], h[4], h[5]);
+      }
     } else {
       ridge_assemble_kernel<<<dim3(32, nsys), 256, 0, st>>>(sp);
       ridge_cholesky_kernel<<<nsys, 512, d * sizeof(double), st>>>(d_A, d_B, d, T, d_info + c0 * fpc);

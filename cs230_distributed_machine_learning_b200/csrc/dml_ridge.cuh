@@ -10,8 +10,15 @@
 //   Xc^T Xc = (M_all - M_fold)[x,x] - n_tr * mu mu^T,  mu = (s_all - s_fold) / n_tr.
 #pragma once
 #include "dml_common.cuh"
+#include "dml_tc.cuh"      // mbarrier helpers
 
 namespace dml {
+
+// 1-D bulk copy global -> shared (TMA, no tensor map): `bytes` and both addresses multiples of 16
+__device__ __forceinline__ void bulk_load_1d(void* dst, const void* src, uint32_t bytes, uint64_t* bar) {
+  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+               ::"r"(tc::smem_u32(dst)), "l"(src), "r"(bytes), "r"(tc::smem_u32(bar)) : "memory");
+}
 
 // Mpart[fold][split][D][ldm] (fp32) -> Mfold[fold][D][D] (fp64), fixed order over splits
 __global__ void reduce_moments_kernel(const float* Mpart, int splits, int D, int ldm, double* Mfold) {
@@ -154,12 +161,28 @@ struct RidgeFused {
   double* mu;             // [systems][d + T], written here (ridge_output_kernel reads it)
 };
 __global__ void __launch_bounds__(512) ridge_cholesky_blocked_kernel(double* Aall, double* ATall, double* Ball, int d, int T, int* info,
-                                                                     const RidgeFused f) {
+                                                                     const RidgeFused f, const int bulk_smem, long long* prof) {
+  // optional phase profile of block 0 (compile with -DDML_CHOL_PROFILE and run with DML_CHOL_PROF=1): clocks spent in
+  // 0 panel update, 1 panel formation, 2 diagonal block, 3 (unused), 4 rows below the block + write-back, 5 solves
+#ifdef DML_CHOL_PROFILE
+  long long pc[6] = {0, 0, 0, 0, 0, 0};
+  long long tprev = clock64();
+#define DML_PROF(i) do { if (prof) { const long long now_ = clock64(); pc[i] += now_ - tprev; tprev = now_; } } while (0)
+#else
+#define DML_PROF(i) do { } while (0)
+#endif
   extern __shared__ double sm[];
   constexpr int NB = kCholNB, PP = NB + 1;
   double* P = sm;                     // [d][PP] panel rows k0..d-1
   double* Lk = sm + (((size_t)d * PP + 1) & ~(size_t)1);   // [NB][NB+2] staged rows of L (16-byte aligned): Lk[jj][c] = L[k0 + c][j0 + jj]
   double* mus = Lk + NB * (NB + 2);   // [d + T] training-fold means (fused form)
+  constexpr int kRing = 4, kRows = 4;   // bulk-copy ring of the panel update: kRing stages of kRows rows of L^T (d doubles each)
+  double* stage = mus + (((size_t)d + T + 1) & ~(size_t)1);   // [kRing][kRows][d], 16-byte aligned
+  __shared__ __align__(8) uint64_t full[kRing];
+  uint32_t issued = 0, consumed = 0;    // chunks issued (thread 0) / consumed (all threads) since the kernel began
+  // bulk copies need 16-byte aligned rows: even d (k0 and nr are then even too).  `bulk_smem` says the launch
+  // reserved the ring.
+  const bool bulk = bulk_smem && (d % 2 == 0);
   __shared__ int bad, weak;
   __shared__ double red[33];
   __shared__ double invD[kCholNB];
@@ -168,7 +191,12 @@ __global__ void __launch_bounds__(512) ridge_cholesky_blocked_kernel(double* Aal
   double* AT = ATall + (int64_t)blockIdx.x * d * d;
   double* B = Ball + (int64_t)blockIdx.x * T * d;
   const int t = threadIdx.x;
-  if (t == 0) { bad = 0; weak = 0; }
+  if (t == 0) {
+    bad = 0; weak = 0;
+    for (int i = 0; i < kRing; ++i) tc::mbar_init(full + i, 1);
+    tc::fence_barrier_init();
+  }
+  __syncthreads();
   const bool fused = f.Mtot != nullptr;
   const int D = f.D;
   const double* Mf = nullptr; double n_tr = 0.0, alpha = 0.0; bool ic = false;
@@ -225,6 +253,46 @@ __global__ void __launch_bounds__(512) ridge_cholesky_blocked_kernel(double* Aal
       }
     };
     const bool ahead = blockDim.x * kStage >= NB * NB;       // small systems (< 256 threads) stage the block directly
+    if (bulk) {
+      // Rows j (< k0) of L^T, elements k0 .. d-1, stream through a ring of kRing stages of kRows rows each by bulk
+      // async copies (one thread issues, an mbarrier counts the bytes): a stage's first nc entries of a row are the
+      // block L[k0 + c][j] the tile multiplies with, its entries 4 rg .. 4 rg + 3 the thread's own rows.  The copies
+      // of the next stages run under the FMAs of this one; nothing waits on L2 / DRAM between barriers.
+      const int n_chunks = k0 / kRows;
+      const uint32_t row_bytes = (uint32_t)nr * 8u;
+      auto issue = [&](int c, uint32_t g) {
+        const uint32_t st = g % kRing;
+        tc::mbar_expect_tx(full + st, kRows * row_bytes);
+#pragma unroll
+        for (int q = 0; q < kRows; ++q)
+          bulk_load_1d(stage + ((size_t)st * kRows + q) * d, AT + (int64_t)(c * kRows + q) * d + k0, row_bytes, full + st);
+      };
+      if (t == 0) for (int c = 0; c < min(kRing - 1, n_chunks); ++c) issue(c, issued++);
+      for (int c = 0; c < n_chunks; ++c) {
+        if (t == 0 && c + kRing - 1 < n_chunks) issue(c + kRing - 1, issued++);
+        const uint32_t st = consumed % kRing;
+        DML_PROF(0);
+        tc::mbar_wait(full + st, (consumed / kRing) & 1u);
+        ++consumed;
+        DML_PROF(3);   // waiting for the stage's bytes
+        if (tile_on) {
+#pragma unroll
+          for (int q = 0; q < kRows; ++q) {
+            const double* row = stage + ((size_t)st * kRows + q) * d;
+            const double2 a01 = *reinterpret_cast<const double2*>(row + 4 * rg), a23 = *reinterpret_cast<const double2*>(row + 4 * rg + 2);
+            const double2* lk = reinterpret_cast<const double2*>(row + 8 * cg);
+            const double2 l01 = lk[0], l23 = lk[1], l45 = lk[2], l67 = lk[3];
+            const double l[8] = {l01.x, l01.y, l23.x, l23.y, l45.x, l45.y, l67.x, l67.y};
+#pragma unroll
+            for (int cc = 0; cc < 8; ++cc) {
+              acc[0][cc] = fma(a01.x, l[cc], acc[0][cc]); acc[1][cc] = fma(a01.y, l[cc], acc[1][cc]);
+              acc[2][cc] = fma(a23.x, l[cc], acc[2][cc]); acc[3][cc] = fma(a23.y, l[cc], acc[3][cc]);
+            }
+          }
+        }
+        __syncthreads();                             // the stage may be refilled
+      }
+    } else {
     if (ahead && k0 > 0) fetch(0);
     for (int j0 = 0; j0 < k0; j0 += NB) {
       __syncthreads();
@@ -259,7 +327,9 @@ __global__ void __launch_bounds__(512) ridge_cholesky_blocked_kernel(double* Aal
         }
       }
     }
+    }
     __syncthreads();
+    DML_PROF(0);   // update loop
     if (tile_on) {
 #pragma unroll
       for (int i = 0; i < 4; ++i) {
@@ -274,6 +344,7 @@ __global__ void __launch_bounds__(512) ridge_cholesky_blocked_kernel(double* Aal
       }
     }
     __syncthreads();
+    DML_PROF(1);   // panel formed
     // Factor the panel.  (A) warp 0 factors the nc x nc diagonal block with one row per lane in registers and
     // lane-to-lane shuffles; (B) every other row is an independent forward substitution against that block,
     // done by the row's thread in registers.  The column-by-column form this replaces (two block barriers and a
@@ -296,7 +367,9 @@ __global__ void __launch_bounds__(512) ridge_cholesky_blocked_kernel(double* Aal
           colj[t] = a[j];                                              // column j of L, for every lane to read
           __syncwarp();
 #pragma unroll
-          for (int c = j + 1; c < NB; ++c) if (c <= t) a[c] = fma(-a[j], colj[c], a[c]);
+          // no "c <= t" test: entries above the diagonal (c > t) only ever hold garbage nobody reads, and 31 predicates
+          // per step made the compiler pack and unpack predicate masks (300 instructions per step, 2 000 clocks)
+          for (int c = j + 1; c < NB; ++c) a[c] = fma(-a[j], colj[c], a[c]);
           __syncwarp();
         }
       }
@@ -308,6 +381,7 @@ __global__ void __launch_bounds__(512) ridge_cholesky_blocked_kernel(double* Aal
       }
     }
     __syncthreads();
+    DML_PROF(2);   // (A) diagonal block
     if (t >= nc && t < nr) {
       double x[NB];
 #pragma unroll
@@ -325,14 +399,20 @@ __global__ void __launch_bounds__(512) ridge_cholesky_blocked_kernel(double* Aal
       for (int c = 0; c < NB; ++c) if (c < nc) P[(size_t)t * PP + c] = x[c];
     }
     __syncthreads();
+    DML_PROF(3);   // (B) rows below the diagonal block
     if (t < nr) {
-      for (int c = 0; c < nc; ++c) {
-        const double v = (k0 + c <= r) ? P[(size_t)t * PP + c] : 0.0;
-        if (k0 + c <= r) A[(int64_t)r * d + k0 + c] = v;
-        AT[(int64_t)(k0 + c) * d + r] = v;             // coalesced over threads
-      }
+      for (int c = 0; c < nc; ++c)                     // L^T: thread = row, coalesced over threads
+        AT[(int64_t)(k0 + c) * d + r] = (k0 + c <= r) ? P[(size_t)t * PP + c] : 0.0;
     }
+    {                                                  // L: lane = column of the panel, a warp writes whole 256-byte rows
+      const int lane = t & 31, w = t >> 5, nw = blockDim.x >> 5;
+      if (lane < nc)
+        for (int row = w; row < nr; row += nw)
+          if (lane <= row) A[(int64_t)(k0 + row) * d + k0 + lane] = P[(size_t)row * PP + lane];
+    }
+    if (bulk) asm volatile("fence.proxy.async;" ::: "memory");   // these rows are read back by bulk async copies
     __syncthreads();
+    DML_PROF(4);   // write-back of the panel
   }
   if (t == 0 && (bad || weak)) atomicExch(info + blockIdx.x, bad ? bad : -weak);
   // Blocked substitution, one right-hand side at a time: the vector lives in shared memory, a 32 x 32
@@ -399,8 +479,13 @@ __global__ void __launch_bounds__(512) ridge_cholesky_blocked_kernel(double* Aal
     for (int i = t; i < d; i += blockDim.x) b[i] = bs[i];
     __syncthreads();
   }
+  DML_PROF(5);
+#ifdef DML_CHOL_PROFILE
+  if (prof && blockIdx.x == 0 && t == 0) for (int i = 0; i < 6; ++i) prof[i] = pc[i];
+#endif
 }
 
+#undef DML_PROF
 // solution -> fp32 coef/intercept outputs and the score-pass operands
 struct RidgeOutParams {
   int d, T, n_folds, has_hold, cand0, ldw;
