@@ -340,10 +340,10 @@ def run_reference(a):
         y = y.astype(np.float32)
     cands_all = candidates_of(cfg, cfg["n_cand"] * a.gpus)
     model, cv = cfg["model"], cfg["cv"]
-    # calibrate on one candidate (cv fits, BLAS on all cores), then size each leg of a step to ~4 s
+    # calibrate on one candidate (cv fits, BLAS on all cores), then size each leg of a step to ~3 s
     t1, _ = cpu_worker_path(model, cands_all[len(cands_all) // 2:len(cands_all) // 2 + 1], X, y, cv, 1, cores)
     workers = max(1, min(cores // 4, 16))
-    per_step = max(1, min(len(cands_all), int(4.0 / max(t1, 1e-3) * max(1, workers // 2))))
+    per_step = max(1, min(len(cands_all), int(3.0 / max(t1, 1e-3) * max(1, workers // 2))))
     sample = [cands_all[i] for i in np.linspace(0, len(cands_all) - 1, per_step).astype(int)]
     w_eff = workers if per_step > 1 else 1
     thr = max(1, cores // w_eff)
