@@ -266,6 +266,28 @@ def parity_report(out: dict, X, y, fold, cv: int, golden_path: str, eps: float =
 
 
 GOLDEN_CFG2 = os.path.join(ROOT, "tests", "golden", "cfg2_full.npz")
+GOLDEN_CFG3 = os.path.join(ROOT, "tests", "golden", "cfg3_full.npz")
+
+
+def parity_report_ridge(full: dict, golden_path: str):
+    """Config 3 against tests/golden/cfg3_full.npz: the float64 Cholesky solution at full size for 8 of the 128
+    alphas x 5 folds (tests/golden/make_cfg3_full.py; pinned there by one scikit-learn Ridge fit)."""
+    if not os.path.exists(golden_path):
+        return {"unavailable": f"{os.path.relpath(golden_path, ROOT)} missing"}
+    z = np.load(golden_path)
+    idx = json.loads(str(z["meta"]))["alpha_index"]
+    if max(idx) >= full["coef"].shape[0]:
+        return {"unavailable": "golden file is for another candidate list"}
+    coef = full["coef"][idx][:, :, 0, :]
+    err = np.abs(coef - z["coef"]).max(axis=2) / np.abs(z["coef"]).max(axis=2)
+    r2 = 1.0 - full["sse"][idx] / (full["syy"][idx] - full["sy"][idx] ** 2 / full["n_test"][idx])
+    return {"against": os.path.relpath(golden_path, ROOT) + " (float64 Cholesky at full size, pinned by scikit-learn Ridge)",
+            "fits_checked": int(err.size), "max_coef_relerr": float(err.max()),
+            "max_intercept_err": float(np.abs(full["intercept"][idx][:, :, 0] - z["intercept"]).max()),
+            "max_sse_relerr": float(np.abs(full["sse"][idx] / z["sse"] - 1.0).max()),
+            "max_r2_diff": float(np.abs(r2 - z["r2"]).max()),
+            "n_test_equal": bool((full["n_test"][idx] == z["n_test"][None, :]).all()),
+            "best_of_checked_equal": bool(int(np.argmax(r2.mean(axis=1))) == int(np.argmax(z["r2"].mean(axis=1))))}
 
 
 def golden_nfev_sum():
@@ -871,7 +893,7 @@ def run_b200(a):
 
     # scores of all candidates on rank 0 (not timed)
     keys = ["correct", "n_test", "n_iter", "nfev", "coef", "intercept"] if model == "LogisticRegression" else \
-        (["correct", "n_test"] if classifier else ["sse", "sy", "syy", "n_test"])
+        (["correct", "n_test"] if classifier else ["sse", "sy", "syy", "n_test", "coef", "intercept"])
     full = ddist.gather_candidates({k: out[k] for k in keys}, n_cand_total, world, rank, keys, device=env.dev)
 
     # ---- e2e: the user's call, host buffers, H2D/D2H inside the timed region ----
@@ -912,6 +934,8 @@ def run_b200(a):
             line["config"]["mean_n_iter"] = float(np.mean(full["n_iter"]))
             if a.config == "2" and a.full_size and world == 1:
                 line["parity"] = parity_report(full, X, y, fold, cv, GOLDEN_CFG2)
+        if a.config == "3" and a.full_size and world == 1:
+            line["parity"] = parity_report_ridge(full, GOLDEN_CFG3)
         line["e2e"] = e2e if e2e else {"value": None, "unit": UNIT, "h2d_bytes_per_step": None, "d2h_bytes_per_step": None,
                                        "note": "not measured for this config (the dataset is generated per row range, never whole on the host)"
                                        if X is None else "skipped (--no-e2e)"}

@@ -759,3 +759,28 @@ def test_scoring_and_train_scores_on_the_b200_executor():
             assert jr["best_params_"] == gs.best_params_
     finally:
         m.close()
+
+
+def test_config3_full_size_vs_cached_oracle(solver, golden_dir):
+    """BASELINE.json config 3 at FULL size (4M x 512, KFold 5), 8 of the 128 alphas, against the float64 answers of
+    tests/golden/make_cfg3_full.py (the oracle's Cholesky restatement from float64 moments, pinned at full size by one
+    real scikit-learn Ridge fit): coefficients, intercepts, squared errors and R^2 within 1e-4."""
+    z = np.load(os.path.join(golden_dir, "cfg3_full.npz"))
+    meta = json.loads(str(z["meta"]))
+    X, y = make_dataset(meta["kind"], meta["n"], meta["d"], seed=meta["seed"])
+    kf = folds.kfold_labels(meta["n"], meta["cv"])
+    ds = solver.upload_dataset(X, y, classifier=False)
+    del X
+    out = solver.ridge_sweep(ds, kf, meta["cv"], meta["alpha"], [True] * len(meta["alpha"]), classifier=False)
+    assert (out["info"] == 0).all() and (out["n_test"] == z["n_test"][None, :]).all()
+    worst = 0.0
+    for i in range(len(meta["alpha"])):
+        for k in range(meta["cv"]):
+            worst = max(worst, rel_err(out["coef"][i, k, 0], z["coef"][i, k]))
+            assert abs(out["intercept"][i, k, 0] - z["intercept"][i, k]) <= RTOL
+    assert worst <= RTOL, worst
+    np.testing.assert_allclose(out["sse"], z["sse"], rtol=RTOL)
+    r2 = 1.0 - out["sse"] / (out["syy"] - out["sy"] ** 2 / out["n_test"])
+    np.testing.assert_allclose(r2, z["r2"], atol=RTOL)
+    assert int(np.argmax(r2.mean(axis=1))) == int(np.argmax(z["r2"].mean(axis=1)))
+    print(f"cfg3 full-size parity: 40 fits, max coef rel. err {worst:.2e}, max R2 diff {np.abs(r2 - z['r2']).max():.2e}")
