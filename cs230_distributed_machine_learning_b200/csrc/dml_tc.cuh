@@ -632,12 +632,24 @@ tc_fwd_kernel(const __grid_constant__ CUtensorMap mapX, const __grid_constant__ 
           const uint32_t hb = valid ? (lds16u(held_f + (c0 >> 4) * 2) | lds16u(held_h + (c0 >> 4) * 2)) : 0xffffu;
           const bool held = (hb >> (c0 & 15)) & 1u;
           const bool exists = slot0 + c0 < n_live;
+          // The T <= 16 classes are walked in quarters of four under a test that is uniform for the launch
+          // (4 * q < T), so that T = 10 costs 12 element slots instead of 16 (the epilogue is what bounds this
+          // kernel: ncu at config 4 has the tensor pipe 35 % busy).
           float z[16];
           float m = -INFINITY; int am = 0;
 #pragma unroll
-          for (int c = 0; c < 16; ++c) {
-            z[c] = c < T ? __uint_as_float(v[c]) + lds32f(bias_s + (c0 + c) * 4) : -INFINITY;
-            if (z[c] > m) { m = z[c]; am = c; }
+          for (int q4 = 0; q4 < 4; ++q4) {
+            if (4 * q4 < T) {
+#pragma unroll
+              for (int cc = 0; cc < 4; ++cc) {
+                const int c = 4 * q4 + cc;
+                z[c] = c < T ? __uint_as_float(v[c]) + lds32f(bias_s + (c0 + c) * 4) : -INFINITY;
+                if (z[c] > m) { m = z[c]; am = c; }
+              }
+            } else {
+#pragma unroll
+              for (int cc = 0; cc < 4; ++cc) z[4 * q4 + cc] = -INFINITY;
+            }
           }
           if (MODE == FWD_SCORE_MULTI) {
             const int ok = (valid && held && exists && am == yv) ? 1 : 0;
@@ -646,23 +658,43 @@ tc_fwd_kernel(const __grid_constant__ CUtensorMap mapX, const __grid_constant__ 
             const bool train = valid && !held && exists;
             float ssum = 0.f, zy = 0.f, rs[16];
 #pragma unroll
-            for (int c = 0; c < 16; ++c) { rs[c] = c < T ? exp_ftz(z[c] - m) : 0.f; ssum += rs[c]; if (c == yv) zy = z[c]; }
+            for (int q4 = 0; q4 < 4; ++q4) {
+              if (4 * q4 < T) {
+#pragma unroll
+                for (int cc = 0; cc < 4; ++cc) {
+                  const int c = 4 * q4 + cc;
+                  rs[c] = c < T ? exp_ftz(z[c] - m) : 0.f; ssum += rs[c]; if (c == yv) zy = z[c];
+                }
+              } else {
+#pragma unroll
+                for (int cc = 0; cc < 4; ++cc) rs[4 * q4 + cc] = 0.f;
+              }
+            }
             const float sw = (p.cw && train) ? colCw[2 * (c0 + yv)] : 1.f;      // weight of the row's class for this fit
-            const float inv = __fdividef(1.f, ssum);
+            const float scale = train ? sw * __fdividef(1.f, ssum) : 0.f, hot = train ? sw : 0.f;
             const float loss = train ? sw * ((__logf(ssum) + m - zy) - p.loss_shift) : 0.f;
 #pragma unroll
-            for (int c = 0; c < 16; ++c) rs[c] = (train && c < T) ? sw * (rs[c] * inv - (c == yv ? 1.f : 0.f)) : 0.f;
+            for (int q4 = 0; q4 < 4; ++q4)
+              if (4 * q4 < T) {
+#pragma unroll
+                for (int cc = 0; cc < 4; ++cc) { const int c = 4 * q4 + cc; rs[c] = rs[c] * scale - (c == yv ? hot : 0.f); }
+              }
             DML_ACC_N(accA, kMyF, (double)warp_sum(loss));
             DML_ACC_N(accB, kMyF, (double)bfly16(rs, lane));
             if (rt < n_row_tiles) {
+              // a fit's T columns sit in one 32-column chunk of R or straddle into the next one
+              const int colb = slot0 + c0, cross = 32 - (colb & 31);
+              const int64_t o0 = (int64_t)(colb >> 5) * p.r_chunk_stride + lrow * 32 + (colb & 31);
+              const int64_t hop = p.r_chunk_stride - 32;
 #pragma unroll
-              for (int c = 0; c < 16; ++c) {
-                const int col = slot0 + c0 + c;
-                if (c < T && col < p.ldr) {
-                  const int64_t o = (int64_t)(col >> 5) * p.r_chunk_stride + lrow * 32 + (col & 31);
-                  p.R[o] = rs[c];
+              for (int q4 = 0; q4 < 4; ++q4)
+                if (4 * q4 < T) {
+#pragma unroll
+                  for (int cc = 0; cc < 4; ++cc) {
+                    const int c = 4 * q4 + cc;
+                    if (c < T && colb + c < p.ldr) p.R[o0 + c + (c >= cross ? hop : 0)] = rs[c];
+                  }
                 }
-              }
             }
           }
         }

@@ -18,6 +18,9 @@ oracle is therefore pinned two ways:
     ``task_handler.create_subtasks`` in this container -- the fixtures under
     ``tests/golden/`` were produced by ``tests/golden/make_golden.py`` from those
     imports.
+  * full-size pins: ``tests/golden/cfg2_full.npz`` (scikit-learn on float64, all 320 fits of BASELINE.json config 2,
+    made by ``tests/golden/make_cfg_full.py``) and ``tests/golden/cfg3_full.npz`` (``ridge.py``'s solver from float64
+    moments of all 4M rows, anchored by one scikit-learn Ridge fit, ``tests/golden/make_cfg3_full.py``).
   * ``lbfgs.py`` / ``ridge.py`` / ``folds.py`` restate the published algorithms
     (L-BFGS-B + MINPACK-2 dcsrch, Cholesky ridge, (Stratified)KFold) in numpy
     fp64 and are checked against scikit-learn / scipy in ``tests/test_oracle_*``.
