@@ -46,6 +46,7 @@ def test_row_shard_blocks_through_master_and_workers_match_one_gpu():
     Xr, yr = make_dataset("regression", 50_000, 64, seed=22)
     pkg.register_dataset("rows-reg", Xr, yr)
     est = GridSearchCV(LogisticRegression(), {"C": [float(c) for c in np.logspace(-4, 1, 6)]}, cv=5)
+    estw = GridSearchCV(LogisticRegression(class_weight="balanced"), {"C": [0.01, 1.0]}, cv=5, return_train_score=True)
     estr = GridSearchCV(Ridge(), {"alpha": [0.1, 10.0, 1000.0]}, cv=5)
     got = {}
     for label, gpus, part in (("one", [0], "candidates"), ("rows", list(range(n_gpus)), "rows"), ("cand", list(range(n_gpus)), "candidates")):
@@ -55,12 +56,14 @@ def test_row_shard_blocks_through_master_and_workers_match_one_gpu():
             assert r["job_status"] == "completed", r
             rr = m.train(estr, "rows-reg", wait_for_completion=True)
             assert rr["job_status"] == "completed", rr
-            got[label] = (r["job_result"], rr["job_result"])
+            rw = m.train(estw, "rows-bin", wait_for_completion=True)      # class weights + training scores, sharded
+            assert rw["job_status"] == "completed", rw
+            got[label] = (r["job_result"], rr["job_result"], rw["job_result"])
         finally:
             m.close()
     one, rows, cand = got["one"], got["rows"], got["cand"]
-    for label, (a, b) in got.items():          # a failed candidate carries its error: show it instead of a NaN score
-        assert not [x["error"] for x in a["results"] + b["results"] if x.get("error")], label
+    for label, (a, b, c) in got.items():       # a failed candidate carries its error: show it instead of a NaN score
+        assert not [x["error"] for x in a["results"] + b["results"] + c["results"] if x.get("error")], label
     assert all(x["executor"] == "b200" and x["row_shards"] == n_gpus for x in rows[0]["results"])
     for other in (rows, cand):
         assert other[0]["cv_results_"]["mean_test_score"] == one[0]["cv_results_"]["mean_test_score"]     # counts are exact
@@ -69,3 +72,8 @@ def test_row_shard_blocks_through_master_and_workers_match_one_gpu():
         assert [x["accuracy"] for x in other[0]["results"]] == [x["accuracy"] for x in one[0]["results"]]
         np.testing.assert_allclose(other[1]["cv_results_"]["mean_test_score"], one[1]["cv_results_"]["mean_test_score"], rtol=1e-6)
         assert other[1]["best_params_"] == one[1]["best_params_"]
+        assert other[2]["cv_results_"]["mean_test_score"] == one[2]["cv_results_"]["mean_test_score"]
+        np.testing.assert_allclose(other[2]["cv_results_"]["mean_train_score"], one[2]["cv_results_"]["mean_train_score"], atol=1e-6)
+    gsw = GridSearchCV(LogisticRegression(class_weight="balanced"), {"C": [0.01, 1.0]}, cv=5, return_train_score=True).fit(X.astype(np.float64), y)
+    np.testing.assert_allclose(rows[2]["cv_results_"]["mean_test_score"], gsw.cv_results_["mean_test_score"], atol=1e-4)
+    np.testing.assert_allclose(rows[2]["cv_results_"]["mean_train_score"], gsw.cv_results_["mean_train_score"], atol=1e-4)
