@@ -218,6 +218,12 @@ __device__ __forceinline__ uint32_t pack_bf16(float lo_k, float hi_k) {   // ele
 }
 
 constexpr uint32_t kHiMask = 0xffffe000u;
+// class weights in the forward epilogues; -DDML_NO_CW compiles them out (A/B builds only)
+#ifdef DML_NO_CW
+#define DML_HAS_CW(p) false
+#else
+#define DML_HAS_CW(p) ((p).cw != nullptr)
+#endif
 __device__ __forceinline__ float tf32_hi(float x) { return __uint_as_float(__float_as_uint(x) & kHiMask); }
 
 __device__ __forceinline__ float4 lds128(uint32_t a) {
@@ -588,7 +594,7 @@ tc_fwd_kernel(const __grid_constant__ CUtensorMap mapX, const __grid_constant__ 
           cur_cb = cb;
           asm volatile("bar.sync 1, %0;" ::"n"(128 * G) : "memory");
           for (int c = et; c < NC; c += 128 * G) colBias[c] = slot0 + c < n_live ? __ldg(p.bt + slot0 + c) : 0.f;
-          if (p.cw) for (int c = et; c < NC; c += 128 * G) colCw[2 * c] = slot0 + c < n_live ? __ldg(p.cw + (int64_t)(slot0 + c) * 2) : 1.f;
+          if (DML_HAS_CW(p)) for (int c = et; c < NC; c += 128 * G) colCw[2 * c] = slot0 + c < n_live ? __ldg(p.cw + (int64_t)(slot0 + c) * 2) : 1.f;
           for (int e = et; e < (kMaxLabel + 2) * NCH; e += 128 * G) {
             const int v = e / NCH, ci = e % NCH;
             uint32_t bits = 0;
@@ -670,7 +676,7 @@ tc_fwd_kernel(const __grid_constant__ CUtensorMap mapX, const __grid_constant__ 
                 for (int cc = 0; cc < 4; ++cc) rs[4 * q4 + cc] = 0.f;
               }
             }
-            const float sw = (p.cw && train) ? colCw[2 * (c0 + yv)] : 1.f;      // weight of the row's class for this fit
+            const float sw = (DML_HAS_CW(p) && train) ? colCw[2 * (c0 + yv)] : 1.f;      // weight of the row's class for this fit
             const float scale = train ? sw * __fdividef(1.f, ssum) : 0.f, hot = train ? sw : 0.f;
             const float loss = train ? sw * ((__logf(ssum) + m - zy) - p.loss_shift) : 0.f;
 #pragma unroll
@@ -747,7 +753,7 @@ tc_fwd_kernel(const __grid_constant__ CUtensorMap mapX, const __grid_constant__ 
         cur_cb = cb;
         asm volatile("bar.sync 1, %0;" ::"n"(128 * G) : "memory");   // everyone is done with the old column tables
         for (int c = et; c < NC; c += 128 * G) colBias[c] = slot0 + c < n_live ? __ldg(p.bt + slot0 + c) : 0.f;
-        if (MODE == FWD_LOGREG && p.cw)
+        if (MODE == FWD_LOGREG && DML_HAS_CW(p))
           for (int c = et; c < 2 * NC; c += 128 * G) colCw[c] = slot0 + (c >> 1) < n_live ? __ldg(p.cw + (int64_t)slot0 * 2 + c) : 1.f;
         for (int e = et; e < (kMaxLabel + 2) * NCH; e += 128 * G) {
           const int v = e / NCH, ci = e % NCH;
@@ -859,7 +865,7 @@ tc_fwd_kernel(const __grid_constant__ CUtensorMap mapX, const __grid_constant__ 
                 ls[j] = train ? (fmaxf(z, 0.f) - yy * z) + (__logf(1.f + e) - p.loss_shift) : 0.f;
               }
             }
-            if (p.cw) {                      // class weights: the row's class picks one of the column's two weights
+            if (DML_HAS_CW(p)) {             // class weights: the row's class picks one of the column's two weights
               const uint32_t cw_s = smem_u32(colCw) + (uint32_t)(c0 * 8 + yv * 4);
 #pragma unroll
               for (int j = 0; j < 16; ++j) { const float sw = lds32f(cw_s + j * 8); rs[j] *= sw; ls[j] *= sw; }
