@@ -171,7 +171,8 @@ int dml_score(dml_ctx* ctx, const float* X, int64_t n, int d, int64_t ldx,
  * `device` is made current; `stream` is a cudaStream_t (NULL = default stream);
  * the call returns after the stream has drained, with correct_out valid.
  * The first call on each device looks up the array's device address and sets a
- * kernel attribute; make that first call outside of any stream capture.
+ * kernel attribute (threads that make that first call at the same time are
+ * serialised inside the library); make that first call outside of any stream capture.
  * All calls on a device share the one array and the array keeps the previous
  * call's contents (the used part is cleared at the start of each call): two
  * calls that overlap on the same GPU, from any streams or threads, race. */
