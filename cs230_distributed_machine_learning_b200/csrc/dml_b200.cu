@@ -1329,10 +1329,10 @@ extern "C" int dml_ridge_sweep(dml_ctx* ctx, const float* X, int64_t n, int d, i
                        xty_rows, xty_chunks, d_xty};
       {
         const dim3 xg((unsigned)xty_chunks, (unsigned)nf);
-        if (d <= 512 && T <= 2) tc::xty_kernel<2, 2><<<xg, 256, 0, st>>>(xp);
-        else if (d <= 512) tc::xty_kernel<2, 16><<<xg, 256, 0, st>>>(xp);
-        else if (T <= 2) tc::xty_kernel<4, 2><<<xg, 256, 0, st>>>(xp);
-        else tc::xty_kernel<4, 16><<<xg, 256, 0, st>>>(xp);
+        if (d <= 512 && T <= 2) tc::xty_kernel<1, 2><<<xg, 256, 0, st>>>(xp);
+        else if (T <= 2) tc::xty_kernel<2, 2><<<xg, 256, 0, st>>>(xp);
+        else if (d <= 512) tc::xty_scalar_kernel<2, 16><<<xg, 256, 0, st>>>(xp);
+        else tc::xty_scalar_kernel<4, 16><<<xg, 256, 0, st>>>(xp);
       }
       KCHECK();
       tc::GramReduceParams rp{d_Mpart, splits, nb, ldm_tc, d_xty, xty_chunks, d, T, dst};

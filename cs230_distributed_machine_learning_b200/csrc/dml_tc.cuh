@@ -1525,8 +1525,9 @@ struct XtyParams {
   int64_t rows_per_chunk; int chunks;
   float* part;   // [folds][chunks][d + 2][1 + T]
 };
+// one feature per thread and row: the general form (many targets)
 template <int JMAX, int TMAX>   // features per thread (d <= 256 * JMAX), targets (T <= TMAX)
-__global__ void __launch_bounds__(256) xty_kernel(const XtyParams p) {
+__global__ void __launch_bounds__(256) xty_scalar_kernel(const XtyParams p) {
   const int fold = blockIdx.y, ch = blockIdx.x;
   const int64_t r0 = (int64_t)ch * p.rows_per_chunk, r1 = min(p.n, r0 + p.rows_per_chunk);
   const int T = p.T, W = 1 + T;
@@ -1589,6 +1590,120 @@ __global__ void __launch_bounds__(256) xty_kernel(const XtyParams p) {
     out[(int64_t)p.d * W] = cnt; out[(int64_t)(p.d + 1) * W] = 0.f;
 #pragma unroll
     for (int t = 0; t < TMAX; ++t) if (t < T) { out[(int64_t)p.d * W + 1 + t] = sy[t]; out[(int64_t)(p.d + 1) * W + 1 + t] = syy[t]; }
+  }
+}
+
+// Thread = four consecutive features (one 16-byte load per row; the tcgen05 path guarantees 16-byte aligned rows)
+// times JV groups 512 features apart, and one of two row phases (even / odd rows of the chunk); the two phases are
+// added through shared memory at the end.  The scalar one-feature-per-thread form this replaces was bound by
+// instruction issue (ncu, config 3: 74 % of the issue slots at 3.2 TB/s).
+template <int JV, int TMAX>   // feature groups per thread (d <= 512 * JV), targets (T <= TMAX)
+__global__ void __launch_bounds__(256) xty_kernel(const XtyParams p) {
+  const int fold = blockIdx.y, ch = blockIdx.x;
+  const int64_t r0 = (int64_t)ch * p.rows_per_chunk, r1 = min(p.n, r0 + p.rows_per_chunk);
+  const int T = p.T, W = 1 + T;
+  const int g = threadIdx.x & 127, ph = threadIdx.x >> 7;
+  float ax[JV][4], axy[JV][4][TMAX];
+#pragma unroll
+  for (int a = 0; a < JV; ++a)
+#pragma unroll
+    for (int e = 0; e < 4; ++e) { ax[a][e] = 0.f;
+#pragma unroll
+      for (int t = 0; t < TMAX; ++t) axy[a][e][t] = 0.f; }
+  float cnt = 0.f, sy[TMAX], syy[TMAX];
+#pragma unroll
+  for (int t = 0; t < TMAX; ++t) { sy[t] = 0.f; syy[t] = 0.f; }
+  constexpr int U = 4;                                  // rows in flight per thread
+  for (int64_t rb = r0; rb < r1; rb += 2 * U) {         // r0 and the chunk length are multiples of 16; 2 U = 8 rows share a mask word
+    if (!((p.blockmask[rb >> 4] >> fold) & 1u)) continue;
+    bool in[U]; float4 xv[U][JV];
+#pragma unroll
+    for (int u = 0; u < U; ++u) { const int64_t r = rb + 2 * u + ph; in[u] = (r < r1) && (p.label[r] == fold); }
+#pragma unroll
+    for (int u = 0; u < U; ++u)
+#pragma unroll
+      for (int a = 0; a < JV; ++a) {
+        const int j = 4 * (g + 128 * a);
+        const int64_t r = rb + 2 * u + ph;
+        float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (in[u] && j < p.d) {
+          const float* src = p.X + r * p.ldx + j;
+          if (j + 3 < p.d) v = __ldg(reinterpret_cast<const float4*>(src));
+          else { v.x = __ldg(src); if (j + 1 < p.d) v.y = __ldg(src + 1); if (j + 2 < p.d) v.z = __ldg(src + 2); }
+        }
+        xv[u][a] = v;
+      }
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      if (!in[u]) continue;
+      const int64_t r = rb + 2 * u + ph;
+      float yv[TMAX];
+#pragma unroll
+      for (int t = 0; t < TMAX; ++t) {
+        if (t < T) {
+          if (p.yreg) yv[t] = p.yreg[r];
+          else { const int c = p.ycls[r]; yv[t] = (T == 1 ? (c == 1) : (c == t)) ? 1.f : -1.f; }
+        } else yv[t] = 0.f;
+      }
+#pragma unroll
+      for (int a = 0; a < JV; ++a) {
+        const float x4[4] = {xv[u][a].x, xv[u][a].y, xv[u][a].z, xv[u][a].w};
+#pragma unroll
+        for (int e = 0; e < 4; ++e) {
+          ax[a][e] += x4[e];
+#pragma unroll
+          for (int t = 0; t < TMAX; ++t) if (t < T) axy[a][e][t] = fmaf(x4[e], yv[t], axy[a][e][t]);
+        }
+      }
+      if (g == 0) {
+        cnt += 1.f;
+#pragma unroll
+        for (int t = 0; t < TMAX; ++t) if (t < T) { sy[t] += yv[t]; syy[t] = fmaf(yv[t], yv[t], syy[t]); }
+      }
+    }
+  }
+  // odd-row phase -> shared memory -> even-row phase adds and writes
+  __shared__ float sh[128 * JV * 4 * (1 + TMAX) + 1 + 2 * TMAX];
+  float* shx = sh;
+  if (ph == 1) {
+#pragma unroll
+    for (int a = 0; a < JV; ++a)
+#pragma unroll
+      for (int e = 0; e < 4; ++e) {
+        float* q = shx + (((g * JV + a) * 4 + e) * (1 + TMAX));
+        q[0] = ax[a][e];
+#pragma unroll
+        for (int t = 0; t < TMAX; ++t) q[1 + t] = axy[a][e][t];
+      }
+    if (g == 0) {
+      float* q = sh + 128 * JV * 4 * (1 + TMAX);
+      q[0] = cnt;
+#pragma unroll
+      for (int t = 0; t < TMAX; ++t) { q[1 + t] = sy[t]; q[1 + TMAX + t] = syy[t]; }
+    }
+  }
+  __syncthreads();
+  if (ph == 1) return;
+  float* out = p.part + ((int64_t)fold * p.chunks + ch) * (p.d + 2) * W;
+#pragma unroll
+  for (int a = 0; a < JV; ++a)
+#pragma unroll
+    for (int e = 0; e < 4; ++e) {
+      const int j = 4 * (g + 128 * a) + e;
+      if (j < p.d) {
+        const float* q = shx + (((g * JV + a) * 4 + e) * (1 + TMAX));
+        out[(int64_t)j * W] = ax[a][e] + q[0];
+#pragma unroll
+        for (int t = 0; t < TMAX; ++t) if (t < T) out[(int64_t)j * W + 1 + t] = axy[a][e][t] + q[1 + t];
+      }
+    }
+  if (g == 0) {
+    const float* q = sh + 128 * JV * 4 * (1 + TMAX);
+    out[(int64_t)p.d * W] = cnt + q[0]; out[(int64_t)(p.d + 1) * W] = 0.f;
+#pragma unroll
+    for (int t = 0; t < TMAX; ++t) if (t < T) {
+      out[(int64_t)p.d * W + 1 + t] = sy[t] + q[1 + t]; out[(int64_t)(p.d + 1) * W + 1 + t] = syy[t] + q[1 + TMAX + t];
+    }
   }
 }
 
