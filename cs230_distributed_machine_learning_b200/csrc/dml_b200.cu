@@ -502,6 +502,29 @@ static int run_score(dml_ctx* ctx, int mode, const float* X, int64_t n, int d, i
   return DML_OK;
 }
 
+// mixed[0] = number of 128-row tiles whose rows do not share one fold, mixed[1 ..] = their indices in ascending
+// order (one block; the order fixes which CTA scores which tile, so sums stay reproducible)
+__global__ void mixed_tiles_kernel(const uint8_t* __restrict__ tile_fold, int64_t n_tiles, int n_groups, int* __restrict__ mixed) {
+  __shared__ int base, warp_tot[32];
+  if (threadIdx.x == 0) base = 0;
+  __syncthreads();
+  const int lane = threadIdx.x & 31, w = threadIdx.x >> 5, nw = blockDim.x >> 5;
+  for (int64_t t0 = 0; t0 < n_tiles; t0 += blockDim.x) {
+    const int64_t t = t0 + threadIdx.x;
+    const int flag = (t < n_tiles) ? ((int)tile_fold[t] >= n_groups) : 0;
+    const unsigned bal = __ballot_sync(0xffffffffu, flag);
+    if (lane == 0) warp_tot[w] = __popc(bal);
+    __syncthreads();
+    int off = base;
+    for (int i = 0; i < w; ++i) off += warp_tot[i];
+    if (flag) mixed[1 + off + __popc(bal & ((1u << lane) - 1))] = (int)t;
+    __syncthreads();
+    if (threadIdx.x == 0) { int tt = 0; for (int i = 0; i < nw; ++i) tt += warp_tot[i]; base += tt; }
+    __syncthreads();
+  }
+  if (threadIdx.x == 0) mixed[0] = base;
+}
+
 // ---- scoring pass on the tensor cores (classifier counts or squared errors) -----------------
 // Launches the scoring kernel(s) for prepared parameters `fp` (labels, masks, bias, groups): builds the tensor
 // maps, zeroes `part` ([<= 2 * n_sms * 4][n_slots] entries of `esz` bytes) and returns the number of partial rows.
@@ -510,11 +533,11 @@ static int run_score(dml_ctx* ctx, int mode, const float* X, int64_t n, int d, i
 // covers the tiles that mix folds.
 static int score_launches(dml_ctx* ctx, int mode, int T, const float* X, int64_t n, int d, int64_t ldx,
                           const float* Whi, const float* Wlo, int ldw, int n_slots, tc::TcFwdParams fp,
-                          int group_width, void* part, size_t esz, int64_t* n_parts) {
+                          int group_width, void* part, size_t esz, int64_t* n_parts, int* mixed = nullptr /*[tiles + 1] scratch*/) {
   cudaStream_t st = ctx->stream;
   int NC = pick_nc(n_slots, T);
   if (NC == 0) return fail(ctx, DML_ERR_ARG, "scoring: no column-block width for T=%d", T);
-  const bool by_group = ctx->score_by_group && T == 1 && group_width > 0 && fp.gstart != nullptr && fp.tile_fold != nullptr && mode != tc::FWD_SCORE_MULTI;
+  const bool by_group = ctx->score_by_group && mixed != nullptr && T == 1 && group_width > 0 && fp.gstart != nullptr && fp.tile_fold != nullptr && mode != tc::FWD_SCORE_MULTI;
   if (by_group) { const int cand[5] = {160, 128, 96, 64, 32}; for (int c : cand) if (group_width % c == 0) { NC = c; break; } }
   CUtensorMap mX, mX2, mWh, mWl;
   int rc;
@@ -542,8 +565,9 @@ static int score_launches(dml_ctx* ctx, int mode, int T, const float* X, int64_t
     fp.score_phase = 0;
     rc = launch(1, grid0, fp);
     if (!rc) {
+      mixed_tiles_kernel<<<1, 1024, 0, st>>>(fp.tile_fold, tiles, fp.n_groups, mixed);
       tc::TcFwdParams q = fp;
-      q.score_phase = 1;
+      q.score_phase = 1; q.mixed_tiles = mixed;
       if (q.cntPart) q.cntPart += (size_t)grid0 * 4 * n_slots;
       if (q.ssePart) q.ssePart += (size_t)grid0 * 4 * n_slots;
       rc = launch(1, grid1, q);
@@ -576,7 +600,7 @@ static int run_score_tc(dml_ctx* ctx, int mode, const float* X, int64_t n, int d
                         const float* Wt, int ldw, const float* bt, const int32_t* sel, const int32_t* val,
                         int n_slots, int T, float* Whi, float* Wlo, void* part, int64_t* n_parts,
                         const uint8_t* tile_fold = nullptr, const int* gstart = nullptr, int n_groups = 0, int hold_group = 0,
-                        int group_width = 0) {
+                        int group_width = 0, int* mixed = nullptr) {
   cudaStream_t st = ctx->stream;
   tc::split_weights_kernel<<<(unsigned)cdiv((int64_t)n_slots * ldw, 256), 256, 0, st>>>(Wt, Whi, Wlo, (int64_t)n_slots * ldw);
   ctx->total_launches += 1;
@@ -587,7 +611,7 @@ static int run_score_tc(dml_ctx* ctx, int mode, const float* X, int64_t n, int d
   fp.tile_fold = tile_fold; fp.gstart = gstart; fp.n_groups = n_groups; fp.hold_group = hold_group;
   const int m = (mode == FWD_SCORE_REG) ? FWD_SCORE_REG : (T == 1 ? FWD_SCORE_CLS : tc::FWD_SCORE_MULTI);
   return score_launches(ctx, m, T, X, n, d, ldx, Whi, Wlo, ldw, n_slots, fp, group_width, part,
-                        mode == FWD_SCORE_REG ? sizeof(double) : sizeof(int32_t), n_parts);
+                        mode == FWD_SCORE_REG ? sizeof(double) : sizeof(int32_t), n_parts, mixed);
 }
 // sse[fit] = sum of the partials of the fit's score column (n_cols columns per partial row; see score_slot)
 __global__ void reduce_sse_parts_kernel(const double* part, int64_t n_parts, int n_cols, double* sse,
@@ -670,7 +694,7 @@ struct EvalCtx {
   float *Wt = nullptr, *bt = nullptr, *R = nullptr, *Whi = nullptr, *Wlo = nullptr, *Gpart = nullptr;
   double *lossPart = nullptr, *gbPart = nullptr, *Gred = nullptr, *gb2 = nullptr; int32_t *sel = nullptr, *val = nullptr, *cntPart = nullptr;
   CUtensorMap mXf, mXf2, mXg, mWh, mWl, mR1;   // mR1: residuals, one 32-column chunk x 32 rows per box
-  const int* gstart = nullptr; int n_groups = 0; uint8_t* tile_fold = nullptr;
+  const int* gstart = nullptr; int n_groups = 0; uint8_t* tile_fold = nullptr; int* mixed = nullptr;   // mixed: list of row tiles that mix folds
   int hold_group = 0;                // scoring: column group n_groups belongs to the hold-out fits
   const int* n_list_dev = nullptr;   // device count of live list entries (n_slots passed to evaluate is then an upper bound)   // fold-major column groups of the current list (device), or null   // mXf2: forward X box of a 2-CTA cluster member (64 rows)
   unsigned long long* hist_local = nullptr;   // [512] label histogram of this rank's rows
@@ -710,6 +734,7 @@ struct EvalCtx {
   void take(Arena& a, int64_t n_groups_max) {
     Gred = a.take<double>((size_t)S_max * ldgr);
     tile_fold = a.take<uint8_t>((size_t)cdiv(n, 128) + 16);
+    mixed = a.take<int>((size_t)cdiv(n, 128) + 8);
     hist_local = a.take<unsigned long long>(512);
     Wt = a.take<float>((size_t)S_max * ldw); bt = a.take<float>(S_max);
     sel = a.take<int32_t>(S_max); val = a.take<int32_t>(S_max);
@@ -848,7 +873,7 @@ struct EvalCtx {
       fp.cntPart = cntPart;
       fp.tile_fold = tile_fold; fp.gstart = gstart; fp.n_groups = n_groups; fp.hold_group = hold_group;
       return score_launches(ctx, T == 1 ? (int)FWD_SCORE_CLS : (int)tc::FWD_SCORE_MULTI, T, X, n, d, ldx, Whi, Wlo, ldw, n_slots, fp,
-                            group_width, cntPart, sizeof(int32_t), n_parts);
+                            group_width, cntPart, sizeof(int32_t), n_parts, mixed);
     }
     *n_parts = tiles_total;
     return run_score(ctx, FWD_SCORE_CLS, X, n, d, ldx, y, nullptr, fold_id, hold_id, Wt, ldw, bt, sel, val, n_slots, T, cntPart);
@@ -1273,7 +1298,7 @@ extern "C" int dml_ridge_sweep(dml_ctx* ctx, const float* X, int64_t n, int d, i
   // fold-major score columns (see dml_logreg_sweep): group k = the fits that hold out fold k, padded to 32
   const int npad = (score_tc && T == 1 && ctx->fold_skip && n_folds >= 2) ? (int)rup(n_cand, 32) : 0;
   const int64_t S_score = npad ? (int64_t)fpc * npad : S_all;
-  uint8_t* d_tfold = nullptr; int* d_gs = nullptr;
+  uint8_t* d_tfold = nullptr; int* d_gs = nullptr; int* d_mixed = nullptr;
   double *d_Mfold, *d_Mtot, *d_A, *d_AT, *d_B, *d_mu, *d_stats, *d_sse, *d_statpart; int32_t *d_sel, *d_val, *d_info; long long* d_cnt;
   for (int pass = 0; pass < 2; ++pass) {
     Arena a(pass ? ctx->ws : nullptr);
@@ -1289,6 +1314,7 @@ extern "C" int dml_ridge_sweep(dml_ctx* ctx, const float* X, int64_t n, int d, i
     d_Wt = a.take<float>((size_t)S_score * ldw); d_bt = a.take<float>(S_score);
     d_sel = a.take<int32_t>(S_score); d_val = a.take<int32_t>(S_score);
     d_tfold = a.take<uint8_t>((size_t)cdiv(n, 128) + 16); d_gs = a.take<int>(fpc + 1);
+    d_mixed = a.take<int>((size_t)cdiv(n, 128) + 8);
     d_info = a.take<int32_t>(F); d_cnt = a.take<long long>(F);
     d_stats = a.take<double>(4 * 256); d_sse = a.take<double>(S_all);
     d_statpart = a.take<double>(256 * (size_t)kStatSlices * 2);
@@ -1412,7 +1438,7 @@ extern "C" int dml_ridge_sweep(dml_ctx* ctx, const float* X, int64_t n, int d, i
   if (score_tc) {
     rc = run_score_tc(ctx, is_classifier ? FWD_SCORE_CLS : FWD_SCORE_REG, X, n, d, ldx, y_cls, y_reg, fold_id, hold_id,
                       d_Wt, ldw, d_bt, d_sel, d_val, (int)S_score, T, d_Whi, d_Wlo, d_part_tc, &n_parts,
-                      npad ? d_tfold : nullptr, npad ? d_gs : nullptr, n_folds, has_hold, npad);
+                      npad ? d_tfold : nullptr, npad ? d_gs : nullptr, n_folds, has_hold, npad, d_mixed);
     parts = d_part_tc;
   } else {
     rc = run_score(ctx, is_classifier ? FWD_SCORE_CLS : FWD_SCORE_REG, X, n, d, ldx, y_cls, y_reg, fold_id, hold_id,

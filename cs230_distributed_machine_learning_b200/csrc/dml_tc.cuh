@@ -294,6 +294,7 @@ struct TcFwdParams {
   // columns instead of once per pair of column blocks.  score_phase 0: those tiles; score_phase 1: the few
   // tiles that mix folds, against every block.  Both launches skip the other's tiles.
   int score_bpg, score_phase;
+  const int* mixed_tiles;                // score_phase 1: [0] = number of row tiles that mix folds, [1 ..] = their indices, ascending
   int grad_skips;                        // what the gradient kernel leaves unread of a hole, so nothing is stored there:
                                          // 1 = whole 64-column segments, 2 = 32-column chunks (TcGradParams::seg_skip)
   // n_slots is the host's upper bound (and the pitch of the partial-sum arrays); when n_list_dev is set the
@@ -404,17 +405,22 @@ tc_fwd_kernel(const __grid_constant__ CUtensorMap mapX, const __grid_constant__ 
   const int64_t cb_groups = (ncb_live + CL - 1) / CL;            // column blocks are dealt out CL at a time
   constexpr bool kScoreAny = MODE == FWD_SCORE_CLS || MODE == FWD_SCORE_REG;
   const bool by_group = kScoreAny && CL == 1 && p.score_bpg > 0 && p.gstart != nullptr;
-  const int64_t n_jobs = by_group ? n_row_tiles * (p.score_phase == 0 ? p.score_bpg * (1 + (p.hold_group ? 1 : 0)) : ncb_live)
+  // second scoring launch: only the listed tiles (looking every tile's fold up again cost one dependent global load
+  // per job and role: 0.47 ms at config 3 for four tiles of real work)
+  const bool by_list = by_group && p.score_phase == 1;
+  const int64_t n_mixed = by_list ? p.mixed_tiles[0] : 0;
+  const int64_t n_jobs = by_list ? n_mixed * ncb_live
+                       : by_group ? n_row_tiles * (p.score_bpg * (1 + (p.hold_group ? 1 : 0)))
                                   : n_row_tiles * cb_groups;     // jobs per cluster (column-block group major)
   const int64_t job0 = blockIdx.x / CL, job_step = gridDim.x / CL;
-  auto job_rt = [&](int64_t job) { return job % n_row_tiles; };
+  auto job_rt = [&](int64_t job) -> int64_t { return by_list ? (int64_t)p.mixed_tiles[1 + job % n_mixed] : job % n_row_tiles; };
   // column block of a job; -1 = nothing to do for this job in this launch (every role skips it)
   auto job_cb = [&](int64_t job) -> int {
+    if (by_list) return (int)(job / n_mixed);
     if (!by_group) return (int)(job / n_row_tiles) * CL + crank;                     // may be >= n_col_blocks (no columns)
     const int j = (int)(job / n_row_tiles);
     const int k = (int)p.tile_fold[p.row0 / 128 + job % n_row_tiles];
-    if (p.score_phase == 1) return k >= p.n_groups ? j : -1;
-    if (k >= p.n_groups) return -1;
+    if (k >= p.n_groups) return -1;                                                  // a tile that mixes folds: second launch
     return j < p.score_bpg ? k * p.score_bpg + j : p.n_groups * p.score_bpg + (j - p.score_bpg);
   };
   // block-local column range [sa, sb) that a tile whose rows all sit in fold k does not train
