@@ -243,6 +243,9 @@ __device__ __forceinline__ float exp_ftz(float x) {
   return y;
 }
 __device__ __forceinline__ float lds32f(uint32_t a) { float v; asm volatile("ld.shared.f32 %0, [%1];" : "=f"(v) : "r"(a)); return v; }
+__device__ __forceinline__ double lds64d(uint32_t a) { double v; asm volatile("ld.shared.f64 %0, [%1];" : "=d"(v) : "r"(a)); return v; }
+__device__ __forceinline__ void sts64d(uint32_t a, double v) { asm volatile("st.shared.f64 [%0], %1;" ::"r"(a), "d"(v) : "memory"); }
+__device__ __forceinline__ void stg64(float* a, float x, float y) { asm volatile("st.global.v2.f32 [%0], {%1, %2};" ::"l"(a), "f"(x), "f"(y) : "memory"); }
 __device__ __forceinline__ uint32_t lds16u(uint32_t a) { uint16_t v; asm volatile("ld.shared.u16 %0, [%1];" : "=h"(v) : "r"(a)); return v; }
 
 // split a stage buffer: lo <- x - (x & mask) (and optionally hi <- x & mask).  `bytes` multiple of
@@ -267,7 +270,7 @@ __device__ __forceinline__ void split_stage(uint32_t hi, uint32_t lo, int bytes,
 
 // ---------------------------------------------------------------- forward kernel
 constexpr int kFwdStages = 3;
-constexpr int kFwdEpiGroups = 4;    // epilogue warps per TMEM lane quadrant
+constexpr int kFwdEpiGroups = 4;    // epilogue warps per TMEM lane quadrant (FwdSmem::kMultiAcc is sized for 4)
 // warps 0-3 operand staging, 4 .. 4+4G-1 epilogue, then the TMA producer and the MMA issuer: the SM's warp
 // arbiter favours the highest warp id, and the two single-thread roles must never wait behind the math warps
 constexpr int kFwdThreads = 192 + 128 * kFwdEpiGroups;
@@ -322,7 +325,9 @@ struct FwdSmem {
   static constexpr int kB = NC * 128;
   static constexpr int kStage = kA + 2 * kB;
   // per column: bias; per label value: 16-bit held-column masks, one per 16-column chunk
-  static constexpr int kMeta = NC * 4 + (kMaxLabel + 2) * (NC / 16) * 2 + (kMaxLabel + 2) * 4 + 64 + NC * 8;   // + column-group starts, class weights
+  // multinomial epilogue: fp64 running sums of every epilogue warp, [warp][fit of the warp][17] (16 class columns + the loss)
+  static constexpr int kMultiAcc = 16 * (32 / 4) * 17 * 8;
+  static constexpr int kMeta = NC * 4 + (kMaxLabel + 2) * (NC / 16) * 2 + (kMaxLabel + 2) * 4 + 64 + NC * 8 + kMultiAcc;   // + column-group starts, class weights
   static constexpr int kBytes = kFwdStages * kStage + 1024 /*align*/ + 256 /*barriers*/ + kMeta;
 };
 
@@ -355,6 +360,7 @@ __device__ __forceinline__ T bfly16(const T (&v)[16], int lane) {
 // column blocks (2k, 2k+1); each CTA fetches half of every X chunk and TMA-multicasts it to both, so
 // X crosses HBM / L2 once per row tile instead of once per (row tile, column block).
 template <int NC, int MODE, int CL>
+// (22 warps = 6 on the fullest of the four SM sub-partitions x 16 384 registers: 80 per thread is the ceiling at this block size)
 __global__ void __launch_bounds__(kFwdThreads, 1)
 tc_fwd_kernel(const __grid_constant__ CUtensorMap mapX, const __grid_constant__ CUtensorMap mapWhi,
               const __grid_constant__ CUtensorMap mapWlo, const TcFwdParams p) {
@@ -374,6 +380,7 @@ tc_fwd_kernel(const __grid_constant__ CUtensorMap mapX, const __grid_constant__ 
   uint16_t* heldTab = reinterpret_cast<uint16_t*>(colBias + NC);                     // [kMaxLabel + 2][NC / 16]
   int* gsTab = reinterpret_cast<int*>(heldTab + (kMaxLabel + 2) * (NC / 16));        // [n_groups + 1] copy of p.gstart
   float* colCw = reinterpret_cast<float*>((reinterpret_cast<uintptr_t>(gsTab + kMaxLabel + 2) + 7) & ~(uintptr_t)7);   // [NC][2] class weights
+  double* accS = reinterpret_cast<double*>(colCw + 2 * NC);                          // multinomial running sums, FwdSmem::kMultiAcc bytes
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   // tensor memory: two accumulators of NC columns, then per stage 32 columns of X_hi and 32 of X_lo
@@ -408,7 +415,7 @@ tc_fwd_kernel(const __grid_constant__ CUtensorMap mapX, const __grid_constant__ 
   // second scoring launch: only the listed tiles (looking every tile's fold up again cost one dependent global load
   // per job and role: 0.47 ms at config 3 for four tiles of real work)
   const bool by_list = by_group && p.score_phase == 1;
-  const int64_t n_mixed = by_list ? p.mixed_tiles[0] : 0;
+  const int64_t n_mixed = by_list ? p.mixed_tiles[0] : 1;      // (1: never used as a count, only keeps the divisions below defined)
   const int64_t n_jobs = by_list ? n_mixed * ncb_live
                        : by_group ? n_row_tiles * (p.score_bpg * (1 + (p.hold_group ? 1 : 0)))
                                   : n_row_tiles * cb_groups;     // jobs per cluster (column-block group major)
@@ -562,35 +569,60 @@ tc_fwd_kernel(const __grid_constant__ CUtensorMap mapX, const __grid_constant__ 
       // g, g + G, ... of the column block; thread = row.  softmax / first arg-max over the T columns. =====
       constexpr int G = kFwdEpiGroups;
       constexpr int kMyF = 32 / G;                          // fits per warp: the host only picks NC / T <= 32
-      const int T = p.T, nfit = NC / T;
       const int q = warp & 3, grp = (warp - 4) >> 2;
       const int qrow = q * 32 + lane;
       const int et = threadIdx.x - 128;
       const int mycol = bfly_col(lane);
-      double accA[kMyF], accB[kMyF]; int accC[kMyF];
+      // Running sums.  Training: fp64 in shared memory, one row of 17 per (warp, fit of the warp): entry c < T is the
+      // intercept gradient of class c, entry 15 the loss (T = 16: entry 16, summed on its own).  The lane that
+      // bfly16 leaves column c on (the even lane with bfly_col == c) owns the entry; nothing else touches it, so
+      // no barrier is needed, and the rolled fit loop needs no predicated walk over register arrays.
+      // Scoring: one count per fit in registers.
+      int accC[kMyF];
 #pragma unroll
-      for (int i = 0; i < kMyF; ++i) { accA[i] = 0.0; accB[i] = 0.0; accC[i] = 0; }
+      for (int i = 0; i < kMyF; ++i) accC[i] = 0;
+      const uint32_t acc_s = smem_u32(accS) + (uint32_t)(((warp - 4) * kMyF) * 17 * 8);
+      const bool own_col = !(lane & 1);
+      if (MODE == FWD_LOGREG_MULTI) {
+#pragma unroll
+        for (int i = 0; i < kMyF; ++i) {
+          if (own_col) sts64d(acc_s + (i * 17 + mycol) * 8, 0.0);
+          if (lane == 0) sts64d(acc_s + (i * 17 + 16) * 8, 0.0);
+        }
+      }
       int cur_cb = -1;
       const int64_t part_row = ((int64_t)blockIdx.x * 4 + q) * p.n_slots;
       const uint32_t bias_s = smem_u32(colBias), held_s = smem_u32(heldTab);
       constexpr int NCH = NC / 16;
+      const int T = p.T, nfit = NC / T;
       auto flush = [&](int cb) {
         if (cb < 0) return;
 #pragma unroll
         for (int i = 0; i < kMyF; ++i) {
           const int f = G * i + grp;
           const int slot = cb * NC + f * T;
-          if (f < nfit && slot < p.n_slots) {
-            if (MODE == FWD_LOGREG_MULTI) {
-              if (lane == 0) p.lossPart[part_row + slot] = accA[i];
-              if (!(lane & 1) && mycol < T) p.gbPart[part_row + slot + mycol] = accB[i];
-            } else if (lane == 0) p.cntPart[part_row + slot] = accC[i];
+          const bool live = f < nfit && slot < p.n_slots;
+          if (MODE == FWD_LOGREG_MULTI) {
+            const uint32_t mine = acc_s + (i * 17 + mycol) * 8, loss_a = acc_s + (i * 17 + 16) * 8;
+            if (own_col) {
+              const double a = lds64d(mine);
+              if (live && mycol < T) p.gbPart[part_row + slot + mycol] = a;
+              if (live && mycol == 15 && T < 16) p.lossPart[part_row + slot] = a;
+              sts64d(mine, 0.0);
+            }
+            if (lane == 0) {
+              if (live && T == 16) p.lossPart[part_row + slot] = lds64d(loss_a);
+              sts64d(loss_a, 0.0);
+            }
+          } else {
+            if (live && lane == 0) p.cntPart[part_row + slot] = accC[i];
+            accC[i] = 0;
           }
-          accA[i] = 0.0; accB[i] = 0.0; accC[i] = 0;
         }
       };
       int last_f = -1;
       for (int i = 0; i < kMyF; ++i) if (G * i + grp < nfit) last_f = G * i + grp;
+      const bool even_T = !(T & 1);
       uint32_t tile = 0;
       for (int64_t job = job0; job < n_jobs; job += job_step, ++tile) {
         const int cb = job_cb(job); const int64_t rt = job_rt(job);
@@ -628,6 +660,7 @@ tc_fwd_kernel(const __grid_constant__ CUtensorMap mapX, const __grid_constant__ 
         }
         const uint32_t held_f = held_s + fold_v * NCH * 2, held_h = held_s + (kMaxLabel + hold_v) * NCH * 2;
         const int acc = tile & 1; const uint32_t aph = (tile >> 1) & 1;
+        float* const r_row = MODE == FWD_LOGREG_MULTI ? p.R + lrow * 32 : nullptr;      // this row inside a 32-column chunk of R
         mbar_wait(tfull + acc, aph);
         tc_fence_after();
         const uint32_t tacc = tmem_base + acc * NC + ((uint32_t)(q * 32) << 16);
@@ -691,22 +724,46 @@ tc_fwd_kernel(const __grid_constant__ CUtensorMap mapX, const __grid_constant__ 
 #pragma unroll
                 for (int cc = 0; cc < 4; ++cc) { const int c = 4 * q4 + cc; rs[c] = rs[c] * scale - (c == yv ? hot : 0.f); }
               }
-            DML_ACC_N(accA, kMyF, (double)warp_sum(loss));
-            DML_ACC_N(accB, kMyF, (double)bfly16(rs, lane));
             if (rt < n_row_tiles) {
-              // a fit's T columns sit in one 32-column chunk of R or straddle into the next one
+              // A fit's T columns sit in one 32-column chunk of R or straddle into the next one: two row
+              // pointers, picked per element.  T even: the fit starts on an even column, a pair of classes
+              // never straddles (chunks are 32 wide) and goes out as one 8-byte store.
               const int colb = slot0 + c0, cross = 32 - (colb & 31);
-              const int64_t o0 = (int64_t)(colb >> 5) * p.r_chunk_stride + lrow * 32 + (colb & 31);
-              const int64_t hop = p.r_chunk_stride - 32;
+              float* const pa = r_row + ((int64_t)(colb >> 5) * p.r_chunk_stride + (colb & 31));
+              float* const pb = pa + (p.r_chunk_stride - 32);
+              if (even_T && colb + T <= p.ldr) {
 #pragma unroll
-              for (int q4 = 0; q4 < 4; ++q4)
-                if (4 * q4 < T) {
+                for (int q4 = 0; q4 < 4; ++q4)
+                  if (4 * q4 < T) {
 #pragma unroll
-                  for (int cc = 0; cc < 4; ++cc) {
-                    const int c = 4 * q4 + cc;
-                    if (c < T && colb + c < p.ldr) p.R[o0 + c + (c >= cross ? hop : 0)] = rs[c];
+                    for (int cc = 0; cc < 4; cc += 2) {
+                      const int c = 4 * q4 + cc;
+                      if (c < T) stg64((c >= cross ? pb : pa) + c, rs[c], rs[c + 1]);
+                    }
                   }
-                }
+              } else {
+#pragma unroll
+                for (int q4 = 0; q4 < 4; ++q4)
+                  if (4 * q4 < T) {
+#pragma unroll
+                    for (int cc = 0; cc < 4; ++cc) {
+                      const int c = 4 * q4 + cc;
+                      if (c < T && colb + c < p.ldr) (c >= cross ? pb : pa)[c] = rs[c];
+                    }
+                  }
+              }
+            }
+            // column sums over the warp's 32 rows in fp32, then into the fp64 running sums; the loss rides along
+            // as column 15 of the same butterfly when that slot is free
+            if (T < 16) rs[15] = loss;                       // slot 15 held a zero
+            const float colsum = bfly16(rs, lane);
+            if (own_col && (mycol < T || mycol == 15)) {
+              const uint32_t mine = acc_s + (i * 17 + mycol) * 8;
+              sts64d(mine, lds64d(mine) + (double)colsum);
+            }
+            if (T == 16) {
+              const float ls = warp_sum(loss);
+              if (lane == 0) { const uint32_t la = acc_s + (i * 17 + 16) * 8; sts64d(la, lds64d(la) + (double)ls); }
             }
           }
         }
