@@ -246,6 +246,8 @@ __device__ __forceinline__ float lds32f(uint32_t a) { float v; asm volatile("ld.
 __device__ __forceinline__ double lds64d(uint32_t a) { double v; asm volatile("ld.shared.f64 %0, [%1];" : "=d"(v) : "r"(a)); return v; }
 __device__ __forceinline__ void sts64d(uint32_t a, double v) { asm volatile("st.shared.f64 [%0], %1;" ::"r"(a), "d"(v) : "memory"); }
 __device__ __forceinline__ void stg64(float* a, float x, float y) { asm volatile("st.global.v2.f32 [%0], {%1, %2};" ::"l"(a), "f"(x), "f"(y) : "memory"); }
+__device__ __forceinline__ float2 lds64f(uint32_t a) { float2 v; asm volatile("ld.shared.v2.f32 {%0, %1}, [%2];" : "=f"(v.x), "=f"(v.y) : "r"(a)); return v; }
+__device__ __forceinline__ void sts64f(uint32_t a, float x, float y) { asm volatile("st.shared.v2.f32 [%0], {%1, %2};" ::"r"(a), "f"(x), "f"(y) : "memory"); }
 __device__ __forceinline__ uint32_t lds16u(uint32_t a) { uint16_t v; asm volatile("ld.shared.u16 %0, [%1];" : "=h"(v) : "r"(a)); return v; }
 
 // split a stage buffer: lo <- x - (x & mask) (and optionally hi <- x & mask).  `bytes` multiple of
@@ -327,8 +329,11 @@ struct FwdSmem {
   // per column: bias; per label value: 16-bit held-column masks, one per 16-column chunk
   // multinomial epilogue: fp64 running sums of every epilogue warp, [warp][fit of the warp][17] (16 class columns + the loss)
   static constexpr int kMultiAcc = 16 * (32 / 4) * 17 * 8;
-  static constexpr int kMeta = NC * 4 + (kMaxLabel + 2) * (NC / 16) * 2 + (kMaxLabel + 2) * 4 + 64 + NC * 8 + kMultiAcc;   // + column-group starts, class weights
+  // multinomial epilogue: [32 rows][T <= 16] fp32 residuals of one fit per epilogue warp, turned row-major -> line-major before they are stored
+  static constexpr int kMultiStage = 16 * 32 * 16 * 4;
+  static constexpr int kMeta = NC * 4 + (kMaxLabel + 2) * (NC / 16) * 2 + (kMaxLabel + 2) * 4 + 64 + NC * 8 + kMultiAcc + kMultiStage;   // + column-group starts, class weights
   static constexpr int kBytes = kFwdStages * kStage + 1024 /*align*/ + 256 /*barriers*/ + kMeta;
+  static_assert(kBytes <= 227 * 1024, "forward kernel: shared memory of one CTA");
 };
 
 // Sum v[c] over the 32 lanes of the warp for 16 columns with 16 shuffles (recursive halving):
@@ -381,6 +386,7 @@ tc_fwd_kernel(const __grid_constant__ CUtensorMap mapX, const __grid_constant__ 
   int* gsTab = reinterpret_cast<int*>(heldTab + (kMaxLabel + 2) * (NC / 16));        // [n_groups + 1] copy of p.gstart
   float* colCw = reinterpret_cast<float*>((reinterpret_cast<uintptr_t>(gsTab + kMaxLabel + 2) + 7) & ~(uintptr_t)7);   // [NC][2] class weights
   double* accS = reinterpret_cast<double*>(colCw + 2 * NC);                          // multinomial running sums, FwdSmem::kMultiAcc bytes
+  float* stageS = reinterpret_cast<float*>(reinterpret_cast<uint8_t*>(accS) + L::kMultiAcc);   // multinomial residual staging, FwdSmem::kMultiStage bytes
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   // tensor memory: two accumulators of NC columns, then per stage 32 columns of X_hi and 32 of X_lo
@@ -623,6 +629,15 @@ tc_fwd_kernel(const __grid_constant__ CUtensorMap mapX, const __grid_constant__ 
       int last_f = -1;
       for (int i = 0; i < kMyF; ++i) if (G * i + grp < nfit) last_f = G * i + grp;
       const bool even_T = !(T & 1);
+      // Residual stores, T even.  A thread holds one ROW of a fit (T floats of that row's 128-byte line of R), so a
+      // store instruction straight from registers touches 32 lines for 8 bytes each, and the L1 spends one tag
+      // cycle per line: 160 per fit at T = 10, which is what bounded this epilogue (ncu: warps waiting to reuse
+      // the address registers of stores still queued).  The fit's 32 x T block goes through shared memory instead
+      // and leaves line-major: pair number lane + 32 k of the block (T / 2 pairs per row), 32 / (T / 2) rows and
+      // about 7 lines per instruction.
+      const int H = T >> 1;
+      const uint32_t stage_s = smem_u32(stageS) + (uint32_t)((warp - 4) * (32 * 16 * 4));
+      const int pr0 = even_T ? lane / H : 0, pc0 = even_T ? lane % H : 0, pdq = even_T ? 32 / H : 0, pdr = even_T ? 32 % H : 0;
       uint32_t tile = 0;
       for (int64_t job = job0; job < n_jobs; job += job_step, ++tile) {
         const int cb = job_cb(job); const int64_t rt = job_rt(job);
@@ -685,10 +700,20 @@ tc_fwd_kernel(const __grid_constant__ CUtensorMap mapX, const __grid_constant__ 
 #pragma unroll
           for (int q4 = 0; q4 < 4; ++q4) {
             if (4 * q4 < T) {
+              float b4[4];
+              if (even_T) {                        // c0 even: the intercepts of a pair of classes are one 8-byte word
+                const float2 b01 = lds64f(bias_s + (c0 + 4 * q4) * 4);
+                b4[0] = b01.x; b4[1] = b01.y;
+                if (4 * q4 + 2 < T) { const float2 b23 = lds64f(bias_s + (c0 + 4 * q4 + 2) * 4); b4[2] = b23.x; b4[3] = b23.y; }
+                else { b4[2] = 0.f; b4[3] = 0.f; }
+              } else {
+#pragma unroll
+                for (int cc = 0; cc < 4; ++cc) b4[cc] = 4 * q4 + cc < T ? lds32f(bias_s + (c0 + 4 * q4 + cc) * 4) : 0.f;
+              }
 #pragma unroll
               for (int cc = 0; cc < 4; ++cc) {
                 const int c = 4 * q4 + cc;
-                z[c] = c < T ? __uint_as_float(v[c]) + lds32f(bias_s + (c0 + c) * 4) : -INFINITY;
+                z[c] = c < T ? __uint_as_float(v[c]) + b4[cc] : -INFINITY;
                 if (z[c] > m) { m = z[c]; am = c; }
               }
             } else {
@@ -732,15 +757,31 @@ tc_fwd_kernel(const __grid_constant__ CUtensorMap mapX, const __grid_constant__ 
               float* const pa = r_row + ((int64_t)(colb >> 5) * p.r_chunk_stride + (colb & 31));
               float* const pb = pa + (p.r_chunk_stride - 32);
               if (even_T && colb + T <= p.ldr) {
+                const uint32_t mine = stage_s + (uint32_t)(lane * T * 4);
 #pragma unroll
                 for (int q4 = 0; q4 < 4; ++q4)
                   if (4 * q4 < T) {
 #pragma unroll
                     for (int cc = 0; cc < 4; cc += 2) {
                       const int c = 4 * q4 + cc;
-                      if (c < T) stg64((c >= cross ? pb : pa) + c, rs[c], rs[c + 1]);
+                      if (c < T) sts64f(mine + c * 4, rs[c], rs[c + 1]);
                     }
                   }
+                __syncwarp();
+                float* const g0 = pa - lane * 32;                 // the warp's first row
+                const int64_t hop = p.r_chunk_stride - 32;
+                int prow = pr0, pcol = pc0;
+#pragma unroll
+                for (int k = 0; k < 8; ++k) {
+                  if (k < H) {
+                    const float2 v2 = lds64f(stage_s + (uint32_t)((lane + 32 * k) * 8));
+                    const int c = 2 * pcol;
+                    stg64(g0 + (prow * 32 + c) + (c >= cross ? hop : 0), v2.x, v2.y);
+                    prow += pdq; pcol += pdr;
+                    if (pcol >= H) { pcol -= H; ++prow; }
+                  }
+                }
+                __syncwarp();                                     // the next fit overwrites the block
               } else {
 #pragma unroll
                 for (int q4 = 0; q4 < 4; ++q4)
