@@ -714,7 +714,8 @@ tc_fwd_kernel(const __grid_constant__ CUtensorMap mapX, const __grid_constant__ 
               for (int cc = 0; cc < 4; ++cc) {
                 const int c = 4 * q4 + cc;
                 z[c] = c < T ? __uint_as_float(v[c]) + b4[cc] : -INFINITY;
-                if (z[c] > m) { m = z[c]; am = c; }
+                if (MODE == FWD_SCORE_MULTI) { if (z[c] > m) { m = z[c]; am = c; } }      // first arg-max
+                else m = fmaxf(m, z[c]);
               }
             } else {
 #pragma unroll

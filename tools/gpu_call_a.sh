@@ -25,3 +25,10 @@ timeout 900 ncu --set full --clock-control none --import-source on -k "regex:tc_
 ncu -i gpurun_out/a_full_cfg3.ncu-rep --page raw --csv > gpurun_out/a_full_cfg3.csv 2>/dev/null
 rm -f gpurun_out/a_full_cfg3.ncu-rep
 ls -la gpurun_out | tail -30
+# config 4: one full-width multinomial forward + gradient launch
+timeout 1200 ncu --set full --clock-control none --import-source on -k "regex:tc_fwd_kernel|tc_grad2_kernel" -s 30 -c 2 \
+  -o gpurun_out/a_full_cfg4 -f python bench.py --config 4 --steps 1 --warmup 3 --no-e2e --no-cpu-baseline > gpurun_out/a_ncu4.log 2>&1; echo "ncu full cfg4 rc=$?"
+ncu -i gpurun_out/a_full_cfg4.ncu-rep --page raw --csv > gpurun_out/a_full_cfg4.csv 2>/dev/null
+ncu -i gpurun_out/a_full_cfg4.ncu-rep --page source --csv --kernel-name regex:tc_fwd_kernel > gpurun_out/a_src_fwd_cfg4.csv 2>/dev/null
+rm -f gpurun_out/a_full_cfg4.ncu-rep
+ls -la gpurun_out | grep " a_"
