@@ -290,6 +290,49 @@ def parity_report_ridge(full: dict, golden_path: str):
             "best_of_checked_equal": bool(int(np.argmax(r2.mean(axis=1))) == int(np.argmax(z["r2"].mean(axis=1))))}
 
 
+GOLDEN_CFG4 = os.path.join(ROOT, "tests", "golden", "cfg4_full.npz")
+
+
+def parity_report_multi(out: dict, X, fold, cv: int, golden_path: str, pos=None, eps: float = 2e-5):
+    """Config 4 against tests/golden/cfg4_full.npz: scikit-learn (float64) at full size on 8 of the 512 sampled
+    candidates x 5 folds (tests/golden/make_cfg4_full.py).  `pos` = where those candidates sit in `out`
+    (default: their index in the 512-candidate draw order).  A count may differ only on rows whose two largest
+    decision values are within eps of each other (an arg-max tie at fp32 accuracy)."""
+    if not os.path.exists(golden_path):
+        return {"unavailable": f"{os.path.relpath(golden_path, ROOT)} missing"}
+    z = np.load(golden_path)
+    pos = [int(i) for i in z["index"]] if pos is None else list(pos)
+    if max(pos) >= out["n_iter"].shape[0]:
+        return {"unavailable": "golden file is for another candidate list"}
+    m = len(pos)
+    same_iter = out["n_iter"][pos] == z["n_iter"]
+    coef_err = np.zeros((m, cv)); icpt_err = np.zeros((m, cv))
+    diffs = np.zeros((m, cv), np.int64); ties = np.zeros((m, cv), np.int64)
+    for k in range(cv):
+        Xk = X[fold == k].astype(np.float64)
+        for i in range(m):
+            W, b = z["coef"][i, k], z["intercept"][i, k]
+            Z = Xk @ W.T + b[None, :]                                       # scikit-learn's decision values
+            top2 = np.partition(Z, Z.shape[1] - 2, axis=1)[:, -2:]
+            ties[i, k] = int(((top2[:, 1] - top2[:, 0]) < eps * max(1.0, float(np.abs(Z).max()))).sum())
+            coef_err[i, k] = np.abs(out["coef"][pos[i], k] - W).max() / np.abs(W).max()
+            icpt_err[i, k] = np.abs(out["intercept"][pos[i], k] - b).max() / max(1.0, float(np.abs(W).max()))
+        diffs[:, k] = np.abs(out["correct"][pos][:, k] - z["correct"][:, k])
+    return {"against": os.path.relpath(golden_path, ROOT) + " (scikit-learn float64, full size, 8 of the 512 candidates)",
+            "fits_checked": int(same_iter.size), "n_iter_equal": int(same_iter.sum()),
+            "nfev_equal": int((out["nfev"][pos] == z["nfev"]).sum()),
+            "max_coef_relerr": float(coef_err[same_iter].max()) if same_iter.any() else None,
+            "max_intercept_err": float(icpt_err[same_iter].max()) if same_iter.any() else None,
+            "count_diffs": int((diffs > 0).sum()), "max_count_diff": int(diffs.max()),
+            "count_diffs_beyond_ties": int((diffs > ties).sum()),
+            "rows_excused_as_ties": int(np.minimum(diffs, ties).sum()), "rows_near_ties": int(ties.sum()),
+            "n_test_equal": bool((out["n_test"][pos] == z["n_test"]).all()),
+            "max_mean_score_diff": float(np.abs((out["correct"][pos] / out["n_test"][pos]).mean(axis=1)
+                                                - (z["correct"] / z["n_test"]).mean(axis=1)).max()),
+            "best_of_checked_equal": bool(int(np.argmax((out["correct"][pos] / out["n_test"][pos]).mean(axis=1)))
+                                          == int(np.argmax((z["correct"] / z["n_test"]).mean(axis=1))))}
+
+
 def golden_nfev_sum():
     """Function evaluations of all 320 fits of config 2 as scikit-learn makes them (for roofline.frac_step)."""
     if not os.path.exists(GOLDEN_CFG2):
@@ -934,6 +977,8 @@ def run_b200(a):
             line["config"]["mean_n_iter"] = float(np.mean(full["n_iter"]))
             if a.config == "2" and a.full_size and world == 1:
                 line["parity"] = parity_report(full, X, y, fold, cv, GOLDEN_CFG2)
+            if a.config == "4" and a.full_size and world == 1:
+                line["parity"] = parity_report_multi(full, X, fold, cv, GOLDEN_CFG4)
         if a.config == "3" and a.full_size and world == 1:
             line["parity"] = parity_report_ridge(full, GOLDEN_CFG3)
         line["e2e"] = e2e if e2e else {"value": None, "unit": UNIT, "h2d_bytes_per_step": None, "d2h_bytes_per_step": None,

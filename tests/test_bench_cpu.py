@@ -71,3 +71,48 @@ def test_committed_golden_file_is_the_headline_config():
     assert z["coef"].shape == (64, 5, 256) and z["n_iter"].shape == (64, 5) and int(z["best_index"]) == 21
     assert meta["C"] == [c["C"] for c in bench.candidates_of(cfg, 64)]
     assert bench.golden_nfev_sum() == int(z["nfev"].sum())
+
+
+def test_parity_report_multi_counts_what_differs(tmp_path):
+    """The config-4 record: a count may differ only on rows whose two largest decision values tie; anything else is
+    reported as beyond ties; the picked candidates are looked up by their index in the full candidate list."""
+    rng = np.random.default_rng(1)
+    n, d, T, cv, pick = 600, 5, 4, 2, [1, 3]
+    X = rng.standard_normal((n, d)).astype(np.float32)
+    y = rng.integers(0, T, n).astype(np.int32)
+    fold = (np.arange(n) % cv).astype(np.int8)
+    coef = rng.standard_normal((len(pick), cv, T, d)); icpt = rng.standard_normal((len(pick), cv, T)) * 0.1
+    correct = np.zeros((len(pick), cv), np.int64); n_test = np.zeros((len(pick), cv), np.int64)
+    for i in range(len(pick)):
+        for k in range(cv):
+            rows = fold == k
+            Z = X[rows].astype(np.float64) @ coef[i, k].T + icpt[i, k]
+            correct[i, k] = (Z.argmax(axis=1) == y[rows]).sum(); n_test[i, k] = rows.sum()
+    golden = tmp_path / "g4.npz"
+    np.savez(golden, index=np.array(pick), coef=coef, intercept=icpt, n_iter=np.full((2, cv), 6), nfev=np.full((2, cv), 7),
+             correct=correct, n_test=n_test, meta=np.array(json.dumps({"index": pick})))
+    n_all = 5                                                   # the sweep holds 5 candidates; the golden ones are 1 and 3
+    out = dict(coef=np.zeros((n_all, cv, T, d), np.float32), intercept=np.zeros((n_all, cv, T), np.float32),
+               n_iter=np.full((n_all, cv), 6), nfev=np.full((n_all, cv), 7), correct=np.zeros((n_all, cv), np.int64),
+               n_test=np.zeros((n_all, cv), np.int64))
+    out["coef"][pick] = coef; out["intercept"][pick] = icpt; out["correct"][pick] = correct; out["n_test"][pick] = n_test
+    rep = bench.parity_report_multi(out, X, fold, cv, str(golden))
+    assert rep["fits_checked"] == 4 and rep["n_iter_equal"] == 4 and rep["nfev_equal"] == 4
+    assert rep["count_diffs"] == 0 and rep["n_test_equal"] and rep["max_coef_relerr"] < 1e-6 and rep["best_of_checked_equal"]
+    out["correct"][3, 1] -= 3; out["n_iter"][1, 0] = 9
+    rep = bench.parity_report_multi(out, X, fold, cv, str(golden))
+    assert rep["count_diffs"] == 1 and rep["max_count_diff"] == 3 and rep["count_diffs_beyond_ties"] == 1 and rep["n_iter_equal"] == 3
+    sub = {k: v[pick] for k, v in out.items()}                  # the GPU test sweeps only the picked candidates
+    assert bench.parity_report_multi(sub, X, fold, cv, str(golden), pos=range(2))["count_diffs"] == 1
+    assert "unavailable" in bench.parity_report_multi(out, X, fold, cv, str(tmp_path / "missing.npz"))
+
+
+def test_committed_config4_golden_file_is_the_bench_config():
+    z = np.load(bench.GOLDEN_CFG4)
+    meta = json.loads(str(z["meta"]))
+    cfg = bench.CONFIGS["4"]
+    assert (meta["kind"], meta["n"], meta["d"], meta["cv"], meta["seed"]) == (cfg["kind"], cfg["n"], cfg["d"], cfg["cv"], cfg["seed"])
+    cands = bench.candidates_of(cfg, cfg["n_cand"])
+    assert [cands[i] for i in z["index"]] == meta["params"] and meta["n_candidates"] == cfg["n_cand"]
+    assert z["coef"].shape == (8, 5, 10, 512) and z["n_iter"].shape == (8, 5) and (z["n_test"].sum(axis=1) == cfg["n"]).all()
+    assert (z["nfev"] >= z["n_iter"]).all() and (z["intercept"][[not p["fit_intercept"] for p in meta["params"]]] == 0).all()

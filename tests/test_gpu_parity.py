@@ -784,3 +784,32 @@ def test_config3_full_size_vs_cached_oracle(solver, golden_dir):
     np.testing.assert_allclose(r2, z["r2"], atol=RTOL)
     assert int(np.argmax(r2.mean(axis=1))) == int(np.argmax(z["r2"].mean(axis=1)))
     print(f"cfg3 full-size parity: 40 fits, max coef rel. err {worst:.2e}, max R2 diff {np.abs(r2 - z['r2']).max():.2e}")
+
+
+def test_config4_full_size_vs_cached_oracle(solver, golden_dir):
+    """BASELINE.json config 4 at FULL size (10-class multinomial, 2M x 512, StratifiedKFold 5), 8 of the 512 sampled
+    candidates (C, tol, fit_intercept as the sampler drew them), against scikit-learn on float64
+    (tests/golden/make_cfg4_full.py): n_iter / nfev, coefficients and intercepts within 1e-4, per-fold correct counts
+    exact except rows whose two largest decision values are within 2e-5 of each other."""
+    import bench
+    path = os.path.join(golden_dir, "cfg4_full.npz")
+    z = np.load(path)
+    meta = json.loads(str(z["meta"]))
+    X, y = make_dataset(meta["kind"], meta["n"], meta["d"], seed=meta["seed"])
+    cv, params = meta["cv"], meta["params"]
+    fold = folds.stratified_labels(y, cv)
+    ds = solver.upload_dataset(X, y, classifier=True)
+    m = len(params)
+    out = solver.logreg_sweep(ds, fold, cv, [p["C"] for p in params], [p["tol"] for p in params],
+                              [p["fit_intercept"] for p in params], [100] * m)
+    rep = bench.parity_report_multi(out, X, fold, cv, path, pos=range(m))
+    print("cfg4 full-size parity:", json.dumps(rep))
+    gout = os.path.join(os.path.dirname(golden_dir), "..", "gpurun_out")
+    if os.path.isdir(gout):
+        json.dump(rep, open(os.path.join(gout, "parity_cfg4_full.json"), "w"))
+    assert rep["n_test_equal"] and (out["status"] == 0).all()
+    assert rep["fits_checked"] == m * cv
+    assert rep["n_iter_equal"] >= 0.95 * rep["fits_checked"], rep       # a fit one iterate apart is counted, not hidden
+    assert rep["max_coef_relerr"] <= RTOL and rep["max_intercept_err"] <= RTOL, rep
+    assert rep["count_diffs_beyond_ties"] == 0, rep
+    assert rep["max_mean_score_diff"] <= RTOL, rep
