@@ -116,3 +116,35 @@ def test_committed_config4_golden_file_is_the_bench_config():
     assert [cands[i] for i in z["index"]] == meta["params"] and meta["n_candidates"] == cfg["n_cand"]
     assert z["coef"].shape == (8, 5, 10, 512) and z["n_iter"].shape == (8, 5) and (z["n_test"].sum(axis=1) == cfg["n"]).all()
     assert (z["nfev"] >= z["n_iter"]).all() and (z["intercept"][[not p["fit_intercept"] for p in meta["params"]]] == 0).all()
+
+
+def test_parity_report_cached_ties(tmp_path):
+    """The config-5 record: the cache carries the near-tie row counts, so no X is needed on the host."""
+    rng = np.random.default_rng(2)
+    m, cv, d, pick = 2, 3, 7, [0, 4]
+    coef = rng.standard_normal((m, cv, d)); icpt = rng.standard_normal((m, cv))
+    correct = rng.integers(100, 200, (m, cv)); n_test = np.full((m, cv), 250); ties = np.array([[0, 2, 0], [1, 0, 0]])
+    golden = tmp_path / "g5.npz"
+    np.savez(golden, index=np.array(pick), coef=coef, intercept=icpt, n_iter=np.full((m, cv), 5), nfev=np.full((m, cv), 6),
+             correct=correct, n_test=n_test, ties=ties)
+    out = dict(coef=np.zeros((6, cv, 1, d), np.float32), intercept=np.zeros((6, cv, 1), np.float32), n_iter=np.full((6, cv), 5),
+               nfev=np.full((6, cv), 6), correct=np.zeros((6, cv), np.int64), n_test=np.full((6, cv), 250))
+    out["coef"][pick] = coef[:, :, None, :]; out["intercept"][pick] = icpt[:, :, None]; out["correct"][pick] = correct
+    rep = bench.parity_report_cached_ties(out, str(golden))
+    assert rep["fits_checked"] == 6 and rep["n_iter_equal"] == 6 and rep["count_diffs"] == 0 and rep["max_coef_relerr"] < 1e-6
+    out["correct"][0, 1] += 2          # two rows, two near ties there: excused, but counted
+    out["correct"][4, 2] -= 1          # one row where the oracle saw no tie: beyond ties
+    rep = bench.parity_report_cached_ties(out, str(golden))
+    assert rep["count_diffs"] == 2 and rep["rows_excused_as_ties"] == 2 and rep["count_diffs_beyond_ties"] == 1
+    assert "unavailable" in bench.parity_report_cached_ties({k: v[:3] for k, v in out.items()}, str(golden))
+
+
+def test_committed_config5_golden_file_is_the_bench_config():
+    z = np.load(bench.GOLDEN_CFG5)
+    meta = json.loads(str(z["meta"]))
+    cfg = bench.CONFIGS["5"]
+    assert (meta["kind"], meta["n"], meta["d"], meta["cv"], meta["seed"]) == (cfg["kind"], cfg["n"], cfg["d"], cfg["cv"], cfg["seed"])
+    cands = bench.candidates_of(cfg, cfg["n_cand"])
+    assert [cands[i]["C"] for i in z["index"]] == meta["C"] and meta["n_candidates"] == cfg["n_cand"]
+    assert z["coef"].shape == (8, 10, 512) and z["ties"].shape == (8, 10) and (z["n_test"].sum(axis=1) == cfg["n"]).all()
+    assert meta["pin"]["n_iter_nfev_equal"] and meta["pin"]["max_coef_reldiff"] < 1e-9 and (z["status"] == 0).all()
