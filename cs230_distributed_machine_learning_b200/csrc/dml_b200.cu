@@ -132,15 +132,19 @@ static inline int64_t cdiv(int64_t a, int64_t b) { return (a + b - 1) / b; }
 static inline int64_t rup(int64_t a, int64_t b) { return cdiv(a, b) * b; }
 static inline bool aligned16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15) == 0; }
 
-// timing helpers
+// timing helpers.  A timing call that fails must neither fail the sweep nor leave its error behind for the
+// caller's next CUDA call to trip over (the runtime keeps the last error per host thread): EVC clears it and
+// says so on stderr.
+#define EVC(call) do { cudaError_t e_ = (call); if (e_ != cudaSuccess) { cudaGetLastError(); \
+  fprintf(stderr, "[dml_b200] timing call %s failed: %s (%s:%d)\n", #call, cudaGetErrorString(e_), __FILE__, __LINE__); } } while (0)
 static void tick(dml_ctx* ctx) {
   if (ctx->ev_used + 2 > ctx->ev.size()) return;
-  cudaEventRecord(ctx->ev[ctx->ev_used], ctx->stream);
+  EVC(cudaEventRecord(ctx->ev[ctx->ev_used], ctx->stream));
 }
 static void tock(dml_ctx* ctx, int launches) {
   ctx->contraction_launches += launches;
   if (ctx->ev_used + 2 > ctx->ev.size()) return;
-  cudaEventRecord(ctx->ev[ctx->ev_used + 1], ctx->stream);
+  EVC(cudaEventRecord(ctx->ev[ctx->ev_used + 1], ctx->stream));
   ctx->ev_used += 2;
 }
 static void timing_begin(dml_ctx* ctx) {
@@ -149,34 +153,42 @@ static void timing_begin(dml_ctx* ctx) {
   ctx->total_ms = ctx->contraction_ms = 0.f;
   ctx->first_pairs = 0; ctx->first_ms = 0.f; ctx->first_cols = 0;
   ctx->ev_comm_used = 0; ctx->comm_ms = 0.f; ctx->comm_calls = 0; ctx->comm_bytes = 0.0;
-  cudaEventRecord(ctx->ev_total[0], ctx->stream);
+  EVC(cudaEventRecord(ctx->ev_total[0], ctx->stream));
 }
 static void timing_end(dml_ctx* ctx) {
-  cudaEventRecord(ctx->ev_total[1], ctx->stream);
-  cudaEventSynchronize(ctx->ev_total[1]);
-  cudaEventElapsedTime(&ctx->total_ms, ctx->ev_total[0], ctx->ev_total[1]);
+  EVC(cudaEventRecord(ctx->ev_total[1], ctx->stream));
+  EVC(cudaEventSynchronize(ctx->ev_total[1]));
+  EVC(cudaEventElapsedTime(&ctx->total_ms, ctx->ev_total[0], ctx->ev_total[1]));
   float acc = 0.f;
   for (size_t i = 0; i + 1 < ctx->ev_used; i += 2) {
     float ms = 0.f;
-    if (cudaEventElapsedTime(&ms, ctx->ev[i], ctx->ev[i + 1]) == cudaSuccess) {
+    const cudaError_t e = cudaEventElapsedTime(&ms, ctx->ev[i], ctx->ev[i + 1]);
+    if (e == cudaSuccess) {
       acc += ms;
       if (i / 2 < ctx->first_pairs) ctx->first_ms += ms;
+    } else {
+      cudaGetLastError();
+      fprintf(stderr, "[dml_b200] elapsed time of event pair %zu of %zu failed: %s\n", i / 2, ctx->ev_used / 2, cudaGetErrorString(e));
     }
   }
   ctx->contraction_ms = acc;
   for (size_t i = 0; i + 1 < ctx->ev_comm_used; i += 2) {
     float ms = 0.f;
     if (cudaEventElapsedTime(&ms, ctx->ev_comm[i], ctx->ev_comm[i + 1]) == cudaSuccess) ctx->comm_ms += ms;
+    else cudaGetLastError();
   }
+  // nothing of this call may stay behind in the thread's error state
+  const cudaError_t stray = cudaGetLastError();
+  if (stray != cudaSuccess) fprintf(stderr, "[dml_b200] a CUDA error was pending at the end of the call: %s\n", cudaGetErrorString(stray));
 }
 
 static int allreduce(dml_ctx* ctx, void* buf, size_t count, int dtype) {
   if (!ctx->comm) return DML_OK;
   const bool timed = ctx->ev_comm_used + 2 <= ctx->ev_comm.size();
-  if (timed) cudaEventRecord(ctx->ev_comm[ctx->ev_comm_used], ctx->stream);
+  if (timed) EVC(cudaEventRecord(ctx->ev_comm[ctx->ev_comm_used], ctx->stream));
   const int rc = g_nccl.AllReduce(buf, buf, count, dtype, kNcclSum, ctx->comm, ctx->stream);
   if (rc != 0) return fail(ctx, DML_ERR_NCCL, "ncclAllReduce failed: %s", g_nccl.GetErrorString ? g_nccl.GetErrorString(rc) : "?");
-  if (timed) { cudaEventRecord(ctx->ev_comm[ctx->ev_comm_used + 1], ctx->stream); ctx->ev_comm_used += 2; }
+  if (timed) { EVC(cudaEventRecord(ctx->ev_comm[ctx->ev_comm_used + 1], ctx->stream)); ctx->ev_comm_used += 2; }
   ctx->comm_calls += 1; ctx->comm_bytes += (double)count * 8.0;   // every reduced type here is 8 bytes wide
   return DML_OK;
 }

@@ -27,6 +27,7 @@ import logging
 import os
 import pickle
 import threading
+import weakref
 import time
 import warnings
 
@@ -355,14 +356,18 @@ class GpuExecutor:
             if id(X) in _PINNED:
                 return
             rt = torch.cuda.cudart()
-            rc = rt.cudaHostRegister(X.ctypes.data, X.nbytes, 0)
+            ptr = X.ctypes.data
+            rc = rt.cudaHostRegister(ptr, X.nbytes, 0)
             if int(rc) == 0:
-                _PINNED.add(id(X))
+                # The registration must end before the memory does: a freed array's address range is handed out
+                # again by the allocator, and a host buffer that overlaps a stale registration makes the next
+                # cudaMemcpy on it fail with "invalid argument".  numpy runs weak-reference callbacks at the start
+                # of an array's deallocation, before its buffer is released.
+                _PINNED[id(X)] = ptr
+                fin = weakref.finalize(X, _unpin, id(X), ptr)
+                fin.atexit = False      # at interpreter exit the driver releases everything itself
             else:                       # e.g. already registered by someone else: not an error for us; do not
-                try:                    # leave it pending for the next cudaGetLastError of this thread
-                    rt.cudaGetLastError()
-                except Exception:
-                    pass
+                _clear_cuda_error()     # leave it pending for the next CUDA call torch makes on this thread
 
     def row_labels(self, dataset_id: str, classifier: bool, cv: int, n: int, y_host, test_size=None, random_state=None,
                    shard: tuple[int, int] | None = None, solver=None):
@@ -536,8 +541,42 @@ class GpuExecutor:
         return results
 
 
-_PINNED: set[int] = set()           # id() of registered arrays that are page-locked, process-wide
-_PIN_LOCK = threading.Lock()
+_PINNED: dict[int, int] = {}        # id() of registered arrays that are page-locked, process-wide -> base address
+_PIN_LOCK = threading.RLock()       # re-entrant: a finalizer may run inside _pin when an allocation triggers a collection
+
+
+def _unpin(key: int, ptr: int) -> None:
+    """End the page-lock of an array that is being deallocated (weakref.finalize callback of GpuExecutor._pin)."""
+    with _PIN_LOCK:
+        if _PINNED.get(key) != ptr:
+            return
+        del _PINNED[key]
+    try:
+        import torch
+        rt = torch.cuda.cudart()
+        if int(rt.cudaHostUnregister(ptr)) != 0:
+            _clear_cuda_error()
+    except Exception:                   # noqa: BLE001 -- never raise from a finalizer
+        pass
+
+
+_CUDART = None
+
+
+def _clear_cuda_error() -> None:
+    """cudaGetLastError() of the CUDA runtime torch uses (torch.cuda.cudart() does not export it; the library's own
+    runtime is a separate, statically linked instance with its own per-thread error state)."""
+    global _CUDART
+    try:
+        if _CUDART is None:
+            import ctypes
+            with open("/proc/self/maps") as f:
+                paths = {ln.split()[-1] for ln in f if "libcudart" in ln}
+            _CUDART = [ctypes.CDLL(p) for p in sorted(paths)]
+        for lib in _CUDART:
+            lib.cudaGetLastError()
+    except Exception:                   # noqa: BLE001
+        pass
 _EXECUTORS: dict[int, GpuExecutor] = {}
 _EXEC_LOCK = threading.Lock()
 
@@ -724,6 +763,7 @@ class Worker(threading.Thread):
                        "status": "completed", "result": result}
         except Exception as e:
             err = str(e)
+            log.exception("subtask %s of job %s failed", task.get("subtask_id"), task.get("job_id"))
             if "candidates" in task:
                 result = [{"subtask_id": c["subtask_id"], "status": "failed", "error": err} for c in task["candidates"]]
                 message = {"subtask_id": task["subtask_id"], "job_id": task["job_id"],

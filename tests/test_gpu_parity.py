@@ -728,6 +728,30 @@ def test_reregistered_dataset_name_is_uploaded_again():
         m.close()
 
 
+def test_page_lock_of_a_registered_array_ends_with_the_array():
+    """The executor page-locks a registered float32 dataset in place (cudaHostRegister).  When the array is freed
+    (its name re-registered, the process moving on) the registration has to go with it: the allocator hands the
+    address range out again, and a host buffer overlapping a stale registration fails the next cudaMemcpy with
+    "invalid argument"."""
+    import gc
+    from cs230_distributed_machine_learning_b200 import worker as W
+    X = np.random.default_rng(5).standard_normal((300_000, 64), dtype=np.float32)        # 77 MB: its own mmap region
+    key, ptr = id(X), X.ctypes.data
+    W.GpuExecutor._pin(None, X)                              # (uses no executor state)
+    assert W._PINNED.get(key) == ptr
+    del X
+    gc.collect()
+    assert key not in W._PINNED
+    Y = np.empty((300_000, 64), dtype=np.float32)            # very likely the same address range
+    W.GpuExecutor._pin(None, Y)
+    assert id(Y) in W._PINNED                                # would fail on a range that still overlaps a registration
+    t = torch.ones(300_000, 64, device="cuda")
+    Y[:] = t.cpu().numpy()                                    # D2H into fresh host memory
+    torch.from_numpy(Y).cuda()                                # and H2D from it
+    torch.cuda.synchronize()
+    assert float(Y.sum()) == 300_000 * 64
+
+
 def test_scoring_and_train_scores_on_the_b200_executor():
     """cv_params.scoring / return_train_score (core.py:123-130) on float32 data: the scores come from the sums of
     the GPU scoring pass (test rows) and of one more scoring call over all rows (training rows = all - test)."""
@@ -752,7 +776,8 @@ def test_scoring_and_train_scores_on_the_b200_executor():
             r = m.train(gs, name, wait_for_completion=True)
             assert r["job_status"] == "completed", r
             jr = r["job_result"]
-            assert all(res["executor"] == "b200" for res in jr["results"]), [res.get("executor_reason") for res in jr["results"]]
+            assert all(res.get("executor") == "b200" for res in jr["results"]), \
+                [(res.get("executor"), res.get("executor_reason"), res.get("error")) for res in jr["results"]]
             want = gs.fit(Xh.astype(np.float64), yh).cv_results_
             for key in ("mean_test_score", "mean_train_score", "split1_train_score", "std_train_score"):
                 np.testing.assert_allclose(jr["cv_results_"][key], want[key], rtol=2 * RTOL, atol=2 * RTOL, err_msg=f"{name} {scoring} {key}")
