@@ -622,3 +622,16 @@ def test_class_weight_table_equals_sklearn_compute_class_weight():
     assert worker.class_weight_table([{}, {}], np.array([0, 1]), y % 2, fold, None, 5) is None
     with pytest.raises(ValueError):
         worker.class_weight_table([{"class_weight": {"7": 1.0}}], np.array([0, 1, 2]), y, fold, None, 5)
+
+
+def test_unpin_bookkeeping_without_a_gpu():
+    """worker._unpin is a finalizer: it must drop the entry it was made for, leave a newer entry of a recycled id()
+    alone, and never raise (here: no CUDA runtime to call)."""
+    from cs230_distributed_machine_learning_b200 import worker as W
+    W._PINNED[123456789] = 4096
+    W._unpin(123456789, 8192)                 # the id was recycled by another array at another address: not ours
+    assert W._PINNED.get(123456789) == 4096
+    W._unpin(123456789, 4096)
+    assert 123456789 not in W._PINNED
+    W._unpin(123456789, 4096)                 # a second call is a no-op
+    W._clear_cuda_error()                     # nothing loaded here: must not raise
