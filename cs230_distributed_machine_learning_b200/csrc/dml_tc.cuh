@@ -328,6 +328,7 @@ struct FwdSmem {
   static constexpr int kStage = kA + 2 * kB;
   // per column: bias; per label value: 16-bit held-column masks, one per 16-column chunk
   // multinomial epilogue: fp64 running sums of every epilogue warp, [warp][fit of the warp][17] (16 class columns + the loss)
+  static_assert(kFwdEpiGroups == 4, "kMultiAcc / kMultiStage below are laid out for 16 epilogue warps");
   static constexpr int kMultiAcc = 16 * (32 / 4) * 17 * 8;
   // multinomial epilogue: [32 rows][T <= 16] fp32 residuals of one fit per epilogue warp, turned row-major -> line-major before they are stored
   static constexpr int kMultiStage = 16 * 32 * 16 * 4;
