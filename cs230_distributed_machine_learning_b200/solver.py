@@ -7,6 +7,7 @@ PyTorch is used for device memory, streams and the NCCL bootstrap only.  One
 from __future__ import annotations
 
 import ctypes as C
+from collections import OrderedDict
 from dataclasses import dataclass
 
 import numpy as np
@@ -47,7 +48,9 @@ class SweepSolver:
         self.lib = self.ctx.lib
         self.h2d_bytes = 0
         self.d2h_bytes = 0
-        self._class_cache: dict[tuple, tuple] = {}
+        # label encodings of the datasets uploaded last, page-locked; bounded: an entry keeps its y alive (so that
+        # id(y) cannot be recycled under the key) and its encoding pinned
+        self._class_cache: "OrderedDict[tuple, tuple]" = OrderedDict()
         self._param_buf = torch.empty(1 << 16, dtype=torch.uint8, pin_memory=True)
 
     # ---- plumbing -------------------------------------------------------------------
@@ -142,6 +145,10 @@ class SweepSolver:
             else:
                 classes, enc = None, torch.from_numpy(np.ascontiguousarray(y, dtype=np.float32)).pin_memory()
             self._class_cache[key] = (classes, enc, y)
+            while len(self._class_cache) > 16:
+                self._class_cache.popitem(last=False)
+        else:
+            self._class_cache.move_to_end(key)
         classes, enc, _ = self._class_cache[key]
         yd = self.to_device(enc)
         if classifier:
