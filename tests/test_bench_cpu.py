@@ -148,3 +148,13 @@ def test_committed_config5_golden_file_is_the_bench_config():
     assert [cands[i]["C"] for i in z["index"]] == meta["C"] and meta["n_candidates"] == cfg["n_cand"]
     assert z["coef"].shape == (8, 10, 512) and z["ties"].shape == (8, 10) and (z["n_test"].sum(axis=1) == cfg["n"]).all()
     assert meta["pin"]["n_iter_nfev_equal"] and meta["pin"]["max_coef_reldiff"] < 1e-9 and (z["status"] == 0).all()
+
+
+def test_committed_config3_golden_file_is_the_bench_config():
+    z = np.load(bench.GOLDEN_CFG3)
+    meta = json.loads(str(z["meta"]))
+    cfg = bench.CONFIGS["3"]
+    assert (meta["kind"], meta["n"], meta["d"], meta["cv"], meta["seed"]) == (cfg["kind"], cfg["n"], cfg["d"], cfg["cv"], cfg["seed"])
+    cands = bench.candidates_of(cfg, cfg["n_cand"])
+    assert [cands[i]["alpha"] for i in meta["alpha_index"]] == meta["alpha"]
+    assert z["coef"].shape == (8, 5, 512) and int(z["n_test"].sum()) == cfg["n"] and meta["sklearn_pin_coef_reldiff"] < 1e-9
